@@ -1,0 +1,144 @@
+/*
+ * scaldpc.h -- C ABI of libscaldpc.so, the B200-native (sm_100a) belief-propagation decoder library.
+ *
+ * This is the drop-in boundary for the decoder hot path of atneit/SCA-LDPC.  Every entry point states the
+ * reference interface it replaces (paths relative to the reference's simulate-with-python/ directory).
+ * Plain pointers and sizes only; no torch / pyo3 types.  All functions return 0 on success or a negative
+ * SCALDPC_ERR_* code; scaldpc_last_error() returns a human-readable description of the last failure on the
+ * calling thread.  The library never aborts the process (the reference panics, SURVEY.md 8b "Errors").
+ *
+ * There is NO CPU fallback anywhere behind this interface: every decode runs on the CUDA device given at
+ * create time, and creation fails if no such device exists.
+ *
+ * Threading: a handle may be used from several host threads (the reference releases the GIL and is called
+ * from a ThreadPoolExecutor, simulate/decode.py:247-262, simulate_rs/src/pydecoder.rs:49-55); calls on one
+ * handle are serialised internally.  The batched calls are the intended fast path.
+ */
+#ifndef SCALDPC_H
+#define SCALDPC_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- status codes ------------------------------------------------------------------------------------- */
+#define SCALDPC_OK 0
+#define SCALDPC_ERR_ARG (-1)        /* bad argument (NULL, negative size, unsupported alphabet) */
+#define SCALDPC_ERR_PROB_SUM (-2)   /* a prior row does not sum to 1 +- 0.001   (decoder.rs:683-684 assert) */
+#define SCALDPC_ERR_NO_MAX (-3)     /* a prior row is all-NaN                     (decoder.rs:680 expect) */
+#define SCALDPC_ERR_NO_CONFIG (-4)  /* a check has no valid configuration        (decoder.rs:618 assert) */
+#define SCALDPC_ERR_DEGREE (-5)     /* node degree exceeds the class's DV / DC   (decoder.rs:465-473 panic) */
+#define SCALDPC_ERR_STRUCTURE (-6)  /* H is not [H' | I]-shaped, BSUM % B != 0, BVARS != N-R
+                                       (decoder_special.rs:388-395, :513-522) */
+#define SCALDPC_ERR_RANGE (-7)      /* a check's sum leaves [-BSUM, BSUM]        (decoder_special.rs:546) */
+#define SCALDPC_ERR_CUDA (-8)       /* CUDA runtime failure (no device, out of memory, launch error) */
+#define SCALDPC_ERR_UNSUPPORTED (-9)
+
+const char *scaldpc_last_error(void);
+/* Library / build identification: "scaldpc <version> sm_100a". */
+const char *scaldpc_version(void);
+/* Number of CUDA devices visible, or a negative error. */
+int scaldpc_device_count(void);
+
+/* ======================================================================================================
+ * q-ary min-sum decoder
+ *   replaces  simulate_rs::Decoder<N,R,DV,DC,Q,B,i8>            (simulate_rs/src/decoder.rs:417-666)
+ *             simulate_rs::DecoderSpecial<N,R,BVARS,SW,DC,DV,B,..>(simulate_rs/src/decoder_special.rs:294-617)
+ *   as bound by the pyo3 classes of simulate_rs/src/pydecoder.rs:13-71 and :85-150.
+ * ==================================================================================================== */
+typedef struct scaldpc_qary scaldpc_qary;
+
+/* decode flags */
+#define SCALDPC_IN_LLR 0x1u       /* inputs are LLRs (skip into_llr); default: probabilities (pydecoder.rs:62) */
+#define SCALDPC_DEVICE_PTRS 0x2u  /* all data pointers are device pointers on the handle's device */
+#define SCALDPC_CN_EXACT 0x4u     /* check node in the reference's rounding order (bit-exact); default: fast
+                                     forward/backward (min,+) convolution, <= ~1e-5 from the reference */
+#define SCALDPC_CN_GENERIC 0x8u   /* force the runtime-shape kernels even where a specialised one exists */
+
+/*
+ * scaldpc_qary_create -- replaces `#[new] fn new(py_parity_check, iterations)` (pydecoder.rs:24-45, 96-117),
+ * i.e. Decoder::new (decoder.rs:494-553) when bsum == 0 and DecoderSpecial::new (decoder_special.rs:387-464)
+ * when bsum > 0.
+ *   H         dense row-major R x N int8 parity-check matrix; only the sign of an entry matters
+ *             (mult_in_gf, decoder.rs:164-172)
+ *   b         alphabet of the first N-R (special) / all N (generic) variables is [-b, b]
+ *   bsum      0: generic single-alphabet decoder.  >0: special decoder, H = [H' | I], the last R variables
+ *             have alphabet [-bsum, bsum]
+ *   dv, dc    capacity limits of the reference class (const generics DV, DC); pass 0 to accept any degree
+ *   max_iter  iterations; 0 and 1 both run one iteration (decoder.rs:575-663)
+ *   device    CUDA device ordinal
+ */
+int scaldpc_qary_create(const int8_t *H, int R, int N, int b, int bsum, int dv, int dc, int max_iter, int device,
+                        scaldpc_qary **out);
+void scaldpc_qary_destroy(scaldpc_qary *h);
+
+/* Shape queries (sizes a caller needs to allocate buffers). */
+int scaldpc_qary_info(const scaldpc_qary *h, int *R, int *N, int *bvars, int *q, int *qs, int *edges,
+                      int *max_iter);
+int scaldpc_qary_set_max_iter(scaldpc_qary *h, int max_iter);
+
+/*
+ * scaldpc_qary_decode -- replaces `fn min_sum(&self, py_channel_output[, py_channel_output_sum])`
+ * (pydecoder.rs:53-65, 125-145) = into_llr (decoder.rs:668-692) + min_sum (decoder.rs:560-666 /
+ * decoder_special.rs:471-617), batched over T independent trials.
+ *   in        T x BVARS x Q   float32, priors of the B-variables (probabilities, or LLRs with SCALDPC_IN_LLR)
+ *   in_sum    T x R x QS      float32, priors of the sum-variables (special decoder only, else NULL)
+ *   hard      T x N           int8 out: hard decisions, B-variables then sum-variables
+ *                             (decoder_special.rs:588, 607)
+ *   post      T x BVARS x Q   float32 out or NULL: final `sum` vectors (decoder.rs:638-642)
+ *   post_sum  T x R x QS      float32 out or NULL
+ *   status    T               int32 out or NULL: per-trial 0 / SCALDPC_ERR_PROB_SUM / _NO_MAX / _NO_CONFIG
+ *   stream    cudaStream_t (as void*), NULL = default stream.  With SCALDPC_DEVICE_PTRS the call is
+ *             asynchronous on `stream`; with host pointers it returns after the results are in `hard`.
+ * Returns 0, or the most severe per-trial error (outputs of failed trials are unspecified).
+ */
+int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in_sum, int8_t *hard, float *post,
+                        float *post_sum, int32_t *status, unsigned flags, void *stream);
+
+/* Kernels launched by this handle so far (for bench.py's "gpu_launches") and device time is NOT tracked
+ * here -- callers time with CUDA events on `stream`. */
+long long scaldpc_qary_launch_count(const scaldpc_qary *h);
+
+/*
+ * Per-kernel timing probe used by bench.py's roofline line: runs `reps` back-to-back launches of ONE kernel
+ * of the decode pipeline on the state left behind by the previous decode of `T` trials and returns the
+ * average duration in milliseconds measured with CUDA events on `stream`.
+ *   which  0 = check-node kernel (middle iteration), 1 = variable-node kernel (middle iteration)
+ */
+int scaldpc_qary_time_kernel(scaldpc_qary *h, int which, int T, unsigned flags, int reps, void *stream,
+                             float *avg_ms);
+
+/* ======================================================================================================
+ * binary soft BP (product-sum, flooding, syndrome-match early stop)
+ *   replaces  ldpc.bp_decoder(H, max_iter=, bp_method="product_sum", channel_probs=) and .decode(vec)
+ *   third-party PyPI package ldpc==0.1.3 (requirements.txt:8); call sites simulate/hqc.py:694-708 and
+ *   simulate/decode.py:155-171.
+ * ==================================================================================================== */
+typedef struct scaldpc_bp scaldpc_bp;
+
+/* CSR parity-check matrix: row_ptr (m+1), col (row_ptr[m]) ascending within a row. */
+int scaldpc_bp_create(int m, int n, const int32_t *row_ptr, const int32_t *col, int max_iter, int device,
+                      scaldpc_bp **out);
+void scaldpc_bp_destroy(scaldpc_bp *h);
+
+#define SCALDPC_BP_PROBS_PER_TRIAL 0x10u /* channel_probs is T x n instead of n */
+#define SCALDPC_BP_NO_EARLY_STOP 0x20u   /* run max_iter iterations regardless of convergence */
+/*
+ *   synd           T x m   uint8 syndromes
+ *   channel_probs  n (or T x n) float64 prior error probabilities           (hqc.py:684-690)
+ *   decoding       T x n   uint8 out: estimated error pattern
+ *   llr            T x n   float32 out or NULL: log(p0/p1) posteriors ("log_prob_ratios")
+ *   iters          T       int32 out or NULL: iterations run per trial ("iter")
+ *   converged      T       int32 out or NULL                              ("converge")
+ */
+int scaldpc_bp_decode(scaldpc_bp *h, int T, const uint8_t *synd, const double *channel_probs, uint8_t *decoding,
+                      float *llr, int32_t *iters, int32_t *converged, unsigned flags, void *stream);
+long long scaldpc_bp_launch_count(const scaldpc_bp *h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SCALDPC_H */

@@ -1,0 +1,486 @@
+// libscaldpc -- q-ary min-sum decoder: graph build, workspace, decode pipeline and the C ABI
+// (include/scaldpc.h).  Replaces the reference's Rust decoder core behind the same boundary
+// (simulate_rs/src/pydecoder.rs, decoder.rs, decoder_special.rs).  No CPU compute path exists here.
+#include <algorithm>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <vector>
+
+#include "common.h"
+#include "qary_graph.h"
+#include "qary_kernels.cuh"
+
+namespace scaldpc {
+
+std::string &last_error()
+{
+    static thread_local std::string s;
+    return s;
+}
+
+int fail(int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    last_error() = buf;
+    return code;
+}
+
+}  // namespace scaldpc
+
+using namespace scaldpc;
+
+struct scaldpc_qary {
+    int R = 0, N = 0, bvars = 0, B = 0, BSUM = 0, Q = 0, QS = 0, E = 0;
+    int max_iter = 1, device = 0;
+    int S = 0, SL = 0, SLS = 0;
+    int lmax = 0;      // max row degree
+    int wmax = 0;      // max DP table width over the checks
+    int fast_sw = 0;   // >0: every row is SW B-variables + 1 sum-variable with BSUM == SW*B and a template exists
+    // device graph
+    int *d_row_ptr = nullptr, *d_col = nullptr, *d_edge_off = nullptr, *d_col_ptr = nullptr;
+    int8_t *d_sign = nullptr;
+    int2 *d_csc = nullptr;
+    // workspace (grown on demand)
+    int cap_tiles = 0;
+    bool cap_post = false;
+    float *d_msg = nullptr, *d_llr = nullptr, *d_llr_sum = nullptr, *d_post = nullptr, *d_post_sum = nullptr;
+    int8_t *d_hard_t = nullptr;
+    int *d_status = nullptr;
+    // staging for host-pointer calls
+    size_t cap_stage_T = 0;
+    float *d_in = nullptr, *d_in_sum = nullptr, *d_opost = nullptr, *d_opost_sum = nullptr;
+    int8_t *d_ohard = nullptr;
+    std::mutex mu;
+    long long launches = 0;
+};
+
+namespace {
+
+template <typename T>
+int upload(T **dst, const std::vector<T> &src)
+{
+    SCALDPC_CUDA(cudaMalloc((void **)dst, std::max<size_t>(1, src.size()) * sizeof(T)));
+    if (!src.empty()) SCALDPC_CUDA(cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+void free_workspace(scaldpc_qary *h)
+{
+    cudaFree(h->d_msg);
+    cudaFree(h->d_llr);
+    cudaFree(h->d_llr_sum);
+    cudaFree(h->d_post);
+    cudaFree(h->d_post_sum);
+    cudaFree(h->d_hard_t);
+    cudaFree(h->d_status);
+    h->d_msg = h->d_llr = h->d_llr_sum = h->d_post = h->d_post_sum = nullptr;
+    h->d_hard_t = nullptr;
+    h->d_status = nullptr;
+    h->cap_tiles = 0;
+    h->cap_post = false;
+}
+
+void free_stage(scaldpc_qary *h)
+{
+    cudaFree(h->d_in);
+    cudaFree(h->d_in_sum);
+    cudaFree(h->d_opost);
+    cudaFree(h->d_opost_sum);
+    cudaFree(h->d_ohard);
+    h->d_in = h->d_in_sum = h->d_opost = h->d_opost_sum = nullptr;
+    h->d_ohard = nullptr;
+    h->cap_stage_T = 0;
+}
+
+int ensure_workspace(scaldpc_qary *h, int tiles, bool want_post)
+{
+    if (tiles <= h->cap_tiles && (!want_post || h->cap_post)) return 0;
+    const int t = std::max(tiles, h->cap_tiles);
+    const bool post = want_post || h->cap_post;
+    free_workspace(h);
+    const size_t lanes = (size_t)t * 32;
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_msg, lanes * h->S * sizeof(float)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_llr, lanes * h->SL * sizeof(float)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_llr_sum, std::max<size_t>(1, lanes * h->SLS) * sizeof(float)));
+    if (post) {
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_post, lanes * h->SL * sizeof(float)));
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_post_sum, std::max<size_t>(1, lanes * h->SLS) * sizeof(float)));
+    }
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_hard_t, lanes * h->N));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_status, lanes * sizeof(int)));
+    h->cap_tiles = t;
+    h->cap_post = post;
+    return 0;
+}
+
+int ensure_stage(scaldpc_qary *h, size_t T, bool want_post)
+{
+    if (T <= h->cap_stage_T && (!want_post || h->d_opost)) return 0;
+    const size_t t = std::max(T, h->cap_stage_T);
+    const bool post = want_post || h->d_opost;
+    free_stage(h);
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_in, t * h->SL * sizeof(float)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_in_sum, std::max<size_t>(1, t * h->SLS) * sizeof(float)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_ohard, t * h->N));
+    if (post) {
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_opost, t * h->SL * sizeof(float)));
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_opost_sum, std::max<size_t>(1, t * h->SLS) * sizeof(float)));
+    }
+    h->cap_stage_T = t;
+    return 0;
+}
+
+QaryDev dev_view(const scaldpc_qary *h, bool want_post)
+{
+    QaryDev p;
+    p.R = h->R;
+    p.N = h->N;
+    p.bvars = h->bvars;
+    p.B = h->B;
+    p.BSUM = h->BSUM;
+    p.Q = h->Q;
+    p.QS = h->QS;
+    p.S = h->S;
+    p.SL = h->SL;
+    p.SLS = h->SLS;
+    p.row_ptr = h->d_row_ptr;
+    p.col = h->d_col;
+    p.sign = h->d_sign;
+    p.edge_off = h->d_edge_off;
+    p.col_ptr = h->d_col_ptr;
+    p.csc = h->d_csc;
+    p.msg = h->d_msg;
+    p.llr = h->d_llr;
+    p.llr_sum = h->d_llr_sum;
+    p.post = want_post ? h->d_post : nullptr;
+    p.post_sum = want_post ? h->d_post_sum : nullptr;
+    p.hard_t = h->d_hard_t;
+    p.status = h->d_status;
+    return p;
+}
+
+// ---- kernel dispatch tables ------------------------------------------------------------------------------
+typedef void (*cn_fast_fn)(const QaryDev, const int, const int);
+typedef void (*vn_fn)(const QaryDev, const int);
+
+cn_fast_fn pick_cn_fast(int sw, int b)
+{
+#define CASE(SW_, B_) \
+    if (sw == SW_ && b == B_) return k_cn_fast<SW_, B_>;
+    CASE(6, 2)  // Kyber-768, sum_weight 6  (lib.rs:54-75 DecoderN1024R256SW6 / DecoderN1280R512SW6)
+    CASE(6, 3)  // Kyber-512, eta1 = 3      (BASELINE.json configs[1])
+    CASE(4, 2)  // Kyber-1024, sum_weight 4
+    CASE(8, 2)  // Kyber-1024, sum_weight 8
+    CASE(3, 2)  // kyber.py:385-392 DecoderN1024R256SW3
+#undef CASE
+    return nullptr;
+}
+
+vn_fn pick_vn(int q)
+{
+    switch (q) {
+#define CASE(Q_) \
+    case Q_:     \
+        return k_vn<Q_>;
+        CASE(3) CASE(5) CASE(7) CASE(9) CASE(11) CASE(13) CASE(15) CASE(17) CASE(19) CASE(21) CASE(23) CASE(25)
+        CASE(27) CASE(29) CASE(31)
+#undef CASE
+    default:
+        return nullptr;
+    }
+}
+
+size_t generic_smem_bytes(const scaldpc_qary *h, CnGenericArgs *g)
+{
+    g->QM = std::max(h->Q, h->QS);
+    g->W = h->wmax;
+    g->LMAX = h->lmax;
+    const size_t floats = (size_t)g->LMAX * g->QM + (size_t)(g->LMAX + 1) * g->W + 2 * (size_t)g->W;
+    return floats * 32 * sizeof(float);  // == generic_scratch_floats(graph) * 128
+}
+
+// One check-node launch / one variable-node launch over `tiles` tiles.
+int launch_cn(scaldpc_qary *h, const QaryDev &p, int tiles, bool first, bool last, unsigned flags, cudaStream_t st)
+{
+    const bool exact = flags & SCALDPC_CN_EXACT;
+    const bool force_generic = flags & SCALDPC_CN_GENERIC;
+    cn_fast_fn fast = (!exact && !force_generic && h->fast_sw) ? pick_cn_fast(h->fast_sw, h->B) : nullptr;
+    if (fast) {
+        dim3 grid((h->R + kCnWarps - 1) / kCnWarps, tiles);
+        fast<<<grid, kCnWarps * 32, 0, st>>>(p, first, last);
+        ++h->launches;
+    } else {
+        if (first) {
+            dim3 grid((h->E + 7) / 8, tiles);
+            k_init_v2c<<<grid, 256, 0, st>>>(p, h->E);
+            ++h->launches;
+        }
+        CnGenericArgs g;
+        g.exact = exact;
+        g.first = first;
+        g.last = last;
+        const size_t smem = generic_smem_bytes(h, &g);
+        dim3 grid(h->R, tiles);
+        k_cn_generic<<<grid, 32, smem, st>>>(p, g);
+        ++h->launches;
+    }
+    SCALDPC_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_vn(scaldpc_qary *h, const QaryDev &p, int tiles, bool last, cudaStream_t st)
+{
+    vn_fn vn = pick_vn(h->Q);
+    dim3 grid((h->bvars + kVnWarps - 1) / kVnWarps, tiles);
+    vn<<<grid, kVnWarps * 32, 0, st>>>(p, last);
+    ++h->launches;
+    SCALDPC_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int load_priors(scaldpc_qary *h, const float *in, float *out, int T, int tiles, int rows, int q, bool is_llr,
+                cudaStream_t st)
+{
+    const int rpb = std::max(1, 256 / q);
+    const int pitch = (rpb * q) | 1;
+    dim3 grid((rows + rpb - 1) / rpb, tiles), block(32, kTrRows);
+    k_load_priors<<<grid, block, (size_t)32 * pitch * sizeof(float), st>>>(in, out, T, rows, q, rpb, is_llr,
+                                                                           h->d_status);
+    ++h->launches;
+    SCALDPC_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace
+
+// ============================================================================================================
+// C ABI
+// ============================================================================================================
+extern "C" {
+
+const char *scaldpc_last_error(void) { return scaldpc::last_error().c_str(); }
+const char *scaldpc_version(void) { return "scaldpc 0.1.0 sm_100a"; }
+
+int scaldpc_device_count(void)
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) return fail(SCALDPC_ERR_CUDA, "cudaGetDeviceCount: %s", cudaGetErrorString(e));
+    return n;
+}
+
+int scaldpc_qary_create(const int8_t *H, int R, int N, int b, int bsum, int dv, int dc, int max_iter, int device,
+                        scaldpc_qary **out)
+{
+    if (!out) return fail(SCALDPC_ERR_ARG, "out is NULL");
+    *out = nullptr;
+    if (max_iter < 0) return fail(SCALDPC_ERR_ARG, "iterations must be >= 0");
+    HostGraph g;
+    {
+        std::string err;
+        const int grc = build_graph(H, R, N, b, bsum, dv, dc, g, err);
+        if (grc) return fail(grc, "%s", err.c_str());
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
+        return fail(SCALDPC_ERR_CUDA, "CUDA device %d not available (%d visible) -- libscaldpc has no CPU path", device,
+                    ndev);
+
+    std::unique_ptr<scaldpc_qary, void (*)(scaldpc_qary *)> h(new scaldpc_qary, scaldpc_qary_destroy);
+    h->R = R;
+    h->N = N;
+    h->B = b;
+    h->BSUM = bsum;
+    h->Q = g.Q;
+    h->QS = g.QS;
+    h->bvars = g.bvars;
+    h->max_iter = max_iter;
+    h->device = device;
+    h->E = g.E;
+    h->S = g.S;
+    h->SL = g.SL;
+    h->SLS = g.SLS;
+    h->lmax = g.lmax;
+    h->wmax = g.wmax;
+    if (g.regular_sw && pick_cn_fast(g.regular_sw, b)) h->fast_sw = g.regular_sw;
+    if (!pick_vn(h->Q)) return fail(SCALDPC_ERR_UNSUPPORTED, "no variable-node kernel for Q=%d", h->Q);
+    std::vector<int2> csc(g.E);
+    for (int e = 0; e < g.E; ++e) csc[e] = make_int2(g.csc[e].off, g.csc[e].sign);
+    const std::vector<int> &row_ptr = g.row_ptr, &col = g.col, &edge_off = g.edge_off, &col_ptr = g.col_ptr;
+    const std::vector<int8_t> &sign = g.sign;
+
+    SCALDPC_CUDA(cudaSetDevice(device));
+    int rc;
+    if ((rc = upload(&h->d_row_ptr, row_ptr)) || (rc = upload(&h->d_col, col)) || (rc = upload(&h->d_sign, sign)) ||
+        (rc = upload(&h->d_edge_off, edge_off)) || (rc = upload(&h->d_col_ptr, col_ptr)) || (rc = upload(&h->d_csc, csc)))
+        return rc;
+    {
+        CnGenericArgs g;
+        const size_t smem = generic_smem_bytes(h.get(), &g);
+        if (smem > 227 * 1024)
+            return fail(SCALDPC_ERR_UNSUPPORTED, "check-node scratch of %zu bytes exceeds shared memory", smem);
+        SCALDPC_CUDA(cudaFuncSetAttribute(k_cn_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
+    *out = h.release();
+    return 0;
+}
+
+void scaldpc_qary_destroy(scaldpc_qary *h)
+{
+    if (!h) return;
+    cudaSetDevice(h->device);
+    free_workspace(h);
+    free_stage(h);
+    cudaFree(h->d_row_ptr);
+    cudaFree(h->d_col);
+    cudaFree(h->d_sign);
+    cudaFree(h->d_edge_off);
+    cudaFree(h->d_col_ptr);
+    cudaFree(h->d_csc);
+    delete h;
+}
+
+int scaldpc_qary_info(const scaldpc_qary *h, int *R, int *N, int *bvars, int *q, int *qs, int *edges, int *max_iter)
+{
+    if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
+    if (R) *R = h->R;
+    if (N) *N = h->N;
+    if (bvars) *bvars = h->bvars;
+    if (q) *q = h->Q;
+    if (qs) *qs = h->QS;
+    if (edges) *edges = h->E;
+    if (max_iter) *max_iter = h->max_iter;
+    return 0;
+}
+
+int scaldpc_qary_set_max_iter(scaldpc_qary *h, int max_iter)
+{
+    if (!h || max_iter < 0) return fail(SCALDPC_ERR_ARG, "bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    h->max_iter = max_iter;
+    return 0;
+}
+
+long long scaldpc_qary_launch_count(const scaldpc_qary *h) { return h ? h->launches : 0; }
+
+int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in_sum, int8_t *hard, float *post,
+                        float *post_sum, int32_t *status, unsigned flags, void *stream)
+{
+    if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
+    if (T < 0) return fail(SCALDPC_ERR_ARG, "T < 0");
+    if (T == 0) return 0;
+    const bool special = h->BSUM > 0;
+    if (!in || !hard || (special && !in_sum)) return fail(SCALDPC_ERR_ARG, "NULL input/output pointer");
+    const bool want_post = post != nullptr || post_sum != nullptr;
+    const bool dev_ptrs = flags & SCALDPC_DEVICE_PTRS;
+    const bool is_llr = flags & SCALDPC_IN_LLR;
+    cudaStream_t st = (cudaStream_t)stream;
+
+    std::lock_guard<std::mutex> lk(h->mu);
+    SCALDPC_CUDA(cudaSetDevice(h->device));
+    const int tiles = (T + 31) / 32;
+    int rc;
+    if ((rc = ensure_workspace(h, tiles, want_post))) return rc;
+
+    const float *din = in, *din_sum = in_sum;
+    int8_t *dhard = hard;
+    float *dpost = post, *dpost_sum = post_sum;
+    if (!dev_ptrs) {
+        if ((rc = ensure_stage(h, (size_t)T, want_post))) return rc;
+        SCALDPC_CUDA(cudaMemcpyAsync(h->d_in, in, (size_t)T * h->SL * sizeof(float), cudaMemcpyHostToDevice, st));
+        if (special)
+            SCALDPC_CUDA(cudaMemcpyAsync(h->d_in_sum, in_sum, (size_t)T * h->SLS * sizeof(float), cudaMemcpyHostToDevice, st));
+        din = h->d_in;
+        din_sum = h->d_in_sum;
+        dhard = h->d_ohard;
+        dpost = post ? h->d_opost : nullptr;
+        dpost_sum = post_sum ? h->d_opost_sum : nullptr;
+    }
+
+    SCALDPC_CUDA(cudaMemsetAsync(h->d_status, 0, (size_t)tiles * 32 * sizeof(int), st));
+    if ((rc = load_priors(h, din, h->d_llr, T, tiles, h->bvars, h->Q, is_llr, st))) return rc;
+    if (special && (rc = load_priors(h, din_sum, h->d_llr_sum, T, tiles, h->R, h->QS, is_llr, st))) return rc;
+
+    const QaryDev p = dev_view(h, want_post);
+    const int iters = std::max(1, h->max_iter);  // decoder.rs:575-663: `it` starts at 1, exit when it >= max_iter
+    for (int it = 1; it <= iters; ++it) {
+        if ((rc = launch_cn(h, p, tiles, it == 1, it == iters, flags, st))) return rc;
+        if ((rc = launch_vn(h, p, tiles, it == iters, st))) return rc;
+    }
+
+    {
+        dim3 block(32, kTrRows);
+        k_untile<int8_t><<<dim3((h->N + 31) / 32, tiles), block, 0, st>>>(h->d_hard_t, dhard, T, h->N);
+        ++h->launches;
+        if (dpost) {
+            k_untile<float><<<dim3((h->SL + 31) / 32, tiles), block, 0, st>>>(h->d_post, dpost, T, h->SL);
+            ++h->launches;
+        }
+        if (dpost_sum && special) {
+            k_untile<float><<<dim3((h->SLS + 31) / 32, tiles), block, 0, st>>>(h->d_post_sum, dpost_sum, T, h->SLS);
+            ++h->launches;
+        }
+        SCALDPC_CUDA(cudaGetLastError());
+    }
+
+    if (!dev_ptrs) {
+        SCALDPC_CUDA(cudaMemcpyAsync(hard, h->d_ohard, (size_t)T * h->N, cudaMemcpyDeviceToHost, st));
+        if (post) SCALDPC_CUDA(cudaMemcpyAsync(post, h->d_opost, (size_t)T * h->SL * sizeof(float), cudaMemcpyDeviceToHost, st));
+        if (post_sum && special)
+            SCALDPC_CUDA(cudaMemcpyAsync(post_sum, h->d_opost_sum, (size_t)T * h->SLS * sizeof(float), cudaMemcpyDeviceToHost, st));
+    }
+    int worst = 0;
+    if (status || !dev_ptrs) {
+        // per-trial status: copy back (host pointer) or device-to-device
+        if (dev_ptrs) {
+            SCALDPC_CUDA(cudaMemcpyAsync(status, h->d_status, (size_t)T * sizeof(int), cudaMemcpyDeviceToDevice, st));
+        } else {
+            std::vector<int> hs(T);
+            SCALDPC_CUDA(cudaMemcpyAsync(hs.data(), h->d_status, (size_t)T * sizeof(int), cudaMemcpyDeviceToHost, st));
+            SCALDPC_CUDA(cudaStreamSynchronize(st));
+            for (int t = 0; t < T; ++t) worst = std::min(worst, hs[t]);
+            if (status) memcpy(status, hs.data(), (size_t)T * sizeof(int));
+        }
+    }
+    if (!dev_ptrs) SCALDPC_CUDA(cudaStreamSynchronize(st));
+    if (worst == SCALDPC_ERR_PROB_SUM) return fail(worst, "a prior row does not sum to 1 +- 0.001 (decoder.rs:683-684)");
+    if (worst == SCALDPC_ERR_NO_MAX) return fail(worst, "No maximum probability found (decoder.rs:680)");
+    if (worst == SCALDPC_ERR_NO_CONFIG) return fail(worst, "a check has no valid configuration (decoder.rs:618)");
+    return 0;
+}
+
+int scaldpc_qary_time_kernel(scaldpc_qary *h, int which, int T, unsigned flags, int reps, void *stream, float *avg_ms)
+{
+    if (!h || !avg_ms || reps <= 0 || T <= 0) return fail(SCALDPC_ERR_ARG, "bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    SCALDPC_CUDA(cudaSetDevice(h->device));
+    const int tiles = (T + 31) / 32;
+    if (tiles > h->cap_tiles) return fail(SCALDPC_ERR_ARG, "time_kernel needs a previous decode of >= T trials");
+    cudaStream_t st = (cudaStream_t)stream;
+    const QaryDev p = dev_view(h, false);
+    cudaEvent_t e0, e1;
+    SCALDPC_CUDA(cudaEventCreate(&e0));
+    SCALDPC_CUDA(cudaEventCreate(&e1));
+    int rc = 0;
+    // one untimed launch, then `reps` timed ones (state stays valid: middle-iteration kernels map a valid
+    // message state to a valid message state)
+    for (int i = -1; i < reps && !rc; ++i) {
+        if (i == 0) SCALDPC_CUDA(cudaEventRecord(e0, st));
+        rc = which == 0 ? launch_cn(h, p, tiles, false, false, flags, st) : launch_vn(h, p, tiles, false, st);
+    }
+    SCALDPC_CUDA(cudaEventRecord(e1, st));
+    SCALDPC_CUDA(cudaEventSynchronize(e1));
+    float ms = 0;
+    SCALDPC_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *avg_ms = ms / reps;
+    return rc;
+}
+
+}  // extern "C"

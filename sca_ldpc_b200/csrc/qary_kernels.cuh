@@ -1,0 +1,580 @@
+// q-ary min-sum BP kernels for sm_100a (B200).  Hand-written CUDA; no tensor cores (the path is an irregular
+// gather plus small (min,+) convolutions).
+//
+// Data layout in HBM ("tile" layout): trials are grouped 32 to a tile, lane = trial % 32 is the innermost
+// index of every per-trial array, so a warp (= one tile) touches one 128-byte line per scalar:
+//     msg     [tile][S      ][32] f32   one slot per (edge, value); edges in CSR order (check-major, column
+//                                        ascending, decoder.rs:507-539); holds v2c before a check-node pass and
+//                                        c2v after it (updated in place -- every slot has exactly one writer)
+//     llr     [tile][bvars*Q][32] f32   channel LLRs of the B-variables        (decoder.rs:668-692)
+//     llr_sum [tile][R*QS   ][32] f32   channel LLRs of the sum-variables      (decoder_special.rs:487-493)
+//     post / post_sum                   final `sum` vectors, same shapes        (decoder.rs:638-642)
+//     hard_t  [tile][N      ][32] i8    hard decisions                          (decoder.rs:654-657)
+// All messages are stored in the CHECK's frame (already mirrored when h < 0), as the reference stores v2c
+// (decoder.rs:571).  Graph indices are warp-uniform and shared by all trials (L2 / constant-cache resident).
+#pragma once
+#include <stdint.h>
+#ifdef SCALDPC_HOST_MODEL
+// tests/hostmodel/hostmodel.cpp compiles these kernels with g++ (threads run one after another) so the kernel
+// logic can be checked against the oracle on a machine without a GPU.  TEST ONLY -- never part of libscaldpc.so.
+#define SCALDPC_DYN_SMEM(type, name) type *name = (type *)scaldpc_host_model_smem
+#else
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#define SCALDPC_DYN_SMEM(type, name) extern __shared__ type name[]
+#endif
+#include "../../include/scaldpc.h"
+
+#define SC_INF (__builtin_huge_valf())
+
+namespace scaldpc {
+
+struct QaryDev {
+    int R, N, bvars, B, BSUM, Q, QS;
+    int S;    // message slots per trial
+    int SL;   // bvars * Q
+    int SLS;  // R * QS (0 for the generic decoder)
+    const int *row_ptr;     // R+1
+    const int *col;         // E
+    const int8_t *sign;     // E
+    const int *edge_off;    // E+1 slot offset of each edge
+    const int *col_ptr;     // N+1
+    const int2 *csc;        // E: {slot offset, sign} of each variable's edges, rows ascending
+    float *msg;
+    const float *llr;
+    const float *llr_sum;
+    float *post;            // may be null
+    float *post_sum;        // may be null
+    int8_t *hard_t;
+    int *status;            // per trial, tiles*32 entries
+};
+
+__device__ __forceinline__ float min3f(float a, float b, float c)
+{
+#ifdef SCALDPC_HOST_MODEL
+    return fminf(fminf(a, b), c);
+#else
+    float r;
+    asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));  // FMNMX3 on sm_100a; NaN operands ignored
+    return r;
+#endif
+}
+
+// NaN -> +inf, everything else unchanged (min.f32 returns the non-NaN operand): "non-finite => excluded".
+__device__ __forceinline__ float sanitize(float x) { return fminf(x, SC_INF); }
+
+// Running minimum that folds two new candidates per FMNMX3.
+struct MinAcc {
+    float best, pend;
+    int n;  // candidates seen (compile-time constant after unrolling)
+    __device__ __forceinline__ MinAcc() : best(SC_INF), pend(SC_INF), n(0) {}
+    __device__ __forceinline__ void add(float x)
+    {
+        if (n == 0) best = x;
+        else if ((n & 1) == 1) pend = x;
+        else best = min3f(best, pend, x);
+        ++n;
+    }
+    __device__ __forceinline__ float get() const { return (n > 1 && (n & 1) == 0) ? fminf(best, pend) : best; }
+};
+
+constexpr int kCnWarps = 4;      // warps (= checks) per CTA of the fast check-node kernel
+constexpr int kCnMinBlocks = 2;  // 255 registers per thread: the DP tables stay in registers without spilling
+
+// -----------------------------------------------------------------------------------------------------------
+// Fast check-node kernel for the special decoder (decoder_special.rs:506-563), regular rows only: every check
+// has exactly SW B-variables followed by its sum-variable, BSUM == SW*B.
+//
+// One thread = one (trial, check); a warp = 32 trials of one check.  Everything lives in registers with
+// compile-time indices.  The brute-force enumeration of (2B+1)^SW configurations is replaced by a forward /
+// backward (min,+) convolution:
+//     F_1 = a_0,  F_{k+1}[u] = min_d F_k[u-d] + a_k[d]                      (prefix sums, |u| <= kB)
+//     G_SW[u] = a_sum[-u],  G_k[u] = min_d a_k[d] + G_{k+1}[u+d]            (cost of the suffix given prefix u)
+//     c2v_k[d] = min_u F_k[u] + G_{k+1}[u+d],   c2v_sum[t] = F_SW[-t]
+// with "non-finite input => value excluded" (sanitize) and "own entry non-finite => +inf out"
+// (decoder.rs:307-311, decoder_special.rs:549-553).
+//
+// The degree-1 sum-variable's own update (decoder_special.rs:591-609) is fused here: its v2c is recomputed
+// from the channel LLR and the previous c2v, so it never travels through HBM, and on the last iteration its
+// hard decision / posterior are emitted from here.
+// -----------------------------------------------------------------------------------------------------------
+template <int SW, int B>
+__global__ void __launch_bounds__(kCnWarps * 32, kCnMinBlocks) k_cn_fast(const QaryDev p, const int FIRST, const int LAST)
+{
+    constexpr int Q = 2 * B + 1, BS = SW * B, QS = 2 * BS + 1;
+    const float INF = SC_INF;
+    const int lane = threadIdx.x & 31;
+    const int check = blockIdx.x * kCnWarps + (threadIdx.x >> 5);
+    const int tile = blockIdx.y;
+    if (check >= p.R) return;
+
+    const int e0 = __ldg(p.row_ptr + check);
+    const int base = __ldg(p.edge_off + e0);
+    float *msg = p.msg + (size_t)tile * p.S * 32 + lane;
+    const float *llr = p.llr + (size_t)tile * p.SL * 32 + lane;
+    const float *llrs = p.llr_sum + (size_t)tile * p.SLS * 32 + lane;
+
+    // ---- load the B-variables' v2c (check frame)
+    float a[SW][Q];
+#pragma unroll
+    for (int k = 0; k < SW; ++k) {
+        if (FIRST) {  // v2c = perm_h(channel) (decoder_special.rs:480-486), gathered straight from llr
+            const int var = __ldg(p.col + e0 + k);
+            const bool neg = __ldg(p.sign + e0 + k) < 0;
+#pragma unroll
+            for (int i = 0; i < Q; ++i) a[k][i] = llr[(size_t)(var * Q + (neg ? Q - 1 - i : i)) * 32];
+        } else {
+#pragma unroll
+            for (int i = 0; i < Q; ++i) a[k][i] = msg[(size_t)(base + k * Q + i) * 32];
+        }
+    }
+    // ---- the sum-variable: v2c from channel + previous c2v (decoder_special.rs:591-604), check frame
+    const int vs = __ldg(p.col + e0 + SW) - p.bvars;
+    const bool negs = __ldg(p.sign + e0 + SW) < 0;
+    const int sbase = base + SW * Q;
+    float as[QS];
+#pragma unroll
+    for (int i = 0; i < QS; ++i) as[i] = llrs[(size_t)(vs * QS + (negs ? QS - 1 - i : i)) * 32];
+    if (!FIRST) {
+        float m = INF;
+#pragma unroll
+        for (int i = 0; i < QS; ++i) {
+            const float c = msg[(size_t)(sbase + i) * 32];
+            const float tot = as[i] + c;   // sum = channel + perm_h(c2v)
+            as[i] = tot - c;               // prim = perm_h(sum - perm_h(c2v))
+            m = fminf(m, as[i]);           // value of the first strict minimum (NaN skipped)
+        }
+#pragma unroll
+        for (int i = 0; i < QS; ++i) as[i] = as[i] - m;
+    }
+#pragma unroll
+    for (int k = 0; k < SW; ++k)
+#pragma unroll
+        for (int i = 0; i < Q; ++i) a[k][i] = sanitize(a[k][i]);
+#pragma unroll
+    for (int i = 0; i < QS; ++i) as[i] = sanitize(as[i]);
+
+    // ---- forward: F[k][u + k*B], k = 1..SW-1
+    float F[SW][2 * (SW - 1) * B + 1];
+#pragma unroll
+    for (int i = 0; i < Q; ++i) F[1 % SW][i] = a[0][i];
+#pragma unroll
+    for (int k = 1; k < SW - 1; ++k) {
+#pragma unroll
+        for (int u = -(k + 1) * B; u <= (k + 1) * B; ++u) {
+            MinAcc acc;
+#pragma unroll
+            for (int d = -B; d <= B; ++d) {
+                const int up = u - d;
+                if (up >= -k * B && up <= k * B) acc.add(F[k][up + k * B] + a[k][d + B]);
+            }
+            F[k + 1][u + (k + 1) * B] = acc.get();
+        }
+    }
+    // ---- c2v of the sum-variable: F_SW[-t]
+    float cs[QS];
+#pragma unroll
+    for (int t = -BS; t <= BS; ++t) {
+        const int u = -t;
+        MinAcc acc;
+        if (SW == 1) {
+            // F_1 = a_0 directly
+            if (u >= -B && u <= B) acc.add(a[0][u + B]);
+        } else {
+            constexpr int k = SW - 1;
+#pragma unroll
+            for (int d = -B; d <= B; ++d) {
+                const int up = u - d;
+                if (up >= -k * B && up <= k * B) acc.add(F[k][up + k * B] + a[k][d + B]);
+            }
+        }
+        const float r = acc.get();
+        cs[t + BS] = (as[t + BS] == INF) ? INF : r;
+        msg[(size_t)(sbase + t + BS) * 32] = cs[t + BS];
+    }
+    if (LAST) {  // decision of the sum-variable (decoder_special.rs:606-608): first minimum in the VARIABLE's frame
+        float min_val = INF;
+        int arg = negs ? QS - 1 : 0;
+        float *post = p.post_sum ? p.post_sum + (size_t)tile * p.SLS * 32 + lane : nullptr;
+#pragma unroll
+        for (int i = 0; i < QS; ++i) {
+            const int iv = negs ? QS - 1 - i : i;
+            const float tot = llrs[(size_t)(vs * QS + iv) * 32] + cs[i];
+            if (negs ? (tot <= min_val && tot < INF) : (tot < min_val)) {
+                min_val = tot;
+                arg = i;
+            }
+            if (post) post[(size_t)(vs * QS + iv) * 32] = tot;
+        }
+        const int argv = negs ? QS - 1 - arg : arg;
+        p.hard_t[((size_t)tile * p.N + p.bvars + vs) * 32 + lane] = (int8_t)(argv - BS);
+    }
+
+    // ---- backward + combine.  Gc = G_{k+1}, indexed [u + (k+1)*B]
+    float Gc[QS], Gn[QS];
+#pragma unroll
+    for (int i = 0; i < QS; ++i) Gc[i] = as[QS - 1 - i];  // G_SW[u] = a_sum[-u]
+#pragma unroll
+    for (int k = SW - 1; k >= 0; --k) {
+        // c2v_k[d] = min_u F_k[u] + G_{k+1}[u + d]
+#pragma unroll
+        for (int d = -B; d <= B; ++d) {
+            MinAcc acc;
+            if (k == 0) {
+                acc.add(Gc[d + B]);
+            } else {
+#pragma unroll
+                for (int u = -k * B; u <= k * B; ++u) acc.add(F[k][u + k * B] + Gc[u + d + (k + 1) * B]);
+            }
+            const float r = acc.get();
+            msg[(size_t)(base + k * Q + d + B) * 32] = (a[k][d + B] == INF) ? INF : r;
+        }
+        if (k > 0) {
+#pragma unroll
+            for (int u = -k * B; u <= k * B; ++u) {
+                MinAcc acc;
+#pragma unroll
+                for (int d = -B; d <= B; ++d) acc.add(a[k][d + B] + Gc[u + d + (k + 1) * B]);
+                Gn[u + k * B] = acc.get();
+            }
+#pragma unroll
+            for (int i = 0; i < QS; ++i) Gc[i] = Gn[i];
+        }
+    }
+}
+
+// -----------------------------------------------------------------------------------------------------------
+// Variable-node kernel for the B-variables (decoder.rs:634-658 / decoder_special.rs:566-590).
+// One warp = (tile, variable), lane = trial.  Exactly the reference's operation order:
+//   sum = channel; for each check (row order): sum = sum + perm_h(c2v)
+//   per edge: prim = perm_h(sum - perm_h(c2v)); v2c = prim - prim[first strict minimum]
+//   last iteration: hard = argmin_first(sum) - B, posterior = sum
+// -----------------------------------------------------------------------------------------------------------
+constexpr int kVnWarps = 8;
+
+template <int Q>
+__global__ void __launch_bounds__(kVnWarps * 32) k_vn(const QaryDev p, const int LAST)
+{
+    const float INF = SC_INF;
+    const int lane = threadIdx.x & 31;
+    const int var = blockIdx.x * kVnWarps + (threadIdx.x >> 5);
+    const int tile = blockIdx.y;
+    if (var >= p.bvars) return;
+    float *msg = p.msg + (size_t)tile * p.S * 32 + lane;
+    const float *llr = p.llr + (size_t)tile * p.SL * 32 + lane;
+
+    float tot[Q];
+#pragma unroll
+    for (int i = 0; i < Q; ++i) tot[i] = llr[(size_t)(var * Q + i) * 32];
+    const int p0 = __ldg(p.col_ptr + var), p1 = __ldg(p.col_ptr + var + 1);
+    for (int e = p0; e < p1; ++e) {
+        const int2 es = __ldg(p.csc + e);
+        const bool neg = es.y < 0;
+#pragma unroll
+        for (int i = 0; i < Q; ++i) tot[i] = tot[i] + msg[(size_t)(es.x + (neg ? Q - 1 - i : i)) * 32];
+    }
+    for (int e = p0; e < p1; ++e) {
+        const int2 es = __ldg(p.csc + e);
+        const bool neg = es.y < 0;
+        float prim[Q];
+        float m = INF;
+#pragma unroll
+        for (int i = 0; i < Q; ++i) {  // i: check frame
+            const float c = msg[(size_t)(es.x + i) * 32];
+            const float t = neg ? tot[Q - 1 - i] : tot[i];
+            prim[i] = t - c;
+            m = fminf(m, prim[i]);
+        }
+#pragma unroll
+        for (int i = 0; i < Q; ++i) msg[(size_t)(es.x + i) * 32] = prim[i] - m;
+    }
+    if (LAST) {
+        float min_val = INF;
+        int arg = 0;
+#pragma unroll
+        for (int i = 0; i < Q; ++i)
+            if (tot[i] < min_val) {
+                min_val = tot[i];
+                arg = i;
+            }
+        p.hard_t[((size_t)tile * p.N + var) * 32 + lane] = (int8_t)(arg - (Q - 1) / 2);
+        if (p.post) {
+            float *post = p.post + (size_t)tile * p.SL * 32 + lane;
+#pragma unroll
+            for (int i = 0; i < Q; ++i) post[(size_t)(var * Q + i) * 32] = tot[i];
+        }
+    }
+}
+
+// First-iteration initialisation of the B-edges for the runtime-shape path: v2c = perm_h(channel)
+// (decoder.rs:567-573).  One warp = (tile, edge).
+__global__ void __launch_bounds__(256) k_init_v2c(const QaryDev p, int E)
+{
+    const int lane = threadIdx.x & 31;
+    const int e = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int tile = blockIdx.y;
+    if (e >= E) return;
+    const int c = __ldg(p.col + e);
+    if (c >= p.bvars) return;  // sum-variable edges are handled inside the check-node kernel
+    const bool neg = __ldg(p.sign + e) < 0;
+    const int off = __ldg(p.edge_off + e);
+    float *msg = p.msg + (size_t)tile * p.S * 32 + lane;
+    const float *llr = p.llr + (size_t)tile * p.SL * 32 + lane;
+    for (int i = 0; i < p.Q; ++i) msg[(size_t)(off + i) * 32] = llr[(size_t)(c * p.Q + (neg ? p.Q - 1 - i : i)) * 32];
+}
+
+// -----------------------------------------------------------------------------------------------------------
+// Runtime-shape check-node kernel: any row degree, any alphabets, both decoders, two algorithms.
+//   exact != 0   "exact-order" DP: P_0 = {0:0}, P_{k+1}[u] = min_d fl(P_k[u-d] + a_k[d]); for every (j, d) the DP
+//                is restarted from P_j with variable j pinned to d and the result is fl(M - a_j[d]).  Because
+//                fl(x + c) is monotone in x this reproduces the reference's min over sequentially-rounded
+//                configuration sums (decoder.rs:600-629, decoder_special.rs:539-553) BIT FOR BIT.
+//   exact == 0   forward/backward as in k_cn_fast.
+// One CTA = one warp = (tile, check); per-thread scratch lives in shared memory as [index][lane] (bank = lane,
+// conflict-free).  Handles the fused sum-variable update like k_cn_fast.  Generic decoder (BSUM == 0): a check
+// without any finite configuration raises SCALDPC_ERR_NO_CONFIG for that trial (decoder.rs:618).
+// -----------------------------------------------------------------------------------------------------------
+struct CnGenericArgs {
+    int exact, first, last;
+    int QM;    // max(Q, QS): stride of the per-variable input vectors in scratch
+    int W;     // width of the DP tables (2 * sum of alphabets + 1, clamped per check at run time)
+    int LMAX;  // max row degree
+};
+
+__global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGenericArgs g)
+{
+    SCALDPC_DYN_SMEM(float, smem);
+    const float INF = SC_INF;
+    const int lane = threadIdx.x;
+    const int check = blockIdx.x, tile = blockIdx.y;
+    const int e0 = __ldg(p.row_ptr + check), L = __ldg(p.row_ptr + check + 1) - e0;
+    if (L <= 0) return;
+    float *msg = p.msg + (size_t)tile * p.S * 32 + lane;
+    const bool special = p.BSUM > 0;
+
+    // scratch: a[L][QM], P[(L+1)][W], A[W], Bv[W]   (all x 32 lanes)
+    float *sa = smem + lane;
+    float *sP = sa + (size_t)g.LMAX * g.QM * 32;
+    float *sA = sP + (size_t)(g.LMAX + 1) * g.W * 32;
+    float *sB = sA + (size_t)g.W * 32;
+#define A_(k, i) sa[((k)*g.QM + (i)) * 32]
+#define P_(k, u) sP[((k)*g.W + (u)) * 32]
+#define TA_(u) sA[(u)*32]
+#define TB_(u) sB[(u)*32]
+
+    // alphabets and total range of this check
+    int tot = 0;
+    for (int k = 0; k < L; ++k) tot += (__ldg(p.col + e0 + k) >= p.bvars) ? p.BSUM : p.B;
+    const int W = 2 * tot + 1;  // <= g.W
+
+    // ---- load inputs (sanitised copies in scratch)
+    for (int k = 0; k < L; ++k) {
+        const int c = __ldg(p.col + e0 + k);
+        const int off = __ldg(p.edge_off + e0 + k);
+        if (c >= p.bvars) {  // sum-variable: fused variable-node update
+            const int vs = c - p.bvars;
+            const bool neg = __ldg(p.sign + e0 + k) < 0;
+            const float *llrs = p.llr_sum + (size_t)tile * p.SLS * 32 + lane;
+            float m = INF;
+            for (int i = 0; i < p.QS; ++i) {
+                float x = llrs[(size_t)(vs * p.QS + (neg ? p.QS - 1 - i : i)) * 32];
+                if (!g.first) {
+                    const float cc = msg[(size_t)(off + i) * 32];
+                    const float t = x + cc;
+                    x = t - cc;
+                    m = fminf(m, x);
+                }
+                A_(k, i) = x;
+            }
+            for (int i = 0; i < p.QS; ++i) A_(k, i) = sanitize(g.first ? A_(k, i) : A_(k, i) - m);
+        } else {
+            for (int i = 0; i < p.Q; ++i) A_(k, i) = sanitize(msg[(size_t)(off + i) * 32]);
+        }
+    }
+#define BK_(k) ((__ldg(p.col + e0 + (k)) >= p.bvars) ? p.BSUM : p.B)
+
+    // ---- forward table P_k[u], u offset by tot
+    for (int u = 0; u < W; ++u) P_(0, u) = INF;
+    P_(0, tot) = 0.0f;
+    for (int k = 0; k < L; ++k) {
+        const int bk = BK_(k);
+        for (int u = 0; u < W; ++u) {
+            float best = INF;
+            for (int i = 0; i <= 2 * bk; ++i) {
+                const int up = u - (i - bk);
+                if (up < 0 || up >= W) continue;
+                best = fminf(best, P_(k, up) + A_(k, i));
+            }
+            P_(k + 1, u) = best;
+        }
+    }
+    if (!special && !(P_(L, tot) < INF)) {
+        atomicMin(p.status + tile * 32 + lane, SCALDPC_ERR_NO_CONFIG);
+    }
+
+    if (g.exact) {
+        for (int j = 0; j < L; ++j) {
+            const int bj = BK_(j);
+            const int offj = __ldg(p.edge_off + e0 + j);
+            for (int i = 0; i <= 2 * bj; ++i) {
+                const float x = A_(j, i);
+                float r = INF;
+                if (x < INF) {
+                    for (int u = 0; u < W; ++u) {
+                        const int up = u - (i - bj);
+                        TA_(u) = (up >= 0 && up < W) ? P_(j, up) + x : INF;
+                    }
+                    for (int k = j + 1; k < L; ++k) {
+                        const int bk = BK_(k);
+                        for (int u = 0; u < W; ++u) {
+                            float best = INF;
+                            for (int i2 = 0; i2 <= 2 * bk; ++i2) {
+                                const int up = u - (i2 - bk);
+                                if (up < 0 || up >= W) continue;
+                                best = fminf(best, TA_(up) + A_(k, i2));
+                            }
+                            TB_(u) = best;
+                        }
+                        for (int u = 0; u < W; ++u) TA_(u) = TB_(u);
+                    }
+                    const float M = TA_(tot);
+                    r = (M < INF) ? M - x : INF;
+                }
+                msg[(size_t)(offj + i) * 32] = r;
+            }
+        }
+    } else {
+        // backward rolling table: TA = G_{k+1}[u] = cost of the suffix when it must total (u - tot)
+        for (int u = 0; u < W; ++u) TA_(u) = INF;
+        TA_(tot) = 0.0f;
+        for (int j = L - 1; j >= 0; --j) {
+            const int bj = BK_(j);
+            const int offj = __ldg(p.edge_off + e0 + j);
+            for (int i = 0; i <= 2 * bj; ++i) {
+                float r = INF;
+                if (A_(j, i) < INF) {
+                    const int d = i - bj;
+                    for (int u = 0; u < W; ++u) {
+                        const int us = -(u - tot) - d + tot;
+                        if (us < 0 || us >= W) continue;
+                        r = fminf(r, P_(j, u) + TA_(us));
+                    }
+                }
+                msg[(size_t)(offj + i) * 32] = r;
+            }
+            if (j > 0) {
+                for (int u = 0; u < W; ++u) {
+                    float best = INF;
+                    for (int i = 0; i <= 2 * bj; ++i) {
+                        const int up = u - (i - bj);
+                        if (up < 0 || up >= W) continue;
+                        best = fminf(best, A_(j, i) + TA_(up));
+                    }
+                    TB_(u) = best;
+                }
+                for (int u = 0; u < W; ++u) TA_(u) = TB_(u);
+            }
+        }
+    }
+
+    // ---- last iteration: decision of the sum-variable
+    if (g.last && special) {
+        const int k = L - 1;
+        const int c = __ldg(p.col + e0 + k);
+        if (c >= p.bvars) {
+            const int vs = c - p.bvars;
+            const bool neg = __ldg(p.sign + e0 + k) < 0;
+            const int off = __ldg(p.edge_off + e0 + k);
+            const float *llrs = p.llr_sum + (size_t)tile * p.SLS * 32 + lane;
+            float *post = p.post_sum ? p.post_sum + (size_t)tile * p.SLS * 32 + lane : nullptr;
+            float min_val = INF;
+            int arg = 0;
+            for (int iv = 0; iv < p.QS; ++iv) {  // variable frame, ascending
+                const int i = neg ? p.QS - 1 - iv : iv;
+                const float t = llrs[(size_t)(vs * p.QS + iv) * 32] + msg[(size_t)(off + i) * 32];
+                if (t < min_val) {
+                    min_val = t;
+                    arg = iv;
+                }
+                if (post) post[(size_t)(vs * p.QS + iv) * 32] = t;
+            }
+            p.hard_t[((size_t)tile * p.N + p.bvars + vs) * 32 + lane] = (int8_t)(arg - p.BSUM);
+        }
+    }
+#undef A_
+#undef P_
+#undef TA_
+#undef TB_
+#undef BK_
+}
+
+// -----------------------------------------------------------------------------------------------------------
+// Layout conversion kernels (host row-major [T][n] <-> tile layout [tile][n][32]) with a shared-memory transpose
+// so both sides are coalesced.  k_load_priors also applies into_llr (decoder.rs:668-692).
+// -----------------------------------------------------------------------------------------------------------
+constexpr int kTrRows = 8;  // threads.y
+
+// in: [T][rows*q] probabilities or LLRs; out: [tile][rows*q][32].  One CTA = one tile x `rpb` rows.
+__global__ void __launch_bounds__(32 * kTrRows) k_load_priors(const float *__restrict__ in, float *__restrict__ out,
+                                                              int T, int rows, int q, int rpb, int is_llr,
+                                                              int *__restrict__ status)
+{
+    SCALDPC_DYN_SMEM(float, sm);
+    const int tile = blockIdx.y;
+    const int r0 = blockIdx.x * rpb;
+    const int nr = min(rpb, rows - r0);
+    const int n = nr * q;             // floats per trial in this chunk
+    const int pitch = (rpb * q) | 1;  // odd pitch: conflict-free column access
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const size_t per_trial = (size_t)rows * q;
+    // coalesced load: thread tx walks the chunk, ty walks trials
+    for (int t = ty; t < 32; t += kTrRows) {
+        const int trial = tile * 32 + t;
+        for (int i = tx; i < n; i += 32)
+            sm[t * pitch + i] = trial < T ? in[(size_t)trial * per_trial + (size_t)r0 * q + i] : (is_llr ? 0.0f : 1.0f / q);
+    }
+    __syncthreads();
+    if (!is_llr) {
+        // thread (tx = trial, ty = row): sum / max / ln(max / p)
+        for (int r = ty; r < nr; r += kTrRows) {
+            float *v = sm + tx * pitch + r * q;
+            float sum = 0.0f, mx = 0.0f;
+            bool have = false;
+            for (int i = 0; i < q; ++i) {
+                const float x = v[i];
+                sum += x;
+                if (x == x && (!have || x > mx)) {
+                    mx = x;
+                    have = true;
+                }
+            }
+            int err = 0;
+            if (!have) err = SCALDPC_ERR_NO_MAX;
+            else if (!(sum < 1.0f + 0.001f) || !(sum > 1.0f - 0.001f)) err = SCALDPC_ERR_PROB_SUM;
+            if (err && tile * 32 + tx < T) atomicMin(status + tile * 32 + tx, err);
+            for (int i = 0; i < q; ++i) v[i] = logf(__fdiv_rn(mx, v[i]));
+        }
+        __syncthreads();
+    }
+    float *o = out + ((size_t)tile * per_trial + (size_t)r0 * q) * 32;
+    for (int i = ty; i < n; i += kTrRows) o[(size_t)i * 32 + tx] = sm[tx * pitch + i];
+}
+
+// tile layout -> row-major.  src [tile][n][32] -> dst [T][n]
+template <typename T_>
+__global__ void __launch_bounds__(32 * kTrRows) k_untile(const T_ *__restrict__ src, T_ *__restrict__ dst, int T, int n)
+{
+    __shared__ T_ sm[32][33];
+    const int tile = blockIdx.y;
+    const int c0 = blockIdx.x * 32;
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    for (int c = ty; c < 32; c += kTrRows)
+        if (c0 + c < n) sm[c][tx] = src[((size_t)tile * n + c0 + c) * 32 + tx];
+    __syncthreads();
+    for (int t = ty; t < 32; t += kTrRows) {
+        const int trial = tile * 32 + t;
+        if (trial < T && c0 + tx < n) dst[(size_t)trial * n + c0 + tx] = sm[tx][t];
+    }
+}
+
+}  // namespace scaldpc

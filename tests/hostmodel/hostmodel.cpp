@@ -1,0 +1,176 @@
+// TEST INFRASTRUCTURE ONLY.  Compiles the CUDA kernels of sca_ldpc_b200/csrc/qary_kernels.cuh with g++ and runs
+// their threads one after another on the host, so that the kernel LOGIC (index arithmetic, DP tables, NaN/inf
+// handling, in-place message updates) can be checked against the oracle in the `-m "not gpu"` test tier, on a
+// machine without a GPU.  This file is never linked into libscaldpc.so and the product has no CPU path.
+//
+// Only kernels whose threads are independent are modelled (k_cn_fast, k_cn_generic, k_vn, k_init_v2c); the two
+// layout-conversion kernels cooperate through shared memory and are replaced by plain loops here.
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#define SCALDPC_HOST_MODEL 1
+struct hm_dim3 {
+    unsigned x = 1, y = 0, z = 0;
+};
+static hm_dim3 threadIdx, blockIdx, blockDim, gridDim;
+static float *scaldpc_host_model_smem = nullptr;
+struct int2 {
+    int x, y;
+};
+static inline int2 make_int2(int x, int y) { return int2{x, y}; }
+#define __global__
+#define __device__
+#define __host__
+#define __forceinline__ inline
+#define __launch_bounds__(...)
+#define __restrict__
+#define __shared__ static
+template <typename T>
+static inline T __ldg(const T *p) { return *p; }
+static inline int atomicMin(int *p, int v)
+{
+    int o = *p;
+    *p = std::min(o, v);
+    return o;
+}
+static inline float __fdiv_rn(float a, float b) { return a / b; }
+static inline void __syncthreads() {}
+using std::max;
+using std::min;
+
+#include "../../sca_ldpc_b200/csrc/qary_graph.h"
+#include "../../sca_ldpc_b200/csrc/qary_kernels.cuh"
+
+using namespace scaldpc;
+
+namespace {
+
+template <typename K, typename... A>
+void run_grid(unsigned gx, unsigned gy, unsigned threads, K kernel, A... args)
+{
+    gridDim.x = gx;
+    gridDim.y = gy;
+    blockDim.x = threads;
+    for (unsigned by = 0; by < gy; ++by)
+        for (unsigned bx = 0; bx < gx; ++bx)
+            for (unsigned t = 0; t < threads; ++t) {
+                blockIdx.x = bx;
+                blockIdx.y = by;
+                threadIdx.x = t;
+                kernel(args...);
+            }
+}
+
+typedef void (*cn_fast_fn)(const QaryDev, const int, const int);
+typedef void (*vn_fn)(const QaryDev, const int);
+
+cn_fast_fn pick_cn_fast(int sw, int b)
+{
+#define CASE(SW_, B_) \
+    if (sw == SW_ && b == B_) return k_cn_fast<SW_, B_>;
+    CASE(6, 2) CASE(6, 3) CASE(4, 2) CASE(8, 2) CASE(3, 2)
+#undef CASE
+    return nullptr;
+}
+
+vn_fn pick_vn(int q)
+{
+    switch (q) {
+#define CASE(Q_) \
+    case Q_:     \
+        return k_vn<Q_>;
+        CASE(3) CASE(5) CASE(7) CASE(9) CASE(11) CASE(13) CASE(15) CASE(17) CASE(19) CASE(21) CASE(23) CASE(25)
+        CASE(27) CASE(29) CASE(31)
+#undef CASE
+    default:
+        return nullptr;
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+// Full decode of T trials from LLRs through the modelled kernels.  Same argument meaning as
+// scaldpc_qary_decode with SCALDPC_IN_LLR; flags: SCALDPC_CN_EXACT / SCALDPC_CN_GENERIC.
+// Returns 0 or a (negative) status code; *used_fast tells whether k_cn_fast ran.
+int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv, int dc, int max_iter, int T,
+                          const float *llr_in, const float *llr_sum_in, int8_t *hard, float *post, float *post_sum,
+                          int32_t *status, unsigned flags, int *used_fast, char *errbuf, int errlen)
+{
+    HostGraph g;
+    std::string err;
+    int rc = build_graph(H, R, N, b, bsum, dv, dc, g, err);
+    if (rc) {
+        if (errbuf) snprintf(errbuf, errlen, "%s", err.c_str());
+        return rc;
+    }
+    const int tiles = (T + 31) / 32;
+    const size_t lanes = (size_t)tiles * 32;
+    std::vector<float> msg(lanes * g.S), llr(lanes * g.SL), llrs(std::max<size_t>(1, lanes * g.SLS));
+    std::vector<float> tpost(lanes * g.SL), tposts(std::max<size_t>(1, lanes * g.SLS));
+    std::vector<int8_t> hard_t(lanes * g.N);
+    std::vector<int> st(lanes, 0);
+    std::vector<int2> csc(g.E);
+    for (int e = 0; e < g.E; ++e) csc[e] = make_int2(g.csc[e].off, g.csc[e].sign);
+    // tile the inputs (what k_load_priors does with is_llr = 1)
+    for (size_t t = 0; t < lanes; ++t) {
+        const size_t tile = t / 32, lane = t % 32;
+        for (int i = 0; i < g.SL; ++i)
+            llr[(tile * g.SL + i) * 32 + lane] = t < (size_t)T ? llr_in[t * g.SL + i] : 0.0f;
+        for (int i = 0; i < g.SLS; ++i)
+            llrs[(tile * g.SLS + i) * 32 + lane] = t < (size_t)T ? llr_sum_in[t * g.SLS + i] : 0.0f;
+    }
+    QaryDev p;
+    p.R = g.R; p.N = g.N; p.bvars = g.bvars; p.B = g.B; p.BSUM = g.BSUM; p.Q = g.Q; p.QS = g.QS;
+    p.S = g.S; p.SL = g.SL; p.SLS = g.SLS;
+    p.row_ptr = g.row_ptr.data(); p.col = g.col.data(); p.sign = g.sign.data(); p.edge_off = g.edge_off.data();
+    p.col_ptr = g.col_ptr.data(); p.csc = csc.data();
+    p.msg = msg.data(); p.llr = llr.data(); p.llr_sum = llrs.data();
+    p.post = tpost.data(); p.post_sum = tposts.data(); p.hard_t = hard_t.data(); p.status = st.data();
+
+    const bool exact = flags & SCALDPC_CN_EXACT, force_generic = flags & SCALDPC_CN_GENERIC;
+    cn_fast_fn fast = (!exact && !force_generic && g.regular_sw) ? pick_cn_fast(g.regular_sw, b) : nullptr;
+    vn_fn vn = pick_vn(g.Q);
+    if (!vn) return SCALDPC_ERR_UNSUPPORTED;
+    if (used_fast) *used_fast = fast != nullptr;
+    std::vector<float> scratch(generic_scratch_floats(g) * 32);
+    scaldpc_host_model_smem = scratch.data();
+
+    const int iters = std::max(1, max_iter);
+    for (int it = 1; it <= iters; ++it) {
+        const int first = it == 1, last = it == iters;
+        if (fast) {
+            run_grid((g.R + kCnWarps - 1) / kCnWarps, tiles, kCnWarps * 32, fast, p, first, last);
+        } else {
+            if (first) run_grid((g.E + 7) / 8, tiles, 256, k_init_v2c, p, g.E);
+            CnGenericArgs a;
+            a.exact = exact; a.first = first; a.last = last;
+            a.QM = std::max(g.Q, g.QS); a.W = g.wmax; a.LMAX = g.lmax;
+            run_grid(g.R, tiles, 32, k_cn_generic, p, a);
+        }
+        run_grid((g.bvars + kVnWarps - 1) / kVnWarps, tiles, kVnWarps * 32, vn, p, last);
+    }
+    // untile
+    int worst = 0;
+    for (int t = 0; t < T; ++t) {
+        const size_t tile = t / 32, lane = t % 32;
+        for (int i = 0; i < g.N; ++i) hard[(size_t)t * g.N + i] = hard_t[(tile * g.N + i) * 32 + lane];
+        if (post)
+            for (int i = 0; i < g.SL; ++i) post[(size_t)t * g.SL + i] = tpost[(tile * g.SL + i) * 32 + lane];
+        if (post_sum)
+            for (int i = 0; i < g.SLS; ++i) post_sum[(size_t)t * g.SLS + i] = tposts[(tile * g.SLS + i) * 32 + lane];
+        if (status) status[t] = st[t];
+        worst = std::min(worst, st[t]);
+    }
+    scaldpc_host_model_smem = nullptr;
+    return worst;
+}
+
+}  // extern "C"
