@@ -1,0 +1,392 @@
+#!/usr/bin/env python
+"""bench.py -- throughput of the belief-propagation decoder hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME] [--trials T]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one pass of the hot path over one batch of synthetic input: decode T independent trials (priors ->
+hard decisions) under the iteration cap.  Default workload = BASELINE.json configs[1]: Kyber-512 q-ary BP
+(eta1 = 3, 7-value alphabet), 10^4 batched trials on one B200, sum_weight 6, check_blocks 1, 10 iterations.
+
+One JSON line on stdout (rank 0):
+  value      whole-job trials/s over all N GPUs with the priors already resident in HBM (device-timed, CUDA events,
+             max over ranks); trials are independent, so each rank decodes its own T trials ("weak" scaling) and the
+             only exchange is an all-reduce of the success counters.
+  e2e        the same metric through the reference-facing API with HOST buffers: every step copies that step's
+             priors from pinned host memory to the device and the hard decisions back.
+  roofline   the dominant kernel (check-node pass) against the measured HBM copy peak (MEASURED_PEAKS.json).
+  cpu_baseline  the CPU oracle (restatement of the reference's brute-force min-sum, one decode per thread as
+             simulate/decode.py:247-262 does) on a bounded sample of the same workload.
+--impl reference times that CPU path alone (the reference's Rust crate cannot be built here: no cargo/rustc).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name: (kind, kwargs, default trials, iterations)
+    "kyber512": ("qary", dict(variant="kyber512", sum_weight=6, check_blocks=1, accuracy=0.98, nbits=4, nbits_sum=5), 10_000, 10),
+    "kyber768": ("qary", dict(variant="kyber768", sum_weight=6, check_blocks=2, accuracy=0.95, nbits=3, nbits_sum=4), 10_000, 10),
+    "kyber768cb1": ("qary", dict(variant="kyber768", sum_weight=6, check_blocks=1, accuracy=0.95, nbits=3, nbits_sum=4), 10_000, 10),
+    "kyber1024": ("qary", dict(variant="kyber1024", sum_weight=8, check_blocks=1, accuracy=0.98, nbits=5, nbits_sum=6), 12_500, 10),
+    "hqc128": ("bp", dict(variant="hqc128", W=50, R=3000, rho=0.9942), 4096, 100),
+    "hqc256": ("bp", dict(variant="hqc256", W=50, R=8000, rho=0.9942), 2048, 100),
+}
+
+
+def measured_peak_gbs():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.perf_counter(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [ln for (t, ln) in self.lines if t0 <= t <= t1 + 0.2] or [ln for (_, ln) in self.lines[-3:]]
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in rows:
+            f = [x.strip() for x in ln.split(",")]
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except Exception:
+                continue
+            for name, val in zip(names, f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+# =====================================================================================================================
+# reference arm / cpu_baseline: the CPU oracle on the host cores
+# =====================================================================================================================
+def cpu_path(kind, wl, iters, trials, threads, warm_only=False):
+    """Times the oracle on `trials` trials with `threads` host threads.  Returns (trials/s, seconds, successes)."""
+    from oracle import oracle as O
+
+    if kind == "qary":
+        b = wl.generate(trials, seed=12345)
+        orc = O.QaryOracle(wl.H, 1 if warm_only else iters, B=wl.B, BSUM=wl.BSUM, DC=wl.sum_weight + 1,
+                           algo=O.ALGO_ENUMERATE)
+        t0 = time.perf_counter()
+        hard, _, _, st = orc.decode_batch(b.priors, b.priors_sum, from_probs=True, threads=threads, want_post=False)
+        dt = time.perf_counter() - t0
+        return trials / dt, dt, int(wl.success(b, hard).sum())
+    b = wl.generate(trials, seed=12345)
+    orc = O.BinaryBpOracle(csr=(wl.row_ptr, wl.col), shape=(wl.m, wl.n), max_iter=iters, channel_probs=wl.channel_probs)
+    t0 = time.perf_counter()
+    out = orc.decode_batch(b.syndromes, threads=threads)
+    dt = time.perf_counter() - t0
+    return trials / dt, dt, int(wl.success(b, out["decoding"]).sum())
+
+
+def cpu_sample_size(kind, cores):
+    # q-ary: the reference's brute-force check node costs ~10 s per Kyber-512 decode and core -> one decode per
+    # thread is a 10-20 s sample.  binary: ~2-5 ms per decode and core -> 64 decodes per thread.
+    return cores if kind == "qary" else 64 * cores
+
+
+def run_reference(args, kind, wl, iters, cfg):
+    from oracle import oracle as O
+
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    cores = O.max_threads()
+    n = cpu_sample_size(kind, cores)
+    for _ in range(args.warmup):  # warm-up: thread pool, page-in (one iteration of one decode per thread)
+        cpu_path(kind, wl, iters, min(n, cores), cores, warm_only=True)
+    total_t, total_n = 0.0, 0
+    for _ in range(args.steps):
+        _, dt, _ = cpu_path(kind, wl, iters, n, cores)
+        total_t += dt
+        total_n += n
+    value = total_n / total_t
+    sample = f"{n} trials per step ({'1 decode' if kind == 'qary' else '64 decodes'} per thread), {args.steps} steps"
+    line = {
+        "impl": "reference", "metric": "decoded trials/sec", "value": value, "unit": "trials/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_t / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32" if kind == "qary" else "f64", "data": "synthetic",
+        "config": cfg,
+        "cpu_baseline": {"value": value, "unit": "trials/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "trials/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "edge_updates_per_sec": value * cfg["edges"] * (iters if kind == "qary" else 1),
+        "note": "CPU restatement of the reference algorithm (oracle/, brute-force check node, one decode per thread); "
+                "the reference's own Rust crate cannot be built in this image (no cargo/rustc)",
+    }
+    print(json.dumps(line), flush=True)
+
+
+# =====================================================================================================================
+# our arm
+# =====================================================================================================================
+def run_ours(args, kind, wl, iters, cfg):
+    import torch
+    import torch.distributed as dist
+
+    from sca_ldpc_b200 import QaryDecoder
+    from sca_ldpc_b200.ldpc import bp_decoder
+
+    rank, world, local = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU path")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    T = args.trials
+    seed = 1000 + rank  # every rank decodes its own independent trials
+
+    # ---- inputs: generated on the host, resident in HBM for `value`, in pinned host memory for `e2e`
+    batch = wl.generate(T, seed=seed)
+    if kind == "qary":
+        dec = QaryDecoder(wl.H, iters, device=local, **wl.decoder_kwargs)
+        h_in = [torch.from_numpy(batch.priors).pin_memory(), torch.from_numpy(batch.priors_sum).pin_memory()]
+        d_in = [t.to(dev) for t in h_in]
+        secret = torch.from_numpy(batch.secret).to(dev)
+        nssum = torch.from_numpy((-batch.ssum).astype(np.int8)).to(dev)
+        bv = wl.bvars
+
+        def step_dev():
+            hard, _, _ = dec.min_sum_batch(d_in[0], d_in[1], want_posterior=False)
+            ok = (hard[:, :bv] == secret).all(1) & (hard[:, bv:] == nssum).all(1)
+            return torch.stack((ok.sum(), torch.tensor(T, device=dev)))
+
+        def step_host():
+            hard, _, _ = dec.min_sum_batch(h_in[0].numpy(), h_in[1].numpy(), want_posterior=False)
+            return hard
+
+        h2d = sum(t.numel() * t.element_size() for t in h_in)
+        d2h = T * wl.N
+        edges = dec.E
+        iters_per_trial = lambda: float(max(1, iters))  # noqa: E731  (no early termination on the q-ary path)
+        bytes_iter = dec.algorithmic_bytes_per_trial_iteration()
+        # dominant kernel = check-node pass: reads + writes every message slot once, reads the sum-variable priors
+        cn_bytes = 8 * dec.msg_slots + 4 * (dec.R * dec.QS if dec.special else 0)
+        vn_bytes = 8 * (dec.msg_slots - (dec.R * dec.QS if dec.special else 0)) + 4 * dec.bvars * dec.Q
+    else:
+        dec = bp_decoder(csr=(wl.row_ptr, wl.col), shape=(wl.m, wl.n), max_iter=iters, channel_probs=wl.channel_probs,
+                         device=local)
+        h_in = [torch.from_numpy(batch.syndromes).pin_memory()]
+        d_in = [t.to(dev) for t in h_in]
+        truth = torch.zeros((T, wl.N), dtype=torch.uint8)
+        truth.scatter_(1, torch.from_numpy(batch.y), 1)
+        truth = truth.to(dev)
+        last = {}
+
+        def step_dev():
+            out = dec.decode_batch(d_in[0])
+            last["iters"] = out["iters"]
+            ok = (out["decoding"][:, : wl.N] == truth).all(1)
+            return torch.stack((ok.sum(), torch.tensor(T, device=dev)))
+
+        def step_host():
+            return dec.decode_batch(h_in[0].numpy())["decoding"]
+
+        h2d = T * wl.m
+        d2h = T * wl.n
+        edges = dec.E
+        iters_per_trial = lambda: float(last["iters"].float().mean().item())  # noqa: E731
+        bytes_iter = dec.algorithmic_bytes_per_trial_iteration()
+        cn_bytes = 8 * dec.E + (wl.m + 7) // 8
+        vn_bytes = 8 * dec.E + 4 * wl.n
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- value: device-resident inputs, CUDA events, max over ranks
+    for _ in range(max(3, args.warmup)):
+        counters = step_dev()
+    sync_all()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    l0 = dec.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync_all()
+    tw0 = time.perf_counter()
+    e0.record()
+    for _ in range(args.steps):
+        counters = step_dev()
+        if world > 1:
+            dist.all_reduce(counters)  # the path's only exchange: success / trial counters
+    e1.record()
+    sync_all()
+    tw1 = time.perf_counter()
+    launches = dec.launch_count - l0
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    clk = clocks.stop(tw0, tw1) if rank == 0 else None
+    successes, trials_total = (int(x) for x in counters.tolist())
+    ipt = iters_per_trial()
+
+    # ---- e2e: host buffers through the public API (H2D of the priors + D2H of the decisions inside the timed region)
+    for _ in range(2):
+        step_host()
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_host()
+    torch.cuda.synchronize()
+    dt = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    e2e_value = world * T * args.steps / float(dt.item())
+
+    # ---- roofline of the dominant kernel (rank 0, N=1 semantics: one GPU's kernel against one GPU's peak)
+    line = None
+    if rank == 0:
+        peak, peak_src = measured_peak_gbs()
+        st = torch.cuda.current_stream(dev).cuda_stream
+        step_dev()
+        torch.cuda.synchronize()
+        cn_ms = dec.time_kernel(0, T, reps=20, stream=st)
+        vn_ms = dec.time_kernel(1, T, reps=20, stream=st)
+        achieved = T * cn_bytes / (cn_ms * 1e-3) / 1e9
+        vn_achieved = T * vn_bytes / (vn_ms * 1e-3) / 1e9
+        roofline = {
+            "bound": "hbm", "kernel": "k_cn_fast (check-node pass)" if kind == "qary" else "k_bp_cn (check-to-bit pass)",
+            "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+            "peak_source": peak_src, "ms_per_launch": cn_ms, "algorithmic_bytes_per_launch": T * cn_bytes,
+            "second_kernel": {"kernel": "k_vn" if kind == "qary" else "k_bp_vn", "achieved": vn_achieved,
+                              "frac": vn_achieved / peak, "ms_per_launch": vn_ms,
+                              "algorithmic_bytes_per_launch": T * vn_bytes},
+            "iteration": {"bytes_per_trial_iteration_survey_8d": bytes_iter,
+                          "achieved": T * bytes_iter / ((cn_ms + vn_ms) * 1e-3) / 1e9,
+                          "frac": T * bytes_iter / ((cn_ms + vn_ms) * 1e-3) / 1e9 / peak},
+        }
+        traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(traffic_file):
+            try:
+                tr = json.load(open(traffic_file)).get(cfg["workload"])
+                if tr:
+                    roofline["traffic"] = tr["dram_bytes_per_launch"] * (T / tr["trials"])
+                    roofline["traffic_source"] = tr.get("source")
+            except Exception:
+                pass
+
+        # ---- cpu_baseline (N=1 only): bounded sample of the same workload on the host cores
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            from oracle import oracle as O
+
+            cores = O.max_threads()
+            n = cpu_sample_size(kind, cores)
+            v, secs, _ = cpu_path(kind, wl, iters, n, cores)
+            cpu = {"value": v, "unit": "trials/s", "cores": cores, "kind": "port",
+                   "sample": f"{n} trials of this workload, one decode per thread "
+                             f"({'brute-force check node as decoder_special.rs:531-554' if kind == 'qary' else 'fp64 product-sum'}), "
+                             f"{secs:.1f} s"}
+        value = world * T * args.steps / (ms * 1e-3)
+        line = {
+            "metric": "decoded trials/sec", "value": value, "unit": "trials/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+            "edge_updates_per_sec": value * edges * ipt, "iterations_per_trial": ipt,
+            "success_rate": successes / max(1, trials_total),
+            "clocks": clk,
+            "e2e": {"value": e2e_value, "unit": "trials/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": int(launches),
+            "roofline": roofline,
+            "cpu_baseline": cpu,
+        }
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if line is not None:
+        print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="kyber512", choices=sorted(WORKLOADS))
+    ap.add_argument("--trials", type=int, default=0, help="trials per GPU per step (default: the workload's)")
+    ap.add_argument("--iters", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    from sca_ldpc_b200.workloads import HqcWorkload, KyberWorkload
+
+    kind, kw, T, iters = WORKLOADS[args.workload]
+    args.trials = args.trials or T
+    iters = args.iters or iters
+    wl = KyberWorkload(seed=0, **kw) if kind == "qary" else HqcWorkload(seed=0, **kw)
+    if kind == "qary":
+        cfg = {"workload": f"{args.workload}: q-ary min-sum BP, H {wl.R}x{wl.N} (sum_weight {wl.sum_weight}, "
+                           f"check_blocks {wl.check_blocks}), alphabets {wl.Q}/{wl.QS}, {args.trials} trials per GPU per step, "
+                           f"{iters} iterations, no early termination (reference semantics)",
+               "trials_per_gpu": args.trials, "iterations": iters, "edges": int((wl.H != 0).sum()),
+               "check_node": "forward/backward (min,+)", "inputs": "larger than L2 (priors + messages > 1 GB per step)",
+               "oracle_accuracy": wl.accuracy}
+    else:
+        cfg = {"workload": f"{args.workload}: binary product-sum BP, n = {wl.N}+{wl.R}, row weight {wl.W}+1, "
+                           f"{args.trials} trials per GPU per step, max_iter {iters}, syndrome early stop",
+               "trials_per_gpu": args.trials, "iterations": iters, "edges": int(wl.row_ptr[-1]),
+               "inputs": "larger than L2 (messages > 1 GB per step)", "rho": wl.rho}
+    if args.impl == "reference":
+        run_reference(args, kind, wl, iters, cfg)
+    else:
+        run_ours(args, kind, wl, iters, cfg)
+
+
+if __name__ == "__main__":
+    main()

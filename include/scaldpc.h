@@ -136,7 +136,12 @@ void scaldpc_bp_destroy(scaldpc_bp *h);
  */
 int scaldpc_bp_decode(scaldpc_bp *h, int T, const uint8_t *synd, const double *channel_probs, uint8_t *decoding,
                       float *llr, int32_t *iters, int32_t *converged, unsigned flags, void *stream);
+/* Shape queries: checks, variables, edges, iteration cap (max_iter = 0 at create time means n, as upstream). */
+int scaldpc_bp_info(const scaldpc_bp *h, int *m, int *n, int *edges, int *max_iter);
 long long scaldpc_bp_launch_count(const scaldpc_bp *h);
+/* Per-kernel timing probe (bench.py roofline leg), as scaldpc_qary_time_kernel:
+ *   which  0 = check-to-bit kernel, 1 = bit-to-check kernel; every tile of the previous decode is re-activated. */
+int scaldpc_bp_time_kernel(scaldpc_bp *h, int which, int T, unsigned flags, int reps, void *stream, float *avg_ms);
 
 #ifdef __cplusplus
 }

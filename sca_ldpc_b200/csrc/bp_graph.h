@@ -1,0 +1,59 @@
+// Host-side Tanner-graph build for the binary BP decoder: CSR (rows ascending, columns ascending within a row --
+// the visiting order of ldpc.bp_decoder's row lists) -> CSC (rows ascending within a column).  Pure C++ so the
+// same code feeds the device upload and the CPU test model.
+#pragma once
+#include <stdint.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "../../include/scaldpc.h"
+
+namespace scaldpc {
+
+struct BpHostGraph {
+    int m = 0, n = 0, E = 0;
+    int dc_max = 0, dv_max = 0;
+    std::vector<int> row_ptr, col, col_ptr, csc_edge;
+};
+
+inline int build_bp_graph(int m, int n, const int32_t *row_ptr, const int32_t *col, BpHostGraph &g, std::string &err)
+{
+    auto bad = [&](int code, const std::string &msg) {
+        err = msg;
+        return code;
+    };
+    if (m <= 0 || n <= 0 || !row_ptr || !col) return bad(SCALDPC_ERR_ARG, "bad parity-check matrix");
+    if (row_ptr[0] != 0) return bad(SCALDPC_ERR_ARG, "row_ptr[0] must be 0");
+    g = BpHostGraph();
+    g.m = m;
+    g.n = n;
+    g.E = row_ptr[m];
+    if (g.E < 0) return bad(SCALDPC_ERR_ARG, "negative edge count");
+    g.row_ptr.assign(row_ptr, row_ptr + m + 1);
+    g.col.assign(col, col + g.E);
+    g.col_ptr.assign(n + 1, 0);
+    for (int r = 0; r < m; ++r) {
+        const int a = row_ptr[r], b = row_ptr[r + 1];
+        if (b < a) return bad(SCALDPC_ERR_ARG, "row_ptr must be non-decreasing");
+        g.dc_max = std::max(g.dc_max, b - a);
+        for (int e = a; e < b; ++e) {
+            if (col[e] < 0 || col[e] >= n) return bad(SCALDPC_ERR_ARG, "column index out of range in row " + std::to_string(r));
+            if (e > a && col[e] <= col[e - 1])
+                return bad(SCALDPC_ERR_ARG, "columns must be strictly ascending within row " + std::to_string(r));
+            g.col_ptr[col[e] + 1]++;
+        }
+    }
+    for (int c = 0; c < n; ++c) {
+        g.dv_max = std::max(g.dv_max, g.col_ptr[c + 1]);
+        g.col_ptr[c + 1] += g.col_ptr[c];
+    }
+    g.csc_edge.resize(std::max(1, g.E));
+    std::vector<int> fill(n, 0);
+    for (int r = 0; r < m; ++r)
+        for (int e = row_ptr[r]; e < row_ptr[r + 1]; ++e) g.csc_edge[g.col_ptr[col[e]] + fill[col[e]]++] = e;
+    return SCALDPC_OK;
+}
+
+}  // namespace scaldpc

@@ -1,0 +1,193 @@
+"""Drop-in for `ldpc.bp_decoder` (third-party PyPI ldpc==0.1.3, simulate-with-python/requirements.txt:8) as the
+reference uses it:
+
+    simulate/hqc.py:694-708     bpd = bp_decoder(H, max_iter=100, bp_method="product_sum", channel_probs=...)
+                                decoded = bpd.decode(msg)            # len(msg) == n: received vector
+    simulate/decode.py:155-171  bpd = bp_decoder(H, error_rate=..., max_iter=n, bp_method="product_sum",
+                                                 channel_probs=[None]*n or [...])
+                                decoding = bpd.decode(syndrome)      # len == m: syndrome
+
+plus the batched entry point `decode_batch` (T syndromes resident on one B200, per-trial early stop).
+The message passing runs on the GPU through scaldpc_bp_decode; nothing here computes messages on the host.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import types
+
+import numpy as np
+
+from . import _lib
+
+try:
+    import torch
+except Exception:  # pragma: no cover
+    torch = None
+
+
+def _csr_from_any(H):
+    """dense ndarray / scipy.sparse matrix -> (m, n, row_ptr int32, col int32) with entries taken mod 2."""
+    if hasattr(H, "tocsr"):
+        S = H.tocsr().copy()
+        S.data = S.data % 2
+        S.eliminate_zeros()
+        S.sort_indices()
+        return S.shape[0], S.shape[1], S.indptr.astype(np.int32), S.indices.astype(np.int32)
+    H = np.asarray(H)
+    if H.ndim != 2:
+        raise ValueError("parity check matrix must be 2-D")
+    m, n = H.shape
+    rows, cols = np.nonzero(H % 2)
+    row_ptr = np.zeros(m + 1, dtype=np.int64)
+    np.add.at(row_ptr, rows + 1, 1)
+    return m, n, np.cumsum(row_ptr).astype(np.int32), cols.astype(np.int32)
+
+
+class bp_decoder:
+    """bp_decoder(H, error_rate=None, max_iter=0, bp_method="product_sum", channel_probs=[None])
+
+    H may be a dense 0/1 array, a scipy.sparse matrix, or `csr=(row_ptr, col), shape=(m, n)`.
+    Attributes after decode(): log_prob_ratios, iter, converge (as upstream).
+    """
+
+    def __init__(self, H=None, error_rate=None, max_iter=0, bp_method="product_sum", channel_probs=None, *,
+                 csr=None, shape=None, device=0, **unused):
+        if bp_method not in ("product_sum", "ps", 0):
+            raise ValueError("only bp_method='product_sum' is implemented (the method the reference uses)")
+        if csr is not None:
+            self.m, self.n = (int(x) for x in shape)
+            row_ptr, col = (np.ascontiguousarray(a, dtype=np.int32) for a in csr)
+        else:
+            self.m, self.n, row_ptr, col = _csr_from_any(H)
+        self.row_ptr, self.col = np.ascontiguousarray(row_ptr), np.ascontiguousarray(col)
+        cp = None
+        if channel_probs is not None and len(channel_probs) and channel_probs[0] is not None:
+            cp = np.asarray(channel_probs, dtype=np.float64)
+            if cp.shape != (self.n,):
+                raise ValueError(f"channel_probs must have length n = {self.n}")
+        elif error_rate is not None:
+            cp = np.full(self.n, float(error_rate), dtype=np.float64)
+        else:
+            raise ValueError("either error_rate or channel_probs is required")
+        self.channel_probs = np.ascontiguousarray(cp)
+        self.device = int(device)
+        self._h = C.c_void_p()
+        _lib.check(_lib.lib().scaldpc_bp_create(self.m, self.n, self.row_ptr.ctypes.data, self.col.ctypes.data,
+                                                int(max_iter), self.device, C.byref(self._h)))
+        vals = [C.c_int() for _ in range(4)]
+        _lib.check(_lib.lib().scaldpc_bp_info(self._h, *[C.byref(v) for v in vals]))
+        self.E, self.max_iter = vals[2].value, vals[3].value
+        self.log_prob_ratios = np.zeros(self.n)
+        self.iter = 0
+        self.converge = 0
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h and _lib._lib is not None:
+            _lib._lib.scaldpc_bp_destroy(h)
+
+    # ---- upstream-shaped single decode ---------------------------------------------------------------------
+    def syndrome_of(self, v):
+        v = np.asarray(v).astype(np.uint8) & 1
+        s = np.zeros(self.m, dtype=np.uint8)
+        rows = np.repeat(np.arange(self.m), np.diff(self.row_ptr))
+        np.bitwise_xor.at(s, rows, v[self.col])
+        return s
+
+    def decode(self, vec):
+        vec = np.asarray(vec).astype(np.uint8) & 1
+        if vec.shape[0] == self.n:       # received vector: decode its syndrome, return the corrected vector
+            synd, received = self.syndrome_of(vec), vec
+        elif vec.shape[0] == self.m:     # syndrome: return the error estimate
+            synd, received = vec, None
+        else:
+            raise ValueError("input vector has the wrong length")
+        out = self.decode_batch(synd[None], want_llr=True)
+        self.log_prob_ratios = out["log_prob_ratios"][0].astype(np.float64)
+        self.iter = int(out["iters"][0])
+        self.converge = int(out["converged"][0])
+        dec = out["decoding"][0]
+        if received is not None:
+            dec = dec ^ received
+        return dec.astype(int)
+
+    # ---- batched fast path -------------------------------------------------------------------------------
+    def decode_batch(self, syndromes, channel_probs=None, *, want_llr=False, early_stop=True):
+        """syndromes (T, m) uint8; channel_probs None (the constructor's), (n,) or (T, n) float64.
+        numpy in -> numpy out; torch CUDA uint8 tensor in -> torch CUDA tensors out.
+        Returns dict(decoding (T,n) uint8, log_prob_ratios (T,n) float32 or None, iters (T,), converged (T,))."""
+        flags = 0 if early_stop else _lib.BP_NO_EARLY_STOP
+        if torch is not None and isinstance(syndromes, torch.Tensor) and syndromes.is_cuda:
+            return self._batch_torch(syndromes, channel_probs, flags, want_llr)
+        synd = np.ascontiguousarray(syndromes, dtype=np.uint8)
+        T = synd.shape[0]
+        if synd.shape != (T, self.m):
+            raise ValueError(f"syndromes must be (T, {self.m}), got {synd.shape}")
+        cp = self.channel_probs if channel_probs is None else np.ascontiguousarray(channel_probs, dtype=np.float64)
+        if cp.ndim == 2:
+            if cp.shape != (T, self.n):
+                raise ValueError(f"channel_probs must be ({T}, {self.n})")
+            flags |= _lib.BP_PROBS_PER_TRIAL
+        elif cp.shape != (self.n,):
+            raise ValueError(f"channel_probs must have length {self.n}")
+        dec = np.empty((T, self.n), np.uint8)
+        llr = np.empty((T, self.n), np.float32) if want_llr else None
+        iters = np.empty(T, np.int32)
+        conv = np.empty(T, np.int32)
+        p = lambda a: None if a is None else a.ctypes.data  # noqa: E731
+        _lib.check(_lib.lib().scaldpc_bp_decode(self._h, T, p(synd), p(cp), p(dec), p(llr), p(iters), p(conv), flags,
+                                                None))
+        return dict(decoding=dec, log_prob_ratios=llr, iters=iters, converged=conv)
+
+    def _batch_torch(self, synd, channel_probs, flags, want_llr):
+        dev = torch.device("cuda", self.device)
+        synd = synd.contiguous()
+        T = synd.shape[0]
+        if synd.dtype != torch.uint8 or tuple(synd.shape) != (T, self.m) or synd.device != dev:
+            raise ValueError(f"syndromes must be a uint8 (T, {self.m}) tensor on {dev}")
+        if channel_probs is None:
+            cp = getattr(self, "_cp_dev", None)
+            if cp is None:
+                cp = self._cp_dev = torch.from_numpy(self.channel_probs).to(dev)
+        else:
+            cp = channel_probs.contiguous()
+            if cp.dtype != torch.float64 or cp.device != dev:
+                raise ValueError("channel_probs must be a float64 tensor on the decoder's device")
+            if cp.dim() == 2:
+                flags |= _lib.BP_PROBS_PER_TRIAL
+        dec = torch.empty((T, self.n), dtype=torch.uint8, device=dev)
+        llr = torch.empty((T, self.n), dtype=torch.float32, device=dev) if want_llr else None
+        iters = torch.empty(T, dtype=torch.int32, device=dev)
+        conv = torch.empty(T, dtype=torch.int32, device=dev)
+        p = lambda t: None if t is None else t.data_ptr()  # noqa: E731
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        _lib.check(_lib.lib().scaldpc_bp_decode(self._h, T, p(synd), p(cp), p(dec), p(llr), p(iters), p(conv),
+                                                flags | _lib.DEVICE_PTRS, C.c_void_p(stream)))
+        return dict(decoding=dec, log_prob_ratios=llr, iters=iters, converged=conv)
+
+    @property
+    def launch_count(self) -> int:
+        return int(_lib.lib().scaldpc_bp_launch_count(self._h))
+
+    def time_kernel(self, which: int, T: int, reps: int = 20, stream=None) -> float:
+        ms = C.c_float()
+        _lib.check(_lib.lib().scaldpc_bp_time_kernel(self._h, which, T, 0, reps,
+                                                     C.c_void_p(stream) if stream else None, C.byref(ms)))
+        return ms.value
+
+    def algorithmic_bytes_per_trial_iteration(self) -> int:
+        """SURVEY.md 8(d), binary case: 16*E + 4*n + m/8 bytes."""
+        return 16 * self.E + 4 * self.n + (self.m + 7) // 8
+
+
+def _rep_code(n):
+    """ldpc.codes.rep_code(n): (n-1) x n parity-check matrix of the repetition code (main.py:41-42)."""
+    H = np.zeros((n - 1, n), dtype=int)
+    idx = np.arange(n - 1)
+    H[idx, idx] = 1
+    H[idx, idx + 1] = 1
+    return H
+
+
+codes = types.ModuleType("ldpc.codes")
+codes.rep_code = _rep_code

@@ -1,0 +1,194 @@
+"""Host-side mirror of the reference's q-ary decoder objects over the libscaldpc C ABI.
+
+Reference interface mirrored (paths relative to simulate-with-python/):
+  simulate_rs/src/pydecoder.rs:13-71    class DecoderN{n}R{r}V{v}C{c}B{b}:  __new__(H, iterations), min_sum(probs)
+  simulate_rs/src/pydecoder.rs:85-150   class DecoderN{n}R{r}SW{sw}:        __new__(H, iterations),
+                                                                           min_sum(probs, probs_sum)
+  simulate_rs/src/lib.rs:32-75          the registered concrete shapes
+The compute runs on the GPU through scaldpc_qary_decode; nothing here computes messages on the host.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+
+import numpy as np
+
+from . import _lib
+
+try:  # torch is plumbing only (device buffers / streams); numpy-only use works without it
+    import torch
+except Exception:  # pragma: no cover
+    torch = None
+
+
+def _is_torch(x) -> bool:
+    return torch is not None and isinstance(x, torch.Tensor)
+
+
+class QaryDecoder:
+    """q-ary min-sum decoder on one B200.
+
+    QaryDecoder(H, iterations, B=b, DV=v, DC=c)                 <-> Decoder<N,R,DV,DC,2B+1,B,i8>   (decoder.rs)
+    QaryDecoder(H, iterations, B=b, BSUM=bsum, DV=v, DC=sw+1)   <-> DecoderSpecial<...>            (decoder_special.rs)
+    """
+
+    def __init__(self, H, iterations, B, BSUM=0, DV=0, DC=0, shape=None, device=0):
+        H = np.asarray(H) if not _is_torch(H) else H.cpu().numpy()
+        if H.dtype != np.int8:
+            # pyo3: PyReadonlyArray2<i8> extraction failure (pydecoder.rs:24, 96)
+            raise TypeError(f"parity check matrix must be a 2-D int8 array, got dtype {H.dtype}")
+        if H.ndim != 2:
+            raise TypeError(f"parity check matrix must be 2-D, got {H.ndim}-D")
+        if int(iterations) < 0:
+            raise OverflowError("iterations must be a non-negative integer (u32, pydecoder.rs:24)")
+        if shape is not None:
+            # the reference copies py_parity_check[(row, col)] for the class's const R x N (pydecoder.rs:28-33):
+            # a larger array is cropped, a smaller one panics on the out-of-bounds index
+            if H.shape[0] < shape[0] or H.shape[1] < shape[1]:
+                raise IndexError(f"parity check matrix is {H.shape[0]}x{H.shape[1]}, smaller than the decoder "
+                                 f"class's {shape[0]}x{shape[1]} (ndarray index out of bounds, pydecoder.rs:31)")
+            H = H[: shape[0], : shape[1]]
+        R, N = H.shape
+        H = np.ascontiguousarray(H)
+        self._h = C.c_void_p()
+        self._lock = threading.Lock()
+        _lib.check(_lib.lib().scaldpc_qary_create(H.ctypes.data, R, N, int(B), int(BSUM), int(DV), int(DC),
+                                                  int(iterations), int(device), C.byref(self._h)))
+        vals = [C.c_int() for _ in range(7)]
+        _lib.check(_lib.lib().scaldpc_qary_info(self._h, *[C.byref(v) for v in vals]))
+        self.R, self.N, self.bvars, self.Q, self.QS, self.E, self.iterations = [v.value for v in vals]
+        self.B, self.BSUM, self.device = int(B), int(BSUM), int(device)
+        self.special = self.BSUM > 0
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h and _lib._lib is not None:
+            _lib._lib.scaldpc_qary_destroy(h)
+
+    # ------------------------------------------------------------------------------------------------------
+    # reference-shaped entry point (pydecoder.rs:53-65, 125-145): probabilities in, list of ints out
+    # ------------------------------------------------------------------------------------------------------
+    def min_sum(self, channel_output, channel_output_sum=None):
+        co = self._one(channel_output, self.bvars, self.Q, "channel_output")
+        cos = None
+        if self.special:
+            if channel_output_sum is None:
+                raise TypeError("min_sum() missing 1 required positional argument: 'channel_output_sum'")
+            cos = self._one(channel_output_sum, self.R, self.QS, "channel_output_sum")
+        elif channel_output_sum is not None:
+            raise TypeError("min_sum() takes 1 positional argument but 2 were given")
+        hard, _, _ = self.min_sum_batch(co[None], None if cos is None else cos[None], want_posterior=False)
+        return [int(x) for x in hard[0]]
+
+    @staticmethod
+    def _one(x, rows, q, name):
+        x = np.asarray(x)
+        if x.dtype != np.float32:
+            raise TypeError(f"{name} must be a float32 array (pydecoder.rs:53), got {x.dtype}")
+        if x.ndim != 2 or x.shape[0] < rows or x.shape[1] < q:
+            raise ValueError(f"{name} must be at least {rows}x{q}, got {x.shape}")
+        return np.ascontiguousarray(x[:rows, :q])
+
+    # ------------------------------------------------------------------------------------------------------
+    # batched fast path: T independent decodes resident on the device
+    # ------------------------------------------------------------------------------------------------------
+    def min_sum_batch(self, priors, priors_sum=None, *, llr=False, want_posterior=True, exact=False,
+                      generic=False, want_status=False):
+        """Decode T trials.
+
+        priors      (T, bvars, Q)  float32 probabilities (or LLRs with llr=True); numpy array or torch CUDA tensor
+        priors_sum  (T, R, QS)     float32, special decoder only
+        Returns (hard int8 (T, N), posterior (T, bvars, Q) or None, posterior_sum (T, R, QS) or None)
+        [+ status int32 (T,) with want_status=True instead of raising on per-trial input errors].
+        numpy in -> numpy out (host buffers, copies inside the call); torch CUDA in -> torch CUDA out
+        (asynchronous on the current stream).
+        """
+        flags = (_lib.IN_LLR if llr else 0) | (_lib.CN_EXACT if exact else 0) | (_lib.CN_GENERIC if generic else 0)
+        on_dev = _is_torch(priors) and priors.is_cuda
+        if self.special and priors_sum is None:
+            raise TypeError("the special decoder needs priors_sum")
+        if on_dev:
+            return self._batch_torch(priors, priors_sum, flags, want_posterior, want_status)
+        x = np.ascontiguousarray(priors, dtype=np.float32)
+        T = x.shape[0]
+        if x.shape != (T, self.bvars, self.Q):
+            raise ValueError(f"priors must be (T, {self.bvars}, {self.Q}), got {x.shape}")
+        xs = None
+        if self.special:
+            xs = np.ascontiguousarray(priors_sum, dtype=np.float32)
+            if xs.shape != (T, self.R, self.QS):
+                raise ValueError(f"priors_sum must be (T, {self.R}, {self.QS}), got {xs.shape}")
+        hard = np.empty((T, self.N), np.int8)
+        post = np.empty((T, self.bvars, self.Q), np.float32) if want_posterior else None
+        posts = np.empty((T, self.R, self.QS), np.float32) if (want_posterior and self.special) else None
+        status = np.zeros(T, np.int32)
+        p = lambda a: None if a is None else a.ctypes.data  # noqa: E731
+        with self._lock:
+            rc = _lib.lib().scaldpc_qary_decode(self._h, T, p(x), p(xs), p(hard), p(post), p(posts), p(status), flags,
+                                                None)
+        return self._finish(rc, hard, post, posts, status, want_status)
+
+    def _batch_torch(self, x, xs, flags, want_posterior, want_status):
+        dev = torch.device("cuda", self.device)
+        if x.device != dev or x.dtype != torch.float32:
+            raise ValueError(f"priors must be a float32 tensor on {dev}")
+        x = x.contiguous()
+        T = x.shape[0]
+        if tuple(x.shape) != (T, self.bvars, self.Q):
+            raise ValueError(f"priors must be (T, {self.bvars}, {self.Q}), got {tuple(x.shape)}")
+        if self.special:
+            if xs.device != dev or xs.dtype != torch.float32 or tuple(xs.shape) != (T, self.R, self.QS):
+                raise ValueError(f"priors_sum must be a float32 (T, {self.R}, {self.QS}) tensor on {dev}")
+            xs = xs.contiguous()
+        hard = torch.empty((T, self.N), dtype=torch.int8, device=dev)
+        post = torch.empty((T, self.bvars, self.Q), dtype=torch.float32, device=dev) if want_posterior else None
+        posts = (torch.empty((T, self.R, self.QS), dtype=torch.float32, device=dev)
+                 if (want_posterior and self.special) else None)
+        status = torch.zeros(T, dtype=torch.int32, device=dev) if want_status else None
+        p = lambda t: None if t is None else t.data_ptr()  # noqa: E731
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        with self._lock:
+            rc = _lib.lib().scaldpc_qary_decode(self._h, T, p(x), p(xs if self.special else None), p(hard), p(post),
+                                                p(posts), p(status), flags | _lib.DEVICE_PTRS, C.c_void_p(stream))
+        return self._finish(rc, hard, post, posts, status, want_status)
+
+    @staticmethod
+    def _finish(rc, hard, post, posts, status, want_status):
+        if want_status and rc in (_lib.ERR_PROB_SUM, _lib.ERR_NO_MAX, _lib.ERR_NO_CONFIG):
+            return hard, post, posts, status
+        if rc in (_lib.ERR_PROB_SUM, _lib.ERR_NO_MAX, _lib.ERR_NO_CONFIG):
+            # the reference panics here (decoder.rs:618, 680, 683-684) -> PanicException; we raise ValueError
+            raise ValueError(_lib.lib().scaldpc_last_error().decode())
+        _lib.check(rc)
+        return (hard, post, posts, status) if want_status else (hard, post, posts)
+
+    # ------------------------------------------------------------------------------------------------------
+    def set_iterations(self, iterations: int):
+        _lib.check(_lib.lib().scaldpc_qary_set_max_iter(self._h, int(iterations)))
+        self.iterations = int(iterations)
+
+    @property
+    def launch_count(self) -> int:
+        return int(_lib.lib().scaldpc_qary_launch_count(self._h))
+
+    def time_kernel(self, which: int, T: int, reps: int = 20, exact=False, generic=False, stream=None) -> float:
+        """Average duration (ms) of one check-node (which=0) or variable-node (which=1) launch over T trials,
+        CUDA events on `stream`, on the message state left by the previous decode (bench.py roofline leg)."""
+        ms = C.c_float()
+        flags = (_lib.CN_EXACT if exact else 0) | (_lib.CN_GENERIC if generic else 0)
+        _lib.check(_lib.lib().scaldpc_qary_time_kernel(self._h, which, T, flags, reps,
+                                                       C.c_void_p(stream) if stream else None, C.byref(ms)))
+        return ms.value
+
+    # algorithmic HBM bytes of SURVEY.md 8(d): per trial-iteration 16*sum_e Q_e + 4*sum_v Q_v
+    @property
+    def msg_slots(self) -> int:
+        return (self.E - (self.R if self.special else 0)) * self.Q + (self.R * self.QS if self.special else 0)
+
+    @property
+    def prior_slots(self) -> int:
+        return self.bvars * self.Q + (self.R * self.QS if self.special else 0)
+
+    def algorithmic_bytes_per_trial_iteration(self) -> int:
+        return 16 * self.msg_slots + 4 * self.prior_slots

@@ -3,8 +3,10 @@
 // handling, in-place message updates) can be checked against the oracle in the `-m "not gpu"` test tier, on a
 // machine without a GPU.  This file is never linked into libscaldpc.so and the product has no CPU path.
 //
-// Only kernels whose threads are independent are modelled (k_cn_fast, k_cn_generic, k_vn, k_init_v2c); the two
-// layout-conversion kernels cooperate through shared memory and are replaced by plain loops here.
+// Only kernels whose threads are independent are modelled (k_cn_fast, k_cn_generic, k_vn, k_init_v2c, k_bp_cn,
+// k_bp_vn, k_bp_syndrome, k_bp_finish_iter -- their warp ballots are replaced by per-lane read-modify-writes under
+// SCALDPC_HOST_MODEL); the layout-conversion kernels cooperate through shared memory and are replaced by plain
+// loops here.
 #include <math.h>
 #include <stdint.h>
 #include <stdlib.h>
@@ -46,6 +48,8 @@ using std::min;
 
 #include "../../sca_ldpc_b200/csrc/qary_graph.h"
 #include "../../sca_ldpc_b200/csrc/qary_kernels.cuh"
+#include "../../sca_ldpc_b200/csrc/bp_graph.h"
+#include "../../sca_ldpc_b200/csrc/bp_kernels.cuh"
 
 using namespace scaldpc;
 
@@ -171,6 +175,70 @@ int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
     }
     scaldpc_host_model_smem = nullptr;
     return worst;
+}
+
+
+// Binary product-sum BP through the modelled kernels.  synd (T x m bytes), probs (n or T x n doubles);
+// outputs decoding (T x n bytes), llr (T x n floats, may be NULL), iters / conv (T ints).
+int hostmodel_bp_decode(int m, int n, const int32_t *row_ptr, const int32_t *col, int max_iter, int T,
+                        const uint8_t *synd, const double *probs, int probs_per_trial, int early_stop,
+                        uint8_t *decoding, float *llr, int32_t *iters, int32_t *conv)
+{
+    BpHostGraph g;
+    std::string err;
+    int rc = build_bp_graph(m, n, row_ptr, col, g, err);
+    if (rc) return rc;
+    if (max_iter == 0) max_iter = n;
+    const int tiles = (T + 31) / 32;
+    const size_t lanes = (size_t)tiles * 32;
+    std::vector<float> msg(std::max<size_t>(1, lanes * g.E)), prior(probs_per_trial ? lanes * n : n), post(lanes * n);
+    std::vector<uint32_t> synd_w((size_t)tiles * m, 0), dec_w((size_t)tiles * n, 0), done(tiles, 0), valid(tiles, 0),
+        unsat(tiles, 0);
+    std::vector<int> vit(lanes, max_iter), vconv(lanes, 0);
+    int n_active = 0;
+    for (int t = 0; t < T; ++t) {
+        valid[t / 32] |= 1u << (t % 32);
+        for (int c = 0; c < m; ++c)
+            if (synd[(size_t)t * m + c] & 1) synd_w[(size_t)(t / 32) * m + c] |= 1u << (t % 32);
+    }
+    if (probs_per_trial) {
+        for (size_t t = 0; t < lanes; ++t)
+            for (int v = 0; v < n; ++v) {
+                const double q = t < (size_t)T ? probs[t * n + v] : 0.5;
+                prior[((t / 32) * n + v) * 32 + t % 32] = (float)log((1.0 - q) / q);
+            }
+    } else {
+        for (int v = 0; v < n; ++v) prior[v] = (float)log((1.0 - probs[v]) / probs[v]);
+    }
+    BpDev p;
+    p.m = m; p.n = n; p.E = g.E; p.dc_max = std::max(1, g.dc_max); p.dv_max = std::max(1, g.dv_max);
+    p.per_trial_prior = probs_per_trial;
+    p.row_ptr = g.row_ptr.data(); p.col = g.col.data(); p.col_ptr = g.col_ptr.data(); p.csc_edge = g.csc_edge.data();
+    p.msg = msg.data(); p.prior = prior.data(); p.synd_w = synd_w.data(); p.dec_w = dec_w.data();
+    p.post = llr ? post.data() : nullptr;
+    p.done = done.data(); p.valid = valid.data(); p.unsat = unsat.data(); p.iters = vit.data(); p.conv = vconv.data();
+    p.n_active = &n_active;
+    std::vector<float> scratch((size_t)kBpWarps * 2 * std::max(p.dc_max, p.dv_max) * 32);
+    scaldpc_host_model_smem = scratch.data();
+    const int tb = (tiles + 255) / 256;
+    for (int it = 1; it <= max_iter; ++it) {
+        run_grid((m + kBpWarps - 1) / kBpWarps, tiles, kBpWarps * 32, k_bp_cn, p, (int)(it == 1));
+        run_grid((n + kBpWarps - 1) / kBpWarps, tiles, kBpWarps * 32, k_bp_vn, p);
+        run_grid((m + 255) / 256, tiles, 256, k_bp_syndrome, p);
+        n_active = 0;
+        run_grid(tb, 1, 256, k_bp_finish_iter, p, tiles, it, early_stop, (int)(it == max_iter));
+        if (early_stop && n_active == 0) break;
+    }
+    scaldpc_host_model_smem = nullptr;
+    for (int t = 0; t < T; ++t) {
+        for (int v = 0; v < n; ++v) {
+            decoding[(size_t)t * n + v] = (dec_w[(size_t)(t / 32) * n + v] >> (t % 32)) & 1u;
+            if (llr) llr[(size_t)t * n + v] = post[((size_t)(t / 32) * n + v) * 32 + t % 32];
+        }
+        iters[t] = vit[t];
+        conv[t] = vconv[t];
+    }
+    return 0;
 }
 
 }  // extern "C"

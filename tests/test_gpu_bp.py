@@ -1,0 +1,109 @@
+"""Parity of the CUDA binary product-sum BP (through the C ABI / the ldpc.bp_decoder-shaped class) with the fp64 CPU
+oracle and the committed fixtures.  Bars: hard decisions, iteration counts and convergence flags identical;
+posterior LLRs within 2e-3 + 2e-4*|L| (fp32 LLR domain vs fp64 probability ratios; parity of this path is
+"unpinned" upstream, see oracle/bp_oracle.c)."""
+import numpy as np
+import pytest
+
+import util
+from oracle import oracle as O
+from sca_ldpc_b200.ldpc import bp_decoder
+from sca_ldpc_b200.workloads import HqcWorkload
+
+pytestmark = pytest.mark.gpu
+
+
+def test_hqc_toy_through_the_boundary():
+    """hqc.py:694-708 call shape on the toy of hqc.py:1229-1274 (outcome pinned by the reference: y recovered)."""
+    z = util.load("hqc_toy.npz")
+    H = util.dense(z, with_vals=False)
+    bpd = bp_decoder(H, max_iter=100, bp_method="product_sum", channel_probs=z["channel_probs"])
+    decoded = bpd.decode(z["msg"])
+    assert sorted(np.nonzero(decoded[:20])[0].tolist()) == z["y_sparse"].tolist()
+    assert np.array_equal(decoded, z["decoded"]) and bpd.iter == int(z["iters"]) and bpd.converge == 1
+    assert util.llr_close(bpd.log_prob_ratios, z["log_prob_ratios"])
+
+
+def test_hqc_small_fixture():
+    z = util.load("hqc_small.npz")
+    H = util.dense(z, with_vals=False)
+    bpd = bp_decoder(H, max_iter=100, bp_method="product_sum", channel_probs=z["channel_probs"])
+    decoded = bpd.decode(z["msg"])
+    assert np.array_equal(decoded, z["decoded"]) and bpd.iter == int(z["iters"])
+    assert bpd.converge == int(z["converged"])
+    assert util.llr_close(bpd.log_prob_ratios, z["log_prob_ratios"])
+
+
+def test_rep_code_fer_loop():
+    """decode.py:139-171: error_rate + channel_probs=[None]*n, syndrome in -> error pattern out; 100/100."""
+    from sca_ldpc_b200.ldpc import codes
+
+    H = codes.rep_code(13)
+    bpd = bp_decoder(H, error_rate=0.05, max_iter=13, bp_method="product_sum", channel_probs=[None] * 13)
+    rs = np.random.RandomState(0)
+    ok = 0
+    for _ in range(100):
+        err = (rs.rand(13) < 0.05).astype(int)
+        ok += int((bpd.decode(H @ err % 2) == err).all())
+    assert ok == 100
+
+
+def test_batch_early_stop_freeze_and_torch():
+    import torch
+
+    w = HqcWorkload(variant=(499, 6), W=9, R=230, rho=0.97, seed=3)
+    batch = w.generate(45, seed=11)
+    synd = batch.syndromes.copy()
+    synd[7] = np.random.RandomState(1).randint(0, 2, w.R)
+    orc = O.BinaryBpOracle(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=20, channel_probs=w.channel_probs)
+    ref = orc.decode_batch(synd)
+    bpd = bp_decoder(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=20, channel_probs=w.channel_probs)
+    out = bpd.decode_batch(synd, want_llr=True)
+    assert np.array_equal(out["iters"], ref["iters"]) and np.array_equal(out["converged"], ref["converged"])
+    assert np.array_equal(out["decoding"], ref["decoding"])
+    for t in range(45):
+        assert util.llr_close(out["log_prob_ratios"][t], ref["log_prob_ratios"][t]), t
+    tout = bpd.decode_batch(torch.from_numpy(synd).cuda(), want_llr=False)
+    torch.cuda.synchronize()
+    assert np.array_equal(tout["decoding"].cpu().numpy(), ref["decoding"])
+    assert np.array_equal(tout["iters"].cpu().numpy(), ref["iters"])
+
+
+def test_per_trial_priors():
+    w = HqcWorkload(variant=(307, 5), W=7, R=150, rho=0.98, seed=5)
+    batch = w.generate(5, seed=2)
+    rs = np.random.RandomState(9)
+    probs = np.tile(w.channel_probs, (5, 1)) * rs.uniform(0.5, 1.5, size=(5, w.n))
+    orc = O.BinaryBpOracle(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=15, channel_probs=w.channel_probs)
+    ref = orc.decode_batch(batch.syndromes, channel_probs=probs)
+    bpd = bp_decoder(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=15, channel_probs=w.channel_probs)
+    out = bpd.decode_batch(batch.syndromes, channel_probs=probs, want_llr=True)
+    assert np.array_equal(out["iters"], ref["iters"]) and np.array_equal(out["decoding"], ref["decoding"])
+    for t in range(5):
+        assert util.llr_close(out["log_prob_ratios"][t], ref["log_prob_ratios"][t]), t
+    out2 = bpd.decode_batch(batch.syndromes, channel_probs=probs, early_stop=False)
+    assert (out2["iters"] == 15).all()
+
+
+def test_hqc128_full_size():
+    """BASELINE.json configs[3]: HQC-128 (n = 17669 + R), W=50, R=3000, rho=0.9942.  A few trials against the fp64
+    oracle, then a larger batch through size-independent properties: converged trials reproduce their syndrome,
+    successful trials recover y exactly."""
+    w = HqcWorkload("hqc128", W=50, R=3000, rho=0.9942, seed=0)
+    batch = w.generate(96, seed=1)
+    bpd = bp_decoder(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=100, channel_probs=w.channel_probs)
+    out = bpd.decode_batch(batch.syndromes, want_llr=True)
+    orc = O.BinaryBpOracle(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=100, channel_probs=w.channel_probs)
+    ref = orc.decode_batch(batch.syndromes[:6])
+    assert np.array_equal(out["iters"][:6], ref["iters"]) and np.array_equal(out["decoding"][:6], ref["decoding"])
+    for t in range(6):
+        assert util.llr_close(out["log_prob_ratios"][t], ref["log_prob_ratios"][t]), t
+    conv = out["converged"].astype(bool)
+    assert conv.mean() > 0.9
+    dec = out["decoding"]
+    rows = np.repeat(np.arange(w.m), np.diff(w.row_ptr))
+    for t in np.nonzero(conv)[0][:16]:
+        s = np.zeros(w.m, np.uint8)
+        np.bitwise_xor.at(s, rows, dec[t][w.col])
+        assert np.array_equal(s, batch.syndromes[t])
+    assert w.success(batch, dec)[conv].mean() > 0.9

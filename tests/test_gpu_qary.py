@@ -1,0 +1,204 @@
+"""Parity of the CUDA q-ary decoder (through the C ABI / the simulate_rs-shaped Python classes) with the CPU oracle
+and the committed golden fixtures.  Bars: hard decisions bit-identical; posteriors bit-identical in exact-order
+mode, within 1e-4 absolute with identical inf/NaN masks in the fast (forward/backward) mode -- the tolerance
+BASELINE.json's north_star states."""
+import json
+from concurrent.futures import ThreadPoolExecutor
+
+import numpy as np
+import pytest
+
+import util
+from oracle import oracle as O
+from sca_ldpc_b200 import QaryDecoder, simulate_rs
+from sca_ldpc_b200.workloads import KyberWorkload
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+def _corrupted(n):
+    co = np.zeros((n, 15), np.float32)
+    co[:, 7] = 1.0
+    co[1, 7], co[1, 14] = 0.1, 0.9
+    return co
+
+
+def test_rust_unit_tests_through_the_boundary():
+    """decoder.rs:770-854 via simulate_rs.DecoderN6R3V3C4B7 and a synthesised DecoderN450R150V3C7B7."""
+    z = util.load("rust_unit_tests.npz")
+    d = simulate_rs.DecoderN6R3V3C4B7(z["H6"], 10)
+    assert d.min_sum(_corrupted(6)) == [0] * 6
+    dm = simulate_rs.DecoderN450R150V3C7B7(util.dense(z, "Hm"), 10)
+    assert dm.min_sum(_corrupted(450)) == [0] * 450
+    for exact in (True, False):
+        hard, post, _ = dm.min_sum_batch(_corrupted(450)[None], exact=exact)
+        assert np.array_equal(hard[0], z["medium_hard"])
+        if exact:
+            assert np.array_equal(post[0], z["medium_post"], equal_nan=True)
+        else:
+            assert util.same_nonfinite(post[0], z["medium_post"]) and util.max_abs_diff(post[0], z["medium_post"]) < TOL
+
+
+def test_decode_doctest_seed1_threadpool():
+    """simulate/decode.py:192-262: class looked up by name, min_sum called from a ThreadPoolExecutor."""
+    z = util.load("decode_doctest_seed1.npz")
+    H = util.dense(z)
+    n, r, v, c, B = 450, 150, 3, 7, 1
+    decoder = getattr(simulate_rs, f"DecoderN{n}R{r}V{v}C{c}B{B}")(H.astype(np.int8), 5)
+    with ThreadPoolExecutor(max_workers=4) as ex:
+        futs = [ex.submit(decoder.min_sum, z["channel_output"].copy()) for _ in range(8)]
+        assert all(f.result() == [0] * n for f in futs)
+    hard, post, _ = decoder.min_sum_batch(z["channel_output"][None], exact=True)
+    assert np.array_equal(hard[0], z["hard"]) and np.array_equal(post[0], z["post"], equal_nan=True)
+
+
+@pytest.mark.parametrize("cb", [1, 2])
+def test_kyber768_fixture(cb):
+    """DecoderN1024R256SW6 / DecoderN1280R512SW6 (lib.rs:54-75) on reference-produced priors."""
+    z = util.load(f"kyber768_cb{cb}.npz")
+    H = util.dense(z)
+    R, N = H.shape
+    cls = getattr(simulate_rs, f"DecoderN{N}R{R}SW6")
+    for i in range(4):
+        it = int(z["iterations"][i])
+        d = cls(H, it)
+        co, cos = z["channel_output"][i], z["channel_output_sum"][i]
+        assert d.min_sum(co, cos) == z["hard"][i].tolist()
+        # fast path (k_cn_fast<6,2>)
+        hard, post, posts = d.min_sum_batch(co[None], cos[None])
+        assert np.array_equal(hard[0], z["hard"][i])
+        assert util.same_nonfinite(post[0], z["post"][i]) and util.same_nonfinite(posts[0], z["post_sum"][i])
+        assert util.max_abs_diff(post[0], z["post"][i]) < TOL and util.max_abs_diff(posts[0], z["post_sum"][i]) < TOL
+        # exact-order path from oracle LLRs: bit-identical posteriors
+        llr, llrs = O.into_llr(co), O.into_llr(cos)
+        hard, post, posts = d.min_sum_batch(llr[None], llrs[None], llr=True, exact=True)
+        assert np.array_equal(hard[0], z["hard"][i])
+        assert np.array_equal(post[0], z["post"][i], equal_nan=True)
+        assert np.array_equal(posts[0], z["post_sum"][i], equal_nan=True)
+        # runtime-shape forward/backward kernel
+        hard, post, posts = d.min_sum_batch(llr[None], llrs[None], llr=True, generic=True)
+        assert np.array_equal(hard[0], z["hard"][i]) and util.max_abs_diff(post[0], z["post"][i]) < TOL
+
+
+def test_device_logf_vs_host():
+    """into_llr on the device (CUDA logf) against the oracle's libm logf: <= 1 ulp, same infinities."""
+    z = util.load("kyber768_cb1.npz")
+    d = simulate_rs.DecoderN1024R256SW6(util.dense(z), 1)
+    co, cos = z["channel_output"][1], z["channel_output_sum"][1]
+    # one iteration with uninformative checks is not needed: compare posteriors of a 0-information decode instead
+    llr = O.into_llr(co)
+    h1, p1, _ = d.min_sum_batch(co[None], cos[None])
+    h2, p2, _ = d.min_sum_batch(llr[None], O.into_llr(cos)[None], llr=True)
+    assert np.array_equal(h1, h2) and util.same_nonfinite(p1, p2) and util.max_abs_diff(p1, p2) < 1e-5
+
+
+@pytest.mark.parametrize("variant,sw,cb", [("kyber512", 6, 1), ("kyber768", 6, 2), ("kyber1024", 8, 1),
+                                           ("kyber1024", 4, 1)])
+def test_batched_parity_with_oracle(variant, sw, cb):
+    """Seeded synthetic batches (T not a multiple of 32) for every BASELINE.json Kyber shape: the fast kernels
+    against the oracle's forward/backward model per trial (hard decisions identical, posteriors within 1e-4),
+    torch CUDA tensors in / out, and the end-to-end property decoded == secret where the oracle also succeeds."""
+    import torch
+
+    w = KyberWorkload(variant, sum_weight=sw, check_blocks=cb, accuracy=0.95, nbits=4, nbits_sum=5, seed=1)
+    T = 40
+    b = w.generate(T, seed=3)
+    d = QaryDecoder(w.H, 6, **w.decoder_kwargs)
+    orc = O.QaryOracle(w.H, 6, B=w.B, BSUM=w.BSUM, DC=sw + 1, algo=O.ALGO_FWD_BWD)
+    rh, rp, rps, st = orc.decode_batch(b.priors, b.priors_sum, from_probs=True)
+    assert (st == 0).all()
+    hard, post, posts = d.min_sum_batch(b.priors, b.priors_sum)
+    assert np.array_equal(hard, rh)
+    assert util.same_nonfinite(post, rp) and util.max_abs_diff(post, rp) < TOL
+    assert util.same_nonfinite(posts, rps) and util.max_abs_diff(posts, rps) < TOL
+    # device-resident tensors, asynchronous on the current stream
+    th, tp, tps = d.min_sum_batch(torch.from_numpy(b.priors).cuda(), torch.from_numpy(b.priors_sum).cuda())
+    torch.cuda.synchronize()
+    assert np.array_equal(th.cpu().numpy(), hard) and np.array_equal(tp.cpu().numpy(), post, equal_nan=True)
+    ok = w.success(b, hard)
+    assert np.array_equal(ok, w.success(b, rh))
+
+
+def test_exact_mode_matches_enumeration_oracle_kyber768():
+    """Bit-exact against the reference's brute-force enumeration (decoder_special.rs:531-554) on a small batch."""
+    w = KyberWorkload("kyber768", 6, 1, accuracy=0.95, nbits=3, nbits_sum=4, seed=2)
+    b = w.generate(3, seed=5)
+    d = QaryDecoder(w.H, 3, **w.decoder_kwargs)
+    orc = O.QaryOracle(w.H, 3, B=2, BSUM=12, DC=7, algo=O.ALGO_ENUMERATE)
+    llr = np.stack([O.into_llr(x) for x in b.priors])
+    llrs = np.stack([O.into_llr(x) for x in b.priors_sum])
+    rh, rp, rps, st = orc.decode_batch(llr, llrs, from_probs=False)
+    hard, post, posts = d.min_sum_batch(llr, llrs, llr=True, exact=True)
+    assert np.array_equal(hard, rh) and np.array_equal(post, rp, equal_nan=True)
+    assert np.array_equal(posts, rps, equal_nan=True)
+
+
+def test_irregular_rows_zero_probabilities_and_errors():
+    rs = np.random.RandomState(5)
+    R, bv, B, sw = 6, 9, 2, 3
+    H = np.zeros((R, bv + R), np.int8)
+    for r in range(R):
+        deg = 2 + (r % 2)
+        cols = rs.choice(bv, deg, replace=False)
+        H[r, cols] = rs.choice([-1, 1], deg)
+        H[r, bv + r] = 1
+    T = 37
+    Q, QS = 2 * B + 1, 2 * B * sw + 1
+    pri = rs.dirichlet(np.ones(Q), size=(T, bv)).astype(np.float32)
+    pri[rs.rand(T, bv, Q) < 0.15] = 0.0
+    pri[..., B] += 1e-3
+    pri /= pri.sum(-1, keepdims=True)
+    pris = rs.dirichlet(np.ones(QS), size=(T, R)).astype(np.float32)
+    d = QaryDecoder(H, 4, B=B, BSUM=B * sw, DC=sw + 1)
+    orc = O.QaryOracle(H, 4, B=B, BSUM=B * sw, DC=sw + 1)
+    rh, rp, rps, st = orc.decode_batch(pri, pris, from_probs=True, algo=O.ALGO_ENUMERATE)
+    llr = np.stack([O.into_llr(x) for x in pri])
+    llrs = np.stack([O.into_llr(x) for x in pris])
+    hard, post, posts = d.min_sum_batch(llr, llrs, llr=True, exact=True)
+    assert np.array_equal(hard, rh) and np.array_equal(post, rp, equal_nan=True)
+    hard, post, posts = d.min_sum_batch(pri, pris)
+    assert np.array_equal(hard, rh) and util.same_nonfinite(post, rp) and util.max_abs_diff(post, rp) < TOL
+    # decoder.rs:683-684: a prior row that does not sum to 1 -> the reference panics; here ValueError / status
+    bad = pri.copy()
+    bad[3, 2] *= 0.5
+    with pytest.raises(ValueError):
+        d.min_sum_batch(bad, pris)
+    _, _, _, status = d.min_sum_batch(bad, pris, want_status=True)
+    assert status[3] == -2 and (np.delete(status, 3) == 0).all()
+    with pytest.raises(TypeError):
+        d.min_sum(pri[0].astype(np.float64), pris[0])
+    # empty batch
+    h0, _, _ = d.min_sum_batch(pri[:0], pris[:0])
+    assert h0.shape == (0, bv + R)
+
+
+def test_no_config_is_reported_per_trial():
+    H = np.array([[1, 1, 0], [0, 1, 1]], np.int8)
+    d = simulate_rs.DecoderN3R2V2C2B1(H, 2)
+    p_ok = np.array([[0.2, 0.6, 0.2]] * 3, np.float32)
+    p_bad = np.array([[0, 0, 1], [0, 0, 1], [0.2, 0.6, 0.2]], np.float32)
+    _, _, _, status = d.min_sum_batch(np.stack([p_ok, p_bad]), want_status=True)
+    assert status.tolist() == [0, -4]
+    with pytest.raises(ValueError):
+        d.min_sum(p_bad)
+
+
+def test_full_size_properties_kyber512():
+    """BASELINE.json configs[1] at full size (10^4 trials): size-independent properties instead of the oracle --
+    decoded words satisfy every parity check (sum_j H_ij s_j + s_sum,i = 0) whenever decoding succeeds, results do
+    not depend on the batch split, and a trial's result does not depend on its batch neighbours."""
+    w = KyberWorkload("kyber512", 6, 1, accuracy=0.98, nbits=4, nbits_sum=5, seed=0)
+    T = 10_000
+    b = w.generate(T, seed=1)
+    d = QaryDecoder(w.H, 10, **w.decoder_kwargs)
+    hard, _, _ = d.min_sum_batch(b.priors, b.priors_sum, want_posterior=False)
+    ok = w.success(b, hard)
+    assert ok.mean() > 0.9
+    synd = hard[ok].astype(np.int32) @ w.H.T.astype(np.int32)
+    assert (synd == 0).all()
+    h2, _, _ = d.min_sum_batch(b.priors[1000:1777], b.priors_sum[1000:1777], want_posterior=False)
+    assert np.array_equal(h2, hard[1000:1777])
+    perm = np.random.RandomState(0).permutation(T)[:512]
+    h3, _, _ = d.min_sum_batch(b.priors[perm], b.priors_sum[perm], want_posterior=False)
+    assert np.array_equal(h3, hard[perm])

@@ -1,0 +1,149 @@
+"""Kernel LOGIC against the oracle without a GPU: tests/hostmodel compiles sca_ldpc_b200/csrc/qary_kernels.cuh with
+g++ and runs the threads one after another (test infrastructure only; the product has no CPU path).  The same
+comparisons run on the real device in tests/test_gpu_qary.py."""
+import json
+
+import numpy as np
+import pytest
+
+import util
+from oracle import oracle as O
+from sca_ldpc_b200 import _lib
+
+EXACT, GENERIC = _lib.CN_EXACT, _lib.CN_GENERIC
+
+
+def _kyber(cb, idx):
+    z = util.load(f"kyber768_cb{cb}.npz")
+    H = util.dense(z)
+    llr = np.stack([O.into_llr(z["channel_output"][i]) for i in idx])
+    llrs = np.stack([O.into_llr(z["channel_output_sum"][i]) for i in idx])
+    return z, H, llr, llrs
+
+
+@pytest.mark.parametrize("cb", [1, 2])
+def test_fast_kernels_match_fixture(cb):
+    """k_cn_fast<6,2> + k_vn<5>: hard decisions identical, posteriors within 1e-4, same inf/NaN masks."""
+    idx = [0, 3] if cb == 2 else [0, 1, 2, 3]
+    z, H, llr, llrs = _kyber(cb, idx)
+    for j, i in enumerate(idx):
+        it = int(z["iterations"][i])
+        rc, hard, post, posts, status, fast = util.hostmodel_qary(H, 2, 12, it, llr[j:j + 1], llrs[j:j + 1], dc=7)
+        assert rc == 0 and fast
+        assert np.array_equal(hard[0], z["hard"][i])
+        assert util.same_nonfinite(post[0], z["post"][i]) and util.same_nonfinite(posts[0], z["post_sum"][i])
+        assert util.max_abs_diff(post[0], z["post"][i]) < 1e-4
+        assert util.max_abs_diff(posts[0], z["post_sum"][i]) < 1e-4
+
+
+def test_fast_kernel_equals_fwd_bwd_oracle_bitwise():
+    """The fast kernel and the oracle's forward/backward model (algo 2) are the same arithmetic."""
+    z, H, llr, llrs = _kyber(1, [1])
+    it = int(z["iterations"][1])
+    d = O.QaryOracle(H, it, B=2, BSUM=12, DC=7)
+    h2, p2, ps2 = d.decode_llr(llr[0], llrs[0], algo=O.ALGO_FWD_BWD)
+    rc, hard, post, posts, _, fast = util.hostmodel_qary(H, 2, 12, it, llr, llrs, dc=7)
+    assert rc == 0 and fast and np.array_equal(hard[0], h2)
+    assert util.same_nonfinite(post[0], p2) and util.max_abs_diff(post[0], p2) < 2e-5
+    assert util.same_nonfinite(posts[0], ps2) and util.max_abs_diff(posts[0], ps2) < 2e-5
+
+
+def test_exact_kernel_is_bit_identical_special():
+    """k_cn_generic in exact-order mode reproduces the reference's rounding bit for bit (decoder_special.rs:539-553)."""
+    z, H, llr, llrs = _kyber(1, [0, 3])
+    for j, i in enumerate([0, 3]):
+        it = min(3, int(z["iterations"][i]))
+        d = O.QaryOracle(H, it, B=2, BSUM=12, DC=7)
+        h, p, ps = d.decode_llr(llr[j], llrs[j], algo=O.ALGO_EXACT_DP)
+        rc, hard, post, posts, _, fast = util.hostmodel_qary(H, 2, 12, it, llr[j:j + 1], llrs[j:j + 1], flags=EXACT,
+                                                             dc=7)
+        assert rc == 0 and not fast
+        assert np.array_equal(hard[0], h)
+        assert np.array_equal(post[0], p, equal_nan=True) and np.array_equal(posts[0], ps, equal_nan=True)
+
+
+def test_generic_fwd_bwd_kernel_special():
+    z, H, llr, llrs = _kyber(1, [2])
+    it = 4
+    d = O.QaryOracle(H, it, B=2, BSUM=12, DC=7)
+    h, p, ps = d.decode_llr(llr[0], llrs[0], algo=O.ALGO_FWD_BWD)
+    rc, hard, post, posts, _, fast = util.hostmodel_qary(H, 2, 12, it, llr, llrs, flags=GENERIC, dc=7)
+    assert rc == 0 and not fast and np.array_equal(hard[0], h)
+    assert util.same_nonfinite(post[0], p) and util.max_abs_diff(post[0], p) < 2e-5
+    assert util.same_nonfinite(posts[0], ps) and util.max_abs_diff(posts[0], ps) < 2e-5
+
+
+def _corrupted(n):
+    co = np.zeros((n, 15), np.float32)
+    co[:, 7] = 1.0
+    co[1, 7], co[1, 14] = 0.1, 0.9
+    return co
+
+
+@pytest.mark.parametrize("flags", [0, EXACT])
+def test_generic_decoder_rust_unit_tests(flags):
+    """decoder.rs:770-854 through the generic kernels."""
+    z = util.load("rust_unit_tests.npz")
+    for H, n, key in ((z["H6"], 6, "small"), (util.dense(z, "Hm"), 450, "medium")):
+        llr = O.into_llr(_corrupted(n))[None]
+        rc, hard, post, _, _, fast = util.hostmodel_qary(H, 7, 0, 10, llr, flags=flags)
+        assert rc == 0 and not fast and (hard == 0).all()
+        if flags & EXACT:
+            assert np.array_equal(post[0], z[f"{key}_post"], equal_nan=True)
+        else:
+            assert util.same_nonfinite(post[0], z[f"{key}_post"])
+            assert util.max_abs_diff(post[0], z[f"{key}_post"]) < 1e-4
+
+
+def test_generic_decoder_doctest_seed1():
+    z = util.load("decode_doctest_seed1.npz")
+    H = util.dense(z)
+    llr = O.into_llr(z["channel_output"])[None]
+    rc, hard, post, _, _, _ = util.hostmodel_qary(H, 1, 0, 5, llr, flags=EXACT, dv=3, dc=7)
+    assert rc == 0 and np.array_equal(hard[0], z["hard"]) and np.array_equal(post[0], z["post"], equal_nan=True)
+
+
+def test_ragged_batch_and_irregular_rows():
+    """T not a multiple of 32 (ragged last tile) and a parity-check matrix with rows of different degree
+    (decoder_special.rs:510-511 trailing Nones) -> runtime-shape kernel, compared with the oracle per trial."""
+    rs = np.random.RandomState(5)
+    R, bv, B, sw = 6, 9, 2, 3
+    H = np.zeros((R, bv + R), np.int8)
+    for r in range(R):
+        deg = 2 + (r % 2)  # rows of degree 2 and 3
+        cols = rs.choice(bv, deg, replace=False)
+        H[r, cols] = rs.choice([-1, 1], deg)
+        H[r, bv + r] = 1
+    T = 37
+    Q, QS = 2 * B + 1, 2 * B * sw + 1
+    pri = rs.dirichlet(np.ones(Q), size=(T, bv)).astype(np.float32)
+    pri[rs.rand(T, bv, Q) < 0.15] = 0.0  # zero-probability entries -> +inf LLRs
+    pri[..., B] += 1e-3
+    pri /= pri.sum(-1, keepdims=True)
+    pris = rs.dirichlet(np.ones(QS), size=(T, R)).astype(np.float32)
+    llr = np.stack([O.into_llr(x) for x in pri])
+    llrs = np.stack([O.into_llr(x) for x in pris])
+    d = O.QaryOracle(H, 4, B=B, BSUM=B * sw, DC=sw + 1)
+    for flags, algo in ((EXACT, O.ALGO_ENUMERATE), (0, O.ALGO_FWD_BWD)):
+        rc, hard, post, posts, _, fast = util.hostmodel_qary(H, B, B * sw, 4, llr, llrs, flags=flags, dc=sw + 1)
+        assert rc == 0 and not fast
+        for t in range(T):
+            h, p, ps = d.decode_llr(llr[t], llrs[t], algo=algo)
+            assert np.array_equal(hard[t], h), (flags, t)
+            if flags & EXACT:
+                assert np.array_equal(post[t], p, equal_nan=True) and np.array_equal(posts[t], ps, equal_nan=True)
+            else:
+                assert util.same_nonfinite(post[t], p) and util.max_abs_diff(post[t], p) < 1e-4
+
+
+def test_no_config_status():
+    """decoder.rs:618: a check whose variables cannot sum to zero -> SCALDPC_ERR_NO_CONFIG for that trial only."""
+    H = np.array([[1, 1, 0], [0, 1, 1]], np.int8)
+    p_ok = np.array([[0.2, 0.6, 0.2]] * 3, np.float32)
+    p_bad = np.array([[0, 0, 1], [0, 0, 1], [0.2, 0.6, 0.2]], np.float32)  # v0 = v1 = +1 cannot satisfy check 0
+    llr = np.stack([O.into_llr(p_ok), O.into_llr(p_bad)])
+    rc, hard, post, _, status, _ = util.hostmodel_qary(H, 1, 0, 2, llr)
+    assert rc == _lib.ERR_NO_CONFIG and status.tolist() == [0, _lib.ERR_NO_CONFIG]
+    with pytest.raises(O.OracleError) as e:
+        O.QaryOracle(H, 2, B=1).decode_llr(llr[1])
+    assert e.value.code == -4

@@ -1,0 +1,101 @@
+"""Binary product-sum BP kernel logic (k_bp_cn / k_bp_vn / k_bp_syndrome / k_bp_finish_iter run on the host by
+tests/hostmodel) against the fp64 oracle of ldpc.bp_decoder.  The same comparisons run on the device in
+tests/test_gpu_bp.py.  Tolerance: hard decisions, iteration counts and convergence flags identical; posterior LLRs
+within 2e-3 + 2e-4*|L| (fp32 LLR domain vs fp64 probability ratios)."""
+import numpy as np
+
+import util
+from oracle import oracle as O
+from sca_ldpc_b200.workloads import HqcWorkload
+
+
+def _fixture(name):
+    z = util.load(name)
+    H = util.dense(z, with_vals=False)
+    row_ptr, col = O.dense_to_csr(H)
+    return z, H, row_ptr, col
+
+
+def test_hqc_toy():
+    """hqc.py:1229-1274 toy instance (certainty-1.0 checks: prior probability 0 -> LLR +inf)."""
+    z, H, row_ptr, col = _fixture("hqc_toy.npz")
+    m, n = H.shape
+    msg = z["msg"].astype(np.uint8)
+    synd = (H @ msg % 2).astype(np.uint8)[None]
+    out = util.hostmodel_bp(row_ptr, col, m, n, 100, synd, z["channel_probs"])
+    decoded = out["decoding"][0] ^ msg
+    assert np.array_equal(decoded, z["decoded"])
+    assert sorted(np.nonzero(decoded[:20])[0].tolist()) == z["y_sparse"].tolist()
+    assert int(out["iters"][0]) == int(z["iters"]) and int(out["converged"][0]) == 1
+    assert util.llr_close(out["llr"][0], z["log_prob_ratios"])
+
+
+def test_hqc_small_fixture():
+    z, H, row_ptr, col = _fixture("hqc_small.npz")
+    m, n = H.shape
+    msg = z["msg"].astype(np.uint8)
+    synd = (H @ msg % 2).astype(np.uint8)[None]
+    out = util.hostmodel_bp(row_ptr, col, m, n, 100, synd, z["channel_probs"])
+    assert np.array_equal(out["decoding"][0] ^ msg, z["decoded"])
+    assert int(out["iters"][0]) == int(z["iters"]) and int(out["converged"][0]) == int(z["converged"])
+    assert util.llr_close(out["llr"][0], z["log_prob_ratios"])
+
+
+def test_batch_early_stop_and_freeze():
+    """T = 45 trials (ragged second tile) with different iteration counts: converged trials freeze while their tile
+    mates keep iterating; a non-converging trial runs to max_iter."""
+    w = HqcWorkload(variant=(499, 6), W=9, R=230, rho=0.97, seed=3)
+    batch = w.generate(45, seed=11)
+    synd = batch.syndromes.copy()
+    synd[7] = np.random.RandomState(1).randint(0, 2, w.R)  # garbage syndrome: will not converge
+    orc = O.BinaryBpOracle(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=20, channel_probs=w.channel_probs)
+    ref = orc.decode_batch(synd)
+    out = util.hostmodel_bp(w.row_ptr, w.col, w.m, w.n, 20, synd, w.channel_probs)
+    assert np.array_equal(out["iters"], ref["iters"])
+    assert np.array_equal(out["converged"], ref["converged"])
+    assert np.array_equal(out["decoding"], ref["decoding"])
+    assert len(set(ref["iters"].tolist())) >= 2 and ref["converged"][7] == 0
+    for t in range(45):
+        assert util.llr_close(out["llr"][t], ref["log_prob_ratios"][t]), t
+
+
+def test_per_trial_priors_and_no_early_stop():
+    w = HqcWorkload(variant=(307, 5), W=7, R=150, rho=0.98, seed=5)
+    batch = w.generate(5, seed=2)
+    rs = np.random.RandomState(9)
+    probs = np.tile(w.channel_probs, (5, 1)) * rs.uniform(0.5, 1.5, size=(5, w.n))
+    orc = O.BinaryBpOracle(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=15, channel_probs=w.channel_probs)
+    ref = orc.decode_batch(batch.syndromes, channel_probs=probs)
+    out = util.hostmodel_bp(w.row_ptr, w.col, w.m, w.n, 15, batch.syndromes, probs)
+    assert np.array_equal(out["iters"], ref["iters"]) and np.array_equal(out["decoding"], ref["decoding"])
+    for t in range(5):
+        assert util.llr_close(out["llr"][t], ref["log_prob_ratios"][t]), t
+    # without early stop every trial runs max_iter iterations; converged = state of the final iteration
+    out2 = util.hostmodel_bp(w.row_ptr, w.col, w.m, w.n, 15, batch.syndromes, probs, early_stop=False)
+    assert (out2["iters"] == 15).all()
+
+
+def test_rep_code_syndrome_decoding():
+    """decode.py:139-171: rep_code(13), error_rate 0.05, syndrome in -> error pattern out.  With a uniform prior the
+    posterior of an end bit is EXACTLY tied (ratio 1 / LLR 0) after one iteration, so fp32 and fp64 may take the
+    decision in different iterations; the decoded pattern is pinned, iteration counts are compared on a
+    non-degenerate prior."""
+    import refshim
+
+    H = refshim.rep_code(13)
+    row_ptr, col = O.dense_to_csr(H)
+    rs = np.random.RandomState(0)
+    errs = (rs.rand(64, 13) < 0.05).astype(np.uint8)
+    synd = (errs @ H.T % 2).astype(np.uint8)
+    orc = O.BinaryBpOracle(H, error_rate=0.05, max_iter=13)
+    ref = orc.decode_batch(synd)
+    out = util.hostmodel_bp(row_ptr, col, 12, 13, 13, synd, np.full(13, 0.05))
+    assert np.array_equal(out["decoding"], ref["decoding"]) and (out["decoding"] == errs).all()
+    assert (out["converged"] == 1).all()
+    probs = rs.uniform(0.03, 0.07, 13)
+    orc = O.BinaryBpOracle(H, max_iter=13, channel_probs=probs)
+    ref = orc.decode_batch(synd)
+    out = util.hostmodel_bp(row_ptr, col, 12, 13, 13, synd, probs)
+    assert np.array_equal(out["decoding"], ref["decoding"]) and np.array_equal(out["iters"], ref["iters"])
+    for t in range(64):
+        assert util.llr_close(out["llr"][t], ref["log_prob_ratios"][t]), t
