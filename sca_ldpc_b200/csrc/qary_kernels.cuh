@@ -552,7 +552,9 @@ __global__ void __launch_bounds__(32 * kTrRows) k_load_priors(const float *__res
             if (!have) err = SCALDPC_ERR_NO_MAX;
             else if (!(sum < 1.0f + 0.001f) || !(sum > 1.0f - 0.001f)) err = SCALDPC_ERR_PROB_SUM;
             if (err && tile * 32 + tx < T) atomicMin(status + tile * 32 + tx, err);
-            for (int i = 0; i < q; ++i) v[i] = logf(__fdiv_rn(mx, v[i]));
+            // (max / p).ln() in f32 (decoder.rs:687).  glibc's logf is correctly rounded in practice; CUDA's logf
+            // is only 1-ulp accurate, so take the fp64 log of the f32 quotient and round once.
+            for (int i = 0; i < q; ++i) v[i] = (float)log((double)__fdiv_rn(mx, v[i]));
         }
         __syncthreads();
     }
