@@ -40,6 +40,7 @@ struct scaldpc_qary {
     int S = 0, SL = 0, SLS = 0;
     int lmax = 0;      // max row degree
     int wmax = 0;      // max DP table width over the checks
+    int num_sms = 148;
     int fast_sw = 0;   // >0: every row is SW B-variables + 1 sum-variable with BSUM == SW*B and a template exists
     // device graph
     int *d_row_ptr = nullptr, *d_col = nullptr, *d_edge_off = nullptr, *d_col_ptr = nullptr;
@@ -165,13 +166,28 @@ QaryDev dev_view(const scaldpc_qary *h, bool want_post)
 }
 
 // ---- kernel dispatch tables ------------------------------------------------------------------------------
-typedef void (*cn_fast_fn)(const QaryDev, const int, const int);
+typedef void (*cn_fast_fn)(const QaryDev, const int);
 typedef void (*vn_fn)(const QaryDev, const int);
 
-cn_fast_fn pick_cn_fast(int sw, int b)
+// The four (FIRST, LAST) instantiations of the persistent check-node kernel for one shape.
+struct CnFast {
+    cn_fast_fn fn[2][2];
+    size_t smem;
+};
+
+template <int SW, int B>
+const CnFast *cn_fast_table()
+{
+    static const CnFast t = {{{k_cn_fast<SW, B, false, false>, k_cn_fast<SW, B, false, true>},
+                              {k_cn_fast<SW, B, true, false>, k_cn_fast<SW, B, true, true>}},
+                             CnFastShape<SW, B>::smem_bytes};
+    return &t;
+}
+
+const CnFast *pick_cn_fast(int sw, int b)
 {
 #define CASE(SW_, B_) \
-    if (sw == SW_ && b == B_) return k_cn_fast<SW_, B_>;
+    if (sw == SW_ && b == B_) return cn_fast_table<SW_, B_>();
     CASE(6, 2)  // Kyber-768, sum_weight 6  (lib.rs:54-75 DecoderN1024R256SW6 / DecoderN1280R512SW6)
     CASE(6, 3)  // Kyber-512, eta1 = 3      (BASELINE.json configs[1])
     CASE(4, 2)  // Kyber-1024, sum_weight 4
@@ -209,10 +225,12 @@ int launch_cn(scaldpc_qary *h, const QaryDev &p, int tiles, bool first, bool las
 {
     const bool exact = flags & SCALDPC_CN_EXACT;
     const bool force_generic = flags & SCALDPC_CN_GENERIC;
-    cn_fast_fn fast = (!exact && !force_generic && h->fast_sw) ? pick_cn_fast(h->fast_sw, h->B) : nullptr;
+    const CnFast *fast = (!exact && !force_generic && h->fast_sw) ? pick_cn_fast(h->fast_sw, h->B) : nullptr;
     if (fast) {
-        dim3 grid((h->R + kCnWarps - 1) / kCnWarps, tiles);
-        fast<<<grid, kCnWarps * 32, 0, st>>>(p, first, last);
+        // persistent: one CTA of kCnWarps warps per SM, warps stride over the (tile, check) items
+        const int n_items = tiles * h->R;
+        const int grid = std::max(1, std::min(h->num_sms, (n_items + kCnWarps - 1) / kCnWarps));
+        fast->fn[first][last]<<<grid, kCnWarps * 32, fast->smem, st>>>(p, n_items);
         ++h->launches;
     } else {
         if (first) {
@@ -315,6 +333,12 @@ int scaldpc_qary_create(const int8_t *H, int R, int N, int b, int bsum, int dv, 
     const std::vector<int8_t> &sign = g.sign;
 
     SCALDPC_CUDA(cudaSetDevice(device));
+    SCALDPC_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
+    if (h->fast_sw) {
+        const CnFast *f = pick_cn_fast(h->fast_sw, b);
+        for (int i = 0; i < 4; ++i)
+            SCALDPC_CUDA(cudaFuncSetAttribute(f->fn[i >> 1][i & 1], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f->smem));
+    }
     int rc;
     if ((rc = upload(&h->d_row_ptr, row_ptr)) || (rc = upload(&h->d_col, col)) || (rc = upload(&h->d_sign, sign)) ||
         (rc = upload(&h->d_edge_off, edge_off)) || (rc = upload(&h->d_col_ptr, col_ptr)) || (rc = upload(&h->d_csc, csc)))

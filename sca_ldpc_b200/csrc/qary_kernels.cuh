@@ -78,170 +78,7 @@ struct MinAcc {
     __device__ __forceinline__ float get() const { return (n > 1 && (n & 1) == 0) ? fminf(best, pend) : best; }
 };
 
-constexpr int kCnWarps = 4;      // warps (= checks) per CTA of the fast check-node kernel
-constexpr int kCnMinBlocks = 2;  // 255 registers per thread: the DP tables stay in registers without spilling
-
-// -----------------------------------------------------------------------------------------------------------
-// Fast check-node kernel for the special decoder (decoder_special.rs:506-563), regular rows only: every check
-// has exactly SW B-variables followed by its sum-variable, BSUM == SW*B.
-//
-// One thread = one (trial, check); a warp = 32 trials of one check.  Everything lives in registers with
-// compile-time indices.  The brute-force enumeration of (2B+1)^SW configurations is replaced by a forward /
-// backward (min,+) convolution:
-//     F_1 = a_0,  F_{k+1}[u] = min_d F_k[u-d] + a_k[d]                      (prefix sums, |u| <= kB)
-//     G_SW[u] = a_sum[-u],  G_k[u] = min_d a_k[d] + G_{k+1}[u+d]            (cost of the suffix given prefix u)
-//     c2v_k[d] = min_u F_k[u] + G_{k+1}[u+d],   c2v_sum[t] = F_SW[-t]
-// with "non-finite input => value excluded" (sanitize) and "own entry non-finite => +inf out"
-// (decoder.rs:307-311, decoder_special.rs:549-553).
-//
-// The degree-1 sum-variable's own update (decoder_special.rs:591-609) is fused here: its v2c is recomputed
-// from the channel LLR and the previous c2v, so it never travels through HBM, and on the last iteration its
-// hard decision / posterior are emitted from here.
-// -----------------------------------------------------------------------------------------------------------
-template <int SW, int B>
-__global__ void __launch_bounds__(kCnWarps * 32, kCnMinBlocks) k_cn_fast(const QaryDev p, const int FIRST, const int LAST)
-{
-    constexpr int Q = 2 * B + 1, BS = SW * B, QS = 2 * BS + 1;
-    const float INF = SC_INF;
-    const int lane = threadIdx.x & 31;
-    const int check = blockIdx.x * kCnWarps + (threadIdx.x >> 5);
-    const int tile = blockIdx.y;
-    if (check >= p.R) return;
-
-    const int e0 = __ldg(p.row_ptr + check);
-    const int base = __ldg(p.edge_off + e0);
-    float *msg = p.msg + (size_t)tile * p.S * 32 + lane;
-    const float *llr = p.llr + (size_t)tile * p.SL * 32 + lane;
-    const float *llrs = p.llr_sum + (size_t)tile * p.SLS * 32 + lane;
-
-    // ---- load the B-variables' v2c (check frame)
-    float a[SW][Q];
-#pragma unroll
-    for (int k = 0; k < SW; ++k) {
-        if (FIRST) {  // v2c = perm_h(channel) (decoder_special.rs:480-486), gathered straight from llr
-            const int var = __ldg(p.col + e0 + k);
-            const bool neg = __ldg(p.sign + e0 + k) < 0;
-#pragma unroll
-            for (int i = 0; i < Q; ++i) a[k][i] = llr[(size_t)(var * Q + (neg ? Q - 1 - i : i)) * 32];
-        } else {
-#pragma unroll
-            for (int i = 0; i < Q; ++i) a[k][i] = msg[(size_t)(base + k * Q + i) * 32];
-        }
-    }
-    // ---- the sum-variable: v2c from channel + previous c2v (decoder_special.rs:591-604), check frame
-    const int vs = __ldg(p.col + e0 + SW) - p.bvars;
-    const bool negs = __ldg(p.sign + e0 + SW) < 0;
-    const int sbase = base + SW * Q;
-    float as[QS];
-#pragma unroll
-    for (int i = 0; i < QS; ++i) as[i] = llrs[(size_t)(vs * QS + (negs ? QS - 1 - i : i)) * 32];
-    if (!FIRST) {
-        float m = INF;
-#pragma unroll
-        for (int i = 0; i < QS; ++i) {
-            const float c = msg[(size_t)(sbase + i) * 32];
-            const float tot = as[i] + c;   // sum = channel + perm_h(c2v)
-            as[i] = tot - c;               // prim = perm_h(sum - perm_h(c2v))
-            m = fminf(m, as[i]);           // value of the first strict minimum (NaN skipped)
-        }
-#pragma unroll
-        for (int i = 0; i < QS; ++i) as[i] = as[i] - m;
-    }
-#pragma unroll
-    for (int k = 0; k < SW; ++k)
-#pragma unroll
-        for (int i = 0; i < Q; ++i) a[k][i] = sanitize(a[k][i]);
-#pragma unroll
-    for (int i = 0; i < QS; ++i) as[i] = sanitize(as[i]);
-
-    // ---- forward: F[k][u + k*B], k = 1..SW-1
-    float F[SW][2 * (SW - 1) * B + 1];
-#pragma unroll
-    for (int i = 0; i < Q; ++i) F[1 % SW][i] = a[0][i];
-#pragma unroll
-    for (int k = 1; k < SW - 1; ++k) {
-#pragma unroll
-        for (int u = -(k + 1) * B; u <= (k + 1) * B; ++u) {
-            MinAcc acc;
-#pragma unroll
-            for (int d = -B; d <= B; ++d) {
-                const int up = u - d;
-                if (up >= -k * B && up <= k * B) acc.add(F[k][up + k * B] + a[k][d + B]);
-            }
-            F[k + 1][u + (k + 1) * B] = acc.get();
-        }
-    }
-    // ---- c2v of the sum-variable: F_SW[-t]
-    float cs[QS];
-#pragma unroll
-    for (int t = -BS; t <= BS; ++t) {
-        const int u = -t;
-        MinAcc acc;
-        if (SW == 1) {
-            // F_1 = a_0 directly
-            if (u >= -B && u <= B) acc.add(a[0][u + B]);
-        } else {
-            constexpr int k = SW - 1;
-#pragma unroll
-            for (int d = -B; d <= B; ++d) {
-                const int up = u - d;
-                if (up >= -k * B && up <= k * B) acc.add(F[k][up + k * B] + a[k][d + B]);
-            }
-        }
-        const float r = acc.get();
-        cs[t + BS] = (as[t + BS] == INF) ? INF : r;
-        msg[(size_t)(sbase + t + BS) * 32] = cs[t + BS];
-    }
-    if (LAST) {  // decision of the sum-variable (decoder_special.rs:606-608): first minimum in the VARIABLE's frame
-        float min_val = INF;
-        int arg = negs ? QS - 1 : 0;
-        float *post = p.post_sum ? p.post_sum + (size_t)tile * p.SLS * 32 + lane : nullptr;
-#pragma unroll
-        for (int i = 0; i < QS; ++i) {
-            const int iv = negs ? QS - 1 - i : i;
-            const float tot = llrs[(size_t)(vs * QS + iv) * 32] + cs[i];
-            if (negs ? (tot <= min_val && tot < INF) : (tot < min_val)) {
-                min_val = tot;
-                arg = i;
-            }
-            if (post) post[(size_t)(vs * QS + iv) * 32] = tot;
-        }
-        const int argv = negs ? QS - 1 - arg : arg;
-        p.hard_t[((size_t)tile * p.N + p.bvars + vs) * 32 + lane] = (int8_t)(argv - BS);
-    }
-
-    // ---- backward + combine.  Gc = G_{k+1}, indexed [u + (k+1)*B]
-    float Gc[QS], Gn[QS];
-#pragma unroll
-    for (int i = 0; i < QS; ++i) Gc[i] = as[QS - 1 - i];  // G_SW[u] = a_sum[-u]
-#pragma unroll
-    for (int k = SW - 1; k >= 0; --k) {
-        // c2v_k[d] = min_u F_k[u] + G_{k+1}[u + d]
-#pragma unroll
-        for (int d = -B; d <= B; ++d) {
-            MinAcc acc;
-            if (k == 0) {
-                acc.add(Gc[d + B]);
-            } else {
-#pragma unroll
-                for (int u = -k * B; u <= k * B; ++u) acc.add(F[k][u + k * B] + Gc[u + d + (k + 1) * B]);
-            }
-            const float r = acc.get();
-            msg[(size_t)(base + k * Q + d + B) * 32] = (a[k][d + B] == INF) ? INF : r;
-        }
-        if (k > 0) {
-#pragma unroll
-            for (int u = -k * B; u <= k * B; ++u) {
-                MinAcc acc;
-#pragma unroll
-                for (int d = -B; d <= B; ++d) acc.add(a[k][d + B] + Gc[u + d + (k + 1) * B]);
-                Gn[u + k * B] = acc.get();
-            }
-#pragma unroll
-            for (int i = 0; i < QS; ++i) Gc[i] = Gn[i];
-        }
-    }
-}
+#include "qary_cn_fast.cuh"
 
 // -----------------------------------------------------------------------------------------------------------
 // Variable-node kernel for the B-variables (decoder.rs:634-658 / decoder_special.rs:566-590).

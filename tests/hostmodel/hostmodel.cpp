@@ -71,13 +71,20 @@ void run_grid(unsigned gx, unsigned gy, unsigned threads, K kernel, A... args)
             }
 }
 
-typedef void (*cn_fast_fn)(const QaryDev, const int, const int);
+typedef void (*cn_fast_fn)(const QaryDev, const int);
 typedef void (*vn_fn)(const QaryDev, const int);
 
-cn_fast_fn pick_cn_fast(int sw, int b)
+template <int SW, int B>
+cn_fast_fn cn_fast_variant(bool first, bool last)
+{
+    if (first) return last ? k_cn_fast<SW, B, true, true> : k_cn_fast<SW, B, true, false>;
+    return last ? k_cn_fast<SW, B, false, true> : k_cn_fast<SW, B, false, false>;
+}
+
+cn_fast_fn pick_cn_fast(int sw, int b, bool first = false, bool last = false)
 {
 #define CASE(SW_, B_) \
-    if (sw == SW_ && b == B_) return k_cn_fast<SW_, B_>;
+    if (sw == SW_ && b == B_) return cn_fast_variant<SW_, B_>(first, last);
     CASE(6, 2) CASE(6, 3) CASE(4, 2) CASE(8, 2) CASE(3, 2)
 #undef CASE
     return nullptr;
@@ -151,7 +158,8 @@ int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
     for (int it = 1; it <= iters; ++it) {
         const int first = it == 1, last = it == iters;
         if (fast) {
-            run_grid((g.R + kCnWarps - 1) / kCnWarps, tiles, kCnWarps * 32, fast, p, first, last);
+            // persistent kernel: a deliberately small grid, so every warp strides over several items
+            run_grid(3, 1, kCnWarps * 32, pick_cn_fast(g.regular_sw, b, first, last), p, tiles * g.R);
         } else {
             if (first) run_grid((g.E + 7) / 8, tiles, 256, k_init_v2c, p, g.E);
             CnGenericArgs a;
