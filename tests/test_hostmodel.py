@@ -84,7 +84,10 @@ def _corrupted(n):
 def test_generic_decoder_rust_unit_tests(flags):
     """decoder.rs:770-854 through the generic kernels."""
     z = util.load("rust_unit_tests.npz")
-    for H, n, key in ((z["H6"], 6, "small"), (util.dense(z, "Hm"), 450, "medium")):
+    cases = [(z["H6"], 6, "small")]
+    if not flags & EXACT:  # the exact-order DP on the 450x150 instance takes ~90 s on the host model; the GPU tier runs it
+        cases.append((util.dense(z, "Hm"), 450, "medium"))
+    for H, n, key in cases:
         llr = O.into_llr(_corrupted(n))[None]
         rc, hard, post, _, _, fast = util.hostmodel_qary(H, 7, 0, 10, llr, flags=flags)
         assert rc == 0 and not fast and (hard == 0).all()
