@@ -342,6 +342,8 @@ def run_ours(args, kind, wl, iters, cfg):
             "clocks": clk,
             "e2e": {"value": e2e_value, "unit": "trials/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches),
+            **({"compactions_last_step": dec.last_run()[1], "iterations_launched_last_step": dec.last_run()[0]}
+               if kind == "bp" else {}),
             "roofline": roofline,
             "cpu_baseline": cpu,
         }

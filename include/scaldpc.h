@@ -126,6 +126,8 @@ void scaldpc_bp_destroy(scaldpc_bp *h);
 
 #define SCALDPC_BP_PROBS_PER_TRIAL 0x10u /* channel_probs is T x n instead of n */
 #define SCALDPC_BP_NO_EARLY_STOP 0x20u   /* run max_iter iterations regardless of convergence */
+#define SCALDPC_BP_NO_COMPACT 0x40u      /* keep converged trials in place (freeze only); default: running trials are
+                                            compacted into fewer tiles whenever they fill <= half of the slots */
 /*
  *   synd           T x m   uint8 syndromes
  *   channel_probs  n (or T x n) float64 prior error probabilities           (hqc.py:684-690)
@@ -139,6 +141,9 @@ int scaldpc_bp_decode(scaldpc_bp *h, int T, const uint8_t *synd, const double *c
 /* Shape queries: checks, variables, edges, iteration cap (max_iter = 0 at create time means n, as upstream). */
 int scaldpc_bp_info(const scaldpc_bp *h, int *m, int *n, int *edges, int *max_iter);
 long long scaldpc_bp_launch_count(const scaldpc_bp *h);
+/* Statistics of the last decode on this handle: iterations launched (the slowest trial's count) and the number of
+ * active-trial compactions performed. */
+int scaldpc_bp_last_run(const scaldpc_bp *h, int *iterations_launched, int *compactions);
 /* Per-kernel timing probe (bench.py roofline leg), as scaldpc_qary_time_kernel:
  *   which  0 = check-to-bit kernel, 1 = bit-to-check kernel; every tile of the previous decode is re-activated. */
 int scaldpc_bp_time_kernel(scaldpc_bp *h, int which, int T, unsigned flags, int reps, void *stream, float *avg_ms);

@@ -17,7 +17,7 @@ ERR_ARG, ERR_PROB_SUM, ERR_NO_MAX, ERR_NO_CONFIG, ERR_DEGREE, ERR_STRUCTURE, ERR
     -1, -2, -3, -4, -5, -6, -7, -8, -9)
 # decode flags
 IN_LLR, DEVICE_PTRS, CN_EXACT, CN_GENERIC = 0x1, 0x2, 0x4, 0x8
-BP_PROBS_PER_TRIAL, BP_NO_EARLY_STOP = 0x10, 0x20
+BP_PROBS_PER_TRIAL, BP_NO_EARLY_STOP, BP_NO_COMPACT = 0x10, 0x20, 0x40
 
 # every exported symbol of include/scaldpc.h (tests/test_abi.py checks this list against the header)
 SYMBOLS = [
@@ -25,7 +25,7 @@ SYMBOLS = [
     "scaldpc_qary_create", "scaldpc_qary_destroy", "scaldpc_qary_info", "scaldpc_qary_set_max_iter",
     "scaldpc_qary_decode", "scaldpc_qary_launch_count", "scaldpc_qary_time_kernel",
     "scaldpc_bp_create", "scaldpc_bp_destroy", "scaldpc_bp_info", "scaldpc_bp_decode", "scaldpc_bp_launch_count",
-    "scaldpc_bp_time_kernel",
+    "scaldpc_bp_last_run", "scaldpc_bp_time_kernel",
 ]
 
 
@@ -84,6 +84,8 @@ def lib() -> C.CDLL:
     L.scaldpc_bp_decode.argtypes = [vp, i, vp, vp, vp, vp, vp, vp, u, vp]
     L.scaldpc_bp_launch_count.restype = C.c_longlong
     L.scaldpc_bp_launch_count.argtypes = [vp]
+    L.scaldpc_bp_last_run.restype = i
+    L.scaldpc_bp_last_run.argtypes = [vp, ip, ip]
     L.scaldpc_bp_time_kernel.restype = i
     L.scaldpc_bp_time_kernel.argtypes = [vp, i, i, u, i, vp, C.POINTER(C.c_float)]
     _lib = L

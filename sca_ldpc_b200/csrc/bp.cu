@@ -13,27 +13,40 @@
 
 using namespace scaldpc;
 
+// One set of per-slot state.  Two sets exist (ping-pong): compaction gathers the running trials of the current set
+// into the other one; set 1 only ever receives <= half of the slots.
+struct BpSet {
+    int cap_tiles = 0;
+    float *msg = nullptr, *prior_t = nullptr;
+    uint32_t *synd_w = nullptr, *valid = nullptr, *done = nullptr, *unsat = nullptr;
+    int *orig = nullptr;
+};
+
 struct scaldpc_bp {
     int m = 0, n = 0, E = 0, dc_max = 0, dv_max = 0;
-    int max_iter = 0, device = 0;
-    int *d_row_ptr = nullptr, *d_col = nullptr, *d_col_ptr = nullptr, *d_csc_edge = nullptr;
+    int max_iter = 0, device = 0, num_sms = 148;
+    int class_end[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int *d_row_ptr = nullptr, *d_col = nullptr, *d_col_ptr = nullptr, *d_csc_edge = nullptr, *d_vn_order = nullptr;
     // workspace
     int cap_tiles = 0;
     bool cap_post = false, cap_prior_t = false;
-    float *d_msg = nullptr, *d_prior = nullptr, *d_prior_t = nullptr, *d_post = nullptr;
-    uint32_t *d_synd_w = nullptr, *d_dec_w = nullptr, *d_done = nullptr, *d_valid = nullptr, *d_unsat = nullptr;
-    int *d_iters = nullptr, *d_conv = nullptr, *d_n_active = nullptr;
-    int *h_n_active = nullptr;  // pinned
+    BpSet set[2];
+    float *d_prior = nullptr, *d_post = nullptr;
+    uint32_t *d_dec_w = nullptr;
+    int *d_iters = nullptr, *d_conv = nullptr, *d_counts = nullptr, *d_src = nullptr, *d_nact = nullptr;
+    int cap_counts = 0;
+    int *h_pin = nullptr;  // pinned: [0] running trials
     // staging for host-pointer calls
     size_t cap_stage_T = 0;
     bool stage_probs_t = false, stage_llr = false;
     uint8_t *d_synd = nullptr, *d_dec = nullptr;
     double *d_probs = nullptr;
     float *d_llr = nullptr;
+    int cn_warps = 8, cn_occ[2] = {1, 1};
     size_t smem_cn = 0, smem_vn = 0;
     std::mutex mu;
     long long launches = 0;
-    int last_iters_run = 0;
+    int last_iters_run = 0, last_compactions = 0;
 };
 
 namespace {
@@ -46,21 +59,30 @@ int upload_vec(T **dst, const std::vector<T> &src)
     return 0;
 }
 
+void free_set(BpSet &s)
+{
+    cudaFree(s.msg);
+    cudaFree(s.prior_t);
+    cudaFree(s.synd_w);
+    cudaFree(s.valid);
+    cudaFree(s.done);
+    cudaFree(s.unsat);
+    cudaFree(s.orig);
+    s = BpSet();
+}
+
 void free_ws(scaldpc_bp *h)
 {
-    cudaFree(h->d_msg);
-    cudaFree(h->d_prior_t);
+    free_set(h->set[0]);
+    free_set(h->set[1]);
     cudaFree(h->d_post);
-    cudaFree(h->d_synd_w);
     cudaFree(h->d_dec_w);
-    cudaFree(h->d_done);
-    cudaFree(h->d_valid);
-    cudaFree(h->d_unsat);
     cudaFree(h->d_iters);
     cudaFree(h->d_conv);
-    h->d_msg = h->d_prior_t = h->d_post = nullptr;
-    h->d_synd_w = h->d_dec_w = h->d_done = h->d_valid = h->d_unsat = nullptr;
-    h->d_iters = h->d_conv = nullptr;
+    cudaFree(h->d_src);
+    h->d_post = nullptr;
+    h->d_dec_w = nullptr;
+    h->d_iters = h->d_conv = h->d_src = nullptr;
     h->cap_tiles = 0;
     h->cap_post = h->cap_prior_t = false;
 }
@@ -78,6 +100,20 @@ void free_stage(scaldpc_bp *h)
     h->stage_probs_t = h->stage_llr = false;
 }
 
+int alloc_set(scaldpc_bp *h, BpSet &s, int t, bool prior_t)
+{
+    const size_t lanes = (size_t)t * 32;
+    SCALDPC_CUDA(cudaMalloc((void **)&s.msg, std::max<size_t>(1, lanes * h->E) * sizeof(float)));
+    if (prior_t) SCALDPC_CUDA(cudaMalloc((void **)&s.prior_t, lanes * h->n * sizeof(float)));
+    SCALDPC_CUDA(cudaMalloc((void **)&s.synd_w, (size_t)t * h->m * sizeof(uint32_t)));
+    SCALDPC_CUDA(cudaMalloc((void **)&s.valid, (size_t)t * sizeof(uint32_t)));
+    SCALDPC_CUDA(cudaMalloc((void **)&s.done, (size_t)t * sizeof(uint32_t)));
+    SCALDPC_CUDA(cudaMalloc((void **)&s.unsat, (size_t)t * sizeof(uint32_t)));
+    SCALDPC_CUDA(cudaMalloc((void **)&s.orig, lanes * sizeof(int)));
+    s.cap_tiles = t;
+    return 0;
+}
+
 int ensure_ws(scaldpc_bp *h, int tiles, bool post, bool prior_t)
 {
     if (tiles <= h->cap_tiles && (!post || h->cap_post) && (!prior_t || h->cap_prior_t)) return 0;
@@ -86,16 +122,14 @@ int ensure_ws(scaldpc_bp *h, int tiles, bool post, bool prior_t)
     prior_t = prior_t || h->cap_prior_t;
     free_ws(h);
     const size_t lanes = (size_t)t * 32;
-    SCALDPC_CUDA(cudaMalloc((void **)&h->d_msg, std::max<size_t>(1, lanes * h->E) * sizeof(float)));
-    if (prior_t) SCALDPC_CUDA(cudaMalloc((void **)&h->d_prior_t, lanes * h->n * sizeof(float)));
+    int rc;
+    if ((rc = alloc_set(h, h->set[0], t, prior_t))) return rc;
+    if ((rc = alloc_set(h, h->set[1], (t + 1) / 2, prior_t))) return rc;  // compaction target: <= half the slots
     if (post) SCALDPC_CUDA(cudaMalloc((void **)&h->d_post, lanes * h->n * sizeof(float)));
-    SCALDPC_CUDA(cudaMalloc((void **)&h->d_synd_w, (size_t)t * h->m * sizeof(uint32_t)));
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_dec_w, (size_t)t * h->n * sizeof(uint32_t)));
-    SCALDPC_CUDA(cudaMalloc((void **)&h->d_done, (size_t)t * sizeof(uint32_t)));
-    SCALDPC_CUDA(cudaMalloc((void **)&h->d_valid, (size_t)t * sizeof(uint32_t)));
-    SCALDPC_CUDA(cudaMalloc((void **)&h->d_unsat, (size_t)t * sizeof(uint32_t)));
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_iters, lanes * sizeof(int)));
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_conv, lanes * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_src, lanes * sizeof(int)));
     h->cap_tiles = t;
     h->cap_post = post;
     h->cap_prior_t = prior_t;
@@ -119,8 +153,9 @@ int ensure_stage(scaldpc_bp *h, size_t T, bool probs_t, bool llr)
     return 0;
 }
 
-BpDev view(const scaldpc_bp *h, bool per_trial_prior, bool want_post)
+BpDev view(const scaldpc_bp *h, int cur, bool per_trial_prior, bool want_post)
 {
+    const BpSet &s = h->set[cur];
     BpDev p;
     p.m = h->m;
     p.n = h->n;
@@ -132,34 +167,99 @@ BpDev view(const scaldpc_bp *h, bool per_trial_prior, bool want_post)
     p.col = h->d_col;
     p.col_ptr = h->d_col_ptr;
     p.csc_edge = h->d_csc_edge;
-    p.msg = h->d_msg;
-    p.prior = per_trial_prior ? h->d_prior_t : h->d_prior;
-    p.synd_w = h->d_synd_w;
+    p.vn_order = h->d_vn_order;
+    p.msg = s.msg;
+    p.prior = per_trial_prior ? s.prior_t : h->d_prior;
+    p.synd_w = s.synd_w;
     p.dec_w = h->d_dec_w;
     p.post = want_post ? h->d_post : nullptr;
-    p.done = h->d_done;
-    p.valid = h->d_valid;
-    p.unsat = h->d_unsat;
+    p.done = s.done;
+    p.valid = s.valid;
+    p.unsat = s.unsat;
+    p.orig = s.orig;
     p.iters = h->d_iters;
     p.conv = h->d_conv;
-    p.n_active = h->d_n_active;
+    p.counts = h->d_counts;
     return p;
 }
 
+// Check pass: persistent grid, `cn_warps` warps per CTA, as many CTAs per SM as the staging buffers allow.
 int launch_cn(scaldpc_bp *h, const BpDev &p, int tiles, bool first, cudaStream_t st)
 {
-    dim3 grid((h->m + kBpWarps - 1) / kBpWarps, tiles);
-    k_bp_cn<<<grid, kBpWarps * 32, h->smem_cn, st>>>(p, first);
+    const long long items = (long long)tiles * h->m;
+    const int ctas = (int)std::min<long long>((long long)h->num_sms * h->cn_occ[first], (items + h->cn_warps - 1) / h->cn_warps);
+    if (first)
+        k_bp_cn<true><<<std::max(1, ctas), h->cn_warps * 32, h->smem_cn, st>>>(p, tiles);
+    else
+        k_bp_cn<false><<<std::max(1, ctas), h->cn_warps * 32, h->smem_cn, st>>>(p, tiles);
     ++h->launches;
     SCALDPC_CUDA(cudaGetLastError());
     return 0;
 }
 
+template <int DMAX>
+void launch_vn_class(const BpDev &p, int lo, int hi, int tiles, cudaStream_t st)
+{
+    k_bp_vn<DMAX><<<dim3((hi - lo + kBpVnWarps - 1) / kBpVnWarps, tiles), kBpVnWarps * 32, 0, st>>>(p, lo, hi);
+}
+
+// Bit pass: one launch per non-empty degree class (variables are sorted by degree).
 int launch_vn(scaldpc_bp *h, const BpDev &p, int tiles, cudaStream_t st)
 {
-    dim3 grid((h->n + kBpWarps - 1) / kBpWarps, tiles);
-    k_bp_vn<<<grid, kBpWarps * 32, h->smem_vn, st>>>(p);
+    int lo = 0;
+    for (int c = 0; c <= kBpVnClasses; ++c) {
+        const int hi = h->class_end[c];
+        if (hi > lo) {
+            switch (c) {
+            case 0: launch_vn_class<1>(p, lo, hi, tiles, st); break;
+            case 1: launch_vn_class<4>(p, lo, hi, tiles, st); break;
+            case 2: launch_vn_class<8>(p, lo, hi, tiles, st); break;
+            case 3: launch_vn_class<12>(p, lo, hi, tiles, st); break;
+            case 4: launch_vn_class<16>(p, lo, hi, tiles, st); break;
+            case 5: launch_vn_class<24>(p, lo, hi, tiles, st); break;
+            case 6: launch_vn_class<32>(p, lo, hi, tiles, st); break;
+            default:
+                k_bp_vn_generic<<<dim3((hi - lo + kBpVnWarps - 1) / kBpVnWarps, tiles), kBpVnWarps * 32, h->smem_vn, st>>>(
+                    p, lo, hi);
+            }
+            ++h->launches;
+        }
+        lo = hi;
+    }
+    SCALDPC_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// Outputs of the slots selected by `mask` (per tile) of set `cur` -> the caller's arrays (original trial order).
+int write_outputs(scaldpc_bp *h, int cur, int tiles, const uint32_t *mask, uint8_t *ddec, float *dllr, cudaStream_t st)
+{
+    k_bp_unpack_dec<<<dim3((h->n + 31) / 32, tiles), 256, 0, st>>>(h->d_dec_w, ddec, h->set[cur].orig, mask, h->n);
     ++h->launches;
+    if (dllr) {
+        k_bp_untile_f32<<<dim3((h->n + 31) / 32, tiles), 256, 0, st>>>(h->d_post, dllr, h->set[cur].orig, mask, h->n);
+        ++h->launches;
+    }
+    SCALDPC_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// Packs the `n_run` running trials of set `cur` (cur_tiles tiles) into set cur^1; finished trials are written out first.
+int compact(scaldpc_bp *h, int cur, int cur_tiles, int n_run, bool probs_t, uint8_t *ddec, float *dllr, cudaStream_t st)
+{
+    BpSet &a = h->set[cur], &b = h->set[cur ^ 1];
+    const int new_tiles = (n_run + 31) / 32;
+    if (new_tiles > b.cap_tiles) return fail(SCALDPC_ERR_ARG, "internal: compaction target too small");
+    int rc;
+    if ((rc = write_outputs(h, cur, cur_tiles, a.done, ddec, dllr, st))) return rc;
+    k_bp_compact_plan<<<1, kBpPlanThreads, 0, st>>>(a.valid, a.done, a.orig, cur_tiles, h->d_src, b.orig, b.valid, b.done,
+                                                    b.unsat, h->d_nact);
+    k_bp_compact_move<<<dim3((h->E + 63) / 64, new_tiles), 256, 0, st>>>(a.msg, b.msg, h->d_src, h->E);
+    if (probs_t) {
+        k_bp_compact_move<<<dim3((h->n + 63) / 64, new_tiles), 256, 0, st>>>(a.prior_t, b.prior_t, h->d_src, h->n);
+        ++h->launches;
+    }
+    k_bp_compact_bits<<<dim3((h->m + 7) / 8, new_tiles), 256, 0, st>>>(a.synd_w, b.synd_w, h->d_src, h->m);
+    h->launches += 3;
     SCALDPC_CUDA(cudaGetLastError());
     return 0;
 }
@@ -192,21 +292,36 @@ int scaldpc_bp_create(int m, int n, const int32_t *row_ptr, const int32_t *col, 
     h->dv_max = std::max(1, g.dv_max);
     h->max_iter = max_iter == 0 ? n : max_iter;  // upstream: max_iter = 0 means n
     h->device = device;
-    h->smem_cn = (size_t)kBpWarps * 2 * h->dc_max * 32 * sizeof(float);
-    h->smem_vn = (size_t)kBpWarps * 2 * h->dv_max * 32 * sizeof(float);
-    if (h->smem_cn > 227 * 1024 || h->smem_vn > 227 * 1024)
-        return fail(SCALDPC_ERR_UNSUPPORTED, "node degree too large for the shared-memory scratch (dc=%d, dv=%d)",
-                    h->dc_max, h->dv_max);
+    for (int c = 0; c <= kBpVnClasses; ++c) h->class_end[c] = g.class_end[c];
+    // check pass: per warp a double-buffered row stage + the prefix array, 3 x dc_max x 128 B
+    const size_t per_warp = (size_t)3 * h->dc_max * 32 * sizeof(float);
+    h->cn_warps = (int)std::min<size_t>(kBpCnWarpsMax, (216 * 1024) / per_warp);
+    if (h->cn_warps < 1)
+        return fail(SCALDPC_ERR_UNSUPPORTED, "row degree %d too large for the shared-memory staging", h->dc_max);
+    h->smem_cn = per_warp * h->cn_warps;
+    h->smem_vn = (size_t)kBpVnWarps * 2 * h->dv_max * 32 * sizeof(float);
+    if (h->dv_max > kBpVnClass[kBpVnClasses - 1] && h->smem_vn > 227 * 1024)
+        return fail(SCALDPC_ERR_UNSUPPORTED, "column degree %d too large for the shared-memory scratch", h->dv_max);
     SCALDPC_CUDA(cudaSetDevice(device));
+    SCALDPC_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
     int rc;
     if ((rc = upload_vec(&h->d_row_ptr, g.row_ptr)) || (rc = upload_vec(&h->d_col, g.col)) ||
-        (rc = upload_vec(&h->d_col_ptr, g.col_ptr)) || (rc = upload_vec(&h->d_csc_edge, g.csc_edge)))
+        (rc = upload_vec(&h->d_col_ptr, g.col_ptr)) || (rc = upload_vec(&h->d_csc_edge, g.csc_edge)) ||
+        (rc = upload_vec(&h->d_vn_order, g.vn_order)))
         return rc;
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_prior, (size_t)n * sizeof(float)));
-    SCALDPC_CUDA(cudaMalloc((void **)&h->d_n_active, sizeof(int)));
-    SCALDPC_CUDA(cudaMallocHost((void **)&h->h_n_active, sizeof(int)));
-    SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_cn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_cn));
-    SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_vn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_vn));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_nact, sizeof(int)));
+    h->cap_counts = h->max_iter + 2;
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_counts, (size_t)h->cap_counts * sizeof(int)));
+    SCALDPC_CUDA(cudaMallocHost((void **)&h->h_pin, 2 * sizeof(int)));
+    SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_cn<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_cn));
+    SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_cn<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_cn));
+    if (h->dv_max > kBpVnClass[kBpVnClasses - 1])
+        SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_vn_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_vn));
+    SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->cn_occ[0], k_bp_cn<false>, h->cn_warps * 32, h->smem_cn));
+    SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->cn_occ[1], k_bp_cn<true>, h->cn_warps * 32, h->smem_cn));
+    h->cn_occ[0] = std::max(1, h->cn_occ[0]);
+    h->cn_occ[1] = std::max(1, h->cn_occ[1]);
     *out = h.release();
     return 0;
 }
@@ -221,9 +336,11 @@ void scaldpc_bp_destroy(scaldpc_bp *h)
     cudaFree(h->d_col);
     cudaFree(h->d_col_ptr);
     cudaFree(h->d_csc_edge);
+    cudaFree(h->d_vn_order);
     cudaFree(h->d_prior);
-    cudaFree(h->d_n_active);
-    if (h->h_n_active) cudaFreeHost(h->h_n_active);
+    cudaFree(h->d_nact);
+    cudaFree(h->d_counts);
+    if (h->h_pin) cudaFreeHost(h->h_pin);
     delete h;
 }
 
@@ -249,6 +366,7 @@ int scaldpc_bp_decode(scaldpc_bp *h, int T, const uint8_t *synd, const double *c
     const bool dev_ptrs = flags & SCALDPC_DEVICE_PTRS;
     const bool probs_t = flags & SCALDPC_BP_PROBS_PER_TRIAL;
     const bool early = !(flags & SCALDPC_BP_NO_EARLY_STOP);
+    const bool compacting = early && !(flags & SCALDPC_BP_NO_COMPACT);
     const bool want_post = llr != nullptr;
     cudaStream_t st = (cudaStream_t)stream;
 
@@ -273,49 +391,52 @@ int scaldpc_bp_decode(scaldpc_bp *h, int T, const uint8_t *synd, const double *c
         dllr = want_post ? h->d_llr : nullptr;
     }
 
-    // ---- inputs -> tile layout
+    // ---- inputs -> tile layout (always into set 0)
+    BpSet &s0 = h->set[0];
     const int tb = (tiles + 255) / 256;
-    k_bp_reset<<<tb, 256, 0, st>>>(h->d_valid, h->d_done, h->d_unsat, h->d_iters, h->d_conv, tiles, T, h->max_iter);
+    k_bp_reset<<<tb, 256, 0, st>>>(s0.valid, s0.done, s0.unsat, s0.orig, h->d_iters, h->d_conv, tiles, T, h->max_iter);
     if (probs_t)
-        k_bp_prior_tiled<<<dim3((h->n + 31) / 32, tiles), 256, 0, st>>>(dprobs, h->d_prior_t, T, h->n);
+        k_bp_prior_tiled<<<dim3((h->n + 31) / 32, tiles), 256, 0, st>>>(dprobs, s0.prior_t, T, h->n);
     else
         k_bp_prior_shared<<<(h->n + 255) / 256, 256, 0, st>>>(dprobs, h->d_prior, h->n);
-    k_bp_pack_synd<<<dim3((h->m + 31) / 32, tiles), 256, 0, st>>>(dsynd, h->d_synd_w, T, h->m);
+    k_bp_pack_synd<<<dim3((h->m + 31) / 32, tiles), 256, 0, st>>>(dsynd, s0.synd_w, T, h->m);
     SCALDPC_CUDA(cudaMemsetAsync(h->d_dec_w, 0, (size_t)tiles * h->n * sizeof(uint32_t), st));
+    SCALDPC_CUDA(cudaMemsetAsync(h->d_counts, 0, (size_t)h->cap_counts * sizeof(int), st));
     h->launches += 3;
     SCALDPC_CUDA(cudaGetLastError());
 
-    // ---- iterations
-    const BpDev p = view(h, probs_t, want_post);
-    // The host looks at the number of running tiles every `poll` iterations (one small D2H + sync) and stops
-    // launching when it reaches zero; in between, retired tiles exit at the top of every kernel.
-    const int poll = 4;
+    // ---- iterations.  The host reads the number of running trials (one 4-byte D2H + sync) after the first
+    // iterations, then every 4th (every iteration while the batch is large enough to hide the sync); it stops
+    // launching at zero and compacts the running trials when they fill at most half of the current slots.
+    int cur = 0, cur_tiles = tiles;
+    h->last_compactions = 0;
     int it = 1;
     for (; it <= h->max_iter; ++it) {
         const bool last = it == h->max_iter;
-        if ((rc = launch_cn(h, p, tiles, it == 1, st))) return rc;
-        if ((rc = launch_vn(h, p, tiles, st))) return rc;
-        k_bp_syndrome<<<dim3((h->m + 255) / 256, tiles), 256, 0, st>>>(p);
-        SCALDPC_CUDA(cudaMemsetAsync(h->d_n_active, 0, sizeof(int), st));
-        k_bp_finish_iter<<<tb, 256, 0, st>>>(p, tiles, it, early, last);
+        const BpDev p = view(h, cur, probs_t, want_post);
+        if ((rc = launch_cn(h, p, cur_tiles, it == 1, st))) return rc;
+        if ((rc = launch_vn(h, p, cur_tiles, st))) return rc;
+        k_bp_syndrome<<<dim3((h->m + 255) / 256, cur_tiles), 256, 0, st>>>(p);
+        k_bp_finish_iter<<<(cur_tiles + 255) / 256, 256, 0, st>>>(p, cur_tiles, it, early, last);
         h->launches += 2;
         SCALDPC_CUDA(cudaGetLastError());
-        if (early && !last && (it % poll == 0 || it <= 3)) {
-            SCALDPC_CUDA(cudaMemcpyAsync(h->h_n_active, h->d_n_active, sizeof(int), cudaMemcpyDeviceToHost, st));
+        if (early && !last && (it <= 4 || it % 4 == 0 || cur_tiles >= 32)) {
+            SCALDPC_CUDA(cudaMemcpyAsync(h->h_pin, h->d_counts + it, sizeof(int), cudaMemcpyDeviceToHost, st));
             SCALDPC_CUDA(cudaStreamSynchronize(st));
-            if (*h->h_n_active == 0) break;
+            const int n_run = h->h_pin[0];
+            if (n_run == 0) break;
+            if (compacting && cur_tiles >= 2 && (long long)n_run * 2 <= (long long)cur_tiles * 32) {
+                if ((rc = compact(h, cur, cur_tiles, n_run, probs_t, ddec, dllr, st))) return rc;
+                cur ^= 1;
+                cur_tiles = (n_run + 31) / 32;
+                ++h->last_compactions;
+            }
         }
     }
     h->last_iters_run = std::min(it, h->max_iter);
 
-    // ---- outputs
-    k_bp_unpack_dec<<<dim3((h->n + 31) / 32, tiles), 256, 0, st>>>(h->d_dec_w, ddec, T, h->n);
-    ++h->launches;
-    if (dllr) {
-        k_bp_untile_f32<<<dim3((h->n + 31) / 32, tiles), 256, 0, st>>>(h->d_post, dllr, T, h->n);
-        ++h->launches;
-    }
-    SCALDPC_CUDA(cudaGetLastError());
+    // ---- outputs of every trial still resident (finished since the last compaction, or never converged)
+    if ((rc = write_outputs(h, cur, cur_tiles, h->set[cur].valid, ddec, dllr, st))) return rc;
     const cudaMemcpyKind kind = dev_ptrs ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
     if (!dev_ptrs) {
         SCALDPC_CUDA(cudaMemcpyAsync(decoding, h->d_dec, (size_t)T * h->n, kind, st));
@@ -324,6 +445,14 @@ int scaldpc_bp_decode(scaldpc_bp *h, int T, const uint8_t *synd, const double *c
     if (iters) SCALDPC_CUDA(cudaMemcpyAsync(iters, h->d_iters, (size_t)T * sizeof(int), kind, st));
     if (converged) SCALDPC_CUDA(cudaMemcpyAsync(converged, h->d_conv, (size_t)T * sizeof(int), kind, st));
     if (!dev_ptrs) SCALDPC_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int scaldpc_bp_last_run(const scaldpc_bp *h, int *iterations_launched, int *compactions)
+{
+    if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
+    if (iterations_launched) *iterations_launched = h->last_iters_run;
+    if (compactions) *compactions = h->last_compactions;
     return 0;
 }
 
@@ -337,13 +466,17 @@ int scaldpc_bp_time_kernel(scaldpc_bp *h, int which, int T, unsigned flags, int 
     cudaStream_t st = (cudaStream_t)stream;
     const bool probs_t = flags & SCALDPC_BP_PROBS_PER_TRIAL;
     if (probs_t && !h->cap_prior_t) return fail(SCALDPC_ERR_ARG, "no per-trial priors resident");
-    const BpDev p = view(h, probs_t, false);
-    // every tile must run: clear the done masks (the message state of a finished decode is a valid BP state)
-    SCALDPC_CUDA(cudaMemsetAsync(h->d_done, 0, (size_t)tiles * sizeof(uint32_t), st));
+    // every slot of set 0 runs again: reset the masks and rebuild an iteration-1 message state from the priors
+    // (the syndrome words are whatever the previous decode left there; the kernels' work does not depend on them)
+    BpSet &s0 = h->set[0];
+    k_bp_reset<<<(tiles + 255) / 256, 256, 0, st>>>(s0.valid, s0.done, s0.unsat, s0.orig, h->d_iters, h->d_conv, tiles, T,
+                                                    h->max_iter);
+    const BpDev p = view(h, 0, probs_t, false);
+    int rc;
+    if ((rc = launch_cn(h, p, tiles, true, st)) || (rc = launch_vn(h, p, tiles, st))) return rc;
     cudaEvent_t e0, e1;
     SCALDPC_CUDA(cudaEventCreate(&e0));
     SCALDPC_CUDA(cudaEventCreate(&e1));
-    int rc = 0;
     for (int i = -1; i < reps && !rc; ++i) {
         if (i == 0) SCALDPC_CUDA(cudaEventRecord(e0, st));
         rc = which == 0 ? launch_cn(h, p, tiles, false, st) : launch_vn(h, p, tiles, st);

@@ -16,7 +16,14 @@ struct BpHostGraph {
     int m = 0, n = 0, E = 0;
     int dc_max = 0, dv_max = 0;
     std::vector<int> row_ptr, col, col_ptr, csc_edge;
+    // variables sorted by degree (ascending, stable) and the end index of each degree class in that order:
+    // class c holds the variables with degree <= kBpVnClass[c] (the last class, "generic", holds the rest)
+    std::vector<int> vn_order;
+    int class_end[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 };
+
+constexpr int kBpVnClasses = 7;
+constexpr int kBpVnClass[kBpVnClasses] = {1, 4, 8, 12, 16, 24, 32};
 
 inline int build_bp_graph(int m, int n, const int32_t *row_ptr, const int32_t *col, BpHostGraph &g, std::string &err)
 {
@@ -53,6 +60,19 @@ inline int build_bp_graph(int m, int n, const int32_t *row_ptr, const int32_t *c
     std::vector<int> fill(n, 0);
     for (int r = 0; r < m; ++r)
         for (int e = row_ptr[r]; e < row_ptr[r + 1]; ++e) g.csc_edge[g.col_ptr[col[e]] + fill[col[e]]++] = e;
+    g.vn_order.resize(n);
+    for (int c = 0; c < n; ++c) g.vn_order[c] = c;
+    std::stable_sort(g.vn_order.begin(), g.vn_order.end(), [&](int a, int b) {
+        return g.col_ptr[a + 1] - g.col_ptr[a] < g.col_ptr[b + 1] - g.col_ptr[b];
+    });
+    {
+        int i = 0;
+        for (int c = 0; c < kBpVnClasses; ++c) {
+            while (i < n && g.col_ptr[g.vn_order[i] + 1] - g.col_ptr[g.vn_order[i]] <= kBpVnClass[c]) ++i;
+            g.class_end[c] = i;
+        }
+        g.class_end[kBpVnClasses] = n;
+    }
     return SCALDPC_OK;
 }
 

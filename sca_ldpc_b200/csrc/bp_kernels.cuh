@@ -1,25 +1,31 @@
 // Binary product-sum BP kernels for sm_100a (B200): flooding schedule, syndrome-match early stop, per-trial
-// freeze + tile retirement.  Replaces ldpc.bp_decoder(bp_method="product_sum") as called at
+// freeze and active-trial compaction.  Replaces ldpc.bp_decoder(bp_method="product_sum") as called at
 // simulate/hqc.py:694-708 and simulate/decode.py:155-171 (third-party PyPI ldpc==0.1.3, algorithm as summarised in
 // SURVEY.md appendix B).  Hand-written CUDA; no tensor cores (irregular gather + scalar updates, HBM-bound).
 //
-// Arithmetic: upstream keeps fp64 probability RATIOS r = p1/p0 and multiplies running products; here messages are
-// fp32 LLRs L = log(p0/p1) = -log r, so every product becomes a sum and the check-node rule
-//     c2b = (1-x)/(1+x),  x = (-1)^synd * prod_{others} (2/(1+r_k) - 1) = (-1)^synd * prod tanh(L_k/2)
-// becomes, with phi(x) = -log tanh(x/2) (its own inverse),
-//     |c2v| = phi( sum_{others} phi(|L_k|) ),   sign(c2v) = (-1)^synd * prod_{others} sign(L_k).
-// The sums over "others" are forward/backward running sums in the row's column order (upstream's running products),
-// never total-minus-self, so there is no cancellation.  The bit-node rule keeps upstream's sequential semantics
-// including "NaN -> neutral element" resets of the running product (0 * inf in ratios == inf - inf in LLRs).
+// Arithmetic: upstream keeps fp64 probability RATIOS r = p1/p0 and multiplies running products.  Here:
+//   * bit -> check messages travel as signed FOLDED PROBABILITIES  q = copysign(u, L),  u = 1/(1+e^|L|) = min(p0,p1)
+//     in (0, 1/2], L = log(p0/p1) the fp32 LLR.  tanh(|L|/2) = 1 - 2u, so upstream's running product of
+//     (2/(1+r) - 1) becomes the parity recurrence  U <- U + u - 2Uu  (U = probability that the magnitudes seen so far
+//     have odd parity, always <= 1/2: only positive terms, no cancellation, exact at u = 0 and u = 1/2) plus an XOR
+//     of the signs; prefix / suffix recurrences in the row's column order replace upstream's forward / backward
+//     products (never total-divided-by-self);
+//   * check -> bit messages travel as LLRs  c2v = +-ln((1-U)/U)  (upstream: c2b = (1-x)/(1+x)), so the bit node sums
+//     where upstream multiplies (no under/overflow for heavy columns) and keeps upstream's sequential semantics
+//     including the "NaN -> neutral element" resets of the running product (0 * inf in ratios == inf - inf in LLRs).
+// Cost per edge and iteration: ex2 + rcp (fold) and 2 x lg2 (unfold) on the MUFU pipe and ~40 other instructions;
+// the earlier phi(x) = -log tanh(x/2) formulation needed ~110 and left both passes issue-bound.
 //
 // Data layout in HBM ("tile" layout, shared with the q-ary decoder): 32 trials per tile, lane = trial % 32 innermost.
-//     msg     [tile][E][32] f32   v2c before a check pass, c2v after it (in place; one writer per slot)
+//     msg     [tile][E][32] f32   q(v2c) before a check pass, c2v (LLR) after it (in place; one writer per slot)
 //     prior   [n] f32 (shared by all trials)  or  [tile][n][32] f32 (per-trial channel_probs)
 //     synd_w  [tile][m]  u32      bit l = syndrome bit of trial l of the tile
 //     dec_w   [tile][n]  u32      bit l = current hard decision of trial l      (warp ballot)
 //     post    [tile][n][32] f32   posterior LLRs (only when the caller asks for them)
 //     done    [tile] u32          bit l = trial l has converged (outputs frozen);  valid [tile] u32 = real trials
 //     unsat   [tile] u32          bit l = some check of trial l is unsatisfied this iteration
+//     orig    [tile*32] i32       original trial index of a slot (slots move when the active trials are compacted)
+//     counts  [max_iter+2] i32    counts[it] = trials still running after iteration it
 #pragma once
 #include <stdint.h>
 #ifdef SCALDPC_HOST_MODEL
@@ -32,6 +38,8 @@
 
 namespace scaldpc {
 
+#include "tma.cuh"
+
 struct BpDev {
     int m, n, E;
     int dc_max, dv_max;
@@ -40,6 +48,7 @@ struct BpDev {
     const int *col;           // E
     const int *col_ptr;       // n+1
     const int *csc_edge;      // E
+    const int *vn_order;      // n: variables sorted by degree (ascending), the bit pass runs one launch per class
     float *msg;
     const float *prior;
     const uint32_t *synd_w;
@@ -48,9 +57,10 @@ struct BpDev {
     uint32_t *done;
     const uint32_t *valid;
     uint32_t *unsat;
-    int *iters;               // tiles*32
-    int *conv;                // tiles*32
-    int *n_active;            // [1] tiles still running after the last finished iteration
+    const int *orig;          // tiles*32
+    int *iters;               // T, indexed by ORIGINAL trial
+    int *conv;                // T
+    int *counts;              // max_iter+2
 };
 
 #ifdef SCALDPC_HOST_MODEL
@@ -60,86 +70,249 @@ __device__ __forceinline__ bool bp_signbit(float x)
     memcpy(&u, &x, 4);
     return u >> 31;
 }
+__device__ __forceinline__ float bp_ex2(float x) { return exp2f(x); }
+__device__ __forceinline__ float bp_lg2(float x) { return log2f(x); }
+__device__ __forceinline__ float bp_rcp(float x) { return 1.0f / x; }
 #else
 __device__ __forceinline__ bool bp_signbit(float x) { return __float_as_uint(x) >> 31; }
+// MUFU.EX2 / MUFU.LG2 with subnormal results / arguments kept (a very reliable message, |L| > 87, must not flush to an
+// exact 0 == "infinitely reliable"); MUFU.RCP only ever sees 1 + t in [1, 2].
+__device__ __forceinline__ float bp_ex2(float x)
+{
+    float r;
+    asm("ex2.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float bp_lg2(float x)
+{
+    float r;
+    asm("lg2.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float bp_rcp(float x)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
 #endif
 
-// phi(x) = -log(tanh(x/2)) = log((1+e^-x)/(1-e^-x)) for x >= 0; phi(0) = +inf, phi(+inf) = 0, phi(NaN) = NaN.
-// Three ranges keep the relative error at a few ulp without expm1/log1p calls.
-__device__ __forceinline__ float bp_phi(float x)
+// LLR -> signed folded probability  q = copysign(1/(1+e^|L|), L).  fold(+-inf) = +-0, fold(+-0) = +-1/2, NaN -> NaN.
+__device__ __forceinline__ float bp_fold(float L)
 {
-    if (x < 0.125f) {  // -log(y) + y^2/3 - 7y^4/90, y = x/2
-        const float y = 0.5f * x, y2 = y * y;
-        return y2 * (0.33333334f - 0.07777778f * y2) - logf(y);
-    }
-    const float t = expf(-x);
-    if (t < 0.03125f) {  // 2 atanh(t) = 2t (1 + t^2/3 + t^4/5 + ...)
-        const float t2 = t * t;
-        return 2.0f * t * (1.0f + t2 * (0.33333334f + 0.2f * t2));
-    }
-    return logf((1.0f + t) / (1.0f - t));  // NaN lands here and stays NaN
+    const float t = bp_ex2(-1.4426950408889634f * fabsf(L));  // e^-|L| in [0, 1]
+    return copysignf(t * bp_rcp(1.0f + t), L);
 }
+// Odd-parity probability U in [0, 1/2] -> LLR magnitude ln((1-U)/U) >= 0.  unfold(0) = +inf, unfold(1/2) = 0.
+__device__ __forceinline__ float bp_unfold(float U) { return 0.6931471805599453f * (bp_lg2(1.0f - U) - bp_lg2(U)); }
+// One more magnitude u joins a parity: U + u - 2Uu.
+__device__ __forceinline__ float bp_parity(float U, float u) { return fmaf(u, fmaf(-2.0f, U, 1.0f), U); }
 
 __device__ __forceinline__ float bp_prior_of(const BpDev &p, int tile, int v, int lane)
 {
     return p.per_trial_prior ? p.prior[((size_t)tile * p.n + v) * 32 + lane] : __ldg(p.prior + v);
 }
 
-constexpr int kBpWarps = 4;  // warps per CTA of the check / bit kernels (each warp owns 2*dmax*128 B of scratch)
+__device__ __forceinline__ bool bp_tile_done(const BpDev &p, int tile) { return __ldg(p.done + tile) == __ldg(p.valid + tile); }
 
 // -----------------------------------------------------------------------------------------------------------
-// Check-to-bit pass.  One warp = (tile, check), lane = trial.  Scratch per lane: A[k] = phi(|L_k|) with the sign
-// of L_k, P[k] = exclusive prefix sum of phi.  FIRST: v2c is the channel prior (upstream's init b2c = p/(1-p)).
+// Check-to-bit pass.  Work item = (tile, check); one warp per item, lane = trial.  A row's messages are ONE
+// contiguous block of d x 128 B in the tile layout.  Persistent kernel: warps stride over the items; lane 0 fetches
+// the NEXT item's block with one bulk-async copy (TMA, cp.async.bulk + mbarrier complete_tx) into the other half of
+// a double buffer while the warp works on the current one, so the HBM latency hides behind ~2 k instructions of
+// arithmetic (v0 issued 4 plain loads at a time from 16 warps per SM: latency-bound at 0.13 of the HBM peak).
+// Per lane: P[k] = parity of the magnitudes before k (shared memory, [k][lane], conflict-free), then backwards
+// c2v_k = sign * unfold(parity(P[k], suffix)), stored straight to global memory (coalesced 128 B per warp store).
+// FIRST: q is computed from the channel prior (upstream's init b2c = p/(1-p)); nothing is staged.
 // -----------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kBpWarps * 32) k_bp_cn(const BpDev p, const int FIRST)
+constexpr int kBpCnWarpsMax = 16;
+
+template <bool FIRST>
+__global__ void __launch_bounds__(kBpCnWarpsMax * 32) k_bp_cn(const BpDev p, const int tiles)
 {
     SCALDPC_DYN_SMEM(float, smem);
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int check = blockIdx.x * kBpWarps + warp;
-    const int tile = blockIdx.y;
-    if (check >= p.m) return;
-    if (__ldg(p.done + tile) == __ldg(p.valid + tile)) return;  // every trial of the tile has converged
-    const int e0 = __ldg(p.row_ptr + check), d = __ldg(p.row_ptr + check + 1) - e0;
-    float *A = smem + (size_t)warp * 2 * p.dc_max * 32 + lane;
-    float *P = A + (size_t)p.dc_max * 32;
-    float *msg = p.msg + ((size_t)tile * p.E + e0) * 32 + lane;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
+    const int gw = blockIdx.x * wpc + warp, nw = gridDim.x * wpc;
+    const int n_items = tiles * p.m;
+    const int stride = p.dc_max * 32;                // floats per per-warp array
+    float *wbase = smem + (size_t)warp * 3 * stride;  // stage[2], P
+    float *P = wbase + 2 * stride + lane;
 
-    bool neg = (__ldg(p.synd_w + (size_t)tile * p.m + check) >> lane) & 1u;
-    float pre = 0.0f;
-#pragma unroll 4
-    for (int k = 0; k < d; ++k) {
-        const float v = FIRST ? bp_prior_of(p, tile, __ldg(p.col + e0 + k), lane) : msg[(size_t)k * 32];
-        const float ph = bp_phi(fabsf(v));
-        A[k * 32] = copysignf(ph, v);
-        P[k * 32] = pre;
-        pre += ph;
-        neg ^= bp_signbit(v);
+    // next item >= `item` (stepping by nw) whose tile still has running trials
+    auto next_live = [&](int item) {
+        while (item < n_items && bp_tile_done(p, item / p.m)) item += nw;
+        return item;
+    };
+#ifndef SCALDPC_HOST_MODEL
+    __shared__ uint64_t bars[kBpCnWarpsMax][2];
+    uint32_t phases = 0;  // bit b = parity to wait for on bars[warp][b]
+    if (!FIRST) {
+        if (lane == 0) {
+            sc_mbar_init(&bars[warp][0], 1);
+            sc_mbar_init(&bars[warp][1], 1);
+        }
+        __syncwarp();
     }
-    float suf = 0.0f;
+    auto issue = [&](int item, int b) {  // lane 0 only
+        const int tile = item / p.m, check = item - tile * p.m;
+        const int e0 = __ldg(p.row_ptr + check), d = __ldg(p.row_ptr + check + 1) - e0;
+        if (d <= 0) return;
+        sc_mbar_expect_tx(&bars[warp][b], (uint32_t)d * 128u);
+        sc_bulk_g2s(wbase + b * stride, p.msg + ((size_t)tile * p.E + e0) * 32, (uint32_t)d * 128u, &bars[warp][b]);
+    };
+#endif
+
+    int item = next_live(gw);
+    int b = 0;
+#ifndef SCALDPC_HOST_MODEL
+    if (!FIRST && item < n_items && lane == 0) issue(item, 0);
+#endif
+    while (item < n_items) {
+        const int nxt = next_live(item + nw);
+#ifndef SCALDPC_HOST_MODEL
+        if (!FIRST && nxt < n_items && lane == 0) {
+            sc_fence_proxy_async();  // the other half was read (generic proxy) during the previous item
+            issue(nxt, b ^ 1);
+        }
+#endif
+        const int tile = item / p.m, check = item - tile * p.m;
+        const int e0 = __ldg(p.row_ptr + check), d = __ldg(p.row_ptr + check + 1) - e0;
+        float *msg = p.msg + ((size_t)tile * p.E + e0) * 32 + lane;
+        if (d > 0) {
+#ifdef SCALDPC_HOST_MODEL
+            const float *a = msg;  // the host model reads the row in place
+#else
+            const float *a = wbase + b * stride + lane;
+            if (!FIRST) {
+                sc_mbar_wait(&bars[warp][b], (phases >> b) & 1u);
+                phases ^= 1u << b;
+            }
+#endif
+            bool neg = (__ldg(p.synd_w + (size_t)tile * p.m + check) >> lane) & 1u;
+            float pre = 0.0f;
+            if (FIRST) {
+#ifdef SCALDPC_HOST_MODEL
+                float *park = msg;  // host model: parked in place, re-read below by the same lane
+#else
+                float *park = wbase + lane;  // stage[0] is unused by the first pass
+#endif
 #pragma unroll 4
-    for (int k = d - 1; k >= 0; --k) {
-        const float a = A[k * 32];
-        const float mag = bp_phi(P[k * 32] + suf);
-        msg[(size_t)k * 32] = (neg != bp_signbit(a)) ? -mag : mag;
-        suf += fabsf(a);
+                for (int k = 0; k < d; ++k) {
+                    const float v = bp_prior_of(p, tile, __ldg(p.col + e0 + k), lane);
+                    const float q = bp_fold(v);
+                    P[k * 32] = pre;
+                    park[(size_t)k * 32] = q;
+                    pre = bp_parity(pre, fabsf(q));
+                    neg ^= bp_signbit(v);
+                }
+                a = park;
+            } else {
+#pragma unroll 8
+                for (int k = 0; k < d; ++k) {
+                    const float x = a[k * 32];
+                    P[k * 32] = pre;
+                    pre = bp_parity(pre, fabsf(x));
+                    neg ^= bp_signbit(x);
+                }
+            }
+            float suf = 0.0f;
+#pragma unroll 4
+            for (int k = d - 1; k >= 0; --k) {
+                const float x = a[k * 32];
+                const float mag = bp_unfold(bp_parity(P[k * 32], suf));  // parity of the OTHER magnitudes
+                msg[(size_t)k * 32] = (neg != bp_signbit(x)) ? -mag : mag;
+                suf = bp_parity(suf, fabsf(x));
+            }
+        }
+#ifndef SCALDPC_HOST_MODEL
+        __syncwarp();  // every lane is done with stage[b] before lane 0 re-arms it (next iteration)
+#endif
+        item = nxt;
+        b ^= 1;
     }
 }
 
 // -----------------------------------------------------------------------------------------------------------
 // Bit-to-check pass + decision.  One warp = (tile, variable), lane = trial.  Upstream's two sweeps over the
 // column (rows ascending): forward running value seeded with the prior, backward running value seeded with the
-// neutral element; a NaN running value is reset to the neutral element (ratio 1 == LLR 0).
-// Decision: upstream decodes 1 when ratio >= 1, i.e. LLR <= 0.  Converged (done) lanes keep their old outputs.
+// neutral element; a NaN running value is reset to the neutral element (ratio 1 == LLR 0).  Stores
+// q = fold(v2c).  Decision: upstream decodes 1 when ratio >= 1, i.e. LLR <= 0.  Converged (done)
+// lanes keep their old outputs.
+// The variables are processed in degree order, one launch per degree class DMAX: all of a variable's incoming
+// messages are gathered into registers by DMAX independent loads (the v0 kernel walked the column 4 loads at a time
+// through shared memory and was latency-bound at 0.35 of the HBM peak).
 // -----------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kBpWarps * 32) k_bp_vn(const BpDev p)
+constexpr int kBpVnWarps = 4;
+
+__device__ __forceinline__ void bp_vn_decide(const BpDev &p, int tile, int var, int lane, uint32_t done, float post)
+{
+    const bool active = !((done >> lane) & 1u);
+    if (p.post && active) p.post[((size_t)tile * p.n + var) * 32 + lane] = post;
+#ifdef SCALDPC_HOST_MODEL
+    uint32_t &w = p.dec_w[(size_t)tile * p.n + var];
+    if (active) w = (w & ~(1u << lane)) | ((post <= 0.0f ? 1u : 0u) << lane);
+#else
+    const uint32_t bits = __ballot_sync(0xffffffffu, post <= 0.0f);
+    if (lane == 0) {
+        uint32_t *w = p.dec_w + (size_t)tile * p.n + var;
+        *w = (*w & done) | (bits & ~done);
+    }
+#endif
+}
+
+template <int DMAX>
+__global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const int v_lo, const int v_hi)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int idx = v_lo + blockIdx.x * kBpVnWarps + warp;
+    const int tile = blockIdx.y;
+    if (idx >= v_hi) return;
+    const uint32_t done = __ldg(p.done + tile);
+    if (done == __ldg(p.valid + tile)) return;
+    const int var = __ldg(p.vn_order + idx);
+    const int p0 = __ldg(p.col_ptr + var), d = __ldg(p.col_ptr + var + 1) - p0;  // d <= DMAX
+    float *msg = p.msg + (size_t)tile * p.E * 32 + lane;
+
+    int off[DMAX];
+    float c[DMAX], F[DMAX];
+#pragma unroll
+    for (int i = 0; i < DMAX; ++i)
+        if (i < d) {
+            off[i] = __ldg(p.csc_edge + p0 + i);
+            c[i] = msg[(size_t)off[i] * 32];
+        }
+    float temp = bp_prior_of(p, tile, var, lane);
+#pragma unroll
+    for (int i = 0; i < DMAX; ++i)
+        if (i < d) {
+            F[i] = temp;
+            temp += c[i];
+            if (temp != temp) temp = 0.0f;
+        }
+    const float post = temp;
+    temp = 0.0f;
+#pragma unroll
+    for (int i = DMAX - 1; i >= 0; --i)
+        if (i < d) {
+            const float v = F[i] + temp;
+            msg[(size_t)off[i] * 32] = bp_fold(v);
+            temp += c[i];
+            if (temp != temp) temp = 0.0f;
+        }
+    bp_vn_decide(p, tile, var, lane, done, post);
+}
+
+// Any degree (columns heavier than the largest register class): per-lane scratch [i][lane] in shared memory.
+__global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_generic(const BpDev p, const int v_lo, const int v_hi)
 {
     SCALDPC_DYN_SMEM(float, smem);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int var = blockIdx.x * kBpWarps + warp;
+    const int idx = v_lo + blockIdx.x * kBpVnWarps + warp;
     const int tile = blockIdx.y;
-    if (var >= p.n) return;
+    if (idx >= v_hi) return;
     const uint32_t done = __ldg(p.done + tile);
     if (done == __ldg(p.valid + tile)) return;
+    const int var = __ldg(p.vn_order + idx);
     const int p0 = __ldg(p.col_ptr + var), d = __ldg(p.col_ptr + var + 1) - p0;
     float *C = smem + (size_t)warp * 2 * p.dv_max * 32 + lane;
     float *F = C + (size_t)p.dv_max * 32;
@@ -157,22 +330,12 @@ __global__ void __launch_bounds__(kBpWarps * 32) k_bp_vn(const BpDev p)
     const float post = temp;
     temp = 0.0f;
     for (int i = d - 1; i >= 0; --i) {
-        msg[(size_t)__ldg(p.csc_edge + p0 + i) * 32] = F[i * 32] + temp;
+        const float v = F[i * 32] + temp;
+        msg[(size_t)__ldg(p.csc_edge + p0 + i) * 32] = bp_fold(v);
         temp += C[i * 32];
         if (temp != temp) temp = 0.0f;
     }
-    const bool active = !((done >> lane) & 1u);
-    if (p.post && active) p.post[((size_t)tile * p.n + var) * 32 + lane] = post;
-#ifdef SCALDPC_HOST_MODEL
-    uint32_t &w = p.dec_w[(size_t)tile * p.n + var];
-    if (active) w = (w & ~(1u << lane)) | ((post <= 0.0f ? 1u : 0u) << lane);
-#else
-    const uint32_t bits = __ballot_sync(0xffffffffu, post <= 0.0f);
-    if (lane == 0) {
-        uint32_t *w = p.dec_w + (size_t)tile * p.n + var;
-        *w = (*w & done) | (bits & ~done);
-    }
-#endif
+    bp_vn_decide(p, tile, var, lane, done, post);
 }
 
 // -----------------------------------------------------------------------------------------------------------
@@ -183,7 +346,7 @@ __global__ void __launch_bounds__(256) k_bp_syndrome(const BpDev p)
 {
     const int tile = blockIdx.y;
     const int check = blockIdx.x * blockDim.x + threadIdx.x;
-    if (__ldg(p.done + tile) == __ldg(p.valid + tile)) return;
+    if (bp_tile_done(p, tile)) return;
     uint32_t bad = 0;
     if (check < p.m) {
         const uint32_t *dec = p.dec_w + (size_t)tile * p.n;
@@ -200,8 +363,8 @@ __global__ void __launch_bounds__(256) k_bp_syndrome(const BpDev p)
 #endif
 }
 
-// End of iteration `it`: trials whose syndrome matched are frozen (iters = it, converged = 1); counts the tiles
-// that still have running trials.  One thread per tile.
+// End of iteration `it`: trials whose syndrome matched are frozen (iters = it, converged = 1); counts[it] receives
+// the number of trials still running.  One thread per tile.
 __global__ void __launch_bounds__(256) k_bp_finish_iter(const BpDev p, int tiles, int it, int early_stop, int last)
 {
     const int tile = blockIdx.x * blockDim.x + threadIdx.x;
@@ -213,25 +376,28 @@ __global__ void __launch_bounds__(256) k_bp_finish_iter(const BpDev p, int tiles
     if (early_stop || last) {
         for (int l = 0; l < 32; ++l)
             if ((ok >> l) & 1u) {
-                p.iters[tile * 32 + l] = it;
-                p.conv[tile * 32 + l] = 1;
+                const int o = p.orig[tile * 32 + l];
+                p.iters[o] = it;
+                p.conv[o] = 1;
             }
     }
     if (early_stop) {
         p.done[tile] = done | ok;
-        if ((done | ok) != valid) {
+        const int running = __popc(valid & ~(done | ok));
+        if (running) {
 #ifdef SCALDPC_HOST_MODEL
-            ++*p.n_active;
+            p.counts[it] += running;
 #else
-            atomicAdd(p.n_active, 1);
+            atomicAdd(p.counts + it, running);
 #endif
         }
     }
 }
 
-// Reset of the per-decode state.  One thread per tile: valid mask from T, done = 0, iters = max_iter, conv = 0.
-__global__ void __launch_bounds__(256) k_bp_reset(uint32_t *valid, uint32_t *done, uint32_t *unsat, int *iters, int *conv,
-                                                  int tiles, int T, int max_iter)
+// Reset of the per-decode state.  One thread per tile: valid mask from T, done = 0, identity slot map,
+// iters = max_iter, conv = 0.
+__global__ void __launch_bounds__(256) k_bp_reset(uint32_t *valid, uint32_t *done, uint32_t *unsat, int *orig, int *iters,
+                                                  int *conv, int tiles, int T, int max_iter)
 {
     const int tile = blockIdx.x * blockDim.x + threadIdx.x;
     if (tile >= tiles) return;
@@ -240,9 +406,108 @@ __global__ void __launch_bounds__(256) k_bp_reset(uint32_t *valid, uint32_t *don
     done[tile] = 0;
     unsat[tile] = 0;
     for (int l = 0; l < 32; ++l) {
-        iters[tile * 32 + l] = max_iter;
-        conv[tile * 32 + l] = 0;
+        const int t = tile * 32 + l;
+        orig[t] = t < T ? t : -1;
+        if (t < T) {
+            iters[t] = max_iter;
+            conv[t] = 0;
+        }
     }
+}
+
+// -----------------------------------------------------------------------------------------------------------
+// Active-trial compaction.  When at most half of the slots still run, the running trials are packed into the
+// leading lanes of fewer tiles (order preserved) so that later iterations touch only live data:
+//   plan   (one CTA)   exclusive scan of the per-tile running counts -> src[new slot] = old slot (-1 = padding),
+//                      new slot map / valid masks, n_act
+//   move   per-trial columns of msg (E lines per tile), of the per-trial priors (n lines) and the syndrome
+//          bit-planes (m words) are gathered into a second buffer set (ping-pong; the new set needs <= half the slots)
+// Finished trials are written to the caller's output arrays before their slots are dropped (k_bp_unpack_* with the
+// `done` masks).  dec_w / post are rewritten for running trials by every bit pass, so they are not moved.
+// -----------------------------------------------------------------------------------------------------------
+constexpr int kBpPlanThreads = 1024;
+
+__global__ void __launch_bounds__(kBpPlanThreads) k_bp_compact_plan(const uint32_t *valid, const uint32_t *done,
+                                                                     const int *orig, int tiles, int *src, int *orig2,
+                                                                     uint32_t *valid2, uint32_t *done2, uint32_t *unsat2,
+                                                                     int *n_act_out)
+{
+    __shared__ int part[kBpPlanThreads + 1];
+    const int nt = blockDim.x, tid = threadIdx.x;
+    const int per = (tiles + nt - 1) / nt;
+    const int t0 = min(tiles, tid * per), t1 = min(tiles, t0 + per);
+    int cnt = 0;
+    for (int t = t0; t < t1; ++t) cnt += __popc(valid[t] & ~done[t]);
+    part[tid] = cnt;
+    __syncthreads();
+    if (tid == 0) {
+        int run = 0;
+        for (int i = 0; i < nt; ++i) {
+            const int c = part[i];
+            part[i] = run;
+            run += c;
+        }
+        part[nt] = run;
+        *n_act_out = run;
+    }
+    __syncthreads();
+    int pos = part[tid];
+    for (int t = t0; t < t1; ++t) {
+        uint32_t a = valid[t] & ~done[t];
+        for (int l = 0; l < 32; ++l)
+            if ((a >> l) & 1u) {
+                src[pos] = t * 32 + l;
+                orig2[pos] = orig[t * 32 + l];
+                ++pos;
+            }
+    }
+    const int n_act = part[nt], new_tiles = (n_act + 31) / 32;
+    for (int t = tid; t < new_tiles; t += nt) {
+        const int left = n_act - t * 32;
+        valid2[t] = left >= 32 ? 0xffffffffu : ((1u << left) - 1u);
+        done2[t] = 0;
+        unsat2[t] = 0;
+    }
+    for (int s = n_act + tid; s < new_tiles * 32; s += nt) {
+        src[s] = -1;
+        orig2[s] = -1;
+    }
+}
+
+// dst[(t', line, l')] = src_arr[(tile(s), line, lane(s))], s = src[t'*32 + l'].  One warp per 8 lines.
+__global__ void __launch_bounds__(256) k_bp_compact_move(const float *__restrict__ from, float *__restrict__ to,
+                                                         const int *__restrict__ src, int lines)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tile = blockIdx.y;
+    const int l0 = (blockIdx.x * (blockDim.x >> 5) + warp) * 8;
+    const int s = src[tile * 32 + lane];
+    const float *f = from + ((size_t)(s >> 5) * lines) * 32 + (s & 31);
+    float v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = (s >= 0 && l0 + i < lines) ? f[(size_t)(l0 + i) * 32] : 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+        if (l0 + i < lines) to[((size_t)tile * lines + l0 + i) * 32 + lane] = v[i];
+}
+
+// Bit-planes: to[t'][w] bit l' = from[tile(s)][w] bit lane(s).  One warp per word.
+__global__ void __launch_bounds__(256) k_bp_compact_bits(const uint32_t *__restrict__ from, uint32_t *__restrict__ to,
+                                                         const int *__restrict__ src, int words)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tile = blockIdx.y;
+    const int w = blockIdx.x * (blockDim.x >> 5) + warp;
+    if (w >= words) return;
+    const int s = src[tile * 32 + lane];
+    const uint32_t bit = s >= 0 ? (from[(size_t)(s >> 5) * words + w] >> (s & 31)) & 1u : 0u;
+#ifdef SCALDPC_HOST_MODEL
+    uint32_t &o = to[(size_t)tile * words + w];
+    o = (lane == 0 ? 0u : o) | (bit << lane);
+#else
+    const uint32_t word = __ballot_sync(0xffffffffu, bit != 0);
+    if (lane == 0) to[(size_t)tile * words + w] = word;
+#endif
 }
 
 #ifndef SCALDPC_HOST_MODEL
@@ -295,32 +560,33 @@ __global__ void __launch_bounds__(256) k_bp_pack_synd(const uint8_t *__restrict_
     }
 }
 
-// dec_w [tile][n] words -> decoding [T][n] bytes
-__global__ void __launch_bounds__(256) k_bp_unpack_dec(const uint32_t *__restrict__ dec_w, uint8_t *__restrict__ out, int T, int n)
+// dec_w [tile][n] words -> decoding [orig trial][n] bytes, for the slots selected by mask[tile]
+__global__ void __launch_bounds__(256) k_bp_unpack_dec(const uint32_t *__restrict__ dec_w, uint8_t *__restrict__ out,
+                                                       const int *__restrict__ orig, const uint32_t *__restrict__ mask, int n)
 {
     const int tile = blockIdx.y, v = blockIdx.x * 32 + (threadIdx.x & 31);
     const int ty = threadIdx.x >> 5;
-    if (v >= n) return;
+    const uint32_t sel = mask[tile];
+    if (v >= n || sel == 0) return;
     const uint32_t w = dec_w[(size_t)tile * n + v];
-    for (int t = ty; t < 32; t += 8) {
-        const int trial = tile * 32 + t;
-        if (trial < T) out[(size_t)trial * n + v] = (w >> t) & 1u;
-    }
+    for (int t = ty; t < 32; t += 8)
+        if ((sel >> t) & 1u) out[(size_t)orig[tile * 32 + t] * n + v] = (w >> t) & 1u;
 }
 
-// post [tile][n][32] -> llr [T][n]
-__global__ void __launch_bounds__(256) k_bp_untile_f32(const float *__restrict__ src, float *__restrict__ dst, int T, int n)
+// post [tile][n][32] -> llr [orig trial][n], for the slots selected by mask[tile]
+__global__ void __launch_bounds__(256) k_bp_untile_f32(const float *__restrict__ src, float *__restrict__ dst,
+                                                       const int *__restrict__ orig, const uint32_t *__restrict__ mask, int n)
 {
     __shared__ float sm[32][33];
     const int tile = blockIdx.y, c0 = blockIdx.x * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const uint32_t sel = mask[tile];
+    if (sel == 0) return;
     for (int c = ty; c < 32; c += 8)
         if (c0 + c < n) sm[c][tx] = src[((size_t)tile * n + c0 + c) * 32 + tx];
     __syncthreads();
-    for (int t = ty; t < 32; t += 8) {
-        const int trial = tile * 32 + t;
-        if (trial < T && c0 + tx < n) dst[(size_t)trial * n + c0 + tx] = sm[tx][t];
-    }
+    for (int t = ty; t < 32; t += 8)
+        if (((sel >> t) & 1u) && c0 + tx < n) dst[(size_t)orig[tile * 32 + t] * n + c0 + tx] = sm[tx][t];
 }
 #endif  // !SCALDPC_HOST_MODEL
 

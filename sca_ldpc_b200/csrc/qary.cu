@@ -52,10 +52,16 @@ struct scaldpc_qary {
     float *d_msg = nullptr, *d_llr = nullptr, *d_llr_sum = nullptr, *d_post = nullptr, *d_post_sum = nullptr;
     int8_t *d_hard_t = nullptr;
     int *d_status = nullptr;
-    // staging for host-pointer calls
-    size_t cap_stage_T = 0;
-    float *d_in = nullptr, *d_in_sum = nullptr, *d_opost = nullptr, *d_opost_sum = nullptr;
-    int8_t *d_ohard = nullptr;
+    // staging for host-pointer calls: the batch is cut into chunks and pipelined (H2D of chunk i+1 and D2H of chunk
+    // i-1 overlap the decode of chunk i), so every staging buffer exists twice
+    size_t cap_stage_T = 0;  // trials per staging buffer
+    size_t cap_status_T = 0;
+    float *d_in[2] = {nullptr, nullptr}, *d_in_sum[2] = {nullptr, nullptr};
+    float *d_opost[2] = {nullptr, nullptr}, *d_opost_sum[2] = {nullptr, nullptr};
+    int8_t *d_ohard[2] = {nullptr, nullptr};
+    int *d_status_all = nullptr;
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
     std::mutex mu;
     long long launches = 0;
 };
@@ -88,13 +94,15 @@ void free_workspace(scaldpc_qary *h)
 
 void free_stage(scaldpc_qary *h)
 {
-    cudaFree(h->d_in);
-    cudaFree(h->d_in_sum);
-    cudaFree(h->d_opost);
-    cudaFree(h->d_opost_sum);
-    cudaFree(h->d_ohard);
-    h->d_in = h->d_in_sum = h->d_opost = h->d_opost_sum = nullptr;
-    h->d_ohard = nullptr;
+    for (int i = 0; i < 2; ++i) {
+        cudaFree(h->d_in[i]);
+        cudaFree(h->d_in_sum[i]);
+        cudaFree(h->d_opost[i]);
+        cudaFree(h->d_opost_sum[i]);
+        cudaFree(h->d_ohard[i]);
+        h->d_in[i] = h->d_in_sum[i] = h->d_opost[i] = h->d_opost_sum[i] = nullptr;
+        h->d_ohard[i] = nullptr;
+    }
     h->cap_stage_T = 0;
 }
 
@@ -119,18 +127,35 @@ int ensure_workspace(scaldpc_qary *h, int tiles, bool want_post)
     return 0;
 }
 
-int ensure_stage(scaldpc_qary *h, size_t T, bool want_post)
+int ensure_stage(scaldpc_qary *h, size_t chunk, size_t T, bool want_post)
 {
-    if (T <= h->cap_stage_T && (!want_post || h->d_opost)) return 0;
-    const size_t t = std::max(T, h->cap_stage_T);
-    const bool post = want_post || h->d_opost;
+    if (!h->s_in) {
+        SCALDPC_CUDA(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
+        SCALDPC_CUDA(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) {
+            SCALDPC_CUDA(cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming));
+            SCALDPC_CUDA(cudaEventCreateWithFlags(&h->ev_comp[i], cudaEventDisableTiming));
+            SCALDPC_CUDA(cudaEventCreateWithFlags(&h->ev_out[i], cudaEventDisableTiming));
+        }
+    }
+    if (T > h->cap_status_T) {
+        cudaFree(h->d_status_all);
+        h->d_status_all = nullptr;
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_status_all, T * sizeof(int)));
+        h->cap_status_T = T;
+    }
+    if (chunk <= h->cap_stage_T && (!want_post || h->d_opost[0])) return 0;
+    const size_t t = std::max(chunk, h->cap_stage_T);
+    const bool post = want_post || h->d_opost[0];
     free_stage(h);
-    SCALDPC_CUDA(cudaMalloc((void **)&h->d_in, t * h->SL * sizeof(float)));
-    SCALDPC_CUDA(cudaMalloc((void **)&h->d_in_sum, std::max<size_t>(1, t * h->SLS) * sizeof(float)));
-    SCALDPC_CUDA(cudaMalloc((void **)&h->d_ohard, t * h->N));
-    if (post) {
-        SCALDPC_CUDA(cudaMalloc((void **)&h->d_opost, t * h->SL * sizeof(float)));
-        SCALDPC_CUDA(cudaMalloc((void **)&h->d_opost_sum, std::max<size_t>(1, t * h->SLS) * sizeof(float)));
+    for (int i = 0; i < 2; ++i) {
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_in[i], t * h->SL * sizeof(float)));
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_in_sum[i], std::max<size_t>(1, t * h->SLS) * sizeof(float)));
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_ohard[i], t * h->N));
+        if (post) {
+            SCALDPC_CUDA(cudaMalloc((void **)&h->d_opost[i], t * h->SL * sizeof(float)));
+            SCALDPC_CUDA(cudaMalloc((void **)&h->d_opost_sum[i], std::max<size_t>(1, t * h->SLS) * sizeof(float)));
+        }
     }
     h->cap_stage_T = t;
     return 0;
@@ -360,6 +385,14 @@ void scaldpc_qary_destroy(scaldpc_qary *h)
     cudaSetDevice(h->device);
     free_workspace(h);
     free_stage(h);
+    cudaFree(h->d_status_all);
+    if (h->s_in) cudaStreamDestroy(h->s_in);
+    if (h->s_out) cudaStreamDestroy(h->s_out);
+    for (int i = 0; i < 2; ++i) {
+        if (h->ev_in[i]) cudaEventDestroy(h->ev_in[i]);
+        if (h->ev_comp[i]) cudaEventDestroy(h->ev_comp[i]);
+        if (h->ev_out[i]) cudaEventDestroy(h->ev_out[i]);
+    }
     cudaFree(h->d_row_ptr);
     cudaFree(h->d_col);
     cudaFree(h->d_sign);
@@ -392,40 +425,15 @@ int scaldpc_qary_set_max_iter(scaldpc_qary *h, int max_iter)
 
 long long scaldpc_qary_launch_count(const scaldpc_qary *h) { return h ? h->launches : 0; }
 
-int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in_sum, int8_t *hard, float *post,
-                        float *post_sum, int32_t *status, unsigned flags, void *stream)
+// The device pipeline of one batch: priors (device, row-major) -> hard decisions (device, row-major), all on `st`.
+static int decode_on_device(scaldpc_qary *h, int T, const float *din, const float *din_sum, int8_t *dhard, float *dpost,
+                            float *dpost_sum, unsigned flags, cudaStream_t st)
 {
-    if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
-    if (T < 0) return fail(SCALDPC_ERR_ARG, "T < 0");
-    if (T == 0) return 0;
     const bool special = h->BSUM > 0;
-    if (!in || !hard || (special && !in_sum)) return fail(SCALDPC_ERR_ARG, "NULL input/output pointer");
-    const bool want_post = post != nullptr || post_sum != nullptr;
-    const bool dev_ptrs = flags & SCALDPC_DEVICE_PTRS;
+    const bool want_post = dpost != nullptr || dpost_sum != nullptr;
     const bool is_llr = flags & SCALDPC_IN_LLR;
-    cudaStream_t st = (cudaStream_t)stream;
-
-    std::lock_guard<std::mutex> lk(h->mu);
-    SCALDPC_CUDA(cudaSetDevice(h->device));
     const int tiles = (T + 31) / 32;
     int rc;
-    if ((rc = ensure_workspace(h, tiles, want_post))) return rc;
-
-    const float *din = in, *din_sum = in_sum;
-    int8_t *dhard = hard;
-    float *dpost = post, *dpost_sum = post_sum;
-    if (!dev_ptrs) {
-        if ((rc = ensure_stage(h, (size_t)T, want_post))) return rc;
-        SCALDPC_CUDA(cudaMemcpyAsync(h->d_in, in, (size_t)T * h->SL * sizeof(float), cudaMemcpyHostToDevice, st));
-        if (special)
-            SCALDPC_CUDA(cudaMemcpyAsync(h->d_in_sum, in_sum, (size_t)T * h->SLS * sizeof(float), cudaMemcpyHostToDevice, st));
-        din = h->d_in;
-        din_sum = h->d_in_sum;
-        dhard = h->d_ohard;
-        dpost = post ? h->d_opost : nullptr;
-        dpost_sum = post_sum ? h->d_opost_sum : nullptr;
-    }
-
     SCALDPC_CUDA(cudaMemsetAsync(h->d_status, 0, (size_t)tiles * 32 * sizeof(int), st));
     if ((rc = load_priors(h, din, h->d_llr, T, tiles, h->bvars, h->Q, is_llr, st))) return rc;
     if (special && (rc = load_priors(h, din_sum, h->d_llr_sum, T, tiles, h->R, h->QS, is_llr, st))) return rc;
@@ -436,42 +444,88 @@ int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in
         if ((rc = launch_cn(h, p, tiles, it == 1, it == iters, flags, st))) return rc;
         if ((rc = launch_vn(h, p, tiles, it == iters, st))) return rc;
     }
-
-    {
-        dim3 block(32, kTrRows);
-        k_untile<int8_t><<<dim3((h->N + 31) / 32, tiles), block, 0, st>>>(h->d_hard_t, dhard, T, h->N);
+    dim3 block(32, kTrRows);
+    k_untile<int8_t><<<dim3((h->N + 31) / 32, tiles), block, 0, st>>>(h->d_hard_t, dhard, T, h->N);
+    ++h->launches;
+    if (dpost) {
+        k_untile<float><<<dim3((h->SL + 31) / 32, tiles), block, 0, st>>>(h->d_post, dpost, T, h->SL);
         ++h->launches;
-        if (dpost) {
-            k_untile<float><<<dim3((h->SL + 31) / 32, tiles), block, 0, st>>>(h->d_post, dpost, T, h->SL);
-            ++h->launches;
-        }
-        if (dpost_sum && special) {
-            k_untile<float><<<dim3((h->SLS + 31) / 32, tiles), block, 0, st>>>(h->d_post_sum, dpost_sum, T, h->SLS);
-            ++h->launches;
-        }
-        SCALDPC_CUDA(cudaGetLastError());
+    }
+    if (dpost_sum && special) {
+        k_untile<float><<<dim3((h->SLS + 31) / 32, tiles), block, 0, st>>>(h->d_post_sum, dpost_sum, T, h->SLS);
+        ++h->launches;
+    }
+    SCALDPC_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in_sum, int8_t *hard, float *post,
+                        float *post_sum, int32_t *status, unsigned flags, void *stream)
+{
+    if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
+    if (T < 0) return fail(SCALDPC_ERR_ARG, "T < 0");
+    if (T == 0) return 0;
+    const bool special = h->BSUM > 0;
+    if (!in || !hard || (special && !in_sum)) return fail(SCALDPC_ERR_ARG, "NULL input/output pointer");
+    const bool want_post = post != nullptr || post_sum != nullptr;
+    const bool dev_ptrs = flags & SCALDPC_DEVICE_PTRS;
+    cudaStream_t st = (cudaStream_t)stream;
+
+    std::lock_guard<std::mutex> lk(h->mu);
+    SCALDPC_CUDA(cudaSetDevice(h->device));
+    int rc;
+
+    if (dev_ptrs) {  // asynchronous on `st`, one pass over the whole batch
+        const int tiles = (T + 31) / 32;
+        if ((rc = ensure_workspace(h, tiles, want_post))) return rc;
+        if ((rc = decode_on_device(h, T, in, in_sum, hard, post, post_sum, flags, st))) return rc;
+        if (status) SCALDPC_CUDA(cudaMemcpyAsync(status, h->d_status, (size_t)T * sizeof(int), cudaMemcpyDeviceToDevice, st));
+        return 0;
     }
 
-    if (!dev_ptrs) {
-        SCALDPC_CUDA(cudaMemcpyAsync(hard, h->d_ohard, (size_t)T * h->N, cudaMemcpyDeviceToHost, st));
-        if (post) SCALDPC_CUDA(cudaMemcpyAsync(post, h->d_opost, (size_t)T * h->SL * sizeof(float), cudaMemcpyDeviceToHost, st));
+    // ---- host buffers: chunked pipeline.  Chunk c is copied in on s_in, decoded on `st`, copied out on s_out; the
+    // two staging buffers alternate, so the H2D of chunk c+1 and the D2H of chunk c-1 overlap the decode of chunk c
+    // (truly asynchronous only for pinned host memory; pageable memory degrades to the serial order, still correct).
+    int chunk = T;
+    if (T >= 4096) chunk = std::max(1024, (T + 7) / 8);
+    chunk = (chunk + 31) / 32 * 32;
+    const int nchunks = (T + chunk - 1) / chunk;
+    if ((rc = ensure_workspace(h, chunk / 32, want_post))) return rc;
+    if ((rc = ensure_stage(h, (size_t)chunk, (size_t)T, want_post))) return rc;
+    for (int c = 0; c < nchunks; ++c) {
+        const int b = c & 1, t0 = c * chunk, tc = std::min(chunk, T - t0);
+        // d_in[b] is free once the decode of chunk c-2 has consumed it
+        if (c >= 2) SCALDPC_CUDA(cudaStreamWaitEvent(h->s_in, h->ev_comp[b], 0));
+        SCALDPC_CUDA(cudaMemcpyAsync(h->d_in[b], in + (size_t)t0 * h->SL, (size_t)tc * h->SL * sizeof(float),
+                                     cudaMemcpyHostToDevice, h->s_in));
+        if (special)
+            SCALDPC_CUDA(cudaMemcpyAsync(h->d_in_sum[b], in_sum + (size_t)t0 * h->SLS, (size_t)tc * h->SLS * sizeof(float),
+                                         cudaMemcpyHostToDevice, h->s_in));
+        SCALDPC_CUDA(cudaEventRecord(h->ev_in[b], h->s_in));
+        SCALDPC_CUDA(cudaStreamWaitEvent(st, h->ev_in[b], 0));
+        if (c >= 2) SCALDPC_CUDA(cudaStreamWaitEvent(st, h->ev_out[b], 0));  // d_ohard[b] has been copied out
+        if ((rc = decode_on_device(h, tc, h->d_in[b], h->d_in_sum[b], h->d_ohard[b], post ? h->d_opost[b] : nullptr,
+                                   post_sum ? h->d_opost_sum[b] : nullptr, flags, st)))
+            return rc;
+        SCALDPC_CUDA(cudaMemcpyAsync(h->d_status_all + t0, h->d_status, (size_t)tc * sizeof(int), cudaMemcpyDeviceToDevice, st));
+        SCALDPC_CUDA(cudaEventRecord(h->ev_comp[b], st));
+        SCALDPC_CUDA(cudaStreamWaitEvent(h->s_out, h->ev_comp[b], 0));
+        SCALDPC_CUDA(cudaMemcpyAsync(hard + (size_t)t0 * h->N, h->d_ohard[b], (size_t)tc * h->N, cudaMemcpyDeviceToHost, h->s_out));
+        if (post)
+            SCALDPC_CUDA(cudaMemcpyAsync(post + (size_t)t0 * h->SL, h->d_opost[b], (size_t)tc * h->SL * sizeof(float),
+                                         cudaMemcpyDeviceToHost, h->s_out));
         if (post_sum && special)
-            SCALDPC_CUDA(cudaMemcpyAsync(post_sum, h->d_opost_sum, (size_t)T * h->SLS * sizeof(float), cudaMemcpyDeviceToHost, st));
+            SCALDPC_CUDA(cudaMemcpyAsync(post_sum + (size_t)t0 * h->SLS, h->d_opost_sum[b],
+                                         (size_t)tc * h->SLS * sizeof(float), cudaMemcpyDeviceToHost, h->s_out));
+        SCALDPC_CUDA(cudaEventRecord(h->ev_out[b], h->s_out));
     }
+    std::vector<int> hs(T);
+    SCALDPC_CUDA(cudaMemcpyAsync(hs.data(), h->d_status_all, (size_t)T * sizeof(int), cudaMemcpyDeviceToHost, st));
+    SCALDPC_CUDA(cudaStreamSynchronize(st));
+    SCALDPC_CUDA(cudaStreamSynchronize(h->s_out));
     int worst = 0;
-    if (status || !dev_ptrs) {
-        // per-trial status: copy back (host pointer) or device-to-device
-        if (dev_ptrs) {
-            SCALDPC_CUDA(cudaMemcpyAsync(status, h->d_status, (size_t)T * sizeof(int), cudaMemcpyDeviceToDevice, st));
-        } else {
-            std::vector<int> hs(T);
-            SCALDPC_CUDA(cudaMemcpyAsync(hs.data(), h->d_status, (size_t)T * sizeof(int), cudaMemcpyDeviceToHost, st));
-            SCALDPC_CUDA(cudaStreamSynchronize(st));
-            for (int t = 0; t < T; ++t) worst = std::min(worst, hs[t]);
-            if (status) memcpy(status, hs.data(), (size_t)T * sizeof(int));
-        }
-    }
-    if (!dev_ptrs) SCALDPC_CUDA(cudaStreamSynchronize(st));
+    for (int t = 0; t < T; ++t) worst = std::min(worst, hs[t]);
+    if (status) memcpy(status, hs.data(), (size_t)T * sizeof(int));
     if (worst == SCALDPC_ERR_PROB_SUM) return fail(worst, "a prior row does not sum to 1 +- 0.001 (decoder.rs:683-684)");
     if (worst == SCALDPC_ERR_NO_MAX) return fail(worst, "No maximum probability found (decoder.rs:680)");
     if (worst == SCALDPC_ERR_NO_CONFIG) return fail(worst, "a check has no valid configuration (decoder.rs:618)");

@@ -112,11 +112,13 @@ class bp_decoder:
         return dec.astype(int)
 
     # ---- batched fast path -------------------------------------------------------------------------------
-    def decode_batch(self, syndromes, channel_probs=None, *, want_llr=False, early_stop=True):
+    def decode_batch(self, syndromes, channel_probs=None, *, want_llr=False, early_stop=True, compact=True):
         """syndromes (T, m) uint8; channel_probs None (the constructor's), (n,) or (T, n) float64.
         numpy in -> numpy out; torch CUDA uint8 tensor in -> torch CUDA tensors out.
         Returns dict(decoding (T,n) uint8, log_prob_ratios (T,n) float32 or None, iters (T,), converged (T,))."""
         flags = 0 if early_stop else _lib.BP_NO_EARLY_STOP
+        if not compact:
+            flags |= _lib.BP_NO_COMPACT
         if torch is not None and isinstance(syndromes, torch.Tensor) and syndromes.is_cuda:
             return self._batch_torch(syndromes, channel_probs, flags, want_llr)
         synd = np.ascontiguousarray(syndromes, dtype=np.uint8)
@@ -168,6 +170,12 @@ class bp_decoder:
     @property
     def launch_count(self) -> int:
         return int(_lib.lib().scaldpc_bp_launch_count(self._h))
+
+    def last_run(self):
+        """(iterations launched, active-trial compactions) of the last decode on this decoder."""
+        a, b = C.c_int(), C.c_int()
+        _lib.check(_lib.lib().scaldpc_bp_last_run(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def time_kernel(self, which: int, T: int, reps: int = 20, stream=None) -> float:
         ms = C.c_float()

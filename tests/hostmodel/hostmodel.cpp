@@ -42,6 +42,7 @@ static inline int atomicMin(int *p, int v)
     return o;
 }
 static inline float __fdiv_rn(float a, float b) { return a / b; }
+static inline int __popc(unsigned x) { return __builtin_popcount(x); }
 static inline void __syncthreads() {}
 using std::max;
 using std::min;
@@ -186,11 +187,13 @@ int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
 }
 
 
-// Binary product-sum BP through the modelled kernels.  synd (T x m bytes), probs (n or T x n doubles);
-// outputs decoding (T x n bytes), llr (T x n floats, may be NULL), iters / conv (T ints).
+// Binary product-sum BP through the modelled kernels, with the host loop of scaldpc_bp_decode (bp.cu): per-trial
+// freeze, polling of the running-trial count and active-trial compaction into a second buffer set (`compact` != 0).
+// synd (T x m bytes), probs (n or T x n doubles); outputs decoding (T x n bytes), llr (T x n floats, may be NULL),
+// iters / conv (T ints), *n_compactions.
 int hostmodel_bp_decode(int m, int n, const int32_t *row_ptr, const int32_t *col, int max_iter, int T,
-                        const uint8_t *synd, const double *probs, int probs_per_trial, int early_stop,
-                        uint8_t *decoding, float *llr, int32_t *iters, int32_t *conv)
+                        const uint8_t *synd, const double *probs, int probs_per_trial, int early_stop, int compact,
+                        uint8_t *decoding, float *llr, int32_t *iters, int32_t *conv, int32_t *n_compactions)
 {
     BpHostGraph g;
     std::string err;
@@ -199,53 +202,125 @@ int hostmodel_bp_decode(int m, int n, const int32_t *row_ptr, const int32_t *col
     if (max_iter == 0) max_iter = n;
     const int tiles = (T + 31) / 32;
     const size_t lanes = (size_t)tiles * 32;
-    std::vector<float> msg(std::max<size_t>(1, lanes * g.E)), prior(probs_per_trial ? lanes * n : n), post(lanes * n);
-    std::vector<uint32_t> synd_w((size_t)tiles * m, 0), dec_w((size_t)tiles * n, 0), done(tiles, 0), valid(tiles, 0),
-        unsat(tiles, 0);
-    std::vector<int> vit(lanes, max_iter), vconv(lanes, 0);
-    int n_active = 0;
+    struct Set {
+        std::vector<float> msg, prior_t;
+        std::vector<uint32_t> synd_w, valid, done, unsat;
+        std::vector<int> orig;
+    } set[2];
+    for (int s = 0; s < 2; ++s) {
+        const size_t t = s == 0 ? tiles : (tiles + 1) / 2;
+        set[s].msg.assign(std::max<size_t>(1, t * 32 * g.E), 0.0f);
+        set[s].prior_t.assign(probs_per_trial ? t * 32 * n : 1, 0.0f);
+        set[s].synd_w.assign(t * m, 0);
+        set[s].valid.assign(t, 0);
+        set[s].done.assign(t, 0);
+        set[s].unsat.assign(t, 0);
+        set[s].orig.assign(t * 32, -1);
+    }
+    std::vector<float> prior(n), post(lanes * n);
+    std::vector<uint32_t> dec_w((size_t)tiles * n, 0);
+    std::vector<int> vit(lanes, max_iter), vconv(lanes, 0), counts(max_iter + 2, 0), src(lanes, -1);
     for (int t = 0; t < T; ++t) {
-        valid[t / 32] |= 1u << (t % 32);
+        set[0].valid[t / 32] |= 1u << (t % 32);
+        set[0].orig[t] = t;
         for (int c = 0; c < m; ++c)
-            if (synd[(size_t)t * m + c] & 1) synd_w[(size_t)(t / 32) * m + c] |= 1u << (t % 32);
+            if (synd[(size_t)t * m + c] & 1) set[0].synd_w[(size_t)(t / 32) * m + c] |= 1u << (t % 32);
     }
     if (probs_per_trial) {
         for (size_t t = 0; t < lanes; ++t)
             for (int v = 0; v < n; ++v) {
                 const double q = t < (size_t)T ? probs[t * n + v] : 0.5;
-                prior[((t / 32) * n + v) * 32 + t % 32] = (float)log((1.0 - q) / q);
+                set[0].prior_t[((t / 32) * n + v) * 32 + t % 32] = (float)log((1.0 - q) / q);
             }
     } else {
         for (int v = 0; v < n; ++v) prior[v] = (float)log((1.0 - probs[v]) / probs[v]);
     }
-    BpDev p;
-    p.m = m; p.n = n; p.E = g.E; p.dc_max = std::max(1, g.dc_max); p.dv_max = std::max(1, g.dv_max);
-    p.per_trial_prior = probs_per_trial;
-    p.row_ptr = g.row_ptr.data(); p.col = g.col.data(); p.col_ptr = g.col_ptr.data(); p.csc_edge = g.csc_edge.data();
-    p.msg = msg.data(); p.prior = prior.data(); p.synd_w = synd_w.data(); p.dec_w = dec_w.data();
-    p.post = llr ? post.data() : nullptr;
-    p.done = done.data(); p.valid = valid.data(); p.unsat = unsat.data(); p.iters = vit.data(); p.conv = vconv.data();
-    p.n_active = &n_active;
-    std::vector<float> scratch((size_t)kBpWarps * 2 * std::max(p.dc_max, p.dv_max) * 32);
+    auto view = [&](int cur) {
+        BpDev p;
+        p.m = m; p.n = n; p.E = g.E; p.dc_max = std::max(1, g.dc_max); p.dv_max = std::max(1, g.dv_max);
+        p.per_trial_prior = probs_per_trial;
+        p.row_ptr = g.row_ptr.data(); p.col = g.col.data(); p.col_ptr = g.col_ptr.data(); p.csc_edge = g.csc_edge.data();
+        p.vn_order = g.vn_order.data();
+        p.msg = set[cur].msg.data();
+        p.prior = probs_per_trial ? set[cur].prior_t.data() : prior.data();
+        p.synd_w = set[cur].synd_w.data(); p.dec_w = dec_w.data();
+        p.post = llr ? post.data() : nullptr;
+        p.done = set[cur].done.data(); p.valid = set[cur].valid.data(); p.unsat = set[cur].unsat.data();
+        p.orig = set[cur].orig.data(); p.iters = vit.data(); p.conv = vconv.data(); p.counts = counts.data();
+        return p;
+    };
+    auto write_outputs = [&](int cur, int cur_tiles, const std::vector<uint32_t> &mask) {
+        for (int tile = 0; tile < cur_tiles; ++tile)
+            for (int l = 0; l < 32; ++l) {
+                if (!((mask[tile] >> l) & 1u)) continue;
+                const int o = set[cur].orig[tile * 32 + l];
+                for (int v = 0; v < n; ++v) {
+                    decoding[(size_t)o * n + v] = (dec_w[(size_t)tile * n + v] >> l) & 1u;
+                    if (llr) llr[(size_t)o * n + v] = post[((size_t)tile * n + v) * 32 + l];
+                }
+            }
+    };
+    const int dmax = std::max(std::max(1, g.dc_max), std::max(1, g.dv_max));
+    const int cn_wpc = 2;  // warps per CTA of the modelled check pass (any value works: items are strided)
+    std::vector<float> scratch((size_t)std::max(cn_wpc * 3, kBpVnWarps * 2) * dmax * 32);
     scaldpc_host_model_smem = scratch.data();
-    const int tb = (tiles + 255) / 256;
+    int cur = 0, cur_tiles = tiles, compactions = 0;
     for (int it = 1; it <= max_iter; ++it) {
-        run_grid((m + kBpWarps - 1) / kBpWarps, tiles, kBpWarps * 32, k_bp_cn, p, (int)(it == 1));
-        run_grid((n + kBpWarps - 1) / kBpWarps, tiles, kBpWarps * 32, k_bp_vn, p);
-        run_grid((m + 255) / 256, tiles, 256, k_bp_syndrome, p);
-        n_active = 0;
-        run_grid(tb, 1, 256, k_bp_finish_iter, p, tiles, it, early_stop, (int)(it == max_iter));
-        if (early_stop && n_active == 0) break;
+        const BpDev p = view(cur);
+        if (it == 1) run_grid(3, 1, cn_wpc * 32, k_bp_cn<true>, p, cur_tiles);
+        else run_grid(3, 1, cn_wpc * 32, k_bp_cn<false>, p, cur_tiles);
+        int lo = 0;
+        for (int c = 0; c <= kBpVnClasses; ++c) {
+            const int hi = g.class_end[c];
+            if (hi > lo) {
+                const unsigned gx = (hi - lo + kBpVnWarps - 1) / kBpVnWarps;
+                switch (c) {
+                case 0: run_grid(gx, cur_tiles, kBpVnWarps * 32, k_bp_vn<1>, p, lo, hi); break;
+                case 1: run_grid(gx, cur_tiles, kBpVnWarps * 32, k_bp_vn<4>, p, lo, hi); break;
+                case 2: run_grid(gx, cur_tiles, kBpVnWarps * 32, k_bp_vn<8>, p, lo, hi); break;
+                case 3: run_grid(gx, cur_tiles, kBpVnWarps * 32, k_bp_vn<12>, p, lo, hi); break;
+                case 4: run_grid(gx, cur_tiles, kBpVnWarps * 32, k_bp_vn<16>, p, lo, hi); break;
+                case 5: run_grid(gx, cur_tiles, kBpVnWarps * 32, k_bp_vn<24>, p, lo, hi); break;
+                case 6: run_grid(gx, cur_tiles, kBpVnWarps * 32, k_bp_vn<32>, p, lo, hi); break;
+                default: run_grid(gx, cur_tiles, kBpVnWarps * 32, k_bp_vn_generic, p, lo, hi);
+                }
+            }
+            lo = hi;
+        }
+        run_grid((m + 255) / 256, cur_tiles, 256, k_bp_syndrome, p);
+        run_grid((cur_tiles + 255) / 256, 1, 256, k_bp_finish_iter, p, cur_tiles, it, early_stop, (int)(it == max_iter));
+        if (early_stop && it < max_iter) {
+            const int n_run = counts[it];
+            if (n_run == 0) break;
+            if (compact && cur_tiles >= 2 && (long long)n_run * 2 <= (long long)cur_tiles * 32) {
+                write_outputs(cur, cur_tiles, set[cur].done);
+                Set &a = set[cur], &b = set[cur ^ 1];
+                int n_act = 0;
+                const int new_tiles = (n_run + 31) / 32;
+                run_grid(1, 1, 1, k_bp_compact_plan, (const uint32_t *)a.valid.data(), (const uint32_t *)a.done.data(),
+                         (const int *)a.orig.data(), cur_tiles, src.data(), b.orig.data(), b.valid.data(), b.done.data(),
+                         b.unsat.data(), &n_act);
+                if (n_act != n_run) return -100;
+                run_grid((g.E + 63) / 64, new_tiles, 256, k_bp_compact_move, (const float *)a.msg.data(), b.msg.data(),
+                         (const int *)src.data(), g.E);
+                if (probs_per_trial)
+                    run_grid((n + 63) / 64, new_tiles, 256, k_bp_compact_move, (const float *)a.prior_t.data(),
+                             b.prior_t.data(), (const int *)src.data(), n);
+                run_grid((m + 7) / 8, new_tiles, 256, k_bp_compact_bits, (const uint32_t *)a.synd_w.data(),
+                         b.synd_w.data(), (const int *)src.data(), m);
+                cur ^= 1;
+                cur_tiles = new_tiles;
+                ++compactions;
+            }
+        }
     }
     scaldpc_host_model_smem = nullptr;
+    write_outputs(cur, cur_tiles, set[cur].valid);
     for (int t = 0; t < T; ++t) {
-        for (int v = 0; v < n; ++v) {
-            decoding[(size_t)t * n + v] = (dec_w[(size_t)(t / 32) * n + v] >> (t % 32)) & 1u;
-            if (llr) llr[(size_t)t * n + v] = post[((size_t)(t / 32) * n + v) * 32 + t % 32];
-        }
         iters[t] = vit[t];
         conv[t] = vconv[t];
     }
+    if (n_compactions) *n_compactions = compactions;
     return 0;
 }
 

@@ -107,3 +107,51 @@ def test_hqc128_full_size():
         np.bitwise_xor.at(s, rows, dec[t][w.col])
         assert np.array_equal(s, batch.syndromes[t])
     assert w.success(batch, dec)[conv].mean() > 0.9
+
+
+def test_active_trial_compaction_is_transparent():
+    """100 trials, five of them never converge, per-trial priors: the running trials are compacted into fewer tiles;
+    outputs must be bit-identical to the run without compaction and agree with the fp64 oracle."""
+    w = HqcWorkload(variant=(499, 6), W=9, R=230, rho=0.97, seed=3)
+    batch = w.generate(100, seed=21)
+    synd = batch.syndromes.copy()
+    rs = np.random.RandomState(4)
+    for t in (3, 40, 41, 77, 99):
+        synd[t] = rs.randint(0, 2, w.R)
+    probs = np.tile(w.channel_probs, (100, 1)) * rs.uniform(0.8, 1.25, size=(100, w.n))
+    bpd = bp_decoder(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=25, channel_probs=w.channel_probs)
+    a = bpd.decode_batch(synd, channel_probs=probs, want_llr=True)
+    assert bpd.last_run()[1] >= 2
+    b = bpd.decode_batch(synd, channel_probs=probs, want_llr=True, compact=False)
+    assert bpd.last_run()[1] == 0
+    for k in ("decoding", "iters", "converged"):
+        assert np.array_equal(a[k], b[k]), k
+    assert np.array_equal(a["log_prob_ratios"], b["log_prob_ratios"], equal_nan=True)
+    orc = O.BinaryBpOracle(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=25, channel_probs=w.channel_probs)
+    ref = orc.decode_batch(synd, channel_probs=probs)
+    assert np.array_equal(a["iters"], ref["iters"]) and np.array_equal(a["decoding"], ref["decoding"])
+    for t in range(100):
+        assert util.llr_close(a["log_prob_ratios"][t], ref["log_prob_ratios"][t]), t
+
+
+def test_large_batch_compaction_hqc128():
+    """1024 trials of the HQC-128 workload plus a few garbage syndromes that never converge: the batch is compacted
+    several times; results of a sample of trials (converging and not) must match a run of just those trials without
+    compaction."""
+    w = HqcWorkload("hqc128", W=50, R=3000, rho=0.9942, seed=0)
+    batch = w.generate(1024, seed=5)
+    synd = batch.syndromes.copy()
+    bad = [5, 100, 513, 1023]
+    rs = np.random.RandomState(8)
+    for t in bad:
+        synd[t] = rs.randint(0, 2, w.R)
+    bpd = bp_decoder(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=40, channel_probs=w.channel_probs)
+    out = bpd.decode_batch(synd)
+    assert bpd.last_run() == (40, bpd.last_run()[1]) and bpd.last_run()[1] >= 2
+    conv = out["converged"].astype(bool)
+    assert conv.mean() > 0.9 and not conv[bad].any()
+    pick = np.concatenate([np.array(bad), np.nonzero(conv)[0][:28]])
+    sub = bpd.decode_batch(synd[pick], compact=False)
+    assert np.array_equal(sub["iters"], out["iters"][pick])
+    assert np.array_equal(sub["decoding"], out["decoding"][pick])
+    assert (out["iters"][~conv] == 40).all()

@@ -49,7 +49,7 @@ def hostmodel():
         src = os.path.join(ROOT, "tests", "hostmodel", "hostmodel.cpp")
         out = os.path.join(ROOT, "tests", "hostmodel", "libhostmodel.so")
         deps = [src] + [os.path.join(ROOT, "sca_ldpc_b200", "csrc", f)
-                        for f in ("qary_kernels.cuh", "qary_graph.h", "bp_kernels.cuh", "bp_graph.h")]
+                        for f in ("qary_kernels.cuh", "qary_cn_fast.cuh", "qary_graph.h", "bp_kernels.cuh", "bp_graph.h", "tma.cuh")]
         deps = [d for d in deps if os.path.exists(d)]
         if not os.path.exists(out) or any(os.path.getmtime(d) > os.path.getmtime(out) for d in deps):
             subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-fno-fast-math",
@@ -82,7 +82,7 @@ def hostmodel_qary(H, b, bsum, max_iter, llr, llr_sum=None, flags=0, dv=0, dc=0)
     return rc, hard, post, posts, status, bool(used.value)
 
 
-def hostmodel_bp(row_ptr, col, m, n, max_iter, synd, probs, early_stop=True, want_llr=True):
+def hostmodel_bp(row_ptr, col, m, n, max_iter, synd, probs, early_stop=True, want_llr=True, compact=True):
     """Run the binary-BP kernels' logic on the host.  Returns dict(decoding, llr, iters, converged)."""
     L = hostmodel()
     L.hostmodel_bp_decode.restype = C.c_int
@@ -97,10 +97,11 @@ def hostmodel_bp(row_ptr, col, m, n, max_iter, synd, probs, early_stop=True, wan
     iters = np.zeros(T, np.int32)
     conv = np.zeros(T, np.int32)
     p = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    ncomp = C.c_int(0)
     rc = L.hostmodel_bp_decode(m, n, p(row_ptr), p(col), max_iter, T, p(synd), p(probs), per_trial, int(early_stop),
-                               p(dec), p(llr), p(iters), p(conv))
+                               int(compact), p(dec), p(llr), p(iters), p(conv), C.byref(ncomp))
     assert rc == 0, rc
-    return dict(decoding=dec, llr=llr, iters=iters, converged=conv)
+    return dict(decoding=dec, llr=llr, iters=iters, converged=conv, compactions=ncomp.value)
 
 
 def llr_close(a, b, atol=2e-3, rtol=2e-4):
