@@ -26,7 +26,8 @@ struct scaldpc_bp {
     int m = 0, n = 0, E = 0, dc_max = 0, dv_max = 0;
     int max_iter = 0, device = 0, num_sms = 148;
     int class_end[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    int *d_row_ptr = nullptr, *d_col = nullptr, *d_col_ptr = nullptr, *d_csc_edge = nullptr, *d_vn_order = nullptr;
+    int *d_row_ptr = nullptr, *d_col = nullptr, *d_col_ptr = nullptr, *d_vn_order = nullptr;
+    uint32_t *d_csc_edge = nullptr;
     // workspace
     int cap_tiles = 0;
     bool cap_post = false, cap_prior_t = false;
@@ -43,7 +44,10 @@ struct scaldpc_bp {
     double *d_probs = nullptr;
     float *d_llr = nullptr;
     int cn_warps = 8, cn_occ[2] = {1, 1};
-    size_t smem_cn = 0, smem_vn = 0;
+    size_t smem_cn = 0;
+    int vn_occ[8] = {0};  // bit pass: resident CTAs per SM of each degree-class kernel
+    int vn_gen_wpc = 1;   // warps per CTA of the shared-memory kernel for heavier columns
+    size_t smem_vn = 0;
     std::mutex mu;
     long long launches = 0;
     int last_iters_run = 0, last_compactions = 0;
@@ -166,7 +170,7 @@ BpDev view(const scaldpc_bp *h, int cur, bool per_trial_prior, bool want_post)
     p.row_ptr = h->d_row_ptr;
     p.col = h->d_col;
     p.col_ptr = h->d_col_ptr;
-    p.csc_edge = h->d_csc_edge;
+    p.csc_off = h->d_csc_edge;
     p.vn_order = h->d_vn_order;
     p.msg = s.msg;
     p.prior = per_trial_prior ? s.prior_t : h->d_prior;
@@ -197,29 +201,35 @@ int launch_cn(scaldpc_bp *h, const BpDev &p, int tiles, bool first, cudaStream_t
     return 0;
 }
 
-template <int DMAX>
-void launch_vn_class(const BpDev &p, int lo, int hi, int tiles, cudaStream_t st)
+typedef void (*bp_vn_fn)(const BpDev, const int, const int, const int);
+bp_vn_fn vn_class_fn(int c)
 {
-    k_bp_vn<DMAX><<<dim3((hi - lo + kBpVnWarps - 1) / kBpVnWarps, tiles), kBpVnWarps * 32, 0, st>>>(p, lo, hi);
+    switch (c) {
+    case 0: return k_bp_vn<0, 1>;
+    case 1: return k_bp_vn<1, 4>;
+    case 2: return k_bp_vn<4, 8>;
+    case 3: return k_bp_vn<8, 12>;
+    case 4: return k_bp_vn<12, 16>;
+    case 5: return k_bp_vn<16, 24>;
+    case 6: return k_bp_vn<24, 32>;
+    default: return nullptr;
+    }
 }
 
-// Bit pass: one launch per non-empty degree class (variables are sorted by degree).
+// Bit pass: one persistent launch per non-empty degree class (variables are sorted by degree); columns heavier than
+// the largest register class go through the shared-memory kernel.
 int launch_vn(scaldpc_bp *h, const BpDev &p, int tiles, cudaStream_t st)
 {
     int lo = 0;
     for (int c = 0; c <= kBpVnClasses; ++c) {
         const int hi = h->class_end[c];
         if (hi > lo) {
-            switch (c) {
-            case 0: launch_vn_class<1>(p, lo, hi, tiles, st); break;
-            case 1: launch_vn_class<4>(p, lo, hi, tiles, st); break;
-            case 2: launch_vn_class<8>(p, lo, hi, tiles, st); break;
-            case 3: launch_vn_class<12>(p, lo, hi, tiles, st); break;
-            case 4: launch_vn_class<16>(p, lo, hi, tiles, st); break;
-            case 5: launch_vn_class<24>(p, lo, hi, tiles, st); break;
-            case 6: launch_vn_class<32>(p, lo, hi, tiles, st); break;
-            default:
-                k_bp_vn_generic<<<dim3((hi - lo + kBpVnWarps - 1) / kBpVnWarps, tiles), kBpVnWarps * 32, h->smem_vn, st>>>(
+            if (c < kBpVnClasses) {
+                const long long items = (long long)tiles * (hi - lo);
+                const int ctas = (int)std::min<long long>((long long)h->num_sms * h->vn_occ[c], (items + kBpVnWarps - 1) / kBpVnWarps);
+                vn_class_fn(c)<<<std::max(1, ctas), kBpVnWarps * 32, 0, st>>>(p, lo, hi, tiles);
+            } else {
+                k_bp_vn_generic<<<dim3((hi - lo + h->vn_gen_wpc - 1) / h->vn_gen_wpc, tiles), h->vn_gen_wpc * 32, h->smem_vn, st>>>(
                     p, lo, hi);
             }
             ++h->launches;
@@ -299,14 +309,18 @@ int scaldpc_bp_create(int m, int n, const int32_t *row_ptr, const int32_t *col, 
     if (h->cn_warps < 1)
         return fail(SCALDPC_ERR_UNSUPPORTED, "row degree %d too large for the shared-memory staging", h->dc_max);
     h->smem_cn = per_warp * h->cn_warps;
-    h->smem_vn = (size_t)kBpVnWarps * 2 * h->dv_max * 32 * sizeof(float);
-    if (h->dv_max > kBpVnClass[kBpVnClasses - 1] && h->smem_vn > 227 * 1024)
-        return fail(SCALDPC_ERR_UNSUPPORTED, "column degree %d too large for the shared-memory scratch", h->dv_max);
+    if (h->dv_max > kBpVnClass[kBpVnClasses - 1]) {
+        const size_t pw = (size_t)2 * h->dv_max * 32 * sizeof(float);
+        h->vn_gen_wpc = (int)std::min<size_t>(kBpVnWarps, (216 * 1024) / pw);
+        if (h->vn_gen_wpc < 1)
+            return fail(SCALDPC_ERR_UNSUPPORTED, "column degree %d too large for the shared-memory scratch", h->dv_max);
+        h->smem_vn = pw * h->vn_gen_wpc;
+    }
     SCALDPC_CUDA(cudaSetDevice(device));
     SCALDPC_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
     int rc;
     if ((rc = upload_vec(&h->d_row_ptr, g.row_ptr)) || (rc = upload_vec(&h->d_col, g.col)) ||
-        (rc = upload_vec(&h->d_col_ptr, g.col_ptr)) || (rc = upload_vec(&h->d_csc_edge, g.csc_edge)) ||
+        (rc = upload_vec(&h->d_col_ptr, g.col_ptr)) || (rc = upload_vec(&h->d_csc_edge, g.csc_off)) ||
         (rc = upload_vec(&h->d_vn_order, g.vn_order)))
         return rc;
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_prior, (size_t)n * sizeof(float)));
@@ -316,8 +330,12 @@ int scaldpc_bp_create(int m, int n, const int32_t *row_ptr, const int32_t *col, 
     SCALDPC_CUDA(cudaMallocHost((void **)&h->h_pin, 2 * sizeof(int)));
     SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_cn<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_cn));
     SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_cn<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_cn));
-    if (h->dv_max > kBpVnClass[kBpVnClasses - 1])
+    if (h->smem_vn)
         SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_vn_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_vn));
+    for (int c = 0; c < kBpVnClasses; ++c) {
+        SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->vn_occ[c], vn_class_fn(c), kBpVnWarps * 32, 0));
+        h->vn_occ[c] = std::max(1, h->vn_occ[c]);
+    }
     SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->cn_occ[0], k_bp_cn<false>, h->cn_warps * 32, h->smem_cn));
     SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->cn_occ[1], k_bp_cn<true>, h->cn_warps * 32, h->smem_cn));
     h->cn_occ[0] = std::max(1, h->cn_occ[0]);

@@ -16,6 +16,7 @@ struct BpHostGraph {
     int m = 0, n = 0, E = 0;
     int dc_max = 0, dv_max = 0;
     std::vector<int> row_ptr, col, col_ptr, csc_edge;
+    std::vector<uint32_t> csc_off;  // csc_edge * 128: byte offset of the edge's 128-byte line inside a tile's message block
     // variables sorted by degree (ascending, stable) and the end index of each degree class in that order:
     // class c holds the variables with degree <= kBpVnClass[c] (the last class, "generic", holds the rest)
     std::vector<int> vn_order;
@@ -60,6 +61,9 @@ inline int build_bp_graph(int m, int n, const int32_t *row_ptr, const int32_t *c
     std::vector<int> fill(n, 0);
     for (int r = 0; r < m; ++r)
         for (int e = row_ptr[r]; e < row_ptr[r + 1]; ++e) g.csc_edge[g.col_ptr[col[e]] + fill[col[e]]++] = e;
+    if ((long long)g.E * 128 > 0xffffffffLL) return bad(SCALDPC_ERR_UNSUPPORTED, "too many edges");
+    g.csc_off.resize(g.csc_edge.size());
+    for (size_t i = 0; i < g.csc_edge.size(); ++i) g.csc_off[i] = (uint32_t)g.csc_edge[i] * 128u;
     g.vn_order.resize(n);
     for (int c = 0; c < n; ++c) g.vn_order[c] = c;
     std::stable_sort(g.vn_order.begin(), g.vn_order.end(), [&](int a, int b) {

@@ -13,7 +13,7 @@
 //   * check -> bit messages travel as LLRs  c2v = +-ln((1-U)/U)  (upstream: c2b = (1-x)/(1+x)), so the bit node sums
 //     where upstream multiplies (no under/overflow for heavy columns) and keeps upstream's sequential semantics
 //     including the "NaN -> neutral element" resets of the running product (0 * inf in ratios == inf - inf in LLRs).
-// Cost per edge and iteration: ex2 + rcp (fold) and 2 x lg2 (unfold) on the MUFU pipe and ~40 other instructions;
+// Cost per edge and iteration: ex2 + rcp (fold) and rcp + lg2 (unfold) on the MUFU pipe and ~40 other instructions;
 // the earlier phi(x) = -log tanh(x/2) formulation needed ~110 and left both passes issue-bound.
 //
 // Data layout in HBM ("tile" layout, shared with the q-ary decoder): 32 trials per tile, lane = trial % 32 innermost.
@@ -47,7 +47,7 @@ struct BpDev {
     const int *row_ptr;       // m+1
     const int *col;           // E
     const int *col_ptr;       // n+1
-    const int *csc_edge;      // E
+    const uint32_t *csc_off;  // E: byte offset (edge * 128) of each variable's edges inside a tile's message block, rows ascending
     const int *vn_order;      // n: variables sorted by degree (ascending), the bit pass runs one launch per class
     float *msg;
     const float *prior;
@@ -64,29 +64,35 @@ struct BpDev {
 };
 
 #ifdef SCALDPC_HOST_MODEL
-__device__ __forceinline__ bool bp_signbit(float x)
+__device__ __forceinline__ uint32_t bp_bits(float x)
 {
     uint32_t u;
     memcpy(&u, &x, 4);
-    return u >> 31;
+    return u;
+}
+__device__ __forceinline__ float bp_float(uint32_t u)
+{
+    float x;
+    memcpy(&x, &u, 4);
+    return x;
 }
 __device__ __forceinline__ float bp_ex2(float x) { return exp2f(x); }
 __device__ __forceinline__ float bp_lg2(float x) { return log2f(x); }
 __device__ __forceinline__ float bp_rcp(float x) { return 1.0f / x; }
 #else
-__device__ __forceinline__ bool bp_signbit(float x) { return __float_as_uint(x) >> 31; }
-// MUFU.EX2 / MUFU.LG2 with subnormal results / arguments kept (a very reliable message, |L| > 87, must not flush to an
-// exact 0 == "infinitely reliable"); MUFU.RCP only ever sees 1 + t in [1, 2].
+__device__ __forceinline__ uint32_t bp_bits(float x) { return __float_as_uint(x); }
+__device__ __forceinline__ float bp_float(uint32_t u) { return __uint_as_float(u); }
+// Single MUFU instructions (flush-to-zero forms: no subnormal fix-up code around them).
 __device__ __forceinline__ float bp_ex2(float x)
 {
     float r;
-    asm("ex2.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
 __device__ __forceinline__ float bp_lg2(float x)
 {
     float r;
-    asm("lg2.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
 __device__ __forceinline__ float bp_rcp(float x)
@@ -96,16 +102,20 @@ __device__ __forceinline__ float bp_rcp(float x)
     return r;
 }
 #endif
+__device__ __forceinline__ bool bp_signbit(float x) { return bp_bits(x) >> 31; }
 
-// LLR -> signed folded probability  q = copysign(1/(1+e^|L|), L).  fold(+-inf) = +-0, fold(+-0) = +-1/2, NaN -> NaN.
+// LLR -> signed folded probability  q = copysign(1/(1+e^|L|), L): FMUL, MUFU.EX2, FADD, MUFU.RCP, LOP3.
+// fold(+-inf) = +-0, fold(+-0) = +-1/2, NaN -> NaN.  e^|L| overflows for |L| > 88.7, where u = 0 ("certain"; the fp64
+// upstream already rounds tanh(|L|/2) to exactly 1 for |L| > 37).
 __device__ __forceinline__ float bp_fold(float L)
 {
-    const float t = bp_ex2(-1.4426950408889634f * fabsf(L));  // e^-|L| in [0, 1]
-    return copysignf(t * bp_rcp(1.0f + t), L);
+    const float u = bp_rcp(1.0f + bp_ex2(1.4426950408889634f * fabsf(L)));
+    return bp_float(bp_bits(u) | (bp_bits(L) & 0x80000000u));
 }
-// Odd-parity probability U in [0, 1/2] -> LLR magnitude ln((1-U)/U) >= 0.  unfold(0) = +inf, unfold(1/2) = 0.
-__device__ __forceinline__ float bp_unfold(float U) { return 0.6931471805599453f * (bp_lg2(1.0f - U) - bp_lg2(U)); }
-// One more magnitude u joins a parity: U + u - 2Uu.
+// Odd-parity probability U in [0, 1/2] -> LLR magnitude ln((1-U)/U) = ln(1/U - 1) >= 0: MUFU.RCP, FADD, MUFU.LG2, FMUL.
+// unfold(0) = +inf, unfold(1/2) = 0 (+- 3e-7 absolute), NaN -> NaN.
+__device__ __forceinline__ float bp_unfold(float U) { return 0.6931471805599453f * bp_lg2(bp_rcp(U) - 1.0f); }
+// One more magnitude u joins a parity: U + u - 2Uu (two FFMA).
 __device__ __forceinline__ float bp_parity(float U, float u) { return fmaf(u, fmaf(-2.0f, U, 1.0f), U); }
 
 __device__ __forceinline__ float bp_prior_of(const BpDev &p, int tile, int v, int lane)
@@ -133,15 +143,36 @@ __global__ void __launch_bounds__(kBpCnWarpsMax * 32) k_bp_cn(const BpDev p, con
     SCALDPC_DYN_SMEM(float, smem);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
     const int gw = blockIdx.x * wpc + warp, nw = gridDim.x * wpc;
-    const int n_items = tiles * p.m;
     const int stride = p.dc_max * 32;                // floats per per-warp array
     float *wbase = smem + (size_t)warp * 3 * stride;  // stage[2], P
     float *P = wbase + 2 * stride + lane;
 
-    // next item >= `item` (stepping by nw) whose tile still has running trials
-    auto next_live = [&](int item) {
-        while (item < n_items && bp_tile_done(p, item / p.m)) item += nw;
-        return item;
+    const int step_t = nw / p.m, step_c = nw - step_t * p.m;  // item -> item + nw without a division per item
+    struct Item {
+        int tile, check, e0, d;
+    };
+    // moves to the next item (stride nw) whose tile still has running trials; tile >= tiles: none left
+    auto advance = [&](Item &it, bool first) {
+        if (!first) {
+            it.tile += step_t;
+            it.check += step_c;
+            if (it.check >= p.m) {
+                it.check -= p.m;
+                ++it.tile;
+            }
+        }
+        while (it.tile < tiles && bp_tile_done(p, it.tile)) {
+            it.tile += step_t;
+            it.check += step_c;
+            if (it.check >= p.m) {
+                it.check -= p.m;
+                ++it.tile;
+            }
+        }
+        if (it.tile < tiles) {
+            it.e0 = __ldg(p.row_ptr + it.check);
+            it.d = __ldg(p.row_ptr + it.check + 1) - it.e0;
+        }
     };
 #ifndef SCALDPC_HOST_MODEL
     __shared__ uint64_t bars[kBpCnWarpsMax][2];
@@ -153,30 +184,31 @@ __global__ void __launch_bounds__(kBpCnWarpsMax * 32) k_bp_cn(const BpDev p, con
         }
         __syncwarp();
     }
-    auto issue = [&](int item, int b) {  // lane 0 only
-        const int tile = item / p.m, check = item - tile * p.m;
-        const int e0 = __ldg(p.row_ptr + check), d = __ldg(p.row_ptr + check + 1) - e0;
-        if (d <= 0) return;
-        sc_mbar_expect_tx(&bars[warp][b], (uint32_t)d * 128u);
-        sc_bulk_g2s(wbase + b * stride, p.msg + ((size_t)tile * p.E + e0) * 32, (uint32_t)d * 128u, &bars[warp][b]);
+    auto issue = [&](const Item &it, int b) {  // lane 0 only
+        if (it.d <= 0) return;
+        sc_mbar_expect_tx(&bars[warp][b], (uint32_t)it.d * 128u);
+        sc_bulk_g2s(wbase + b * stride, p.msg + ((size_t)it.tile * p.E + it.e0) * 32, (uint32_t)it.d * 128u, &bars[warp][b]);
     };
 #endif
 
-    int item = next_live(gw);
+    Item cur;
+    cur.tile = gw / p.m;
+    cur.check = gw - cur.tile * p.m;
+    advance(cur, true);
     int b = 0;
 #ifndef SCALDPC_HOST_MODEL
-    if (!FIRST && item < n_items && lane == 0) issue(item, 0);
+    if (!FIRST && cur.tile < tiles && lane == 0) issue(cur, 0);
 #endif
-    while (item < n_items) {
-        const int nxt = next_live(item + nw);
+    while (cur.tile < tiles) {
+        Item nxt = cur;
+        advance(nxt, false);
 #ifndef SCALDPC_HOST_MODEL
-        if (!FIRST && nxt < n_items && lane == 0) {
+        if (!FIRST && nxt.tile < tiles && lane == 0) {
             sc_fence_proxy_async();  // the other half was read (generic proxy) during the previous item
             issue(nxt, b ^ 1);
         }
 #endif
-        const int tile = item / p.m, check = item - tile * p.m;
-        const int e0 = __ldg(p.row_ptr + check), d = __ldg(p.row_ptr + check + 1) - e0;
+        const int tile = cur.tile, check = cur.check, e0 = cur.e0, d = cur.d;
         float *msg = p.msg + ((size_t)tile * p.E + e0) * 32 + lane;
         if (d > 0) {
 #ifdef SCALDPC_HOST_MODEL
@@ -188,7 +220,8 @@ __global__ void __launch_bounds__(kBpCnWarpsMax * 32) k_bp_cn(const BpDev p, con
                 phases ^= 1u << b;
             }
 #endif
-            bool neg = (__ldg(p.synd_w + (size_t)tile * p.m + check) >> lane) & 1u;
+            // sign word: bit 31 = (-1)^synd * product of the signs of ALL inputs (lower bits are garbage)
+            uint32_t neg = (__ldg(p.synd_w + (size_t)tile * p.m + check) >> lane) << 31;
             float pre = 0.0f;
             if (FIRST) {
 #ifdef SCALDPC_HOST_MODEL
@@ -203,7 +236,7 @@ __global__ void __launch_bounds__(kBpCnWarpsMax * 32) k_bp_cn(const BpDev p, con
                     P[k * 32] = pre;
                     park[(size_t)k * 32] = q;
                     pre = bp_parity(pre, fabsf(q));
-                    neg ^= bp_signbit(v);
+                    neg ^= bp_bits(v);
                 }
                 a = park;
             } else {
@@ -212,7 +245,7 @@ __global__ void __launch_bounds__(kBpCnWarpsMax * 32) k_bp_cn(const BpDev p, con
                     const float x = a[k * 32];
                     P[k * 32] = pre;
                     pre = bp_parity(pre, fabsf(x));
-                    neg ^= bp_signbit(x);
+                    neg ^= bp_bits(x);
                 }
             }
             float suf = 0.0f;
@@ -220,29 +253,32 @@ __global__ void __launch_bounds__(kBpCnWarpsMax * 32) k_bp_cn(const BpDev p, con
             for (int k = d - 1; k >= 0; --k) {
                 const float x = a[k * 32];
                 const float mag = bp_unfold(bp_parity(P[k * 32], suf));  // parity of the OTHER magnitudes
-                msg[(size_t)k * 32] = (neg != bp_signbit(x)) ? -mag : mag;
+                msg[(size_t)k * 32] = bp_float(bp_bits(mag) ^ ((neg ^ bp_bits(x)) & 0x80000000u));  // sign of the OTHERS
                 suf = bp_parity(suf, fabsf(x));
             }
         }
 #ifndef SCALDPC_HOST_MODEL
         __syncwarp();  // every lane is done with stage[b] before lane 0 re-arms it (next iteration)
 #endif
-        item = nxt;
+        cur = nxt;
         b ^= 1;
     }
 }
 
 // -----------------------------------------------------------------------------------------------------------
-// Bit-to-check pass + decision.  One warp = (tile, variable), lane = trial.  Upstream's two sweeps over the
-// column (rows ascending): forward running value seeded with the prior, backward running value seeded with the
-// neutral element; a NaN running value is reset to the neutral element (ratio 1 == LLR 0).  Stores
-// q = fold(v2c).  Decision: upstream decodes 1 when ratio >= 1, i.e. LLR <= 0.  Converged (done)
-// lanes keep their old outputs.
-// The variables are processed in degree order, one launch per degree class DMAX: all of a variable's incoming
-// messages are gathered into registers by DMAX independent loads (the v0 kernel walked the column 4 loads at a time
-// through shared memory and was latency-bound at 0.35 of the HBM peak).
+// Bit-to-check pass + decision.  Work item = (tile, variable); one warp per item, lane = trial.  Upstream's two
+// sweeps over the column (rows ascending): forward running value seeded with the prior, backward running value
+// seeded with the neutral element; a NaN running value is reset to the neutral element (ratio 1 == LLR 0).  Stores
+// q = fold(v2c).  Decision: upstream decodes 1 when ratio >= 1, i.e. LLR <= 0.  Converged (done) lanes keep their old
+// outputs.
+// A variable's incoming messages are d scattered 128-byte lines.  Persistent kernel, registers only: a warp gathers
+// the column of its NEXT item into registers (DMAX independent loads) before it works on the current one, so every
+// resident warp always has a full column in flight (v1 loaded, computed, stored in sequence: 12.8 warps stalled on
+// long_scoreboard per issue, 0.34 of the HBM peak; a cp.async/shared-memory variant hid the latency but executed
+// 2.3x the instructions of the check pass and became issue-bound at 0.43).  The variables are sorted by degree and
+// the pass runs one launch per degree class DMAX, so light columns do not pay for heavy ones.
 // -----------------------------------------------------------------------------------------------------------
-constexpr int kBpVnWarps = 4;
+constexpr int kBpVnWarps = 8;
 
 __device__ __forceinline__ void bp_vn_decide(const BpDev &p, int tile, int var, int lane, uint32_t done, float post)
 {
@@ -260,54 +296,121 @@ __device__ __forceinline__ void bp_vn_decide(const BpDev &p, int tile, int var, 
 #endif
 }
 
-template <int DMAX>
-__global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const int v_lo, const int v_hi)
-{
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int idx = v_lo + blockIdx.x * kBpVnWarps + warp;
-    const int tile = blockIdx.y;
-    if (idx >= v_hi) return;
-    const uint32_t done = __ldg(p.done + tile);
-    if (done == __ldg(p.valid + tile)) return;
-    const int var = __ldg(p.vn_order + idx);
-    const int p0 = __ldg(p.col_ptr + var), d = __ldg(p.col_ptr + var + 1) - p0;  // d <= DMAX
-    float *msg = p.msg + (size_t)tile * p.E * 32 + lane;
+// An item of the bit pass and everything its phases need to know about it.
+struct BpVnItem {
+    int tile, j, var, p0, d;
+};
 
-    int off[DMAX];
-    float c[DMAX], F[DMAX];
+// `base` + byte offset, with the base kept as an opaque 64-bit register so that the address is one 64-bit add.
+__device__ __forceinline__ float *bp_at(float *base, uint32_t byte_off) { return (float *)((char *)base + byte_off); }
+
+// The two sweeps of one variable of degree exactly D (straight-line code, no guards).
+template <int D, int DMAX>
+__device__ __forceinline__ void bp_vn_body(const BpDev &p, const BpVnItem &it, int lane, const float (&c)[DMAX])
+{
+    const uint32_t done = __ldg(p.done + it.tile);
+    float *msg = p.msg + (size_t)it.tile * p.E * 32 + lane;
+#ifndef SCALDPC_HOST_MODEL
+    asm volatile("" : "+l"(msg));
+#endif
+    const uint32_t *off = p.csc_off + it.p0;
+    float F[D > 0 ? D : 1];
+    float temp = bp_prior_of(p, it.tile, it.var, lane);
 #pragma unroll
-    for (int i = 0; i < DMAX; ++i)
-        if (i < d) {
-            off[i] = __ldg(p.csc_edge + p0 + i);
-            c[i] = msg[(size_t)off[i] * 32];
-        }
-    float temp = bp_prior_of(p, tile, var, lane);
-#pragma unroll
-    for (int i = 0; i < DMAX; ++i)
-        if (i < d) {
-            F[i] = temp;
-            temp += c[i];
-            if (temp != temp) temp = 0.0f;
-        }
+    for (int i = 0; i < D; ++i) {
+        F[i] = temp;
+        temp += c[i];
+        if (temp != temp) temp = 0.0f;
+    }
     const float post = temp;
     temp = 0.0f;
 #pragma unroll
-    for (int i = DMAX - 1; i >= 0; --i)
-        if (i < d) {
-            const float v = F[i] + temp;
-            msg[(size_t)off[i] * 32] = bp_fold(v);
-            temp += c[i];
-            if (temp != temp) temp = 0.0f;
-        }
-    bp_vn_decide(p, tile, var, lane, done, post);
+    for (int i = D - 1; i >= 0; --i) {
+        *bp_at(msg, __ldg(off + i)) = bp_fold(F[i] + temp);
+        temp += c[i];
+        if (temp != temp) temp = 0.0f;
+    }
+    bp_vn_decide(p, it.tile, it.var, lane, done, post);
 }
 
-// Any degree (columns heavier than the largest register class): per-lane scratch [i][lane] in shared memory.
+template <int D, int DMIN, int DMAX>
+__device__ __forceinline__ void bp_vn_dispatch(const BpDev &p, const BpVnItem &it, int lane, const float (&c)[DMAX])
+{
+    if constexpr (D < DMIN) {
+        bp_vn_body<DMAX, DMAX>(p, it, lane, c);  // unreachable for a correctly sorted class; keeps the code total
+    } else {
+        if (it.d == D)
+            bp_vn_body<D, DMAX>(p, it, lane, c);
+        else
+            bp_vn_dispatch<D - 1, DMIN, DMAX>(p, it, lane, c);
+    }
+}
+
+// Degree class (DMIN .. DMAX].  The class of degree <= 1 is instantiated as <0, 1> and also takes isolated variables.
+template <int DMIN, int DMAX>
+__global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const int v_lo, const int v_hi, const int tiles)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
+    const int gw = blockIdx.x * wpc + warp, nw = gridDim.x * wpc;
+    const int nv = v_hi - v_lo;
+    const int step_t = nw / nv, step_j = nw - step_t * nv;  // item -> item + nw without a division per item
+
+    // moves to the next item (stride nw) whose tile still has running trials; tile >= tiles: none left
+    auto advance = [&](BpVnItem &it, bool first) {
+        bool step = !first;
+        while (true) {
+            if (step) {
+                it.tile += step_t;
+                it.j += step_j;
+                if (it.j >= nv) {
+                    it.j -= nv;
+                    ++it.tile;
+                }
+            }
+            if (it.tile >= tiles || !bp_tile_done(p, it.tile)) break;
+            step = true;
+        }
+        if (it.tile < tiles) {
+            it.var = __ldg(p.vn_order + v_lo + it.j);
+            it.p0 = __ldg(p.col_ptr + it.var);
+            it.d = __ldg(p.col_ptr + it.var + 1) - it.p0;  // in (DMIN, DMAX] (host guarantees)
+        }
+    };
+    auto gather = [&](const BpVnItem &it, float (&c)[DMAX]) {
+        float *src = p.msg + (size_t)it.tile * p.E * 32 + lane;
+#ifndef SCALDPC_HOST_MODEL
+        asm volatile("" : "+l"(src));
+#endif
+        const uint32_t *off = p.csc_off + it.p0;
+#pragma unroll
+        for (int i = 0; i < DMAX; ++i)
+            if ((DMIN > 0 && i <= DMIN) || i < it.d) c[i] = *bp_at(src, __ldg(off + i));  // d > DMIN: the first are unguarded
+    };
+
+    BpVnItem cur;
+    cur.tile = gw / nv;
+    cur.j = gw - cur.tile * nv;
+    advance(cur, true);
+    float c[DMAX], cn[DMAX];
+    if (cur.tile < tiles) gather(cur, c);
+    while (cur.tile < tiles) {
+        BpVnItem nxt = cur;
+        advance(nxt, false);
+        if (nxt.tile < tiles) gather(nxt, cn);
+        bp_vn_dispatch<DMAX, (DMIN == 0 ? 0 : DMIN + 1), DMAX>(p, cur, lane, c);  // the first class also takes degree 0
+        cur = nxt;
+#pragma unroll
+        for (int i = 0; i < DMAX; ++i) c[i] = cn[i];
+    }
+}
+
+// Any degree (columns heavier than the largest register class): per-lane scratch [i][lane] in shared memory,
+// one CTA pass over (variable, tile) without prefetch.
 __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_generic(const BpDev p, const int v_lo, const int v_hi)
 {
     SCALDPC_DYN_SMEM(float, smem);
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int idx = v_lo + blockIdx.x * kBpVnWarps + warp;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
+    const int idx = v_lo + blockIdx.x * wpc + warp;
     const int tile = blockIdx.y;
     if (idx >= v_hi) return;
     const uint32_t done = __ldg(p.done + tile);
@@ -317,11 +420,12 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_generic(const BpDev p
     float *C = smem + (size_t)warp * 2 * p.dv_max * 32 + lane;
     float *F = C + (size_t)p.dv_max * 32;
     float *msg = p.msg + (size_t)tile * p.E * 32 + lane;
+    const uint32_t *off = p.csc_off + p0;
 
     float temp = bp_prior_of(p, tile, var, lane);
 #pragma unroll 4
     for (int i = 0; i < d; ++i) {
-        const float c = msg[(size_t)__ldg(p.csc_edge + p0 + i) * 32];
+        const float c = *bp_at(msg, __ldg(off + i));
         C[i * 32] = c;
         F[i * 32] = temp;
         temp += c;
@@ -330,8 +434,7 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_generic(const BpDev p
     const float post = temp;
     temp = 0.0f;
     for (int i = d - 1; i >= 0; --i) {
-        const float v = F[i * 32] + temp;
-        msg[(size_t)__ldg(p.csc_edge + p0 + i) * 32] = bp_fold(v);
+        *bp_at(msg, __ldg(off + i)) = bp_fold(F[i * 32] + temp);
         temp += C[i * 32];
         if (temp != temp) temp = 0.0f;
     }

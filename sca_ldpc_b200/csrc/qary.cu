@@ -492,23 +492,21 @@ int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in
     const int nchunks = (T + chunk - 1) / chunk;
     if ((rc = ensure_workspace(h, chunk / 32, want_post))) return rc;
     if ((rc = ensure_stage(h, (size_t)chunk, (size_t)T, want_post))) return rc;
-    for (int c = 0; c < nchunks; ++c) {
+    // Host-side enqueue order per chunk c: H2D(c+1), decode(c), D2H(c-1).  A D2H into pageable memory blocks the
+    // host until decode(c-1) is done; by then decode(c) and H2D(c+1) are already queued, so the device never idles.
+    auto h2d = [&](int c) -> int {
         const int b = c & 1, t0 = c * chunk, tc = std::min(chunk, T - t0);
-        // d_in[b] is free once the decode of chunk c-2 has consumed it
-        if (c >= 2) SCALDPC_CUDA(cudaStreamWaitEvent(h->s_in, h->ev_comp[b], 0));
+        if (c >= 2) SCALDPC_CUDA(cudaStreamWaitEvent(h->s_in, h->ev_comp[b], 0));  // decode(c-2) has consumed d_in[b]
         SCALDPC_CUDA(cudaMemcpyAsync(h->d_in[b], in + (size_t)t0 * h->SL, (size_t)tc * h->SL * sizeof(float),
                                      cudaMemcpyHostToDevice, h->s_in));
         if (special)
             SCALDPC_CUDA(cudaMemcpyAsync(h->d_in_sum[b], in_sum + (size_t)t0 * h->SLS, (size_t)tc * h->SLS * sizeof(float),
                                          cudaMemcpyHostToDevice, h->s_in));
         SCALDPC_CUDA(cudaEventRecord(h->ev_in[b], h->s_in));
-        SCALDPC_CUDA(cudaStreamWaitEvent(st, h->ev_in[b], 0));
-        if (c >= 2) SCALDPC_CUDA(cudaStreamWaitEvent(st, h->ev_out[b], 0));  // d_ohard[b] has been copied out
-        if ((rc = decode_on_device(h, tc, h->d_in[b], h->d_in_sum[b], h->d_ohard[b], post ? h->d_opost[b] : nullptr,
-                                   post_sum ? h->d_opost_sum[b] : nullptr, flags, st)))
-            return rc;
-        SCALDPC_CUDA(cudaMemcpyAsync(h->d_status_all + t0, h->d_status, (size_t)tc * sizeof(int), cudaMemcpyDeviceToDevice, st));
-        SCALDPC_CUDA(cudaEventRecord(h->ev_comp[b], st));
+        return 0;
+    };
+    auto d2h = [&](int c) -> int {
+        const int b = c & 1, t0 = c * chunk, tc = std::min(chunk, T - t0);
         SCALDPC_CUDA(cudaStreamWaitEvent(h->s_out, h->ev_comp[b], 0));
         SCALDPC_CUDA(cudaMemcpyAsync(hard + (size_t)t0 * h->N, h->d_ohard[b], (size_t)tc * h->N, cudaMemcpyDeviceToHost, h->s_out));
         if (post)
@@ -518,7 +516,22 @@ int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in
             SCALDPC_CUDA(cudaMemcpyAsync(post_sum + (size_t)t0 * h->SLS, h->d_opost_sum[b],
                                          (size_t)tc * h->SLS * sizeof(float), cudaMemcpyDeviceToHost, h->s_out));
         SCALDPC_CUDA(cudaEventRecord(h->ev_out[b], h->s_out));
+        return 0;
+    };
+    if ((rc = h2d(0))) return rc;
+    for (int c = 0; c < nchunks; ++c) {
+        const int b = c & 1, t0 = c * chunk, tc = std::min(chunk, T - t0);
+        if (c + 1 < nchunks && (rc = h2d(c + 1))) return rc;
+        SCALDPC_CUDA(cudaStreamWaitEvent(st, h->ev_in[b], 0));
+        if (c >= 2) SCALDPC_CUDA(cudaStreamWaitEvent(st, h->ev_out[b], 0));  // d_ohard[b] of chunk c-2 has been copied out
+        if ((rc = decode_on_device(h, tc, h->d_in[b], h->d_in_sum[b], h->d_ohard[b], post ? h->d_opost[b] : nullptr,
+                                   post_sum ? h->d_opost_sum[b] : nullptr, flags, st)))
+            return rc;
+        SCALDPC_CUDA(cudaMemcpyAsync(h->d_status_all + t0, h->d_status, (size_t)tc * sizeof(int), cudaMemcpyDeviceToDevice, st));
+        SCALDPC_CUDA(cudaEventRecord(h->ev_comp[b], st));
+        if (c >= 1 && (rc = d2h(c - 1))) return rc;
     }
+    if ((rc = d2h(nchunks - 1))) return rc;
     std::vector<int> hs(T);
     SCALDPC_CUDA(cudaMemcpyAsync(hs.data(), h->d_status_all, (size_t)T * sizeof(int), cudaMemcpyDeviceToHost, st));
     SCALDPC_CUDA(cudaStreamSynchronize(st));

@@ -239,7 +239,7 @@ int hostmodel_bp_decode(int m, int n, const int32_t *row_ptr, const int32_t *col
         BpDev p;
         p.m = m; p.n = n; p.E = g.E; p.dc_max = std::max(1, g.dc_max); p.dv_max = std::max(1, g.dv_max);
         p.per_trial_prior = probs_per_trial;
-        p.row_ptr = g.row_ptr.data(); p.col = g.col.data(); p.col_ptr = g.col_ptr.data(); p.csc_edge = g.csc_edge.data();
+        p.row_ptr = g.row_ptr.data(); p.col = g.col.data(); p.col_ptr = g.col_ptr.data(); p.csc_off = g.csc_off.data();
         p.vn_order = g.vn_order.data();
         p.msg = set[cur].msg.data();
         p.prior = probs_per_trial ? set[cur].prior_t.data() : prior.data();
@@ -262,7 +262,7 @@ int hostmodel_bp_decode(int m, int n, const int32_t *row_ptr, const int32_t *col
     };
     const int dmax = std::max(std::max(1, g.dc_max), std::max(1, g.dv_max));
     const int cn_wpc = 2;  // warps per CTA of the modelled check pass (any value works: items are strided)
-    std::vector<float> scratch((size_t)std::max(cn_wpc * 3, kBpVnWarps * 2) * dmax * 32);
+    std::vector<float> scratch((size_t)std::max(cn_wpc * 3, 2 * 3) * dmax * 32);
     scaldpc_host_model_smem = scratch.data();
     int cur = 0, cur_tiles = tiles, compactions = 0;
     for (int it = 1; it <= max_iter; ++it) {
@@ -273,16 +273,15 @@ int hostmodel_bp_decode(int m, int n, const int32_t *row_ptr, const int32_t *col
         for (int c = 0; c <= kBpVnClasses; ++c) {
             const int hi = g.class_end[c];
             if (hi > lo) {
-                const unsigned gx = (hi - lo + kBpVnWarps - 1) / kBpVnWarps;
                 switch (c) {
-                case 0: run_grid(gx, cur_tiles, kBpVnWarps * 32, k_bp_vn<1>, p, lo, hi); break;
-                case 1: run_grid(gx, cur_tiles, kBpVnWarps * 32, k_bp_vn<4>, p, lo, hi); break;
-                case 2: run_grid(gx, cur_tiles, kBpVnWarps * 32, k_bp_vn<8>, p, lo, hi); break;
-                case 3: run_grid(gx, cur_tiles, kBpVnWarps * 32, k_bp_vn<12>, p, lo, hi); break;
-                case 4: run_grid(gx, cur_tiles, kBpVnWarps * 32, k_bp_vn<16>, p, lo, hi); break;
-                case 5: run_grid(gx, cur_tiles, kBpVnWarps * 32, k_bp_vn<24>, p, lo, hi); break;
-                case 6: run_grid(gx, cur_tiles, kBpVnWarps * 32, k_bp_vn<32>, p, lo, hi); break;
-                default: run_grid(gx, cur_tiles, kBpVnWarps * 32, k_bp_vn_generic, p, lo, hi);
+                case 0: run_grid(3, 1, 2 * 32, k_bp_vn<0, 1>, p, lo, hi, cur_tiles); break;
+                case 1: run_grid(3, 1, 2 * 32, k_bp_vn<1, 4>, p, lo, hi, cur_tiles); break;
+                case 2: run_grid(3, 1, 2 * 32, k_bp_vn<4, 8>, p, lo, hi, cur_tiles); break;
+                case 3: run_grid(3, 1, 2 * 32, k_bp_vn<8, 12>, p, lo, hi, cur_tiles); break;
+                case 4: run_grid(3, 1, 2 * 32, k_bp_vn<12, 16>, p, lo, hi, cur_tiles); break;
+                case 5: run_grid(3, 1, 2 * 32, k_bp_vn<16, 24>, p, lo, hi, cur_tiles); break;
+                case 6: run_grid(3, 1, 2 * 32, k_bp_vn<24, 32>, p, lo, hi, cur_tiles); break;
+                default: run_grid((hi - lo + 1) / 2, cur_tiles, 2 * 32, k_bp_vn_generic, p, lo, hi);
                 }
             }
             lo = hi;
