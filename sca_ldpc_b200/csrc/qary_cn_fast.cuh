@@ -22,6 +22,94 @@
 // (decoder_special.rs:591-609) is fused: its v2c is recomputed from the channel LLR and the previous c2v, so it
 // never travels through HBM, and on the last iteration its hard decision / posterior are emitted from here.
 
+// ---- packed f32x2 arithmetic (sm_100a: add.rn.f32x2 -> FADD2 with a broadcast scalar operand).  One instruction
+// adds the same scalar to two neighbouring table entries, halving the FADD count of the (min,+) convolutions.
+// Rounding is IEEE round-to-nearest per element, identical to the scalar FADD (and to the host model).
+#ifdef SCALDPC_HOST_MODEL
+struct F2 {
+    float lo, hi;
+};
+__device__ __forceinline__ F2 f2_make(float lo, float hi) { return F2{lo, hi}; }
+__device__ __forceinline__ float f2_lo(const F2 &x) { return x.lo; }
+__device__ __forceinline__ float f2_hi(const F2 &x) { return x.hi; }
+__device__ __forceinline__ F2 f2_add_s(const F2 &x, float s) { return F2{x.lo + s, x.hi + s}; }
+#else
+struct F2 {
+    unsigned long long v;
+};
+__device__ __forceinline__ F2 f2_make(float lo, float hi)
+{
+    F2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ float f2_lo(const F2 &x)
+{
+    float lo, hi;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(x.v));
+    return lo;
+}
+__device__ __forceinline__ float f2_hi(const F2 &x)
+{
+    float lo, hi;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(x.v));
+    return hi;
+}
+__device__ __forceinline__ F2 f2_add_s(const F2 &x, float s)
+{
+    F2 r;
+    asm("{\n\t.reg .b64 t;\n\tmov.b64 t, {%2, %2};\n\tadd.rn.f32x2 %0, %1, t;\n\t}" : "=l"(r.v) : "l"(x.v), "f"(s));
+    return r;
+}
+#endif
+
+// out[o] = min_i X[o - i] + a[i], o = 0 .. nx + Q - 2 (X given as pairs, nx entries).  The sum X[j] + a[i] for even j
+// also yields X[j+1] + a[i], which the next output consumes (carry).
+template <int Q, int NP, int NO>
+__device__ __forceinline__ void cn_conv_fwd(const F2 (&Xp)[NP], const int nx, const float (&a)[Q], float (&out)[NO])
+{
+    F2 carry[Q];
+#pragma unroll
+    for (int o = 0; o < 2 * NP + Q; ++o) {
+        if (o < nx + Q - 1) {
+            MinAcc acc;
+#pragma unroll
+            for (int i = 0; i < Q; ++i) {
+                const int j = o - i;
+                if (j >= 0 && j < nx) {
+                    if ((j & 1) == 0) {
+                        carry[i] = f2_add_s(Xp[j >> 1], a[i]);
+                        acc.add(f2_lo(carry[i]));
+                    } else {
+                        acc.add(f2_hi(carry[i]));
+                    }
+                }
+            }
+            out[o] = acc.get();
+        }
+    }
+}
+
+// out[o] = min_i a[i] + X[o + i], o = 0 .. no - 1 (X given as pairs, at least no + Q - 1 entries).
+template <int Q, int NP, int NO>
+__device__ __forceinline__ void cn_conv_bwd(const F2 (&Xp)[NP], const int no, const float (&a)[Q], float (&out)[NO])
+{
+    F2 carry[Q];
+#pragma unroll
+    for (int o = 0; o < 2 * NP; ++o) {
+        if (o < no) {
+            MinAcc acc;
+#pragma unroll
+            for (int i = 0; i < Q; ++i) {
+                const int j = o + i;
+                if ((j & 1) == 0 || o == 0) carry[i] = f2_add_s(Xp[j >> 1], a[i]);
+                acc.add((j & 1) ? f2_hi(carry[i]) : f2_lo(carry[i]));
+            }
+            out[o] = acc.get();
+        }
+    }
+}
+
 constexpr int kCnWarps = 8;  // warps per persistent CTA; 8 x 32 x 255 registers = one SM's register file
 
 #include "tma.cuh"
@@ -38,6 +126,7 @@ struct CnFastShape {
 template <int SW, int B, bool FIRST, bool LAST>
 __global__ void __launch_bounds__(kCnWarps * 32, 1) k_cn_fast(const QaryDev p, const int n_items)
 {
+    static_assert(SW >= 2, "k_cn_fast needs at least two B-variables per check");
     using Sh = CnFastShape<SW, B>;
     constexpr int Q = Sh::Q, BS = Sh::BS, QS = Sh::QS, NS = Sh::NS;
     const float INF = SC_INF;
@@ -97,18 +186,26 @@ __global__ void __launch_bounds__(kCnWarps * 32, 1) k_cn_fast(const QaryDev p, c
         sc_mbar_wait(bar, phase);
         phase ^= 1u;
 #endif
-        // ---- staged inputs -> registers
+        // ---- staged inputs -> registers (messages are already in the check frame after the first iteration)
         float a[SW][Q];
 #pragma unroll
         for (int k = 0; k < SW; ++k) {
-            const bool neg = FIRST && (__ldg(p.sign + e0 + k) < 0);  // later iterations: already in the check frame
+            const bool neg = FIRST && (__ldg(p.sign + e0 + k) < 0);
 #pragma unroll
-            for (int i = 0; i < Q; ++i) a[k][i] = SC_BUF(k * Q + (neg ? Q - 1 - i : i));
+            for (int i = 0; i < Q; ++i) a[k][i] = FIRST ? SC_BUF(k * Q + (neg ? Q - 1 - i : i)) : SC_BUF(k * Q + i);
         }
         // the sum-variable: v2c from channel + previous c2v (decoder_special.rs:591-604), check frame
         float as[QS];
 #pragma unroll
-        for (int i = 0; i < QS; ++i) as[i] = SC_BUF(NS + (negs ? QS - 1 - i : i));
+        for (int i = 0; i < QS; ++i) as[i] = SC_BUF(NS + i);
+        if (negs) {  // warp-uniform; never taken for H = [H' | I]
+#pragma unroll
+            for (int i = 0; i < QS / 2; ++i) {
+                const float t = as[i];
+                as[i] = as[QS - 1 - i];
+                as[QS - 1 - i] = t;
+            }
+        }
         if (!FIRST) {
             float m = INF;
 #pragma unroll
@@ -137,42 +234,34 @@ __global__ void __launch_bounds__(kCnWarps * 32, 1) k_cn_fast(const QaryDev p, c
 #pragma unroll
         for (int i = 0; i < QS; ++i) as[i] = sanitize(as[i]);
 
-        // ---- forward: F[k][u + k*B], k = 1..SW-1
-        float F[SW][2 * (SW - 1) * B + 1];
+        // ---- forward: Fp[k] = F_k as pairs, F_k[j] <-> u = j - k*B, j = 0 .. 2kB
+        F2 Fp[SW][(SW - 1) * B + 1];
 #pragma unroll
-        for (int i = 0; i < Q; ++i) F[1 % SW][i] = a[0][i];
+        for (int jj = 0; jj < (Q + 1) / 2; ++jj) Fp[1 % SW][jj] = f2_make(a[0][2 * jj], 2 * jj + 1 < Q ? a[0][2 * jj + 1] : INF);
 #pragma unroll
         for (int k = 1; k < SW - 1; ++k) {
+            float Fs[2 * (SW - 1) * B + 2];
+            cn_conv_fwd<Q>(Fp[k], 2 * k * B + 1, a[k], Fs);
+            Fs[2 * (k + 1) * B + 1] = INF;
 #pragma unroll
-            for (int u = -(k + 1) * B; u <= (k + 1) * B; ++u) {
-                MinAcc acc;
-#pragma unroll
-                for (int d = -B; d <= B; ++d) {
-                    const int up = u - d;
-                    if (up >= -k * B && up <= k * B) acc.add(F[k][up + k * B] + a[k][d + B]);
-                }
-                F[k + 1][u + (k + 1) * B] = acc.get();
-            }
+            for (int jj = 0; jj < (k + 1) * B + 1; ++jj) Fp[k + 1][jj] = f2_make(Fs[2 * jj], Fs[2 * jj + 1]);
         }
         // ---- c2v of the sum-variable: F_SW[-t]
+        float *out = msg + (size_t)base * 32;  // the check's slot block: constant offsets from here on
         float cs[QS];
-#pragma unroll
-        for (int t = -BS; t <= BS; ++t) {
-            const int u = -t;
-            MinAcc acc;
+        {
+            float Fs[QS + 1];
             if (SW == 1) {
-                if (u >= -B && u <= B) acc.add(a[0][u + B]);
-            } else {
-                constexpr int k = SW - 1;
 #pragma unroll
-                for (int d = -B; d <= B; ++d) {
-                    const int up = u - d;
-                    if (up >= -k * B && up <= k * B) acc.add(F[k][up + k * B] + a[k][d + B]);
-                }
+                for (int i = 0; i < QS; ++i) Fs[i] = a[0][i];
+            } else {
+                cn_conv_fwd<Q>(Fp[(SW - 1) % SW], 2 * (SW - 1) * B + 1, a[SW - 1], Fs);
             }
-            const float r = acc.get();
-            cs[t + BS] = (as[t + BS] == INF) ? INF : r;
-            msg[(size_t)(sbase + t + BS) * 32] = cs[t + BS];
+#pragma unroll
+            for (int i = 0; i < QS; ++i) {  // i = t + BS, F_SW index = QS - 1 - i
+                cs[i] = (as[i] == INF) ? INF : Fs[QS - 1 - i];
+                out[(size_t)(SW * Q + i) * 32] = cs[i];
+            }
         }
         if (LAST) {  // decision of the sum-variable (decoder_special.rs:606-608): first minimum in the VARIABLE's frame
             float min_val = INF;
@@ -199,34 +288,43 @@ __global__ void __launch_bounds__(kCnWarps * 32, 1) k_cn_fast(const QaryDev p, c
 #endif
         }
 
-        // ---- backward + combine.  Gc = G_{k+1}, indexed [u + (k+1)*B]
-        float Gc[QS], Gn[QS];
+        // ---- backward + combine.  Gp = G_{k+1} as pairs, G_{k+1}[j] <-> u = j - (k+1)*B
+        F2 Gp[BS + 1];
 #pragma unroll
-        for (int i = 0; i < QS; ++i) Gc[i] = as[QS - 1 - i];  // G_SW[u] = a_sum[-u]
+        for (int jj = 0; jj < BS + 1; ++jj)  // G_SW[u] = a_sum[-u]
+            Gp[jj] = f2_make(as[QS - 1 - 2 * jj], 2 * jj + 1 < QS ? as[QS - 2 - 2 * jj] : INF);
 #pragma unroll
         for (int k = SW - 1; k >= 0; --k) {
+            const int nk = 2 * k * B + 1;
+            // c2v_k[i] = min_j F_k[j] + G_{k+1}[j + i]
+            float r[Q];
+            if (k == 0) {
 #pragma unroll
-            for (int d = -B; d <= B; ++d) {  // c2v_k[d] = min_u F_k[u] + G_{k+1}[u + d]
-                MinAcc acc;
-                if (k == 0) {
-                    acc.add(Gc[d + B]);
-                } else {
+                for (int i = 0; i < Q; ++i) r[i] = (i & 1) ? f2_hi(Gp[i >> 1]) : f2_lo(Gp[i >> 1]);
+            } else {
+                MinAcc acc[Q];
 #pragma unroll
-                    for (int u = -k * B; u <= k * B; ++u) acc.add(F[k][u + k * B] + Gc[u + d + (k + 1) * B]);
+                for (int j = 0; j < nk; ++j) {
+                    const float s = (j & 1) ? f2_hi(Fp[k][j >> 1]) : f2_lo(Fp[k][j >> 1]);
+#pragma unroll
+                    for (int jj = j >> 1; jj <= (j + Q - 1) >> 1; ++jj) {
+                        const F2 t = f2_add_s(Gp[jj], s);
+                        const int i0 = 2 * jj - j, i1 = 2 * jj + 1 - j;
+                        if (i0 >= 0 && i0 < Q) acc[i0].add(f2_lo(t));
+                        if (i1 >= 0 && i1 < Q) acc[i1].add(f2_hi(t));
+                    }
                 }
-                const float r = acc.get();
-                msg[(size_t)(base + k * Q + d + B) * 32] = (a[k][d + B] == INF) ? INF : r;
+#pragma unroll
+                for (int i = 0; i < Q; ++i) r[i] = acc[i].get();
             }
-            if (k > 0) {
 #pragma unroll
-                for (int u = -k * B; u <= k * B; ++u) {
-                    MinAcc acc;
+            for (int i = 0; i < Q; ++i) out[(size_t)(k * Q + i) * 32] = (a[k][i] == INF) ? INF : r[i];
+            if (k > 0) {  // G_k[o] = min_i a_k[i] + G_{k+1}[o + i]
+                float Gs[QS + 1];
+                cn_conv_bwd<Q>(Gp, nk, a[k], Gs);
+                Gs[nk] = INF;
 #pragma unroll
-                    for (int d = -B; d <= B; ++d) acc.add(a[k][d + B] + Gc[u + d + (k + 1) * B]);
-                    Gn[u + k * B] = acc.get();
-                }
-#pragma unroll
-                for (int i = 0; i < QS; ++i) Gc[i] = Gn[i];
+                for (int jj = 0; jj < k * B + 1; ++jj) Gp[jj] = f2_make(Gs[2 * jj], Gs[2 * jj + 1]);
             }
         }
     }
