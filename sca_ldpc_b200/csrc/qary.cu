@@ -42,6 +42,7 @@ struct scaldpc_qary {
     int wmax = 0;      // max DP table width over the checks
     int num_sms = 148;
     int fast_sw = 0;   // >0: every row is SW B-variables + 1 sum-variable with BSUM == SW*B and a template exists
+    int vn_reg_d = 0;  // >0: every B-variable has exactly this degree and a register-resident k_vn_reg exists
     // device graph
     int *d_row_ptr = nullptr, *d_col = nullptr, *d_edge_off = nullptr, *d_col_ptr = nullptr;
     int8_t *d_sign = nullptr;
@@ -236,6 +237,15 @@ vn_fn pick_vn(int q)
     }
 }
 
+vn_fn pick_vn_reg(int q, int d)
+{
+#define CASE(Q_, D_) \
+    if (q == Q_ && d == D_) return k_vn_reg<Q_, D_>;
+    CASE(5, 1) CASE(5, 2) CASE(5, 3) CASE(5, 4) CASE(7, 1) CASE(7, 2) CASE(7, 3) CASE(7, 4) CASE(7, 6) CASE(3, 3)
+#undef CASE
+    return nullptr;
+}
+
 size_t generic_smem_bytes(const scaldpc_qary *h, CnGenericArgs *g)
 {
     g->QM = std::max(h->Q, h->QS);
@@ -278,7 +288,7 @@ int launch_cn(scaldpc_qary *h, const QaryDev &p, int tiles, bool first, bool las
 
 int launch_vn(scaldpc_qary *h, const QaryDev &p, int tiles, bool last, cudaStream_t st)
 {
-    vn_fn vn = pick_vn(h->Q);
+    vn_fn vn = h->vn_reg_d ? pick_vn_reg(h->Q, h->vn_reg_d) : pick_vn(h->Q);
     dim3 grid((h->bvars + kVnWarps - 1) / kVnWarps, tiles);
     vn<<<grid, kVnWarps * 32, 0, st>>>(p, last);
     ++h->launches;
@@ -351,6 +361,12 @@ int scaldpc_qary_create(const int8_t *H, int R, int N, int b, int bsum, int dv, 
     h->lmax = g.lmax;
     h->wmax = g.wmax;
     if (g.regular_sw && pick_cn_fast(g.regular_sw, b)) h->fast_sw = g.regular_sw;
+    {  // regular columns (all B-variables of one degree, edges of variable v at csc[v*D ..]): register-resident kernel
+        int d0 = g.bvars > 0 ? g.col_ptr[1] - g.col_ptr[0] : 0;
+        for (int v = 0; v < g.bvars && d0 > 0; ++v)
+            if (g.col_ptr[v + 1] - g.col_ptr[v] != d0) d0 = 0;
+        if (d0 > 0 && pick_vn_reg(g.Q, d0)) h->vn_reg_d = d0;
+    }
     if (!pick_vn(h->Q)) return fail(SCALDPC_ERR_UNSUPPORTED, "no variable-node kernel for Q=%d", h->Q);
     std::vector<int2> csc(g.E);
     for (int e = 0; e < g.E; ++e) csc[e] = make_int2(g.csc[e].off, g.csc[e].sign);

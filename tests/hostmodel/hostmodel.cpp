@@ -105,6 +105,15 @@ vn_fn pick_vn(int q)
     }
 }
 
+vn_fn pick_vn_reg(int q, int d)
+{
+#define CASE(Q_, D_) \
+    if (q == Q_ && d == D_) return k_vn_reg<Q_, D_>;
+    CASE(5, 1) CASE(5, 2) CASE(5, 3) CASE(5, 4) CASE(7, 1) CASE(7, 2) CASE(7, 3) CASE(7, 4) CASE(7, 6) CASE(3, 3)
+#undef CASE
+    return nullptr;
+}
+
 }  // namespace
 
 extern "C" {
@@ -151,6 +160,12 @@ int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
     cn_fast_fn fast = (!exact && !force_generic && g.regular_sw) ? pick_cn_fast(g.regular_sw, b) : nullptr;
     vn_fn vn = pick_vn(g.Q);
     if (!vn) return SCALDPC_ERR_UNSUPPORTED;
+    {  // regular columns: the register-resident kernel, as scaldpc_qary_create chooses it (qary.cu)
+        int d0 = g.bvars > 0 ? g.col_ptr[1] - g.col_ptr[0] : 0;
+        for (int v = 0; v < g.bvars && d0 > 0; ++v)
+            if (g.col_ptr[v + 1] - g.col_ptr[v] != d0) d0 = 0;
+        if (d0 > 0 && !force_generic && pick_vn_reg(g.Q, d0)) vn = pick_vn_reg(g.Q, d0);
+    }
     if (used_fast) *used_fast = fast != nullptr;
     std::vector<float> scratch(generic_scratch_floats(g) * 32);
     scaldpc_host_model_smem = scratch.data();
