@@ -14,6 +14,7 @@
 // (decoder.rs:571).  Graph indices are warp-uniform and shared by all trials (L2 / constant-cache resident).
 #pragma once
 #include <stdint.h>
+#include <string.h>
 #ifdef SCALDPC_HOST_MODEL
 // tests/hostmodel/hostmodel.cpp compiles these kernels with g++ (threads run one after another) so the kernel
 // logic can be checked against the oracle on a machine without a GPU.  TEST ONLY -- never part of libscaldpc.so.
@@ -79,6 +80,7 @@ struct MinAcc {
 };
 
 #include "qary_cn_fast.cuh"
+#include "sc_logf.cuh"
 
 // -----------------------------------------------------------------------------------------------------------
 // Variable-node kernel for the B-variables (decoder.rs:634-658 / decoder_special.rs:566-590).
@@ -437,6 +439,8 @@ __global__ void __launch_bounds__(32 * kTrRows) k_load_priors(const float *__res
     const int pitch = (rpb * q) | 1;  // odd pitch: conflict-free column access
     const int tx = threadIdx.x, ty = threadIdx.y;
     const size_t per_trial = (size_t)rows * q;
+    __shared__ ScLogfTab ltab[16];  // per-lane table index: shared memory, not the constant bank
+    if (ty == 0 && tx < 16) ltab[tx] = sc_logf_tab[tx];
     // coalesced load: thread tx walks the chunk, ty walks trials
     for (int t = ty; t < 32; t += kTrRows) {
         const int trial = tile * 32 + t;
@@ -462,9 +466,8 @@ __global__ void __launch_bounds__(32 * kTrRows) k_load_priors(const float *__res
             if (!have) err = SCALDPC_ERR_NO_MAX;
             else if (!(sum < 1.0f + 0.001f) || !(sum > 1.0f - 0.001f)) err = SCALDPC_ERR_PROB_SUM;
             if (err && tile * 32 + tx < T) atomicMin(status + tile * 32 + tx, err);
-            // (max / p).ln() in f32 (decoder.rs:687).  glibc's logf is correctly rounded in practice; CUDA's logf
-            // is only 1-ulp accurate, so take the fp64 log of the f32 quotient and round once.
-            for (int i = 0; i < q; ++i) v[i] = (float)log((double)__fdiv_rn(mx, v[i]));
+            // (max / p).ln() in f32 (decoder.rs:687): IEEE f32 division, then glibc's logf bit for bit (sc_logf.cuh)
+            for (int i = 0; i < q; ++i) v[i] = sc_logf(__fdiv_rn(mx, v[i]), ltab);
         }
         __syncthreads();
     }

@@ -118,6 +118,12 @@ vn_fn pick_vn_reg(int q, int d)
 
 extern "C" {
 
+// sc_logf (sca_ldpc_b200/csrc/sc_logf.cuh), the device restatement of glibc's logf, evaluated on the host.
+void hostmodel_logf(const float *x, float *y, long n)
+{
+    for (long i = 0; i < n; ++i) y[i] = sc_logf(x[i], sc_logf_tab);
+}
+
 // Full decode of T trials from LLRs through the modelled kernels.  Same argument meaning as
 // scaldpc_qary_decode with SCALDPC_IN_LLR; flags: SCALDPC_CN_EXACT / SCALDPC_CN_GENERIC.
 // Returns 0 or a (negative) status code; *used_fast tells whether k_cn_fast ran.
