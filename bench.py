@@ -203,8 +203,26 @@ def run_ours(args, kind, wl, iters, cfg):
             ok = (hard[:, :bv] == secret).all(1) & (hard[:, bv:] == nssum).all(1)
             return torch.stack((ok.sum(), torch.tensor(T, device=dev)))
 
+        h_out = torch.empty((T, wl.N), dtype=torch.int8).pin_memory().numpy()  # pinned result buffer (D2H target)
+
         def step_host():
-            hard, _, _ = dec.min_sum_batch(h_in[0].numpy(), h_in[1].numpy(), want_posterior=False)
+            hard, _, _ = dec.min_sum_batch(h_in[0].numpy(), h_in[1].numpy(), want_posterior=False, out=h_out)
+            return hard
+
+        # the same trials as oracle observations: row indices + prior tables instead of vectors
+        ob = wl.generate_observed(T, seed=seed)
+        h_obs = [torch.from_numpy(ob.obs.view(np.int16)).pin_memory(), torch.from_numpy(ob.obs_sum.view(np.int16)).pin_memory()]
+        d_obs = [t.to(dev) for t in h_obs]
+        d_tab = [torch.from_numpy(wl.table).to(dev), torch.from_numpy(wl.table_sum).to(dev)]
+
+        def step_dev_obs():
+            hard, _, _ = dec.min_sum_observed(d_tab[0], d_obs[0], d_tab[1], d_obs[1])
+            ok = (hard[:, :bv] == secret).all(1) & (hard[:, bv:] == nssum).all(1)
+            return torch.stack((ok.sum(), torch.tensor(T, device=dev)))
+
+        def step_host_obs():
+            hard, _, _ = dec.min_sum_observed(wl.table, h_obs[0].numpy().view(np.uint16), wl.table_sum,
+                                              h_obs[1].numpy().view(np.uint16), out=h_out)
             return hard
 
         h2d = sum(t.numel() * t.element_size() for t in h_in)
@@ -231,8 +249,10 @@ def run_ours(args, kind, wl, iters, cfg):
             ok = (out["decoding"][:, : wl.N] == truth).all(1)
             return torch.stack((ok.sum(), torch.tensor(T, device=dev)))
 
+        h_out = torch.empty((T, wl.n), dtype=torch.uint8).pin_memory().numpy()  # pinned result buffer (D2H target)
+
         def step_host():
-            return dec.decode_batch(h_in[0].numpy())["decoding"]
+            return dec.decode_batch(h_in[0].numpy(), out=h_out)["decoding"]
 
         h2d = T * wl.m
         d2h = T * wl.n
@@ -288,6 +308,39 @@ def run_ours(args, kind, wl, iters, cfg):
         dist.all_reduce(dt, op=dist.ReduceOp.MAX)
     e2e_value = world * T * args.steps / float(dt.item())
 
+    # ---- the same trials fed as oracle observations (q-ary only): device-resident and host-buffer throughput
+    observed = None
+    if kind == "qary":
+        for _ in range(3):
+            c_obs = step_dev_obs()
+        sync_all()
+        e0.record()
+        for _ in range(args.steps):
+            c_obs = step_dev_obs()
+        e1.record()
+        sync_all()
+        ms_obs = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        for _ in range(2):
+            step_host_obs()
+        sync_all()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step_host_obs()
+        torch.cuda.synchronize()
+        dt_obs = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms_obs, op=dist.ReduceOp.MAX)
+            dist.all_reduce(dt_obs, op=dist.ReduceOp.MAX)
+        observed = {
+            "api": "scaldpc_qary_decode_observed: uint16 row indices into the oracle's posterior tables instead of "
+                   "prior vectors (SURVEY.md 8f.1); results bit-identical to the prior-vector API",
+            "value": world * T * args.steps / (float(ms_obs.item()) * 1e-3), "unit": "trials/s",
+            "e2e": {"value": world * T * args.steps / float(dt_obs.item()), "unit": "trials/s",
+                    "h2d_bytes_per_step": sum(t.numel() * t.element_size() for t in h_obs) + wl.table.nbytes + wl.table_sum.nbytes,
+                    "d2h_bytes_per_step": T * wl.N},
+            "success_rate": int(c_obs[0]) / max(1, int(c_obs[1])),
+        }
+
     # ---- roofline of the dominant kernel (rank 0, N=1 semantics: one GPU's kernel against one GPU's peak)
     line = None
     if rank == 0:
@@ -342,6 +395,7 @@ def run_ours(args, kind, wl, iters, cfg):
             "clocks": clk,
             "e2e": {"value": e2e_value, "unit": "trials/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches),
+            **({"observed": observed} if observed else {}),
             **({"compactions_last_step": dec.last_run()[1], "iterations_launched_last_step": dec.last_run()[0]}
                if kind == "bp" else {}),
             "roofline": roofline,

@@ -98,6 +98,28 @@ int scaldpc_qary_set_max_iter(scaldpc_qary *h, int max_iter);
 int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in_sum, int8_t *hard, float *post,
                         float *post_sum, int32_t *status, unsigned flags, void *stream);
 
+/*
+ * scaldpc_qary_decode_observed -- the same decode fed by ORACLE OBSERVATIONS instead of prior vectors.
+ * Replaces the reference-side composition that produces min_sum's arguments for every trial:
+ *   max_likelihood.s_distribution_from_hard_y (simulate/max_likelihood.py:87-105)  posterior of a value given the
+ *                                                                                  observed oracle bits y
+ *   kyber.get_channel_probabilities           (simulate/kyber.py:362-376)          packing into channel_output[_sum]
+ * followed by pydecoder.rs:125-145 min_sum.  The posterior depends only on y, so a batch of priors is a table with one
+ * row per bit pattern plus one row index per (trial, variable); into_llr (decoder.rs:668-692) runs once per table row
+ * and 2 bytes per variable instead of 4*Q cross PCIe / are read from HBM.
+ *   table      n_rows x Q        float32: table[y] = Pr[S = . | Y = y] (LLRs with SCALDPC_IN_LLR); 1 <= n_rows <= 65535
+ *   table_sum  n_rows_sum x QS   float32, special decoder only (already REVERSED as kyber.py:374-375 does)
+ *   obs        T x BVARS         uint16 row index of every B-variable
+ *   obs_sum    T x R             uint16 row index of every sum-variable (special decoder only, else NULL)
+ * Outputs, flags, stream and return value as scaldpc_qary_decode; with SCALDPC_DEVICE_PTRS the tables are device
+ * pointers too.  A row index >= n_rows gives that trial the status SCALDPC_ERR_ARG; a table row that violates
+ * into_llr's checks gives every trial that uses it SCALDPC_ERR_PROB_SUM / SCALDPC_ERR_NO_MAX.
+ * Results are bit-identical to scaldpc_qary_decode on the expanded priors table[obs].
+ */
+int scaldpc_qary_decode_observed(scaldpc_qary *h, int T, const float *table, int n_rows, const float *table_sum,
+                                 int n_rows_sum, const uint16_t *obs, const uint16_t *obs_sum, int8_t *hard, float *post,
+                                 float *post_sum, int32_t *status, unsigned flags, void *stream);
+
 /* Kernels launched by this handle so far (for bench.py's "gpu_launches") and device time is NOT tracked
  * here -- callers time with CUDA events on `stream`. */
 long long scaldpc_qary_launch_count(const scaldpc_qary *h);

@@ -55,12 +55,18 @@ struct scaldpc_qary {
     int *d_status = nullptr;
     // staging for host-pointer calls: the batch is cut into chunks and pipelined (H2D of chunk i+1 and D2H of chunk
     // i-1 overlap the decode of chunk i), so every staging buffer exists twice
-    size_t cap_stage_T = 0;  // trials per staging buffer
+    size_t cap_stage_T = 0;  // trials per output staging buffer
+    size_t cap_in_T = 0;     // trials per prior-vector input staging buffer
     size_t cap_status_T = 0;
     float *d_in[2] = {nullptr, nullptr}, *d_in_sum[2] = {nullptr, nullptr};
     float *d_opost[2] = {nullptr, nullptr}, *d_opost_sum[2] = {nullptr, nullptr};
     int8_t *d_ohard[2] = {nullptr, nullptr};
     int *d_status_all = nullptr;
+    // observation-indexed priors (scaldpc_qary_decode_observed): index staging + LLR tables
+    size_t cap_obs_T = 0, cap_tab = 0, cap_tab_sum = 0;
+    uint16_t *d_obs[2] = {nullptr, nullptr}, *d_obs_sum[2] = {nullptr, nullptr};
+    float *d_tab_in = nullptr, *d_tab_sum_in = nullptr, *d_tab_llr = nullptr, *d_tab_sum_llr = nullptr;
+    int *d_tab_st = nullptr, *d_tab_sum_st = nullptr;
     cudaStream_t s_in = nullptr, s_out = nullptr;
     cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
     std::mutex mu;
@@ -105,6 +111,25 @@ void free_stage(scaldpc_qary *h)
         h->d_ohard[i] = nullptr;
     }
     h->cap_stage_T = 0;
+    h->cap_in_T = 0;
+}
+
+void free_observed(scaldpc_qary *h)
+{
+    for (int i = 0; i < 2; ++i) {
+        cudaFree(h->d_obs[i]);
+        cudaFree(h->d_obs_sum[i]);
+        h->d_obs[i] = h->d_obs_sum[i] = nullptr;
+    }
+    cudaFree(h->d_tab_in);
+    cudaFree(h->d_tab_sum_in);
+    cudaFree(h->d_tab_llr);
+    cudaFree(h->d_tab_sum_llr);
+    cudaFree(h->d_tab_st);
+    cudaFree(h->d_tab_sum_st);
+    h->d_tab_in = h->d_tab_sum_in = h->d_tab_llr = h->d_tab_sum_llr = nullptr;
+    h->d_tab_st = h->d_tab_sum_st = nullptr;
+    h->cap_obs_T = h->cap_tab = h->cap_tab_sum = 0;
 }
 
 int ensure_workspace(scaldpc_qary *h, int tiles, bool want_post)
@@ -128,7 +153,8 @@ int ensure_workspace(scaldpc_qary *h, int tiles, bool want_post)
     return 0;
 }
 
-int ensure_stage(scaldpc_qary *h, size_t chunk, size_t T, bool want_post)
+// Streams / events of the chunked host pipeline, the whole-batch status array and the per-chunk OUTPUT staging.
+int ensure_pipeline(scaldpc_qary *h, size_t chunk, size_t T, bool want_post)
 {
     if (!h->s_in) {
         SCALDPC_CUDA(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
@@ -148,10 +174,15 @@ int ensure_stage(scaldpc_qary *h, size_t chunk, size_t T, bool want_post)
     if (chunk <= h->cap_stage_T && (!want_post || h->d_opost[0])) return 0;
     const size_t t = std::max(chunk, h->cap_stage_T);
     const bool post = want_post || h->d_opost[0];
-    free_stage(h);
     for (int i = 0; i < 2; ++i) {
-        SCALDPC_CUDA(cudaMalloc((void **)&h->d_in[i], t * h->SL * sizeof(float)));
-        SCALDPC_CUDA(cudaMalloc((void **)&h->d_in_sum[i], std::max<size_t>(1, t * h->SLS) * sizeof(float)));
+        cudaFree(h->d_opost[i]);
+        cudaFree(h->d_opost_sum[i]);
+        cudaFree(h->d_ohard[i]);
+        h->d_opost[i] = h->d_opost_sum[i] = nullptr;
+        h->d_ohard[i] = nullptr;
+    }
+    h->cap_stage_T = 0;
+    for (int i = 0; i < 2; ++i) {
         SCALDPC_CUDA(cudaMalloc((void **)&h->d_ohard[i], t * h->N));
         if (post) {
             SCALDPC_CUDA(cudaMalloc((void **)&h->d_opost[i], t * h->SL * sizeof(float)));
@@ -159,6 +190,72 @@ int ensure_stage(scaldpc_qary *h, size_t chunk, size_t T, bool want_post)
         }
     }
     h->cap_stage_T = t;
+    return 0;
+}
+
+// Per-chunk INPUT staging of prior vectors (scaldpc_qary_decode with host pointers).
+int ensure_stage_priors(scaldpc_qary *h, size_t chunk)
+{
+    if (chunk <= h->cap_in_T) return 0;
+    for (int i = 0; i < 2; ++i) {
+        cudaFree(h->d_in[i]);
+        cudaFree(h->d_in_sum[i]);
+        h->d_in[i] = h->d_in_sum[i] = nullptr;
+    }
+    h->cap_in_T = 0;
+    for (int i = 0; i < 2; ++i) {
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_in[i], chunk * h->SL * sizeof(float)));
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_in_sum[i], std::max<size_t>(1, chunk * h->SLS) * sizeof(float)));
+    }
+    h->cap_in_T = chunk;
+    return 0;
+}
+
+// Per-chunk INPUT staging of observation indices (scaldpc_qary_decode_observed with host pointers).
+int ensure_stage_observed(scaldpc_qary *h, size_t chunk)
+{
+    if (chunk <= h->cap_obs_T) return 0;
+    for (int i = 0; i < 2; ++i) {
+        cudaFree(h->d_obs[i]);
+        cudaFree(h->d_obs_sum[i]);
+        h->d_obs[i] = h->d_obs_sum[i] = nullptr;
+    }
+    h->cap_obs_T = 0;
+    for (int i = 0; i < 2; ++i) {
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_obs[i], chunk * h->bvars * sizeof(uint16_t)));
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_obs_sum[i], std::max<size_t>(1, chunk * h->R) * sizeof(uint16_t)));
+    }
+    h->cap_obs_T = chunk;
+    return 0;
+}
+
+// Device copies of the prior tables and their LLR form.
+int ensure_tables(scaldpc_qary *h, size_t n_rows, size_t n_rows_sum)
+{
+    if (n_rows > h->cap_tab) {
+        cudaFree(h->d_tab_in);
+        cudaFree(h->d_tab_llr);
+        cudaFree(h->d_tab_st);
+        h->d_tab_in = h->d_tab_llr = nullptr;
+        h->d_tab_st = nullptr;
+        h->cap_tab = 0;
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_tab_in, n_rows * h->Q * sizeof(float)));
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_tab_llr, n_rows * h->Q * sizeof(float)));
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_tab_st, n_rows * sizeof(int)));
+        h->cap_tab = n_rows;
+    }
+    if (n_rows_sum > h->cap_tab_sum) {
+        cudaFree(h->d_tab_sum_in);
+        cudaFree(h->d_tab_sum_llr);
+        cudaFree(h->d_tab_sum_st);
+        h->d_tab_sum_in = h->d_tab_sum_llr = nullptr;
+        h->d_tab_sum_st = nullptr;
+        h->cap_tab_sum = 0;
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_tab_sum_in, n_rows_sum * h->QS * sizeof(float)));
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_tab_sum_llr, n_rows_sum * h->QS * sizeof(float)));
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_tab_sum_st, n_rows_sum * sizeof(int)));
+        h->cap_tab_sum = n_rows_sum;
+    }
     return 0;
 }
 
@@ -401,6 +498,7 @@ void scaldpc_qary_destroy(scaldpc_qary *h)
     cudaSetDevice(h->device);
     free_workspace(h);
     free_stage(h);
+    free_observed(h);
     cudaFree(h->d_status_all);
     if (h->s_in) cudaStreamDestroy(h->s_in);
     if (h->s_out) cudaStreamDestroy(h->s_out);
@@ -441,9 +539,18 @@ int scaldpc_qary_set_max_iter(scaldpc_qary *h, int max_iter)
 
 long long scaldpc_qary_launch_count(const scaldpc_qary *h) { return h ? h->launches : 0; }
 
+// Where the priors of a batch come from.  Vectors: in / in_sum as scaldpc_qary_decode documents them.  Observed:
+// row indices into prior tables (scaldpc_qary_decode_observed); d_tab* are the handle's device LLR tables.
+struct PriorSrc {
+    bool observed = false;
+    const float *in = nullptr, *in_sum = nullptr;
+    const uint16_t *obs = nullptr, *obs_sum = nullptr;
+    int n_rows = 0, n_rows_sum = 0;
+};
+
 // The device pipeline of one batch: priors (device, row-major) -> hard decisions (device, row-major), all on `st`.
-static int decode_on_device(scaldpc_qary *h, int T, const float *din, const float *din_sum, int8_t *dhard, float *dpost,
-                            float *dpost_sum, unsigned flags, cudaStream_t st)
+static int decode_on_device(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *dhard, float *dpost, float *dpost_sum,
+                            unsigned flags, cudaStream_t st)
 {
     const bool special = h->BSUM > 0;
     const bool want_post = dpost != nullptr || dpost_sum != nullptr;
@@ -451,8 +558,20 @@ static int decode_on_device(scaldpc_qary *h, int T, const float *din, const floa
     const int tiles = (T + 31) / 32;
     int rc;
     SCALDPC_CUDA(cudaMemsetAsync(h->d_status, 0, (size_t)tiles * 32 * sizeof(int), st));
-    if ((rc = load_priors(h, din, h->d_llr, T, tiles, h->bvars, h->Q, is_llr, st))) return rc;
-    if (special && (rc = load_priors(h, din_sum, h->d_llr_sum, T, tiles, h->R, h->QS, is_llr, st))) return rc;
+    if (src.observed) {
+        k_load_observed<<<dim3((h->bvars + kObsRows - 1) / kObsRows, tiles), 256, 0, st>>>(
+            src.obs, h->d_tab_llr, h->d_tab_st, h->d_llr, T, h->bvars, h->Q, src.n_rows, h->d_status);
+        ++h->launches;
+        if (special) {
+            k_load_observed<<<dim3((h->R + kObsRows - 1) / kObsRows, tiles), 256, 0, st>>>(
+                src.obs_sum, h->d_tab_sum_llr, h->d_tab_sum_st, h->d_llr_sum, T, h->R, h->QS, src.n_rows_sum, h->d_status);
+            ++h->launches;
+        }
+        SCALDPC_CUDA(cudaGetLastError());
+    } else {
+        if ((rc = load_priors(h, src.in, h->d_llr, T, tiles, h->bvars, h->Q, is_llr, st))) return rc;
+        if (special && (rc = load_priors(h, src.in_sum, h->d_llr_sum, T, tiles, h->R, h->QS, is_llr, st))) return rc;
+    }
 
     const QaryDev p = dev_view(h, want_post);
     const int iters = std::max(1, h->max_iter);  // decoder.rs:575-663: `it` starts at 1, exit when it >= max_iter
@@ -475,26 +594,20 @@ static int decode_on_device(scaldpc_qary *h, int T, const float *din, const floa
     return 0;
 }
 
-int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in_sum, int8_t *hard, float *post,
-                        float *post_sum, int32_t *status, unsigned flags, void *stream)
+// Shared body of scaldpc_qary_decode / scaldpc_qary_decode_observed.  `src` holds the caller's pointers (host or
+// device); tables (observed mode) are already resident in the handle as LLRs.
+static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *hard, float *post, float *post_sum,
+                        int32_t *status, unsigned flags, cudaStream_t st)
 {
-    if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
-    if (T < 0) return fail(SCALDPC_ERR_ARG, "T < 0");
-    if (T == 0) return 0;
     const bool special = h->BSUM > 0;
-    if (!in || !hard || (special && !in_sum)) return fail(SCALDPC_ERR_ARG, "NULL input/output pointer");
     const bool want_post = post != nullptr || post_sum != nullptr;
     const bool dev_ptrs = flags & SCALDPC_DEVICE_PTRS;
-    cudaStream_t st = (cudaStream_t)stream;
-
-    std::lock_guard<std::mutex> lk(h->mu);
-    SCALDPC_CUDA(cudaSetDevice(h->device));
     int rc;
 
     if (dev_ptrs) {  // asynchronous on `st`, one pass over the whole batch
         const int tiles = (T + 31) / 32;
         if ((rc = ensure_workspace(h, tiles, want_post))) return rc;
-        if ((rc = decode_on_device(h, T, in, in_sum, hard, post, post_sum, flags, st))) return rc;
+        if ((rc = decode_on_device(h, T, src, hard, post, post_sum, flags, st))) return rc;
         if (status) SCALDPC_CUDA(cudaMemcpyAsync(status, h->d_status, (size_t)T * sizeof(int), cudaMemcpyDeviceToDevice, st));
         return 0;
     }
@@ -507,17 +620,26 @@ int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in
     chunk = (chunk + 31) / 32 * 32;
     const int nchunks = (T + chunk - 1) / chunk;
     if ((rc = ensure_workspace(h, chunk / 32, want_post))) return rc;
-    if ((rc = ensure_stage(h, (size_t)chunk, (size_t)T, want_post))) return rc;
+    if ((rc = ensure_pipeline(h, (size_t)chunk, (size_t)T, want_post))) return rc;
+    if ((rc = src.observed ? ensure_stage_observed(h, (size_t)chunk) : ensure_stage_priors(h, (size_t)chunk))) return rc;
     // Host-side enqueue order per chunk c: H2D(c+1), decode(c), D2H(c-1).  A D2H into pageable memory blocks the
     // host until decode(c-1) is done; by then decode(c) and H2D(c+1) are already queued, so the device never idles.
     auto h2d = [&](int c) -> int {
         const int b = c & 1, t0 = c * chunk, tc = std::min(chunk, T - t0);
-        if (c >= 2) SCALDPC_CUDA(cudaStreamWaitEvent(h->s_in, h->ev_comp[b], 0));  // decode(c-2) has consumed d_in[b]
-        SCALDPC_CUDA(cudaMemcpyAsync(h->d_in[b], in + (size_t)t0 * h->SL, (size_t)tc * h->SL * sizeof(float),
-                                     cudaMemcpyHostToDevice, h->s_in));
-        if (special)
-            SCALDPC_CUDA(cudaMemcpyAsync(h->d_in_sum[b], in_sum + (size_t)t0 * h->SLS, (size_t)tc * h->SLS * sizeof(float),
+        if (c >= 2) SCALDPC_CUDA(cudaStreamWaitEvent(h->s_in, h->ev_comp[b], 0));  // decode(c-2) has consumed the buffer
+        if (src.observed) {
+            SCALDPC_CUDA(cudaMemcpyAsync(h->d_obs[b], src.obs + (size_t)t0 * h->bvars, (size_t)tc * h->bvars * sizeof(uint16_t),
                                          cudaMemcpyHostToDevice, h->s_in));
+            if (special)
+                SCALDPC_CUDA(cudaMemcpyAsync(h->d_obs_sum[b], src.obs_sum + (size_t)t0 * h->R,
+                                             (size_t)tc * h->R * sizeof(uint16_t), cudaMemcpyHostToDevice, h->s_in));
+        } else {
+            SCALDPC_CUDA(cudaMemcpyAsync(h->d_in[b], src.in + (size_t)t0 * h->SL, (size_t)tc * h->SL * sizeof(float),
+                                         cudaMemcpyHostToDevice, h->s_in));
+            if (special)
+                SCALDPC_CUDA(cudaMemcpyAsync(h->d_in_sum[b], src.in_sum + (size_t)t0 * h->SLS,
+                                             (size_t)tc * h->SLS * sizeof(float), cudaMemcpyHostToDevice, h->s_in));
+        }
         SCALDPC_CUDA(cudaEventRecord(h->ev_in[b], h->s_in));
         return 0;
     };
@@ -540,7 +662,12 @@ int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in
         if (c + 1 < nchunks && (rc = h2d(c + 1))) return rc;
         SCALDPC_CUDA(cudaStreamWaitEvent(st, h->ev_in[b], 0));
         if (c >= 2) SCALDPC_CUDA(cudaStreamWaitEvent(st, h->ev_out[b], 0));  // d_ohard[b] of chunk c-2 has been copied out
-        if ((rc = decode_on_device(h, tc, h->d_in[b], h->d_in_sum[b], h->d_ohard[b], post ? h->d_opost[b] : nullptr,
+        PriorSrc dsrc = src;
+        dsrc.in = h->d_in[b];
+        dsrc.in_sum = h->d_in_sum[b];
+        dsrc.obs = h->d_obs[b];
+        dsrc.obs_sum = h->d_obs_sum[b];
+        if ((rc = decode_on_device(h, tc, dsrc, h->d_ohard[b], post ? h->d_opost[b] : nullptr,
                                    post_sum ? h->d_opost_sum[b] : nullptr, flags, st)))
             return rc;
         SCALDPC_CUDA(cudaMemcpyAsync(h->d_status_all + t0, h->d_status, (size_t)tc * sizeof(int), cudaMemcpyDeviceToDevice, st));
@@ -558,7 +685,63 @@ int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in
     if (worst == SCALDPC_ERR_PROB_SUM) return fail(worst, "a prior row does not sum to 1 +- 0.001 (decoder.rs:683-684)");
     if (worst == SCALDPC_ERR_NO_MAX) return fail(worst, "No maximum probability found (decoder.rs:680)");
     if (worst == SCALDPC_ERR_NO_CONFIG) return fail(worst, "a check has no valid configuration (decoder.rs:618)");
+    if (worst == SCALDPC_ERR_ARG) return fail(worst, "an observation index is outside its prior table");
     return 0;
+}
+
+int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in_sum, int8_t *hard, float *post,
+                        float *post_sum, int32_t *status, unsigned flags, void *stream)
+{
+    if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
+    if (T < 0) return fail(SCALDPC_ERR_ARG, "T < 0");
+    if (T == 0) return 0;
+    const bool special = h->BSUM > 0;
+    if (!in || !hard || (special && !in_sum)) return fail(SCALDPC_ERR_ARG, "NULL input/output pointer");
+    std::lock_guard<std::mutex> lk(h->mu);
+    SCALDPC_CUDA(cudaSetDevice(h->device));
+    PriorSrc src;
+    src.in = in;
+    src.in_sum = in_sum;
+    return decode_batch(h, T, src, hard, post, post_sum, status, flags, (cudaStream_t)stream);
+}
+
+int scaldpc_qary_decode_observed(scaldpc_qary *h, int T, const float *table, int n_rows, const float *table_sum,
+                                 int n_rows_sum, const uint16_t *obs, const uint16_t *obs_sum, int8_t *hard, float *post,
+                                 float *post_sum, int32_t *status, unsigned flags, void *stream)
+{
+    if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
+    if (T < 0) return fail(SCALDPC_ERR_ARG, "T < 0");
+    const bool special = h->BSUM > 0;
+    if (!table || n_rows <= 0 || n_rows > 65535 || (special && (!table_sum || n_rows_sum <= 0 || n_rows_sum > 65535)))
+        return fail(SCALDPC_ERR_ARG, "prior tables must have 1 .. 65535 rows");
+    if (T == 0) return 0;
+    if (!obs || !hard || (special && !obs_sum)) return fail(SCALDPC_ERR_ARG, "NULL input/output pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    std::lock_guard<std::mutex> lk(h->mu);
+    SCALDPC_CUDA(cudaSetDevice(h->device));
+    int rc;
+    if ((rc = ensure_tables(h, (size_t)n_rows, special ? (size_t)n_rows_sum : 0))) return rc;
+    // tables -> device LLR tables (into_llr once per row, decoder.rs:668-692), on the compute stream
+    const bool dev_ptrs = flags & SCALDPC_DEVICE_PTRS;
+    const bool is_llr = flags & SCALDPC_IN_LLR;
+    const cudaMemcpyKind kind = dev_ptrs ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    SCALDPC_CUDA(cudaMemcpyAsync(h->d_tab_in, table, (size_t)n_rows * h->Q * sizeof(float), kind, st));
+    k_table_llr<<<(n_rows + 127) / 128, 128, 0, st>>>(h->d_tab_in, h->d_tab_llr, h->d_tab_st, n_rows, h->Q, is_llr);
+    ++h->launches;
+    if (special) {
+        SCALDPC_CUDA(cudaMemcpyAsync(h->d_tab_sum_in, table_sum, (size_t)n_rows_sum * h->QS * sizeof(float), kind, st));
+        k_table_llr<<<(n_rows_sum + 127) / 128, 128, 0, st>>>(h->d_tab_sum_in, h->d_tab_sum_llr, h->d_tab_sum_st, n_rows_sum,
+                                                              h->QS, is_llr);
+        ++h->launches;
+    }
+    SCALDPC_CUDA(cudaGetLastError());
+    PriorSrc src;
+    src.observed = true;
+    src.obs = obs;
+    src.obs_sum = obs_sum;
+    src.n_rows = n_rows;
+    src.n_rows_sum = n_rows_sum;
+    return decode_batch(h, T, src, hard, post, post_sum, status, flags, st);
 }
 
 int scaldpc_qary_time_kernel(scaldpc_qary *h, int which, int T, unsigned flags, int reps, void *stream, float *avg_ms)

@@ -426,6 +426,28 @@ __global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGene
 // -----------------------------------------------------------------------------------------------------------
 constexpr int kTrRows = 8;  // threads.y
 
+// into_llr of one prior row, in place (decoder.rs:668-692): f32 sum in index order (assert 1 +- 0.001, :683-684),
+// NaN-ignoring maximum (:671-680), llr[i] = ln(max / p[i]) (:687) with an IEEE f32 division and glibc's logf bit for
+// bit (sc_logf.cuh).  Returns 0 or the SCALDPC_ERR_* the reference panics with.
+__device__ __forceinline__ int into_llr_row(float *v, int q, const ScLogfTab *ltab)
+{
+    float sum = 0.0f, mx = 0.0f;
+    bool have = false;
+    for (int i = 0; i < q; ++i) {
+        const float x = v[i];
+        sum += x;
+        if (x == x && (!have || x > mx)) {
+            mx = x;
+            have = true;
+        }
+    }
+    int err = 0;
+    if (!have) err = SCALDPC_ERR_NO_MAX;
+    else if (!(sum < 1.0f + 0.001f) || !(sum > 1.0f - 0.001f)) err = SCALDPC_ERR_PROB_SUM;
+    for (int i = 0; i < q; ++i) v[i] = sc_logf(__fdiv_rn(mx, v[i]), ltab);
+    return err;
+}
+
 // in: [T][rows*q] probabilities or LLRs; out: [tile][rows*q][32].  One CTA = one tile x `rpb` rows.
 __global__ void __launch_bounds__(32 * kTrRows) k_load_priors(const float *__restrict__ in, float *__restrict__ out,
                                                               int T, int rows, int q, int rpb, int is_llr,
@@ -451,28 +473,63 @@ __global__ void __launch_bounds__(32 * kTrRows) k_load_priors(const float *__res
     if (!is_llr) {
         // thread (tx = trial, ty = row): sum / max / ln(max / p)
         for (int r = ty; r < nr; r += kTrRows) {
-            float *v = sm + tx * pitch + r * q;
-            float sum = 0.0f, mx = 0.0f;
-            bool have = false;
-            for (int i = 0; i < q; ++i) {
-                const float x = v[i];
-                sum += x;
-                if (x == x && (!have || x > mx)) {
-                    mx = x;
-                    have = true;
-                }
-            }
-            int err = 0;
-            if (!have) err = SCALDPC_ERR_NO_MAX;
-            else if (!(sum < 1.0f + 0.001f) || !(sum > 1.0f - 0.001f)) err = SCALDPC_ERR_PROB_SUM;
+            const int err = into_llr_row(sm + tx * pitch + r * q, q, ltab);
             if (err && tile * 32 + tx < T) atomicMin(status + tile * 32 + tx, err);
-            // (max / p).ln() in f32 (decoder.rs:687): IEEE f32 division, then glibc's logf bit for bit (sc_logf.cuh)
-            for (int i = 0; i < q; ++i) v[i] = sc_logf(__fdiv_rn(mx, v[i]), ltab);
         }
         __syncthreads();
     }
     float *o = out + ((size_t)tile * per_trial + (size_t)r0 * q) * 32;
     for (int i = ty; i < n; i += kTrRows) o[(size_t)i * 32 + tx] = sm[tx * pitch + i];
+}
+
+// ---- priors given as ORACLE OBSERVATIONS -----------------------------------------------------
+// The prior of a variable depends only on the bit pattern y the side-channel oracle returned for it
+// (max_likelihood.py:87-105 s_distribution_from_hard_y; kyber.py:362-376 get_channel_probabilities), so a batch of
+// priors is a small table [n_rows][q] plus one row index per (trial, variable): 2 bytes instead of 4q cross PCIe /
+// are read from HBM, and into_llr runs once per table row instead of once per trial.
+
+// into_llr of the table rows (one thread per row; rows are tiny and the kernel runs once per decode call).
+__global__ void __launch_bounds__(128) k_table_llr(const float *__restrict__ tab, float *__restrict__ out,
+                                                   int *__restrict__ row_status, int n_rows, int q, int is_llr)
+{
+    const int row = blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= n_rows) return;
+    float *v = out + (size_t)row * q;
+    for (int i = 0; i < q; ++i) v[i] = tab[(size_t)row * q + i];
+    row_status[row] = is_llr ? 0 : into_llr_row(v, q, sc_logf_tab);
+}
+
+constexpr int kObsRows = 64;  // variables per CTA of k_load_observed
+
+// obs [T][rows] u16 row indices -> out [tile][rows*q][32] channel LLRs.  One CTA = one tile x kObsRows variables:
+// coalesced load of the index block into shared memory, then one warp per variable (lane = trial) copies its table
+// row (L1/L2-resident) into the tile layout with coalesced 128-byte stores.  Per-trial status: the row's into_llr
+// status, SCALDPC_ERR_ARG for an index >= n_rows.
+__global__ void __launch_bounds__(256) k_load_observed(const uint16_t *__restrict__ obs, const float *__restrict__ tab,
+                                                       const int *__restrict__ row_status, float *__restrict__ out, int T,
+                                                       int rows, int q, int n_rows, int *__restrict__ status)
+{
+    __shared__ uint16_t so[32][kObsRows + 2];  // pitch 33 words: conflict-free column reads
+    const int tile = blockIdx.y, r0 = blockIdx.x * kObsRows;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int t = ty; t < 32; t += 8) {
+        const int trial = tile * 32 + t;
+        for (int c = tx; c < kObsRows; c += 32)
+            so[t][c] = (trial < T && r0 + c < rows) ? obs[(size_t)trial * rows + r0 + c] : (uint16_t)0xffff;
+    }
+    __syncthreads();
+    const bool real = tile * 32 + tx < T;
+    for (int c = ty; c < kObsRows && r0 + c < rows; c += 8) {
+        const int idx = so[tx][c];
+        const bool ok = real && idx < n_rows;
+        if (real) {
+            const int err = idx < n_rows ? row_status[idx] : SCALDPC_ERR_ARG;
+            if (err) atomicMin(status + tile * 32 + tx, err);
+        }
+        const float *src = tab + (size_t)(ok ? idx : 0) * q;
+        float *o = out + ((size_t)tile * rows + r0 + c) * q * 32 + tx;
+        for (int i = 0; i < q; ++i) o[(size_t)i * 32] = ok ? src[i] : 0.0f;
+    }
 }
 
 // tile layout -> row-major.  src [tile][n][32] -> dst [T][n]

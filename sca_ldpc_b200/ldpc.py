@@ -112,10 +112,12 @@ class bp_decoder:
         return dec.astype(int)
 
     # ---- batched fast path -------------------------------------------------------------------------------
-    def decode_batch(self, syndromes, channel_probs=None, *, want_llr=False, early_stop=True, compact=True):
+    def decode_batch(self, syndromes, channel_probs=None, *, want_llr=False, early_stop=True, compact=True, out=None):
         """syndromes (T, m) uint8; channel_probs None (the constructor's), (n,) or (T, n) float64.
         numpy in -> numpy out; torch CUDA uint8 tensor in -> torch CUDA tensors out.
-        Returns dict(decoding (T,n) uint8, log_prob_ratios (T,n) float32 or None, iters (T,), converged (T,))."""
+        Returns dict(decoding (T,n) uint8, log_prob_ratios (T,n) float32 or None, iters (T,), converged (T,)).
+        out: optional preallocated C-contiguous uint8 (T, n) numpy array for `decoding` (host path only), e.g. a view
+        of pinned memory so the device-to-host copy of the T*n decision bytes is a true asynchronous DMA."""
         flags = 0 if early_stop else _lib.BP_NO_EARLY_STOP
         if not compact:
             flags |= _lib.BP_NO_COMPACT
@@ -132,7 +134,13 @@ class bp_decoder:
             flags |= _lib.BP_PROBS_PER_TRIAL
         elif cp.shape != (self.n,):
             raise ValueError(f"channel_probs must have length {self.n}")
-        dec = np.empty((T, self.n), np.uint8)
+        if out is None:
+            dec = np.empty((T, self.n), np.uint8)
+        else:
+            dec = out
+            if not (isinstance(dec, np.ndarray) and dec.dtype == np.uint8 and dec.shape == (T, self.n)
+                    and dec.flags.c_contiguous and dec.flags.writeable):
+                raise ValueError(f"out must be a writable C-contiguous uint8 array of shape ({T}, {self.n})")
         llr = np.empty((T, self.n), np.float32) if want_llr else None
         iters = np.empty(T, np.int32)
         conv = np.empty(T, np.int32)

@@ -94,7 +94,7 @@ class QaryDecoder:
     # batched fast path: T independent decodes resident on the device
     # ------------------------------------------------------------------------------------------------------
     def min_sum_batch(self, priors, priors_sum=None, *, llr=False, want_posterior=True, exact=False,
-                      generic=False, want_status=False):
+                      generic=False, want_status=False, out=None):
         """Decode T trials.
 
         priors      (T, bvars, Q)  float32 probabilities (or LLRs with llr=True); numpy array or torch CUDA tensor
@@ -103,6 +103,8 @@ class QaryDecoder:
         [+ status int32 (T,) with want_status=True instead of raising on per-trial input errors].
         numpy in -> numpy out (host buffers, copies inside the call); torch CUDA in -> torch CUDA out
         (asynchronous on the current stream).
+        out: optional preallocated C-contiguous int8 (T, N) numpy array that receives the hard decisions (host
+        path only) -- e.g. a view of pinned memory, so the device-to-host copy is a true asynchronous DMA.
         """
         flags = (_lib.IN_LLR if llr else 0) | (_lib.CN_EXACT if exact else 0) | (_lib.CN_GENERIC if generic else 0)
         on_dev = _is_torch(priors) and priors.is_cuda
@@ -119,7 +121,13 @@ class QaryDecoder:
             xs = np.ascontiguousarray(priors_sum, dtype=np.float32)
             if xs.shape != (T, self.R, self.QS):
                 raise ValueError(f"priors_sum must be (T, {self.R}, {self.QS}), got {xs.shape}")
-        hard = np.empty((T, self.N), np.int8)
+        if out is None:
+            hard = np.empty((T, self.N), np.int8)
+        else:
+            hard = out
+            if not (isinstance(hard, np.ndarray) and hard.dtype == np.int8 and hard.shape == (T, self.N)
+                    and hard.flags.c_contiguous and hard.flags.writeable):
+                raise ValueError(f"out must be a writable C-contiguous int8 array of shape ({T}, {self.N})")
         post = np.empty((T, self.bvars, self.Q), np.float32) if want_posterior else None
         posts = np.empty((T, self.R, self.QS), np.float32) if (want_posterior and self.special) else None
         status = np.zeros(T, np.int32)
@@ -127,6 +135,81 @@ class QaryDecoder:
         with self._lock:
             rc = _lib.lib().scaldpc_qary_decode(self._h, T, p(x), p(xs), p(hard), p(post), p(posts), p(status), flags,
                                                 None)
+        return self._finish(rc, hard, post, posts, status, want_status)
+
+    def min_sum_observed(self, table, obs, table_sum=None, obs_sum=None, *, llr=False, want_posterior=False,
+                         exact=False, generic=False, want_status=False, out=None):
+        """Decode T trials whose priors are rows of small tables (scaldpc_qary_decode_observed): the posterior of a
+        variable given the oracle's bit pattern y is `table[y]` (max_likelihood.py:87-105, kyber.py:362-376), so only
+        the row indices travel.  Bit-identical to min_sum_batch(table[obs], table_sum[obs_sum]).
+
+        table      (n_rows, Q) float32      obs      (T, bvars) uint16
+        table_sum  (n_rows_sum, QS) float32 obs_sum  (T, R) uint16            (special decoder)
+        numpy in -> numpy out; torch CUDA tensors in (obs int16/uint16 storage) -> torch CUDA out.
+        """
+        flags = (_lib.IN_LLR if llr else 0) | (_lib.CN_EXACT if exact else 0) | (_lib.CN_GENERIC if generic else 0)
+        if self.special and (table_sum is None or obs_sum is None):
+            raise TypeError("the special decoder needs table_sum and obs_sum")
+        on_dev = _is_torch(obs) and obs.is_cuda
+        if on_dev:
+            dev = torch.device("cuda", self.device)
+            i16 = (torch.int16, getattr(torch, "uint16", torch.int16))
+
+            def chk(t, shape, dts, name):
+                if t.device != dev or t.dtype not in dts or (shape is not None and tuple(t.shape) != shape):
+                    raise ValueError(f"{name} must be a {dts[0]} tensor of shape {shape} on {dev}")
+                return t.contiguous()
+
+            T = obs.shape[0]
+            obs = chk(obs, (T, self.bvars), i16, "obs")
+            table = chk(table, None, (torch.float32,), "table")
+            n_rows = table.shape[0]
+            n_rows_sum = 0
+            if self.special:
+                obs_sum = chk(obs_sum, (T, self.R), i16, "obs_sum")
+                table_sum = chk(table_sum, None, (torch.float32,), "table_sum")
+                n_rows_sum = table_sum.shape[0]
+            hard = torch.empty((T, self.N), dtype=torch.int8, device=dev)
+            post = torch.empty((T, self.bvars, self.Q), dtype=torch.float32, device=dev) if want_posterior else None
+            posts = (torch.empty((T, self.R, self.QS), dtype=torch.float32, device=dev)
+                     if (want_posterior and self.special) else None)
+            status = torch.zeros(T, dtype=torch.int32, device=dev) if want_status else None
+            p = lambda t: None if t is None else t.data_ptr()  # noqa: E731
+            stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            flags |= _lib.DEVICE_PTRS
+        else:
+            table = np.ascontiguousarray(table, dtype=np.float32)
+            obs = np.ascontiguousarray(obs, dtype=np.uint16)
+            T = obs.shape[0]
+            if table.ndim != 2 or table.shape[1] != self.Q or obs.shape != (T, self.bvars):
+                raise ValueError(f"table must be (n_rows, {self.Q}) and obs (T, {self.bvars})")
+            n_rows, n_rows_sum = table.shape[0], 0
+            if self.special:
+                table_sum = np.ascontiguousarray(table_sum, dtype=np.float32)
+                obs_sum = np.ascontiguousarray(obs_sum, dtype=np.uint16)
+                if table_sum.ndim != 2 or table_sum.shape[1] != self.QS or obs_sum.shape != (T, self.R):
+                    raise ValueError(f"table_sum must be (n_rows_sum, {self.QS}) and obs_sum (T, {self.R})")
+                n_rows_sum = table_sum.shape[0]
+            if out is None:
+                hard = np.empty((T, self.N), np.int8)
+            else:
+                hard = out
+                if not (isinstance(hard, np.ndarray) and hard.dtype == np.int8 and hard.shape == (T, self.N)
+                        and hard.flags.c_contiguous and hard.flags.writeable):
+                    raise ValueError(f"out must be a writable C-contiguous int8 array of shape ({T}, {self.N})")
+            post = np.empty((T, self.bvars, self.Q), np.float32) if want_posterior else None
+            posts = np.empty((T, self.R, self.QS), np.float32) if (want_posterior and self.special) else None
+            status = np.zeros(T, np.int32)
+            p = lambda a: None if a is None else a.ctypes.data  # noqa: E731
+            stream = None
+        with self._lock:
+            rc = _lib.lib().scaldpc_qary_decode_observed(
+                self._h, T, p(table), n_rows, p(table_sum if self.special else None), n_rows_sum, p(obs),
+                p(obs_sum if self.special else None), p(hard), p(post), p(posts), p(status), flags, stream)
+        if rc == _lib.ERR_ARG and T > 0:  # shapes were validated above: a row index outside its table (per trial)
+            if want_status:
+                return hard, post, posts, status
+            raise ValueError(_lib.lib().scaldpc_last_error().decode())
         return self._finish(rc, hard, post, posts, status, want_status)
 
     def _batch_torch(self, x, xs, flags, want_posterior, want_status):

@@ -102,6 +102,14 @@ class KyberBatch:
     ssum: np.ndarray         # (T, R)          int16
 
 
+@dataclass
+class KyberObserved:
+    obs: np.ndarray          # (T, bvars)      uint16    observed bit pattern of every secret coefficient
+    obs_sum: np.ndarray      # (T, R)          uint16    observed bit pattern of every check sum
+    secret: np.ndarray       # (T, bvars)      int8
+    ssum: np.ndarray         # (T, R)          int16
+
+
 class KyberWorkload:
     """One BASELINE.json Kyber configuration: H, code tables, posterior tables; generate(T, seed) draws trials."""
 
@@ -142,8 +150,18 @@ class KyberWorkload:
         ysum = self._observe(rs, ssum, self.coding_sum, self.BSUM)
         return KyberBatch(self.table[y], self.table_sum[ysum], s, ssum)
 
+    def generate_observed(self, T: int, seed=0) -> "KyberObserved":
+        """The same trials as generate(T, seed), as oracle observations: row indices into self.table / self.table_sum
+        instead of the expanded prior vectors (priors == table[obs], priors_sum == table_sum[obs_sum])."""
+        rs = np.random.RandomState(seed)
+        s = sample_secrets(rs, (T, self.bvars), self.eta)
+        ssum = (s.astype(np.int16) @ self.Hs.T).astype(np.int16)
+        y = self._observe(rs, s, self.coding, self.B)
+        ysum = self._observe(rs, ssum, self.coding_sum, self.BSUM)
+        return KyberObserved(y.astype(np.uint16), ysum.astype(np.uint16), s, ssum)
+
     @staticmethod
-    def success(batch: KyberBatch, hard: np.ndarray) -> np.ndarray:
+    def success(batch, hard: np.ndarray) -> np.ndarray:
         """Per-trial success: decoded secret == s and decoded sum-variables == -ssum."""
         bv = batch.secret.shape[1]
         return (hard[:, :bv] == batch.secret).all(1) & (hard[:, bv:].astype(np.int16) == -batch.ssum).all(1)

@@ -13,6 +13,6 @@ for wl in $wls; do
 import json
 d=json.load(open("$out/${tag}_bench_$wl.json"))
 r=d["roofline"]
-print("$wl", "value %.0f e2e %.0f ms/step %.3f | cn %.4f ms frac %.3f | vn %.4f ms frac %.3f" % (d["value"], d["e2e"]["value"], d["ms_per_step"], r["ms_per_launch"], r["frac"], r["second_kernel"]["ms_per_launch"], r["second_kernel"]["frac"]))
+print("$wl", "obs value %.0f e2e %.0f |" % ((d.get("observed") or {}).get("value",0), ((d.get("observed") or {}).get("e2e") or {}).get("value",0)), "value %.0f e2e %.0f ms/step %.3f | cn %.4f ms frac %.3f | vn %.4f ms frac %.3f" % (d["value"], d["e2e"]["value"], d["ms_per_step"], r["ms_per_launch"], r["frac"], r["second_kernel"]["ms_per_launch"], r["second_kernel"]["frac"]))
 PY
 done

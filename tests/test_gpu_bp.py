@@ -67,6 +67,11 @@ def test_batch_early_stop_freeze_and_torch():
     torch.cuda.synchronize()
     assert np.array_equal(tout["decoding"].cpu().numpy(), ref["decoding"])
     assert np.array_equal(tout["iters"].cpu().numpy(), ref["iters"])
+    pinned = torch.empty((45, w.n), dtype=torch.uint8).pin_memory().numpy()
+    pout = bpd.decode_batch(synd, out=pinned)
+    assert pout["decoding"] is pinned and np.array_equal(pinned, ref["decoding"])
+    with pytest.raises(ValueError):
+        bpd.decode_batch(synd, out=np.empty((45, w.n), np.int8))
 
 
 def test_per_trial_priors():

@@ -64,3 +64,12 @@ def test_against_the_reference_python_helpers():
                                                         kyber.secret_distribution(1), 1)
         assert np.allclose(table[y], ref, rtol=1e-12, atol=1e-15)
     assert np.allclose(W.cbd_prior(2, 6), [kyber.secret_distribution(6)[s] for s in range(-12, 13)])
+
+
+def test_observed_batches_expand_to_the_prior_vectors():
+    """generate_observed is generate in index form: table[obs] reproduces the priors bit for bit."""
+    w = W.KyberWorkload("kyber512", sum_weight=6, check_blocks=1, accuracy=0.97, nbits=4, nbits_sum=5, seed=2)
+    a, b = w.generate(33, seed=9), w.generate_observed(33, seed=9)
+    assert b.obs.dtype == np.uint16 and b.obs.shape == (33, w.bvars) and b.obs_sum.shape == (33, w.R)
+    assert np.array_equal(w.table[b.obs], a.priors) and np.array_equal(w.table_sum[b.obs_sum], a.priors_sum)
+    assert np.array_equal(a.secret, b.secret) and np.array_equal(a.ssum, b.ssum)
