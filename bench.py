@@ -131,10 +131,12 @@ def cpu_path(kind, wl, iters, trials, threads, warm_only=False):
     return trials / dt, dt, int(wl.success(b, out["decoding"]).sum())
 
 
-def cpu_sample_size(kind, cores):
-    # q-ary: the reference's brute-force check node costs ~10 s per Kyber-512 decode and core -> one decode per
-    # thread is a 10-20 s sample.  binary: ~2-5 ms per decode and core -> 64 decodes per thread.
-    return cores if kind == "qary" else 64 * cores
+def cpu_sample_size(kind, cores, per_step=False):
+    # q-ary: the reference's brute-force check node costs 1-3.5 s per decode and core -> 4 decodes per thread is a
+    # 4-14 s sample.  binary: ~5 ms per decode and core -> 512 decodes per thread (~3 s + generating the syndromes).
+    if per_step:  # --impl reference: one step of K; K steps must stay within a few minutes
+        return cores if kind == "qary" else 128 * cores
+    return 4 * cores if kind == "qary" else 512 * cores
 
 
 def run_reference(args, kind, wl, iters, cfg):
@@ -144,7 +146,7 @@ def run_reference(args, kind, wl, iters, cfg):
     if rank != 0:
         return
     cores = O.max_threads()
-    n = cpu_sample_size(kind, cores)
+    n = cpu_sample_size(kind, cores, per_step=True)
     for _ in range(args.warmup):  # warm-up: thread pool, page-in (one iteration of one decode per thread)
         cpu_path(kind, wl, iters, min(n, cores), cores, warm_only=True)
     total_t, total_n = 0.0, 0
@@ -153,7 +155,7 @@ def run_reference(args, kind, wl, iters, cfg):
         total_t += dt
         total_n += n
     value = total_n / total_t
-    sample = f"{n} trials per step ({'1 decode' if kind == 'qary' else '64 decodes'} per thread), {args.steps} steps"
+    sample = f"{n} trials per step ({'1 decode' if kind == 'qary' else '128 decodes'} per thread), {args.steps} steps"
     line = {
         "impl": "reference", "metric": "decoded trials/sec", "value": value, "unit": "trials/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_t / args.steps, "higher_is_better": True,
@@ -366,7 +368,7 @@ def run_ours(args, kind, wl, iters, cfg):
         traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(traffic_file):
             try:
-                tr = json.load(open(traffic_file)).get(cfg["workload"])
+                tr = json.load(open(traffic_file)).get(cfg["workload"].split(":")[0])
                 if tr:
                     roofline["traffic"] = tr["dram_bytes_per_launch"] * (T / tr["trials"])
                     roofline["traffic_source"] = tr.get("source")
@@ -382,7 +384,7 @@ def run_ours(args, kind, wl, iters, cfg):
             n = cpu_sample_size(kind, cores)
             v, secs, _ = cpu_path(kind, wl, iters, n, cores)
             cpu = {"value": v, "unit": "trials/s", "cores": cores, "kind": "port",
-                   "sample": f"{n} trials of this workload, one decode per thread "
+                   "sample": f"{n} trials of this workload, one decode at a time per thread "
                              f"({'brute-force check node as decoder_special.rs:531-554' if kind == 'qary' else 'fp64 product-sum'}), "
                              f"{secs:.1f} s"}
         value = world * T * args.steps / (ms * 1e-3)

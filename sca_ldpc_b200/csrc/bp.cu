@@ -318,6 +318,8 @@ int scaldpc_bp_create(int m, int n, const int32_t *row_ptr, const int32_t *col, 
     }
     SCALDPC_CUDA(cudaSetDevice(device));
     SCALDPC_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
+    if (getenv("SCALDPC_EXP_SEQ_CSC"))  // EXPERIMENT ONLY (timing): pretend the variables' edges are contiguous
+        for (size_t i = 0; i < g.csc_off.size(); ++i) g.csc_off[i] = (uint32_t)(i * 128);
     int rc;
     if ((rc = upload_vec(&h->d_row_ptr, g.row_ptr)) || (rc = upload_vec(&h->d_col, g.col)) ||
         (rc = upload_vec(&h->d_col_ptr, g.col_ptr)) || (rc = upload_vec(&h->d_csc_edge, g.csc_off)) ||

@@ -15,8 +15,8 @@ timeout 600 python bench.py --workload hqc128 --steps 3 --warmup 3 > $out/${tag}
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/${tag}_launches_k512.csv \
   python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $out/${tag}_ncu_list.log 2>&1
 # ncu: one full capture of the dominant kernel (skip the FIRST-iteration variant and warm-up launches)
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_cn_fast -s 20 -c 1 -f -o $out/${tag}_cn_fast_k512 \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_cn_fast -s 23 -c 1 -f -o $out/${tag}_cn_fast_k512 \
   python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $out/${tag}_ncu_full.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_vn -s 20 -c 1 -f -o $out/${tag}_vn_k512 \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_vn -s 23 -c 1 -f -o $out/${tag}_vn_k512 \
   python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $out/${tag}_ncu_full_vn.log 2>&1
 tail -3 $out/${tag}_pytest.log; tail -2 $out/${tag}_smoke.log; cat $out/${tag}_bench_kyber512.json
