@@ -281,10 +281,12 @@ def run_ours(args, kind, wl, iters, cfg):
     sync_all()
     tw0 = time.perf_counter()
     e0.record()
+    counters = None
     for _ in range(args.steps):
-        counters = step_dev()
-        if world > 1:
-            dist.all_reduce(counters)  # the path's only exchange: success / trial counters
+        c = step_dev()
+        counters = c if counters is None else counters + c
+    if world > 1:
+        dist.all_reduce(counters)  # the path's only exchange: success / trial counters, once per job
     e1.record()
     sync_all()
     tw1 = time.perf_counter()
