@@ -57,48 +57,67 @@ def measured_peak_gbs():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
-
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons DURING the timed region (the B200_PROFILING.md clocks line), read in-process
+    through NVML (nvidia_ml_py) from a thread every 20 ms.  A polling `nvidia-smi -lms` subprocess was measured to
+    stall kernel launches for ~1 ms per 6 ms step; plain NVML getters do not.  Falls back to one nvidia-smi query
+    after the timed region when NVML is not importable."""
 
     def __init__(self, index=0):
-        self.index, self.proc, self.lines = index, None, []
+        self.index, self.samples, self.thread, self.stop_flag, self.nv, self.handle = index, [], None, False, None, None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
-                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            import pynvml as nv
+
+            nv.nvmlInit()
+            self.nv, self.handle = nv, nv.nvmlDeviceGetHandleByIndex(self.index)
             self.thread = threading.Thread(target=self._pump, daemon=True)
             self.thread.start()
         except Exception:
-            self.proc = None
+            self.nv = None
 
     def _pump(self):
-        for line in self.proc.stdout:
-            self.lines.append((time.perf_counter(), line.strip()))
+        nv = self.nv
+        while not self.stop_flag:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM)
+                mx = nv.nvmlDeviceGetMaxClockInfo(self.handle, nv.NVML_CLOCK_SM)
+                rs = nv.nvmlDeviceGetCurrentClocksEventReasons(self.handle) if hasattr(
+                    nv, "nvmlDeviceGetCurrentClocksEventReasons") else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+                self.samples.append((time.perf_counter(), sm, mx, rs))
+            except Exception:
+                pass
+            time.sleep(0.02)
 
     def stop(self, t0, t1):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        rows = [ln for (t, ln) in self.lines if t0 <= t <= t1 + 0.2] or [ln for (_, ln) in self.lines[-3:]]
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in rows:
-            f = [x.strip() for x in ln.split(",")]
-            try:
-                sm.append(float(f[0]))
-                mx.append(float(f[1]))
-            except Exception:
-                continue
-            for name, val in zip(names, f[3:7]):
-                if val.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        self.stop_flag = True
+        if self.nv is None:
+            return self._smi_once()
+        self.thread.join(timeout=1.0)
+        nv = self.nv
+        rows = [x for x in self.samples if t0 <= x[0] <= t1] or self.samples[-3:]
+        bits = {"hw_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8),
+                "hw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+                "sw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20),
+                "sw_power_cap": getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4)}
+        reasons = sorted({name for (_, _, _, rs) in rows for name, bit in bits.items() if rs & bit})
+        sm = [x[1] for x in rows]
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max((x[2] for x in rows), default=None),
+                "reasons": reasons, "samples": len(rows), "source": "nvml, 20 ms period, inside the timed region"}
+
+    def _smi_once(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                 capture_output=True, text=True, timeout=20).stdout.strip().splitlines()[0]
+            f = [x.strip() for x in out.split(",")]
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            return {"sm_mhz": float(f[0]), "sm_max_mhz": float(f[1]),
+                    "reasons": [n for n, v in zip(names, f[2:6]) if v.lower().startswith("active")], "samples": 1,
+                    "source": "nvidia-smi, one query right after the timed region"}
+        except Exception:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"], "samples": 0}
 
 
 def dist_env():
@@ -189,6 +208,11 @@ def run_ours(args, kind, wl, iters, cfg):
         dist.init_process_group("nccl", device_id=dev)
     T = args.trials
     seed = 1000 + rank  # every rank decodes its own independent trials
+    # nvidia-smi sampler: started long before the timed region, so that its NVML start-up (hundreds of ms of driver
+    # calls that stall kernel launches) is over by then; during the timed region it only polls every 100 ms
+    clocks = ClockSampler(local)
+    if rank == 0 and not os.environ.get("BENCH_NO_CLOCKS"):
+        clocks.start()
 
     # ---- inputs: generated on the host, resident in HBM for `value`, in pinned host memory for `e2e`
     batch = wl.generate(T, seed=seed)
@@ -232,8 +256,9 @@ def run_ours(args, kind, wl, iters, cfg):
         edges = dec.E
         iters_per_trial = lambda: float(max(1, iters))  # noqa: E731  (no early termination on the q-ary path)
         bytes_iter = dec.algorithmic_bytes_per_trial_iteration()
-        # dominant kernel = check-node pass: reads + writes every message slot once, reads the sum-variable priors
-        cn_bytes = 8 * dec.msg_slots + 4 * (dec.R * dec.QS if dec.special else 0)
+        # dominant kernel = check-node pass (middle iteration): reads + writes every B-edge message slot once and
+        # reads the sum-variable priors; the sum-variables' own messages never travel
+        cn_bytes = 8 * (dec.msg_slots - (dec.R * dec.QS if dec.special else 0)) + 4 * (dec.R * dec.QS if dec.special else 0)
         vn_bytes = 8 * (dec.msg_slots - (dec.R * dec.QS if dec.special else 0)) + 4 * dec.bvars * dec.Q
     else:
         dec = bp_decoder(csr=(wl.row_ptr, wl.col), shape=(wl.m, wl.n), max_iter=iters, channel_probs=wl.channel_probs,
@@ -270,27 +295,33 @@ def run_ours(args, kind, wl, iters, cfg):
         torch.cuda.synchronize()
 
     # ---- value: device-resident inputs, CUDA events, max over ranks
-    for _ in range(max(3, args.warmup)):
-        counters = step_dev()
+    counters = None
+    for _ in range(max(3, args.warmup)):  # warm-up runs everything the timed loop runs (CUDA loads kernels lazily: the
+        c = step_dev()                    # first launch of any kernel, torch's included, stalls the device ~10 ms)
+        counters = c if counters is None else counters + c
     sync_all()
-    clocks = ClockSampler(local)
-    if rank == 0:
-        clocks.start()
     l0 = dec.launch_count
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync_all()
     tw0 = time.perf_counter()
     e0.record()
     counters = None
+    dbg = [] if os.environ.get("BENCH_DEBUG_STEPS") else None
     for _ in range(args.steps):
         c = step_dev()
         counters = c if counters is None else counters + c
+        if dbg is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            dbg.append(ev)
     if world > 1:
         dist.all_reduce(counters)  # the path's only exchange: success / trial counters, once per job
     e1.record()
     sync_all()
     tw1 = time.perf_counter()
     launches = dec.launch_count - l0
+    if dbg:
+        print("per-step ms:", [round(a.elapsed_time(b), 3) for a, b in zip([e0] + dbg[:-1], dbg)], file=sys.stderr)
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -363,6 +394,9 @@ def run_ours(args, kind, wl, iters, cfg):
             "second_kernel": {"kernel": "k_vn" if kind == "qary" else "k_bp_vn", "achieved": vn_achieved,
                               "frac": vn_achieved / peak, "ms_per_launch": vn_ms,
                               "algorithmic_bytes_per_launch": T * vn_bytes},
+            "note": ("q-ary: the sum-variables' messages are not moved in middle iterations, 38 % fewer bytes than SURVEY.md "
+                     "8(d) assumes for this pass; the check pass is instruction-issue-bound, see `iteration` for the 8(d) figure"
+                     if kind == "qary" else "binary: the bit pass (second_kernel) is the slower of the two"),
             "iteration": {"bytes_per_trial_iteration_survey_8d": bytes_iter,
                           "achieved": T * bytes_iter / ((cn_ms + vn_ms) * 1e-3) / 1e9,
                           "frac": T * bytes_iter / ((cn_ms + vn_ms) * 1e-3) / 1e9 / peak},

@@ -292,17 +292,27 @@ QaryDev dev_view(const scaldpc_qary *h, bool want_post)
 typedef void (*cn_fast_fn)(const QaryDev, const int);
 typedef void (*vn_fn)(const QaryDev, const int);
 
-// The four (FIRST, LAST) instantiations of the persistent check-node kernel for one shape.
+// The instantiations of the persistent check-node kernel for one shape, indexed by cn_mode_index().
 struct CnFast {
-    cn_fast_fn fn[2][2];
+    cn_fast_fn fn[6];
     size_t smem;
 };
+
+// Iteration `it` of `iters` -> kernel variant (qary_cn_fast.cuh MODE bits): the sum-variable's c2v is written only by
+// the second-to-last iteration and read only by the last one.
+int cn_mode_index(int it, int iters)
+{
+    const bool first = it == 1, last = it == iters, penult = it == iters - 1;
+    if (first) return last ? 1 : (penult ? 2 : 0);
+    return last ? 5 : (penult ? 4 : 3);
+}
 
 template <int SW, int B>
 const CnFast *cn_fast_table()
 {
-    static const CnFast t = {{{k_cn_fast<SW, B, false, false>, k_cn_fast<SW, B, false, true>},
-                              {k_cn_fast<SW, B, true, false>, k_cn_fast<SW, B, true, true>}},
+    static const CnFast t = {{k_cn_fast<SW, B, kCnFirst>, k_cn_fast<SW, B, kCnFirst | kCnLast>,
+                              k_cn_fast<SW, B, kCnFirst | kCnWsum>, k_cn_fast<SW, B, 0>, k_cn_fast<SW, B, kCnWsum>,
+                              k_cn_fast<SW, B, kCnLast | kCnRsum>},
                              CnFastShape<SW, B>::smem_bytes};
     return &t;
 }
@@ -353,8 +363,9 @@ size_t generic_smem_bytes(const scaldpc_qary *h, CnGenericArgs *g)
 }
 
 // One check-node launch / one variable-node launch over `tiles` tiles.
-int launch_cn(scaldpc_qary *h, const QaryDev &p, int tiles, bool first, bool last, unsigned flags, cudaStream_t st)
+int launch_cn(scaldpc_qary *h, const QaryDev &p, int tiles, int it, int iters, unsigned flags, cudaStream_t st)
 {
+    const bool first = it == 1, last = it == iters;
     const bool exact = flags & SCALDPC_CN_EXACT;
     const bool force_generic = flags & SCALDPC_CN_GENERIC;
     const CnFast *fast = (!exact && !force_generic && h->fast_sw) ? pick_cn_fast(h->fast_sw, h->B) : nullptr;
@@ -362,7 +373,7 @@ int launch_cn(scaldpc_qary *h, const QaryDev &p, int tiles, bool first, bool las
         // persistent: one CTA of kCnWarps warps per SM, warps stride over the (tile, check) items
         const int n_items = tiles * h->R;
         const int grid = std::max(1, std::min(h->num_sms, (n_items + kCnWarps - 1) / kCnWarps));
-        fast->fn[first][last]<<<grid, kCnWarps * 32, fast->smem, st>>>(p, n_items);
+        fast->fn[cn_mode_index(it, iters)]<<<grid, kCnWarps * 32, fast->smem, st>>>(p, n_items);
         ++h->launches;
     } else {
         if (first) {
@@ -474,8 +485,8 @@ int scaldpc_qary_create(const int8_t *H, int R, int N, int b, int bsum, int dv, 
     SCALDPC_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
     if (h->fast_sw) {
         const CnFast *f = pick_cn_fast(h->fast_sw, b);
-        for (int i = 0; i < 4; ++i)
-            SCALDPC_CUDA(cudaFuncSetAttribute(f->fn[i >> 1][i & 1], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f->smem));
+        for (int i = 0; i < 6; ++i)
+            SCALDPC_CUDA(cudaFuncSetAttribute(f->fn[i], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f->smem));
     }
     int rc;
     if ((rc = upload(&h->d_row_ptr, row_ptr)) || (rc = upload(&h->d_col, col)) || (rc = upload(&h->d_sign, sign)) ||
@@ -576,7 +587,7 @@ static int decode_on_device(scaldpc_qary *h, int T, const PriorSrc &src, int8_t 
     const QaryDev p = dev_view(h, want_post);
     const int iters = std::max(1, h->max_iter);  // decoder.rs:575-663: `it` starts at 1, exit when it >= max_iter
     for (int it = 1; it <= iters; ++it) {
-        if ((rc = launch_cn(h, p, tiles, it == 1, it == iters, flags, st))) return rc;
+        if ((rc = launch_cn(h, p, tiles, it, iters, flags, st))) return rc;
         if ((rc = launch_vn(h, p, tiles, it == iters, st))) return rc;
     }
     dim3 block(32, kTrRows);
@@ -761,7 +772,7 @@ int scaldpc_qary_time_kernel(scaldpc_qary *h, int which, int T, unsigned flags, 
     // message state to a valid message state)
     for (int i = -1; i < reps && !rc; ++i) {
         if (i == 0) SCALDPC_CUDA(cudaEventRecord(e0, st));
-        rc = which == 0 ? launch_cn(h, p, tiles, false, false, flags, st) : launch_vn(h, p, tiles, false, st);
+        rc = which == 0 ? launch_cn(h, p, tiles, 2, 4, flags, st) : launch_vn(h, p, tiles, false, st);  // middle iteration
     }
     SCALDPC_CUDA(cudaEventRecord(e1, st));
     SCALDPC_CUDA(cudaEventSynchronize(e1));

@@ -123,9 +123,25 @@ struct CnFastShape {
     static constexpr size_t smem_bytes = (size_t)kCnWarps * NB * 32 * sizeof(float);
 };
 
-template <int SW, int B, bool FIRST, bool LAST>
+// MODE bits: which iteration of the decode this launch is.
+//   kCnFirst  iteration 1: inputs are the variables' channel LLRs (k_init_v2c fused)
+//   kCnLast   last iteration: emits the sum-variable's hard decision / posterior
+//   kCnWsum   writes the sum-variable's c2v (F_SW) to its message slots -- only the second-to-last iteration needs to
+//   kCnRsum   reads it back and forms the sum-variable's v2c as the reference does, normalise((channel + c2v) - c2v)
+//             (decoder_special.rs:591-604) -- only the last iteration does
+// Every other iteration takes the sum-variable's v2c straight from the channel, normalise(channel), and neither
+// computes nor moves its c2v: (a + c) - c is `a` up to one rounding, a value excluded by c2v = +inf stays
+// unreachable through the B-variables (their exclusions are sticky), and the only other effect of an exclusion -- a
+// different normalisation constant -- shifts all of the check's outputs uniformly, which the variable node's own
+// normalisation removes from every later message.  It survives only in the posteriors, which is why the LAST
+// iteration uses the reference's formula on the c2v the iteration before it stored (oracle algo 3 models exactly this).
+constexpr int kCnFirst = 1, kCnLast = 2, kCnWsum = 4, kCnRsum = 8;
+
+template <int SW, int B, int MODE>
 __global__ void __launch_bounds__(kCnWarps * 32, 1) k_cn_fast(const QaryDev p, const int n_items)
 {
+    constexpr bool FIRST = MODE & kCnFirst, LAST = MODE & kCnLast, WSUM = MODE & kCnWsum, RSUM = MODE & kCnRsum;
+    static_assert(!(FIRST && RSUM), "the first iteration has no previous c2v");
     static_assert(SW >= 2, "k_cn_fast needs at least two B-variables per check");
     using Sh = CnFastShape<SW, B>;
     constexpr int Q = Sh::Q, BS = Sh::BS, QS = Sh::QS, NS = Sh::NS;
@@ -155,7 +171,7 @@ __global__ void __launch_bounds__(kCnWarps * 32, 1) k_cn_fast(const QaryDev p, c
         const int tile = item / p.R, check = item - tile * p.R;
         const int e0 = __ldg(p.row_ptr + check);
 #ifndef SCALDPC_HOST_MODEL
-        sc_mbar_expect_tx(bar, (uint32_t)((FIRST ? SW * Q + QS : Sh::NB) * 128));
+        sc_mbar_expect_tx(bar, (uint32_t)(((RSUM ? NS : SW * Q) + QS) * 128));
 #endif
         if (FIRST) {  // v2c = perm_h(channel) (decoder_special.rs:480-486): gather the variables' channel LLRs
             for (int k = 0; k < SW; ++k) {
@@ -163,7 +179,7 @@ __global__ void __launch_bounds__(kCnWarps * 32, 1) k_cn_fast(const QaryDev p, c
                 SC_STAGE(k * Q, p.llr + ((size_t)tile * p.SL + (size_t)var * Q) * 32, Q);
             }
         } else {
-            SC_STAGE(0, p.msg + ((size_t)tile * p.S + __ldg(p.edge_off + e0)) * 32, NS);
+            SC_STAGE(0, p.msg + ((size_t)tile * p.S + __ldg(p.edge_off + e0)) * 32, RSUM ? NS : SW * Q);
         }
         const int vs = __ldg(p.col + e0 + SW) - p.bvars;
         SC_STAGE(NS, p.llr_sum + ((size_t)tile * p.SLS + (size_t)vs * QS) * 32, QS);
@@ -206,7 +222,7 @@ __global__ void __launch_bounds__(kCnWarps * 32, 1) k_cn_fast(const QaryDev p, c
                 as[QS - 1 - i] = t;
             }
         }
-        if (!FIRST) {
+        if (RSUM) {
             float m = INF;
 #pragma unroll
             for (int i = 0; i < QS; ++i) {
@@ -215,6 +231,13 @@ __global__ void __launch_bounds__(kCnWarps * 32, 1) k_cn_fast(const QaryDev p, c
                 as[i] = tot - c;              // prim = perm_h(sum - perm_h(c2v))
                 m = fminf(m, as[i]);          // value of the first strict minimum (NaN skipped)
             }
+#pragma unroll
+            for (int i = 0; i < QS; ++i) as[i] = as[i] - m;
+        } else if (!FIRST) {  // normalise(channel): value of the first strict minimum (NaN skipped) subtracted
+            MinAcc macc;
+#pragma unroll
+            for (int i = 0; i < QS; ++i) macc.add(as[i]);
+            const float m = macc.get();
 #pragma unroll
             for (int i = 0; i < QS; ++i) as[i] = as[i] - m;
         }
@@ -246,21 +269,15 @@ __global__ void __launch_bounds__(kCnWarps * 32, 1) k_cn_fast(const QaryDev p, c
 #pragma unroll
             for (int jj = 0; jj < (k + 1) * B + 1; ++jj) Fp[k + 1][jj] = f2_make(Fs[2 * jj], Fs[2 * jj + 1]);
         }
-        // ---- c2v of the sum-variable: F_SW[-t]
         float *out = msg + (size_t)base * 32;  // the check's slot block: constant offsets from here on
         float cs[QS];
-        {
+        if (LAST || WSUM) {  // c2v of the sum-variable: F_SW[-t]
             float Fs[QS + 1];
-            if (SW == 1) {
+            cn_conv_fwd<Q>(Fp[(SW - 1) % SW], 2 * (SW - 1) * B + 1, a[SW - 1], Fs);
 #pragma unroll
-                for (int i = 0; i < QS; ++i) Fs[i] = a[0][i];
-            } else {
-                cn_conv_fwd<Q>(Fp[(SW - 1) % SW], 2 * (SW - 1) * B + 1, a[SW - 1], Fs);
-            }
-#pragma unroll
-            for (int i = 0; i < QS; ++i) {  // i = t + BS, F_SW index = QS - 1 - i
+            for (int i = 0; i < QS; ++i) {  // i = t + BS, F_SW index QS - 1 - i
                 cs[i] = (as[i] == INF) ? INF : Fs[QS - 1 - i];
-                out[(size_t)(SW * Q + i) * 32] = cs[i];
+                if (WSUM) out[(size_t)(SW * Q + i) * 32] = cs[i];
             }
         }
         if (LAST) {  // decision of the sum-variable (decoder_special.rs:606-608): first minimum in the VARIABLE's frame

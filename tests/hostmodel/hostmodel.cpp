@@ -75,17 +75,21 @@ void run_grid(unsigned gx, unsigned gy, unsigned threads, K kernel, A... args)
 typedef void (*cn_fast_fn)(const QaryDev, const int);
 typedef void (*vn_fn)(const QaryDev, const int);
 
+// iteration `it` of `iters` -> kernel variant, as cn_mode_index() / cn_fast_table() in qary.cu
 template <int SW, int B>
-cn_fast_fn cn_fast_variant(bool first, bool last)
+cn_fast_fn cn_fast_variant(int it, int iters)
 {
-    if (first) return last ? k_cn_fast<SW, B, true, true> : k_cn_fast<SW, B, true, false>;
-    return last ? k_cn_fast<SW, B, false, true> : k_cn_fast<SW, B, false, false>;
+    const bool first = it == 1, last = it == iters, penult = it == iters - 1;
+    if (first)
+        return last ? k_cn_fast<SW, B, kCnFirst | kCnLast>
+                    : (penult ? k_cn_fast<SW, B, kCnFirst | kCnWsum> : k_cn_fast<SW, B, kCnFirst>);
+    return last ? k_cn_fast<SW, B, kCnLast | kCnRsum> : (penult ? k_cn_fast<SW, B, kCnWsum> : k_cn_fast<SW, B, 0>);
 }
 
-cn_fast_fn pick_cn_fast(int sw, int b, bool first = false, bool last = false)
+cn_fast_fn pick_cn_fast(int sw, int b, int it = 2, int iters = 4)
 {
 #define CASE(SW_, B_) \
-    if (sw == SW_ && b == B_) return cn_fast_variant<SW_, B_>(first, last);
+    if (sw == SW_ && b == B_) return cn_fast_variant<SW_, B_>(it, iters);
     CASE(6, 2) CASE(6, 3) CASE(4, 2) CASE(8, 2) CASE(3, 2)
 #undef CASE
     return nullptr;
@@ -181,7 +185,7 @@ int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
         const int first = it == 1, last = it == iters;
         if (fast) {
             // persistent kernel: a deliberately small grid, so every warp strides over several items
-            run_grid(3, 1, kCnWarps * 32, pick_cn_fast(g.regular_sw, b, first, last), p, tiles * g.R);
+            run_grid(3, 1, kCnWarps * 32, pick_cn_fast(g.regular_sw, b, it, iters), p, tiles * g.R);
         } else {
             if (first) run_grid((g.E + 7) / 8, tiles, 256, k_init_v2c, p, g.E);
             CnGenericArgs a;

@@ -106,7 +106,7 @@ def test_batched_parity_with_oracle(variant, sw, cb):
     T = 40
     b = w.generate(T, seed=3)
     d = QaryDecoder(w.H, 6, **w.decoder_kwargs)
-    orc = O.QaryOracle(w.H, 6, B=w.B, BSUM=w.BSUM, DC=sw + 1, algo=O.ALGO_FWD_BWD)
+    orc = O.QaryOracle(w.H, 6, B=w.B, BSUM=w.BSUM, DC=sw + 1, algo=O.ALGO_FAST)
     # identical LLR inputs (the oracle's into_llr) -> strict comparison
     llr = np.stack([O.into_llr(x) for x in b.priors])
     llrs = np.stack([O.into_llr(x) for x in b.priors_sum])

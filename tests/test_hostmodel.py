@@ -36,16 +36,30 @@ def test_fast_kernels_match_fixture(cb):
         assert util.max_abs_diff(posts[0], z["post_sum"][i]) < 1e-4
 
 
-def test_fast_kernel_equals_fwd_bwd_oracle_bitwise():
-    """The fast kernel and the oracle's forward/backward model (algo 2) are the same arithmetic."""
-    z, H, llr, llrs = _kyber(1, [1])
-    it = int(z["iterations"][1])
-    d = O.QaryOracle(H, it, B=2, BSUM=12, DC=7)
-    h2, p2, ps2 = d.decode_llr(llr[0], llrs[0], algo=O.ALGO_FWD_BWD)
-    rc, hard, post, posts, _, fast = util.hostmodel_qary(H, 2, 12, it, llr, llrs, dc=7)
-    assert rc == 0 and fast and np.array_equal(hard[0], h2)
-    assert util.same_nonfinite(post[0], p2) and util.max_abs_diff(post[0], p2) < 2e-5
-    assert util.same_nonfinite(posts[0], ps2) and util.max_abs_diff(posts[0], ps2) < 2e-5
+def test_fast_kernel_equals_fast_oracle_bitwise():
+    """The fast kernel and the oracle's model of it (algo 3: forward/backward check node, sum-variable messages taken
+    from the channel except for the last iteration) are the same arithmetic, bit for bit -- including the trial whose
+    priors are deterministic (most entries +inf), where an excluded sum value changes the normalisation constant."""
+    for cb, idx in ((1, [1, 3]), (2, [0, 3])):
+        z, H, llr, llrs = _kyber(cb, idx)
+        for j, i in enumerate(idx):
+            it = int(z["iterations"][i])
+            d = O.QaryOracle(H, it, B=2, BSUM=12, DC=7)
+            h2, p2, ps2 = d.decode_llr(llr[j], llrs[j], algo=O.ALGO_FAST)
+            rc, hard, post, posts, _, fast = util.hostmodel_qary(H, 2, 12, it, llr[j:j + 1], llrs[j:j + 1], dc=7)
+            assert rc == 0 and fast and np.array_equal(hard[0], h2)
+            assert np.array_equal(post[0], p2, equal_nan=True) and np.array_equal(posts[0], ps2, equal_nan=True)
+    # one and two iterations: FIRST|LAST and FIRST|WSUM -> LAST|RSUM variants
+    z, H, llr, llrs = _kyber(1, [0])
+    for it in (1, 2, 3):
+        d = O.QaryOracle(H, it, B=2, BSUM=12, DC=7)
+        h2, p2, ps2 = d.decode_llr(llr[0], llrs[0], algo=O.ALGO_FAST)
+        rc, hard, post, posts, _, fast = util.hostmodel_qary(H, 2, 12, it, llr, llrs, dc=7)
+        assert rc == 0 and fast and np.array_equal(hard[0], h2)
+        assert np.array_equal(post[0], p2, equal_nan=True) and np.array_equal(posts[0], ps2, equal_nan=True)
+        if it == 1:  # a single iteration has no simplification at all: equals the forward/backward model
+            h3, p3, ps3 = d.decode_llr(llr[0], llrs[0], algo=O.ALGO_FWD_BWD)
+            assert np.array_equal(p2, p3, equal_nan=True) and np.array_equal(ps2, ps3, equal_nan=True)
 
 
 def test_exact_kernel_is_bit_identical_special():

@@ -85,11 +85,11 @@ def test_kyber768_fixture(cb):
         it = int(z["iterations"][i])
         d = O.QaryOracle(H, it, B=2, BSUM=12, DC=7)
         llr, llrs = O.into_llr(z["channel_output"][i]), O.into_llr(z["channel_output_sum"][i])
-        algos = [O.ALGO_EXACT_DP, O.ALGO_FWD_BWD] + ([O.ALGO_ENUMERATE] if (cb == 1 and i == 0) else [])
+        algos = [O.ALGO_EXACT_DP, O.ALGO_FWD_BWD, O.ALGO_FAST] + ([O.ALGO_ENUMERATE] if (cb == 1 and i == 0) else [])
         for algo in algos:
             hard, post, posts = d.decode_llr(llr, llrs, algo=algo)
             assert np.array_equal(hard, z["hard"][i]), (cb, i, algo)
-            if algo == O.ALGO_FWD_BWD:
+            if algo in (O.ALGO_FWD_BWD, O.ALGO_FAST):
                 assert util.same_nonfinite(post, z["post"][i]) and util.same_nonfinite(posts, z["post_sum"][i])
                 assert util.max_abs_diff(post, z["post"][i]) < 1e-4
                 assert util.max_abs_diff(posts, z["post_sum"][i]) < 1e-4
