@@ -26,7 +26,7 @@ struct scaldpc_bp {
     int m = 0, n = 0, E = 0, dc_max = 0, dv_max = 0;
     int max_iter = 0, device = 0, num_sms = 148;
     int class_end[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    int *d_row_ptr = nullptr, *d_col = nullptr, *d_col_ptr = nullptr, *d_vn_order = nullptr;
+    int *d_row_ptr = nullptr, *d_col = nullptr, *d_col_ptr = nullptr, *d_vn_order = nullptr, *d_vn_desc = nullptr;
     uint32_t *d_csc_edge = nullptr;
     // workspace
     int cap_tiles = 0;
@@ -46,6 +46,10 @@ struct scaldpc_bp {
     int cn_warps = 8, cn_occ[2] = {1, 1};
     size_t smem_cn = 0;
     int vn_occ[8] = {0};  // bit pass: resident CTAs per SM of each degree-class kernel
+    bool vn_tma = false;  // SCALDPC_BP_VN_TMA=1: column gather by bulk-async copies (k_bp_vn_tma) instead of k_bp_vn.
+                          // Measured on hqc128 / hqc256: 1.41 / 1.98 ms against 1.35 / 1.91 ms -- the per-lane bulk copies
+                          // are serialised (one UBLKCP per lane) and four columns in flight per warp buy nothing, so
+                          // the register-prefetch kernel stays the default.
     int vn_gen_wpc = 1;   // warps per CTA of the shared-memory kernel for heavier columns
     size_t smem_vn = 0;
     std::mutex mu;
@@ -172,6 +176,7 @@ BpDev view(const scaldpc_bp *h, int cur, bool per_trial_prior, bool want_post)
     p.col_ptr = h->d_col_ptr;
     p.csc_off = h->d_csc_edge;
     p.vn_order = h->d_vn_order;
+    p.vn_desc = (const int4 *)h->d_vn_desc;
     p.msg = s.msg;
     p.prior = per_trial_prior ? s.prior_t : h->d_prior;
     p.synd_w = s.synd_w;
@@ -216,6 +221,21 @@ bp_vn_fn vn_class_fn(int c)
     }
 }
 
+// TMA-gather variants of the register classes above degree 1 (bp_kernels.cuh k_bp_vn_tma).
+bp_vn_fn vn_class_tma_fn(int c)
+{
+    switch (c) {
+    case 1: return k_bp_vn_tma<1, 4>;
+    case 2: return k_bp_vn_tma<4, 8>;
+    case 3: return k_bp_vn_tma<8, 12>;
+    case 4: return k_bp_vn_tma<12, 16>;
+    case 5: return k_bp_vn_tma<16, 24>;
+    case 6: return k_bp_vn_tma<24, 32>;
+    default: return nullptr;
+    }
+}
+size_t vn_tma_smem(int c) { return (size_t)kBpVnWarps * kBpVnStages * kBpVnClass[c] * 32 * sizeof(float); }
+
 // Bit pass: one persistent launch per non-empty degree class (variables are sorted by degree); columns heavier than
 // the largest register class go through the shared-memory kernel.
 int launch_vn(scaldpc_bp *h, const BpDev &p, int tiles, cudaStream_t st)
@@ -227,7 +247,10 @@ int launch_vn(scaldpc_bp *h, const BpDev &p, int tiles, cudaStream_t st)
             if (c < kBpVnClasses) {
                 const long long items = (long long)tiles * (hi - lo);
                 const int ctas = (int)std::min<long long>((long long)h->num_sms * h->vn_occ[c], (items + kBpVnWarps - 1) / kBpVnWarps);
-                vn_class_fn(c)<<<std::max(1, ctas), kBpVnWarps * 32, 0, st>>>(p, lo, hi, tiles);
+                if (h->vn_tma && vn_class_tma_fn(c))
+                    vn_class_tma_fn(c)<<<std::max(1, ctas), kBpVnWarps * 32, vn_tma_smem(c), st>>>(p, lo, hi, tiles);
+                else
+                    vn_class_fn(c)<<<std::max(1, ctas), kBpVnWarps * 32, 0, st>>>(p, lo, hi, tiles);
             } else {
                 k_bp_vn_generic<<<dim3((hi - lo + h->vn_gen_wpc - 1) / h->vn_gen_wpc, tiles), h->vn_gen_wpc * 32, h->smem_vn, st>>>(
                     p, lo, hi);
@@ -318,12 +341,10 @@ int scaldpc_bp_create(int m, int n, const int32_t *row_ptr, const int32_t *col, 
     }
     SCALDPC_CUDA(cudaSetDevice(device));
     SCALDPC_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
-    if (getenv("SCALDPC_EXP_SEQ_CSC"))  // EXPERIMENT ONLY (timing): pretend the variables' edges are contiguous
-        for (size_t i = 0; i < g.csc_off.size(); ++i) g.csc_off[i] = (uint32_t)(i * 128);
     int rc;
     if ((rc = upload_vec(&h->d_row_ptr, g.row_ptr)) || (rc = upload_vec(&h->d_col, g.col)) ||
         (rc = upload_vec(&h->d_col_ptr, g.col_ptr)) || (rc = upload_vec(&h->d_csc_edge, g.csc_off)) ||
-        (rc = upload_vec(&h->d_vn_order, g.vn_order)))
+        (rc = upload_vec(&h->d_vn_order, g.vn_order)) || (rc = upload_vec(&h->d_vn_desc, g.vn_desc)))
         return rc;
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_prior, (size_t)n * sizeof(float)));
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_nact, sizeof(int)));
@@ -334,8 +355,15 @@ int scaldpc_bp_create(int m, int n, const int32_t *row_ptr, const int32_t *col, 
     SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_cn<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_cn));
     if (h->smem_vn)
         SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_vn_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_vn));
+    h->vn_tma = getenv("SCALDPC_BP_VN_TMA") != nullptr;
     for (int c = 0; c < kBpVnClasses; ++c) {
-        SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->vn_occ[c], vn_class_fn(c), kBpVnWarps * 32, 0));
+        if (h->vn_tma && vn_class_tma_fn(c)) {
+            SCALDPC_CUDA(cudaFuncSetAttribute(vn_class_tma_fn(c), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vn_tma_smem(c)));
+            SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->vn_occ[c], vn_class_tma_fn(c), kBpVnWarps * 32,
+                                                                       vn_tma_smem(c)));
+        } else {
+            SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->vn_occ[c], vn_class_fn(c), kBpVnWarps * 32, 0));
+        }
         h->vn_occ[c] = std::max(1, h->vn_occ[c]);
     }
     SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->cn_occ[0], k_bp_cn<false>, h->cn_warps * 32, h->smem_cn));
@@ -357,6 +385,7 @@ void scaldpc_bp_destroy(scaldpc_bp *h)
     cudaFree(h->d_col_ptr);
     cudaFree(h->d_csc_edge);
     cudaFree(h->d_vn_order);
+    cudaFree(h->d_vn_desc);
     cudaFree(h->d_prior);
     cudaFree(h->d_nact);
     cudaFree(h->d_counts);

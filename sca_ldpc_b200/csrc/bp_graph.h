@@ -16,6 +16,7 @@ struct BpHostGraph {
     int m = 0, n = 0, E = 0;
     int dc_max = 0, dv_max = 0;
     std::vector<int> row_ptr, col, col_ptr, csc_edge;
+    std::vector<int> vn_desc;       // 4 ints per sorted position i: {var, col_ptr[var], degree, 0} of var = vn_order[i]
     std::vector<uint32_t> csc_off;  // csc_edge * 128: byte offset of the edge's 128-byte line inside a tile's message block
     // variables sorted by degree (ascending, stable) and the end index of each degree class in that order:
     // class c holds the variables with degree <= kBpVnClass[c] (the last class, "generic", holds the rest)
@@ -69,6 +70,14 @@ inline int build_bp_graph(int m, int n, const int32_t *row_ptr, const int32_t *c
     std::stable_sort(g.vn_order.begin(), g.vn_order.end(), [&](int a, int b) {
         return g.col_ptr[a + 1] - g.col_ptr[a] < g.col_ptr[b + 1] - g.col_ptr[b];
     });
+    g.vn_desc.resize((size_t)4 * std::max(1, n));
+    for (int i = 0; i < n; ++i) {
+        const int v = g.vn_order[i];
+        g.vn_desc[4 * i + 0] = v;
+        g.vn_desc[4 * i + 1] = g.col_ptr[v];
+        g.vn_desc[4 * i + 2] = g.col_ptr[v + 1] - g.col_ptr[v];
+        g.vn_desc[4 * i + 3] = 0;
+    }
     {
         int i = 0;
         for (int c = 0; c < kBpVnClasses; ++c) {

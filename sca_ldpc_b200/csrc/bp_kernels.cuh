@@ -49,6 +49,7 @@ struct BpDev {
     const int *col_ptr;       // n+1
     const uint32_t *csc_off;  // E: byte offset (edge * 128) of each variable's edges inside a tile's message block, rows ascending
     const int *vn_order;      // n: variables sorted by degree (ascending), the bit pass runs one launch per class
+    const int4 *vn_desc;      // n: {var, col_ptr[var], degree, 0} of vn_order[i] in one 16-byte load (device kernels)
     float *msg;
     const float *prior;
     const uint32_t *synd_w;
@@ -290,8 +291,15 @@ __device__ __forceinline__ void bp_vn_decide(const BpDev &p, int tile, int var, 
 #else
     const uint32_t bits = __ballot_sync(0xffffffffu, post <= 0.0f);
     if (lane == 0) {
+        // w = (w & done) | (bits & ~done) without waiting for w: two fire-and-forget reductions (the word has one
+        // writer); a plain read-modify-write stalled the whole warp for an L2 round trip per item (17 % of all samples)
         uint32_t *w = p.dec_w + (size_t)tile * p.n + var;
-        *w = (*w & done) | (bits & ~done);
+        if (done == 0u) {
+            *w = bits;
+        } else {
+            atomicAnd(w, done | bits);
+            atomicOr(w, bits & ~done);
+        }
     }
 #endif
 }
@@ -306,7 +314,8 @@ __device__ __forceinline__ float *bp_at(float *base, uint32_t byte_off) { return
 
 // The two sweeps of one variable of degree exactly D (straight-line code, no guards).
 template <int D, int DMAX>
-__device__ __forceinline__ void bp_vn_body(const BpDev &p, const BpVnItem &it, int lane, const float (&c)[DMAX])
+__device__ __forceinline__ void bp_vn_body(const BpDev &p, const BpVnItem &it, int lane, const float (&c)[DMAX],
+                                           const float prior)
 {
     const uint32_t done = __ldg(p.done + it.tile);
     float *msg = p.msg + (size_t)it.tile * p.E * 32 + lane;
@@ -315,7 +324,7 @@ __device__ __forceinline__ void bp_vn_body(const BpDev &p, const BpVnItem &it, i
 #endif
     const uint32_t *off = p.csc_off + it.p0;
     float F[D > 0 ? D : 1];
-    float temp = bp_prior_of(p, it.tile, it.var, lane);
+    float temp = prior;
 #pragma unroll
     for (int i = 0; i < D; ++i) {
         F[i] = temp;
@@ -334,15 +343,16 @@ __device__ __forceinline__ void bp_vn_body(const BpDev &p, const BpVnItem &it, i
 }
 
 template <int D, int DMIN, int DMAX>
-__device__ __forceinline__ void bp_vn_dispatch(const BpDev &p, const BpVnItem &it, int lane, const float (&c)[DMAX])
+__device__ __forceinline__ void bp_vn_dispatch(const BpDev &p, const BpVnItem &it, int lane, const float (&c)[DMAX],
+                                               const float prior)
 {
     if constexpr (D < DMIN) {
-        bp_vn_body<DMAX, DMAX>(p, it, lane, c);  // unreachable for a correctly sorted class; keeps the code total
+        bp_vn_body<DMAX, DMAX>(p, it, lane, c, prior);  // unreachable for a correctly sorted class; keeps the code total
     } else {
         if (it.d == D)
-            bp_vn_body<D, DMAX>(p, it, lane, c);
+            bp_vn_body<D, DMAX>(p, it, lane, c, prior);
         else
-            bp_vn_dispatch<D - 1, DMIN, DMAX>(p, it, lane, c);
+            bp_vn_dispatch<D - 1, DMIN, DMAX>(p, it, lane, c, prior);
     }
 }
 
@@ -392,17 +402,144 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const 
     cur.j = gw - cur.tile * nv;
     advance(cur, true);
     float c[DMAX], cn[DMAX];
-    if (cur.tile < tiles) gather(cur, c);
+    float pr = 0.0f, prn = 0.0f;  // the variable's prior travels with its column (44 % of the stall samples sat on it)
+    if (cur.tile < tiles) {
+        gather(cur, c);
+        pr = bp_prior_of(p, cur.tile, cur.var, lane);
+    }
     while (cur.tile < tiles) {
         BpVnItem nxt = cur;
         advance(nxt, false);
-        if (nxt.tile < tiles) gather(nxt, cn);
-        bp_vn_dispatch<DMAX, (DMIN == 0 ? 0 : DMIN + 1), DMAX>(p, cur, lane, c);  // the first class also takes degree 0
+        if (nxt.tile < tiles) {
+            gather(nxt, cn);
+            prn = bp_prior_of(p, nxt.tile, nxt.var, lane);
+        }
+        bp_vn_dispatch<DMAX, (DMIN == 0 ? 0 : DMIN + 1), DMAX>(p, cur, lane, c, pr);
         cur = nxt;
+        pr = prn;
 #pragma unroll
         for (int i = 0; i < DMAX; ++i) c[i] = cn[i];
     }
 }
+
+#ifndef SCALDPC_HOST_MODEL
+// The same pass with the column gather done by the TMA engine.  The d lines of a column are scattered, but each is one
+// 128-byte bulk-async copy: lane i of the warp issues the copy of edge i (ONE warp instruction for the whole column)
+// into a shared-memory ring of kBpVnStages columns per warp, completion counted on one mbarrier per stage.  A warp
+// always has kBpVnStages columns in flight (k_bp_vn: one), nothing waits in registers, and the address arithmetic of
+// the gather runs once per lane instead of once per edge.  Arithmetic and stores are bp_vn_body's: results are
+// bit-identical to k_bp_vn (which remains the host-model / fallback kernel and serves the degree <= 1 class).
+constexpr int kBpVnStages = 4;
+
+// An item of k_bp_vn_tma on its way through the software pipeline.
+struct BpVnSlot {
+    BpVnItem it;
+    uint32_t off;  // lane i < d: byte offset of edge i's line (csc_off[p0 + i])
+    float prior;   // channel LLR of the variable (per lane when the priors are per trial)
+};
+
+template <int DMIN, int DMAX>
+__global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_tma(const BpDev p, const int v_lo, const int v_hi, const int tiles)
+{
+    extern __shared__ __align__(128) float sc_vn_smem[];  // [warp][stage][DMAX][32]
+    __shared__ uint64_t bars[kBpVnWarps][kBpVnStages];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
+    const int gw = blockIdx.x * wpc + warp, nw = gridDim.x * wpc;
+    const int nv = v_hi - v_lo;
+    const int step_t = nw / nv, step_j = nw - step_t * nv;
+    float *ring = sc_vn_smem + (size_t)warp * kBpVnStages * DMAX * 32;
+
+    // Three pipeline steps, one loop iteration apart, so that no load is consumed in the iteration that issues it:
+    //   step()     next (tile, j) whose tile still runs; ONE 16-byte load of {var, p0, d}
+    //   resolve()  per-lane line offset + the variable's prior (needs var / p0 of the previous step)
+    //   issue()    lane i < d copies line i of the column into a free stage (needs the offsets)
+    auto step = [&](BpVnItem &it, bool first) {
+        bool go = !first;
+        while (true) {
+            if (go) {
+                it.tile += step_t;
+                it.j += step_j;
+                if (it.j >= nv) {
+                    it.j -= nv;
+                    ++it.tile;
+                }
+            }
+            if (it.tile >= tiles || !bp_tile_done(p, it.tile)) break;
+            go = true;
+        }
+        if (it.tile < tiles) {
+            const int4 dsc = __ldg(p.vn_desc + v_lo + it.j);
+            it.var = dsc.x;
+            it.p0 = dsc.y;
+            it.d = dsc.z;  // in (DMIN, DMAX], d >= 1 here
+        }
+    };
+    auto resolve = [&](const BpVnItem &it) {
+        BpVnSlot s;
+        s.it = it;
+        s.off = 0;
+        s.prior = 0.0f;
+        if (it.tile < tiles) {
+            if (lane < it.d) s.off = __ldg(p.csc_off + it.p0 + lane);
+            s.prior = bp_prior_of(p, it.tile, it.var, lane);
+        }
+        return s;
+    };
+    auto issue = [&](const BpVnSlot &sl, int s) {
+        uint64_t *bar = &bars[warp][s];
+        if (lane == 0) sc_mbar_expect_tx(bar, (uint32_t)sl.it.d * 128u);
+        __syncwarp();
+        if (lane < sl.it.d)
+            sc_bulk_g2s(ring + ((size_t)s * DMAX + lane) * 32, (const char *)(p.msg + (size_t)sl.it.tile * p.E * 32) + sl.off, 128u, bar);
+    };
+
+    if (lane < kBpVnStages) sc_mbar_init(&bars[warp][lane], 1);
+    __syncwarp();
+
+    // f[0] is the current item, f[1 .. S-1] are in flight (f[k] sits in stage (head + k) % S), r is resolved and waits
+    // for a free stage, x is the item after r (its descriptor load is in flight)
+    BpVnSlot f[kBpVnStages], r;
+    BpVnItem x;
+    x.tile = gw / nv;
+    x.j = gw - x.tile * nv;
+    step(x, true);
+#pragma unroll
+    for (int k = 0; k < kBpVnStages; ++k) {
+        f[k] = resolve(x);
+        if (x.tile < tiles) step(x, false);
+    }
+    r = resolve(x);
+    if (x.tile < tiles) step(x, false);
+#pragma unroll
+    for (int k = 0; k < kBpVnStages; ++k)
+        if (f[k].it.tile < tiles) issue(f[k], k);
+
+    int head = 0;
+    uint32_t phases = 0;  // bit s = parity to wait for on stage s
+    while (f[0].it.tile < tiles) {
+        sc_mbar_wait(&bars[warp][head], (phases >> head) & 1u);
+        phases ^= 1u << head;
+        float c[DMAX];
+        const float *st = ring + (size_t)head * DMAX * 32 + lane;
+#pragma unroll
+        for (int i = 0; i < DMAX; ++i)
+            if ((DMIN > 0 && i <= DMIN) || i < f[0].it.d) c[i] = st[i * 32];
+        const BpVnSlot cur = f[0];
+#pragma unroll
+        for (int k = 0; k + 1 < kBpVnStages; ++k) f[k] = f[k + 1];
+        f[kBpVnStages - 1] = r;
+        __syncwarp();  // every lane has drained the stage
+        if (r.it.tile < tiles) {
+            sc_fence_proxy_async();
+            issue(r, head);
+        }
+        r = resolve(x);
+        if (x.tile < tiles) step(x, false);
+        head = head + 1 == kBpVnStages ? 0 : head + 1;
+        bp_vn_dispatch<DMAX, (DMIN == 0 ? 0 : DMIN + 1), DMAX>(p, cur.it, lane, c, cur.prior);
+    }
+}
+#endif
 
 // Any degree (columns heavier than the largest register class): per-lane scratch [i][lane] in shared memory,
 // one CTA pass over (variable, tile) without prefetch.

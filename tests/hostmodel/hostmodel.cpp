@@ -26,6 +26,9 @@ struct int2 {
     int x, y;
 };
 static inline int2 make_int2(int x, int y) { return int2{x, y}; }
+struct int4 {
+    int x, y, z, w;
+};
 #define __global__
 #define __device__
 #define __host__
