@@ -56,7 +56,8 @@ typedef struct scaldpc_qary scaldpc_qary;
 #define SCALDPC_DEVICE_PTRS 0x2u  /* all data pointers are device pointers on the handle's device */
 #define SCALDPC_CN_EXACT 0x4u     /* check node in the reference's rounding order (bit-exact); default: fast
                                      forward/backward (min,+) convolution, <= ~1e-5 from the reference */
-#define SCALDPC_CN_GENERIC 0x8u   /* force the runtime-shape kernels even where a specialised one exists */
+#define SCALDPC_CN_GENERIC 0x8u   /* force the runtime-shape kernels (check node AND variable node) even where a
+                                     specialised one exists */
 
 /*
  * scaldpc_qary_create -- replaces `#[new] fn new(py_parity_check, iterations)` (pydecoder.rs:24-45, 96-117),

@@ -394,9 +394,9 @@ int launch_cn(scaldpc_qary *h, const QaryDev &p, int tiles, int it, int iters, u
     return 0;
 }
 
-int launch_vn(scaldpc_qary *h, const QaryDev &p, int tiles, bool last, cudaStream_t st)
+int launch_vn(scaldpc_qary *h, const QaryDev &p, int tiles, bool last, unsigned flags, cudaStream_t st)
 {
-    vn_fn vn = h->vn_reg_d ? pick_vn_reg(h->Q, h->vn_reg_d) : pick_vn(h->Q);
+    vn_fn vn = (h->vn_reg_d && !(flags & SCALDPC_CN_GENERIC)) ? pick_vn_reg(h->Q, h->vn_reg_d) : pick_vn(h->Q);
     dim3 grid((h->bvars + kVnWarps - 1) / kVnWarps, tiles);
     vn<<<grid, kVnWarps * 32, 0, st>>>(p, last);
     ++h->launches;
@@ -588,7 +588,7 @@ static int decode_on_device(scaldpc_qary *h, int T, const PriorSrc &src, int8_t 
     const int iters = std::max(1, h->max_iter);  // decoder.rs:575-663: `it` starts at 1, exit when it >= max_iter
     for (int it = 1; it <= iters; ++it) {
         if ((rc = launch_cn(h, p, tiles, it, iters, flags, st))) return rc;
-        if ((rc = launch_vn(h, p, tiles, it == iters, st))) return rc;
+        if ((rc = launch_vn(h, p, tiles, it == iters, flags, st))) return rc;
     }
     dim3 block(32, kTrRows);
     k_untile<int8_t><<<dim3((h->N + 31) / 32, tiles), block, 0, st>>>(h->d_hard_t, dhard, T, h->N);
@@ -626,8 +626,10 @@ static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *har
     // ---- host buffers: chunked pipeline.  Chunk c is copied in on s_in, decoded on `st`, copied out on s_out; the
     // two staging buffers alternate, so the H2D of chunk c+1 and the D2H of chunk c-1 overlap the decode of chunk c
     // (truly asynchronous only for pinned host memory; pageable memory degrades to the serial order, still correct).
+    // prior vectors: 8 chunks keep the PCIe link busy behind the decode; observations are ~35x smaller, so two large
+    // chunks (better-filled persistent kernels) are enough to overlap the copies
     int chunk = T;
-    if (T >= 4096) chunk = std::max(1024, (T + 7) / 8);
+    if (T >= 4096) chunk = src.observed ? (T + 1) / 2 : std::max(1024, (T + 7) / 8);
     chunk = (chunk + 31) / 32 * 32;
     const int nchunks = (T + chunk - 1) / chunk;
     if ((rc = ensure_workspace(h, chunk / 32, want_post))) return rc;
@@ -772,7 +774,7 @@ int scaldpc_qary_time_kernel(scaldpc_qary *h, int which, int T, unsigned flags, 
     // message state to a valid message state)
     for (int i = -1; i < reps && !rc; ++i) {
         if (i == 0) SCALDPC_CUDA(cudaEventRecord(e0, st));
-        rc = which == 0 ? launch_cn(h, p, tiles, 2, 4, flags, st) : launch_vn(h, p, tiles, false, st);  // middle iteration
+        rc = which == 0 ? launch_cn(h, p, tiles, 2, 4, flags, st) : launch_vn(h, p, tiles, false, flags, st);  // middle iteration
     }
     SCALDPC_CUDA(cudaEventRecord(e1, st));
     SCALDPC_CUDA(cudaEventSynchronize(e1));

@@ -116,6 +116,10 @@ def test_batched_parity_with_oracle(variant, sw, cb):
     assert np.array_equal(hard, rh)
     assert util.same_nonfinite(post, rp) and util.max_abs_diff(post, rp) < TOL
     assert util.same_nonfinite(posts, rps) and util.max_abs_diff(posts, rps) < TOL
+    # runtime-shape kernels (k_cn_generic forward/backward + k_vn, full sum-variable round trip) on the same inputs
+    gh, gp, gps = d.min_sum_batch(llr, llrs, llr=True, generic=True)
+    assert np.array_equal(gh, rh) and util.same_nonfinite(gp, rp) and util.max_abs_diff(gp, rp) < TOL
+    assert util.same_nonfinite(gps, rps) and util.max_abs_diff(gps, rps) < TOL
     # probabilities in (into_llr on the device), device-resident tensors, asynchronous on the current stream
     th, tp, tps = d.min_sum_batch(torch.from_numpy(b.priors).cuda(), torch.from_numpy(b.priors_sum).cuda())
     torch.cuda.synchronize()
