@@ -28,6 +28,8 @@ struct scaldpc_bp {
     int class_end[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     int *d_row_ptr = nullptr, *d_col = nullptr, *d_col_ptr = nullptr, *d_vn_order = nullptr, *d_vn_desc = nullptr;
     uint32_t *d_csc_edge = nullptr;
+    int *d_edge_row = nullptr;     // E: check of every edge (first pass with shared priors)
+    float *d_first_tab = nullptr;  // E: first-iteration check-to-bit messages for syndrome bit 0 (shared priors)
     // workspace
     int cap_tiles = 0;
     bool cap_post = false, cap_prior_t = false;
@@ -346,6 +348,13 @@ int scaldpc_bp_create(int m, int n, const int32_t *row_ptr, const int32_t *col, 
         (rc = upload_vec(&h->d_col_ptr, g.col_ptr)) || (rc = upload_vec(&h->d_csc_edge, g.csc_off)) ||
         (rc = upload_vec(&h->d_vn_order, g.vn_order)) || (rc = upload_vec(&h->d_vn_desc, g.vn_desc)))
         return rc;
+    {
+        std::vector<int> edge_row(std::max(1, g.E));
+        for (int r = 0; r < m; ++r)
+            for (int e = g.row_ptr[r]; e < g.row_ptr[r + 1]; ++e) edge_row[e] = r;
+        if ((rc = upload_vec(&h->d_edge_row, edge_row))) return rc;
+    }
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_first_tab, (size_t)std::max(1, g.E) * sizeof(float)));
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_prior, (size_t)n * sizeof(float)));
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_nact, sizeof(int)));
     h->cap_counts = h->max_iter + 2;
@@ -386,6 +395,8 @@ void scaldpc_bp_destroy(scaldpc_bp *h)
     cudaFree(h->d_csc_edge);
     cudaFree(h->d_vn_order);
     cudaFree(h->d_vn_desc);
+    cudaFree(h->d_edge_row);
+    cudaFree(h->d_first_tab);
     cudaFree(h->d_prior);
     cudaFree(h->d_nact);
     cudaFree(h->d_counts);
@@ -463,7 +474,15 @@ int scaldpc_bp_decode(scaldpc_bp *h, int T, const uint8_t *synd, const double *c
     for (; it <= h->max_iter; ++it) {
         const bool last = it == h->max_iter;
         const BpDev p = view(h, cur, probs_t, want_post);
-        if ((rc = launch_cn(h, p, cur_tiles, it == 1, st))) return rc;
+        if (it == 1 && !probs_t && !getenv("SCALDPC_BP_NO_FIRST_TABLE")) {
+            // shared priors: the first check-to-bit messages differ between trials only in sign (bp_kernels.cuh)
+            k_bp_first_table<<<(h->m + 127) / 128, 128, 0, st>>>(p, h->d_first_tab);
+            k_bp_first_fill<<<dim3((h->E + 63) / 64, cur_tiles), 256, 0, st>>>(p, h->d_first_tab, h->d_edge_row, cur_tiles);
+            h->launches += 2;
+            SCALDPC_CUDA(cudaGetLastError());
+        } else if ((rc = launch_cn(h, p, cur_tiles, it == 1, st))) {
+            return rc;
+        }
         if ((rc = launch_vn(h, p, cur_tiles, st))) return rc;
         k_bp_syndrome<<<dim3((h->m + 255) / 256, cur_tiles), 256, 0, st>>>(p);
         k_bp_finish_iter<<<(cur_tiles + 255) / 256, 256, 0, st>>>(p, cur_tiles, it, early, last);

@@ -7,10 +7,12 @@ mkdir -p $out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $out/${tag}_smi.txt 2>&1
 timeout 900 python -m pytest tests -m gpu -x -q > $out/${tag}_pytest.log 2>&1; echo "pytest exit $?" >> $out/${tag}_pytest.log
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $out/${tag}_smoke.log 2>&1; echo "smoke exit $?" >> $out/${tag}_smoke.log
-for wl in kyber512 kyber768; do
+for wl in kyber512 kyber768 kyber1024; do
   timeout 600 python bench.py --workload $wl --steps 10 --warmup 3 > $out/${tag}_bench_$wl.json 2> $out/${tag}_bench_$wl.err; echo "bench $wl exit $?" >> $out/${tag}_bench_$wl.err
 done
-timeout 600 python bench.py --workload hqc128 --steps 3 --warmup 3 > $out/${tag}_bench_hqc128.json 2> $out/${tag}_bench_hqc128.err
+for wl in hqc128 hqc256; do
+  timeout 900 python bench.py --workload $wl --steps 3 --warmup 3 > $out/${tag}_bench_$wl.json 2> $out/${tag}_bench_$wl.err; echo "bench $wl exit $?" >> $out/${tag}_bench_$wl.err
+done
 # ncu: launch list (cold-cache serialised) of the default bench command
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/${tag}_launches_k512.csv \
   python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $out/${tag}_ncu_list.log 2>&1

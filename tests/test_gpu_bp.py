@@ -160,3 +160,16 @@ def test_large_batch_compaction_hqc128():
     assert np.array_equal(sub["iters"], out["iters"][pick])
     assert np.array_equal(sub["decoding"], out["decoding"][pick])
     assert (out["iters"][~conv] == 40).all()
+
+
+def test_shared_prior_first_pass_is_bit_identical(monkeypatch):
+    """k_bp_first_table + k_bp_first_fill (shared priors: the first check-to-bit messages differ between trials only
+    in sign) against k_bp_cn<FIRST>: decisions, iteration counts and posterior LLRs bit for bit."""
+    w = HqcWorkload(variant=(997, 12), W=11, R=420, rho=0.97, seed=7)
+    b = w.generate(70, seed=3)
+    d = bp_decoder(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=30, channel_probs=w.channel_probs)
+    a = d.decode_batch(b.syndromes, want_llr=True)
+    monkeypatch.setenv("SCALDPC_BP_NO_FIRST_TABLE", "1")
+    c = d.decode_batch(b.syndromes, want_llr=True)
+    assert np.array_equal(a["decoding"], c["decoding"]) and np.array_equal(a["iters"], c["iters"])
+    assert np.array_equal(a["log_prob_ratios"], c["log_prob_ratios"], equal_nan=True)
