@@ -48,6 +48,7 @@ struct scaldpc_bp {
     int cn_warps = 8, cn_occ[2] = {1, 1};
     size_t smem_cn = 0;
     int vn_occ[8] = {0};  // bit pass: resident CTAs per SM of each degree-class kernel
+    int vn_single_tiles = 64;  // at most this many tiles: one any-degree launch per bit pass (SCALDPC_BP_VN_SINGLE=n)
     bool vn_tma = false;  // SCALDPC_BP_VN_TMA=1: column gather by bulk-async copies (k_bp_vn_tma) instead of k_bp_vn.
                           // Measured on hqc128 / hqc256: 1.41 / 1.98 ms against 1.35 / 1.91 ms -- the per-lane bulk copies
                           // are serialised (one UBLKCP per lane) and four columns in flight per warp buy nothing, so
@@ -242,6 +243,14 @@ size_t vn_tma_smem(int c) { return (size_t)kBpVnWarps * kBpVnStages * kBpVnClass
 // the largest register class go through the shared-memory kernel.
 int launch_vn(scaldpc_bp *h, const BpDev &p, int tiles, cudaStream_t st)
 {
+    if (tiles <= h->vn_single_tiles) {
+        // few tiles (the non-converging tail after compaction): the iteration is bound by kernel launches, so ONE launch
+        // of the any-degree kernel over all variables replaces one launch per degree class (same arithmetic)
+        k_bp_vn_generic<<<dim3((h->n + h->vn_gen_wpc - 1) / h->vn_gen_wpc, tiles), h->vn_gen_wpc * 32, h->smem_vn, st>>>(p, 0, h->n);
+        ++h->launches;
+        SCALDPC_CUDA(cudaGetLastError());
+        return 0;
+    }
     int lo = 0;
     for (int c = 0; c <= kBpVnClasses; ++c) {
         const int hi = h->class_end[c];
@@ -334,7 +343,7 @@ int scaldpc_bp_create(int m, int n, const int32_t *row_ptr, const int32_t *col, 
     if (h->cn_warps < 1)
         return fail(SCALDPC_ERR_UNSUPPORTED, "row degree %d too large for the shared-memory staging", h->dc_max);
     h->smem_cn = per_warp * h->cn_warps;
-    if (h->dv_max > kBpVnClass[kBpVnClasses - 1]) {
+    {  // shared-memory bit-pass kernel: heavy columns, and the whole pass of small (launch-bound) batches
         const size_t pw = (size_t)2 * h->dv_max * 32 * sizeof(float);
         h->vn_gen_wpc = (int)std::min<size_t>(kBpVnWarps, (216 * 1024) / pw);
         if (h->vn_gen_wpc < 1)
@@ -365,6 +374,7 @@ int scaldpc_bp_create(int m, int n, const int32_t *row_ptr, const int32_t *col, 
     if (h->smem_vn)
         SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_vn_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_vn));
     h->vn_tma = getenv("SCALDPC_BP_VN_TMA") != nullptr;
+    if (const char *e = getenv("SCALDPC_BP_VN_SINGLE")) h->vn_single_tiles = atoi(e);
     for (int c = 0; c < kBpVnClasses; ++c) {
         if (h->vn_tma && vn_class_tma_fn(c)) {
             SCALDPC_CUDA(cudaFuncSetAttribute(vn_class_tma_fn(c), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vn_tma_smem(c)));
@@ -488,7 +498,10 @@ int scaldpc_bp_decode(scaldpc_bp *h, int T, const uint8_t *synd, const double *c
         k_bp_finish_iter<<<(cur_tiles + 255) / 256, 256, 0, st>>>(p, cur_tiles, it, early, last);
         h->launches += 2;
         SCALDPC_CUDA(cudaGetLastError());
-        if (early && !last && (it <= 4 || it % 4 == 0 || cur_tiles >= 32)) {
+        // polling = one 4-byte D2H + a stream sync (the GPU idles for the round trip, ~30 us): every iteration while most
+        // trials converge (the first four) or while the batch is large enough to hide it, then every 4th / 8th --
+        // kernels launched for tiles that have retired meanwhile exit at once
+        if (early && !last && (it <= 4 || cur_tiles >= 512 || (it <= 16 ? it % 4 == 0 : it % 8 == 0))) {
             SCALDPC_CUDA(cudaMemcpyAsync(h->h_pin, h->d_counts + it, sizeof(int), cudaMemcpyDeviceToHost, st));
             SCALDPC_CUDA(cudaStreamSynchronize(st));
             const int n_run = h->h_pin[0];
