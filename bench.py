@@ -378,6 +378,23 @@ def run_ours(args, kind, wl, iters, cfg):
             "success_rate": int(c_obs[0]) / max(1, int(c_obs[1])),
         }
 
+    # ---- latency of ONE decode through the reference-shaped call (min_sum / decode on host arrays, T = 1)
+    single = None
+    if rank == 0:
+        if kind == "qary":
+            one = lambda: dec.min_sum(batch.priors[0], batch.priors_sum[0])  # noqa: E731
+        else:
+            one = lambda: dec.decode(batch.syndromes[0])  # noqa: E731
+        for _ in range(3):
+            one()
+        t0 = time.perf_counter()
+        n_one = 50
+        for _ in range(n_one):
+            one()
+        ms_one = 1e3 * (time.perf_counter() - t0) / n_one
+        single = {"call": "min_sum(channel_output, channel_output_sum)" if kind == "qary" else "decode(syndrome)",
+                  "ms_per_call": ms_one, "trials_per_s": 1e3 / ms_one}
+
     # ---- roofline of the dominant kernel (rank 0, N=1 semantics: one GPU's kernel against one GPU's peak)
     line = None
     if rank == 0:
@@ -436,6 +453,7 @@ def run_ours(args, kind, wl, iters, cfg):
             "e2e": {"value": e2e_value, "unit": "trials/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches),
             **({"observed": observed} if observed else {}),
+            "single_decode": single,
             **({"compactions_last_step": dec.last_run()[1], "iterations_launched_last_step": dec.last_run()[0]}
                if kind == "bp" else {}),
             "roofline": roofline,

@@ -2,6 +2,7 @@
 // (include/scaldpc.h).  Replaces ldpc.bp_decoder at the call sites simulate/hqc.py:694-708 and
 // simulate/decode.py:155-171.  No CPU compute path exists here.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <mutex>

@@ -2,6 +2,7 @@
 // (include/scaldpc.h).  Replaces the reference's Rust decoder core behind the same boundary
 // (simulate_rs/src/pydecoder.rs, decoder.rs, decoder_special.rs).  No CPU compute path exists here.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <mutex>
@@ -42,6 +43,7 @@ struct scaldpc_qary {
     int wmax = 0;      // max DP table width over the checks
     int num_sms = 148;
     int fast_sw = 0;   // >0: every row is SW B-variables + 1 sum-variable with BSUM == SW*B and a template exists
+    int max_resident = 65536;  // trials decoded per pass of the device-pointer path (workspace bound: ~0.1-0.2 MB each)
     int vn_reg_d = 0;  // >0: every B-variable has exactly this degree and a register-resident k_vn_reg exists
     // device graph
     int *d_row_ptr = nullptr, *d_col = nullptr, *d_edge_off = nullptr, *d_col_ptr = nullptr;
@@ -462,6 +464,7 @@ int scaldpc_qary_create(const int8_t *H, int R, int N, int b, int bsum, int dv, 
     h->bvars = g.bvars;
     h->max_iter = max_iter;
     h->device = device;
+    if (const char *e = getenv("SCALDPC_MAX_RESIDENT_TRIALS")) h->max_resident = std::max(32, atoi(e));
     h->E = g.E;
     h->S = g.S;
     h->SL = g.SL;
@@ -615,11 +618,25 @@ static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *har
     const bool dev_ptrs = flags & SCALDPC_DEVICE_PTRS;
     int rc;
 
-    if (dev_ptrs) {  // asynchronous on `st`, one pass over the whole batch
-        const int tiles = (T + 31) / 32;
-        if ((rc = ensure_workspace(h, tiles, want_post))) return rc;
-        if ((rc = decode_on_device(h, T, src, hard, post, post_sum, flags, st))) return rc;
-        if (status) SCALDPC_CUDA(cudaMemcpyAsync(status, h->d_status, (size_t)T * sizeof(int), cudaMemcpyDeviceToDevice, st));
+    if (dev_ptrs) {  // asynchronous on `st`; at most `max_resident` trials' messages live in the workspace at a time
+        const int cap = std::max(32, h->max_resident / 32 * 32);
+        if ((rc = ensure_workspace(h, (std::min(T, cap) + 31) / 32, want_post))) return rc;
+        for (int t0 = 0; t0 < T; t0 += cap) {
+            const int tc = std::min(cap, T - t0);
+            PriorSrc part = src;
+            if (src.observed) {
+                part.obs = src.obs + (size_t)t0 * h->bvars;
+                part.obs_sum = src.obs_sum ? src.obs_sum + (size_t)t0 * h->R : nullptr;
+            } else {
+                part.in = src.in + (size_t)t0 * h->SL;
+                part.in_sum = src.in_sum ? src.in_sum + (size_t)t0 * h->SLS : nullptr;
+            }
+            if ((rc = decode_on_device(h, tc, part, hard + (size_t)t0 * h->N, post ? post + (size_t)t0 * h->SL : nullptr,
+                                       post_sum ? post_sum + (size_t)t0 * h->SLS : nullptr, flags, st)))
+                return rc;
+            if (status)
+                SCALDPC_CUDA(cudaMemcpyAsync(status + t0, h->d_status, (size_t)tc * sizeof(int), cudaMemcpyDeviceToDevice, st));
+        }
         return 0;
     }
 

@@ -265,3 +265,18 @@ def test_observed_priors_equal_expanded_priors():
     # empty batch
     h0, _, _ = d.min_sum_observed(w.table, b.obs[:0], w.table_sum, b.obs_sum[:0])
     assert h0.shape == (0, w.N)
+
+
+def test_device_path_bounds_its_workspace(monkeypatch):
+    """Device-pointer batches larger than the resident-trial cap are decoded in passes; results do not change."""
+    import torch
+
+    w = KyberWorkload("kyber768", sum_weight=6, check_blocks=1, accuracy=0.95, nbits=3, nbits_sum=4, seed=2)
+    b = w.generate(150, seed=8)
+    pri, pris = torch.from_numpy(b.priors).cuda(), torch.from_numpy(b.priors_sum).cuda()
+    ref = QaryDecoder(w.H, 4, **w.decoder_kwargs).min_sum_batch(pri, pris, want_status=True)
+    monkeypatch.setenv("SCALDPC_MAX_RESIDENT_TRIALS", "64")
+    got = QaryDecoder(w.H, 4, **w.decoder_kwargs).min_sum_batch(pri, pris, want_status=True)
+    torch.cuda.synchronize()
+    for a, c in zip(ref, got):
+        assert np.array_equal(a.cpu().numpy(), c.cpu().numpy(), equal_nan=True)
