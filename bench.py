@@ -394,6 +394,17 @@ def run_ours(args, kind, wl, iters, cfg):
         ms_one = 1e3 * (time.perf_counter() - t0) / n_one
         single = {"call": "min_sum(channel_output, channel_output_sum)" if kind == "qary" else "decode(syndrome)",
                   "ms_per_call": ms_one, "trials_per_s": 1e3 / ms_one}
+        if kind == "qary":  # the reference's FER loop: one decoder object, a ThreadPoolExecutor (decode.py:247-262)
+            from concurrent.futures import ThreadPoolExecutor
+
+            nthr, ncall = 16, 1024
+            with ThreadPoolExecutor(max_workers=nthr) as ex:
+                list(ex.map(lambda i: dec.min_sum(batch.priors[i], batch.priors_sum[i]), range(64)))
+                t0 = time.perf_counter()
+                list(ex.map(lambda i: dec.min_sum(batch.priors[i], batch.priors_sum[i]), range(ncall)))
+                single["threadpool"] = {"threads": nthr, "calls": ncall,
+                                        "trials_per_s": ncall / (time.perf_counter() - t0),
+                                        "note": "concurrent min_sum() calls on one decoder are combined into batches"}
 
     # ---- roofline of the dominant kernel (rank 0, N=1 semantics: one GPU's kernel against one GPU's peak)
     line = None

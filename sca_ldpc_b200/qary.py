@@ -26,6 +26,21 @@ def _is_torch(x) -> bool:
     return torch is not None and isinstance(x, torch.Tensor)
 
 
+_STATUS_TEXT = {
+    _lib.ERR_PROB_SUM: "a prior row does not sum to 1 +- 0.001 (decoder.rs:683-684)",
+    _lib.ERR_NO_MAX: "No maximum probability found (decoder.rs:680)",
+    _lib.ERR_NO_CONFIG: "a check has no valid configuration (decoder.rs:618)",
+}
+
+
+class _Request:
+    """One min_sum() call waiting to be decoded as part of a combined batch."""
+    __slots__ = ("co", "cos", "result", "error", "done")
+
+    def __init__(self, co, cos):
+        self.co, self.cos, self.result, self.error, self.done = co, cos, None, None, threading.Event()
+
+
 class QaryDecoder:
     """q-ary min-sum decoder on one B200.
 
@@ -53,6 +68,8 @@ class QaryDecoder:
         H = np.ascontiguousarray(H)
         self._h = C.c_void_p()
         self._lock = threading.Lock()
+        self._qlock = threading.Lock()
+        self._pending, self._leading = [], False  # min_sum() requests waiting for the next combined batch
         _lib.check(_lib.lib().scaldpc_qary_create(H.ctypes.data, R, N, int(B), int(BSUM), int(DV), int(DC),
                                                   int(iterations), int(device), C.byref(self._h)))
         vals = [C.c_int() for _ in range(7)]
@@ -78,8 +95,43 @@ class QaryDecoder:
             cos = self._one(channel_output_sum, self.R, self.QS, "channel_output_sum")
         elif channel_output_sum is not None:
             raise TypeError("min_sum() takes 1 positional argument but 2 were given")
-        hard, _, _ = self.min_sum_batch(co[None], None if cos is None else cos[None], want_posterior=False)
-        return [int(x) for x in hard[0]]
+        # Concurrent callers are COMBINED: the reference calls one decoder object from a ThreadPoolExecutor
+        # (simulate/decode.py:247-262, GIL released in pydecoder.rs:55).  Whichever thread finds no batch in progress
+        # becomes the leader and decodes every request queued so far as one batch (a tile holds 32 trials, so 32
+        # concurrent decodes cost what one costs); the others wait for their row of the result.
+        req = _Request(co, cos)
+        with self._qlock:
+            self._pending.append(req)
+            leader = not self._leading
+            if leader:
+                self._leading = True
+        if leader:
+            while True:
+                with self._qlock:
+                    batch, self._pending = self._pending, []
+                    if not batch:
+                        self._leading = False
+                        break
+                try:
+                    x = np.stack([r.co for r in batch])
+                    xs = np.stack([r.cos for r in batch]) if self.special else None
+                    hard, _, _, status = self.min_sum_batch(x, xs, want_posterior=False, want_status=True)
+                    for i, r in enumerate(batch):
+                        if status[i] == 0:
+                            r.result = hard[i].tolist()  # Python ints, like the pyo3 return value
+                        else:  # the reference panics in THAT call only (decoder.rs:618, 680, 683-684)
+                            r.error = ValueError(_STATUS_TEXT.get(int(status[i]), f"libscaldpc status {int(status[i])}"))
+                except BaseException as e:  # noqa: BLE001 -- every waiter must be released
+                    for r in batch:
+                        if r.result is None and r.error is None:
+                            r.error = e
+                finally:
+                    for r in batch:
+                        r.done.set()
+        req.done.wait()
+        if req.error is not None:
+            raise req.error
+        return req.result
 
     @staticmethod
     def _one(x, rows, q, name):

@@ -280,3 +280,30 @@ def test_device_path_bounds_its_workspace(monkeypatch):
     torch.cuda.synchronize()
     for a, c in zip(ref, got):
         assert np.array_equal(a.cpu().numpy(), c.cpu().numpy(), equal_nan=True)
+
+
+def test_concurrent_min_sum_calls_are_combined():
+    """simulate/decode.py:247-262 drives ONE decoder object from a thread pool; concurrent min_sum() calls are decoded
+    as combined batches and every caller gets its own result (or its own error)."""
+    w = KyberWorkload("kyber768", sum_weight=6, check_blocks=1, accuracy=0.95, nbits=3, nbits_sum=4, seed=6)
+    b = w.generate(96, seed=2)
+    d = simulate_rs.DecoderN1024R256SW6(w.H, 4)
+    ref, _, _ = d.min_sum_batch(b.priors, b.priors_sum, want_posterior=False)
+    bad = b.priors[5].copy()
+    bad[3] *= 0.5  # decoder.rs:683-684: this call, and only this call, must fail
+
+    def call(i):
+        if i == 5:
+            with pytest.raises(ValueError):
+                d.min_sum(bad, b.priors_sum[5])
+            return None
+        return d.min_sum(b.priors[i], b.priors_sum[i])
+
+    n0 = d.launch_count
+    with ThreadPoolExecutor(max_workers=16) as ex:
+        out = list(ex.map(call, range(96)))
+    for i, o in enumerate(out):
+        if i != 5:
+            assert o == ref[i].tolist(), i
+    per_batch = 2 + 2 * 4 + 1  # k_load_priors x2, (check + variable pass) x4, k_untile
+    assert (d.launch_count - n0) < 96 * per_batch  # fewer batches than calls: calls were combined
