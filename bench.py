@@ -44,6 +44,9 @@ WORKLOADS = {
     "kyber1024": ("qary", dict(variant="kyber1024", sum_weight=8, check_blocks=1, accuracy=0.98, nbits=5, nbits_sum=6), 12_500, 10),
     # binary batches: large enough that the ~8 % of trials that never converge (and run all 100 iterations on a few
     # tiles after compaction) do not dominate: 4096 -> 250k, 16384 -> 342k, 32768 -> 357k trials/s on hqc128 (measured)
+    # the reference's own criterion case (simulate_rs/benches/decoder.rs "medium decoder"): generic Decoder<450,150,3,7,15,7>
+    "decoder450": ("qary", dict(generic=True), 10_000, 10),
+    "hqc192": ("bp", dict(variant="hqc192", W=50, R=5000, rho=0.9942), 8192, 100),
     "hqc128": ("bp", dict(variant="hqc128", W=50, R=3000, rho=0.9942), 16384, 100),
     "hqc256": ("bp", dict(variant="hqc256", W=50, R=8000, rho=0.9942), 8192, 100),
 }
@@ -155,6 +158,8 @@ def cpu_path(kind, wl, iters, trials, threads, warm_only=False):
 def cpu_sample_size(kind, cores, per_step=False):
     # q-ary: the reference's brute-force check node costs 1-3.5 s per decode and core -> 4 decodes per thread is a
     # 4-14 s sample.  binary: ~5 ms per decode and core -> 512 decodes per thread (~3 s + generating the syndromes).
+    if kind == "qary-generic":  # near-deterministic priors: the finite-support enumeration is ~1.5 ms per decode
+        return (500 if per_step else 4000) * cores
     if per_step:  # --impl reference: one step of K; K steps must stay within a few minutes
         return cores if kind == "qary" else 128 * cores
     return 4 * cores if kind == "qary" else 512 * cores
@@ -167,7 +172,7 @@ def run_reference(args, kind, wl, iters, cfg):
     if rank != 0:
         return
     cores = O.max_threads()
-    n = cpu_sample_size(kind, cores, per_step=True)
+    n = cpu_sample_size("qary-generic" if getattr(wl, "BSUM", 1) == 0 else kind, cores, per_step=True)
     for _ in range(args.warmup):  # warm-up: thread pool, page-in (one iteration of one decode per thread)
         cpu_path(kind, wl, iters, min(n, cores), cores, warm_only=True)
     total_t, total_n = 0.0, 0
@@ -220,38 +225,48 @@ def run_ours(args, kind, wl, iters, cfg):
     batch = wl.generate(T, seed=seed)
     if kind == "qary":
         dec = QaryDecoder(wl.H, iters, device=local, **wl.decoder_kwargs)
-        h_in = [torch.from_numpy(batch.priors).pin_memory(), torch.from_numpy(batch.priors_sum).pin_memory()]
-        d_in = [t.to(dev) for t in h_in]
+        special = dec.special
+        h_in = [torch.from_numpy(batch.priors).pin_memory()]
+        if special:
+            h_in.append(torch.from_numpy(batch.priors_sum).pin_memory())
+        d_in = [t.to(dev) for t in h_in] + [None]
+        h_np = [t.numpy() for t in h_in] + [None]
         secret = torch.from_numpy(batch.secret).to(dev)
-        nssum = torch.from_numpy((-batch.ssum).astype(np.int8)).to(dev)
+        nssum = torch.from_numpy((-batch.ssum).astype(np.int8)).to(dev) if special else None
         bv = wl.bvars
+
+        def count(hard):
+            ok = (hard[:, :bv] == secret).all(1)
+            if special:
+                ok = ok & (hard[:, bv:] == nssum).all(1)
+            return torch.stack((ok.sum(), torch.tensor(T, device=dev)))
 
         def step_dev():
             hard, _, _ = dec.min_sum_batch(d_in[0], d_in[1], want_posterior=False)
-            ok = (hard[:, :bv] == secret).all(1) & (hard[:, bv:] == nssum).all(1)
-            return torch.stack((ok.sum(), torch.tensor(T, device=dev)))
+            return count(hard)
 
         h_out = torch.empty((T, wl.N), dtype=torch.int8).pin_memory().numpy()  # pinned result buffer (D2H target)
 
         def step_host():
-            hard, _, _ = dec.min_sum_batch(h_in[0].numpy(), h_in[1].numpy(), want_posterior=False, out=h_out)
+            hard, _, _ = dec.min_sum_batch(h_np[0], h_np[1], want_posterior=False, out=h_out)
             return hard
 
         # the same trials as oracle observations: row indices + prior tables instead of vectors
-        ob = wl.generate_observed(T, seed=seed)
-        h_obs = [torch.from_numpy(ob.obs.view(np.int16)).pin_memory(), torch.from_numpy(ob.obs_sum.view(np.int16)).pin_memory()]
-        d_obs = [t.to(dev) for t in h_obs]
-        d_tab = [torch.from_numpy(wl.table).to(dev), torch.from_numpy(wl.table_sum).to(dev)]
+        has_observed = hasattr(wl, "generate_observed")
+        ob = wl.generate_observed(T, seed=seed) if has_observed else None
+        if has_observed:
+            h_obs = [torch.from_numpy(ob.obs.view(np.int16)).pin_memory(), torch.from_numpy(ob.obs_sum.view(np.int16)).pin_memory()]
+            d_obs = [t.to(dev) for t in h_obs]
+            d_tab = [torch.from_numpy(wl.table).to(dev), torch.from_numpy(wl.table_sum).to(dev)]
 
-        def step_dev_obs():
-            hard, _, _ = dec.min_sum_observed(d_tab[0], d_obs[0], d_tab[1], d_obs[1])
-            ok = (hard[:, :bv] == secret).all(1) & (hard[:, bv:] == nssum).all(1)
-            return torch.stack((ok.sum(), torch.tensor(T, device=dev)))
+            def step_dev_obs():
+                hard, _, _ = dec.min_sum_observed(d_tab[0], d_obs[0], d_tab[1], d_obs[1])
+                return count(hard)
 
-        def step_host_obs():
-            hard, _, _ = dec.min_sum_observed(wl.table, h_obs[0].numpy().view(np.uint16), wl.table_sum,
-                                              h_obs[1].numpy().view(np.uint16), out=h_out)
-            return hard
+            def step_host_obs():
+                hard, _, _ = dec.min_sum_observed(wl.table, h_obs[0].numpy().view(np.uint16), wl.table_sum,
+                                                  h_obs[1].numpy().view(np.uint16), out=h_out)
+                return hard
 
         h2d = sum(t.numel() * t.element_size() for t in h_in)
         d2h = T * wl.N
@@ -262,6 +277,7 @@ def run_ours(args, kind, wl, iters, cfg):
         # reads the sum-variable priors; the sum-variables' own messages never travel
         cn_bytes = 8 * (dec.msg_slots - (dec.R * dec.QS if dec.special else 0)) + 4 * (dec.R * dec.QS if dec.special else 0)
         vn_bytes = 8 * (dec.msg_slots - (dec.R * dec.QS if dec.special else 0)) + 4 * dec.bvars * dec.Q
+        cn_name = "k_cn_fast (check-node pass)" if special else "k_cn_generic (check-node pass, runtime shape)"
     else:
         dec = bp_decoder(csr=(wl.row_ptr, wl.col), shape=(wl.m, wl.n), max_iter=iters, channel_probs=wl.channel_probs,
                          device=local)
@@ -347,7 +363,7 @@ def run_ours(args, kind, wl, iters, cfg):
 
     # ---- the same trials fed as oracle observations (q-ary only): device-resident and host-buffer throughput
     observed = None
-    if kind == "qary":
+    if kind == "qary" and has_observed:
         for _ in range(3):
             c_obs = step_dev_obs()
         sync_all()
@@ -382,7 +398,7 @@ def run_ours(args, kind, wl, iters, cfg):
     single = None
     if rank == 0:
         if kind == "qary":
-            one = lambda: dec.min_sum(batch.priors[0], batch.priors_sum[0])  # noqa: E731
+            one = (lambda: dec.min_sum(batch.priors[0], batch.priors_sum[0])) if special else (lambda: dec.min_sum(batch.priors[0]))
         else:
             one = lambda: dec.decode(batch.syndromes[0])  # noqa: E731
         for _ in range(3):
@@ -399,9 +415,10 @@ def run_ours(args, kind, wl, iters, cfg):
 
             nthr, ncall = 16, 1024
             with ThreadPoolExecutor(max_workers=nthr) as ex:
-                list(ex.map(lambda i: dec.min_sum(batch.priors[i], batch.priors_sum[i]), range(64)))
+                call = (lambda i: dec.min_sum(batch.priors[i], batch.priors_sum[i])) if special else (lambda i: dec.min_sum(batch.priors[i]))
+                list(ex.map(call, range(64)))
                 t0 = time.perf_counter()
-                list(ex.map(lambda i: dec.min_sum(batch.priors[i], batch.priors_sum[i]), range(ncall)))
+                list(ex.map(call, range(ncall)))
                 single["threadpool"] = {"threads": nthr, "calls": ncall,
                                         "trials_per_s": ncall / (time.perf_counter() - t0),
                                         "note": "concurrent min_sum() calls on one decoder are combined into batches"}
@@ -418,7 +435,7 @@ def run_ours(args, kind, wl, iters, cfg):
         achieved = T * cn_bytes / (cn_ms * 1e-3) / 1e9
         vn_achieved = T * vn_bytes / (vn_ms * 1e-3) / 1e9
         roofline = {
-            "bound": "hbm", "kernel": "k_cn_fast (check-node pass)" if kind == "qary" else "k_bp_cn (check-to-bit pass)",
+            "bound": "hbm", "kernel": cn_name if kind == "qary" else "k_bp_cn (check-to-bit pass)",
             "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
             "peak_source": peak_src, "ms_per_launch": cn_ms, "algorithmic_bytes_per_launch": T * cn_bytes,
             "second_kernel": {"kernel": "k_vn" if kind == "qary" else "k_bp_vn", "achieved": vn_achieved,
@@ -447,7 +464,7 @@ def run_ours(args, kind, wl, iters, cfg):
             from oracle import oracle as O
 
             cores = O.max_threads()
-            n = cpu_sample_size(kind, cores)
+            n = cpu_sample_size("qary-generic" if getattr(wl, "BSUM", 1) == 0 else kind, cores)
             v, secs, _ = cpu_path(kind, wl, iters, n, cores)
             cpu = {"value": v, "unit": "trials/s", "cores": cores, "kind": "port",
                    "sample": f"{n} trials of this workload, one decode at a time per thread "
@@ -494,8 +511,21 @@ def main():
     kind, kw, T, iters = WORKLOADS[args.workload]
     args.trials = args.trials or T
     iters = args.iters or iters
-    wl = KyberWorkload(seed=0, **kw) if kind == "qary" else HqcWorkload(seed=0, **kw)
-    if kind == "qary":
+    if kw.get("generic"):
+        from sca_ldpc_b200.workloads import DecoderBenchWorkload
+
+        z = np.load(os.path.join(ROOT, "tests", "golden", "rust_unit_tests.npz"))  # benches/parity_check_150_450.txt
+        Hm = np.zeros(tuple(int(x) for x in z["Hm_shape"]), np.int8)
+        Hm[z["Hm_rows"], z["Hm_cols"]] = z["Hm_vals"]
+        wl = DecoderBenchWorkload(Hm, B=7)
+    else:
+        wl = KyberWorkload(seed=0, **kw) if kind == "qary" else HqcWorkload(seed=0, **kw)
+    if kw.get("generic"):
+        cfg = {"workload": f"{args.workload}: generic q-ary min-sum decoder Decoder<450,150,3,7,15,7> on the reference's criterion "
+                           f"input (benches/decoder.rs:38-62), {args.trials} trials per GPU per step, {iters} iterations",
+               "trials_per_gpu": args.trials, "iterations": iters, "edges": int((wl.H != 0).sum()),
+               "check_node": "forward/backward (min,+), runtime-shape kernel", "inputs": "larger than L2", "oracle_accuracy": None}
+    elif kind == "qary":
         cfg = {"workload": f"{args.workload}: q-ary min-sum BP, H {wl.R}x{wl.N} (sum_weight {wl.sum_weight}, "
                            f"check_blocks {wl.check_blocks}), alphabets {wl.Q}/{wl.QS}, {args.trials} trials per GPU per step, "
                            f"{iters} iterations, no early termination (reference semantics)",

@@ -24,7 +24,7 @@ struct HostGraph {
     int SL = 0;      // bvars * Q
     int SLS = 0;     // R * QS (special decoder) or 0
     int lmax = 0;    // max row degree
-    int wmax = 0;    // max DP table width 2 * (sum of a check's alphabets) + 1
+    int wmax = 0;    // max DP table width 2 * hh + 1, hh = max_k min(sum of a check's first k alphabets, sum of the others)
     int regular_sw = 0;  // >0: every check is exactly `regular_sw` B-variables + its sum-variable, BSUM == sw*B
     std::vector<int> row_ptr, col, edge_off, col_ptr;
     std::vector<int8_t> sign;
@@ -94,7 +94,14 @@ inline int build_graph(const int8_t *H, int R, int N, int b, int bsum, int dv, i
             return bad(SCALDPC_ERR_NO_CONFIG, where + "no variables (decoder.rs:327 underflow panic)");
         }
         g.lmax = std::max(g.lmax, L);
-        g.wmax = std::max(g.wmax, 2 * tot + 1);
+        {  // half-width of the DP tables (k_cn_generic): max over k of min(first k alphabets, the others)
+            int hh = 0, pre = 0;
+            for (int k = 0; k < L; ++k) {
+                pre += (g.col[g.row_ptr[r] + k] >= g.bvars) ? bsum : b;
+                hh = std::max(hh, std::min(pre, tot - pre));
+            }
+            g.wmax = std::max(g.wmax, 2 * hh + 1);
+        }
     }
     g.row_ptr[R] = (int)g.col.size();
     g.edge_off.push_back(slots);

@@ -274,9 +274,16 @@ __global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGene
 #define TA_(u) sA[(u)*32]
 #define TB_(u) sB[(u)*32]
 
-    // alphabets and total range of this check
+    // Half-width of the DP tables: a partial sum after k variables matters only if the remaining ones can bring it back
+    // to 0, |u| <= min(sum of the first k alphabets, sum of the others); `tot` = the largest such bound over k is the
+    // centre offset of every table (a uniform window: entries outside it belong to no valid configuration).
+    int all = 0;
+    for (int k = 0; k < L; ++k) all += (__ldg(p.col + e0 + k) >= p.bvars) ? p.BSUM : p.B;
     int tot = 0;
-    for (int k = 0; k < L; ++k) tot += (__ldg(p.col + e0 + k) >= p.bvars) ? p.BSUM : p.B;
+    for (int k = 0, pre = 0; k < L; ++k) {
+        pre += (__ldg(p.col + e0 + k) >= p.bvars) ? p.BSUM : p.B;
+        tot = max(tot, min(pre, all - pre));
+    }
     const int W = 2 * tot + 1;  // <= g.W
 
     // ---- load inputs (sanitised copies in scratch)

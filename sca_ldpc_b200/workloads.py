@@ -168,6 +168,45 @@ class KyberWorkload:
 
 
 # -----------------------------------------------------------------------------------------------------------------
+# The reference's own micro-benchmark input (simulate_rs/benches/decoder.rs:38-62, "medium decoder"): the generic
+# single-alphabet Decoder<450,150,3,7,15,7>, all-zero message, ONE corrupted symbol (0.1 on 0, 0.9 on +7).
+# -----------------------------------------------------------------------------------------------------------------
+@dataclass
+class GenericBatch:
+    priors: np.ndarray       # (T, N, Q) float32
+    priors_sum: None
+    secret: np.ndarray       # (T, N) int8: the transmitted word (all zero)
+
+
+class DecoderBenchWorkload:
+    """H = benches/parity_check_150_450.txt (passed in as a dense int8 matrix), B = 7; trial t corrupts symbol
+    1 + (t mod (N-1))' -- the criterion input is trial 0."""
+
+    def __init__(self, H, B=7, seed=0):
+        self.H = np.ascontiguousarray(H, dtype=np.int8)
+        self.R, self.N = self.H.shape
+        self.bvars, self.B, self.BSUM = self.N, B, 0
+        self.Q, self.QS = 2 * B + 1, 0
+        self.sum_weight, self.check_blocks, self.accuracy = int((self.H != 0).sum(1).max()) - 1, 0, 0.9  # DC = sum_weight + 1
+
+    @property
+    def decoder_kwargs(self):
+        return dict(B=self.B, DV=3, DC=7)
+
+    def generate(self, T: int, seed=0) -> GenericBatch:
+        pri = np.zeros((T, self.N, self.Q), np.float32)
+        pri[:, :, self.B] = 1.0
+        pos = (1 + (np.arange(T) + seed) % (self.N - 1)) if T > 1 else np.array([1])
+        pri[np.arange(T), pos, self.B] = 0.1
+        pri[np.arange(T), pos, 2 * self.B] = 0.9
+        return GenericBatch(pri, None, np.zeros((T, self.N), np.int8))
+
+    @staticmethod
+    def success(batch, hard):
+        return (hard == batch.secret).all(1)
+
+
+# -----------------------------------------------------------------------------------------------------------------
 # HQC (binary) workload: shared sparse graph, T independent noise realisations   (SURVEY.md 8(d) configs 4, 5)
 # -----------------------------------------------------------------------------------------------------------------
 HQC = {  # N, omega          dependencies/liboqs-rs-bindings/src/hqc.rs:346-352, 378-384, 410-416
