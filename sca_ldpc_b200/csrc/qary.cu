@@ -43,6 +43,7 @@ struct scaldpc_qary {
     int wmax = 0;      // max DP table width over the checks
     int num_sms = 148;
     int fast_sw = 0;   // >0: every row is SW B-variables + 1 sum-variable with BSUM == SW*B and a template exists
+    bool uniform_ok = false;   // generic decoder with a k_cn_uniform<Q> instantiation whose tables fit shared memory
     int max_resident = 65536;  // trials decoded per pass of the device-pointer path (workspace bound: ~0.1-0.2 MB each)
     int vn_reg_d = 0;  // >0: every B-variable has exactly this degree and a register-resident k_vn_reg exists
     // device graph
@@ -355,6 +356,25 @@ vn_fn pick_vn_reg(int q, int d)
     return nullptr;
 }
 
+typedef void (*cn_uniform_fn)(const QaryDev, const int, const int);
+cn_uniform_fn pick_cn_uniform(int q)
+{
+    switch (q) {
+#define CASE(Q_) \
+    case Q_:     \
+        return k_cn_uniform<Q_>;
+        CASE(3) CASE(5) CASE(7) CASE(9) CASE(11) CASE(13) CASE(15)
+#undef CASE
+    default:
+        return nullptr;
+    }
+}
+size_t uniform_smem_bytes(const scaldpc_qary *h)
+{
+    const int hh = (h->wmax - 1) / 2, wp = 2 * (hh + h->B) + 1;
+    return ((size_t)h->lmax * h->Q + (size_t)(h->lmax + 1) * wp + 2 * (size_t)wp) * 32 * sizeof(float);
+}
+
 size_t generic_smem_bytes(const scaldpc_qary *h, CnGenericArgs *g)
 {
     g->QM = std::max(h->Q, h->QS);
@@ -376,6 +396,15 @@ int launch_cn(scaldpc_qary *h, const QaryDev &p, int tiles, int it, int iters, u
         const int n_items = tiles * h->R;
         const int grid = std::max(1, std::min(h->num_sms, (n_items + kCnWarps - 1) / kCnWarps));
         fast->fn[cn_mode_index(it, iters)]<<<grid, kCnWarps * 32, fast->smem, st>>>(p, n_items);
+        ++h->launches;
+    } else if (h->BSUM == 0 && !exact && !force_generic && h->uniform_ok) {
+        // generic decoder, one alphabet: the unrolled / padded forward-backward kernel
+        if (first) {
+            dim3 grid((h->E + 7) / 8, tiles);
+            k_init_v2c<<<grid, 256, 0, st>>>(p, h->E);
+            ++h->launches;
+        }
+        pick_cn_uniform(h->Q)<<<dim3(h->R, tiles), 32, uniform_smem_bytes(h), st>>>(p, h->lmax, (h->wmax - 1) / 2);
         ++h->launches;
     } else {
         if (first) {
@@ -495,6 +524,11 @@ int scaldpc_qary_create(const int8_t *H, int R, int N, int b, int bsum, int dv, 
     if ((rc = upload(&h->d_row_ptr, row_ptr)) || (rc = upload(&h->d_col, col)) || (rc = upload(&h->d_sign, sign)) ||
         (rc = upload(&h->d_edge_off, edge_off)) || (rc = upload(&h->d_col_ptr, col_ptr)) || (rc = upload(&h->d_csc, csc)))
         return rc;
+    if (h->BSUM == 0 && pick_cn_uniform(h->Q) && uniform_smem_bytes(h.get()) <= 227 * 1024) {
+        h->uniform_ok = true;
+        SCALDPC_CUDA(cudaFuncSetAttribute(pick_cn_uniform(h->Q), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)uniform_smem_bytes(h.get())));
+    }
     {
         CnGenericArgs g;
         const size_t smem = generic_smem_bytes(h.get(), &g);

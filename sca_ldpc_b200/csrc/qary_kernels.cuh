@@ -428,6 +428,102 @@ __global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGene
 }
 
 // -----------------------------------------------------------------------------------------------------------
+// Check node of the GENERIC decoder (decoder.rs:585-631) when every variable has the same alphabet [-B, B]
+// (BSUM == 0): k_cn_generic's forward/backward algorithm with the alphabet as a template parameter -- inner loops
+// over the Q values fully unrolled, tables padded by B entries of +inf on both sides so that no index is ever
+// tested, every stage restricted to the partial sums that can still return to 0 (|u| <= r_k = min(sum of the first k
+// alphabets, sum of the others)).  One warp = (tile, check), lane = trial, tables in shared memory as [index][lane].
+//   forward   P_0 = {0: 0},  P_{k+1}[u] = min_d P_k[u - d] + a_k[d]
+//   backward  G_L = {0: 0},  G_j[t] = min_d a_j[d] + G_{j+1}[t - d]          (t = total of variables j .. L-1)
+//   output    c2v_j[d] = min_u P_j[u] + G_{j+1}[-u - d],  +inf where a_j[d] is not finite (decoder.rs:307-311)
+// A trial whose check has no finite configuration gets SCALDPC_ERR_NO_CONFIG (decoder.rs:618).
+// The reference's criterion case (benches/decoder.rs, Decoder<450,150,3,7,15,7>, 10^4 trials): k_cn_generic 202 ms per
+// launch (full-range tables, one warp per SM), 30 ms with the reachable window, 6.9 ms here (u loops unrolled by 2 for
+// loads in flight: two 86 KB CTAs per SM leave the pass bound by shared-memory latency).
+// -----------------------------------------------------------------------------------------------------------
+template <int Q>
+__global__ void __launch_bounds__(32) k_cn_uniform(const QaryDev p, const int LMAX, const int HH)
+{
+    SCALDPC_DYN_SMEM(float, smem);
+    constexpr int B = (Q - 1) / 2;
+    const float INF = SC_INF;
+    const int lane = threadIdx.x;
+    const int check = blockIdx.x, tile = blockIdx.y;
+    const int e0 = __ldg(p.row_ptr + check), L = __ldg(p.row_ptr + check + 1) - e0;
+    if (L <= 0) return;
+    float *msg = p.msg + (size_t)tile * p.S * 32 + lane;
+    const int WP = 2 * (HH + B) + 1;  // padded table width; index of partial sum u is u + HH + B
+    float *sA = smem + lane;                          // [L][Q]
+    float *sP = sA + (size_t)LMAX * Q * 32;           // [L+1][WP]
+    float *sG = sP + (size_t)(LMAX + 1) * WP * 32;    // [2][WP]
+#define UA_(k, i) sA[((k)*Q + (i)) * 32]
+#define UP_(k, u) sP[((k)*WP + (u) + HH + B) * 32]
+#define UG_(b, u) sG[((b)*WP + (u) + HH + B) * 32]
+    const int all = L * B;
+    auto reach = [&](int k) { return min(min(k * B, all - k * B), HH); };  // r_k
+
+    for (int k = 0; k < L; ++k) {
+        const int off = __ldg(p.edge_off + e0 + k);
+#pragma unroll
+        for (int i = 0; i < Q; ++i) UA_(k, i) = sanitize(msg[(size_t)(off + i) * 32]);
+    }
+    for (int i = 0; i < (L + 1) * WP; ++i) sP[(size_t)i * 32] = INF;
+    for (int i = 0; i < 2 * WP; ++i) sG[(size_t)i * 32] = INF;
+
+    // ---- forward
+    UP_(0, 0) = 0.0f;
+    for (int k = 0; k < L; ++k) {
+        float a[Q];
+#pragma unroll
+        for (int i = 0; i < Q; ++i) a[i] = UA_(k, i);
+        const int r = reach(k + 1);
+#pragma unroll 2
+        for (int u = -r; u <= r; ++u) {
+            MinAcc acc;
+#pragma unroll
+            for (int i = 0; i < Q; ++i) acc.add(UP_(k, u - (i - B)) + a[i]);
+            UP_(k + 1, u) = acc.get();
+        }
+    }
+    if (!(UP_(L, 0) < INF)) atomicMin(p.status + tile * 32 + lane, SCALDPC_ERR_NO_CONFIG);
+
+    // ---- backward + combine; G_{j+1} lives in sG[cur]
+    int cur = 0;
+    UG_(0, 0) = 0.0f;
+    for (int j = L - 1; j >= 0; --j) {
+        float a[Q];
+#pragma unroll
+        for (int i = 0; i < Q; ++i) a[i] = UA_(j, i);
+        const int r = reach(j);
+        MinAcc out[Q];
+#pragma unroll 2
+        for (int u = -r; u <= r; ++u) {
+            const float f = UP_(j, u);
+#pragma unroll
+            for (int i = 0; i < Q; ++i) out[i].add(f + UG_(cur, -u - (i - B)));
+        }
+        const int offj = __ldg(p.edge_off + e0 + j);
+#pragma unroll
+        for (int i = 0; i < Q; ++i) msg[(size_t)(offj + i) * 32] = (a[i] < INF) ? out[i].get() : INF;
+        if (j > 0) {
+            const int nxt = cur ^ 1;
+            for (int i = 0; i < WP; ++i) sG[((size_t)nxt * WP + i) * 32] = INF;
+#pragma unroll 2
+            for (int t = -r; t <= r; ++t) {
+                MinAcc acc;
+#pragma unroll
+                for (int i = 0; i < Q; ++i) acc.add(a[i] + UG_(cur, t - (i - B)));
+                UG_(nxt, t) = acc.get();
+            }
+            cur = nxt;
+        }
+    }
+#undef UA_
+#undef UP_
+#undef UG_
+}
+
+// -----------------------------------------------------------------------------------------------------------
 // Layout conversion kernels (host row-major [T][n] <-> tile layout [tile][n][32]) with a shared-memory transpose
 // so both sides are coalesced.  k_load_priors also applies into_llr (decoder.rs:668-692).
 // -----------------------------------------------------------------------------------------------------------

@@ -189,6 +189,14 @@ int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
         if (fast) {
             // persistent kernel: a deliberately small grid, so every warp strides over several items
             run_grid(3, 1, kCnWarps * 32, pick_cn_fast(g.regular_sw, b, it, iters), p, tiles * g.R);
+        } else if (g.BSUM == 0 && !exact && !force_generic && (g.Q == 3 || g.Q == 15)) {
+            // generic decoder, one alphabet: k_cn_uniform<Q>, as launch_cn chooses it (qary.cu)
+            if (first) run_grid((g.E + 7) / 8, tiles, 256, k_init_v2c, p, g.E);
+            std::vector<float> us(((size_t)g.lmax * g.Q + (size_t)(g.lmax + 2 + 1) * (g.wmax + 2 * g.B)) * 32);
+            scaldpc_host_model_smem = us.data();
+            if (g.Q == 3) run_grid(g.R, tiles, 32, k_cn_uniform<3>, p, g.lmax, (g.wmax - 1) / 2);
+            else run_grid(g.R, tiles, 32, k_cn_uniform<15>, p, g.lmax, (g.wmax - 1) / 2);
+            scaldpc_host_model_smem = scratch.data();
         } else {
             if (first) run_grid((g.E + 7) / 8, tiles, 256, k_init_v2c, p, g.E);
             CnGenericArgs a;
