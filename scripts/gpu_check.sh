@@ -10,7 +10,7 @@ timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $out/${tag}_smo
 for wl in kyber512 kyber768 kyber1024; do
   timeout 600 python bench.py --workload $wl --steps 10 --warmup 3 > $out/${tag}_bench_$wl.json 2> $out/${tag}_bench_$wl.err; echo "bench $wl exit $?" >> $out/${tag}_bench_$wl.err
 done
-for wl in hqc128 hqc256; do
+for wl in hqc128 hqc192 hqc256 decoder450; do
   timeout 900 python bench.py --workload $wl --steps 3 --warmup 3 > $out/${tag}_bench_$wl.json 2> $out/${tag}_bench_$wl.err; echo "bench $wl exit $?" >> $out/${tag}_bench_$wl.err
 done
 # ncu: launch list (cold-cache serialised) of the default bench command
