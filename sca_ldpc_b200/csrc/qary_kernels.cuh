@@ -438,8 +438,9 @@ __global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGene
 //   output    c2v_j[d] = min_u P_j[u] + G_{j+1}[-u - d],  +inf where a_j[d] is not finite (decoder.rs:307-311)
 // A trial whose check has no finite configuration gets SCALDPC_ERR_NO_CONFIG (decoder.rs:618).
 // The reference's criterion case (benches/decoder.rs, Decoder<450,150,3,7,15,7>, 10^4 trials): k_cn_generic 202 ms per
-// launch (full-range tables, one warp per SM), 30 ms with the reachable window, 6.9 ms here (u loops unrolled by 2 for
-// loads in flight: two 86 KB CTAs per SM leave the pass bound by shared-memory latency).
+// launch (full-range tables, one warp per SM), 30 ms with the reachable window, 4.1 ms here (u loops unrolled by 2 for
+// loads in flight; P_0 and P_L are scalars, which leaves 72 KB per warp = three CTAs per SM: the pass is bound by
+// shared-memory latency).
 // -----------------------------------------------------------------------------------------------------------
 template <int Q>
 __global__ void __launch_bounds__(32) k_cn_uniform(const QaryDev p, const int LMAX, const int HH)
@@ -454,10 +455,10 @@ __global__ void __launch_bounds__(32) k_cn_uniform(const QaryDev p, const int LM
     float *msg = p.msg + (size_t)tile * p.S * 32 + lane;
     const int WP = 2 * (HH + B) + 1;  // padded table width; index of partial sum u is u + HH + B
     float *sA = smem + lane;                          // [L][Q]
-    float *sP = sA + (size_t)LMAX * Q * 32;           // [L+1][WP]
-    float *sG = sP + (size_t)(LMAX + 1) * WP * 32;    // [2][WP]
+    float *sP = sA + (size_t)LMAX * Q * 32;           // [L-1][WP]: P_1 .. P_{L-1} (P_0 = {0: 0} and P_L[0] are scalars)
+    float *sG = sP + (size_t)(LMAX - 1) * WP * 32;    // [2][WP]
 #define UA_(k, i) sA[((k)*Q + (i)) * 32]
-#define UP_(k, u) sP[((k)*WP + (u) + HH + B) * 32]
+#define UP_(k, u) sP[(((k)-1) * WP + (u) + HH + B) * 32]
 #define UG_(b, u) sG[((b)*WP + (u) + HH + B) * 32]
     const int all = L * B;
     auto reach = [&](int k) { return min(min(k * B, all - k * B), HH); };  // r_k
@@ -467,25 +468,35 @@ __global__ void __launch_bounds__(32) k_cn_uniform(const QaryDev p, const int LM
 #pragma unroll
         for (int i = 0; i < Q; ++i) UA_(k, i) = sanitize(msg[(size_t)(off + i) * 32]);
     }
-    for (int i = 0; i < (L + 1) * WP; ++i) sP[(size_t)i * 32] = INF;
+    for (int i = 0; i < (L - 1) * WP; ++i) sP[(size_t)i * 32] = INF;
     for (int i = 0; i < 2 * WP; ++i) sG[(size_t)i * 32] = INF;
 
-    // ---- forward
-    UP_(0, 0) = 0.0f;
-    for (int k = 0; k < L; ++k) {
-        float a[Q];
+    // ---- forward: P_1 = 0 + a_0, then P_{k+1} from P_k for k = 1 .. L-2; P_L only at u = 0
+    float pl0;  // P_L[0]: the cheapest complete configuration
+    if (L == 1) {
+        pl0 = 0.0f + UA_(0, B);
+    } else {
+        const int r1 = reach(1);
+        for (int u = -r1; u <= r1; ++u) UP_(1, u) = 0.0f + UA_(0, u + B);
+        for (int k = 1; k < L - 1; ++k) {
+            float a[Q];
 #pragma unroll
-        for (int i = 0; i < Q; ++i) a[i] = UA_(k, i);
-        const int r = reach(k + 1);
+            for (int i = 0; i < Q; ++i) a[i] = UA_(k, i);
+            const int r = reach(k + 1);
 #pragma unroll 2
-        for (int u = -r; u <= r; ++u) {
-            MinAcc acc;
+            for (int u = -r; u <= r; ++u) {
+                MinAcc acc;
 #pragma unroll
-            for (int i = 0; i < Q; ++i) acc.add(UP_(k, u - (i - B)) + a[i]);
-            UP_(k + 1, u) = acc.get();
+                for (int i = 0; i < Q; ++i) acc.add(UP_(k, u - (i - B)) + a[i]);
+                UP_(k + 1, u) = acc.get();
+            }
         }
+        MinAcc acc;
+#pragma unroll
+        for (int i = 0; i < Q; ++i) acc.add(UP_(L - 1, -(i - B)) + UA_(L - 1, i));
+        pl0 = acc.get();
     }
-    if (!(UP_(L, 0) < INF)) atomicMin(p.status + tile * 32 + lane, SCALDPC_ERR_NO_CONFIG);
+    if (!(pl0 < INF)) atomicMin(p.status + tile * 32 + lane, SCALDPC_ERR_NO_CONFIG);
 
     // ---- backward + combine; G_{j+1} lives in sG[cur]
     int cur = 0;
@@ -496,11 +507,16 @@ __global__ void __launch_bounds__(32) k_cn_uniform(const QaryDev p, const int LM
         for (int i = 0; i < Q; ++i) a[i] = UA_(j, i);
         const int r = reach(j);
         MinAcc out[Q];
-#pragma unroll 2
-        for (int u = -r; u <= r; ++u) {
-            const float f = UP_(j, u);
+        if (j == 0) {
 #pragma unroll
-            for (int i = 0; i < Q; ++i) out[i].add(f + UG_(cur, -u - (i - B)));
+            for (int i = 0; i < Q; ++i) out[i].add(0.0f + UG_(cur, -(i - B)));
+        } else {
+#pragma unroll 2
+            for (int u = -r; u <= r; ++u) {
+                const float f = UP_(j, u);
+#pragma unroll
+                for (int i = 0; i < Q; ++i) out[i].add(f + UG_(cur, -u - (i - B)));
+            }
         }
         const int offj = __ldg(p.edge_off + e0 + j);
 #pragma unroll
