@@ -121,6 +121,35 @@ int scaldpc_qary_decode_observed(scaldpc_qary *h, int T, const float *table, int
                                  int n_rows_sum, const uint16_t *obs, const uint16_t *obs_sum, int8_t *hard, float *post,
                                  float *post_sum, int32_t *status, unsigned flags, void *stream);
 
+/*
+ * scaldpc_qary_simulate -- T Monte-Carlo trials of the Kyber attack simulation, synthesised, decoded and scored on the
+ * device: no per-trial data crosses PCIe.  Replaces, per trial, the reference-side composition
+ *   kyber.sample_secret_coefs / generate_secret_for_H  (simulate/kyber.py:35-47, 100-105)   s ~ centred binomial(eta)
+ *   kyber.compute_ssum                                 (simulate/kyber.py:85-92)            ssum = H' s
+ *   SimpleOracle                                       (simulate/max_likelihood.py:9-18)    every bit of the value's code
+ *                                                       word is observed correctly with probability `accuracy`
+ *   s_distribution_from_hard_y + get_channel_probabilities + min_sum                        (= scaldpc_qary_decode_observed)
+ *   success <=> decoded[:BVARS] == s  (and decoded[BVARS:] == -ssum)                        
+ * The reference draws from os.urandom; here trial g = first_trial + t draws from Philox4x32-10 keyed by `seed` with the
+ * counter layout documented in sca_ldpc_b200/csrc/qary_sim.cuh, so a campaign's trials do not depend on how it is cut
+ * into calls or spread over GPUs.  oracle/kyber_sim.py restates the generator.
+ *   table, table_sum   as scaldpc_qary_decode_observed (host pointers); row y = posterior given observed pattern y
+ *   code       Q   uint16: code word (bit k = oracle bit k) of secret value v at index v + B; nbits <= 16 bits each
+ *   code_sum   QS  uint16: code word of check-sum value v at index v + BSUM; nbits_sum bits each
+ *                  (kyber.coding_from_patterns, simulate/kyber.py:50-57)
+ *   accuracy   probability that one oracle bit is right; eta: secret coefficients are centred binomial(eta), eta <= B
+ *   counters   5 x int64 out: trials, successes (secret and sum variables right), trials whose secret is right,
+ *              wrong secret coefficients, wrong sum variables
+ *   secret (T x BVARS int8), ssum (T x R int16), obs (T x BVARS uint16), obs_sum (T x R uint16), hard (T x N int8):
+ *              optional host outputs of the synthesised trials and their decisions (NULL = not copied)
+ * Needs a special decoder (BSUM > 0) whose BSUM covers row weight * eta.  Synchronous; flags as scaldpc_qary_decode
+ * (SCALDPC_DEVICE_PTRS is rejected).
+ */
+int scaldpc_qary_simulate(scaldpc_qary *h, int T, uint64_t seed, uint64_t first_trial, const float *table, int n_rows,
+                          const float *table_sum, int n_rows_sum, const uint16_t *code, int nbits, const uint16_t *code_sum,
+                          int nbits_sum, double accuracy, int eta, int64_t *counters, int8_t *secret, int16_t *ssum,
+                          uint16_t *obs, uint16_t *obs_sum, int8_t *hard, unsigned flags, void *stream);
+
 /* Kernels launched by this handle so far (for bench.py's "gpu_launches") and device time is NOT tracked
  * here -- callers time with CUDA events on `stream`. */
 long long scaldpc_qary_launch_count(const scaldpc_qary *h);

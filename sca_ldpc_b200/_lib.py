@@ -23,7 +23,7 @@ BP_PROBS_PER_TRIAL, BP_NO_EARLY_STOP, BP_NO_COMPACT = 0x10, 0x20, 0x40
 SYMBOLS = [
     "scaldpc_last_error", "scaldpc_version", "scaldpc_device_count",
     "scaldpc_qary_create", "scaldpc_qary_destroy", "scaldpc_qary_info", "scaldpc_qary_set_max_iter",
-    "scaldpc_qary_decode", "scaldpc_qary_decode_observed", "scaldpc_qary_launch_count", "scaldpc_qary_time_kernel",
+    "scaldpc_qary_decode", "scaldpc_qary_decode_observed", "scaldpc_qary_simulate", "scaldpc_qary_launch_count", "scaldpc_qary_time_kernel",
     "scaldpc_bp_create", "scaldpc_bp_destroy", "scaldpc_bp_info", "scaldpc_bp_decode", "scaldpc_bp_launch_count",
     "scaldpc_bp_last_run", "scaldpc_bp_time_kernel",
 ]
@@ -71,6 +71,9 @@ def lib() -> C.CDLL:
     L.scaldpc_qary_decode.argtypes = [vp, i, vp, vp, vp, vp, vp, vp, u, vp]
     L.scaldpc_qary_decode_observed.restype = i
     L.scaldpc_qary_decode_observed.argtypes = [vp, i, vp, i, vp, i, vp, vp, vp, vp, vp, vp, u, vp]
+    L.scaldpc_qary_simulate.restype = i
+    L.scaldpc_qary_simulate.argtypes = [vp, i, C.c_uint64, C.c_uint64, vp, i, vp, i, vp, i, vp, i, C.c_double, i,
+                                        vp, vp, vp, vp, vp, vp, u, vp]
     L.scaldpc_qary_launch_count.restype = C.c_longlong
     L.scaldpc_qary_launch_count.argtypes = [vp]
     L.scaldpc_qary_time_kernel.restype = i

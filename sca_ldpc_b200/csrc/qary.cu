@@ -11,6 +11,7 @@
 #include "common.h"
 #include "qary_graph.h"
 #include "qary_kernels.cuh"
+#include "qary_sim.cuh"
 
 namespace scaldpc {
 
@@ -70,6 +71,12 @@ struct scaldpc_qary {
     uint16_t *d_obs[2] = {nullptr, nullptr}, *d_obs_sum[2] = {nullptr, nullptr};
     float *d_tab_in = nullptr, *d_tab_sum_in = nullptr, *d_tab_llr = nullptr, *d_tab_sum_llr = nullptr;
     int *d_tab_st = nullptr, *d_tab_sum_st = nullptr;
+    // on-device trial synthesis (scaldpc_qary_simulate): per-pass trial data + code tables + counters
+    size_t cap_sim_T = 0;
+    int8_t *d_sim_secret = nullptr, *d_sim_hard = nullptr;
+    int16_t *d_sim_ssum = nullptr;
+    uint16_t *d_sim_code = nullptr, *d_sim_code_sum = nullptr;
+    unsigned long long *d_sim_cnt = nullptr;
     cudaStream_t s_in = nullptr, s_out = nullptr;
     cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
     std::mutex mu;
@@ -133,6 +140,42 @@ void free_observed(scaldpc_qary *h)
     h->d_tab_in = h->d_tab_sum_in = h->d_tab_llr = h->d_tab_sum_llr = nullptr;
     h->d_tab_st = h->d_tab_sum_st = nullptr;
     h->cap_obs_T = h->cap_tab = h->cap_tab_sum = 0;
+}
+
+void free_sim(scaldpc_qary *h)
+{
+    cudaFree(h->d_sim_secret);
+    cudaFree(h->d_sim_hard);
+    cudaFree(h->d_sim_ssum);
+    cudaFree(h->d_sim_code);
+    cudaFree(h->d_sim_code_sum);
+    cudaFree(h->d_sim_cnt);
+    h->d_sim_secret = h->d_sim_hard = nullptr;
+    h->d_sim_ssum = nullptr;
+    h->d_sim_code = h->d_sim_code_sum = nullptr;
+    h->d_sim_cnt = nullptr;
+    h->cap_sim_T = 0;
+}
+
+int ensure_sim(scaldpc_qary *h, size_t chunk)
+{
+    if (!h->d_sim_cnt) {
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_sim_cnt, 8 * sizeof(unsigned long long)));
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_sim_code, (size_t)h->Q * sizeof(uint16_t)));
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_sim_code_sum, (size_t)h->QS * sizeof(uint16_t)));
+    }
+    if (chunk <= h->cap_sim_T) return 0;
+    cudaFree(h->d_sim_secret);
+    cudaFree(h->d_sim_hard);
+    cudaFree(h->d_sim_ssum);
+    h->d_sim_secret = h->d_sim_hard = nullptr;
+    h->d_sim_ssum = nullptr;
+    h->cap_sim_T = 0;
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_sim_secret, chunk * h->bvars));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_sim_hard, chunk * h->N));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_sim_ssum, chunk * h->R * sizeof(int16_t)));
+    h->cap_sim_T = chunk;
+    return 0;
 }
 
 int ensure_workspace(scaldpc_qary *h, int tiles, bool want_post)
@@ -547,6 +590,7 @@ void scaldpc_qary_destroy(scaldpc_qary *h)
     free_workspace(h);
     free_stage(h);
     free_observed(h);
+    free_sim(h);
     cudaFree(h->d_status_all);
     if (h->s_in) cudaStreamDestroy(h->s_in);
     if (h->s_out) cudaStreamDestroy(h->s_out);
@@ -769,6 +813,29 @@ int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in
     return decode_batch(h, T, src, hard, post, post_sum, status, flags, (cudaStream_t)stream);
 }
 
+// tables -> device LLR tables (into_llr once per row, decoder.rs:668-692), on the compute stream
+static int upload_tables(scaldpc_qary *h, const float *table, int n_rows, const float *table_sum, int n_rows_sum,
+                         unsigned flags, cudaStream_t st)
+{
+    const bool special = h->BSUM > 0;
+    int rc;
+    if ((rc = ensure_tables(h, (size_t)n_rows, special ? (size_t)n_rows_sum : 0))) return rc;
+    const bool dev_ptrs = flags & SCALDPC_DEVICE_PTRS;
+    const bool is_llr = flags & SCALDPC_IN_LLR;
+    const cudaMemcpyKind kind = dev_ptrs ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    SCALDPC_CUDA(cudaMemcpyAsync(h->d_tab_in, table, (size_t)n_rows * h->Q * sizeof(float), kind, st));
+    k_table_llr<<<(n_rows + 127) / 128, 128, 0, st>>>(h->d_tab_in, h->d_tab_llr, h->d_tab_st, n_rows, h->Q, is_llr);
+    ++h->launches;
+    if (special) {
+        SCALDPC_CUDA(cudaMemcpyAsync(h->d_tab_sum_in, table_sum, (size_t)n_rows_sum * h->QS * sizeof(float), kind, st));
+        k_table_llr<<<(n_rows_sum + 127) / 128, 128, 0, st>>>(h->d_tab_sum_in, h->d_tab_sum_llr, h->d_tab_sum_st, n_rows_sum,
+                                                              h->QS, is_llr);
+        ++h->launches;
+    }
+    SCALDPC_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int scaldpc_qary_decode_observed(scaldpc_qary *h, int T, const float *table, int n_rows, const float *table_sum,
                                  int n_rows_sum, const uint16_t *obs, const uint16_t *obs_sum, int8_t *hard, float *post,
                                  float *post_sum, int32_t *status, unsigned flags, void *stream)
@@ -784,21 +851,7 @@ int scaldpc_qary_decode_observed(scaldpc_qary *h, int T, const float *table, int
     std::lock_guard<std::mutex> lk(h->mu);
     SCALDPC_CUDA(cudaSetDevice(h->device));
     int rc;
-    if ((rc = ensure_tables(h, (size_t)n_rows, special ? (size_t)n_rows_sum : 0))) return rc;
-    // tables -> device LLR tables (into_llr once per row, decoder.rs:668-692), on the compute stream
-    const bool dev_ptrs = flags & SCALDPC_DEVICE_PTRS;
-    const bool is_llr = flags & SCALDPC_IN_LLR;
-    const cudaMemcpyKind kind = dev_ptrs ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
-    SCALDPC_CUDA(cudaMemcpyAsync(h->d_tab_in, table, (size_t)n_rows * h->Q * sizeof(float), kind, st));
-    k_table_llr<<<(n_rows + 127) / 128, 128, 0, st>>>(h->d_tab_in, h->d_tab_llr, h->d_tab_st, n_rows, h->Q, is_llr);
-    ++h->launches;
-    if (special) {
-        SCALDPC_CUDA(cudaMemcpyAsync(h->d_tab_sum_in, table_sum, (size_t)n_rows_sum * h->QS * sizeof(float), kind, st));
-        k_table_llr<<<(n_rows_sum + 127) / 128, 128, 0, st>>>(h->d_tab_sum_in, h->d_tab_sum_llr, h->d_tab_sum_st, n_rows_sum,
-                                                              h->QS, is_llr);
-        ++h->launches;
-    }
-    SCALDPC_CUDA(cudaGetLastError());
+    if ((rc = upload_tables(h, table, n_rows, table_sum, n_rows_sum, flags, st))) return rc;
     PriorSrc src;
     src.observed = true;
     src.obs = obs;
@@ -806,6 +859,101 @@ int scaldpc_qary_decode_observed(scaldpc_qary *h, int T, const float *table, int
     src.n_rows = n_rows;
     src.n_rows_sum = n_rows_sum;
     return decode_batch(h, T, src, hard, post, post_sum, status, flags, st);
+}
+
+int scaldpc_qary_simulate(scaldpc_qary *h, int T, uint64_t seed, uint64_t first_trial, const float *table, int n_rows,
+                          const float *table_sum, int n_rows_sum, const uint16_t *code, int nbits, const uint16_t *code_sum,
+                          int nbits_sum, double accuracy, int eta, int64_t *counters, int8_t *secret, int16_t *ssum,
+                          uint16_t *obs, uint16_t *obs_sum, int8_t *hard, unsigned flags, void *stream)
+{
+    if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
+    if (h->BSUM <= 0) return fail(SCALDPC_ERR_UNSUPPORTED, "trial synthesis needs a decoder with sum variables (BSUM > 0)");
+    if (flags & SCALDPC_DEVICE_PTRS) return fail(SCALDPC_ERR_ARG, "scaldpc_qary_simulate takes host pointers");
+    if (T < 0 || !counters || !table || !table_sum || !code || !code_sum)
+        return fail(SCALDPC_ERR_ARG, "NULL pointer or T < 0");
+    if (n_rows <= 0 || n_rows > 65535 || n_rows_sum <= 0 || n_rows_sum > 65535)
+        return fail(SCALDPC_ERR_ARG, "prior tables must have 1 .. 65535 rows");
+    if (nbits < 1 || nbits > 16 || nbits_sum < 1 || nbits_sum > 16 || (1 << nbits) > n_rows || (1 << nbits_sum) > n_rows_sum)
+        return fail(SCALDPC_ERR_ARG, "code words of nbits / nbits_sum bits need tables of 2^nbits / 2^nbits_sum rows");
+    if (eta < 1 || eta > 16 || eta > h->B) return fail(SCALDPC_ERR_ARG, "eta must be in 1 .. B");
+    if (!(accuracy >= 0.0 && accuracy <= 1.0)) return fail(SCALDPC_ERR_ARG, "accuracy must be in [0, 1]");
+    for (int i = 0; i < h->Q; ++i)
+        if (code[i] >> nbits) return fail(SCALDPC_ERR_ARG, "code word %d has more than nbits bits", i);
+    for (int i = 0; i < h->QS; ++i)
+        if (code_sum[i] >> nbits_sum) return fail(SCALDPC_ERR_ARG, "sum code word %d has more than nbits_sum bits", i);
+    for (int i = 0; i < 5; ++i) counters[i] = 0;
+    if (T == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    std::lock_guard<std::mutex> lk(h->mu);
+    SCALDPC_CUDA(cudaSetDevice(h->device));
+    int rc;
+    if ((rc = upload_tables(h, table, n_rows, table_sum, n_rows_sum, flags, st))) return rc;
+    const int cap = std::max(32, h->max_resident / 32 * 32);
+    const int chunk = (std::min(T, cap) + 31) / 32 * 32;
+    if ((rc = ensure_sim(h, (size_t)chunk))) return rc;
+    if ((rc = ensure_stage_observed(h, (size_t)chunk))) return rc;
+    if ((rc = ensure_workspace(h, chunk / 32, false))) return rc;
+    SCALDPC_CUDA(cudaMemcpyAsync(h->d_sim_code, code, (size_t)h->Q * sizeof(uint16_t), cudaMemcpyHostToDevice, st));
+    SCALDPC_CUDA(cudaMemcpyAsync(h->d_sim_code_sum, code_sum, (size_t)h->QS * sizeof(uint16_t), cudaMemcpyHostToDevice, st));
+    SCALDPC_CUDA(cudaMemsetAsync(h->d_sim_cnt, 0, 8 * sizeof(unsigned long long), st));
+    SimParams sp;
+    sp.seed = seed;
+    sp.eta = eta;
+    sp.nbits = nbits;
+    sp.nbits_sum = nbits_sum;
+    sp.flip_thr = accuracy >= 1.0 ? (1ull << 32) : (uint64_t)(accuracy * 4294967296.0);
+    const QaryDev p = dev_view(h, false);
+    PriorSrc src;
+    src.observed = true;
+    src.obs = h->d_obs[0];
+    src.obs_sum = h->d_obs_sum[0];
+    src.n_rows = n_rows;
+    src.n_rows_sum = n_rows_sum;
+    int worst = 0;
+    std::vector<int> hs;
+    for (int t0 = 0; t0 < T; t0 += cap) {
+        const int tc = std::min(cap, T - t0);
+        sp.first_trial = first_trial + (uint64_t)t0;
+        const int grid = h->num_sms * 8;
+        k_sim_secret<<<grid, 256, 0, st>>>(sp, h->d_sim_code, h->d_sim_secret, h->d_obs[0], tc, h->bvars, h->B);
+        // decode_on_device clears d_status first, so the range check of k_sim_sum reports through the counters' slot 5
+        k_sim_sum<<<grid, 256, 0, st>>>(sp, p, h->d_sim_code_sum, h->d_sim_secret, h->d_sim_ssum, h->d_obs_sum[0],
+                                        (int *)(h->d_sim_cnt + 5), tc);
+        h->launches += 2;
+        SCALDPC_CUDA(cudaGetLastError());
+        if ((rc = decode_on_device(h, tc, src, h->d_sim_hard, nullptr, nullptr, flags, st))) return rc;
+        k_sim_count<<<grid, 256, 0, st>>>(h->d_sim_hard, h->d_sim_secret, h->d_sim_ssum, h->d_sim_cnt, tc, h->N, h->bvars);
+        ++h->launches;
+        SCALDPC_CUDA(cudaGetLastError());
+        // optional per-trial outputs (parity tests, debugging); production calls pass NULL and copy nothing
+        if (secret)
+            SCALDPC_CUDA(cudaMemcpyAsync(secret + (size_t)t0 * h->bvars, h->d_sim_secret, (size_t)tc * h->bvars, cudaMemcpyDeviceToHost, st));
+        if (ssum)
+            SCALDPC_CUDA(cudaMemcpyAsync(ssum + (size_t)t0 * h->R, h->d_sim_ssum, (size_t)tc * h->R * sizeof(int16_t),
+                                         cudaMemcpyDeviceToHost, st));
+        if (obs)
+            SCALDPC_CUDA(cudaMemcpyAsync(obs + (size_t)t0 * h->bvars, h->d_obs[0], (size_t)tc * h->bvars * sizeof(uint16_t),
+                                         cudaMemcpyDeviceToHost, st));
+        if (obs_sum)
+            SCALDPC_CUDA(cudaMemcpyAsync(obs_sum + (size_t)t0 * h->R, h->d_obs_sum[0], (size_t)tc * h->R * sizeof(uint16_t),
+                                         cudaMemcpyDeviceToHost, st));
+        if (hard)
+            SCALDPC_CUDA(cudaMemcpyAsync(hard + (size_t)t0 * h->N, h->d_sim_hard, (size_t)tc * h->N, cudaMemcpyDeviceToHost, st));
+        hs.resize(tc);
+        SCALDPC_CUDA(cudaMemcpyAsync(hs.data(), h->d_status, (size_t)tc * sizeof(int), cudaMemcpyDeviceToHost, st));
+        SCALDPC_CUDA(cudaStreamSynchronize(st));  // the pass's buffers are reused by the next one
+        for (int t = 0; t < tc; ++t) worst = std::min(worst, hs[t]);
+    }
+    unsigned long long cnt[8];
+    SCALDPC_CUDA(cudaMemcpyAsync(cnt, h->d_sim_cnt, sizeof(cnt), cudaMemcpyDeviceToHost, st));
+    SCALDPC_CUDA(cudaStreamSynchronize(st));
+    for (int i = 0; i < 5; ++i) counters[i] = (int64_t)cnt[i];
+    if (cnt[5]) return fail(SCALDPC_ERR_ARG, "a check sum left [-BSUM, BSUM]: BSUM is smaller than row weight * eta");
+    if (worst == SCALDPC_ERR_PROB_SUM) return fail(worst, "a prior row does not sum to 1 +- 0.001 (decoder.rs:683-684)");
+    if (worst == SCALDPC_ERR_NO_MAX) return fail(worst, "No maximum probability found (decoder.rs:680)");
+    if (worst == SCALDPC_ERR_NO_CONFIG) return fail(worst, "a check has no valid configuration (decoder.rs:618)");
+    if (worst < 0) return fail(worst, "trial synthesis failed with status %d", worst);
+    return 0;
 }
 
 int scaldpc_qary_time_kernel(scaldpc_qary *h, int which, int T, unsigned flags, int reps, void *stream, float *avg_ms)

@@ -264,6 +264,48 @@ class QaryDecoder:
             raise ValueError(_lib.lib().scaldpc_last_error().decode())
         return self._finish(rc, hard, post, posts, status, want_status)
 
+    def simulate(self, T, seed, table, table_sum, code, code_sum, nbits, nbits_sum, accuracy, eta, *, first_trial=0,
+                 want_trials=False, exact=False, generic=False):
+        """T Kyber attack-simulation trials synthesised, decoded and scored on the device (scaldpc_qary_simulate,
+        SURVEY.md 8f.1): secret ~ centred binomial(eta) (kyber.py:35-47), ssum = H' s (kyber.py:85-92), every bit of
+        the code word of a value observed correctly with probability `accuracy` (max_likelihood.py:9-18), priors =
+        table[observed pattern], min_sum, success = decoded secret == s and decoded sums == -ssum.
+
+        code / code_sum: one code word per value (index value + B / value + BSUM), bit k = oracle bit k.
+        Returns a dict of counters; with want_trials also the per-trial arrays secret, ssum, obs, obs_sum, hard.
+        Trial g = first_trial + t depends only on (seed, g)."""
+        table = np.ascontiguousarray(table, dtype=np.float32)
+        table_sum = np.ascontiguousarray(table_sum, dtype=np.float32)
+        code = np.ascontiguousarray(code, dtype=np.uint16)
+        code_sum = np.ascontiguousarray(code_sum, dtype=np.uint16)
+        if table.ndim != 2 or table.shape[1] != self.Q or table_sum.ndim != 2 or table_sum.shape[1] != self.QS:
+            raise ValueError(f"table must be (n_rows, {self.Q}) and table_sum (n_rows_sum, {self.QS})")
+        if code.shape != (self.Q,) or code_sum.shape != (self.QS,):
+            raise ValueError(f"code must have {self.Q} entries and code_sum {self.QS}")
+        T = int(T)
+        flags = (_lib.CN_EXACT if exact else 0) | (_lib.CN_GENERIC if generic else 0)
+        counters = np.zeros(5, np.int64)
+        tr = {}
+        if want_trials:
+            tr = dict(secret=np.empty((T, self.bvars), np.int8), ssum=np.empty((T, self.R), np.int16),
+                      obs=np.empty((T, self.bvars), np.uint16), obs_sum=np.empty((T, self.R), np.uint16),
+                      hard=np.empty((T, self.N), np.int8))
+        p = lambda k: tr[k].ctypes.data if k in tr else None  # noqa: E731
+        with self._lock:
+            rc = _lib.lib().scaldpc_qary_simulate(
+                self._h, T, int(seed), int(first_trial), table.ctypes.data, table.shape[0], table_sum.ctypes.data,
+                table_sum.shape[0], code.ctypes.data, int(nbits), code_sum.ctypes.data, int(nbits_sum), float(accuracy),
+                int(eta), counters.ctypes.data, p("secret"), p("ssum"), p("obs"), p("obs_sum"), p("hard"), flags, None)
+        if rc:
+            msg = _lib.lib().scaldpc_last_error().decode()
+            if rc == _lib.ERR_ARG:
+                raise ValueError(msg)
+            raise _lib.ScaldpcError(rc, msg)
+        res = dict(zip(("trials", "successes", "secret_successes", "symbol_errors", "sum_symbol_errors"),
+                       (int(c) for c in counters)))
+        res.update(tr)
+        return res
+
     def _batch_torch(self, x, xs, flags, want_posterior, want_status):
         dev = torch.device("cuda", self.device)
         if x.device != dev or x.dtype != torch.float32:

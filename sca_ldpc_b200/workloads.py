@@ -136,6 +136,14 @@ class KyberWorkload:
     def decoder_kwargs(self):
         return dict(B=self.B, BSUM=self.BSUM, DC=self.sum_weight + 1)
 
+    @property
+    def simulate_kwargs(self):
+        """Arguments of QaryDecoder.simulate (on-device trial synthesis): tables, code words (bit k of the word =
+        oracle bit k, the integer _observe builds), bit counts, accuracy, eta."""
+        word = lambda c: (c.astype(np.int64) << np.arange(c.shape[1])).sum(-1).astype(np.uint16)  # noqa: E731
+        return dict(table=self.table, table_sum=self.table_sum, code=word(self.coding), code_sum=word(self.coding_sum),
+                    nbits=self.coding.shape[1], nbits_sum=self.coding_sum.shape[1], accuracy=self.accuracy, eta=self.eta)
+
     def _observe(self, rs, values, coding, offset):
         bits = coding[values.astype(np.int64) + offset]                           # (..., nbits)
         flips = rs.random_sample(bits.shape) >= self.accuracy
