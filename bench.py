@@ -394,6 +394,31 @@ def run_ours(args, kind, wl, iters, cfg):
             "success_rate": int(c_obs[0]) / max(1, int(c_obs[1])),
         }
 
+    # ---- binary path: host buffers in, hqc.decode's statistics out (scaldpc_bp_decode_scored) instead of T x n decisions
+    scored = None
+    if kind == "bp":
+        y32 = np.ascontiguousarray(batch.y, dtype=np.int32)
+        synd_h = h_in[0].numpy()
+        for _ in range(2):
+            sc = dec.decode_scored(synd_h, y32)
+        sync_all()
+        t0 = time.perf_counter()
+        ok = 0
+        for _ in range(args.steps):
+            sc = dec.decode_scored(synd_h, y32)
+            ok += int(sc["stats"][:, 5].sum())
+        dt_sc = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+        cnt_sc = torch.tensor([ok], device=dev, dtype=torch.int64)
+        if world > 1:
+            dist.all_reduce(dt_sc, op=dist.ReduceOp.MAX)
+            dist.all_reduce(cnt_sc)
+        scored = {
+            "api": "scaldpc_bp_decode_scored: syndromes + true supports in, the statistics of hqc.py:709-758 out "
+                   "(computed on the device, SURVEY.md 8f.2) instead of the T x n decision bytes",
+            "e2e": {"value": world * T * args.steps / float(dt_sc.item()), "unit": "trials/s",
+                    "h2d_bytes_per_step": T * wl.m + y32.nbytes + wl.n * 8, "d2h_bytes_per_step": T * (24 + 8)},
+            "success_rate": int(cnt_sc.item()) / (world * T * args.steps)}
+
     # ---- the whole Monte-Carlo loop on the device (scaldpc_qary_simulate): trial synthesis + decode + scoring
     if observed is not None and special:
         first = rank * T * (args.steps + 3)
@@ -503,6 +528,7 @@ def run_ours(args, kind, wl, iters, cfg):
             "e2e": {"value": e2e_value, "unit": "trials/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches),
             **({"observed": observed} if observed else {}),
+            **({"scored": scored} if scored else {}),
             "single_decode": single,
             **({"compactions_last_step": dec.last_run()[1], "iterations_launched_last_step": dec.last_run()[0]}
                if kind == "bp" else {}),

@@ -190,6 +190,19 @@ void scaldpc_bp_destroy(scaldpc_bp *h);
  */
 int scaldpc_bp_decode(scaldpc_bp *h, int T, const uint8_t *synd, const double *channel_probs, uint8_t *decoding,
                       float *llr, int32_t *iters, int32_t *converged, unsigned flags, void *stream);
+/*
+ * scaldpc_bp_decode_scored -- decode, then the statistics hqc.decode computes from the decoded vector (hqc.py:709-758)
+ * on the device, so a campaign moves 24 bytes per trial back instead of n.  Needs H = [Hin | I_m]
+ * (hqc.py:680): columns < n_msg = n - m are message bits, column n_msg + i is the measurement error of check i.
+ *   truth     T x weight int32: support of the true message of every trial (y_sparse, hqc.py:1043-1046), distinct
+ *   stats     T x 6 int32 out: unsatisfied, good_flips, bad_flips, found_bad_satisfied_checks,
+ *             found_bad_unsatisfied_checks, success   -- the arguments of tracking.add_decoder_stats (hqc.py:751-759)
+ *   decoding  T x n uint8 out, or NULL with host pointers (not copied back)
+ * Other arguments, flags and return value as scaldpc_bp_decode.
+ */
+int scaldpc_bp_decode_scored(scaldpc_bp *h, int T, int n_msg, const uint8_t *synd, const double *channel_probs,
+                             const int32_t *truth, int weight, int32_t *stats, uint8_t *decoding, int32_t *iters,
+                             int32_t *converged, unsigned flags, void *stream);
 /* Shape queries: checks, variables, edges, iteration cap (max_iter = 0 at create time means n, as upstream). */
 int scaldpc_bp_info(const scaldpc_bp *h, int *m, int *n, int *edges, int *max_iter);
 long long scaldpc_bp_launch_count(const scaldpc_bp *h);

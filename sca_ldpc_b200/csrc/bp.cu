@@ -44,6 +44,8 @@ struct scaldpc_bp {
     size_t cap_stage_T = 0;
     bool stage_probs_t = false, stage_llr = false;
     uint8_t *d_synd = nullptr, *d_dec = nullptr;
+    int32_t *d_truth = nullptr, *d_stats = nullptr;  // scaldpc_bp_decode_scored staging (host-pointer calls)
+    size_t cap_truth = 0, cap_stats_T = 0;
     double *d_probs = nullptr;
     float *d_llr = nullptr;
     int cn_warps = 8, cn_occ[2] = {1, 1};
@@ -400,6 +402,8 @@ void scaldpc_bp_destroy(scaldpc_bp *h)
     cudaSetDevice(h->device);
     free_ws(h);
     free_stage(h);
+    cudaFree(h->d_truth);
+    cudaFree(h->d_stats);
     cudaFree(h->d_row_ptr);
     cudaFree(h->d_col);
     cudaFree(h->d_col_ptr);
@@ -427,14 +431,28 @@ int scaldpc_bp_info(const scaldpc_bp *h, int *m, int *n, int *edges, int *max_it
 
 long long scaldpc_bp_launch_count(const scaldpc_bp *h) { return h ? h->launches : 0; }
 
-int scaldpc_bp_decode(scaldpc_bp *h, int T, const uint8_t *synd, const double *channel_probs, uint8_t *decoding,
-                      float *llr, int32_t *iters, int32_t *converged, unsigned flags, void *stream)
+// Scoring request of scaldpc_bp_decode_scored (hqc.py:709-758).
+struct BpScore {
+    const int32_t *truth;  // T x weight: support of the true message per trial
+    int weight, n_msg;
+    int32_t *stats;        // T x 6
+};
+
+static int bp_decode_impl(scaldpc_bp *h, int T, const uint8_t *synd, const double *channel_probs, uint8_t *decoding,
+                          float *llr, int32_t *iters, int32_t *converged, unsigned flags, void *stream,
+                          const BpScore *score)
 {
     if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
     if (T < 0) return fail(SCALDPC_ERR_ARG, "T < 0");
     if (T == 0) return 0;
-    if (!synd || !channel_probs || !decoding) return fail(SCALDPC_ERR_ARG, "NULL input/output pointer");
     const bool dev_ptrs = flags & SCALDPC_DEVICE_PTRS;
+    if (!synd || !channel_probs || (!decoding && (dev_ptrs || !score)))
+        return fail(SCALDPC_ERR_ARG, "NULL input/output pointer");
+    if (score) {
+        if (!score->truth || !score->stats || score->weight < 0) return fail(SCALDPC_ERR_ARG, "NULL truth/stats pointer");
+        if (score->n_msg < 0 || score->n_msg + h->m != h->n)
+            return fail(SCALDPC_ERR_ARG, "scoring needs H = [Hin | I]: n_msg + m must equal n (hqc.py:680)");
+    }
     const bool probs_t = flags & SCALDPC_BP_PROBS_PER_TRIAL;
     const bool early = !(flags & SCALDPC_BP_NO_EARLY_STOP);
     const bool compacting = early && !(flags & SCALDPC_BP_NO_COMPACT);
@@ -520,14 +538,54 @@ int scaldpc_bp_decode(scaldpc_bp *h, int T, const uint8_t *synd, const double *c
     // ---- outputs of every trial still resident (finished since the last compaction, or never converged)
     if ((rc = write_outputs(h, cur, cur_tiles, h->set[cur].valid, ddec, dllr, st))) return rc;
     const cudaMemcpyKind kind = dev_ptrs ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+    if (score) {
+        const int32_t *dtruth = score->truth;
+        int32_t *dstats = score->stats;
+        const size_t nt = std::max<size_t>(1, (size_t)T * score->weight);
+        if (!dev_ptrs) {
+            if (nt > h->cap_truth || (size_t)T > h->cap_stats_T) {
+                cudaFree(h->d_truth);
+                cudaFree(h->d_stats);
+                h->d_truth = h->d_stats = nullptr;
+                h->cap_truth = h->cap_stats_T = 0;
+                SCALDPC_CUDA(cudaMalloc((void **)&h->d_truth, nt * sizeof(int32_t)));
+                SCALDPC_CUDA(cudaMalloc((void **)&h->d_stats, (size_t)T * 6 * sizeof(int32_t)));
+                h->cap_truth = nt;
+                h->cap_stats_T = (size_t)T;
+            }
+            SCALDPC_CUDA(cudaMemcpyAsync(h->d_truth, score->truth, (size_t)T * score->weight * sizeof(int32_t),
+                                         cudaMemcpyHostToDevice, st));
+            dtruth = h->d_truth;
+            dstats = h->d_stats;
+        }
+        k_bp_score<<<(T + 7) / 8, 256, 0, st>>>(ddec, dsynd, dtruth, dstats, T, h->n, score->n_msg, score->weight);
+        ++h->launches;
+        SCALDPC_CUDA(cudaGetLastError());
+        if (!dev_ptrs)
+            SCALDPC_CUDA(cudaMemcpyAsync(score->stats, h->d_stats, (size_t)T * 6 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    }
     if (!dev_ptrs) {
-        SCALDPC_CUDA(cudaMemcpyAsync(decoding, h->d_dec, (size_t)T * h->n, kind, st));
+        if (decoding) SCALDPC_CUDA(cudaMemcpyAsync(decoding, h->d_dec, (size_t)T * h->n, kind, st));
         if (llr) SCALDPC_CUDA(cudaMemcpyAsync(llr, h->d_llr, (size_t)T * h->n * sizeof(float), kind, st));
     }
     if (iters) SCALDPC_CUDA(cudaMemcpyAsync(iters, h->d_iters, (size_t)T * sizeof(int), kind, st));
     if (converged) SCALDPC_CUDA(cudaMemcpyAsync(converged, h->d_conv, (size_t)T * sizeof(int), kind, st));
     if (!dev_ptrs) SCALDPC_CUDA(cudaStreamSynchronize(st));
     return 0;
+}
+
+int scaldpc_bp_decode(scaldpc_bp *h, int T, const uint8_t *synd, const double *channel_probs, uint8_t *decoding,
+                      float *llr, int32_t *iters, int32_t *converged, unsigned flags, void *stream)
+{
+    return bp_decode_impl(h, T, synd, channel_probs, decoding, llr, iters, converged, flags, stream, nullptr);
+}
+
+int scaldpc_bp_decode_scored(scaldpc_bp *h, int T, int n_msg, const uint8_t *synd, const double *channel_probs,
+                             const int32_t *truth, int weight, int32_t *stats, uint8_t *decoding, int32_t *iters,
+                             int32_t *converged, unsigned flags, void *stream)
+{
+    const BpScore score{truth, weight, n_msg, stats};
+    return bp_decode_impl(h, T, synd, channel_probs, decoding, nullptr, iters, converged, flags, stream, &score);
 }
 
 int scaldpc_bp_last_run(const scaldpc_bp *h, int *iterations_launched, int *compactions)

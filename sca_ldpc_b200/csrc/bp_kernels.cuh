@@ -868,6 +868,50 @@ __global__ void __launch_bounds__(256) k_bp_unpack_dec(const uint32_t *__restric
         if ((sel >> t) & 1u) out[(size_t)orig[tile * 32 + t] * n + v] = (w >> t) & 1u;
 }
 
+// The statistics hqc.decode derives from the decoded vector (hqc.py:709-758), one warp per trial.  H = [Hin | I_m]
+// (hqc.py:680): columns < n_msg are message bits, column n_msg + i is the measurement error of check i.
+// stats[t] = {unsatisfied, good_flips, bad_flips, found_bad_satisfied_checks, found_bad_unsatisfied_checks, success}:
+//   good/bad flips        decoded message bits inside / outside the true support (:717-725)
+//   unsatisfied           checks with syndrome bit 1 (:727-728)
+//   found_bad_unsatisfied syndrome bit 1 and NO measurement error decoded (:729-731); found_bad_satisfied: syndrome bit 0
+//                         and a measurement error decoded (:732-734)
+//   success               support(decoded[:n_msg]) == truth (:741-749)
+__global__ void __launch_bounds__(256) k_bp_score(const uint8_t *__restrict__ dec, const uint8_t *__restrict__ synd,
+                                                  const int32_t *__restrict__ truth, int32_t *__restrict__ stats, int T, int n,
+                                                  int n_msg, int weight)
+{
+    const int t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (t >= T) return;
+    const uint8_t *d = dec + (size_t)t * n;
+    const uint8_t *s = synd + (size_t)t * (n - n_msg);
+    int flips = 0, good = 0, unsat = 0, fbs = 0, fbu = 0;
+    for (int i = lane; i < n_msg; i += 32) flips += d[i] != 0;
+    for (int k = lane; k < weight; k += 32) {
+        const int pos = truth[(size_t)t * weight + k];
+        good += pos >= 0 && pos < n_msg && d[pos] != 0;
+    }
+    for (int i = lane; i < n - n_msg; i += 32) {
+        const bool c = s[i] != 0, x = d[n_msg + i] != 0;
+        unsat += c;
+        fbu += c && !x;
+        fbs += !c && x;
+    }
+    flips = __reduce_add_sync(0xffffffffu, flips);
+    good = __reduce_add_sync(0xffffffffu, good);
+    unsat = __reduce_add_sync(0xffffffffu, unsat);
+    fbs = __reduce_add_sync(0xffffffffu, fbs);
+    fbu = __reduce_add_sync(0xffffffffu, fbu);
+    if (lane == 0) {
+        int32_t *o = stats + (size_t)t * 6;
+        o[0] = unsat;
+        o[1] = good;
+        o[2] = flips - good;
+        o[3] = fbs;
+        o[4] = fbu;
+        o[5] = (flips == good && good == weight) ? 1 : 0;
+    }
+}
+
 // post [tile][n][32] -> llr [orig trial][n], for the slots selected by mask[tile]
 __global__ void __launch_bounds__(256) k_bp_untile_f32(const float *__restrict__ src, float *__restrict__ dst,
                                                        const int *__restrict__ orig, const uint32_t *__restrict__ mask, int n)

@@ -149,6 +149,38 @@ class bp_decoder:
                                                 None))
         return dict(decoding=dec, log_prob_ratios=llr, iters=iters, converged=conv)
 
+    STAT_NAMES = ("unsatisfied", "good_flips", "bad_flips", "found_bad_satisfied_checks",
+                  "found_bad_unsatisfied_checks", "success")
+
+    def decode_scored(self, syndromes, truth, channel_probs=None, *, want_decoding=False, early_stop=True):
+        """decode_batch followed, on the device, by the statistics hqc.decode computes from the decoded vector
+        (hqc.py:709-758; scaldpc_bp_decode_scored): 24 bytes per trial come back instead of n.  H must be [Hin | I_m].
+        syndromes (T, m) uint8, truth (T, weight) int32 = support of the true message of every trial (y_sparse).
+        Returns dict(stats (T, 6) int32 in STAT_NAMES order, iters, converged, decoding or None)."""
+        flags = 0 if early_stop else _lib.BP_NO_EARLY_STOP
+        synd = np.ascontiguousarray(syndromes, dtype=np.uint8)
+        T = synd.shape[0]
+        if synd.shape != (T, self.m):
+            raise ValueError(f"syndromes must be (T, {self.m}), got {synd.shape}")
+        truth = np.ascontiguousarray(truth, dtype=np.int32)
+        if truth.ndim != 2 or truth.shape[0] != T:
+            raise ValueError(f"truth must be ({T}, weight)")
+        cp = self.channel_probs if channel_probs is None else np.ascontiguousarray(channel_probs, dtype=np.float64)
+        if cp.ndim == 2:
+            if cp.shape != (T, self.n):
+                raise ValueError(f"channel_probs must be ({T}, {self.n})")
+            flags |= _lib.BP_PROBS_PER_TRIAL
+        elif cp.shape != (self.n,):
+            raise ValueError(f"channel_probs must have length {self.n}")
+        stats = np.empty((T, 6), np.int32)
+        dec = np.empty((T, self.n), np.uint8) if want_decoding else None
+        iters = np.empty(T, np.int32)
+        conv = np.empty(T, np.int32)
+        p = lambda a: None if a is None else a.ctypes.data  # noqa: E731
+        _lib.check(_lib.lib().scaldpc_bp_decode_scored(self._h, T, self.n - self.m, p(synd), p(cp), p(truth), truth.shape[1],
+                                                       p(stats), p(dec), p(iters), p(conv), flags, None))
+        return dict(stats=stats, iters=iters, converged=conv, decoding=dec)
+
     def _batch_torch(self, synd, channel_probs, flags, want_llr):
         dev = torch.device("cuda", self.device)
         synd = synd.contiguous()

@@ -173,3 +173,48 @@ def test_shared_prior_first_pass_is_bit_identical(monkeypatch):
     c = d.decode_batch(b.syndromes, want_llr=True)
     assert np.array_equal(a["decoding"], c["decoding"]) and np.array_equal(a["iters"], c["iters"])
     assert np.array_equal(a["log_prob_ratios"], c["log_prob_ratios"], equal_nan=True)
+
+
+def reference_stats(N, decoded, checks, y_sparse):
+    """hqc.py:709-749, restated loop for loop: -> the 6 arguments of tracking.add_decoder_stats (:751-759)."""
+    y_sparse = set(int(v) for v in y_sparse)
+    unsatisfied = good = bad = fbs = fbu = 0
+    for i, x in enumerate(decoded[:N]):
+        if x:
+            if i in y_sparse:
+                good += 1
+            else:
+                bad += 1
+    for x, c in zip(decoded[N:], checks):
+        if c:
+            unsatisfied += 1
+            if not x:
+                fbu += 1
+        elif x:
+            fbs += 1
+    unequal = 0
+    for i, yip in enumerate(decoded[:N]):
+        yi = i in y_sparse
+        if yi or yip:
+            unequal |= yi != bool(yip)
+    return [unsatisfied, good, bad, fbs, fbu, int(not unequal)]
+
+
+def test_decode_scored_equals_reference_stats():
+    """scaldpc_bp_decode_scored: the device statistics equal hqc.decode's loops on the decoded vectors,
+    for a workload where some trials fail (few checks) so every counter is exercised."""
+    w = HqcWorkload("hqc128", W=50, R=1400, rho=0.98, seed=2)
+    batch = w.generate(70, seed=4)
+    bpd = bp_decoder(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=40, channel_probs=w.channel_probs)
+    plain = bpd.decode_batch(batch.syndromes)
+    out = bpd.decode_scored(batch.syndromes, batch.y, want_decoding=True)
+    assert np.array_equal(out["decoding"], plain["decoding"]) and np.array_equal(out["iters"], plain["iters"])
+    want = np.array([reference_stats(w.N, plain["decoding"][t], batch.syndromes[t], batch.y[t]) for t in range(70)])
+    assert np.array_equal(out["stats"], want)
+    assert np.array_equal(out["stats"][:, 5].astype(bool), w.success(batch, plain["decoding"]))
+    assert 0 < out["stats"][:, 5].sum() < 70 or out["stats"][:, 2].sum() > 0   # not a degenerate all-success case
+    # without the decoded vectors (the production call): same statistics
+    lean = bpd.decode_scored(batch.syndromes, batch.y)
+    assert lean["decoding"] is None and np.array_equal(lean["stats"], want)
+    with pytest.raises(ValueError):
+        bpd.decode_scored(batch.syndromes, batch.y[:3])
