@@ -198,11 +198,24 @@ int scaldpc_bp_decode(scaldpc_bp *h, int T, const uint8_t *synd, const double *c
  *   stats     T x 6 int32 out: unsatisfied, good_flips, bad_flips, found_bad_satisfied_checks,
  *             found_bad_unsatisfied_checks, success   -- the arguments of tracking.add_decoder_stats (hqc.py:751-759)
  *   decoding  T x n uint8 out, or NULL with host pointers (not copied back)
+ *   n_checks  NULL, or T int32 as scaldpc_bp_decode_nested (the statistics then cover the active checks only)
  * Other arguments, flags and return value as scaldpc_bp_decode.
  */
-int scaldpc_bp_decode_scored(scaldpc_bp *h, int T, int n_msg, const uint8_t *synd, const double *channel_probs,
-                             const int32_t *truth, int weight, int32_t *stats, uint8_t *decoding, int32_t *iters,
-                             int32_t *converged, unsigned flags, void *stream);
+int scaldpc_bp_decode_scored(scaldpc_bp *h, int T, int n_msg, const int32_t *n_checks, const uint8_t *synd,
+                             const double *channel_probs, const int32_t *truth, int weight, int32_t *stats, uint8_t *decoding,
+                             int32_t *iters, int32_t *converged, unsigned flags, void *stream);
+/*
+ * scaldpc_bp_decode_nested -- one batch over NESTED graphs.  The reference's decode_every loop
+ * (hqc.py:953-984) appends measured checks to H and re-decodes on the first R_k rows: H_k = [Hin[:R_k] | I_{R_k}]
+ * (hqc.py:680).  With the handle built on the largest graph [Hin | I_m], trial t decodes on its own prefix:
+ *   n_checks  T int32, 0 <= n_checks[t] <= m: only the checks < n_checks[t] take part (messages, syndrome test);
+ *             the others send the neutral message, so iterations, convergence and the decisions of the message bits and
+ *             of the active checks' error bits equal a decode on H_k with channel_probs / synd cut to match.  The
+ *             decisions reported for the inactive checks' error bits are their priors' (0 when p < 1/2).
+ * Everything else as scaldpc_bp_decode.
+ */
+int scaldpc_bp_decode_nested(scaldpc_bp *h, int T, const int32_t *n_checks, const uint8_t *synd, const double *channel_probs,
+                             uint8_t *decoding, float *llr, int32_t *iters, int32_t *converged, unsigned flags, void *stream);
 /* Shape queries: checks, variables, edges, iteration cap (max_iter = 0 at create time means n, as upstream). */
 int scaldpc_bp_info(const scaldpc_bp *h, int *m, int *n, int *edges, int *max_iter);
 long long scaldpc_bp_launch_count(const scaldpc_bp *h);

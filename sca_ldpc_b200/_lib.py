@@ -24,7 +24,7 @@ SYMBOLS = [
     "scaldpc_last_error", "scaldpc_version", "scaldpc_device_count",
     "scaldpc_qary_create", "scaldpc_qary_destroy", "scaldpc_qary_info", "scaldpc_qary_set_max_iter",
     "scaldpc_qary_decode", "scaldpc_qary_decode_observed", "scaldpc_qary_simulate", "scaldpc_qary_launch_count", "scaldpc_qary_time_kernel",
-    "scaldpc_bp_create", "scaldpc_bp_destroy", "scaldpc_bp_info", "scaldpc_bp_decode", "scaldpc_bp_decode_scored", "scaldpc_bp_launch_count",
+    "scaldpc_bp_create", "scaldpc_bp_destroy", "scaldpc_bp_info", "scaldpc_bp_decode", "scaldpc_bp_decode_scored", "scaldpc_bp_decode_nested", "scaldpc_bp_launch_count",
     "scaldpc_bp_last_run", "scaldpc_bp_time_kernel",
 ]
 
@@ -88,7 +88,9 @@ def lib() -> C.CDLL:
     L.scaldpc_bp_decode.restype = i
     L.scaldpc_bp_decode.argtypes = [vp, i, vp, vp, vp, vp, vp, vp, u, vp]
     L.scaldpc_bp_decode_scored.restype = i
-    L.scaldpc_bp_decode_scored.argtypes = [vp, i, i, vp, vp, vp, i, vp, vp, vp, vp, u, vp]
+    L.scaldpc_bp_decode_scored.argtypes = [vp, i, i, vp, vp, vp, vp, i, vp, vp, vp, vp, u, vp]
+    L.scaldpc_bp_decode_nested.restype = i
+    L.scaldpc_bp_decode_nested.argtypes = [vp, i, vp, vp, vp, vp, vp, vp, vp, u, vp]
     L.scaldpc_bp_launch_count.restype = C.c_longlong
     L.scaldpc_bp_launch_count.argtypes = [vp]
     L.scaldpc_bp_last_run.restype = i

@@ -44,6 +44,9 @@ struct scaldpc_bp {
     size_t cap_stage_T = 0;
     bool stage_probs_t = false, stage_llr = false;
     uint8_t *d_synd = nullptr, *d_dec = nullptr;
+    int32_t *d_nrows = nullptr;        // per-trial active-check counts of a nested-graph decode (device copy, T entries)
+    size_t cap_nrows = 0;
+    const int *cur_nrows = nullptr;    // what the kernels of the running decode see (null outside nested decodes)
     int32_t *d_truth = nullptr, *d_stats = nullptr;  // scaldpc_bp_decode_scored staging (host-pointer calls)
     size_t cap_truth = 0, cap_stats_T = 0;
     double *d_probs = nullptr;
@@ -195,6 +198,7 @@ BpDev view(const scaldpc_bp *h, int cur, bool per_trial_prior, bool want_post)
     p.iters = h->d_iters;
     p.conv = h->d_conv;
     p.counts = h->d_counts;
+    p.nrows = h->cur_nrows;
     return p;
 }
 
@@ -404,6 +408,7 @@ void scaldpc_bp_destroy(scaldpc_bp *h)
     free_stage(h);
     cudaFree(h->d_truth);
     cudaFree(h->d_stats);
+    cudaFree(h->d_nrows);
     cudaFree(h->d_row_ptr);
     cudaFree(h->d_col);
     cudaFree(h->d_col_ptr);
@@ -440,7 +445,7 @@ struct BpScore {
 
 static int bp_decode_impl(scaldpc_bp *h, int T, const uint8_t *synd, const double *channel_probs, uint8_t *decoding,
                           float *llr, int32_t *iters, int32_t *converged, unsigned flags, void *stream,
-                          const BpScore *score)
+                          const BpScore *score, const int32_t *n_checks)
 {
     if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
     if (T < 0) return fail(SCALDPC_ERR_ARG, "T < 0");
@@ -464,6 +469,27 @@ static int bp_decode_impl(scaldpc_bp *h, int T, const uint8_t *synd, const doubl
     const int tiles = (T + 31) / 32;
     int rc;
     if ((rc = ensure_ws(h, tiles, want_post, probs_t))) return rc;
+    struct NrowsGuard {  // the kernels see the per-trial row limits only while this decode runs
+        scaldpc_bp *h;
+        ~NrowsGuard() { h->cur_nrows = nullptr; }
+    } nrows_guard{h};
+    h->cur_nrows = nullptr;
+    if (n_checks) {
+        if (!dev_ptrs)
+            for (int t = 0; t < T; ++t)
+                if (n_checks[t] < 0 || n_checks[t] > h->m)
+                    return fail(SCALDPC_ERR_ARG, "n_checks[%d] = %d is outside 0 .. m = %d", t, n_checks[t], h->m);
+        if ((size_t)T > h->cap_nrows) {
+            cudaFree(h->d_nrows);
+            h->d_nrows = nullptr;
+            h->cap_nrows = 0;
+            SCALDPC_CUDA(cudaMalloc((void **)&h->d_nrows, (size_t)T * sizeof(int32_t)));
+            h->cap_nrows = (size_t)T;
+        }
+        SCALDPC_CUDA(cudaMemcpyAsync(h->d_nrows, n_checks, (size_t)T * sizeof(int32_t),
+                                     dev_ptrs ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+        h->cur_nrows = h->d_nrows;
+    }
 
     const uint8_t *dsynd = synd;
     const double *dprobs = channel_probs;
@@ -558,7 +584,7 @@ static int bp_decode_impl(scaldpc_bp *h, int T, const uint8_t *synd, const doubl
             dtruth = h->d_truth;
             dstats = h->d_stats;
         }
-        k_bp_score<<<(T + 7) / 8, 256, 0, st>>>(ddec, dsynd, dtruth, dstats, T, h->n, score->n_msg, score->weight);
+        k_bp_score<<<(T + 7) / 8, 256, 0, st>>>(ddec, dsynd, dtruth, h->cur_nrows, dstats, T, h->n, score->n_msg, score->weight);
         ++h->launches;
         SCALDPC_CUDA(cudaGetLastError());
         if (!dev_ptrs)
@@ -577,15 +603,22 @@ static int bp_decode_impl(scaldpc_bp *h, int T, const uint8_t *synd, const doubl
 int scaldpc_bp_decode(scaldpc_bp *h, int T, const uint8_t *synd, const double *channel_probs, uint8_t *decoding,
                       float *llr, int32_t *iters, int32_t *converged, unsigned flags, void *stream)
 {
-    return bp_decode_impl(h, T, synd, channel_probs, decoding, llr, iters, converged, flags, stream, nullptr);
+    return bp_decode_impl(h, T, synd, channel_probs, decoding, llr, iters, converged, flags, stream, nullptr, nullptr);
 }
 
-int scaldpc_bp_decode_scored(scaldpc_bp *h, int T, int n_msg, const uint8_t *synd, const double *channel_probs,
-                             const int32_t *truth, int weight, int32_t *stats, uint8_t *decoding, int32_t *iters,
-                             int32_t *converged, unsigned flags, void *stream)
+int scaldpc_bp_decode_nested(scaldpc_bp *h, int T, const int32_t *n_checks, const uint8_t *synd, const double *channel_probs,
+                             uint8_t *decoding, float *llr, int32_t *iters, int32_t *converged, unsigned flags, void *stream)
+{
+    if (!n_checks) return fail(SCALDPC_ERR_ARG, "n_checks is NULL");
+    return bp_decode_impl(h, T, synd, channel_probs, decoding, llr, iters, converged, flags, stream, nullptr, n_checks);
+}
+
+int scaldpc_bp_decode_scored(scaldpc_bp *h, int T, int n_msg, const int32_t *n_checks, const uint8_t *synd,
+                             const double *channel_probs, const int32_t *truth, int weight, int32_t *stats, uint8_t *decoding,
+                             int32_t *iters, int32_t *converged, unsigned flags, void *stream)
 {
     const BpScore score{truth, weight, n_msg, stats};
-    return bp_decode_impl(h, T, synd, channel_probs, decoding, nullptr, iters, converged, flags, stream, &score);
+    return bp_decode_impl(h, T, synd, channel_probs, decoding, nullptr, iters, converged, flags, stream, &score, n_checks);
 }
 
 int scaldpc_bp_last_run(const scaldpc_bp *h, int *iterations_launched, int *compactions)

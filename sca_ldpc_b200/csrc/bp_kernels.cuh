@@ -62,6 +62,7 @@ struct BpDev {
     int *iters;               // T, indexed by ORIGINAL trial
     int *conv;                // T
     int *counts;              // max_iter+2
+    const int *nrows;         // T, indexed by ORIGINAL trial: active checks (a prefix of the rows) of every trial, or null
 };
 
 #ifdef SCALDPC_HOST_MODEL
@@ -122,6 +123,16 @@ __device__ __forceinline__ float bp_parity(float U, float u) { return fmaf(u, fm
 __device__ __forceinline__ float bp_prior_of(const BpDev &p, int tile, int v, int lane)
 {
     return p.per_trial_prior ? p.prior[((size_t)tile * p.n + v) * 32 + lane] : __ldg(p.prior + v);
+}
+
+// Nested graphs (the decode_every loop, hqc.py:953-984, decodes on the first R_k rows of one growing H): every trial has
+// its own prefix of active checks.  An inactive check sends the neutral message (LLR +0: the bit node's sums are
+// unchanged, exactly as if the row were absent) and is left out of the syndrome test.
+__device__ __forceinline__ int bp_row_limit(const BpDev &p, int tile, int lane)
+{
+    if (!p.nrows) return p.m;
+    const int o = __ldg(p.orig + tile * 32 + lane);
+    return o >= 0 ? __ldg(p.nrows + o) : p.m;
 }
 
 __device__ __forceinline__ bool bp_tile_done(const BpDev &p, int tile) { return __ldg(p.done + tile) == __ldg(p.valid + tile); }
@@ -223,6 +234,7 @@ __global__ void __launch_bounds__(kBpCnWarpsMax * 32) k_bp_cn(const BpDev p, con
 #endif
             // sign word: bit 31 = (-1)^synd * product of the signs of ALL inputs (lower bits are garbage)
             uint32_t neg = (__ldg(p.synd_w + (size_t)tile * p.m + check) >> lane) << 31;
+            const uint32_t keep = check < bp_row_limit(p, tile, lane) ? 0xffffffffu : 0u;  // inactive check: +0
             float pre = 0.0f;
             if (FIRST) {
 #ifdef SCALDPC_HOST_MODEL
@@ -254,7 +266,7 @@ __global__ void __launch_bounds__(kBpCnWarpsMax * 32) k_bp_cn(const BpDev p, con
             for (int k = d - 1; k >= 0; --k) {
                 const float x = a[k * 32];
                 const float mag = bp_unfold(bp_parity(P[k * 32], suf));  // parity of the OTHER magnitudes
-                msg[(size_t)k * 32] = bp_float(bp_bits(mag) ^ ((neg ^ bp_bits(x)) & 0x80000000u));  // sign of the OTHERS
+                msg[(size_t)k * 32] = bp_float((bp_bits(mag) ^ ((neg ^ bp_bits(x)) & 0x80000000u)) & keep);  // sign of the OTHERS
                 suf = bp_parity(suf, fabsf(x));
             }
         }
@@ -310,12 +322,14 @@ __global__ void __launch_bounds__(256) k_bp_first_fill(const BpDev p, const floa
     if (bp_tile_done(p, tile)) return;
     const int e_lo = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 8;
     float *msg = p.msg + ((size_t)tile * p.E) * 32 + lane;
+    const int limit = bp_row_limit(p, tile, lane);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         const int e = e_lo + i;
         if (e < p.E) {
-            const uint32_t w = __ldg(p.synd_w + (size_t)tile * p.m + __ldg(edge_row + e));
-            msg[(size_t)e * 32] = bp_float(bp_bits(__ldg(tab + e)) ^ ((w >> lane) << 31));
+            const int row = __ldg(edge_row + e);
+            const uint32_t w = __ldg(p.synd_w + (size_t)tile * p.m + row);
+            msg[(size_t)e * 32] = row < limit ? bp_float(bp_bits(__ldg(tab + e)) ^ ((w >> lane) << 31)) : 0.0f;
         }
     }
 }
@@ -642,6 +656,13 @@ __global__ void __launch_bounds__(256) k_bp_syndrome(const BpDev p)
     const int tile = blockIdx.y;
     const int check = blockIdx.x * blockDim.x + threadIdx.x;
     if (bp_tile_done(p, tile)) return;
+#ifndef SCALDPC_HOST_MODEL
+    __shared__ int lim[32];
+    if (p.nrows) {  // uniform
+        if (threadIdx.x < 32) lim[threadIdx.x] = bp_row_limit(p, tile, threadIdx.x);
+        __syncthreads();
+    }
+#endif
     uint32_t bad = 0;
     if (check < p.m) {
         const uint32_t *dec = p.dec_w + (size_t)tile * p.n;
@@ -649,6 +670,16 @@ __global__ void __launch_bounds__(256) k_bp_syndrome(const BpDev p)
         const int e0 = __ldg(p.row_ptr + check), e1 = __ldg(p.row_ptr + check + 1);
         for (int e = e0; e < e1; ++e) par ^= dec[__ldg(p.col + e)];
         bad = par;
+        if (p.nrows) {  // trials for which this check is inactive cannot fail it
+            uint32_t act = 0;
+#ifdef SCALDPC_HOST_MODEL
+            for (int l = 0; l < 32; ++l) act |= (check < bp_row_limit(p, tile, l) ? 1u : 0u) << l;
+#else
+#pragma unroll
+            for (int l = 0; l < 32; ++l) act |= (check < lim[l] ? 1u : 0u) << l;
+#endif
+            bad &= act;
+        }
     }
 #ifdef SCALDPC_HOST_MODEL
     p.unsat[tile] |= bad;
@@ -877,8 +908,8 @@ __global__ void __launch_bounds__(256) k_bp_unpack_dec(const uint32_t *__restric
 //                         and a measurement error decoded (:732-734)
 //   success               support(decoded[:n_msg]) == truth (:741-749)
 __global__ void __launch_bounds__(256) k_bp_score(const uint8_t *__restrict__ dec, const uint8_t *__restrict__ synd,
-                                                  const int32_t *__restrict__ truth, int32_t *__restrict__ stats, int T, int n,
-                                                  int n_msg, int weight)
+                                                  const int32_t *__restrict__ truth, const int32_t *__restrict__ n_checks,
+                                                  int32_t *__restrict__ stats, int T, int n, int n_msg, int weight)
 {
     const int t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (t >= T) return;
@@ -890,7 +921,8 @@ __global__ void __launch_bounds__(256) k_bp_score(const uint8_t *__restrict__ de
         const int pos = truth[(size_t)t * weight + k];
         good += pos >= 0 && pos < n_msg && d[pos] != 0;
     }
-    for (int i = lane; i < n - n_msg; i += 32) {
+    const int active = n_checks ? min(max(n_checks[t], 0), n - n_msg) : n - n_msg;  // nested graph: the first rows only
+    for (int i = lane; i < active; i += 32) {
         const bool c = s[i] != 0, x = d[n_msg + i] != 0;
         unsat += c;
         fbu += c && !x;

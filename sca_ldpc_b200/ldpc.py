@@ -112,16 +112,21 @@ class bp_decoder:
         return dec.astype(int)
 
     # ---- batched fast path -------------------------------------------------------------------------------
-    def decode_batch(self, syndromes, channel_probs=None, *, want_llr=False, early_stop=True, compact=True, out=None):
+    def decode_batch(self, syndromes, channel_probs=None, *, want_llr=False, early_stop=True, compact=True, out=None,
+                     n_checks=None):
         """syndromes (T, m) uint8; channel_probs None (the constructor's), (n,) or (T, n) float64.
         numpy in -> numpy out; torch CUDA uint8 tensor in -> torch CUDA tensors out.
         Returns dict(decoding (T,n) uint8, log_prob_ratios (T,n) float32 or None, iters (T,), converged (T,)).
         out: optional preallocated C-contiguous uint8 (T, n) numpy array for `decoding` (host path only), e.g. a view
-        of pinned memory so the device-to-host copy of the T*n decision bytes is a true asynchronous DMA."""
+        of pinned memory so the device-to-host copy of the T*n decision bytes is a true asynchronous DMA.
+        n_checks: optional (T,) int32 (host path): nested graphs (scaldpc_bp_decode_nested, hqc.py:953-984): trial t
+        decodes on the first n_checks[t] rows of H = [Hin | I_m] as if the later rows did not exist."""
         flags = 0 if early_stop else _lib.BP_NO_EARLY_STOP
         if not compact:
             flags |= _lib.BP_NO_COMPACT
         if torch is not None and isinstance(syndromes, torch.Tensor) and syndromes.is_cuda:
+            if n_checks is not None:
+                raise NotImplementedError("n_checks is supported for numpy (host) inputs")
             return self._batch_torch(syndromes, channel_probs, flags, want_llr)
         synd = np.ascontiguousarray(syndromes, dtype=np.uint8)
         T = synd.shape[0]
@@ -145,17 +150,31 @@ class bp_decoder:
         iters = np.empty(T, np.int32)
         conv = np.empty(T, np.int32)
         p = lambda a: None if a is None else a.ctypes.data  # noqa: E731
-        _lib.check(_lib.lib().scaldpc_bp_decode(self._h, T, p(synd), p(cp), p(dec), p(llr), p(iters), p(conv), flags,
-                                                None))
+        nc = self._n_checks(n_checks, T)
+        if nc is not None:
+            _lib.check(_lib.lib().scaldpc_bp_decode_nested(self._h, T, p(nc), p(synd), p(cp), p(dec), p(llr), p(iters),
+                                                           p(conv), flags, None))
+        else:
+            _lib.check(_lib.lib().scaldpc_bp_decode(self._h, T, p(synd), p(cp), p(dec), p(llr), p(iters), p(conv), flags,
+                                                    None))
         return dict(decoding=dec, log_prob_ratios=llr, iters=iters, converged=conv)
+
+    def _n_checks(self, n_checks, T):
+        if n_checks is None:
+            return None
+        nc = np.ascontiguousarray(n_checks, dtype=np.int32)
+        if nc.shape != (T,) or (nc < 0).any() or (nc > self.m).any():
+            raise ValueError(f"n_checks must be ({T},) with values in 0 .. {self.m}")
+        return nc
 
     STAT_NAMES = ("unsatisfied", "good_flips", "bad_flips", "found_bad_satisfied_checks",
                   "found_bad_unsatisfied_checks", "success")
 
-    def decode_scored(self, syndromes, truth, channel_probs=None, *, want_decoding=False, early_stop=True):
+    def decode_scored(self, syndromes, truth, channel_probs=None, *, want_decoding=False, early_stop=True, n_checks=None):
         """decode_batch followed, on the device, by the statistics hqc.decode computes from the decoded vector
         (hqc.py:709-758; scaldpc_bp_decode_scored): 24 bytes per trial come back instead of n.  H must be [Hin | I_m].
         syndromes (T, m) uint8, truth (T, weight) int32 = support of the true message of every trial (y_sparse).
+        n_checks: optional (T,) int32, nested graphs as decode_batch(n_checks=...): trial t uses its first n_checks[t] rows.
         Returns dict(stats (T, 6) int32 in STAT_NAMES order, iters, converged, decoding or None)."""
         flags = 0 if early_stop else _lib.BP_NO_EARLY_STOP
         synd = np.ascontiguousarray(syndromes, dtype=np.uint8)
@@ -172,12 +191,13 @@ class bp_decoder:
             flags |= _lib.BP_PROBS_PER_TRIAL
         elif cp.shape != (self.n,):
             raise ValueError(f"channel_probs must have length {self.n}")
+        nc = self._n_checks(n_checks, T)
         stats = np.empty((T, 6), np.int32)
         dec = np.empty((T, self.n), np.uint8) if want_decoding else None
         iters = np.empty(T, np.int32)
         conv = np.empty(T, np.int32)
         p = lambda a: None if a is None else a.ctypes.data  # noqa: E731
-        _lib.check(_lib.lib().scaldpc_bp_decode_scored(self._h, T, self.n - self.m, p(synd), p(cp), p(truth), truth.shape[1],
+        _lib.check(_lib.lib().scaldpc_bp_decode_scored(self._h, T, self.n - self.m, p(nc), p(synd), p(cp), p(truth), truth.shape[1],
                                                        p(stats), p(dec), p(iters), p(conv), flags, None))
         return dict(stats=stats, iters=iters, converged=conv, decoding=dec)
 

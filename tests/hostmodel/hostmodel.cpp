@@ -283,6 +283,7 @@ int hostmodel_bp_decode(int m, int n, const int32_t *row_ptr, const int32_t *col
         p.post = llr ? post.data() : nullptr;
         p.done = set[cur].done.data(); p.valid = set[cur].valid.data(); p.unsat = set[cur].unsat.data();
         p.orig = set[cur].orig.data(); p.iters = vit.data(); p.conv = vconv.data(); p.counts = counts.data();
+        p.nrows = nullptr;
         return p;
     };
     auto write_outputs = [&](int cur, int cur_tiles, const std::vector<uint32_t> &mask) {

@@ -218,3 +218,63 @@ def test_decode_scored_equals_reference_stats():
     assert lean["decoding"] is None and np.array_equal(lean["stats"], want)
     with pytest.raises(ValueError):
         bpd.decode_scored(batch.syndromes, batch.y[:3])
+
+
+def test_nested_graphs_equal_decodes_on_the_truncated_graphs():
+    """scaldpc_bp_decode_nested (the decode_every loop of hqc.py:953-984): one batch whose trials use
+    different prefixes of the rows == separate fp64-oracle decodes on H_k = [Hin[:R_k] | I_{R_k}]."""
+    w = HqcWorkload(variant=(997, 12), W=11, R=420, rho=0.97, seed=7)
+    T = 96
+    batch = w.generate(T, seed=3)
+    levels = np.array([100, 200, 300, 420])
+    n_checks = levels[np.arange(T) % 4].astype(np.int32)
+    bpd = bp_decoder(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=30, channel_probs=w.channel_probs)
+    out = bpd.decode_batch(batch.syndromes, want_llr=True, n_checks=n_checks)
+    sc = bpd.decode_scored(batch.syndromes, batch.y, n_checks=n_checks, want_decoding=True)
+    assert np.array_equal(sc["decoding"], out["decoding"]) and np.array_equal(sc["iters"], out["iters"])
+    some_unconverged = False
+    for R in levels:
+        sel = np.nonzero(n_checks == R)[0]
+        rp, col = w.row_ptr[: R + 1], w.col[: w.row_ptr[R]]
+        probs = w.channel_probs[: w.N + R]
+        ref = O.BinaryBpOracle(csr=(rp, col), shape=(R, w.N + R), max_iter=30, channel_probs=probs).decode_batch(
+            np.ascontiguousarray(batch.syndromes[sel, :R]))
+        assert np.array_equal(out["decoding"][sel, : w.N + R], ref["decoding"]), R
+        assert np.array_equal(out["iters"][sel], ref["iters"]) and np.array_equal(out["converged"][sel], ref["converged"]), R
+        assert (out["decoding"][sel, w.N + R:] == 0).all()
+        for i, t in enumerate(sel):
+            assert util.llr_close(out["log_prob_ratios"][t, : w.N + R], ref["log_prob_ratios"][i]), (R, t)
+            want = reference_stats(w.N, ref["decoding"][i], batch.syndromes[t, :R], batch.y[t])
+            assert sc["stats"][t].tolist() == want, (R, t)
+        some_unconverged |= not ref["converged"].all()
+    assert some_unconverged  # the short prefixes cannot all decode: the freeze / tail paths ran with masks too
+    # full prefix for everybody == the plain decode; no checks at all == the priors' decisions after one iteration
+    full = bpd.decode_batch(batch.syndromes, n_checks=np.full(T, w.m, np.int32))
+    plain = bpd.decode_batch(batch.syndromes)
+    assert np.array_equal(full["decoding"], plain["decoding"]) and np.array_equal(full["iters"], plain["iters"])
+    none = bpd.decode_batch(batch.syndromes, n_checks=np.zeros(T, np.int32))
+    assert (none["decoding"] == 0).all() and (none["iters"] == 1).all() and none["converged"].all()
+    with pytest.raises(ValueError):
+        bpd.decode_batch(batch.syndromes, n_checks=np.full(T, w.m + 1, np.int32))
+
+
+def test_nested_graphs_hqc128_with_compaction():
+    """Nested decode at HQC-128 size with enough trials for active-trial compaction: every trial equals its own
+    single-level decode (same handle, all trials on that level)."""
+    w = HqcWorkload("hqc128", W=50, R=3000, rho=0.9942, seed=0)
+    T = 512
+    batch = w.generate(T, seed=5)
+    levels = np.array([1500, 2000, 2500, 3000])
+    n_checks = levels[(np.arange(T) * 7 // 3) % 4].astype(np.int32)
+    bpd = bp_decoder(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=60, channel_probs=w.channel_probs)
+    out = bpd.decode_batch(batch.syndromes, n_checks=n_checks)
+    assert bpd.last_run()[1] >= 1  # compacted at least once
+    for R in levels:
+        sel = np.nonzero(n_checks == R)[0]
+        one = bpd.decode_batch(np.ascontiguousarray(batch.syndromes[sel]), n_checks=np.full(len(sel), R, np.int32))
+        assert np.array_equal(out["decoding"][sel], one["decoding"]), R
+        assert np.array_equal(out["iters"][sel], one["iters"]), R
+    # success improves with the number of checks (the point of the decode_every loop)
+    ok = w.success(batch, out["decoding"])
+    rates = [ok[n_checks == R].mean() for R in levels]
+    assert rates[-1] > rates[0]
