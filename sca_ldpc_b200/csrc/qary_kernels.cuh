@@ -447,6 +447,7 @@ __global__ void __launch_bounds__(32) k_cn_uniform(const QaryDev p, const int LM
 {
     SCALDPC_DYN_SMEM(float, smem);
     constexpr int B = (Q - 1) / 2;
+    constexpr int TU = 4;  // outputs per register tile: Q + TU - 1 shared-memory loads feed Q * TU candidates
     const float INF = SC_INF;
     const int lane = threadIdx.x;
     const int check = blockIdx.x, tile = blockIdx.y;
@@ -483,8 +484,20 @@ __global__ void __launch_bounds__(32) k_cn_uniform(const QaryDev p, const int LM
 #pragma unroll
             for (int i = 0; i < Q; ++i) a[i] = UA_(k, i);
             const int r = reach(k + 1);
-#pragma unroll 2
-            for (int u = -r; u <= r; ++u) {
+            int u = -r;
+            for (; u + TU - 1 <= r; u += TU) {  // TU outputs share one window of Q + TU - 1 table entries
+                float w[Q + TU - 1];
+#pragma unroll
+                for (int j = 0; j < Q + TU - 1; ++j) w[j] = UP_(k, u - B + j);
+#pragma unroll
+                for (int t = 0; t < TU; ++t) {
+                    MinAcc acc;
+#pragma unroll
+                    for (int i = 0; i < Q; ++i) acc.add(w[t - i + Q - 1] + a[i]);
+                    UP_(k + 1, u + t) = acc.get();
+                }
+            }
+            for (; u <= r; ++u) {
                 MinAcc acc;
 #pragma unroll
                 for (int i = 0; i < Q; ++i) acc.add(UP_(k, u - (i - B)) + a[i]);
@@ -506,26 +519,54 @@ __global__ void __launch_bounds__(32) k_cn_uniform(const QaryDev p, const int LM
 #pragma unroll
         for (int i = 0; i < Q; ++i) a[i] = UA_(j, i);
         const int r = reach(j);
-        MinAcc out[Q];
+        // out[i] = min over u of P_j[u] + G_{j+1}[-u - (i - B)]: every candidate is one addition and no candidate is NaN or
+        // -0 (sanitised inputs), so the minimum does not depend on how the candidates are grouped
+        float out[Q];
         if (j == 0) {
 #pragma unroll
-            for (int i = 0; i < Q; ++i) out[i].add(0.0f + UG_(cur, -(i - B)));
+            for (int i = 0; i < Q; ++i) out[i] = 0.0f + UG_(cur, -(i - B));
         } else {
-#pragma unroll 2
-            for (int u = -r; u <= r; ++u) {
+#pragma unroll
+            for (int i = 0; i < Q; ++i) out[i] = INF;
+            int u = -r;
+            for (; u + TU - 1 <= r; u += TU) {  // TU values of u share one window of G
+                float f[TU], g[Q + TU - 1];
+#pragma unroll
+                for (int t = 0; t < TU; ++t) f[t] = UP_(j, u + t);
+#pragma unroll
+                for (int jj = 0; jj < Q + TU - 1; ++jj) g[jj] = UG_(cur, -u + B - jj);
+#pragma unroll
+                for (int i = 0; i < Q; ++i) {
+                    static_assert(TU == 4, "the grouping below folds four candidates");
+                    out[i] = min3f(min3f(out[i], f[0] + g[i], f[1] + g[1 + i]), f[2] + g[2 + i], f[3] + g[3 + i]);
+                }
+            }
+            for (; u <= r; ++u) {
                 const float f = UP_(j, u);
 #pragma unroll
-                for (int i = 0; i < Q; ++i) out[i].add(f + UG_(cur, -u - (i - B)));
+                for (int i = 0; i < Q; ++i) out[i] = fminf(out[i], f + UG_(cur, -u - (i - B)));
             }
         }
         const int offj = __ldg(p.edge_off + e0 + j);
 #pragma unroll
-        for (int i = 0; i < Q; ++i) msg[(size_t)(offj + i) * 32] = (a[i] < INF) ? out[i].get() : INF;
+        for (int i = 0; i < Q; ++i) msg[(size_t)(offj + i) * 32] = (a[i] < INF) ? out[i] : INF;
         if (j > 0) {
             const int nxt = cur ^ 1;
             for (int i = 0; i < WP; ++i) sG[((size_t)nxt * WP + i) * 32] = INF;
-#pragma unroll 2
-            for (int t = -r; t <= r; ++t) {
+            int t0 = -r;
+            for (; t0 + TU - 1 <= r; t0 += TU) {
+                float w[Q + TU - 1];
+#pragma unroll
+                for (int jj = 0; jj < Q + TU - 1; ++jj) w[jj] = UG_(cur, t0 - B + jj);
+#pragma unroll
+                for (int t = 0; t < TU; ++t) {
+                    MinAcc acc;
+#pragma unroll
+                    for (int i = 0; i < Q; ++i) acc.add(a[i] + w[t - i + Q - 1]);
+                    UG_(nxt, t0 + t) = acc.get();
+                }
+            }
+            for (int t = t0; t <= r; ++t) {
                 MinAcc acc;
 #pragma unroll
                 for (int i = 0; i < Q; ++i) acc.add(a[i] + UG_(cur, t - (i - B)));
