@@ -442,12 +442,49 @@ __global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGene
 // loads in flight; P_0 and P_L are scalars, which leaves 72 KB per warp = three CTAs per SM: the pass is bound by
 // shared-memory latency).
 // -----------------------------------------------------------------------------------------------------------
+// Register tiles of k_cn_uniform.  conv: TU outputs dst[t] = min_i (src[t - i + Q - 1] + a[i]) from ONE window of
+// Q + TU - 1 consecutive table entries (src -> entry of the lowest index; entries are 32 floats apart), candidates in
+// the order i = 0 .. Q-1 as the scalar code.  comb: folds TU values f[t] of P_j into out[i] = min(out[i], f[t] + g[t + i]),
+// g[jj] = the entry jj BELOW gtop.
+template <int Q, int TU>
+__device__ __forceinline__ void cn_uniform_conv(const float *src, const float (&a)[Q], float *dst)
+{
+    float w[Q + TU - 1];
+#pragma unroll
+    for (int j = 0; j < Q + TU - 1; ++j) w[j] = src[j * 32];
+#pragma unroll
+    for (int t = 0; t < TU; ++t) {
+        MinAcc acc;
+#pragma unroll
+        for (int i = 0; i < Q; ++i) acc.add(w[t - i + Q - 1] + a[i]);
+        dst[t * 32] = acc.get();
+    }
+}
+
+template <int Q, int TU>
+__device__ __forceinline__ void cn_uniform_comb(const float *fsrc, const float *gtop, float (&out)[Q])
+{
+    float f[TU], g[Q + TU - 1];
+#pragma unroll
+    for (int t = 0; t < TU; ++t) f[t] = fsrc[t * 32];
+#pragma unroll
+    for (int jj = 0; jj < Q + TU - 1; ++jj) g[jj] = gtop[-jj * 32];
+#pragma unroll
+    for (int i = 0; i < Q; ++i) {
+        if (TU == 1) {
+            out[i] = fminf(out[i], f[0] + g[i]);
+        } else {
+#pragma unroll
+            for (int t = 0; t < TU; t += 2) out[i] = min3f(out[i], f[t] + g[t + i], f[t + 1] + g[t + 1 + i]);
+        }
+    }
+}
+
 template <int Q>
 __global__ void __launch_bounds__(32) k_cn_uniform(const QaryDev p, const int LMAX, const int HH)
 {
     SCALDPC_DYN_SMEM(float, smem);
     constexpr int B = (Q - 1) / 2;
-    constexpr int TU = 4;  // outputs per register tile: Q + TU - 1 shared-memory loads feed Q * TU candidates
     const float INF = SC_INF;
     const int lane = threadIdx.x;
     const int check = blockIdx.x, tile = blockIdx.y;
@@ -484,25 +521,13 @@ __global__ void __launch_bounds__(32) k_cn_uniform(const QaryDev p, const int LM
 #pragma unroll
             for (int i = 0; i < Q; ++i) a[i] = UA_(k, i);
             const int r = reach(k + 1);
-            int u = -r;
-            for (; u + TU - 1 <= r; u += TU) {  // TU outputs share one window of Q + TU - 1 table entries
-                float w[Q + TU - 1];
-#pragma unroll
-                for (int j = 0; j < Q + TU - 1; ++j) w[j] = UP_(k, u - B + j);
-#pragma unroll
-                for (int t = 0; t < TU; ++t) {
-                    MinAcc acc;
-#pragma unroll
-                    for (int i = 0; i < Q; ++i) acc.add(w[t - i + Q - 1] + a[i]);
-                    UP_(k + 1, u + t) = acc.get();
-                }
+            int u = -r;  // P_{k+1}[u] = min_i P_k[u - (i - B)] + a[i]
+            for (; u + 7 <= r; u += 8) cn_uniform_conv<Q, 8>(&UP_(k, u - B), a, &UP_(k + 1, u));
+            if (u + 3 <= r) {
+                cn_uniform_conv<Q, 4>(&UP_(k, u - B), a, &UP_(k + 1, u));
+                u += 4;
             }
-            for (; u <= r; ++u) {
-                MinAcc acc;
-#pragma unroll
-                for (int i = 0; i < Q; ++i) acc.add(UP_(k, u - (i - B)) + a[i]);
-                UP_(k + 1, u) = acc.get();
-            }
+            for (; u <= r; ++u) cn_uniform_conv<Q, 1>(&UP_(k, u - B), a, &UP_(k + 1, u));
         }
         MinAcc acc;
 #pragma unroll
@@ -529,23 +554,12 @@ __global__ void __launch_bounds__(32) k_cn_uniform(const QaryDev p, const int LM
 #pragma unroll
             for (int i = 0; i < Q; ++i) out[i] = INF;
             int u = -r;
-            for (; u + TU - 1 <= r; u += TU) {  // TU values of u share one window of G
-                float f[TU], g[Q + TU - 1];
-#pragma unroll
-                for (int t = 0; t < TU; ++t) f[t] = UP_(j, u + t);
-#pragma unroll
-                for (int jj = 0; jj < Q + TU - 1; ++jj) g[jj] = UG_(cur, -u + B - jj);
-#pragma unroll
-                for (int i = 0; i < Q; ++i) {
-                    static_assert(TU == 4, "the grouping below folds four candidates");
-                    out[i] = min3f(min3f(out[i], f[0] + g[i], f[1] + g[1 + i]), f[2] + g[2 + i], f[3] + g[3 + i]);
-                }
+            for (; u + 7 <= r; u += 8) cn_uniform_comb<Q, 8>(&UP_(j, u), &UG_(cur, -u + B), out);
+            if (u + 3 <= r) {
+                cn_uniform_comb<Q, 4>(&UP_(j, u), &UG_(cur, -u + B), out);
+                u += 4;
             }
-            for (; u <= r; ++u) {
-                const float f = UP_(j, u);
-#pragma unroll
-                for (int i = 0; i < Q; ++i) out[i] = fminf(out[i], f + UG_(cur, -u - (i - B)));
-            }
+            for (; u <= r; ++u) cn_uniform_comb<Q, 1>(&UP_(j, u), &UG_(cur, -u + B), out);
         }
         const int offj = __ldg(p.edge_off + e0 + j);
 #pragma unroll
@@ -553,25 +567,13 @@ __global__ void __launch_bounds__(32) k_cn_uniform(const QaryDev p, const int LM
         if (j > 0) {
             const int nxt = cur ^ 1;
             for (int i = 0; i < WP; ++i) sG[((size_t)nxt * WP + i) * 32] = INF;
-            int t0 = -r;
-            for (; t0 + TU - 1 <= r; t0 += TU) {
-                float w[Q + TU - 1];
-#pragma unroll
-                for (int jj = 0; jj < Q + TU - 1; ++jj) w[jj] = UG_(cur, t0 - B + jj);
-#pragma unroll
-                for (int t = 0; t < TU; ++t) {
-                    MinAcc acc;
-#pragma unroll
-                    for (int i = 0; i < Q; ++i) acc.add(a[i] + w[t - i + Q - 1]);
-                    UG_(nxt, t0 + t) = acc.get();
-                }
+            int t = -r;  // G_j[t] = min_i a[i] + G_{j+1}[t - (i - B)]
+            for (; t + 7 <= r; t += 8) cn_uniform_conv<Q, 8>(&UG_(cur, t - B), a, &UG_(nxt, t));
+            if (t + 3 <= r) {
+                cn_uniform_conv<Q, 4>(&UG_(cur, t - B), a, &UG_(nxt, t));
+                t += 4;
             }
-            for (int t = t0; t <= r; ++t) {
-                MinAcc acc;
-#pragma unroll
-                for (int i = 0; i < Q; ++i) acc.add(a[i] + UG_(cur, t - (i - B)));
-                UG_(nxt, t) = acc.get();
-            }
+            for (; t <= r; ++t) cn_uniform_conv<Q, 1>(&UG_(cur, t - B), a, &UG_(nxt, t));
             cur = nxt;
         }
     }
