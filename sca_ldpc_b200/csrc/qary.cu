@@ -414,8 +414,7 @@ cn_uniform_fn pick_cn_uniform(int q)
 }
 size_t uniform_smem_bytes(const scaldpc_qary *h)
 {
-    const int hh = (h->wmax - 1) / 2, wp = 2 * (hh + h->B) + 1;
-    return ((size_t)h->lmax * h->Q + (size_t)std::max(0, h->lmax - 1) * wp + 2 * (size_t)wp) * 32 * sizeof(float);
+    return (size_t)cn_uniform_rows(h->lmax, h->Q, (h->wmax - 1) / 2) * 32 * sizeof(float);
 }
 
 size_t generic_smem_bytes(const scaldpc_qary *h, CnGenericArgs *g)

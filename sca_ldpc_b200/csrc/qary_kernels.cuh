@@ -480,6 +480,29 @@ __device__ __forceinline__ void cn_uniform_comb(const float *fsrc, const float *
     }
 }
 
+// Shared-memory rows (of 32 floats) of k_cn_uniform for rows of up to L variables of alphabet [-B, B], window half
+// width HH: the middle variables' messages, P_1 .. P_{L-1} at their exact padded widths, two G buffers.
+__host__ __device__ inline int cn_uniform_reach(int k, int L, int B, int HH)
+{
+    const int a = k * B, b = (L - k) * B;
+    const int m = a < b ? a : b;
+    return m < HH ? m : HH;
+}
+__host__ __device__ inline int cn_uniform_p_rows(int L, int B, int HH)
+{
+    int rows = 0;
+    for (int k = 1; k <= L - 1; ++k) rows += 2 * (cn_uniform_reach(k + 1, L, B, HH) + B) + 1;
+    return rows;
+}
+__host__ __device__ inline int cn_uniform_rows(int L, int Q, int HH)
+{
+    const int B = (Q - 1) / 2;
+    return (L > 2 ? (L - 2) * Q : 0) + cn_uniform_p_rows(L, B, HH) + 2 * (2 * (HH + B) + 1);
+}
+
+// One CTA (one warp) = one (check, tile); lane = trial.  Shared memory per item: the messages of the middle variables
+// (the first and the last stay in registers), P_1 .. P_{L-1} at their exact padded widths 2 (r_{k+1} + B) + 1 and two
+// G buffers -- 55 KB for (L, B) = (7, 7), so FOUR items are resident per SM, one warp per scheduler.
 template <int Q>
 __global__ void __launch_bounds__(32) k_cn_uniform(const QaryDev p, const int LMAX, const int HH)
 {
@@ -491,58 +514,83 @@ __global__ void __launch_bounds__(32) k_cn_uniform(const QaryDev p, const int LM
     const int e0 = __ldg(p.row_ptr + check), L = __ldg(p.row_ptr + check + 1) - e0;
     if (L <= 0) return;
     float *msg = p.msg + (size_t)tile * p.S * 32 + lane;
-    const int WP = 2 * (HH + B) + 1;  // padded table width; index of partial sum u is u + HH + B
-    float *sA = smem + lane;                          // [L][Q]
-    float *sP = sA + (size_t)LMAX * Q * 32;           // [L-1][WP]: P_1 .. P_{L-1} (P_0 = {0: 0} and P_L[0] are scalars)
-    float *sG = sP + (size_t)(LMAX - 1) * WP * 32;    // [2][WP]
-#define UA_(k, i) sA[((k)*Q + (i)) * 32]
-#define UP_(k, u) sP[(((k)-1) * WP + (u) + HH + B) * 32]
+    const int WP = 2 * (HH + B) + 1;  // width of a G buffer; index of partial sum u is u + HH + B
+    float *sA = smem + lane;                                                     // [L-2][Q]: variables 1 .. L-2
+    float *sP = sA + (size_t)(LMAX > 2 ? LMAX - 2 : 0) * Q * 32;                 // P_1 .. P_{L-1}, back to back
+    float *sG = sP + (size_t)cn_uniform_p_rows(LMAX, B, HH) * 32;                // [2][WP]
+#define UA_(k, i) sA[(((k)-1) * Q + (i)) * 32]
 #define UG_(b, u) sG[((b)*WP + (u) + HH + B) * 32]
-    const int all = L * B;
-    auto reach = [&](int k) { return min(min(k * B, all - k * B), HH); };  // r_k
+    auto reach = [&](int k) { return cn_uniform_reach(k, L, B, HH); };  // r_k
+    auto phw = [&](int k) { return reach(k + 1) + B; };                 // half width of the stored P_k
 
-    for (int k = 0; k < L; ++k) {
+    float afirst[Q], alast[Q];  // messages of variable 0 and variable L-1
+    {
+        const int off0 = __ldg(p.edge_off + e0), offl = __ldg(p.edge_off + e0 + L - 1);
+#pragma unroll
+        for (int i = 0; i < Q; ++i) afirst[i] = sanitize(msg[(size_t)(off0 + i) * 32]);
+#pragma unroll
+        for (int i = 0; i < Q; ++i) alast[i] = sanitize(msg[(size_t)(offl + i) * 32]);
+    }
+    for (int k = 1; k < L - 1; ++k) {
         const int off = __ldg(p.edge_off + e0 + k);
 #pragma unroll
         for (int i = 0; i < Q; ++i) UA_(k, i) = sanitize(msg[(size_t)(off + i) * 32]);
     }
-    for (int i = 0; i < (L - 1) * WP; ++i) sP[(size_t)i * 32] = INF;
+    const int prows = cn_uniform_p_rows(L, B, HH);
+    for (int i = 0; i < prows; ++i) sP[(size_t)i * 32] = INF;
     for (int i = 0; i < 2 * WP; ++i) sG[(size_t)i * 32] = INF;
 
     // ---- forward: P_1 = 0 + a_0, then P_{k+1} from P_k for k = 1 .. L-2; P_L only at u = 0
-    float pl0;  // P_L[0]: the cheapest complete configuration
+    float pl0;           // P_L[0]: the cheapest complete configuration
+    int poff = 0;        // first row of the current P table
+    float *Pc = sP;      // its entry u = 0
     if (L == 1) {
-        pl0 = 0.0f + UA_(0, B);
+        pl0 = 0.0f + afirst[B];
     } else {
         const int r1 = reach(1);
-        for (int u = -r1; u <= r1; ++u) UP_(1, u) = 0.0f + UA_(0, u + B);
+        Pc = sP + (size_t)(poff + phw(1)) * 32;
+#pragma unroll
+        for (int i = 0; i < Q; ++i)
+            if (i - B >= -r1 && i - B <= r1) Pc[(i - B) * 32] = 0.0f + afirst[i];
         for (int k = 1; k < L - 1; ++k) {
             float a[Q];
 #pragma unroll
             for (int i = 0; i < Q; ++i) a[i] = UA_(k, i);
             const int r = reach(k + 1);
+            const int noff = poff + 2 * phw(k) + 1;
+            float *Pn = sP + (size_t)(noff + phw(k + 1)) * 32;
             int u = -r;  // P_{k+1}[u] = min_i P_k[u - (i - B)] + a[i]
-            for (; u + 7 <= r; u += 8) cn_uniform_conv<Q, 8>(&UP_(k, u - B), a, &UP_(k + 1, u));
+            for (; u + 7 <= r; u += 8) cn_uniform_conv<Q, 8>(Pc + (u - B) * 32, a, Pn + u * 32);
             if (u + 3 <= r) {
-                cn_uniform_conv<Q, 4>(&UP_(k, u - B), a, &UP_(k + 1, u));
+                cn_uniform_conv<Q, 4>(Pc + (u - B) * 32, a, Pn + u * 32);
                 u += 4;
             }
-            for (; u <= r; ++u) cn_uniform_conv<Q, 1>(&UP_(k, u - B), a, &UP_(k + 1, u));
+            for (; u <= r; ++u) cn_uniform_conv<Q, 1>(Pc + (u - B) * 32, a, Pn + u * 32);
+            poff = noff;
+            Pc = Pn;
         }
-        MinAcc acc;
+        MinAcc acc;  // Pc = P_{L-1}
 #pragma unroll
-        for (int i = 0; i < Q; ++i) acc.add(UP_(L - 1, -(i - B)) + UA_(L - 1, i));
+        for (int i = 0; i < Q; ++i) acc.add(Pc[-(i - B) * 32] + alast[i]);
         pl0 = acc.get();
     }
     if (!(pl0 < INF)) atomicMin(p.status + tile * 32 + lane, SCALDPC_ERR_NO_CONFIG);
 
-    // ---- backward + combine; G_{j+1} lives in sG[cur]
+    // ---- backward + combine; G_{j+1} lives in sG[cur]; Pc / poff walk back from P_{L-1} to P_1
     int cur = 0;
     UG_(0, 0) = 0.0f;
     for (int j = L - 1; j >= 0; --j) {
         float a[Q];
+        if (j == L - 1) {
 #pragma unroll
-        for (int i = 0; i < Q; ++i) a[i] = UA_(j, i);
+            for (int i = 0; i < Q; ++i) a[i] = alast[i];
+        } else if (j == 0) {
+#pragma unroll
+            for (int i = 0; i < Q; ++i) a[i] = afirst[i];
+        } else {
+#pragma unroll
+            for (int i = 0; i < Q; ++i) a[i] = UA_(j, i);
+        }
         const int r = reach(j);
         // out[i] = min over u of P_j[u] + G_{j+1}[-u - (i - B)]: every candidate is one addition and no candidate is NaN or
         // -0 (sanitised inputs), so the minimum does not depend on how the candidates are grouped
@@ -554,12 +602,12 @@ __global__ void __launch_bounds__(32) k_cn_uniform(const QaryDev p, const int LM
 #pragma unroll
             for (int i = 0; i < Q; ++i) out[i] = INF;
             int u = -r;
-            for (; u + 7 <= r; u += 8) cn_uniform_comb<Q, 8>(&UP_(j, u), &UG_(cur, -u + B), out);
+            for (; u + 7 <= r; u += 8) cn_uniform_comb<Q, 8>(Pc + u * 32, &UG_(cur, -u + B), out);
             if (u + 3 <= r) {
-                cn_uniform_comb<Q, 4>(&UP_(j, u), &UG_(cur, -u + B), out);
+                cn_uniform_comb<Q, 4>(Pc + u * 32, &UG_(cur, -u + B), out);
                 u += 4;
             }
-            for (; u <= r; ++u) cn_uniform_comb<Q, 1>(&UP_(j, u), &UG_(cur, -u + B), out);
+            for (; u <= r; ++u) cn_uniform_comb<Q, 1>(Pc + u * 32, &UG_(cur, -u + B), out);
         }
         const int offj = __ldg(p.edge_off + e0 + j);
 #pragma unroll
@@ -575,10 +623,13 @@ __global__ void __launch_bounds__(32) k_cn_uniform(const QaryDev p, const int LM
             }
             for (; t <= r; ++t) cn_uniform_conv<Q, 1>(&UG_(cur, t - B), a, &UG_(nxt, t));
             cur = nxt;
+            if (j > 1) {
+                poff -= 2 * phw(j - 1) + 1;
+                Pc = sP + (size_t)(poff + phw(j - 1)) * 32;
+            }
         }
     }
 #undef UA_
-#undef UP_
 #undef UG_
 }
 
