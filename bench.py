@@ -277,7 +277,8 @@ def run_ours(args, kind, wl, iters, cfg):
         # reads the sum-variable priors; the sum-variables' own messages never travel
         cn_bytes = 8 * (dec.msg_slots - (dec.R * dec.QS if dec.special else 0)) + 4 * (dec.R * dec.QS if dec.special else 0)
         vn_bytes = 8 * (dec.msg_slots - (dec.R * dec.QS if dec.special else 0)) + 4 * dec.bvars * dec.Q
-        cn_name = "k_cn_fast (check-node pass)" if special else "k_cn_generic (check-node pass, runtime shape)"
+        cn_name = ("k_cn_fast (check-node pass)" if special else
+                   f"k_cn_uniform<{dec.Q}> (check-node pass, generic decoder, reachable-window tables in shared memory)")
     else:
         dec = bp_decoder(csr=(wl.row_ptr, wl.col), shape=(wl.m, wl.n), max_iter=iters, channel_probs=wl.channel_probs,
                          device=local)
@@ -572,7 +573,7 @@ def main():
         cfg = {"workload": f"{args.workload}: generic q-ary min-sum decoder Decoder<450,150,3,7,15,7> on the reference's criterion "
                            f"input (benches/decoder.rs:38-62), {args.trials} trials per GPU per step, {iters} iterations",
                "trials_per_gpu": args.trials, "iterations": iters, "edges": int((wl.H != 0).sum()),
-               "check_node": "forward/backward (min,+), runtime-shape kernel", "inputs": "larger than L2", "oracle_accuracy": None}
+               "check_node": "forward/backward (min,+), k_cn_uniform<Q>: Q templated, row weights at run time", "inputs": "larger than L2", "oracle_accuracy": None}
     elif kind == "qary":
         cfg = {"workload": f"{args.workload}: q-ary min-sum BP, H {wl.R}x{wl.N} (sum_weight {wl.sum_weight}, "
                            f"check_blocks {wl.check_blocks}), alphabets {wl.Q}/{wl.QS}, {args.trials} trials per GPU per step, "
