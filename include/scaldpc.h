@@ -54,10 +54,22 @@ typedef struct scaldpc_qary scaldpc_qary;
 /* decode flags */
 #define SCALDPC_IN_LLR 0x1u       /* inputs are LLRs (skip into_llr); default: probabilities (pydecoder.rs:62) */
 #define SCALDPC_DEVICE_PTRS 0x2u  /* all data pointers are device pointers on the handle's device */
-#define SCALDPC_CN_EXACT 0x4u     /* check node in the reference's rounding order (bit-exact); default: fast
-                                     forward/backward (min,+) convolution, <= ~1e-5 from the reference */
+#define SCALDPC_CN_EXACT 0x4u     /* every trial with the check node in the reference's rounding order (decisions AND
+                                     posteriors bit-exact).  Default: fast forward/backward (min,+) convolution,
+                                     VERIFIED -- see SCALDPC_NO_VERIFY */
 #define SCALDPC_CN_GENERIC 0x8u   /* force the runtime-shape kernels (check node AND variable node) even where a
                                      specialised one exists */
+#define SCALDPC_NO_VERIFY 0x100u  /* skip the verification of the fast path.  By default the last iteration flags
+                                     every trial whose hard decisions could depend on the rounding order of the check
+                                     node -- a posterior whose two smallest entries are within the risk margin
+                                     (default 1e-2, scaldpc_qary_set_risk_margin), or decisions that violate a parity
+                                     check sum_j h_ij s_j (+ s_sum,i) = 0, i.e. every trial that did not converge --
+                                     and decodes the flagged trials AGAIN with the exact-order check node
+                                     (decoder_special.rs:539-553 arithmetic), overwriting their outputs.  Unflagged
+                                     trials keep the fast path's posteriors (measured <= 6.1e-5 from the reference's;
+                                     the flagged ones, where up to 2.6e-4 was seen, become bit-exact).  Costs one
+                                     stream synchronisation per batch and the re-decode of ~1-3 % of a decodable
+                                     workload's trials (all of an undecodable one's). */
 
 /*
  * scaldpc_qary_create -- replaces `#[new] fn new(py_parity_check, iterations)` (pydecoder.rs:24-45, 96-117),
@@ -92,9 +104,14 @@ int scaldpc_qary_set_max_iter(scaldpc_qary *h, int max_iter);
  *   post      T x BVARS x Q   float32 out or NULL: final `sum` vectors (decoder.rs:638-642)
  *   post_sum  T x R x QS      float32 out or NULL
  *   status    T               int32 out or NULL: per-trial 0 / SCALDPC_ERR_PROB_SUM / _NO_MAX / _NO_CONFIG
- *   stream    cudaStream_t (as void*), NULL = default stream.  With SCALDPC_DEVICE_PTRS the call is
- *             asynchronous on `stream`; with host pointers it returns after the results are in `hard`.
- * Returns 0, or the most severe per-trial error (outputs of failed trials are unspecified).
+ *   stream    cudaStream_t (as void*), NULL = default stream.  With host pointers the call returns after the
+ *             results are in `hard`.  With SCALDPC_DEVICE_PTRS all work is enqueued on `stream`; the default
+ *             (verified) mode synchronises the stream once per pass of <= 65536 trials to read the flagged-trial
+ *             count, the exact-order re-decode that may follow is asynchronous again.  With SCALDPC_DEVICE_PTRS and
+ *             SCALDPC_NO_VERIFY or SCALDPC_CN_EXACT the call never synchronises.
+ * Returns 0, or the most severe per-trial error (outputs of failed trials are unspecified).  Exception: a
+ * SCALDPC_DEVICE_PTRS call that does not synchronise (previous sentence) cannot know the per-trial errors when it
+ * returns -- it returns 0 and reports them through `status` only.
  */
 int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in_sum, int8_t *hard, float *post,
                         float *post_sum, int32_t *status, unsigned flags, void *stream);
@@ -153,6 +170,12 @@ int scaldpc_qary_simulate(scaldpc_qary *h, int T, uint64_t seed, uint64_t first_
 /* Kernels launched by this handle so far (for bench.py's "gpu_launches") and device time is NOT tracked
  * here -- callers time with CUDA events on `stream`. */
 long long scaldpc_qary_launch_count(const scaldpc_qary *h);
+/* Statistics of the last decode / decode_observed / simulate call on this handle: trials decoded and how many of
+ * them the verification re-decoded with the exact-order check node (0 with SCALDPC_NO_VERIFY / SCALDPC_CN_EXACT). */
+int scaldpc_qary_last_run(const scaldpc_qary *h, long long *trials, long long *redecoded);
+/* Risk margin of the verification (absolute LLR difference between a posterior's two smallest entries below which
+ * the trial is re-decoded); default 1e-2, or the environment variable SCALDPC_RISK_MARGIN at create time. */
+int scaldpc_qary_set_risk_margin(scaldpc_qary *h, float eps);
 
 /*
  * Per-kernel timing probe used by bench.py's roofline line: runs `reps` back-to-back launches of ONE kernel
@@ -196,8 +219,12 @@ int scaldpc_bp_decode(scaldpc_bp *h, int T, const uint8_t *synd, const double *c
  * (hqc.py:680): columns < n_msg = n - m are message bits, column n_msg + i is the measurement error of check i.
  *   truth     T x weight int32: support of the true message of every trial (y_sparse, hqc.py:1043-1046), distinct
  *   stats     T x 6 int32 out: unsatisfied, good_flips, bad_flips, found_bad_satisfied_checks,
- *             found_bad_unsatisfied_checks, success   -- the arguments of tracking.add_decoder_stats (hqc.py:751-759)
- *   decoding  T x n uint8 out, or NULL with host pointers (not copied back)
+ *             found_bad_unsatisfied_checks, success   -- the arguments of tracking.add_decoder_stats (hqc.py:751-759).
+ *             hqc.decode scores the CORRECTED word msg ^ error (bpd.decode of a length-n vector, hqc.py:703-708): with
+ *             c_i the measured check bit and e_i the decoded measurement error, found_bad_unsatisfied counts c_i = 1 and
+ *             e_i = 1, found_bad_satisfied counts c_i = 0 and e_i = 1.
+ *   decoding  T x n uint8 out, or NULL with host pointers (not copied back): the ERROR ESTIMATE as scaldpc_bp_decode
+ *             returns it, not the corrected word
  *   n_checks  NULL, or T int32 as scaldpc_bp_decode_nested (the statistics then cover the active checks only)
  * Other arguments, flags and return value as scaldpc_bp_decode.
  */

@@ -70,6 +70,7 @@ def lib():
         L.oracle_min_sum_batch_f32.argtypes = [vp, i, i, i, i, vp, vp, vp, vp, vp, vp, i]
         L.oracle_min_sum_batch_f32.restype = i
         L.oracle_max_threads.restype = i
+        L.oracle_has_openmp.restype = i
         L.bp_graph_build.argtypes = [i, i, vp, vp, C.POINTER(vp)]
         L.bp_graph_build.restype = i
         L.bp_graph_free.argtypes = [vp]
@@ -182,6 +183,10 @@ class QaryOracle:
 
 def max_threads() -> int:
     return lib().oracle_max_threads()
+
+
+def has_openmp() -> bool:
+    return bool(lib().oracle_has_openmp())
 
 
 def dense_to_csr(H):

@@ -186,6 +186,16 @@ int oracle_min_sum_batch_f32(const oracle_graph *g, int max_iter, int algo, int 
     return worst;
 }
 
+/* 1 when the batched drivers really run one decode per thread (built with -fopenmp). */
+int oracle_has_openmp(void)
+{
+#ifdef _OPENMP
+    return 1;
+#else
+    return 0;
+#endif
+}
+
 int oracle_max_threads(void)
 {
 #ifdef _OPENMP

@@ -21,6 +21,7 @@ NVCC_FLAGS = [
     "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC,-O2,-Wall",
     "-shared",
+    "--threads", "2",  # qary.cu and bp.cu compile side by side
 ]
 
 

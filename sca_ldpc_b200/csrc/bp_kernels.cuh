@@ -904,8 +904,11 @@ __global__ void __launch_bounds__(256) k_bp_unpack_dec(const uint32_t *__restric
 // stats[t] = {unsatisfied, good_flips, bad_flips, found_bad_satisfied_checks, found_bad_unsatisfied_checks, success}:
 //   good/bad flips        decoded message bits inside / outside the true support (:717-725)
 //   unsatisfied           checks with syndrome bit 1 (:727-728)
-//   found_bad_unsatisfied syndrome bit 1 and NO measurement error decoded (:729-731); found_bad_satisfied: syndrome bit 0
-//                         and a measurement error decoded (:732-734)
+//   found_bad_*           hqc.decode scores the CORRECTED vector decoded = msg ^ error (bpd.decode of a length-n word,
+//                         hqc.py:703-708), so decoded[n_msg + i] = c_i ^ e_i with c_i the measured check bit and e_i the
+//                         decoded measurement error (`dec` here is the error estimate e):
+//                         found_bad_unsatisfied = #{c_i = 1 and not decoded} = #{c_i = 1 and e_i = 1} (:729-731),
+//                         found_bad_satisfied   = #{c_i = 0 and decoded}     = #{c_i = 0 and e_i = 1} (:732-734)
 //   success               support(decoded[:n_msg]) == truth (:741-749)
 __global__ void __launch_bounds__(256) k_bp_score(const uint8_t *__restrict__ dec, const uint8_t *__restrict__ synd,
                                                   const int32_t *__restrict__ truth, const int32_t *__restrict__ n_checks,
@@ -923,10 +926,10 @@ __global__ void __launch_bounds__(256) k_bp_score(const uint8_t *__restrict__ de
     }
     const int active = n_checks ? min(max(n_checks[t], 0), n - n_msg) : n - n_msg;  // nested graph: the first rows only
     for (int i = lane; i < active; i += 32) {
-        const bool c = s[i] != 0, x = d[n_msg + i] != 0;
+        const bool c = s[i] != 0, e = d[n_msg + i] != 0;
         unsat += c;
-        fbu += c && !x;
-        fbs += !c && x;
+        fbu += c && e;
+        fbs += !c && e;
     }
     flips = __reduce_add_sync(0xffffffffu, flips);
     good = __reduce_add_sync(0xffffffffu, good);

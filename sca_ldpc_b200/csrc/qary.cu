@@ -56,7 +56,14 @@ struct scaldpc_qary {
     bool cap_post = false;
     float *d_msg = nullptr, *d_llr = nullptr, *d_llr_sum = nullptr, *d_post = nullptr, *d_post_sum = nullptr;
     int8_t *d_hard_t = nullptr;
-    int *d_status = nullptr;
+    int *d_status = nullptr;   // 2 x lanes: per-trial status, then scratch for the re-decode pass
+    // at-risk detection + exact-order re-decode of the fast path
+    uint32_t *d_risk = nullptr;   // [tiles] flag words
+    int *d_risk_list = nullptr;   // [tiles*32] flagged trial indices, ascending
+    int *d_scan_out = nullptr;    // {count, worst status}
+    int *h_scan_out = nullptr;    // pinned mirror
+    float risk_eps = 1e-2f;
+    long long last_trials = 0, last_redecoded = 0;  // of the last decode / simulate call
     // staging for host-pointer calls: the batch is cut into chunks and pipelined (H2D of chunk i+1 and D2H of chunk
     // i-1 overlap the decode of chunk i), so every staging buffer exists twice
     size_t cap_stage_T = 0;  // trials per output staging buffer
@@ -102,9 +109,13 @@ void free_workspace(scaldpc_qary *h)
     cudaFree(h->d_post_sum);
     cudaFree(h->d_hard_t);
     cudaFree(h->d_status);
+    cudaFree(h->d_risk);
+    cudaFree(h->d_risk_list);
     h->d_msg = h->d_llr = h->d_llr_sum = h->d_post = h->d_post_sum = nullptr;
     h->d_hard_t = nullptr;
     h->d_status = nullptr;
+    h->d_risk = nullptr;
+    h->d_risk_list = nullptr;
     h->cap_tiles = 0;
     h->cap_post = false;
 }
@@ -193,7 +204,13 @@ int ensure_workspace(scaldpc_qary *h, int tiles, bool want_post)
         SCALDPC_CUDA(cudaMalloc((void **)&h->d_post_sum, std::max<size_t>(1, lanes * h->SLS) * sizeof(float)));
     }
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_hard_t, lanes * h->N));
-    SCALDPC_CUDA(cudaMalloc((void **)&h->d_status, lanes * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_status, 2 * lanes * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_risk, (size_t)t * sizeof(uint32_t)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_risk_list, lanes * sizeof(int)));
+    if (!h->d_scan_out) {
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_scan_out, 2 * sizeof(int)));
+        SCALDPC_CUDA(cudaHostAlloc((void **)&h->h_scan_out, 2 * sizeof(int), cudaHostAllocDefault));
+    }
     h->cap_tiles = t;
     h->cap_post = post;
     return 0;
@@ -376,6 +393,25 @@ const CnFast *pick_cn_fast(int sw, int b)
     return nullptr;
 }
 
+// The exact-order check-node kernel for the same shapes (qary_cn_exact.cuh).
+typedef void (*cn_exact_fn)(const QaryDev, const int, const int, const int);
+struct CnExact {
+    cn_exact_fn fn;
+    size_t smem;
+};
+
+const CnExact *pick_cn_exact(int sw, int b)
+{
+#define CASE(SW_, B_)                                                                            \
+    if (sw == SW_ && b == B_) {                                                                  \
+        static const CnExact t = {k_cn_exact<SW_, B_>, CnExactShape<SW_, B_>::smem_bytes};       \
+        return &t;                                                                               \
+    }
+    CASE(6, 2) CASE(6, 3) CASE(4, 2) CASE(8, 2) CASE(3, 2)
+#undef CASE
+    return nullptr;
+}
+
 vn_fn pick_vn(int q)
 {
     switch (q) {
@@ -439,6 +475,12 @@ int launch_cn(scaldpc_qary *h, const QaryDev &p, int tiles, int it, int iters, u
         const int grid = std::max(1, std::min(h->num_sms, (n_items + kCnWarps - 1) / kCnWarps));
         fast->fn[cn_mode_index(it, iters)]<<<grid, kCnWarps * 32, fast->smem, st>>>(p, n_items);
         ++h->launches;
+    } else if (exact && !force_generic && h->fast_sw) {
+        // exact-order dynamic programme in registers, one warp per (tile, check)
+        const CnExact *ex = pick_cn_exact(h->fast_sw, h->B);
+        const int n_items = tiles * h->R;
+        ex->fn<<<(n_items + kCnExactWarps - 1) / kCnExactWarps, kCnExactWarps * 32, ex->smem, st>>>(p, n_items, first, last);
+        ++h->launches;
     } else if (h->BSUM == 0 && !exact && !force_generic && h->uniform_ok) {
         // generic decoder, one alphabet: the unrolled / padded forward-backward kernel
         if (first) {
@@ -478,13 +520,13 @@ int launch_vn(scaldpc_qary *h, const QaryDev &p, int tiles, bool last, unsigned 
 }
 
 int load_priors(scaldpc_qary *h, const float *in, float *out, int T, int tiles, int rows, int q, bool is_llr,
-                cudaStream_t st)
+                cudaStream_t st, int *status, const int *map)
 {
     const int rpb = std::max(1, 256 / q);
     const int pitch = (rpb * q) | 1;
     dim3 grid((rows + rpb - 1) / rpb, tiles), block(32, kTrRows);
-    k_load_priors<<<grid, block, (size_t)32 * pitch * sizeof(float), st>>>(in, out, T, rows, q, rpb, is_llr,
-                                                                           h->d_status);
+    k_load_priors<<<grid, block, (size_t)32 * pitch * sizeof(float), st>>>(in, out, T, rows, q, rpb, is_llr, status,
+                                                                           map);
     ++h->launches;
     SCALDPC_CUDA(cudaGetLastError());
     return 0;
@@ -536,6 +578,7 @@ int scaldpc_qary_create(const int8_t *H, int R, int N, int b, int bsum, int dv, 
     h->max_iter = max_iter;
     h->device = device;
     if (const char *e = getenv("SCALDPC_MAX_RESIDENT_TRIALS")) h->max_resident = std::max(32, atoi(e));
+    if (const char *e = getenv("SCALDPC_RISK_MARGIN")) h->risk_eps = std::max(0.0f, (float)atof(e));
     h->E = g.E;
     h->S = g.S;
     h->SL = g.SL;
@@ -561,6 +604,8 @@ int scaldpc_qary_create(const int8_t *H, int R, int N, int b, int bsum, int dv, 
         const CnFast *f = pick_cn_fast(h->fast_sw, b);
         for (int i = 0; i < 6; ++i)
             SCALDPC_CUDA(cudaFuncSetAttribute(f->fn[i], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f->smem));
+        const CnExact *ex = pick_cn_exact(h->fast_sw, b);
+        SCALDPC_CUDA(cudaFuncSetAttribute(ex->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ex->smem));
     }
     int rc;
     if ((rc = upload(&h->d_row_ptr, row_ptr)) || (rc = upload(&h->d_col, col)) || (rc = upload(&h->d_sign, sign)) ||
@@ -591,6 +636,8 @@ void scaldpc_qary_destroy(scaldpc_qary *h)
     free_observed(h);
     free_sim(h);
     cudaFree(h->d_status_all);
+    cudaFree(h->d_scan_out);
+    if (h->h_scan_out) cudaFreeHost(h->h_scan_out);
     if (h->s_in) cudaStreamDestroy(h->s_in);
     if (h->s_out) cudaStreamDestroy(h->s_out);
     for (int i = 0; i < 2; ++i) {
@@ -630,6 +677,33 @@ int scaldpc_qary_set_max_iter(scaldpc_qary *h, int max_iter)
 
 long long scaldpc_qary_launch_count(const scaldpc_qary *h) { return h ? h->launches : 0; }
 
+int scaldpc_qary_last_run(const scaldpc_qary *h, long long *trials, long long *redecoded)
+{
+    if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
+    if (trials) *trials = h->last_trials;
+    if (redecoded) *redecoded = h->last_redecoded;
+    return 0;
+}
+
+int scaldpc_qary_set_risk_margin(scaldpc_qary *h, float eps)
+{
+    if (!h || !(eps >= 0.0f)) return fail(SCALDPC_ERR_ARG, "bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    h->risk_eps = eps;
+    return 0;
+}
+
+// The most severe per-trial status of a batch -> return value + error text.
+static int status_error(int worst)
+{
+    if (worst == SCALDPC_ERR_PROB_SUM) return fail(worst, "a prior row does not sum to 1 +- 0.001 (decoder.rs:683-684)");
+    if (worst == SCALDPC_ERR_NO_MAX) return fail(worst, "No maximum probability found (decoder.rs:680)");
+    if (worst == SCALDPC_ERR_NO_CONFIG) return fail(worst, "a check has no valid configuration (decoder.rs:618)");
+    if (worst == SCALDPC_ERR_ARG) return fail(worst, "an observation index is outside its prior table");
+    if (worst < 0) return fail(worst, "a trial failed with status %d", worst);
+    return 0;
+}
+
 // Where the priors of a batch come from.  Vectors: in / in_sum as scaldpc_qary_decode documents them.  Observed:
 // row indices into prior tables (scaldpc_qary_decode_observed); d_tab* are the handle's device LLR tables.
 struct PriorSrc {
@@ -639,50 +713,114 @@ struct PriorSrc {
     int n_rows = 0, n_rows_sum = 0;
 };
 
-// The device pipeline of one batch: priors (device, row-major) -> hard decisions (device, row-major), all on `st`.
-static int decode_on_device(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *dhard, float *dpost, float *dpost_sum,
-                            unsigned flags, cudaStream_t st)
+// Priors of `T` trials (device, row-major; slot t = row map[t] when `map` is given) -> channel LLRs in the tile layout.
+static int stage_priors(scaldpc_qary *h, int T, const PriorSrc &src, unsigned flags, int *status, const int *map,
+                        cudaStream_t st)
 {
     const bool special = h->BSUM > 0;
-    const bool want_post = dpost != nullptr || dpost_sum != nullptr;
     const bool is_llr = flags & SCALDPC_IN_LLR;
     const int tiles = (T + 31) / 32;
     int rc;
-    SCALDPC_CUDA(cudaMemsetAsync(h->d_status, 0, (size_t)tiles * 32 * sizeof(int), st));
     if (src.observed) {
         k_load_observed<<<dim3((h->bvars + kObsRows - 1) / kObsRows, tiles), 256, 0, st>>>(
-            src.obs, h->d_tab_llr, h->d_tab_st, h->d_llr, T, h->bvars, h->Q, src.n_rows, h->d_status);
+            src.obs, h->d_tab_llr, h->d_tab_st, h->d_llr, T, h->bvars, h->Q, src.n_rows, status, map);
         ++h->launches;
         if (special) {
             k_load_observed<<<dim3((h->R + kObsRows - 1) / kObsRows, tiles), 256, 0, st>>>(
-                src.obs_sum, h->d_tab_sum_llr, h->d_tab_sum_st, h->d_llr_sum, T, h->R, h->QS, src.n_rows_sum, h->d_status);
+                src.obs_sum, h->d_tab_sum_llr, h->d_tab_sum_st, h->d_llr_sum, T, h->R, h->QS, src.n_rows_sum, status, map);
             ++h->launches;
         }
         SCALDPC_CUDA(cudaGetLastError());
     } else {
-        if ((rc = load_priors(h, src.in, h->d_llr, T, tiles, h->bvars, h->Q, is_llr, st))) return rc;
-        if (special && (rc = load_priors(h, src.in_sum, h->d_llr_sum, T, tiles, h->R, h->QS, is_llr, st))) return rc;
+        if ((rc = load_priors(h, src.in, h->d_llr, T, tiles, h->bvars, h->Q, is_llr, st, status, map))) return rc;
+        if (special && (rc = load_priors(h, src.in_sum, h->d_llr_sum, T, tiles, h->R, h->QS, is_llr, st, status, map)))
+            return rc;
     }
+    return 0;
+}
 
-    const QaryDev p = dev_view(h, want_post);
-    const int iters = std::max(1, h->max_iter);  // decoder.rs:575-663: `it` starts at 1, exit when it >= max_iter
+// max(1, max_iter) flooding iterations over `tiles` tiles (decoder.rs:575-663: `it` starts at 1, exit when it >= max_iter).
+static int run_iterations(scaldpc_qary *h, const QaryDev &p, int tiles, unsigned flags, cudaStream_t st)
+{
+    const int iters = std::max(1, h->max_iter);
+    int rc;
     for (int it = 1; it <= iters; ++it) {
         if ((rc = launch_cn(h, p, tiles, it, iters, flags, st))) return rc;
         if ((rc = launch_vn(h, p, tiles, it == iters, flags, st))) return rc;
     }
+    return 0;
+}
+
+// Tile-layout results of `T` trials -> the caller's row-major arrays (slot t -> row map[t] when `map` is given).
+static int emit_outputs(scaldpc_qary *h, int T, const int *map, int8_t *dhard, float *dpost, float *dpost_sum,
+                        cudaStream_t st)
+{
+    const int tiles = (T + 31) / 32;
     dim3 block(32, kTrRows);
-    k_untile<int8_t><<<dim3((h->N + 31) / 32, tiles), block, 0, st>>>(h->d_hard_t, dhard, T, h->N);
+    k_untile<int8_t><<<dim3((h->N + 31) / 32, tiles), block, 0, st>>>(h->d_hard_t, dhard, T, h->N, map);
     ++h->launches;
     if (dpost) {
-        k_untile<float><<<dim3((h->SL + 31) / 32, tiles), block, 0, st>>>(h->d_post, dpost, T, h->SL);
+        k_untile<float><<<dim3((h->SL + 31) / 32, tiles), block, 0, st>>>(h->d_post, dpost, T, h->SL, map);
         ++h->launches;
     }
-    if (dpost_sum && special) {
-        k_untile<float><<<dim3((h->SLS + 31) / 32, tiles), block, 0, st>>>(h->d_post_sum, dpost_sum, T, h->SLS);
+    if (dpost_sum && h->BSUM > 0) {
+        k_untile<float><<<dim3((h->SLS + 31) / 32, tiles), block, 0, st>>>(h->d_post_sum, dpost_sum, T, h->SLS, map);
         ++h->launches;
     }
     SCALDPC_CUDA(cudaGetLastError());
     return 0;
+}
+
+// The device pipeline of one batch: priors (device, row-major) -> hard decisions (device, row-major), all on `st`.
+//
+// Default mode = the fast forward/backward check node, VERIFIED: the last iteration flags every trial
+// whose decisions could depend on the rounding order (a posterior with two near-equal smallest entries, or decisions that
+// violate a parity check -- i.e. every trial that did not converge), the flagged trials are decoded AGAIN from their priors
+// with the exact-order check node (the reference's arithmetic bit for bit, decoder_special.rs:539-553) and their outputs
+// replace the fast ones.  That needs the flagged count on the host: ONE stream synchronisation per batch, which also
+// returns the most severe per-trial status (*worst, may be null).  SCALDPC_NO_VERIFY / SCALDPC_CN_EXACT skip all of it.
+static int decode_on_device(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *dhard, float *dpost, float *dpost_sum,
+                            unsigned flags, cudaStream_t st, int *worst)
+{
+    const bool want_post = dpost != nullptr || dpost_sum != nullptr;
+    const bool verify = !(flags & (SCALDPC_CN_EXACT | SCALDPC_NO_VERIFY));
+    const int tiles = (T + 31) / 32;
+    int rc;
+    if (worst) *worst = 0;
+    h->last_trials += T;
+    SCALDPC_CUDA(cudaMemsetAsync(h->d_status, 0, (size_t)tiles * 32 * sizeof(int), st));
+    if ((rc = stage_priors(h, T, src, flags, h->d_status, nullptr, st))) return rc;
+
+    QaryDev p = dev_view(h, want_post);
+    if (verify) {
+        SCALDPC_CUDA(cudaMemsetAsync(h->d_risk, 0, (size_t)tiles * sizeof(uint32_t), st));
+        p.risk = h->d_risk;
+        p.risk_eps = h->risk_eps;
+    }
+    if ((rc = run_iterations(h, p, tiles, flags, st))) return rc;
+    if (verify) {
+        k_qary_syndrome<<<dim3((h->R + 7) / 8, tiles), 256, 0, st>>>(p);
+        ++h->launches;
+    }
+    if ((rc = emit_outputs(h, T, nullptr, dhard, dpost, dpost_sum, st))) return rc;
+    if (!verify) return 0;
+
+    k_risk_scan<<<1, 1024, 0, st>>>(h->d_risk, tiles, T, h->d_status, h->d_risk_list, h->d_scan_out);
+    ++h->launches;
+    SCALDPC_CUDA(cudaGetLastError());
+    SCALDPC_CUDA(cudaMemcpyAsync(h->h_scan_out, h->d_scan_out, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    SCALDPC_CUDA(cudaStreamSynchronize(st));
+    const int nf = h->h_scan_out[0];
+    if (worst) *worst = h->h_scan_out[1];
+    if (nf <= 0) return 0;
+    // ---- exact-order re-decode of the flagged trials, compacted into the leading tiles of the same workspace
+    h->last_redecoded += nf;
+    const int ftiles = (nf + 31) / 32;
+    if ((rc = stage_priors(h, nf, src, flags, nullptr, h->d_risk_list, st))) return rc;
+    QaryDev p2 = dev_view(h, want_post);
+    p2.status = h->d_status + (size_t)h->cap_tiles * 32;  // scratch: the fast pass has already recorded every status
+    if ((rc = run_iterations(h, p2, ftiles, (flags | SCALDPC_CN_EXACT) & ~SCALDPC_CN_GENERIC, st))) return rc;
+    return emit_outputs(h, nf, h->d_risk_list, dhard, dpost, dpost_sum, st);
 }
 
 // Shared body of scaldpc_qary_decode / scaldpc_qary_decode_observed.  `src` holds the caller's pointers (host or
@@ -693,9 +831,10 @@ static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *har
     const bool special = h->BSUM > 0;
     const bool want_post = post != nullptr || post_sum != nullptr;
     const bool dev_ptrs = flags & SCALDPC_DEVICE_PTRS;
-    int rc;
+    int rc, worst = 0;
+    h->last_trials = h->last_redecoded = 0;
 
-    if (dev_ptrs) {  // asynchronous on `st`; at most `max_resident` trials' messages live in the workspace at a time
+    if (dev_ptrs) {  // asynchronous on `st` (one synchronisation per pass unless SCALDPC_NO_VERIFY); at most `max_resident` trials' messages live in the workspace at a time
         const int cap = std::max(32, h->max_resident / 32 * 32);
         if ((rc = ensure_workspace(h, (std::min(T, cap) + 31) / 32, want_post))) return rc;
         for (int t0 = 0; t0 < T; t0 += cap) {
@@ -708,13 +847,15 @@ static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *har
                 part.in = src.in + (size_t)t0 * h->SL;
                 part.in_sum = src.in_sum ? src.in_sum + (size_t)t0 * h->SLS : nullptr;
             }
+            int w = 0;
             if ((rc = decode_on_device(h, tc, part, hard + (size_t)t0 * h->N, post ? post + (size_t)t0 * h->SL : nullptr,
-                                       post_sum ? post_sum + (size_t)t0 * h->SLS : nullptr, flags, st)))
+                                       post_sum ? post_sum + (size_t)t0 * h->SLS : nullptr, flags, st, &w)))
                 return rc;
+            worst = std::min(worst, w);
             if (status)
                 SCALDPC_CUDA(cudaMemcpyAsync(status + t0, h->d_status, (size_t)tc * sizeof(int), cudaMemcpyDeviceToDevice, st));
         }
-        return 0;
+        return status_error(worst);
     }
 
     // ---- host buffers: chunked pipeline.  Chunk c is copied in on s_in, decoded on `st`, copied out on s_out; the
@@ -775,7 +916,7 @@ static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *har
         dsrc.obs = h->d_obs[b];
         dsrc.obs_sum = h->d_obs_sum[b];
         if ((rc = decode_on_device(h, tc, dsrc, h->d_ohard[b], post ? h->d_opost[b] : nullptr,
-                                   post_sum ? h->d_opost_sum[b] : nullptr, flags, st)))
+                                   post_sum ? h->d_opost_sum[b] : nullptr, flags, st, nullptr)))
             return rc;
         SCALDPC_CUDA(cudaMemcpyAsync(h->d_status_all + t0, h->d_status, (size_t)tc * sizeof(int), cudaMemcpyDeviceToDevice, st));
         SCALDPC_CUDA(cudaEventRecord(h->ev_comp[b], st));
@@ -786,14 +927,9 @@ static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *har
     SCALDPC_CUDA(cudaMemcpyAsync(hs.data(), h->d_status_all, (size_t)T * sizeof(int), cudaMemcpyDeviceToHost, st));
     SCALDPC_CUDA(cudaStreamSynchronize(st));
     SCALDPC_CUDA(cudaStreamSynchronize(h->s_out));
-    int worst = 0;
     for (int t = 0; t < T; ++t) worst = std::min(worst, hs[t]);
     if (status) memcpy(status, hs.data(), (size_t)T * sizeof(int));
-    if (worst == SCALDPC_ERR_PROB_SUM) return fail(worst, "a prior row does not sum to 1 +- 0.001 (decoder.rs:683-684)");
-    if (worst == SCALDPC_ERR_NO_MAX) return fail(worst, "No maximum probability found (decoder.rs:680)");
-    if (worst == SCALDPC_ERR_NO_CONFIG) return fail(worst, "a check has no valid configuration (decoder.rs:618)");
-    if (worst == SCALDPC_ERR_ARG) return fail(worst, "an observation index is outside its prior table");
-    return 0;
+    return status_error(worst);
 }
 
 int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in_sum, int8_t *hard, float *post,
@@ -884,6 +1020,7 @@ int scaldpc_qary_simulate(scaldpc_qary *h, int T, uint64_t seed, uint64_t first_
     if (T == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     std::lock_guard<std::mutex> lk(h->mu);
+    h->last_trials = h->last_redecoded = 0;
     SCALDPC_CUDA(cudaSetDevice(h->device));
     int rc;
     if ((rc = upload_tables(h, table, n_rows, table_sum, n_rows_sum, flags, st))) return rc;
@@ -920,7 +1057,7 @@ int scaldpc_qary_simulate(scaldpc_qary *h, int T, uint64_t seed, uint64_t first_
                                         (int *)(h->d_sim_cnt + 5), tc);
         h->launches += 2;
         SCALDPC_CUDA(cudaGetLastError());
-        if ((rc = decode_on_device(h, tc, src, h->d_sim_hard, nullptr, nullptr, flags, st))) return rc;
+        if ((rc = decode_on_device(h, tc, src, h->d_sim_hard, nullptr, nullptr, flags, st, nullptr))) return rc;
         k_sim_count<<<grid, 256, 0, st>>>(h->d_sim_hard, h->d_sim_secret, h->d_sim_ssum, h->d_sim_cnt, tc, h->N, h->bvars);
         ++h->launches;
         SCALDPC_CUDA(cudaGetLastError());

@@ -284,6 +284,7 @@ __global__ void __launch_bounds__(kCnWarps * 32, 1) k_cn_fast(const QaryDev p, c
             float min_val = INF;
             int arg = negs ? QS - 1 : 0;
             float *post = p.post_sum ? p.post_sum + (size_t)tile * p.SLS * 32 + lane : nullptr;
+            Min2 mm;
 #pragma unroll
             for (int i = 0; i < QS; ++i) {
                 const int iv = negs ? QS - 1 - i : i;
@@ -292,10 +293,12 @@ __global__ void __launch_bounds__(kCnWarps * 32, 1) k_cn_fast(const QaryDev p, c
                     min_val = tot;
                     arg = i;
                 }
+                mm.add(tot);
                 if (post) post[(size_t)(vs * QS + iv) * 32] = tot;
             }
             const int argv = negs ? QS - 1 - arg : arg;
             p.hard_t[((size_t)tile * p.N + p.bvars + vs) * 32 + lane] = (int8_t)(argv - BS);
+            if (p.risk) flag_risk(p, tile, lane, mm.risky(p.risk_eps));
 #ifndef SCALDPC_HOST_MODEL
             __syncwarp();
             if (item + nw < n_items && lane == 0) {

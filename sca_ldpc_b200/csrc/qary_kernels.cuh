@@ -48,7 +48,37 @@ struct QaryDev {
     float *post_sum;        // may be null
     int8_t *hard_t;
     int *status;            // per trial, tiles*32 entries
+    // at-risk detection of the fast (forward/backward) path, last iteration only; null = off.  Bit l of risk[tile] is set
+    // when trial l's decisions could differ from the reference's rounding order: a posterior whose two smallest entries are
+    // closer than risk_eps, or decisions that violate a parity check.
+    uint32_t *risk = nullptr;
+    float risk_eps = 0.0f;
 };
+
+// The two smallest entries of a vector (NaN = excluded = +inf).
+struct Min2 {
+    float m1, m2;
+    __device__ __forceinline__ Min2() : m1(SC_INF), m2(SC_INF) {}
+    __device__ __forceinline__ void add(float x)
+    {
+        const float xs = fminf(x, SC_INF);
+        m2 = fminf(m2, fmaxf(m1, xs));
+        m1 = fminf(m1, xs);
+    }
+    // true unless the runner-up is clearly (> eps) above the minimum; all-excluded vectors (inf - inf = NaN) are risky
+    __device__ __forceinline__ bool risky(float eps) const { return !(m2 - m1 > eps); }
+};
+
+// Every lane of the warp calls this with its own verdict; one atomic per warp.
+__device__ __forceinline__ void flag_risk(const QaryDev &p, int tile, int lane, bool risky)
+{
+#ifdef SCALDPC_HOST_MODEL
+    if (risky) p.risk[tile] |= 1u << lane;
+#else
+    const unsigned m = __ballot_sync(0xffffffffu, risky);
+    if (m != 0u && lane == 0) atomicOr(p.risk + tile, m);
+#endif
+}
 
 __device__ __forceinline__ float min3f(float a, float b, float c)
 {
@@ -80,6 +110,7 @@ struct MinAcc {
 };
 
 #include "qary_cn_fast.cuh"
+#include "qary_cn_exact.cuh"
 #include "sc_logf.cuh"
 
 // -----------------------------------------------------------------------------------------------------------
@@ -137,6 +168,12 @@ __global__ void __launch_bounds__(kVnWarps * 32) k_vn(const QaryDev p, const int
                 arg = i;
             }
         p.hard_t[((size_t)tile * p.N + var) * 32 + lane] = (int8_t)(arg - (Q - 1) / 2);
+        if (p.risk) {
+            Min2 mm;
+#pragma unroll
+            for (int i = 0; i < Q; ++i) mm.add(tot[i]);
+            flag_risk(p, tile, lane, mm.risky(p.risk_eps));
+        }
         if (p.post) {
             float *post = p.post + (size_t)tile * p.SL * 32 + lane;
 #pragma unroll
@@ -210,6 +247,12 @@ __global__ void __launch_bounds__(kVnWarps * 32) k_vn_reg(const QaryDev p, const
                 arg = i;
             }
         p.hard_t[((size_t)tile * p.N + var) * 32 + lane] = (int8_t)(arg - (Q - 1) / 2);
+        if (p.risk) {
+            Min2 mm;
+#pragma unroll
+            for (int i = 0; i < Q; ++i) mm.add(tot[i]);
+            flag_risk(p, tile, lane, mm.risky(p.risk_eps));
+        }
         if (p.post) {
             float *post = p.post + (size_t)tile * p.SL * 32 + lane;
 #pragma unroll
@@ -408,6 +451,7 @@ __global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGene
             float *post = p.post_sum ? p.post_sum + (size_t)tile * p.SLS * 32 + lane : nullptr;
             float min_val = INF;
             int arg = 0;
+            Min2 mm;
             for (int iv = 0; iv < p.QS; ++iv) {  // variable frame, ascending
                 const int i = neg ? p.QS - 1 - iv : iv;
                 const float t = llrs[(size_t)(vs * p.QS + iv) * 32] + msg[(size_t)(off + i) * 32];
@@ -415,9 +459,11 @@ __global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGene
                     min_val = t;
                     arg = iv;
                 }
+                mm.add(t);
                 if (post) post[(size_t)(vs * p.QS + iv) * 32] = t;
             }
             p.hard_t[((size_t)tile * p.N + p.bvars + vs) * 32 + lane] = (int8_t)(arg - p.BSUM);
+            if (p.risk) flag_risk(p, tile, lane, mm.risky(p.risk_eps));
         }
     }
 #undef A_
@@ -662,9 +708,10 @@ __device__ __forceinline__ int into_llr_row(float *v, int q, const ScLogfTab *lt
 }
 
 // in: [T][rows*q] probabilities or LLRs; out: [tile][rows*q][32].  One CTA = one tile x `rpb` rows.
+// `map` (may be null): slot t of the batch is row map[t] of `in` (re-decode of a sub-list of trials).
 __global__ void __launch_bounds__(32 * kTrRows) k_load_priors(const float *__restrict__ in, float *__restrict__ out,
                                                               int T, int rows, int q, int rpb, int is_llr,
-                                                              int *__restrict__ status)
+                                                              int *__restrict__ status, const int *__restrict__ map)
 {
     SCALDPC_DYN_SMEM(float, sm);
     const int tile = blockIdx.y;
@@ -679,15 +726,16 @@ __global__ void __launch_bounds__(32 * kTrRows) k_load_priors(const float *__res
     // coalesced load: thread tx walks the chunk, ty walks trials
     for (int t = ty; t < 32; t += kTrRows) {
         const int trial = tile * 32 + t;
+        const size_t row = trial < T ? (size_t)(map ? map[trial] : trial) : 0;
         for (int i = tx; i < n; i += 32)
-            sm[t * pitch + i] = trial < T ? in[(size_t)trial * per_trial + (size_t)r0 * q + i] : (is_llr ? 0.0f : 1.0f / q);
+            sm[t * pitch + i] = trial < T ? in[row * per_trial + (size_t)r0 * q + i] : (is_llr ? 0.0f : 1.0f / q);
     }
     __syncthreads();
     if (!is_llr) {
         // thread (tx = trial, ty = row): sum / max / ln(max / p)
         for (int r = ty; r < nr; r += kTrRows) {
             const int err = into_llr_row(sm + tx * pitch + r * q, q, ltab);
-            if (err && tile * 32 + tx < T) atomicMin(status + tile * 32 + tx, err);
+            if (err && status && tile * 32 + tx < T) atomicMin(status + tile * 32 + tx, err);
         }
         __syncthreads();
     }
@@ -720,22 +768,24 @@ constexpr int kObsRows = 64;  // variables per CTA of k_load_observed
 // status, SCALDPC_ERR_ARG for an index >= n_rows.
 __global__ void __launch_bounds__(256) k_load_observed(const uint16_t *__restrict__ obs, const float *__restrict__ tab,
                                                        const int *__restrict__ row_status, float *__restrict__ out, int T,
-                                                       int rows, int q, int n_rows, int *__restrict__ status)
+                                                       int rows, int q, int n_rows, int *__restrict__ status,
+                                                       const int *__restrict__ map)
 {
     __shared__ uint16_t so[32][kObsRows + 2];  // pitch 33 words: conflict-free column reads
     const int tile = blockIdx.y, r0 = blockIdx.x * kObsRows;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     for (int t = ty; t < 32; t += 8) {
         const int trial = tile * 32 + t;
+        const size_t row = trial < T ? (size_t)(map ? map[trial] : trial) : 0;
         for (int c = tx; c < kObsRows; c += 32)
-            so[t][c] = (trial < T && r0 + c < rows) ? obs[(size_t)trial * rows + r0 + c] : (uint16_t)0xffff;
+            so[t][c] = (trial < T && r0 + c < rows) ? obs[row * rows + r0 + c] : (uint16_t)0xffff;
     }
     __syncthreads();
     const bool real = tile * 32 + tx < T;
     for (int c = ty; c < kObsRows && r0 + c < rows; c += 8) {
         const int idx = so[tx][c];
         const bool ok = real && idx < n_rows;
-        if (real) {
+        if (real && status) {
             const int err = idx < n_rows ? row_status[idx] : SCALDPC_ERR_ARG;
             if (err) atomicMin(status + tile * 32 + tx, err);
         }
@@ -745,9 +795,10 @@ __global__ void __launch_bounds__(256) k_load_observed(const uint16_t *__restric
     }
 }
 
-// tile layout -> row-major.  src [tile][n][32] -> dst [T][n]
+// tile layout -> row-major.  src [tile][n][32] -> dst [T][n]; with `map`, slot t goes to row map[t] of dst.
 template <typename T_>
-__global__ void __launch_bounds__(32 * kTrRows) k_untile(const T_ *__restrict__ src, T_ *__restrict__ dst, int T, int n)
+__global__ void __launch_bounds__(32 * kTrRows) k_untile(const T_ *__restrict__ src, T_ *__restrict__ dst, int T, int n,
+                                                         const int *__restrict__ map)
 {
     __shared__ T_ sm[32][33];
     const int tile = blockIdx.y;
@@ -758,8 +809,87 @@ __global__ void __launch_bounds__(32 * kTrRows) k_untile(const T_ *__restrict__ 
     __syncthreads();
     for (int t = ty; t < 32; t += kTrRows) {
         const int trial = tile * 32 + t;
-        if (trial < T && c0 + tx < n) dst[(size_t)trial * n + c0 + tx] = sm[tx][t];
+        if (trial < T && c0 + tx < n) dst[(size_t)(map ? map[trial] : trial) * n + c0 + tx] = sm[tx][t];
     }
 }
+
+// ---- at-risk detection, part 2: the row test of the final hard decisions,
+// sum_j h_ij * s_j (+ s_sum,i) == 0 for every check (SURVEY.md 7 "hard parts"; kyber.py:85-92 / :374-375 make the
+// decoded sum-variable equal -ssum_i).  One warp = (tile, check), lane = trial; a violated row flags the trial.
+__global__ void __launch_bounds__(256) k_qary_syndrome(const QaryDev p)
+{
+    const int lane = threadIdx.x & 31;
+    const int check = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int tile = blockIdx.y;
+    if (check >= p.R) return;
+    const int e0 = __ldg(p.row_ptr + check), e1 = __ldg(p.row_ptr + check + 1);
+    const int8_t *hard = p.hard_t + (size_t)tile * p.N * 32 + lane;
+    int s = 0;
+    for (int e = e0; e < e1; ++e) {
+        const int v = hard[(size_t)__ldg(p.col + e) * 32];
+        s += __ldg(p.sign + e) < 0 ? -v : v;
+    }
+    flag_risk(p, tile, lane, s != 0);
+}
+
+#ifndef SCALDPC_HOST_MODEL
+// Flag words -> ascending list of the flagged trials (< T) + their count, and the most severe per-trial status.
+// One CTA of 1024 threads.  out[0] = count, out[1] = min over status[0 .. T).
+__global__ void __launch_bounds__(1024) k_risk_scan(const uint32_t *__restrict__ risk, int tiles, int T,
+                                                    const int *__restrict__ status, int *__restrict__ list,
+                                                    int *__restrict__ out)
+{
+    __shared__ int wsum[32];
+    __shared__ int s_base;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_base = 0;
+    __syncthreads();
+    for (int t0 = 0; t0 < tiles; t0 += 1024) {
+        const int tile = t0 + tid;
+        uint32_t word = (risk && tile < tiles) ? risk[tile] : 0u;
+        const int rem = T - tile * 32;
+        if (rem < 32) word &= rem <= 0 ? 0u : ((1u << rem) - 1u);
+        const int c = __popc(word);
+        int incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) wsum[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            int w = wsum[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += v;
+            }
+            wsum[lane] = w;  // inclusive over warps
+        }
+        __syncthreads();
+        int pos = s_base + (warp ? wsum[warp - 1] : 0) + incl - c;
+        while (word) {
+            const int b = __ffs(word) - 1;
+            list[pos++] = tile * 32 + b;
+            word &= word - 1u;
+        }
+        __syncthreads();
+        if (tid == 0) s_base += wsum[31];
+        __syncthreads();
+    }
+    int w = 0;
+    for (int i = tid; i < T; i += 1024) w = min(w, status[i]);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) w = min(w, __shfl_xor_sync(0xffffffffu, w, o));
+    if (lane == 0) wsum[warp] = w;
+    __syncthreads();
+    if (tid == 0) {
+        for (int i = 1; i < 32; ++i) w = min(w, wsum[i]);
+        out[0] = s_base;
+        out[1] = w;
+    }
+}
+#endif
 
 }  // namespace scaldpc

@@ -96,10 +96,11 @@ class bp_decoder:
 
     def decode(self, vec):
         vec = np.asarray(vec).astype(np.uint8) & 1
-        if vec.shape[0] == self.n:       # received vector: decode its syndrome, return the corrected vector
-            synd, received = self.syndrome_of(vec), vec
-        elif vec.shape[0] == self.m:     # syndrome: return the error estimate
+        # upstream ldpc 0.1.x tests the SYNDROME length first, so for a square H (m == n) the vector is a syndrome
+        if vec.shape[0] == self.m:       # syndrome: return the error estimate
             synd, received = vec, None
+        elif vec.shape[0] == self.n:     # received vector: decode its syndrome, return the corrected vector
+            synd, received = self.syndrome_of(vec), vec
         else:
             raise ValueError("input vector has the wrong length")
         out = self.decode_batch(synd[None], want_llr=True)
@@ -175,7 +176,10 @@ class bp_decoder:
         (hqc.py:709-758; scaldpc_bp_decode_scored): 24 bytes per trial come back instead of n.  H must be [Hin | I_m].
         syndromes (T, m) uint8, truth (T, weight) int32 = support of the true message of every trial (y_sparse).
         n_checks: optional (T,) int32, nested graphs as decode_batch(n_checks=...): trial t uses its first n_checks[t] rows.
-        Returns dict(stats (T, 6) int32 in STAT_NAMES order, iters, converged, decoding or None)."""
+        Returns dict(stats (T, 6) int32 in STAT_NAMES order, iters, converged, decoding or None).
+        `decoding` (want_decoding=True) is the ERROR ESTIMATE decode_batch returns; hqc.decode itself works on the
+        corrected word msg ^ error (bpd.decode of a length-n vector, hqc.py:703-708) and the statistics are scored on
+        that word, as the reference does (found_bad_unsatisfied = check bit 1 AND a decoded measurement error)."""
         flags = 0 if early_stop else _lib.BP_NO_EARLY_STOP
         synd = np.ascontiguousarray(syndromes, dtype=np.uint8)
         T = synd.shape[0]

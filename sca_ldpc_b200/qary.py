@@ -146,7 +146,7 @@ class QaryDecoder:
     # batched fast path: T independent decodes resident on the device
     # ------------------------------------------------------------------------------------------------------
     def min_sum_batch(self, priors, priors_sum=None, *, llr=False, want_posterior=True, exact=False,
-                      generic=False, want_status=False, out=None):
+                      generic=False, want_status=False, out=None, verify=True):
         """Decode T trials.
 
         priors      (T, bvars, Q)  float32 probabilities (or LLRs with llr=True); numpy array or torch CUDA tensor
@@ -157,8 +157,12 @@ class QaryDecoder:
         (asynchronous on the current stream).
         out: optional preallocated C-contiguous int8 (T, N) numpy array that receives the hard decisions (host
         path only) -- e.g. a view of pinned memory, so the device-to-host copy is a true asynchronous DMA.
+        exact=True: every trial with the exact-order check node (the reference's rounding, bit for bit).
+        verify (default True): the fast check node's results are verified -- trials whose decisions could depend on
+        the rounding order are re-decoded with the exact-order check node (SCALDPC_NO_VERIFY in scaldpc.h), so hard
+        decisions equal the reference's per trial; `last_run` tells how many were re-decoded.
         """
-        flags = (_lib.IN_LLR if llr else 0) | (_lib.CN_EXACT if exact else 0) | (_lib.CN_GENERIC if generic else 0)
+        flags = self._flags(llr, exact, generic, verify)
         on_dev = _is_torch(priors) and priors.is_cuda
         if self.special and priors_sum is None:
             raise TypeError("the special decoder needs priors_sum")
@@ -189,8 +193,13 @@ class QaryDecoder:
                                                 None)
         return self._finish(rc, hard, post, posts, status, want_status)
 
+    @staticmethod
+    def _flags(llr=False, exact=False, generic=False, verify=True):
+        return ((_lib.IN_LLR if llr else 0) | (_lib.CN_EXACT if exact else 0) | (_lib.CN_GENERIC if generic else 0)
+                | (0 if verify else _lib.NO_VERIFY))
+
     def min_sum_observed(self, table, obs, table_sum=None, obs_sum=None, *, llr=False, want_posterior=False,
-                         exact=False, generic=False, want_status=False, out=None):
+                         exact=False, generic=False, want_status=False, out=None, verify=True):
         """Decode T trials whose priors are rows of small tables (scaldpc_qary_decode_observed): the posterior of a
         variable given the oracle's bit pattern y is `table[y]` (max_likelihood.py:87-105, kyber.py:362-376), so only
         the row indices travel.  Bit-identical to min_sum_batch(table[obs], table_sum[obs_sum]).
@@ -199,7 +208,7 @@ class QaryDecoder:
         table_sum  (n_rows_sum, QS) float32 obs_sum  (T, R) uint16            (special decoder)
         numpy in -> numpy out; torch CUDA tensors in (obs int16/uint16 storage) -> torch CUDA out.
         """
-        flags = (_lib.IN_LLR if llr else 0) | (_lib.CN_EXACT if exact else 0) | (_lib.CN_GENERIC if generic else 0)
+        flags = self._flags(llr, exact, generic, verify)
         if self.special and (table_sum is None or obs_sum is None):
             raise TypeError("the special decoder needs table_sum and obs_sum")
         on_dev = _is_torch(obs) and obs.is_cuda
@@ -265,7 +274,7 @@ class QaryDecoder:
         return self._finish(rc, hard, post, posts, status, want_status)
 
     def simulate(self, T, seed, table, table_sum, code, code_sum, nbits, nbits_sum, accuracy, eta, *, first_trial=0,
-                 want_trials=False, exact=False, generic=False):
+                 want_trials=False, exact=False, generic=False, verify=True):
         """T Kyber attack-simulation trials synthesised, decoded and scored on the device (scaldpc_qary_simulate,
         SURVEY.md 8f.1): secret ~ centred binomial(eta) (kyber.py:35-47), ssum = H' s (kyber.py:85-92), every bit of
         the code word of a value observed correctly with probability `accuracy` (max_likelihood.py:9-18), priors =
@@ -283,7 +292,7 @@ class QaryDecoder:
         if code.shape != (self.Q,) or code_sum.shape != (self.QS,):
             raise ValueError(f"code must have {self.Q} entries and code_sum {self.QS}")
         T = int(T)
-        flags = (_lib.CN_EXACT if exact else 0) | (_lib.CN_GENERIC if generic else 0)
+        flags = self._flags(False, exact, generic, verify)
         counters = np.zeros(5, np.int64)
         tr = {}
         if want_trials:
@@ -348,6 +357,16 @@ class QaryDecoder:
     @property
     def launch_count(self) -> int:
         return int(_lib.lib().scaldpc_qary_launch_count(self._h))
+
+    @property
+    def last_run(self) -> dict:
+        """Trials of the last batch call and how many of them the verification re-decoded (scaldpc_qary_last_run)."""
+        t, r = C.c_longlong(), C.c_longlong()
+        _lib.check(_lib.lib().scaldpc_qary_last_run(self._h, C.byref(t), C.byref(r)))
+        return {"trials": t.value, "redecoded": r.value}
+
+    def set_risk_margin(self, eps: float):
+        _lib.check(_lib.lib().scaldpc_qary_set_risk_margin(self._h, float(eps)))
 
     def time_kernel(self, which: int, T: int, reps: int = 20, exact=False, generic=False, stream=None) -> float:
         """Average duration (ms) of one check-node (which=0) or variable-node (which=1) launch over T trials,

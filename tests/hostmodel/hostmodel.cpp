@@ -98,6 +98,16 @@ cn_fast_fn pick_cn_fast(int sw, int b, int it = 2, int iters = 4)
     return nullptr;
 }
 
+typedef void (*cn_exact_fn)(const QaryDev, const int, const int, const int);
+cn_exact_fn pick_cn_exact(int sw, int b)
+{
+#define CASE(SW_, B_) \
+    if (sw == SW_ && b == B_) return k_cn_exact<SW_, B_>;
+    CASE(6, 2) CASE(6, 3) CASE(4, 2) CASE(8, 2) CASE(3, 2)
+#undef CASE
+    return nullptr;
+}
+
 vn_fn pick_vn(int q)
 {
     switch (q) {
@@ -123,7 +133,12 @@ vn_fn pick_vn_reg(int q, int d)
 
 }  // namespace
 
+static int g_last_redecoded = 0;
+
 extern "C" {
+
+// Trials the verification of the last hostmodel_qary_decode call re-decoded with the exact-order check node.
+int hostmodel_last_redecoded(void) { return g_last_redecoded; }
 
 // sc_logf (sca_ldpc_b200/csrc/sc_logf.cuh), the device restatement of glibc's logf, evaluated on the host.
 void hostmodel_logf(const float *x, float *y, long n)
@@ -170,6 +185,13 @@ int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
     p.post = tpost.data(); p.post_sum = tposts.data(); p.hard_t = hard_t.data(); p.status = st.data();
 
     const bool exact = flags & SCALDPC_CN_EXACT, force_generic = flags & SCALDPC_CN_GENERIC;
+    const bool verify = !(flags & (SCALDPC_CN_EXACT | SCALDPC_NO_VERIFY));  // as decode_on_device (qary.cu)
+    std::vector<uint32_t> risk(tiles, 0u);
+    if (verify) {
+        p.risk = risk.data();
+        p.risk_eps = 1e-2f;
+    }
+    if (!(flags & SCALDPC_CN_EXACT)) g_last_redecoded = 0;
     cn_fast_fn fast = (!exact && !force_generic && g.regular_sw) ? pick_cn_fast(g.regular_sw, b) : nullptr;
     vn_fn vn = pick_vn(g.Q);
     if (!vn) return SCALDPC_ERR_UNSUPPORTED;
@@ -189,6 +211,11 @@ int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
         if (fast) {
             // persistent kernel: a deliberately small grid, so every warp strides over several items
             run_grid(3, 1, kCnWarps * 32, pick_cn_fast(g.regular_sw, b, it, iters), p, tiles * g.R);
+        } else if (exact && !force_generic && g.regular_sw && pick_cn_exact(g.regular_sw, b)) {
+            // exact-order DP in registers (qary_cn_exact.cuh), as launch_cn chooses it (qary.cu)
+            const int n_items = tiles * g.R;
+            run_grid((n_items + kCnExactWarps - 1) / kCnExactWarps, 1, kCnExactWarps * 32, pick_cn_exact(g.regular_sw, b), p,
+                     n_items, first, last);
         } else if (g.BSUM == 0 && !exact && !force_generic && (g.Q == 3 || g.Q == 15)) {
             // generic decoder, one alphabet: k_cn_uniform<Q>, as launch_cn chooses it (qary.cu)
             if (first) run_grid((g.E + 7) / 8, tiles, 256, k_init_v2c, p, g.E);
@@ -206,6 +233,7 @@ int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
         }
         run_grid((g.bvars + kVnWarps - 1) / kVnWarps, tiles, kVnWarps * 32, vn, p, last);
     }
+    if (verify) run_grid((g.R + 7) / 8, tiles, 256, k_qary_syndrome, p);
     // untile
     int worst = 0;
     for (int t = 0; t < T; ++t) {
@@ -219,6 +247,31 @@ int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
         worst = std::min(worst, st[t]);
     }
     scaldpc_host_model_smem = nullptr;
+    if (verify) {  // exact-order re-decode of the flagged trials (k_risk_scan + the second pass of decode_on_device)
+        std::vector<int> list;
+        for (int t = 0; t < T; ++t)
+            if ((risk[t / 32] >> (t % 32)) & 1u) list.push_back(t);
+        const int nf = (int)list.size();
+        g_last_redecoded = nf;
+        if (nf) {
+            std::vector<float> l2((size_t)nf * g.SL), ls2(std::max<size_t>(1, (size_t)nf * g.SLS));
+            std::vector<float> p2((size_t)nf * g.SL), ps2(std::max<size_t>(1, (size_t)nf * g.SLS));
+            std::vector<int8_t> h2((size_t)nf * g.N);
+            for (int i = 0; i < nf; ++i) {
+                memcpy(&l2[(size_t)i * g.SL], llr_in + (size_t)list[i] * g.SL, sizeof(float) * g.SL);
+                if (g.SLS) memcpy(&ls2[(size_t)i * g.SLS], llr_sum_in + (size_t)list[i] * g.SLS, sizeof(float) * g.SLS);
+            }
+            hostmodel_qary_decode(H, R, N, b, bsum, dv, dc, max_iter, nf, l2.data(), g.SLS ? ls2.data() : nullptr, h2.data(),
+                                  p2.data(), g.SLS ? ps2.data() : nullptr, nullptr,
+                                  (flags | SCALDPC_CN_EXACT) & ~SCALDPC_CN_GENERIC, nullptr, nullptr, 0);
+            for (int i = 0; i < nf; ++i) {
+                memcpy(hard + (size_t)list[i] * g.N, &h2[(size_t)i * g.N], g.N);
+                if (post) memcpy(post + (size_t)list[i] * g.SL, &p2[(size_t)i * g.SL], sizeof(float) * g.SL);
+                if (post_sum && g.SLS)
+                    memcpy(post_sum + (size_t)list[i] * g.SLS, &ps2[(size_t)i * g.SLS], sizeof(float) * g.SLS);
+            }
+        }
+    }
     return worst;
 }
 

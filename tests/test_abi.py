@@ -108,6 +108,12 @@ def test_simulate_rs_class_lookup():
     assert simulate_rs.DecoderN1280R512SW6.__name__ == "DecoderN1280R512SW6"
     with pytest.raises(AttributeError):
         simulate_rs.NoSuchDecoder
+    # special-decoder names do not carry the alphabets: only the reference's own shapes resolve by the bare name
+    # (lib.rs:54-75, kyber.py:385-392); other shapes spell B out or go through the factory
+    assert simulate_rs.DecoderN1024R256SW3.__name__ == "DecoderN1024R256SW3"
+    with pytest.raises(AttributeError, match="make_special_decoder_class"):
+        simulate_rs.DecoderN768R256SW6
+    assert simulate_rs.DecoderN768R256SW6B3 is simulate_rs.make_special_decoder_class(768, 256, 7, 3, 18, name="DecoderN768R256SW6B3")
     with pytest.raises(TypeError):  # pydecoder.rs:24: PyReadonlyArray2<i8>
         simulate_rs.DecoderN6R3V3C4B7(np.zeros((3, 6), np.int64), 10)
     with pytest.raises(IndexError):  # smaller than the class's const shape (pydecoder.rs:31)

@@ -175,9 +175,13 @@ def test_shared_prior_first_pass_is_bit_identical(monkeypatch):
     assert np.array_equal(a["log_prob_ratios"], c["log_prob_ratios"], equal_nan=True)
 
 
-def reference_stats(N, decoded, checks, y_sparse):
-    """hqc.py:709-749, restated loop for loop: -> the 6 arguments of tracking.add_decoder_stats (:751-759)."""
+def reference_stats(N, error, checks, y_sparse):
+    """hqc.py:709-749, restated loop for loop: -> the 6 arguments of tracking.add_decoder_stats (:751-759).
+    `error` is the decoder's error estimate; hqc.decode scores `decoded = bpd.decode(msg)` with msg = [0]*N ++ checks of
+    length n, i.e. the CORRECTED vector msg ^ error (hqc.py:703-708)."""
     y_sparse = set(int(v) for v in y_sparse)
+    decoded = np.asarray(error).copy()
+    decoded[N:N + len(checks)] ^= np.asarray(checks, dtype=decoded.dtype)
     unsatisfied = good = bad = fbs = fbu = 0
     for i, x in enumerate(decoded[:N]):
         if x:

@@ -94,53 +94,103 @@ def test_device_logf_vs_host():
     assert np.array_equal(h1, h2) and np.array_equal(p1, p2, equal_nan=True)
 
 
+# (variant, sum_weight, check_blocks, oracle accuracy, code bits, sum code bits, trials, iterations)
+PARITY_CASES = [
+    ("kyber512", 6, 1, 0.98, 4, 5, 256, 10),   # THE bench workload (BASELINE.json configs[1], bench.py WORKLOADS)
+    ("kyber512", 6, 1, 0.90, 4, 5, 48, 10),    # the same shape where (almost) nothing converges
+    ("kyber768", 6, 2, 0.95, 3, 4, 64, 10),    # bench.py's kyber768 workload (north_star's target shape)
+    ("kyber768", 6, 2, 0.90, 3, 4, 40, 10),
+    ("kyber1024", 8, 1, 0.98, 5, 6, 40, 6),    # bench.py's kyber1024 workload
+    ("kyber1024", 8, 1, 0.95, 4, 5, 40, 6),    # undecodable at this accuracy
+    ("kyber1024", 4, 1, 0.95, 4, 5, 45, 6),
+    ("kyber1024", 4, 1, 0.90, 4, 5, 45, 3),
+]
+
+
+@pytest.mark.parametrize("variant,sw,cb,acc,nb,nbs,T,it", PARITY_CASES)
+def test_batched_parity_with_oracle(variant, sw, cb, acc, nb, nbs, T, it):
+    """Every BASELINE.json Kyber shape, decodable and undecodable workloads, against the REFERENCE's arithmetic: the
+    oracle's exact-order DP (ALGO_EXACT_DP, asserted bit-identical to the enumeration of decoder_special.rs:531-554 in
+    tests/golden/make_golden.py and tests/test_oracle_golden.py).  north_star's bar: hard decisions identical per trial,
+    posteriors within 1e-4 absolute."""
+    w = KyberWorkload(variant, sum_weight=sw, check_blocks=cb, accuracy=acc, nbits=nb, nbits_sum=nbs, seed=0 if T >= 256 else 1)
+    b = w.generate(T, seed=1 if T >= 256 else 3)
+    d = QaryDecoder(w.H, it, **w.decoder_kwargs)
+    orc = O.QaryOracle(w.H, it, B=w.B, BSUM=w.BSUM, DC=sw + 1)
+    # identical LLR inputs (the oracle's into_llr) -> strict comparison
+    llr = np.stack([O.into_llr(x) for x in b.priors])
+    llrs = np.stack([O.into_llr(x) for x in b.priors_sum])
+    rh, rp, rps, st = orc.decode_batch(llr, llrs, from_probs=False, algo=O.ALGO_EXACT_DP)
+    assert (st == 0).all()
+    # 1. the DEFAULT path: fast check node, verified (at-risk trials re-decoded in the reference's rounding order)
+    hard, post, posts = d.min_sum_batch(llr, llrs, llr=True)
+    run = d.last_run
+    assert run["trials"] == T
+    assert np.array_equal(hard, rh), f"{int((hard != rh).any(1).sum())} trials differ from the reference arithmetic"
+    assert util.same_nonfinite(post, rp) and util.max_abs_diff(post, rp) < TOL
+    assert util.same_nonfinite(posts, rps) and util.max_abs_diff(posts, rps) < TOL
+    synd = rh.astype(np.int32) @ w.H.T.astype(np.int32)
+    assert run["redecoded"] >= int((synd != 0).any(1).sum())  # every trial that did not converge was decoded again
+    if acc >= 0.98:
+        assert run["redecoded"] < T // 2
+    # 2. the exact-order kernel on every trial: bit-identical posteriors
+    eh, ep, eps_ = d.min_sum_batch(llr, llrs, llr=True, exact=True)
+    assert np.array_equal(eh, rh)
+    assert np.array_equal(ep, rp, equal_nan=True) and np.array_equal(eps_, rps, equal_nan=True)
+    # 3. separately: the UNVERIFIED fast kernel is the arithmetic of its CPU model (oracle algo 3) bit for bit
+    fh, fp, fps, st = orc.decode_batch(llr, llrs, from_probs=False, algo=O.ALGO_FAST)
+    uh, up, ups = d.min_sum_batch(llr, llrs, llr=True, verify=False)
+    assert d.last_run["redecoded"] == 0
+    assert np.array_equal(uh, fh)
+    assert np.array_equal(up, fp, equal_nan=True) and np.array_equal(ups, fps, equal_nan=True)
+    assert np.array_equal(w.success(b, hard), w.success(b, rh))
+
+
 @pytest.mark.parametrize("variant,sw,cb", [("kyber512", 6, 1), ("kyber768", 6, 2), ("kyber1024", 8, 1),
                                            ("kyber1024", 4, 1)])
-def test_batched_parity_with_oracle(variant, sw, cb):
-    """Seeded synthetic batches (T not a multiple of 32) for every BASELINE.json Kyber shape: the fast kernels
-    against the oracle's forward/backward model per trial (hard decisions identical, posteriors within 1e-4),
-    torch CUDA tensors in / out, and the end-to-end property decoded == secret where the oracle also succeeds."""
+def test_batched_api_variants(variant, sw, cb):
+    """Seeded synthetic batches (T not a multiple of 32): the runtime-shape kernels, torch CUDA tensors in / out, device-side
+    into_llr, caller-provided pinned result buffer -- all against the default path's results."""
     import torch
 
     w = KyberWorkload(variant, sum_weight=sw, check_blocks=cb, accuracy=0.95, nbits=4, nbits_sum=5, seed=1)
     T = 40
     b = w.generate(T, seed=3)
     d = QaryDecoder(w.H, 6, **w.decoder_kwargs)
-    orc = O.QaryOracle(w.H, 6, B=w.B, BSUM=w.BSUM, DC=sw + 1, algo=O.ALGO_FAST)
-    # identical LLR inputs (the oracle's into_llr) -> strict comparison
     llr = np.stack([O.into_llr(x) for x in b.priors])
     llrs = np.stack([O.into_llr(x) for x in b.priors_sum])
-    rh, rp, rps, st = orc.decode_batch(llr, llrs, from_probs=False)
-    assert (st == 0).all()
     hard, post, posts = d.min_sum_batch(llr, llrs, llr=True)
-    assert np.array_equal(hard, rh)
-    assert util.same_nonfinite(post, rp) and util.max_abs_diff(post, rp) < TOL
-    assert util.same_nonfinite(posts, rps) and util.max_abs_diff(posts, rps) < TOL
-    # runtime-shape kernels (k_cn_generic forward/backward + k_vn, full sum-variable round trip) on the same inputs
+    # runtime-shape kernels (k_cn_generic forward/backward + k_vn, full sum-variable round trip; flagged trials go through
+    # the exact-order kernel as well): same decisions, posteriors within the tolerance
     gh, gp, gps = d.min_sum_batch(llr, llrs, llr=True, generic=True)
-    assert util.same_nonfinite(gp, rp) and util.max_abs_diff(gp, rp) < TOL
-    assert util.same_nonfinite(gps, rps) and util.max_abs_diff(gps, rps) < TOL
-    # two different roundings of the same arithmetic: decisions may differ only at exact ties of the posterior (they
-    # occur in trials that do not converge; kyber1024/sw=8 at this accuracy is such a workload), never on decodable ones
-    tt, vv = np.nonzero(gh[:, : w.bvars] != rh[:, : w.bvars])
-    assert len(tt) <= 4
-    for t, v in zip(tt, vv):
-        assert abs(rp[t, v, gh[t, v] + w.B] - rp[t, v, rh[t, v] + w.B]) < TOL
-    assert np.array_equal(w.success(b, gh), w.success(b, rh))
-    # probabilities in (into_llr on the device), device-resident tensors, asynchronous on the current stream
+    assert np.array_equal(gh, hard)
+    assert util.same_nonfinite(gp, post) and util.max_abs_diff(gp, post) < TOL
+    assert util.same_nonfinite(gps, posts) and util.max_abs_diff(gps, posts) < TOL
+    # the two exact-order kernels (registers / run-time shapes) agree bit for bit
+    d.set_iterations(2)
+    e1 = d.min_sum_batch(llr[:8], llrs[:8], llr=True, exact=True)
+    e2 = d.min_sum_batch(llr[:8], llrs[:8], llr=True, exact=True, generic=True)
+    for a, c in zip(e1, e2):
+        assert np.array_equal(a, c, equal_nan=True)
+    d.set_iterations(6)
+    # probabilities in (into_llr on the device), device-resident tensors; per-trial errors are returned, not dropped
     th, tp, tps = d.min_sum_batch(torch.from_numpy(b.priors).cuda(), torch.from_numpy(b.priors_sum).cuda())
     torch.cuda.synchronize()
     assert np.array_equal(th.cpu().numpy(), hard), "device-side into_llr must equal libm's logf bit for bit"
     assert np.array_equal(tp.cpu().numpy(), post, equal_nan=True)
     assert np.array_equal(tps.cpu().numpy(), posts, equal_nan=True)
+    bad = b.priors.copy()
+    bad[3, 2] *= 0.5
+    with pytest.raises(ValueError):  # decoder.rs:683-684 through the device-pointer path
+        d.min_sum_batch(torch.from_numpy(bad).cuda(), torch.from_numpy(b.priors_sum).cuda())
+    _, _, _, st = d.min_sum_batch(torch.from_numpy(bad).cuda(), torch.from_numpy(b.priors_sum).cuda(), want_status=True)
+    assert st[3].item() == -2 and int((st != 0).sum().item()) == 1
     # host buffers with a caller-provided (pinned) result buffer
     pinned = torch.empty((T, w.N), dtype=torch.int8).pin_memory().numpy()
     oh, _, _ = d.min_sum_batch(b.priors, b.priors_sum, want_posterior=False, out=pinned)
     assert oh is pinned and np.array_equal(pinned, hard)
     with pytest.raises(ValueError):
         d.min_sum_batch(b.priors, b.priors_sum, out=np.empty((T, w.N + 1), np.int8))
-    ok = w.success(b, hard)
-    assert np.array_equal(ok, w.success(b, rh))
 
 
 def test_exact_mode_matches_enumeration_oracle_kyber768():
@@ -225,6 +275,15 @@ def test_full_size_properties_kyber512():
     perm = np.random.RandomState(0).permutation(T)[:512]
     h3, _, _ = d.min_sum_batch(b.priors[perm], b.priors_sum[perm], want_posterior=False)
     assert np.array_equal(h3, hard[perm])
+    # the whole batch against the exact-order kernel (the reference's arithmetic, test_batched_parity_with_oracle):
+    # hard decisions identical for EVERY trial, posteriors within 1e-4
+    _, post, posts = d.min_sum_batch(b.priors[:4096], b.priors_sum[:4096])
+    n_re = d.last_run["redecoded"]
+    assert 0 < n_re < 4096 // 4
+    eh, ep, eps_ = d.min_sum_batch(b.priors, b.priors_sum, exact=True)
+    assert np.array_equal(hard, eh)
+    assert util.same_nonfinite(post, ep[:4096]) and util.max_abs_diff(post, ep[:4096]) < TOL
+    assert util.same_nonfinite(posts, eps_[:4096]) and util.max_abs_diff(posts, eps_[:4096]) < TOL
 
 
 def test_observed_priors_equal_expanded_priors():

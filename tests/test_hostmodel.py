@@ -10,7 +10,7 @@ import util
 from oracle import oracle as O
 from sca_ldpc_b200 import _lib
 
-EXACT, GENERIC = _lib.CN_EXACT, _lib.CN_GENERIC
+EXACT, GENERIC, NO_VERIFY = _lib.CN_EXACT, _lib.CN_GENERIC, _lib.NO_VERIFY
 
 
 def _kyber(cb, idx):
@@ -46,7 +46,8 @@ def test_fast_kernel_equals_fast_oracle_bitwise():
             it = int(z["iterations"][i])
             d = O.QaryOracle(H, it, B=2, BSUM=12, DC=7)
             h2, p2, ps2 = d.decode_llr(llr[j], llrs[j], algo=O.ALGO_FAST)
-            rc, hard, post, posts, _, fast = util.hostmodel_qary(H, 2, 12, it, llr[j:j + 1], llrs[j:j + 1], dc=7)
+            rc, hard, post, posts, _, fast = util.hostmodel_qary(H, 2, 12, it, llr[j:j + 1], llrs[j:j + 1], dc=7,
+                                                                 flags=NO_VERIFY)
             assert rc == 0 and fast and np.array_equal(hard[0], h2)
             assert np.array_equal(post[0], p2, equal_nan=True) and np.array_equal(posts[0], ps2, equal_nan=True)
     # one and two iterations: FIRST|LAST and FIRST|WSUM -> LAST|RSUM variants
@@ -54,7 +55,7 @@ def test_fast_kernel_equals_fast_oracle_bitwise():
     for it in (1, 2, 3):
         d = O.QaryOracle(H, it, B=2, BSUM=12, DC=7)
         h2, p2, ps2 = d.decode_llr(llr[0], llrs[0], algo=O.ALGO_FAST)
-        rc, hard, post, posts, _, fast = util.hostmodel_qary(H, 2, 12, it, llr, llrs, dc=7)
+        rc, hard, post, posts, _, fast = util.hostmodel_qary(H, 2, 12, it, llr, llrs, dc=7, flags=NO_VERIFY)
         assert rc == 0 and fast and np.array_equal(hard[0], h2)
         assert np.array_equal(post[0], p2, equal_nan=True) and np.array_equal(posts[0], ps2, equal_nan=True)
         if it == 1:  # a single iteration has no simplification at all: equals the forward/backward model
@@ -62,18 +63,65 @@ def test_fast_kernel_equals_fast_oracle_bitwise():
             assert np.array_equal(p2, p3, equal_nan=True) and np.array_equal(ps2, ps3, equal_nan=True)
 
 
-def test_exact_kernel_is_bit_identical_special():
-    """k_cn_generic in exact-order mode reproduces the reference's rounding bit for bit (decoder_special.rs:539-553)."""
+@pytest.mark.parametrize("flags", [EXACT, EXACT | GENERIC])
+def test_exact_kernel_is_bit_identical_special(flags):
+    """k_cn_exact<6,2> (registers) and k_cn_generic in exact-order mode (run-time shapes) both reproduce the reference's
+    rounding bit for bit (decoder_special.rs:539-553)."""
     z, H, llr, llrs = _kyber(1, [0, 3])
     for j, i in enumerate([0, 3]):
         it = min(3, int(z["iterations"][i]))
         d = O.QaryOracle(H, it, B=2, BSUM=12, DC=7)
         h, p, ps = d.decode_llr(llr[j], llrs[j], algo=O.ALGO_EXACT_DP)
-        rc, hard, post, posts, _, fast = util.hostmodel_qary(H, 2, 12, it, llr[j:j + 1], llrs[j:j + 1], flags=EXACT,
+        rc, hard, post, posts, _, fast = util.hostmodel_qary(H, 2, 12, it, llr[j:j + 1], llrs[j:j + 1], flags=flags,
                                                              dc=7)
         assert rc == 0 and not fast
         assert np.array_equal(hard[0], h)
         assert np.array_equal(post[0], p, equal_nan=True) and np.array_equal(posts[0], ps, equal_nan=True)
+
+
+@pytest.mark.parametrize("variant,sw,it", [("kyber512", 6, 1), ("kyber512", 6, 3), ("kyber1024", 8, 2), ("kyber1024", 4, 3)])
+def test_exact_register_kernel_every_shape(variant, sw, it):
+    """k_cn_exact<SW,B> for the other template shapes, with excluded values (+inf LLRs) on both kinds of variable and
+    1 / 2 / 3 iterations (first = last, first + last, a middle one): bit-identical to the oracle's exact-order DP, which
+    tests/golden/make_golden.py asserts bit-identical to the reference's enumeration."""
+    from sca_ldpc_b200.workloads import KyberWorkload
+
+    w = KyberWorkload(variant, sw, 1, accuracy=0.9, nbits=3, nbits_sum=4, seed=3)
+    b = w.generate(3, seed=2)
+    llr = np.stack([O.into_llr(x) for x in b.priors])
+    llrs = np.stack([O.into_llr(x) for x in b.priors_sum])
+    llr[0, ::7, 0] = np.inf
+    llrs[1, ::5, 3] = np.inf
+    d = O.QaryOracle(w.H, it, B=w.B, BSUM=w.BSUM, DC=sw + 1)
+    rh, rp, rps, st = d.decode_batch(llr, llrs, from_probs=False, algo=O.ALGO_EXACT_DP)
+    rc, hard, post, posts, _, fast = util.hostmodel_qary(w.H, w.B, w.BSUM, it, llr, llrs, flags=EXACT, dc=sw + 1)
+    assert rc == 0 and not fast and np.array_equal(hard, rh)
+    assert np.array_equal(post, rp, equal_nan=True) and np.array_equal(posts, rps, equal_nan=True)
+
+
+def test_verified_fast_path_equals_reference_order():
+    """The DEFAULT path (fast check node + verification) against the reference's rounding order on a
+    Kyber-512 batch with converging and non-converging trials: the last iteration flags the trials at risk, they are
+    decoded again with the exact-order check node, and every trial's hard decisions equal the oracle's; posteriors within
+    1e-4 (bit-identical for the re-decoded ones)."""
+    from sca_ldpc_b200.workloads import KyberWorkload
+
+    w = KyberWorkload("kyber512", 6, 1, accuracy=0.95, nbits=4, nbits_sum=5, seed=0)
+    T, it = 12, 6
+    b = w.generate(T, seed=1)
+    llr = np.stack([O.into_llr(x) for x in b.priors])
+    llrs = np.stack([O.into_llr(x) for x in b.priors_sum])
+    d = O.QaryOracle(w.H, it, B=w.B, BSUM=w.BSUM, DC=7)
+    rh, rp, rps, st = d.decode_batch(llr, llrs, from_probs=False, algo=O.ALGO_EXACT_DP)
+    rc, hard, post, posts, _, fast = util.hostmodel_qary(w.H, w.B, w.BSUM, it, llr, llrs, dc=7)
+    n_re = util.hostmodel().hostmodel_last_redecoded()
+    assert rc == 0 and fast and 0 < n_re < T
+    assert np.array_equal(hard, rh)
+    assert util.same_nonfinite(post, rp) and util.max_abs_diff(post, rp) < 1e-4
+    assert util.same_nonfinite(posts, rps) and util.max_abs_diff(posts, rps) < 1e-4
+    # the flagged trials are exactly those whose decisions violate a parity check (none has a near-tie here)
+    synd = rh.astype(np.int32) @ w.H.T.astype(np.int32)
+    assert n_re >= int((synd != 0).any(1).sum())
 
 
 def test_generic_fwd_bwd_kernel_special():
@@ -81,7 +129,7 @@ def test_generic_fwd_bwd_kernel_special():
     it = 4
     d = O.QaryOracle(H, it, B=2, BSUM=12, DC=7)
     h, p, ps = d.decode_llr(llr[0], llrs[0], algo=O.ALGO_FWD_BWD)
-    rc, hard, post, posts, _, fast = util.hostmodel_qary(H, 2, 12, it, llr, llrs, flags=GENERIC, dc=7)
+    rc, hard, post, posts, _, fast = util.hostmodel_qary(H, 2, 12, it, llr, llrs, flags=GENERIC | NO_VERIFY, dc=7)
     assert rc == 0 and not fast and np.array_equal(hard[0], h)
     assert util.same_nonfinite(post[0], p) and util.max_abs_diff(post[0], p) < 2e-5
     assert util.same_nonfinite(posts[0], ps) and util.max_abs_diff(posts[0], ps) < 2e-5
@@ -141,7 +189,9 @@ def test_ragged_batch_and_irregular_rows():
     llr = np.stack([O.into_llr(x) for x in pri])
     llrs = np.stack([O.into_llr(x) for x in pris])
     d = O.QaryOracle(H, 4, B=B, BSUM=B * sw, DC=sw + 1)
-    for flags, algo in ((EXACT, O.ALGO_ENUMERATE), (0, O.ALGO_FWD_BWD)):
+    # exact-order mode: bit-identical; default (verified forward/backward): decisions identical to the ENUMERATION too;
+    # unverified forward/backward: its own CPU model
+    for flags, algo in ((EXACT, O.ALGO_ENUMERATE), (0, O.ALGO_ENUMERATE), (NO_VERIFY, O.ALGO_FWD_BWD)):
         rc, hard, post, posts, _, fast = util.hostmodel_qary(H, B, B * sw, 4, llr, llrs, flags=flags, dc=sw + 1)
         assert rc == 0 and not fast
         for t in range(T):

@@ -49,7 +49,7 @@ def hostmodel():
         src = os.path.join(ROOT, "tests", "hostmodel", "hostmodel.cpp")
         out = os.path.join(ROOT, "tests", "hostmodel", "libhostmodel.so")
         deps = [src] + [os.path.join(ROOT, "sca_ldpc_b200", "csrc", f)
-                        for f in ("qary_kernels.cuh", "qary_cn_fast.cuh", "qary_graph.h", "bp_kernels.cuh", "bp_graph.h", "tma.cuh")]
+                        for f in ("qary_kernels.cuh", "qary_cn_fast.cuh", "qary_cn_exact.cuh", "qary_graph.h", "bp_kernels.cuh", "bp_graph.h", "tma.cuh")]
         deps = [d for d in deps if os.path.exists(d)]
         if not os.path.exists(out) or any(os.path.getmtime(d) > os.path.getmtime(out) for d in deps):
             subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-fno-fast-math",
