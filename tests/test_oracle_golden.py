@@ -164,3 +164,37 @@ def test_rep_code_doctest():
         ok += int((bpd.decode(err) == 0).all())
     assert ok == 100
     assert util.reference_doctests()["decode.py:139-149 simulate_frame_error_rate(rep_code(13))"] == 100
+
+
+@pytest.mark.parametrize("B,col_w", [(2, 2), (3, 3), (1, 4)])
+def test_special_oracle_equals_pinned_generic_oracle_when_alphabets_coincide(B, col_w):
+    """DecoderSpecial has no live test in the reference (decoder_special.rs:687-747 are commented
+    out), the generic Decoder is pinned by the Rust goldens above.  With sum_weight 1 the sum-variables' alphabet
+    [-BSUM, BSUM] = [-B, B] IS the B-variables' alphabet, so H = [H' | I] is an ordinary single-alphabet problem and both
+    restatements must agree bit for bit on finite priors: same graph order (columns ascending inside a row: the
+    sum-variable last, decoder_special.rs:507-522 / decoder.rs:507-539), same S = (0 + a_0) + a_sum, same total-minus-self
+    variable node.  This ties the unpinned half of oracle/qary_impl.inc to the pinned half."""
+    rs = np.random.RandomState(17 + B)
+    bv, Q = 7, 2 * B + 1
+    R = bv * col_w  # every check: ONE B-variable (+-1) and its own sum-variable; every B-variable sits in col_w checks
+    H = np.zeros((R, bv + R), np.int8)
+    for r in range(R):
+        H[r, r % bv] = rs.choice([-1, 1])
+        H[r, bv + r] = 1
+    T, it = 9, 4
+    pri = rs.dirichlet(np.ones(Q) * 0.7, size=(T, bv)).astype(np.float32) + np.float32(1e-4)
+    pri /= pri.sum(-1, keepdims=True)
+    pris = rs.dirichlet(np.ones(Q) * 0.7, size=(T, R)).astype(np.float32) + np.float32(1e-4)
+    pris /= pris.sum(-1, keepdims=True)
+    special = O.QaryOracle(H, it, B=B, BSUM=B, DC=2)
+    generic = O.QaryOracle(H, it, B=B, DV=col_w, DC=2)
+    assert special.bvars == bv and generic.bvars == bv + R
+    for algo in (O.ALGO_ENUMERATE, O.ALGO_EXACT_DP):
+        sh, sp, sps, st = special.decode_batch(pri, pris, from_probs=True, algo=algo)
+        gh, gp, _, gst = generic.decode_batch(np.concatenate([pri, pris], axis=1), from_probs=True, algo=algo)
+        assert (st == 0).all() and (gst == 0).all()
+        assert np.array_equal(sh, gh)
+        assert np.array_equal(sp, gp[:, :bv]) and np.array_equal(sps, gp[:, bv:])
+    # and the two are not trivially equal to the priors' decisions: the checks did move something
+    prior_dec = np.concatenate([pri, pris], axis=1).argmax(-1) - B
+    assert (sh != prior_dec).any()
