@@ -71,6 +71,22 @@ typedef struct scaldpc_qary scaldpc_qary;
                                      stream synchronisation per batch and the re-decode of ~1-3 % of a decodable
                                      workload's trials (all of an undecodable one's). */
 
+#define SCALDPC_QARY_EARLY_STOP 0x200u /* OPT-IN per-trial early termination with active-trial compaction -- an EXTENSION:
+                                     the reference has no syndrome test and always runs max_iter iterations
+                                     (decoder_special.rs:501-504 "noop, we use only num iterations", exit at :611-613), so
+                                     parity runs leave this off.  Every iteration emits hard decisions; a trial whose
+                                     decisions satisfy every row, sum_j h_ij s_j (+ s_sum,i) = 0, and whose posteriors
+                                     are clear of ties (risk margin) is frozen with that iteration's outputs.  Once at
+                                     most 1/8 of a batch of >= 2048 trials is still running the stragglers are re-staged
+                                     compactly and decoded from scratch (the same results, fewer idle lanes).  Trials
+                                     still running at max_iter keep their last decisions (SCALDPC_NO_VERIFY) or are
+                                     decoded with the exact-order check node and the fixed iteration count, i.e. they get
+                                     the reference's result.  The sum-variables' messages make the full round trip in
+                                     this mode (plain forward/backward flooding).  Frozen trials can differ from the
+                                     fixed-iteration decode only if their decisions would still have moved after the row
+                                     tests first held; bench.py reports that count.  Synchronises the stream once per
+                                     iteration.  Ignored with SCALDPC_CN_EXACT. */
+
 /*
  * scaldpc_qary_create -- replaces `#[new] fn new(py_parity_check, iterations)` (pydecoder.rs:24-45, 96-117),
  * i.e. Decoder::new (decoder.rs:494-553) when bsum == 0 and DecoderSpecial::new (decoder_special.rs:387-464)
@@ -170,9 +186,13 @@ int scaldpc_qary_simulate(scaldpc_qary *h, int T, uint64_t seed, uint64_t first_
 /* Kernels launched by this handle so far (for bench.py's "gpu_launches") and device time is NOT tracked
  * here -- callers time with CUDA events on `stream`. */
 long long scaldpc_qary_launch_count(const scaldpc_qary *h);
-/* Statistics of the last decode / decode_observed / simulate call on this handle: trials decoded and how many of
- * them the verification re-decoded with the exact-order check node (0 with SCALDPC_NO_VERIFY / SCALDPC_CN_EXACT). */
-int scaldpc_qary_last_run(const scaldpc_qary *h, long long *trials, long long *redecoded);
+/* Statistics of the last decode / decode_observed / simulate call on this handle: trials decoded, how many of them the
+ * verification re-decoded with the exact-order check node (0 with SCALDPC_NO_VERIFY / SCALDPC_CN_EXACT), and the
+ * trial-iterations actually launched (restarted and re-decoded trials counted again) -- any pointer may be NULL. */
+int scaldpc_qary_last_run(const scaldpc_qary *h, long long *trials, long long *redecoded, long long *trial_iterations);
+/* Per-trial iteration counts of the last decode / decode_observed call, which must have used SCALDPC_QARY_EARLY_STOP on
+ * at least T trials: the iteration in which the trial was frozen, or max_iter.  flags: SCALDPC_DEVICE_PTRS or 0. */
+int scaldpc_qary_last_iterations(scaldpc_qary *h, int32_t *iters, int T, unsigned flags, void *stream);
 /* Risk margin of the verification (absolute LLR difference between a posterior's two smallest entries below which
  * the trial is re-decoded); default 1e-2, or the environment variable SCALDPC_RISK_MARGIN at create time. */
 int scaldpc_qary_set_risk_margin(scaldpc_qary *h, float eps);

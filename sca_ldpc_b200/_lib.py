@@ -16,7 +16,7 @@ OK = 0
 ERR_ARG, ERR_PROB_SUM, ERR_NO_MAX, ERR_NO_CONFIG, ERR_DEGREE, ERR_STRUCTURE, ERR_RANGE, ERR_CUDA, ERR_UNSUPPORTED = (
     -1, -2, -3, -4, -5, -6, -7, -8, -9)
 # decode flags
-IN_LLR, DEVICE_PTRS, CN_EXACT, CN_GENERIC, NO_VERIFY = 0x1, 0x2, 0x4, 0x8, 0x100
+IN_LLR, DEVICE_PTRS, CN_EXACT, CN_GENERIC, NO_VERIFY, QARY_EARLY_STOP = 0x1, 0x2, 0x4, 0x8, 0x100, 0x200
 BP_PROBS_PER_TRIAL, BP_NO_EARLY_STOP, BP_NO_COMPACT = 0x10, 0x20, 0x40
 
 # every exported symbol of include/scaldpc.h (tests/test_abi.py checks this list against the header)
@@ -24,7 +24,7 @@ SYMBOLS = [
     "scaldpc_last_error", "scaldpc_version", "scaldpc_device_count",
     "scaldpc_qary_create", "scaldpc_qary_destroy", "scaldpc_qary_info", "scaldpc_qary_set_max_iter",
     "scaldpc_qary_decode", "scaldpc_qary_decode_observed", "scaldpc_qary_simulate", "scaldpc_qary_launch_count", "scaldpc_qary_time_kernel",
-    "scaldpc_qary_last_run", "scaldpc_qary_set_risk_margin",
+    "scaldpc_qary_last_run", "scaldpc_qary_set_risk_margin", "scaldpc_qary_last_iterations",
     "scaldpc_bp_create", "scaldpc_bp_destroy", "scaldpc_bp_info", "scaldpc_bp_decode", "scaldpc_bp_decode_scored", "scaldpc_bp_decode_nested", "scaldpc_bp_launch_count",
     "scaldpc_bp_last_run", "scaldpc_bp_time_kernel",
 ]
@@ -78,7 +78,9 @@ def lib() -> C.CDLL:
     L.scaldpc_qary_launch_count.restype = C.c_longlong
     L.scaldpc_qary_launch_count.argtypes = [vp]
     L.scaldpc_qary_last_run.restype = i
-    L.scaldpc_qary_last_run.argtypes = [vp, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
+    L.scaldpc_qary_last_run.argtypes = [vp, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
+    L.scaldpc_qary_last_iterations.restype = i
+    L.scaldpc_qary_last_iterations.argtypes = [vp, vp, i, u, vp]
     L.scaldpc_qary_set_risk_margin.restype = i
     L.scaldpc_qary_set_risk_margin.argtypes = [vp, C.c_float]
     L.scaldpc_qary_time_kernel.restype = i

@@ -64,6 +64,13 @@ struct scaldpc_qary {
     int *h_scan_out = nullptr;    // pinned mirror
     float risk_eps = 1e-2f;
     long long last_trials = 0, last_redecoded = 0;  // of the last decode / simulate call
+    long long last_work = 0;      // trial-iterations launched by the last call (restarts and re-decodes included)
+    // early termination (SCALDPC_QARY_EARLY_STOP)
+    uint32_t *d_done = nullptr;   // [tiles] frozen-trial words
+    int *d_iters = nullptr;       // [tiles*32] last iteration of every slot of the current round
+    int *d_iters_all = nullptr;   // [cap_iters_T] per-trial iteration counts of the last call
+    size_t cap_iters_T = 0;
+    int es_restart_min = 2048;    // batches at least this large restart their stragglers in a compacted second round
     // staging for host-pointer calls: the batch is cut into chunks and pipelined (H2D of chunk i+1 and D2H of chunk
     // i-1 overlap the decode of chunk i), so every staging buffer exists twice
     size_t cap_stage_T = 0;  // trials per output staging buffer
@@ -111,6 +118,10 @@ void free_workspace(scaldpc_qary *h)
     cudaFree(h->d_status);
     cudaFree(h->d_risk);
     cudaFree(h->d_risk_list);
+    cudaFree(h->d_done);
+    cudaFree(h->d_iters);
+    h->d_done = nullptr;
+    h->d_iters = nullptr;
     h->d_msg = h->d_llr = h->d_llr_sum = h->d_post = h->d_post_sum = nullptr;
     h->d_hard_t = nullptr;
     h->d_status = nullptr;
@@ -206,7 +217,9 @@ int ensure_workspace(scaldpc_qary *h, int tiles, bool want_post)
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_hard_t, lanes * h->N));
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_status, 2 * lanes * sizeof(int)));
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_risk, (size_t)t * sizeof(uint32_t)));
-    SCALDPC_CUDA(cudaMalloc((void **)&h->d_risk_list, lanes * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_risk_list, 2 * lanes * sizeof(int)));  // two lists (rounds of early termination)
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_done, (size_t)t * sizeof(uint32_t)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_iters, lanes * sizeof(int)));
     if (!h->d_scan_out) {
         SCALDPC_CUDA(cudaMalloc((void **)&h->d_scan_out, 2 * sizeof(int)));
         SCALDPC_CUDA(cudaHostAlloc((void **)&h->h_scan_out, 2 * sizeof(int), cudaHostAllocDefault));
@@ -357,14 +370,18 @@ typedef void (*vn_fn)(const QaryDev, const int);
 
 // The instantiations of the persistent check-node kernel for one shape, indexed by cn_mode_index().
 struct CnFast {
-    cn_fast_fn fn[6];
+    cn_fast_fn fn[8];
     size_t smem;
 };
+constexpr int kCnFastVariants = 8;
 
 // Iteration `it` of `iters` -> kernel variant (qary_cn_fast.cuh MODE bits): the sum-variable's c2v is written only by
 // the second-to-last iteration and read only by the last one.
-int cn_mode_index(int it, int iters)
+int cn_mode_index(int it, int iters, bool every_iteration_decides)
 {
+    // early termination: every iteration emits decisions (LAST) and the sum-variable's message makes the full round trip
+    // (WSUM now, RSUM next time) -- plain forward/backward flooding, oracle algo 2
+    if (every_iteration_decides) return it == 1 ? 6 : 7;
     const bool first = it == 1, last = it == iters, penult = it == iters - 1;
     if (first) return last ? 1 : (penult ? 2 : 0);
     return last ? 5 : (penult ? 4 : 3);
@@ -375,7 +392,8 @@ const CnFast *cn_fast_table()
 {
     static const CnFast t = {{k_cn_fast<SW, B, kCnFirst>, k_cn_fast<SW, B, kCnFirst | kCnLast>,
                               k_cn_fast<SW, B, kCnFirst | kCnWsum>, k_cn_fast<SW, B, 0>, k_cn_fast<SW, B, kCnWsum>,
-                              k_cn_fast<SW, B, kCnLast | kCnRsum>},
+                              k_cn_fast<SW, B, kCnLast | kCnRsum>, k_cn_fast<SW, B, kCnFirst | kCnLast | kCnWsum>,
+                              k_cn_fast<SW, B, kCnLast | kCnRsum | kCnWsum>},
                              CnFastShape<SW, B>::smem_bytes};
     return &t;
 }
@@ -465,7 +483,8 @@ size_t generic_smem_bytes(const scaldpc_qary *h, CnGenericArgs *g)
 // One check-node launch / one variable-node launch over `tiles` tiles.
 int launch_cn(scaldpc_qary *h, const QaryDev &p, int tiles, int it, int iters, unsigned flags, cudaStream_t st)
 {
-    const bool first = it == 1, last = it == iters;
+    const bool decide = flags & SCALDPC_QARY_EARLY_STOP;  // every iteration emits hard decisions
+    const bool first = it == 1, last = it == iters || decide;
     const bool exact = flags & SCALDPC_CN_EXACT;
     const bool force_generic = flags & SCALDPC_CN_GENERIC;
     const CnFast *fast = (!exact && !force_generic && h->fast_sw) ? pick_cn_fast(h->fast_sw, h->B) : nullptr;
@@ -473,7 +492,7 @@ int launch_cn(scaldpc_qary *h, const QaryDev &p, int tiles, int it, int iters, u
         // persistent: one CTA of kCnWarps warps per SM, warps stride over the (tile, check) items
         const int n_items = tiles * h->R;
         const int grid = std::max(1, std::min(h->num_sms, (n_items + kCnWarps - 1) / kCnWarps));
-        fast->fn[cn_mode_index(it, iters)]<<<grid, kCnWarps * 32, fast->smem, st>>>(p, n_items);
+        fast->fn[cn_mode_index(it, iters, decide)]<<<grid, kCnWarps * 32, fast->smem, st>>>(p, n_items);
         ++h->launches;
     } else if (exact && !force_generic && h->fast_sw) {
         // exact-order dynamic programme in registers, one warp per (tile, check)
@@ -579,6 +598,7 @@ int scaldpc_qary_create(const int8_t *H, int R, int N, int b, int bsum, int dv, 
     h->device = device;
     if (const char *e = getenv("SCALDPC_MAX_RESIDENT_TRIALS")) h->max_resident = std::max(32, atoi(e));
     if (const char *e = getenv("SCALDPC_RISK_MARGIN")) h->risk_eps = std::max(0.0f, (float)atof(e));
+    if (const char *e = getenv("SCALDPC_ES_RESTART_MIN")) h->es_restart_min = std::max(1, atoi(e));
     h->E = g.E;
     h->S = g.S;
     h->SL = g.SL;
@@ -602,7 +622,7 @@ int scaldpc_qary_create(const int8_t *H, int R, int N, int b, int bsum, int dv, 
     SCALDPC_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
     if (h->fast_sw) {
         const CnFast *f = pick_cn_fast(h->fast_sw, b);
-        for (int i = 0; i < 6; ++i)
+        for (int i = 0; i < kCnFastVariants; ++i)
             SCALDPC_CUDA(cudaFuncSetAttribute(f->fn[i], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f->smem));
         const CnExact *ex = pick_cn_exact(h->fast_sw, b);
         SCALDPC_CUDA(cudaFuncSetAttribute(ex->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ex->smem));
@@ -637,6 +657,7 @@ void scaldpc_qary_destroy(scaldpc_qary *h)
     free_sim(h);
     cudaFree(h->d_status_all);
     cudaFree(h->d_scan_out);
+    cudaFree(h->d_iters_all);
     if (h->h_scan_out) cudaFreeHost(h->h_scan_out);
     if (h->s_in) cudaStreamDestroy(h->s_in);
     if (h->s_out) cudaStreamDestroy(h->s_out);
@@ -677,11 +698,27 @@ int scaldpc_qary_set_max_iter(scaldpc_qary *h, int max_iter)
 
 long long scaldpc_qary_launch_count(const scaldpc_qary *h) { return h ? h->launches : 0; }
 
-int scaldpc_qary_last_run(const scaldpc_qary *h, long long *trials, long long *redecoded)
+int scaldpc_qary_last_run(const scaldpc_qary *h, long long *trials, long long *redecoded, long long *trial_iterations)
 {
     if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
     if (trials) *trials = h->last_trials;
     if (redecoded) *redecoded = h->last_redecoded;
+    if (trial_iterations) *trial_iterations = h->last_work;
+    return 0;
+}
+
+int scaldpc_qary_last_iterations(scaldpc_qary *h, int32_t *iters, int T, unsigned flags, void *stream)
+{
+    if (!h || !iters || T < 0) return fail(SCALDPC_ERR_ARG, "bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->d_iters_all || (size_t)T > h->cap_iters_T)
+        return fail(SCALDPC_ERR_ARG, "the last decode on this handle did not use SCALDPC_QARY_EARLY_STOP on >= T trials");
+    SCALDPC_CUDA(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool dev = flags & SCALDPC_DEVICE_PTRS;
+    SCALDPC_CUDA(cudaMemcpyAsync(iters, h->d_iters_all, (size_t)T * sizeof(int),
+                                 dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
+    if (!dev) SCALDPC_CUDA(cudaStreamSynchronize(st));
     return 0;
 }
 
@@ -771,6 +808,76 @@ static int emit_outputs(scaldpc_qary *h, int T, const int *map, int8_t *dhard, f
     return 0;
 }
 
+// Flagged / still-running trials of the `n` slots -> ascending list + count (and, with `status`, the most severe per-trial
+// status of slots 0 .. n-1).  Synchronises `st`.
+static int scan_flags(scaldpc_qary *h, int n, const int *status, int *list, cudaStream_t st, int *count, int *worst)
+{
+    k_risk_scan<<<1, 1024, 0, st>>>(h->d_risk, (n + 31) / 32, n, status, list, h->d_scan_out);
+    ++h->launches;
+    SCALDPC_CUDA(cudaGetLastError());
+    SCALDPC_CUDA(cudaMemcpyAsync(h->h_scan_out, h->d_scan_out, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    SCALDPC_CUDA(cudaStreamSynchronize(st));
+    *count = h->h_scan_out[0];
+    if (worst) *worst = h->h_scan_out[1];
+    return 0;
+}
+
+// Exact-order decode (the reference's arithmetic, fixed iteration count) of the `nf` trials listed in `list`, staged
+// compactly into the leading tiles of the workspace; their outputs overwrite rows list[i] of the caller's arrays.
+static int redecode_exact(scaldpc_qary *h, int nf, const int *list, const PriorSrc &src, int8_t *dhard, float *dpost,
+                          float *dpost_sum, unsigned flags, cudaStream_t st)
+{
+    const bool want_post = dpost != nullptr || dpost_sum != nullptr;
+    int rc;
+    h->last_redecoded += nf;
+    h->last_work += (long long)nf * std::max(1, h->max_iter);
+    if ((rc = stage_priors(h, nf, src, flags, nullptr, list, st))) return rc;
+    QaryDev p2 = dev_view(h, want_post);
+    p2.status = h->d_status + (size_t)h->cap_tiles * 32;  // scratch: the fast pass has already recorded every status
+    const unsigned f2 = (flags | SCALDPC_CN_EXACT) & ~(SCALDPC_CN_GENERIC | SCALDPC_QARY_EARLY_STOP);
+    if ((rc = run_iterations(h, p2, (nf + 31) / 32, f2, st))) return rc;
+    return emit_outputs(h, nf, list, dhard, dpost, dpost_sum, st);
+}
+
+// One round of early termination over the `n` trials staged in the workspace: after every iteration each trial whose
+// hard decisions satisfy every row (and whose posteriors are clear of ties) is frozen; the round ends when nobody is
+// running, at the iteration cap, or -- `may_restart` -- as soon as at most 1/8 of the slots are still running, so that the
+// caller can re-stage those stragglers compactly instead of dragging 7/8 idle lanes along.  Synchronises once per iteration
+// (4 bytes).  Leaves risk[] = the slots still running.
+static int early_stop_round(scaldpc_qary *h, int n, bool want_post, unsigned flags, bool may_restart, cudaStream_t st,
+                            int *iterations, int *running)
+{
+    const int tiles = (n + 31) / 32;
+    const int iters = std::max(1, h->max_iter);
+    int rc;
+    SCALDPC_CUDA(cudaMemsetAsync(h->d_done, 0, (size_t)tiles * sizeof(uint32_t), st));
+    SCALDPC_CUDA(cudaMemsetAsync(h->d_iters, 0, (size_t)tiles * 32 * sizeof(int), st));
+    QaryDev p = dev_view(h, want_post);
+    p.risk = h->d_risk;
+    p.risk_eps = h->risk_eps;
+    p.done = h->d_done;
+    int it = 0, run = n;
+    while (it < iters && run > 0) {
+        ++it;
+        SCALDPC_CUDA(cudaMemsetAsync(h->d_risk, 0, (size_t)tiles * sizeof(uint32_t), st));
+        SCALDPC_CUDA(cudaMemsetAsync(h->d_scan_out, 0, sizeof(int), st));
+        if ((rc = launch_cn(h, p, tiles, it, iters, flags, st))) return rc;
+        if ((rc = launch_vn(h, p, tiles, true, flags, st))) return rc;
+        k_qary_syndrome<<<dim3((h->R + 7) / 8, tiles), 256, 0, st>>>(p);
+        k_qary_finish<<<(tiles + 255) / 256, 256, 0, st>>>(h->d_risk, h->d_done, h->d_iters, tiles, n, it, h->d_scan_out);
+        h->launches += 2;
+        SCALDPC_CUDA(cudaGetLastError());
+        SCALDPC_CUDA(cudaMemcpyAsync(h->h_scan_out, h->d_scan_out, sizeof(int), cudaMemcpyDeviceToHost, st));
+        SCALDPC_CUDA(cudaStreamSynchronize(st));
+        run = h->h_scan_out[0];
+        if (may_restart && it < iters && (long long)run * 8 <= n) break;
+    }
+    h->last_work += (long long)n * it;
+    *iterations = it;
+    *running = run;
+    return 0;
+}
+
 // The device pipeline of one batch: priors (device, row-major) -> hard decisions (device, row-major), all on `st`.
 //
 // Default mode = the fast forward/backward check node, VERIFIED: the last iteration flags every trial
@@ -779,17 +886,60 @@ static int emit_outputs(scaldpc_qary *h, int T, const int *map, int8_t *dhard, f
 // with the exact-order check node (the reference's arithmetic bit for bit, decoder_special.rs:539-553) and their outputs
 // replace the fast ones.  That needs the flagged count on the host: ONE stream synchronisation per batch, which also
 // returns the most severe per-trial status (*worst, may be null).  SCALDPC_NO_VERIFY / SCALDPC_CN_EXACT skip all of it.
+//
+// SCALDPC_QARY_EARLY_STOP (an extension, off by default): round 1 decodes everybody and freezes trials as
+// they converge; if it was cut short (<= 1/8 still running) the stragglers are re-staged compactly and decoded from
+// scratch in round 2, freezing again; what is still running at the iteration cap keeps its last decisions or -- verified
+// mode -- is decoded once more with the exact-order check node and the reference's fixed iteration count.
+// `iters_out` (device, may be null): per-trial iteration counts.
 static int decode_on_device(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *dhard, float *dpost, float *dpost_sum,
-                            unsigned flags, cudaStream_t st, int *worst)
+                            unsigned flags, cudaStream_t st, int *worst, int *iters_out)
 {
     const bool want_post = dpost != nullptr || dpost_sum != nullptr;
+    const bool exact = flags & SCALDPC_CN_EXACT;
+    const bool early = (flags & SCALDPC_QARY_EARLY_STOP) && !exact;
     const bool verify = !(flags & (SCALDPC_CN_EXACT | SCALDPC_NO_VERIFY));
     const int tiles = (T + 31) / 32;
+    const int iters = std::max(1, h->max_iter);
     int rc;
     if (worst) *worst = 0;
     h->last_trials += T;
     SCALDPC_CUDA(cudaMemsetAsync(h->d_status, 0, (size_t)tiles * 32 * sizeof(int), st));
     if ((rc = stage_priors(h, T, src, flags, h->d_status, nullptr, st))) return rc;
+    int *list_a = h->d_risk_list, *list_b = h->d_risk_list + (size_t)h->cap_tiles * 32;
+
+    if (early) {
+        int its = 0, run = 0;
+        if ((rc = early_stop_round(h, T, want_post, flags, T >= h->es_restart_min, st, &its, &run))) return rc;
+        if ((rc = emit_outputs(h, T, nullptr, dhard, dpost, dpost_sum, st))) return rc;
+        if (iters_out) {
+            k_scatter_int<<<(T + 255) / 256, 256, 0, st>>>(h->d_iters, nullptr, iters_out, T);
+            ++h->launches;
+        }
+        int nf = 0;
+        if ((rc = scan_flags(h, T, h->d_status, list_a, st, &nf, worst))) return rc;  // also fetches the statuses
+        if (nf > 0 && its < iters) {  // round 2: the stragglers, compacted, from scratch
+            const int n2 = nf;
+            if ((rc = stage_priors(h, n2, src, flags, nullptr, list_a, st))) return rc;
+            if ((rc = early_stop_round(h, n2, want_post, flags, false, st, &its, &run))) return rc;
+            if ((rc = emit_outputs(h, n2, list_a, dhard, dpost, dpost_sum, st))) return rc;
+            if (iters_out) {
+                k_scatter_int<<<(n2 + 255) / 256, 256, 0, st>>>(h->d_iters, list_a, iters_out, n2);
+                ++h->launches;
+            }
+            nf = 0;
+            if (run > 0 && verify) {  // slots of round 2 still running -> trial indices of the batch
+                if ((rc = scan_flags(h, n2, nullptr, list_b, st, &nf, nullptr))) return rc;
+                k_compose_map<<<(nf + 255) / 256, 256, 0, st>>>(list_b, list_a, h->d_scan_out);
+                ++h->launches;
+                SCALDPC_CUDA(cudaGetLastError());
+                if (nf > 0) return redecode_exact(h, nf, list_b, src, dhard, dpost, dpost_sum, flags, st);
+            }
+            return 0;
+        }
+        if (nf > 0 && verify) return redecode_exact(h, nf, list_a, src, dhard, dpost, dpost_sum, flags, st);
+        return 0;
+    }
 
     QaryDev p = dev_view(h, want_post);
     if (verify) {
@@ -798,29 +948,17 @@ static int decode_on_device(scaldpc_qary *h, int T, const PriorSrc &src, int8_t 
         p.risk_eps = h->risk_eps;
     }
     if ((rc = run_iterations(h, p, tiles, flags, st))) return rc;
+    h->last_work += (long long)T * iters;
     if (verify) {
         k_qary_syndrome<<<dim3((h->R + 7) / 8, tiles), 256, 0, st>>>(p);
         ++h->launches;
     }
     if ((rc = emit_outputs(h, T, nullptr, dhard, dpost, dpost_sum, st))) return rc;
     if (!verify) return 0;
-
-    k_risk_scan<<<1, 1024, 0, st>>>(h->d_risk, tiles, T, h->d_status, h->d_risk_list, h->d_scan_out);
-    ++h->launches;
-    SCALDPC_CUDA(cudaGetLastError());
-    SCALDPC_CUDA(cudaMemcpyAsync(h->h_scan_out, h->d_scan_out, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
-    SCALDPC_CUDA(cudaStreamSynchronize(st));
-    const int nf = h->h_scan_out[0];
-    if (worst) *worst = h->h_scan_out[1];
+    int nf = 0;
+    if ((rc = scan_flags(h, T, h->d_status, list_a, st, &nf, worst))) return rc;
     if (nf <= 0) return 0;
-    // ---- exact-order re-decode of the flagged trials, compacted into the leading tiles of the same workspace
-    h->last_redecoded += nf;
-    const int ftiles = (nf + 31) / 32;
-    if ((rc = stage_priors(h, nf, src, flags, nullptr, h->d_risk_list, st))) return rc;
-    QaryDev p2 = dev_view(h, want_post);
-    p2.status = h->d_status + (size_t)h->cap_tiles * 32;  // scratch: the fast pass has already recorded every status
-    if ((rc = run_iterations(h, p2, ftiles, (flags | SCALDPC_CN_EXACT) & ~SCALDPC_CN_GENERIC, st))) return rc;
-    return emit_outputs(h, nf, h->d_risk_list, dhard, dpost, dpost_sum, st);
+    return redecode_exact(h, nf, list_a, src, dhard, dpost, dpost_sum, flags, st);
 }
 
 // Shared body of scaldpc_qary_decode / scaldpc_qary_decode_observed.  `src` holds the caller's pointers (host or
@@ -832,7 +970,20 @@ static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *har
     const bool want_post = post != nullptr || post_sum != nullptr;
     const bool dev_ptrs = flags & SCALDPC_DEVICE_PTRS;
     int rc, worst = 0;
-    h->last_trials = h->last_redecoded = 0;
+    h->last_trials = h->last_redecoded = h->last_work = 0;
+    if (flags & SCALDPC_QARY_EARLY_STOP) {  // per-trial iteration counts of this call (scaldpc_qary_last_iterations)
+        if ((size_t)T > h->cap_iters_T) {
+            cudaFree(h->d_iters_all);
+            h->d_iters_all = nullptr;
+            h->cap_iters_T = 0;
+            SCALDPC_CUDA(cudaMalloc((void **)&h->d_iters_all, (size_t)T * sizeof(int)));
+            h->cap_iters_T = (size_t)T;
+        }
+    } else if (h->d_iters_all) {
+        cudaFree(h->d_iters_all);
+        h->d_iters_all = nullptr;
+        h->cap_iters_T = 0;
+    }
 
     if (dev_ptrs) {  // asynchronous on `st` (one synchronisation per pass unless SCALDPC_NO_VERIFY); at most `max_resident` trials' messages live in the workspace at a time
         const int cap = std::max(32, h->max_resident / 32 * 32);
@@ -849,7 +1000,8 @@ static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *har
             }
             int w = 0;
             if ((rc = decode_on_device(h, tc, part, hard + (size_t)t0 * h->N, post ? post + (size_t)t0 * h->SL : nullptr,
-                                       post_sum ? post_sum + (size_t)t0 * h->SLS : nullptr, flags, st, &w)))
+                                       post_sum ? post_sum + (size_t)t0 * h->SLS : nullptr, flags, st, &w,
+                                       h->d_iters_all ? h->d_iters_all + t0 : nullptr)))
                 return rc;
             worst = std::min(worst, w);
             if (status)
@@ -916,7 +1068,8 @@ static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *har
         dsrc.obs = h->d_obs[b];
         dsrc.obs_sum = h->d_obs_sum[b];
         if ((rc = decode_on_device(h, tc, dsrc, h->d_ohard[b], post ? h->d_opost[b] : nullptr,
-                                   post_sum ? h->d_opost_sum[b] : nullptr, flags, st, nullptr)))
+                                   post_sum ? h->d_opost_sum[b] : nullptr, flags, st, nullptr,
+                                   h->d_iters_all ? h->d_iters_all + t0 : nullptr)))
             return rc;
         SCALDPC_CUDA(cudaMemcpyAsync(h->d_status_all + t0, h->d_status, (size_t)tc * sizeof(int), cudaMemcpyDeviceToDevice, st));
         SCALDPC_CUDA(cudaEventRecord(h->ev_comp[b], st));
@@ -1020,7 +1173,7 @@ int scaldpc_qary_simulate(scaldpc_qary *h, int T, uint64_t seed, uint64_t first_
     if (T == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     std::lock_guard<std::mutex> lk(h->mu);
-    h->last_trials = h->last_redecoded = 0;
+    h->last_trials = h->last_redecoded = h->last_work = 0;
     SCALDPC_CUDA(cudaSetDevice(h->device));
     int rc;
     if ((rc = upload_tables(h, table, n_rows, table_sum, n_rows_sum, flags, st))) return rc;
@@ -1057,7 +1210,7 @@ int scaldpc_qary_simulate(scaldpc_qary *h, int T, uint64_t seed, uint64_t first_
                                         (int *)(h->d_sim_cnt + 5), tc);
         h->launches += 2;
         SCALDPC_CUDA(cudaGetLastError());
-        if ((rc = decode_on_device(h, tc, src, h->d_sim_hard, nullptr, nullptr, flags, st, nullptr))) return rc;
+        if ((rc = decode_on_device(h, tc, src, h->d_sim_hard, nullptr, nullptr, flags, st, nullptr, nullptr))) return rc;
         k_sim_count<<<grid, 256, 0, st>>>(h->d_sim_hard, h->d_sim_secret, h->d_sim_ssum, h->d_sim_cnt, tc, h->N, h->bvars);
         ++h->launches;
         SCALDPC_CUDA(cudaGetLastError());

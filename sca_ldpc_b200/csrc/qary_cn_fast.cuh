@@ -169,6 +169,7 @@ __global__ void __launch_bounds__(kCnWarps * 32, 1) k_cn_fast(const QaryDev p, c
     // Stage the inputs of `item` (device: lane 0 only, asynchronous; host model: every thread, synchronous).
     auto issue = [&](int item) {
         const int tile = item / p.R, check = item - tile * p.R;
+        if (done_word(p, tile) == 0xffffffffu) return;  // early termination: the item is skipped, nothing is staged
         const int e0 = __ldg(p.row_ptr + check);
 #ifndef SCALDPC_HOST_MODEL
         sc_mbar_expect_tx(bar, (uint32_t)(((RSUM ? NS : SW * Q) + QS) * 128));
@@ -190,6 +191,14 @@ __global__ void __launch_bounds__(kCnWarps * 32, 1) k_cn_fast(const QaryDev p, c
 #endif
     for (int item = gw; item < n_items; item += nw) {
         const int tile = item / p.R, check = item - tile * p.R;
+        const uint32_t frozen_w = done_word(p, tile);
+        if (frozen_w == 0xffffffffu) {  // every trial of the tile is final: `issue` staged nothing for this item either
+#ifndef SCALDPC_HOST_MODEL
+            if (item + nw < n_items && lane == 0) issue(item + nw);
+#endif
+            continue;
+        }
+        const bool frozen = (frozen_w >> lane) & 1u;
         const int e0 = __ldg(p.row_ptr + check);
         const int base = __ldg(p.edge_off + e0);
         const int vs = __ldg(p.col + e0 + SW) - p.bvars;
@@ -294,11 +303,11 @@ __global__ void __launch_bounds__(kCnWarps * 32, 1) k_cn_fast(const QaryDev p, c
                     arg = i;
                 }
                 mm.add(tot);
-                if (post) post[(size_t)(vs * QS + iv) * 32] = tot;
+                if (post && !frozen) post[(size_t)(vs * QS + iv) * 32] = tot;
             }
             const int argv = negs ? QS - 1 - arg : arg;
-            p.hard_t[((size_t)tile * p.N + p.bvars + vs) * 32 + lane] = (int8_t)(argv - BS);
-            if (p.risk) flag_risk(p, tile, lane, mm.risky(p.risk_eps));
+            if (!frozen) p.hard_t[((size_t)tile * p.N + p.bvars + vs) * 32 + lane] = (int8_t)(argv - BS);
+            if (p.risk) flag_risk(p, tile, lane, !frozen && mm.risky(p.risk_eps));
 #ifndef SCALDPC_HOST_MODEL
             __syncwarp();
             if (item + nw < n_items && lane == 0) {

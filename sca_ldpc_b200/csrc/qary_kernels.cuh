@@ -53,7 +53,14 @@ struct QaryDev {
     // closer than risk_eps, or decisions that violate a parity check.
     uint32_t *risk = nullptr;
     float risk_eps = 0.0f;
+    // opt-in early termination (SCALDPC_QARY_EARLY_STOP; an extension, the reference has none: decoder_special.rs:501-504):
+    // bit l of done[tile] = trial l is FROZEN -- its hard decisions / posteriors of the iteration in which every row test
+    // first held are final and are not written again; a tile whose 32 bits are all set is skipped altogether.  null = off.
+    const uint32_t *done = nullptr;
 };
+
+// Frozen-lane helpers for the kernels (warp-uniform word, per-lane bit).
+__device__ __forceinline__ uint32_t done_word(const QaryDev &p, int tile) { return p.done ? __ldg(p.done + tile) : 0u; }
 
 // The two smallest entries of a vector (NaN = excluded = +inf).
 struct Min2 {
@@ -130,6 +137,9 @@ __global__ void __launch_bounds__(kVnWarps * 32) k_vn(const QaryDev p, const int
     const int var = blockIdx.x * kVnWarps + (threadIdx.x >> 5);
     const int tile = blockIdx.y;
     if (var >= p.bvars) return;
+    const uint32_t frozen_w = done_word(p, tile);
+    if (frozen_w == 0xffffffffu) return;  // early termination: every trial of the tile is final
+    const bool frozen = (frozen_w >> lane) & 1u;
     float *msg = p.msg + (size_t)tile * p.S * 32 + lane;
     const float *llr = p.llr + (size_t)tile * p.SL * 32 + lane;
 
@@ -167,14 +177,14 @@ __global__ void __launch_bounds__(kVnWarps * 32) k_vn(const QaryDev p, const int
                 min_val = tot[i];
                 arg = i;
             }
-        p.hard_t[((size_t)tile * p.N + var) * 32 + lane] = (int8_t)(arg - (Q - 1) / 2);
+        if (!frozen) p.hard_t[((size_t)tile * p.N + var) * 32 + lane] = (int8_t)(arg - (Q - 1) / 2);
         if (p.risk) {
             Min2 mm;
 #pragma unroll
             for (int i = 0; i < Q; ++i) mm.add(tot[i]);
-            flag_risk(p, tile, lane, mm.risky(p.risk_eps));
+            flag_risk(p, tile, lane, !frozen && mm.risky(p.risk_eps));
         }
-        if (p.post) {
+        if (p.post && !frozen) {
             float *post = p.post + (size_t)tile * p.SL * 32 + lane;
 #pragma unroll
             for (int i = 0; i < Q; ++i) post[(size_t)(var * Q + i) * 32] = tot[i];
@@ -194,6 +204,9 @@ __global__ void __launch_bounds__(kVnWarps * 32) k_vn_reg(const QaryDev p, const
     const int var = blockIdx.x * kVnWarps + (threadIdx.x >> 5);
     const int tile = blockIdx.y;
     if (var >= p.bvars) return;
+    const uint32_t frozen_w = done_word(p, tile);
+    if (frozen_w == 0xffffffffu) return;  // early termination: every trial of the tile is final
+    const bool frozen = (frozen_w >> lane) & 1u;
     float *msg = p.msg + (size_t)tile * p.S * 32 + lane;
     const float *llr = p.llr + (size_t)tile * p.SL * 32 + lane + (size_t)var * Q * 32;
     const int p0 = var * D;  // regular columns: col_ptr[var] == var * D
@@ -246,14 +259,14 @@ __global__ void __launch_bounds__(kVnWarps * 32) k_vn_reg(const QaryDev p, const
                 min_val = tot[i];
                 arg = i;
             }
-        p.hard_t[((size_t)tile * p.N + var) * 32 + lane] = (int8_t)(arg - (Q - 1) / 2);
+        if (!frozen) p.hard_t[((size_t)tile * p.N + var) * 32 + lane] = (int8_t)(arg - (Q - 1) / 2);
         if (p.risk) {
             Min2 mm;
 #pragma unroll
             for (int i = 0; i < Q; ++i) mm.add(tot[i]);
-            flag_risk(p, tile, lane, mm.risky(p.risk_eps));
+            flag_risk(p, tile, lane, !frozen && mm.risky(p.risk_eps));
         }
-        if (p.post) {
+        if (p.post && !frozen) {
             float *post = p.post + (size_t)tile * p.SL * 32 + lane;
 #pragma unroll
             for (int i = 0; i < Q; ++i) post[(size_t)(var * Q + i) * 32] = tot[i];
@@ -304,6 +317,9 @@ __global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGene
     const int check = blockIdx.x, tile = blockIdx.y;
     const int e0 = __ldg(p.row_ptr + check), L = __ldg(p.row_ptr + check + 1) - e0;
     if (L <= 0) return;
+    const uint32_t frozen_w = done_word(p, tile);
+    if (frozen_w == 0xffffffffu) return;
+    const bool frozen = (frozen_w >> lane) & 1u;
     float *msg = p.msg + (size_t)tile * p.S * 32 + lane;
     const bool special = p.BSUM > 0;
 
@@ -460,10 +476,10 @@ __global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGene
                     arg = iv;
                 }
                 mm.add(t);
-                if (post) post[(size_t)(vs * p.QS + iv) * 32] = t;
+                if (post && !frozen) post[(size_t)(vs * p.QS + iv) * 32] = t;
             }
-            p.hard_t[((size_t)tile * p.N + p.bvars + vs) * 32 + lane] = (int8_t)(arg - p.BSUM);
-            if (p.risk) flag_risk(p, tile, lane, mm.risky(p.risk_eps));
+            if (!frozen) p.hard_t[((size_t)tile * p.N + p.bvars + vs) * 32 + lane] = (int8_t)(arg - p.BSUM);
+            if (p.risk) flag_risk(p, tile, lane, !frozen && mm.risky(p.risk_eps));
         }
     }
 #undef A_
@@ -559,6 +575,7 @@ __global__ void __launch_bounds__(32) k_cn_uniform(const QaryDev p, const int LM
     const int check = blockIdx.x, tile = blockIdx.y;
     const int e0 = __ldg(p.row_ptr + check), L = __ldg(p.row_ptr + check + 1) - e0;
     if (L <= 0) return;
+    if (done_word(p, tile) == 0xffffffffu) return;
     float *msg = p.msg + (size_t)tile * p.S * 32 + lane;
     const int WP = 2 * (HH + B) + 1;  // width of a G buffer; index of partial sum u is u + HH + B
     float *sA = smem + lane;                                                     // [L-2][Q]: variables 1 .. L-2
@@ -832,6 +849,57 @@ __global__ void __launch_bounds__(256) k_qary_syndrome(const QaryDev p)
     flag_risk(p, tile, lane, s != 0);
 }
 
+// ---- early termination: close one iteration.  risk[tile] holds this iteration's verdicts (a violated row test, or a
+// posterior too close to a tie to trust); a valid, not yet frozen trial with a clean word is FROZEN now (done bit set, its
+// iteration count recorded), the others keep running.  Afterwards risk[tile] = the trials still running, which is both
+// the at-risk list of the verification (k_risk_scan) and the list a restart re-stages.  One thread per tile.
+__global__ void __launch_bounds__(256) k_qary_finish(uint32_t *__restrict__ risk, uint32_t *__restrict__ done,
+                                                     int *__restrict__ iters, int tiles, int T, int it,
+                                                     int *__restrict__ running)
+{
+    const int tile = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tile >= tiles) return;
+    const int rem = T - tile * 32;
+    const uint32_t valid = rem >= 32 ? 0xffffffffu : (rem <= 0 ? 0u : ((1u << rem) - 1u));
+    uint32_t d = done[tile];
+    uint32_t touched = ~d & valid;  // trials that ran this iteration
+    const uint32_t newly = touched & ~risk[tile];
+    while (touched) {
+#ifdef SCALDPC_HOST_MODEL
+        const int l = __builtin_ctz(touched);
+#else
+        const int l = __ffs(touched) - 1;
+#endif
+        iters[tile * 32 + l] = it;  // last iteration this trial took part in
+        touched &= touched - 1u;
+    }
+    d |= newly | ~valid;
+    done[tile] = d;
+    risk[tile] = ~d;
+    const int n = __popc(~d);
+#ifdef SCALDPC_HOST_MODEL
+    *running += n;
+#else
+    if (n) atomicAdd(running, n);
+#endif
+}
+
+// dst[map[i]] = src[i], i < n (map null: identity).
+__global__ void __launch_bounds__(256) k_scatter_int(const int *__restrict__ src, const int *__restrict__ map,
+                                                     int *__restrict__ dst, int n)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[map ? map[i] : i] = src[i];
+}
+
+// list[i] <- map[list[i]], i < *n_dev: slot indices of a round -> trial indices of the batch.
+__global__ void __launch_bounds__(256) k_compose_map(int *__restrict__ list, const int *__restrict__ map,
+                                                     const int *__restrict__ n_dev)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < *n_dev) list[i] = map[list[i]];
+}
+
 #ifndef SCALDPC_HOST_MODEL
 // Flag words -> ascending list of the flagged trials (< T) + their count, and the most severe per-trial status.
 // One CTA of 1024 threads.  out[0] = count, out[1] = min over status[0 .. T).
@@ -879,7 +947,8 @@ __global__ void __launch_bounds__(1024) k_risk_scan(const uint32_t *__restrict__
         __syncthreads();
     }
     int w = 0;
-    for (int i = tid; i < T; i += 1024) w = min(w, status[i]);
+    if (status)
+        for (int i = tid; i < T; i += 1024) w = min(w, status[i]);
 #pragma unroll
     for (int o = 16; o; o >>= 1) w = min(w, __shfl_xor_sync(0xffffffffu, w, o));
     if (lane == 0) wsum[warp] = w;

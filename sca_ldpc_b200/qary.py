@@ -146,7 +146,7 @@ class QaryDecoder:
     # batched fast path: T independent decodes resident on the device
     # ------------------------------------------------------------------------------------------------------
     def min_sum_batch(self, priors, priors_sum=None, *, llr=False, want_posterior=True, exact=False,
-                      generic=False, want_status=False, out=None, verify=True):
+                      generic=False, want_status=False, out=None, verify=True, early_stop=False):
         """Decode T trials.
 
         priors      (T, bvars, Q)  float32 probabilities (or LLRs with llr=True); numpy array or torch CUDA tensor
@@ -161,8 +161,11 @@ class QaryDecoder:
         verify (default True): the fast check node's results are verified -- trials whose decisions could depend on
         the rounding order are re-decoded with the exact-order check node (SCALDPC_NO_VERIFY in scaldpc.h), so hard
         decisions equal the reference's per trial; `last_run` tells how many were re-decoded.
+        early_stop (default False; an extension, the reference always runs every iteration): freeze every trial in
+        the iteration its decisions first satisfy all parity checks (SCALDPC_QARY_EARLY_STOP); `last_iterations(T)`
+        returns the per-trial iteration counts.
         """
-        flags = self._flags(llr, exact, generic, verify)
+        flags = self._flags(llr, exact, generic, verify, early_stop)
         on_dev = _is_torch(priors) and priors.is_cuda
         if self.special and priors_sum is None:
             raise TypeError("the special decoder needs priors_sum")
@@ -194,12 +197,12 @@ class QaryDecoder:
         return self._finish(rc, hard, post, posts, status, want_status)
 
     @staticmethod
-    def _flags(llr=False, exact=False, generic=False, verify=True):
+    def _flags(llr=False, exact=False, generic=False, verify=True, early_stop=False):
         return ((_lib.IN_LLR if llr else 0) | (_lib.CN_EXACT if exact else 0) | (_lib.CN_GENERIC if generic else 0)
-                | (0 if verify else _lib.NO_VERIFY))
+                | (0 if verify else _lib.NO_VERIFY) | (_lib.QARY_EARLY_STOP if early_stop else 0))
 
     def min_sum_observed(self, table, obs, table_sum=None, obs_sum=None, *, llr=False, want_posterior=False,
-                         exact=False, generic=False, want_status=False, out=None, verify=True):
+                         exact=False, generic=False, want_status=False, out=None, verify=True, early_stop=False):
         """Decode T trials whose priors are rows of small tables (scaldpc_qary_decode_observed): the posterior of a
         variable given the oracle's bit pattern y is `table[y]` (max_likelihood.py:87-105, kyber.py:362-376), so only
         the row indices travel.  Bit-identical to min_sum_batch(table[obs], table_sum[obs_sum]).
@@ -208,7 +211,7 @@ class QaryDecoder:
         table_sum  (n_rows_sum, QS) float32 obs_sum  (T, R) uint16            (special decoder)
         numpy in -> numpy out; torch CUDA tensors in (obs int16/uint16 storage) -> torch CUDA out.
         """
-        flags = self._flags(llr, exact, generic, verify)
+        flags = self._flags(llr, exact, generic, verify, early_stop)
         if self.special and (table_sum is None or obs_sum is None):
             raise TypeError("the special decoder needs table_sum and obs_sum")
         on_dev = _is_torch(obs) and obs.is_cuda
@@ -274,7 +277,7 @@ class QaryDecoder:
         return self._finish(rc, hard, post, posts, status, want_status)
 
     def simulate(self, T, seed, table, table_sum, code, code_sum, nbits, nbits_sum, accuracy, eta, *, first_trial=0,
-                 want_trials=False, exact=False, generic=False, verify=True):
+                 want_trials=False, exact=False, generic=False, verify=True, early_stop=False):
         """T Kyber attack-simulation trials synthesised, decoded and scored on the device (scaldpc_qary_simulate,
         SURVEY.md 8f.1): secret ~ centred binomial(eta) (kyber.py:35-47), ssum = H' s (kyber.py:85-92), every bit of
         the code word of a value observed correctly with probability `accuracy` (max_likelihood.py:9-18), priors =
@@ -292,7 +295,7 @@ class QaryDecoder:
         if code.shape != (self.Q,) or code_sum.shape != (self.QS,):
             raise ValueError(f"code must have {self.Q} entries and code_sum {self.QS}")
         T = int(T)
-        flags = self._flags(False, exact, generic, verify)
+        flags = self._flags(False, exact, generic, verify, early_stop)
         counters = np.zeros(5, np.int64)
         tr = {}
         if want_trials:
@@ -361,9 +364,15 @@ class QaryDecoder:
     @property
     def last_run(self) -> dict:
         """Trials of the last batch call and how many of them the verification re-decoded (scaldpc_qary_last_run)."""
-        t, r = C.c_longlong(), C.c_longlong()
-        _lib.check(_lib.lib().scaldpc_qary_last_run(self._h, C.byref(t), C.byref(r)))
-        return {"trials": t.value, "redecoded": r.value}
+        t, r, w = C.c_longlong(), C.c_longlong(), C.c_longlong()
+        _lib.check(_lib.lib().scaldpc_qary_last_run(self._h, C.byref(t), C.byref(r), C.byref(w)))
+        return {"trials": t.value, "redecoded": r.value, "trial_iterations": w.value}
+
+    def last_iterations(self, T: int) -> np.ndarray:
+        """Per-trial iteration counts of the last batch call, which must have used early_stop=True."""
+        out = np.empty(int(T), np.int32)
+        _lib.check(_lib.lib().scaldpc_qary_last_iterations(self._h, out.ctypes.data, int(T), 0, None))
+        return out
 
     def set_risk_margin(self, eps: float):
         _lib.check(_lib.lib().scaldpc_qary_set_risk_margin(self._h, float(eps)))

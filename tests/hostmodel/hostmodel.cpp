@@ -80,8 +80,10 @@ typedef void (*vn_fn)(const QaryDev, const int);
 
 // iteration `it` of `iters` -> kernel variant, as cn_mode_index() / cn_fast_table() in qary.cu
 template <int SW, int B>
-cn_fast_fn cn_fast_variant(int it, int iters)
+cn_fast_fn cn_fast_variant(int it, int iters, bool decide)
 {
+    if (decide)  // early termination: every iteration emits decisions, full sum-variable round trip
+        return it == 1 ? k_cn_fast<SW, B, kCnFirst | kCnLast | kCnWsum> : k_cn_fast<SW, B, kCnLast | kCnRsum | kCnWsum>;
     const bool first = it == 1, last = it == iters, penult = it == iters - 1;
     if (first)
         return last ? k_cn_fast<SW, B, kCnFirst | kCnLast>
@@ -89,10 +91,10 @@ cn_fast_fn cn_fast_variant(int it, int iters)
     return last ? k_cn_fast<SW, B, kCnLast | kCnRsum> : (penult ? k_cn_fast<SW, B, kCnWsum> : k_cn_fast<SW, B, 0>);
 }
 
-cn_fast_fn pick_cn_fast(int sw, int b, int it = 2, int iters = 4)
+cn_fast_fn pick_cn_fast(int sw, int b, int it = 2, int iters = 4, bool decide = false)
 {
 #define CASE(SW_, B_) \
-    if (sw == SW_ && b == B_) return cn_fast_variant<SW_, B_>(it, iters);
+    if (sw == SW_ && b == B_) return cn_fast_variant<SW_, B_>(it, iters, decide);
     CASE(6, 2) CASE(6, 3) CASE(4, 2) CASE(8, 2) CASE(3, 2)
 #undef CASE
     return nullptr;
@@ -134,11 +136,24 @@ vn_fn pick_vn_reg(int q, int d)
 }  // namespace
 
 static int g_last_redecoded = 0;
+static long long g_last_work = 0;
+static std::vector<int> g_last_iters;
+constexpr unsigned kHmNoRestart = 0x40000000u;  // internal: second round of early termination
+
+static int hm_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv, int dc, int max_iter, int T,
+                          const float *llr_in, const float *llr_sum_in, int8_t *hard, float *post, float *post_sum,
+                          int32_t *status, unsigned flags, int *used_fast, char *errbuf, int errlen, int *iters_out);
 
 extern "C" {
 
 // Trials the verification of the last hostmodel_qary_decode call re-decoded with the exact-order check node.
 int hostmodel_last_redecoded(void) { return g_last_redecoded; }
+// Trial-iterations the last call launched (restarts and re-decodes counted again) and its per-trial iteration counts.
+long long hostmodel_last_work(void) { return g_last_work; }
+void hostmodel_last_iterations(int32_t *out, int T)
+{
+    for (int t = 0; t < T && t < (int)g_last_iters.size(); ++t) out[t] = g_last_iters[t];
+}
 
 // sc_logf (sca_ldpc_b200/csrc/sc_logf.cuh), the device restatement of glibc's logf, evaluated on the host.
 void hostmodel_logf(const float *x, float *y, long n)
@@ -152,6 +167,19 @@ void hostmodel_logf(const float *x, float *y, long n)
 int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv, int dc, int max_iter, int T,
                           const float *llr_in, const float *llr_sum_in, int8_t *hard, float *post, float *post_sum,
                           int32_t *status, unsigned flags, int *used_fast, char *errbuf, int errlen)
+{
+    g_last_redecoded = 0;
+    g_last_work = 0;
+    g_last_iters.assign(T, 0);
+    return hm_qary_decode(H, R, N, b, bsum, dv, dc, max_iter, T, llr_in, llr_sum_in, hard, post, post_sum, status, flags,
+                          used_fast, errbuf, errlen, g_last_iters.data());
+}
+
+}  // extern "C"
+
+static int hm_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv, int dc, int max_iter, int T,
+                          const float *llr_in, const float *llr_sum_in, int8_t *hard, float *post, float *post_sum,
+                          int32_t *status, unsigned flags, int *used_fast, char *errbuf, int errlen, int *iters_out)
 {
     HostGraph g;
     std::string err;
@@ -186,12 +214,17 @@ int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
 
     const bool exact = flags & SCALDPC_CN_EXACT, force_generic = flags & SCALDPC_CN_GENERIC;
     const bool verify = !(flags & (SCALDPC_CN_EXACT | SCALDPC_NO_VERIFY));  // as decode_on_device (qary.cu)
-    std::vector<uint32_t> risk(tiles, 0u);
-    if (verify) {
+    const bool early = (flags & SCALDPC_QARY_EARLY_STOP) && !exact;
+    int restart_min = 2048;
+    if (const char *e = getenv("SCALDPC_ES_RESTART_MIN")) restart_min = std::max(1, atoi(e));
+    const bool may_restart = early && !(flags & kHmNoRestart) && T >= restart_min;
+    std::vector<uint32_t> risk(tiles, 0u), done(tiles, 0u);
+    std::vector<int> slot_iters(lanes, 0);
+    if (verify || early) {
         p.risk = risk.data();
         p.risk_eps = 1e-2f;
     }
-    if (!(flags & SCALDPC_CN_EXACT)) g_last_redecoded = 0;
+    if (early) p.done = done.data();
     cn_fast_fn fast = (!exact && !force_generic && g.regular_sw) ? pick_cn_fast(g.regular_sw, b) : nullptr;
     vn_fn vn = pick_vn(g.Q);
     if (!vn) return SCALDPC_ERR_UNSUPPORTED;
@@ -206,11 +239,14 @@ int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
     scaldpc_host_model_smem = scratch.data();
 
     const int iters = std::max(1, max_iter);
-    for (int it = 1; it <= iters; ++it) {
-        const int first = it == 1, last = it == iters;
+    int it_run = 0, running = T;
+    for (int it = 1; it <= iters && running > 0; ++it) {
+        it_run = it;
+        const int first = it == 1, last = it == iters || early;
+        if (early) std::fill(risk.begin(), risk.end(), 0u);
         if (fast) {
             // persistent kernel: a deliberately small grid, so every warp strides over several items
-            run_grid(3, 1, kCnWarps * 32, pick_cn_fast(g.regular_sw, b, it, iters), p, tiles * g.R);
+            run_grid(3, 1, kCnWarps * 32, pick_cn_fast(g.regular_sw, b, it, iters, early), p, tiles * g.R);
         } else if (exact && !force_generic && g.regular_sw && pick_cn_exact(g.regular_sw, b)) {
             // exact-order DP in registers (qary_cn_exact.cuh), as launch_cn chooses it (qary.cu)
             const int n_items = tiles * g.R;
@@ -232,8 +268,18 @@ int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
             run_grid(g.R, tiles, 32, k_cn_generic, p, a);
         }
         run_grid((g.bvars + kVnWarps - 1) / kVnWarps, tiles, kVnWarps * 32, vn, p, last);
+        if (early) {  // early_stop_round (qary.cu): row tests, freeze, count
+            run_grid((g.R + 7) / 8, tiles, 256, k_qary_syndrome, p);
+            running = 0;
+            run_grid((tiles + 255) / 256, 1, 256, k_qary_finish, risk.data(), done.data(), slot_iters.data(), tiles, T, it,
+                     &running);
+            if (may_restart && it < iters && (long long)running * 8 <= T) break;
+        }
     }
-    if (verify) run_grid((g.R + 7) / 8, tiles, 256, k_qary_syndrome, p);
+    g_last_work += (long long)T * it_run;
+    if (verify && !early) run_grid((g.R + 7) / 8, tiles, 256, k_qary_syndrome, p);
+    if (iters_out)
+        for (int t = 0; t < T; ++t) iters_out[t] = early ? slot_iters[t] : iters;
     // untile
     int worst = 0;
     for (int t = 0; t < T; ++t) {
@@ -247,12 +293,13 @@ int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
         worst = std::min(worst, st[t]);
     }
     scaldpc_host_model_smem = nullptr;
-    if (verify) {  // exact-order re-decode of the flagged trials (k_risk_scan + the second pass of decode_on_device)
+    const bool second_round = early && it_run < iters && running > 0;  // cut short: the stragglers start again, compacted
+    if (verify || second_round) {  // exact-order re-decode of the flagged trials (k_risk_scan + redecode_exact, qary.cu)
         std::vector<int> list;
         for (int t = 0; t < T; ++t)
             if ((risk[t / 32] >> (t % 32)) & 1u) list.push_back(t);
         const int nf = (int)list.size();
-        g_last_redecoded = nf;
+        if (!second_round) g_last_redecoded += nf;
         if (nf) {
             std::vector<float> l2((size_t)nf * g.SL), ls2(std::max<size_t>(1, (size_t)nf * g.SLS));
             std::vector<float> p2((size_t)nf * g.SL), ps2(std::max<size_t>(1, (size_t)nf * g.SLS));
@@ -261,9 +308,13 @@ int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
                 memcpy(&l2[(size_t)i * g.SL], llr_in + (size_t)list[i] * g.SL, sizeof(float) * g.SL);
                 if (g.SLS) memcpy(&ls2[(size_t)i * g.SLS], llr_sum_in + (size_t)list[i] * g.SLS, sizeof(float) * g.SLS);
             }
-            hostmodel_qary_decode(H, R, N, b, bsum, dv, dc, max_iter, nf, l2.data(), g.SLS ? ls2.data() : nullptr, h2.data(),
-                                  p2.data(), g.SLS ? ps2.data() : nullptr, nullptr,
-                                  (flags | SCALDPC_CN_EXACT) & ~SCALDPC_CN_GENERIC, nullptr, nullptr, 0);
+            std::vector<int> it2(nf, 0);
+            const unsigned f2 = second_round ? (flags | kHmNoRestart)
+                                             : ((flags | SCALDPC_CN_EXACT) & ~(SCALDPC_CN_GENERIC | SCALDPC_QARY_EARLY_STOP));
+            hm_qary_decode(H, R, N, b, bsum, dv, dc, max_iter, nf, l2.data(), g.SLS ? ls2.data() : nullptr, h2.data(), p2.data(),
+                           g.SLS ? ps2.data() : nullptr, nullptr, f2, nullptr, nullptr, 0, it2.data());
+            if (iters_out)
+                for (int i = 0; i < nf; ++i) iters_out[list[i]] = it2[i];
             for (int i = 0; i < nf; ++i) {
                 memcpy(hard + (size_t)list[i] * g.N, &h2[(size_t)i * g.N], g.N);
                 if (post) memcpy(post + (size_t)list[i] * g.SL, &p2[(size_t)i * g.SL], sizeof(float) * g.SL);
@@ -274,6 +325,8 @@ int hostmodel_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
     }
     return worst;
 }
+
+extern "C" {
 
 
 // Binary product-sum BP through the modelled kernels, with the host loop of scaldpc_bp_decode (bp.cu): per-trial

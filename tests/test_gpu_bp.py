@@ -114,6 +114,36 @@ def test_hqc128_full_size():
     assert w.success(batch, dec)[conv].mean() > 0.9
 
 
+@pytest.mark.parametrize("variant,R", [("hqc192", 5000), ("hqc256", 8000)])
+def test_hqc192_hqc256_full_size(variant, R):
+    """BASELINE.json configs[4] (HQC-256, n = 57637 + R) and the HQC-192 shape at the sizes bench.py quotes: six trials
+    against the fp64 oracle (decisions, iteration counts, convergence identical; posteriors within the stated tolerance),
+    one of them made undecodable so that the 100-iteration tail and the compaction around it run, then the
+    size-independent properties on the whole batch."""
+    w = HqcWorkload(variant, W=50, R=R, rho=0.9942, seed=0)
+    batch = w.generate(70, seed=1)
+    synd = batch.syndromes.copy()
+    synd[3] = np.random.RandomState(9).randint(0, 2, w.R)  # garbage check bits: never converges
+    bpd = bp_decoder(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=100, channel_probs=w.channel_probs)
+    out = bpd.decode_batch(synd, want_llr=True)
+    orc = O.BinaryBpOracle(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=100, channel_probs=w.channel_probs)
+    ref = orc.decode_batch(synd[:6])
+    assert np.array_equal(out["iters"][:6], ref["iters"]) and np.array_equal(out["converged"][:6], ref["converged"])
+    assert np.array_equal(out["decoding"][:6], ref["decoding"])
+    assert ref["iters"][3] == 100 and not ref["converged"][3]
+    for t in range(6):
+        assert util.llr_close(out["log_prob_ratios"][t], ref["log_prob_ratios"][t]), t
+    conv = out["converged"].astype(bool)
+    assert conv.mean() > 0.9 and bpd.last_run()[1] >= 1   # the running trials were compacted at least once
+    dec = out["decoding"]
+    rows = np.repeat(np.arange(w.m), np.diff(w.row_ptr))
+    for t in np.nonzero(conv)[0][:8]:
+        s = np.zeros(w.m, np.uint8)
+        np.bitwise_xor.at(s, rows, dec[t][w.col])
+        assert np.array_equal(s, synd[t])
+    assert w.success(batch, dec)[conv].mean() > 0.9
+
+
 def test_active_trial_compaction_is_transparent():
     """100 trials, five of them never converge, per-trial priors: the running trials are compacted into fewer tiles;
     outputs must be bit-identical to the run without compaction and agree with the fp64 oracle."""

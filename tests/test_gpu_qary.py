@@ -366,3 +366,61 @@ def test_concurrent_min_sum_calls_are_combined():
             assert o == ref[i].tolist(), i
     per_batch = 2 + 2 * 4 + 1  # k_load_priors x2, (check + variable pass) x4, k_untile
     assert (d.launch_count - n0) < 96 * per_batch  # fewer batches than calls: calls were combined
+
+
+def test_early_termination_small_batch_equals_model(monkeypatch):
+    """SCALDPC_QARY_EARLY_STOP (an extension; off = the reference's fixed iteration count) against the per-trial model
+    built from the oracle (tests/util.py early_stop_model): decisions, per-trial iteration counts, the re-decode of what
+    never converges; with and without the compacted second round."""
+    w = KyberWorkload("kyber768", 6, 1, accuracy=0.995, nbits=3, nbits_sum=4, seed=0)
+    T, it = 70, 7
+    b = w.generate(T, seed=1)
+    llr = np.stack([O.into_llr(x) for x in b.priors])
+    llrs = np.stack([O.into_llr(x) for x in b.priors_sum])
+    llr[5, ::2] = 0.0   # two trials that cannot converge
+    llr[40, 1::2] = 0.0
+    for restart_min in ("1", "100000"):
+        monkeypatch.setenv("SCALDPC_ES_RESTART_MIN", restart_min)
+        d = QaryDecoder(w.H, it, **w.decoder_kwargs)
+        for verify in (True, False):
+            want_h, want_it, never = util.early_stop_model(w, llr, llrs, it, verify)
+            hard, _, _ = d.min_sum_batch(llr, llrs, llr=True, early_stop=True, verify=verify)
+            assert np.array_equal(d.last_iterations(T), want_it)
+            assert np.array_equal(hard, want_h)
+            run = d.last_run
+            assert run["redecoded"] == (int(never.sum()) if verify else 0)
+            if restart_min == "1":
+                assert run["trial_iterations"] < T * it
+        # flag off: nothing changes
+        h0, _, _ = d.min_sum_batch(llr, llrs, llr=True)
+        assert d.last_run["trial_iterations"] == T * it + d.last_run["redecoded"] * it
+
+
+@pytest.mark.parametrize("variant,cb,acc,nb,nbs", [("kyber512", 1, 0.98, 4, 5), ("kyber768", 2, 0.95, 3, 4)])
+def test_early_termination_full_size(variant, cb, acc, nb, nbs):
+    """10^4 trials of the bench workloads: early termination against the fixed-iteration (reference semantics) decode.
+    Trials that never converge get the reference's result (verified mode); a frozen trial may differ only if its
+    decisions would still have moved after every row test held -- counted, and rare."""
+    w = KyberWorkload(variant, 6, cb, accuracy=acc, nbits=nb, nbits_sum=nbs, seed=0)
+    T = 10_000
+    b = w.generate(T, seed=1)
+    d = QaryDecoder(w.H, 10, **w.decoder_kwargs)
+    ref, _, _ = d.min_sum_batch(b.priors, b.priors_sum, want_posterior=False)
+    hard, _, _ = d.min_sum_batch(b.priors, b.priors_sum, want_posterior=False, early_stop=True)
+    its = d.last_iterations(T)
+    run = d.last_run
+    differ = (hard != ref).any(1)
+    assert differ.sum() <= T // 100, int(differ.sum())
+    assert not differ[its == 10].any()          # ran to the cap: re-decoded like the fixed-iteration path does
+    synd = hard[its < 10].astype(np.int32) @ w.H.T.astype(np.int32)
+    assert (synd == 0).all()                    # frozen trials satisfy every row
+    assert 1 <= its.min() and its.max() == 10 and its.mean() < 6
+    assert run["trial_iterations"] < 0.75 * T * 10
+    assert np.array_equal(w.success(b, hard)[~differ], w.success(b, ref)[~differ])
+    # observation-indexed priors and the on-device Monte-Carlo loop take the same flag
+    ob = w.generate_observed(2048, seed=1)
+    oh, _, _ = d.min_sum_observed(w.table, ob.obs, w.table_sum, ob.obs_sum, early_stop=True)
+    assert np.array_equal(oh, hard[:2048])
+    sim_a = d.simulate(4096, 7, **w.simulate_kwargs)
+    sim_b = d.simulate(4096, 7, early_stop=True, **w.simulate_kwargs)
+    assert abs(sim_a["successes"] - sim_b["successes"]) <= 41

@@ -214,3 +214,33 @@ def test_no_config_status():
     with pytest.raises(O.OracleError) as e:
         O.QaryOracle(H, 2, B=1).decode_llr(llr[1])
     assert e.value.code == -4
+
+
+@pytest.mark.parametrize("restart_min", ["1", "100000"])
+def test_early_termination_rounds(monkeypatch, restart_min):
+    """SCALDPC_QARY_EARLY_STOP through the modelled kernels (frozen lanes, skipped tiles, the compacted second round when
+    at most 1/8 is still running, exact-order decode of what never converges) == the per-trial model above."""
+    from sca_ldpc_b200.workloads import KyberWorkload
+
+    monkeypatch.setenv("SCALDPC_ES_RESTART_MIN", restart_min)
+    w = KyberWorkload("kyber768", 6, 1, accuracy=0.995, nbits=3, nbits_sum=4, seed=0)
+    T, it = 70, 7
+    b = w.generate(T, seed=1)
+    llr = np.stack([O.into_llr(x) for x in b.priors])
+    llrs = np.stack([O.into_llr(x) for x in b.priors_sum])
+    # two trials that cannot converge: the information of half of their variables is wiped out
+    llr[5, ::2] = 0.0
+    llr[40, 1::2] = 0.0
+    for verify in (True, False):
+        want_h, want_it, never = util.early_stop_model(w, llr, llrs, it, verify)
+        assert never.sum() >= 2 and (want_it < it).sum() > T // 2
+        flags = _lib.QARY_EARLY_STOP | (0 if verify else NO_VERIFY)
+        rc, hard, post, posts, _, fast = util.hostmodel_qary(w.H, w.B, w.BSUM, it, llr, llrs, flags=flags, dc=7)
+        got_it = util.hostmodel_last_iterations(T)
+        assert rc == 0 and fast
+        assert np.array_equal(got_it, want_it)
+        assert np.array_equal(hard, want_h)
+        assert util.hostmodel().hostmodel_last_redecoded() == (int(never.sum()) if verify else 0)
+        # slot-iterations launched: the compacted second round makes it fewer than the fixed-iteration decode's T * it
+        work = util.hostmodel_last_work()
+        assert work < T * it if restart_min == "1" else work == T * it + (never.sum() * it if verify else 0)

@@ -82,6 +82,18 @@ def hostmodel_qary(H, b, bsum, max_iter, llr, llr_sum=None, flags=0, dv=0, dc=0)
     return rc, hard, post, posts, status, bool(used.value)
 
 
+def hostmodel_last_iterations(T):
+    out = np.zeros(T, np.int32)
+    hostmodel().hostmodel_last_iterations(out.ctypes.data_as(C.c_void_p), int(T))
+    return out
+
+
+def hostmodel_last_work():
+    L = hostmodel()
+    L.hostmodel_last_work.restype = C.c_longlong
+    return int(L.hostmodel_last_work())
+
+
 def hostmodel_bp(row_ptr, col, m, n, max_iter, synd, probs, early_stop=True, want_llr=True, compact=True):
     """Run the binary-BP kernels' logic on the host.  Returns dict(decoding, llr, iters, converged)."""
     L = hostmodel()
@@ -112,3 +124,37 @@ def llr_close(a, b, atol=2e-3, rtol=2e-4):
     if not np.array_equal(np.isposinf(a), np.isposinf(b)) or not np.array_equal(np.isneginf(a), np.isneginf(b)):
         return False
     return bool(np.all(np.abs(a[fin] - b[fin]) <= atol + rtol * np.abs(b[fin])))
+
+
+def early_stop_model(w, llr, llrs, iters, verify, eps=1e-2):
+    """Per-trial early termination restated with the oracle: plain forward/backward flooding (algo 2); the trial stops in
+    the first iteration whose hard decisions satisfy every row and whose posteriors are clear of ties; a trial that never
+    does gets the reference's fixed-iteration decode (exact-order) in verified mode, else its last decisions."""
+    T = llr.shape[0]
+    Hs = w.H.astype(np.int32)
+    hard = np.zeros((T, w.N), np.int8)
+    its = np.zeros(T, np.int32)
+    open_ = np.ones(T, bool)
+
+    def margin(p):
+        q = np.sort(np.where(np.isnan(p), np.inf, p), axis=-1)
+        with np.errstate(invalid="ignore"):
+            m = q[..., 1] - q[..., 0]
+        return np.where(np.isnan(m), -1.0, m).min(axis=1)
+
+    from oracle import oracle as O
+
+    for k in range(1, iters + 1):
+        d = O.QaryOracle(w.H, k, B=w.B, BSUM=w.BSUM, DC=w.sum_weight + 1)
+        h, p, ps, _ = d.decode_batch(llr, llrs, from_probs=False, algo=O.ALGO_FWD_BWD)
+        ok = ((h.astype(np.int32) @ Hs.T) == 0).all(1) & (np.minimum(margin(p), margin(ps)) > eps)
+        newly = open_ & ok
+        hard[newly], its[newly] = h[newly], k
+        open_ &= ~ok
+        if k == iters:
+            hard[open_], its[open_] = h[open_], k
+    if verify and open_.any():
+        d = O.QaryOracle(w.H, iters, B=w.B, BSUM=w.BSUM, DC=w.sum_weight + 1)
+        h, _, _, _ = d.decode_batch(llr[open_], llrs[open_], from_probs=False, algo=O.ALGO_EXACT_DP)
+        hard[open_] = h
+    return hard, its, open_
