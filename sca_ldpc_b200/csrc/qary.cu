@@ -60,8 +60,14 @@ struct scaldpc_qary {
     // at-risk detection + exact-order re-decode of the fast path
     uint32_t *d_risk = nullptr;   // [tiles] flag words
     int *d_risk_list = nullptr;   // [tiles*32] flagged trial indices, ascending
-    int *d_scan_out = nullptr;    // {count, worst status}
-    int *h_scan_out = nullptr;    // pinned mirror
+    int *d_scan_out = nullptr;    // {count, worst status, list offset} of the last scan; [4..5] = call-wide {count, worst}
+    int *h_scan_out = nullptr;    // pinned mirror (6 ints)
+    int *d_glist = nullptr;       // flagged trials of the whole call (batch-wide indices), re-decoded once at the end
+    size_t cap_glist = 0;
+    // host pipeline: priors of the flagged trials, put aside before their chunk's staging buffer is reused
+    size_t cap_retry = 0;         // rows
+    float *d_retry_in = nullptr, *d_retry_in_sum = nullptr;
+    uint16_t *d_retry_obs = nullptr, *d_retry_obs_sum = nullptr;
     float risk_eps = 1e-2f;
     long long last_trials = 0, last_redecoded = 0;  // of the last decode / simulate call
     long long last_work = 0;      // trial-iterations launched by the last call (restarts and re-decodes included)
@@ -221,8 +227,8 @@ int ensure_workspace(scaldpc_qary *h, int tiles, bool want_post)
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_done, (size_t)t * sizeof(uint32_t)));
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_iters, lanes * sizeof(int)));
     if (!h->d_scan_out) {
-        SCALDPC_CUDA(cudaMalloc((void **)&h->d_scan_out, 2 * sizeof(int)));
-        SCALDPC_CUDA(cudaHostAlloc((void **)&h->h_scan_out, 2 * sizeof(int), cudaHostAllocDefault));
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_scan_out, 8 * sizeof(int)));
+        SCALDPC_CUDA(cudaHostAlloc((void **)&h->h_scan_out, 8 * sizeof(int), cudaHostAllocDefault));
     }
     h->cap_tiles = t;
     h->cap_post = post;
@@ -302,6 +308,28 @@ int ensure_stage_observed(scaldpc_qary *h, size_t chunk)
         SCALDPC_CUDA(cudaMalloc((void **)&h->d_obs_sum[i], std::max<size_t>(1, chunk * h->R) * sizeof(uint16_t)));
     }
     h->cap_obs_T = chunk;
+    return 0;
+}
+
+// Host pipeline: room for the priors of `rows` flagged trials (see finish_verify).
+int ensure_retry(scaldpc_qary *h, size_t rows, bool observed)
+{
+    const bool have = observed ? h->d_retry_obs != nullptr : h->d_retry_in != nullptr;
+    if (rows <= h->cap_retry && have) return 0;
+    const size_t r = std::max(rows, h->cap_retry);
+    cudaFree(h->d_retry_in);
+    cudaFree(h->d_retry_in_sum);
+    cudaFree(h->d_retry_obs);
+    cudaFree(h->d_retry_obs_sum);
+    h->d_retry_in = h->d_retry_in_sum = nullptr;
+    h->d_retry_obs = h->d_retry_obs_sum = nullptr;
+    h->cap_retry = 0;
+    // both kinds are (re)allocated together so that cap_retry describes every buffer that exists
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_retry_in, r * h->SL * sizeof(float)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_retry_in_sum, std::max<size_t>(1, r * h->SLS) * sizeof(float)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_retry_obs, r * h->bvars * sizeof(uint16_t)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_retry_obs_sum, std::max<size_t>(1, r * h->R) * sizeof(uint16_t)));
+    h->cap_retry = r;
     return 0;
 }
 
@@ -657,6 +685,11 @@ void scaldpc_qary_destroy(scaldpc_qary *h)
     free_sim(h);
     cudaFree(h->d_status_all);
     cudaFree(h->d_scan_out);
+    cudaFree(h->d_glist);
+    cudaFree(h->d_retry_in);
+    cudaFree(h->d_retry_in_sum);
+    cudaFree(h->d_retry_obs);
+    cudaFree(h->d_retry_obs_sum);
     cudaFree(h->d_iters_all);
     if (h->h_scan_out) cudaFreeHost(h->h_scan_out);
     if (h->s_in) cudaStreamDestroy(h->s_in);
@@ -812,7 +845,7 @@ static int emit_outputs(scaldpc_qary *h, int T, const int *map, int8_t *dhard, f
 // status of slots 0 .. n-1).  Synchronises `st`.
 static int scan_flags(scaldpc_qary *h, int n, const int *status, int *list, cudaStream_t st, int *count, int *worst)
 {
-    k_risk_scan<<<1, 1024, 0, st>>>(h->d_risk, (n + 31) / 32, n, status, list, h->d_scan_out);
+    k_risk_scan<<<1, 1024, 0, st>>>(h->d_risk, (n + 31) / 32, n, status, list, h->d_scan_out, nullptr, nullptr, 0);
     ++h->launches;
     SCALDPC_CUDA(cudaGetLastError());
     SCALDPC_CUDA(cudaMemcpyAsync(h->h_scan_out, h->d_scan_out, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -825,7 +858,7 @@ static int scan_flags(scaldpc_qary *h, int n, const int *status, int *list, cuda
 // Exact-order decode (the reference's arithmetic, fixed iteration count) of the `nf` trials listed in `list`, staged
 // compactly into the leading tiles of the workspace; their outputs overwrite rows list[i] of the caller's arrays.
 static int redecode_exact(scaldpc_qary *h, int nf, const int *list, const PriorSrc &src, int8_t *dhard, float *dpost,
-                          float *dpost_sum, unsigned flags, cudaStream_t st)
+                          float *dpost_sum, unsigned flags, cudaStream_t st, const int *out_list)
 {
     const bool want_post = dpost != nullptr || dpost_sum != nullptr;
     int rc;
@@ -836,7 +869,7 @@ static int redecode_exact(scaldpc_qary *h, int nf, const int *list, const PriorS
     p2.status = h->d_status + (size_t)h->cap_tiles * 32;  // scratch: the fast pass has already recorded every status
     const unsigned f2 = (flags | SCALDPC_CN_EXACT) & ~(SCALDPC_CN_GENERIC | SCALDPC_QARY_EARLY_STOP);
     if ((rc = run_iterations(h, p2, (nf + 31) / 32, f2, st))) return rc;
-    return emit_outputs(h, nf, list, dhard, dpost, dpost_sum, st);
+    return emit_outputs(h, nf, out_list, dhard, dpost, dpost_sum, st);
 }
 
 // One round of early termination over the `n` trials staged in the workspace: after every iteration each trial whose
@@ -893,7 +926,7 @@ static int early_stop_round(scaldpc_qary *h, int n, bool want_post, unsigned fla
 // mode -- is decoded once more with the exact-order check node and the reference's fixed iteration count.
 // `iters_out` (device, may be null): per-trial iteration counts.
 static int decode_on_device(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *dhard, float *dpost, float *dpost_sum,
-                            unsigned flags, cudaStream_t st, int *worst, int *iters_out)
+                            unsigned flags, cudaStream_t st, int *worst, int *iters_out, int base, bool stash)
 {
     const bool want_post = dpost != nullptr || dpost_sum != nullptr;
     const bool exact = flags & SCALDPC_CN_EXACT;
@@ -933,11 +966,11 @@ static int decode_on_device(scaldpc_qary *h, int T, const PriorSrc &src, int8_t 
                 k_compose_map<<<(nf + 255) / 256, 256, 0, st>>>(list_b, list_a, h->d_scan_out);
                 ++h->launches;
                 SCALDPC_CUDA(cudaGetLastError());
-                if (nf > 0) return redecode_exact(h, nf, list_b, src, dhard, dpost, dpost_sum, flags, st);
+                if (nf > 0) return redecode_exact(h, nf, list_b, src, dhard, dpost, dpost_sum, flags, st, list_b);
             }
             return 0;
         }
-        if (nf > 0 && verify) return redecode_exact(h, nf, list_a, src, dhard, dpost, dpost_sum, flags, st);
+        if (nf > 0 && verify) return redecode_exact(h, nf, list_a, src, dhard, dpost, dpost_sum, flags, st, list_a);
         return 0;
     }
 
@@ -955,10 +988,125 @@ static int decode_on_device(scaldpc_qary *h, int T, const PriorSrc &src, int8_t 
     }
     if ((rc = emit_outputs(h, T, nullptr, dhard, dpost, dpost_sum, st))) return rc;
     if (!verify) return 0;
-    int nf = 0;
-    if ((rc = scan_flags(h, T, h->d_status, list_a, st, &nf, worst))) return rc;
-    if (nf <= 0) return 0;
-    return redecode_exact(h, nf, list_a, src, dhard, dpost, dpost_sum, flags, st);
+    // The flagged trials join the call-wide list (no synchronisation here); finish_verify() decodes them again, once, after
+    // the last chunk / pass -- a re-decode per chunk costs its fixed latency (~0.3 ms of small launches) every time.
+    k_risk_scan<<<1, 1024, 0, st>>>(h->d_risk, tiles, T, h->d_status, list_a, h->d_scan_out, h->d_glist, h->d_scan_out + 4,
+                                    base);
+    ++h->launches;
+    if (stash) {  // host pipeline: the staging buffer holding these priors is about to be overwritten
+        const int grid = std::min(T, 512);
+        if (src.observed) {
+            k_gather_rows<uint16_t><<<grid, 256, 0, st>>>(src.obs, h->d_retry_obs, list_a, h->d_scan_out, h->bvars, (int)h->cap_retry);
+            if (h->BSUM > 0)
+                k_gather_rows<uint16_t><<<grid, 256, 0, st>>>(src.obs_sum, h->d_retry_obs_sum, list_a, h->d_scan_out, h->R, (int)h->cap_retry);
+        } else {
+            k_gather_rows<float><<<grid, 256, 0, st>>>(src.in, h->d_retry_in, list_a, h->d_scan_out, h->SL, (int)h->cap_retry);
+            if (h->BSUM > 0)
+                k_gather_rows<float><<<grid, 256, 0, st>>>(src.in_sum, h->d_retry_in_sum, list_a, h->d_scan_out, h->SLS, (int)h->cap_retry);
+        }
+        h->launches += h->BSUM > 0 ? 2 : 1;
+    }
+    SCALDPC_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// Start of a call: the call-wide list of flagged trials is empty.
+static int begin_verify(scaldpc_qary *h, int T, cudaStream_t st)
+{
+    if ((size_t)T > h->cap_glist) {
+        cudaFree(h->d_glist);
+        h->d_glist = nullptr;
+        h->cap_glist = 0;
+        SCALDPC_CUDA(cudaMalloc((void **)&h->d_glist, (size_t)T * sizeof(int)));
+        h->cap_glist = (size_t)T;
+    }
+    SCALDPC_CUDA(cudaMemsetAsync(h->d_scan_out + 4, 0, 2 * sizeof(int), st));
+    return 0;
+}
+
+// End of a call (default, verified mode): ONE synchronisation to learn how many trials the chunks / passes flagged, then
+// their exact-order re-decode.  Device mode: priors are read from the caller's arrays `src` through the
+// list, results are written to rows list[i] of the caller's device arrays.  Host mode (`host` = the caller's HOST arrays,
+// src = null): the first cap_retry flagged trials' priors were put aside on the device by decode_on_device(stash), the
+// others are uploaded again; results come back through the output staging buffers and are scattered on the host.
+static int finish_verify(scaldpc_qary *h, const PriorSrc *src, const PriorSrc *host, int8_t *hard, float *post,
+                         float *post_sum, unsigned flags, cudaStream_t st, int *worst)
+{
+    int rc;
+    SCALDPC_CUDA(cudaMemcpyAsync(h->h_scan_out + 4, h->d_scan_out + 4, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    SCALDPC_CUDA(cudaStreamSynchronize(st));
+    const int count = h->h_scan_out[4];
+    if (worst) *worst = std::min(*worst, h->h_scan_out[5]);
+    if (count <= 0) return 0;
+    const int room = h->cap_tiles * 32;  // trials the workspace holds
+    if (src) {
+        for (int o = 0; o < count; o += room) {
+            const int nb = std::min(room, count - o);
+            if ((rc = redecode_exact(h, nb, h->d_glist + o, *src, hard, post, post_sum, flags, st, h->d_glist + o))) return rc;
+        }
+        return 0;
+    }
+    // ---- host mode
+    const bool special = h->BSUM > 0;
+    std::vector<int> hl(count);
+    SCALDPC_CUDA(cudaMemcpy(hl.data(), h->d_glist, (size_t)count * sizeof(int), cudaMemcpyDeviceToHost));
+    const int cap = (int)std::min<size_t>(h->cap_retry, std::min<size_t>((size_t)room, h->cap_stage_T));
+    std::vector<int8_t> th;
+    std::vector<float> tp, tps;
+    for (int o = 0; o < count;) {
+        const int resident = (int)std::min<size_t>((size_t)count, h->cap_retry);  // rows 0 .. resident-1 are on the device
+        int nb, first_row;
+        if (o < resident) {  // a batch of resident rows, read in place
+            nb = std::min(cap, resident - o);
+            first_row = o;
+        } else {  // not resident (more flagged trials than the retry buffers hold): upload them again, row by row
+            nb = std::min(cap, count - o);
+            first_row = 0;
+            for (int i = 0; i < nb; ++i) {
+                const size_t t = (size_t)hl[o + i];
+                if (host->observed) {
+                    SCALDPC_CUDA(cudaMemcpyAsync(h->d_retry_obs + (size_t)i * h->bvars, host->obs + t * h->bvars,
+                                                 (size_t)h->bvars * sizeof(uint16_t), cudaMemcpyHostToDevice, st));
+                    if (special)
+                        SCALDPC_CUDA(cudaMemcpyAsync(h->d_retry_obs_sum + (size_t)i * h->R, host->obs_sum + t * h->R,
+                                                     (size_t)h->R * sizeof(uint16_t), cudaMemcpyHostToDevice, st));
+                } else {
+                    SCALDPC_CUDA(cudaMemcpyAsync(h->d_retry_in + (size_t)i * h->SL, host->in + t * h->SL,
+                                                 (size_t)h->SL * sizeof(float), cudaMemcpyHostToDevice, st));
+                    if (special)
+                        SCALDPC_CUDA(cudaMemcpyAsync(h->d_retry_in_sum + (size_t)i * h->SLS, host->in_sum + t * h->SLS,
+                                                     (size_t)h->SLS * sizeof(float), cudaMemcpyHostToDevice, st));
+                }
+            }
+        }
+        PriorSrc rs = *host;
+        rs.in = h->d_retry_in ? h->d_retry_in + (size_t)first_row * h->SL : nullptr;
+        rs.in_sum = h->d_retry_in_sum ? h->d_retry_in_sum + (size_t)first_row * h->SLS : nullptr;
+        rs.obs = h->d_retry_obs ? h->d_retry_obs + (size_t)first_row * h->bvars : nullptr;
+        rs.obs_sum = h->d_retry_obs_sum ? h->d_retry_obs_sum + (size_t)first_row * h->R : nullptr;
+        if ((rc = redecode_exact(h, nb, nullptr, rs, h->d_ohard[0], post ? h->d_opost[0] : nullptr,
+                                 (post_sum && special) ? h->d_opost_sum[0] : nullptr, flags, st, nullptr)))
+            return rc;
+        th.resize((size_t)nb * h->N);
+        SCALDPC_CUDA(cudaMemcpyAsync(th.data(), h->d_ohard[0], th.size(), cudaMemcpyDeviceToHost, st));
+        if (post) {
+            tp.resize((size_t)nb * h->SL);
+            SCALDPC_CUDA(cudaMemcpyAsync(tp.data(), h->d_opost[0], tp.size() * sizeof(float), cudaMemcpyDeviceToHost, st));
+        }
+        if (post_sum && special) {
+            tps.resize((size_t)nb * h->SLS);
+            SCALDPC_CUDA(cudaMemcpyAsync(tps.data(), h->d_opost_sum[0], tps.size() * sizeof(float), cudaMemcpyDeviceToHost, st));
+        }
+        SCALDPC_CUDA(cudaStreamSynchronize(st));
+        for (int i = 0; i < nb; ++i) {
+            const size_t t = (size_t)hl[o + i];
+            memcpy(hard + t * h->N, th.data() + (size_t)i * h->N, (size_t)h->N);
+            if (post) memcpy(post + t * h->SL, tp.data() + (size_t)i * h->SL, (size_t)h->SL * sizeof(float));
+            if (post_sum && special) memcpy(post_sum + t * h->SLS, tps.data() + (size_t)i * h->SLS, (size_t)h->SLS * sizeof(float));
+        }
+        o += nb;
+    }
+    return 0;
 }
 
 // Shared body of scaldpc_qary_decode / scaldpc_qary_decode_observed.  `src` holds the caller's pointers (host or
@@ -985,9 +1133,14 @@ static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *har
         h->cap_iters_T = 0;
     }
 
-    if (dev_ptrs) {  // asynchronous on `st` (one synchronisation per pass unless SCALDPC_NO_VERIFY); at most `max_resident` trials' messages live in the workspace at a time
+    // default (verified) mode without early termination: the chunks / passes only LIST their at-risk trials, the exact
+    // re-decode runs once at the end of the call (finish_verify)
+    const bool deferred = !(flags & (SCALDPC_CN_EXACT | SCALDPC_NO_VERIFY | SCALDPC_QARY_EARLY_STOP));
+
+    if (dev_ptrs) {  // asynchronous on `st` (one synchronisation per call unless SCALDPC_NO_VERIFY); at most `max_resident` trials' messages live in the workspace at a time
         const int cap = std::max(32, h->max_resident / 32 * 32);
         if ((rc = ensure_workspace(h, (std::min(T, cap) + 31) / 32, want_post))) return rc;
+        if (deferred && (rc = begin_verify(h, T, st))) return rc;
         for (int t0 = 0; t0 < T; t0 += cap) {
             const int tc = std::min(cap, T - t0);
             PriorSrc part = src;
@@ -1001,12 +1154,13 @@ static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *har
             int w = 0;
             if ((rc = decode_on_device(h, tc, part, hard + (size_t)t0 * h->N, post ? post + (size_t)t0 * h->SL : nullptr,
                                        post_sum ? post_sum + (size_t)t0 * h->SLS : nullptr, flags, st, &w,
-                                       h->d_iters_all ? h->d_iters_all + t0 : nullptr)))
+                                       h->d_iters_all ? h->d_iters_all + t0 : nullptr, t0, false)))
                 return rc;
             worst = std::min(worst, w);
             if (status)
                 SCALDPC_CUDA(cudaMemcpyAsync(status + t0, h->d_status, (size_t)tc * sizeof(int), cudaMemcpyDeviceToDevice, st));
         }
+        if (deferred && (rc = finish_verify(h, &src, nullptr, hard, post, post_sum, flags, st, &worst))) return rc;
         return status_error(worst);
     }
 
@@ -1022,6 +1176,7 @@ static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *har
     if ((rc = ensure_workspace(h, chunk / 32, want_post))) return rc;
     if ((rc = ensure_pipeline(h, (size_t)chunk, (size_t)T, want_post))) return rc;
     if ((rc = src.observed ? ensure_stage_observed(h, (size_t)chunk) : ensure_stage_priors(h, (size_t)chunk))) return rc;
+    if (deferred && ((rc = ensure_retry(h, (size_t)chunk, src.observed)) || (rc = begin_verify(h, T, st)))) return rc;
     // Host-side enqueue order per chunk c: H2D(c+1), decode(c), D2H(c-1).  A D2H into pageable memory blocks the
     // host until decode(c-1) is done; by then decode(c) and H2D(c+1) are already queued, so the device never idles.
     auto h2d = [&](int c) -> int {
@@ -1069,7 +1224,7 @@ static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *har
         dsrc.obs_sum = h->d_obs_sum[b];
         if ((rc = decode_on_device(h, tc, dsrc, h->d_ohard[b], post ? h->d_opost[b] : nullptr,
                                    post_sum ? h->d_opost_sum[b] : nullptr, flags, st, nullptr,
-                                   h->d_iters_all ? h->d_iters_all + t0 : nullptr)))
+                                   h->d_iters_all ? h->d_iters_all + t0 : nullptr, t0, deferred)))
             return rc;
         SCALDPC_CUDA(cudaMemcpyAsync(h->d_status_all + t0, h->d_status, (size_t)tc * sizeof(int), cudaMemcpyDeviceToDevice, st));
         SCALDPC_CUDA(cudaEventRecord(h->ev_comp[b], st));
@@ -1082,6 +1237,8 @@ static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *har
     SCALDPC_CUDA(cudaStreamSynchronize(h->s_out));
     for (int t = 0; t < T; ++t) worst = std::min(worst, hs[t]);
     if (status) memcpy(status, hs.data(), (size_t)T * sizeof(int));
+    // every chunk's fast results are in the caller's arrays; the flagged trials' exact-order results overwrite theirs
+    if (deferred && (rc = finish_verify(h, nullptr, &src, hard, post, post_sum, flags, st, nullptr))) return rc;
     return status_error(worst);
 }
 
@@ -1210,7 +1367,10 @@ int scaldpc_qary_simulate(scaldpc_qary *h, int T, uint64_t seed, uint64_t first_
                                         (int *)(h->d_sim_cnt + 5), tc);
         h->launches += 2;
         SCALDPC_CUDA(cudaGetLastError());
-        if ((rc = decode_on_device(h, tc, src, h->d_sim_hard, nullptr, nullptr, flags, st, nullptr, nullptr))) return rc;
+        const bool deferred = !(flags & (SCALDPC_CN_EXACT | SCALDPC_NO_VERIFY | SCALDPC_QARY_EARLY_STOP));
+        if (deferred && (rc = begin_verify(h, tc, st))) return rc;
+        if ((rc = decode_on_device(h, tc, src, h->d_sim_hard, nullptr, nullptr, flags, st, nullptr, nullptr, 0, false))) return rc;
+        if (deferred && (rc = finish_verify(h, &src, nullptr, h->d_sim_hard, nullptr, nullptr, flags, st, nullptr))) return rc;
         k_sim_count<<<grid, 256, 0, st>>>(h->d_sim_hard, h->d_sim_secret, h->d_sim_ssum, h->d_sim_cnt, tc, h->N, h->bvars);
         ++h->launches;
         SCALDPC_CUDA(cudaGetLastError());

@@ -902,11 +902,15 @@ __global__ void __launch_bounds__(256) k_compose_map(int *__restrict__ list, con
 
 #ifndef SCALDPC_HOST_MODEL
 // Flag words -> ascending list of the flagged trials (< T) + their count, and the most severe per-trial status.
-// One CTA of 1024 threads.  out[0] = count, out[1] = min over status[0 .. T).
+// One CTA of 1024 threads.  out[0] = count, out[1] = min over status[0 .. T), out[2] = gstate[0] before this call.
+// With `glist` / `gstate` the flagged trials are also APPENDED, as batch-wide indices `base + t`, to the list of the
+// whole call: gstate[0] = entries so far, gstate[1] = most severe status so far.  Calls are serialised by the stream.
 __global__ void __launch_bounds__(1024) k_risk_scan(const uint32_t *__restrict__ risk, int tiles, int T,
                                                     const int *__restrict__ status, int *__restrict__ list,
-                                                    int *__restrict__ out)
+                                                    int *__restrict__ out, int *__restrict__ glist,
+                                                    int *__restrict__ gstate, int base)
 {
+    const int gold = gstate ? gstate[0] : 0;
     __shared__ int wsum[32];
     __shared__ int s_base;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -939,7 +943,9 @@ __global__ void __launch_bounds__(1024) k_risk_scan(const uint32_t *__restrict__
         int pos = s_base + (warp ? wsum[warp - 1] : 0) + incl - c;
         while (word) {
             const int b = __ffs(word) - 1;
-            list[pos++] = tile * 32 + b;
+            list[pos] = tile * 32 + b;
+            if (glist) glist[gold + pos] = base + tile * 32 + b;
+            ++pos;
             word &= word - 1u;
         }
         __syncthreads();
@@ -957,6 +963,27 @@ __global__ void __launch_bounds__(1024) k_risk_scan(const uint32_t *__restrict__
         for (int i = 1; i < 32; ++i) w = min(w, wsum[i]);
         out[0] = s_base;
         out[1] = w;
+        out[2] = gold;
+        if (gstate) {
+            gstate[0] = gold + s_base;
+            gstate[1] = min(gstate[1], w);
+        }
+    }
+}
+
+// Rows list[i] (i < scan[0]) of src [.][n] -> rows scan[2] + i of dst, as long as they fit (< cap): the priors of a
+// chunk's flagged trials are put aside before the chunk's staging buffer is overwritten.  One CTA per row (grid-stride).
+template <typename T_>
+__global__ void __launch_bounds__(256) k_gather_rows(const T_ *__restrict__ src, T_ *__restrict__ dst,
+                                                     const int *__restrict__ list, const int *__restrict__ scan, int n,
+                                                     int cap)
+{
+    const int count = scan[0], off = scan[2];
+    for (int i = blockIdx.x; i < count; i += gridDim.x) {
+        if (off + i >= cap) return;
+        const T_ *s_ = src + (size_t)list[i] * n;
+        T_ *d_ = dst + (size_t)(off + i) * n;
+        for (int k = threadIdx.x; k < n; k += blockDim.x) d_[k] = s_[k];
     }
 }
 #endif

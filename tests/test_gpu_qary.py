@@ -424,3 +424,32 @@ def test_early_termination_full_size(variant, cb, acc, nb, nbs):
     sim_a = d.simulate(4096, 7, **w.simulate_kwargs)
     sim_b = d.simulate(4096, 7, early_stop=True, **w.simulate_kwargs)
     assert abs(sim_a["successes"] - sim_b["successes"]) <= 41
+
+
+def test_host_pipeline_deferred_redecode_and_overflow():
+    """Host buffers, chunked pipeline (T >= 4096): the chunks only list their at-risk trials and put their priors aside, the
+    exact-order re-decode runs once at the end.  An undecodable workload flags (almost) every trial, far more than the
+    retry buffers hold, so the overflow path (priors uploaded again) runs too.  Results must equal the exact-order decode
+    of the whole batch, the device-pointer path, and the observation-indexed path."""
+    import torch
+
+    w = KyberWorkload("kyber1024", sum_weight=4, check_blocks=1, accuracy=0.9, nbits=4, nbits_sum=5, seed=1)
+    T = 4200
+    b = w.generate(T, seed=3)
+    d = QaryDecoder(w.H, 3, **w.decoder_kwargs)
+    eh, ep, eps_ = d.min_sum_batch(b.priors, b.priors_sum, exact=True)
+    hard, post, posts = d.min_sum_batch(b.priors, b.priors_sum)
+    run = d.last_run
+    assert run["trials"] == T and run["redecoded"] > 2048   # more than two chunks' worth of flagged trials
+    assert np.array_equal(hard, eh)
+    assert util.same_nonfinite(post, ep) and util.max_abs_diff(post, ep) < TOL
+    assert util.same_nonfinite(posts, eps_) and util.max_abs_diff(posts, eps_) < TOL
+    th, tp, tps = d.min_sum_batch(torch.from_numpy(b.priors).cuda(), torch.from_numpy(b.priors_sum).cuda())
+    torch.cuda.synchronize()
+    assert d.last_run["redecoded"] == run["redecoded"]
+    assert np.array_equal(th.cpu().numpy(), hard) and np.array_equal(tp.cpu().numpy(), post, equal_nan=True)
+    assert np.array_equal(tps.cpu().numpy(), posts, equal_nan=True)
+    ob = w.generate_observed(T, seed=3)
+    oh, op, ops = d.min_sum_observed(w.table, ob.obs, w.table_sum, ob.obs_sum, want_posterior=True)
+    assert d.last_run["redecoded"] == run["redecoded"]
+    assert np.array_equal(oh, hard) and np.array_equal(op, post, equal_nan=True) and np.array_equal(ops, posts, equal_nan=True)
