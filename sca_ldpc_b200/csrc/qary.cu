@@ -4,8 +4,10 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <memory>
 #include <mutex>
+#include <tuple>
 #include <vector>
 
 #include "common.h"
@@ -97,6 +99,14 @@ struct scaldpc_qary {
     int16_t *d_sim_ssum = nullptr;
     uint16_t *d_sim_code = nullptr, *d_sim_code_sum = nullptr;
     unsigned long long *d_sim_cnt = nullptr;
+    // reference-shaped single calls (host buffers, T <= 32 = one tile): the whole decode -- copies in, ~25 launches,
+    // copies out -- is ONE CUDA graph per (T, iterations, flags, posteriors wanted), replayed on an internal stream
+    std::map<std::tuple<int, int, unsigned, int>, std::pair<cudaGraphExec_t, int>> small_graphs;  // -> (graph, launches)
+    cudaStream_t s_small = nullptr;
+    float *h_pin_in = nullptr, *h_pin_in_sum = nullptr, *h_pin_post = nullptr, *h_pin_post_sum = nullptr;
+    int8_t *h_pin_hard = nullptr;
+    int *h_pin_status = nullptr;
+    bool small_graph_off = false;  // SCALDPC_NO_GRAPH=1
     cudaStream_t s_in = nullptr, s_out = nullptr;
     cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
     std::mutex mu;
@@ -627,6 +637,7 @@ int scaldpc_qary_create(const int8_t *H, int R, int N, int b, int bsum, int dv, 
     if (const char *e = getenv("SCALDPC_MAX_RESIDENT_TRIALS")) h->max_resident = std::max(32, atoi(e));
     if (const char *e = getenv("SCALDPC_RISK_MARGIN")) h->risk_eps = std::max(0.0f, (float)atof(e));
     if (const char *e = getenv("SCALDPC_ES_RESTART_MIN")) h->es_restart_min = std::max(1, atoi(e));
+    if (const char *e = getenv("SCALDPC_NO_GRAPH")) h->small_graph_off = atoi(e) != 0;
     h->E = g.E;
     h->S = g.S;
     h->SL = g.SL;
@@ -684,6 +695,15 @@ void scaldpc_qary_destroy(scaldpc_qary *h)
     free_observed(h);
     free_sim(h);
     cudaFree(h->d_status_all);
+    for (auto &kv : h->small_graphs) cudaGraphExecDestroy(kv.second.first);
+    h->small_graphs.clear();
+    if (h->s_small) cudaStreamDestroy(h->s_small);
+    cudaFreeHost(h->h_pin_in);
+    cudaFreeHost(h->h_pin_in_sum);
+    cudaFreeHost(h->h_pin_post);
+    cudaFreeHost(h->h_pin_post_sum);
+    cudaFreeHost(h->h_pin_hard);
+    cudaFreeHost(h->h_pin_status);
     cudaFree(h->d_scan_out);
     cudaFree(h->d_glist);
     cudaFree(h->d_retry_in);
@@ -1109,6 +1129,108 @@ static int finish_verify(scaldpc_qary *h, const PriorSrc *src, const PriorSrc *h
     return 0;
 }
 
+// Host buffers, one tile (T <= 32), prior vectors, default stream: the reference-shaped call min_sum(channel_output[,
+// channel_output_sum]) (pydecoder.rs:53-65, 125-145; decode.py:262 calls it once per decode).  ~25 dependent launches of
+// ~2-5 us of work each are launch-latency-bound (0.25 ms per call in round 1), so the whole sequence -- H2D of the priors,
+// into_llr, the iterations, the row test, the flag scan, D2H of decisions / posteriors / statuses / flagged count -- is
+// captured once into a CUDA graph and replayed.  Flagged trials (the graph's last copy brings their count) are decoded
+// again outside the graph, as in every other path.
+static int decode_small_graph(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *hard, float *post, float *post_sum,
+                              int32_t *status, unsigned flags)
+{
+    const bool special = h->BSUM > 0;
+    const bool want_post = post != nullptr || post_sum != nullptr;
+    const bool deferred = !(flags & (SCALDPC_CN_EXACT | SCALDPC_NO_VERIFY));
+    int rc;
+    if (!h->s_small) {
+        SCALDPC_CUDA(cudaStreamCreateWithFlags(&h->s_small, cudaStreamNonBlocking));
+        SCALDPC_CUDA(cudaHostAlloc((void **)&h->h_pin_in, (size_t)32 * h->SL * sizeof(float), cudaHostAllocDefault));
+        SCALDPC_CUDA(cudaHostAlloc((void **)&h->h_pin_in_sum, std::max<size_t>(1, (size_t)32 * h->SLS) * sizeof(float), cudaHostAllocDefault));
+        SCALDPC_CUDA(cudaHostAlloc((void **)&h->h_pin_post, (size_t)32 * h->SL * sizeof(float), cudaHostAllocDefault));
+        SCALDPC_CUDA(cudaHostAlloc((void **)&h->h_pin_post_sum, std::max<size_t>(1, (size_t)32 * h->SLS) * sizeof(float), cudaHostAllocDefault));
+        SCALDPC_CUDA(cudaHostAlloc((void **)&h->h_pin_hard, (size_t)32 * h->N, cudaHostAllocDefault));
+        SCALDPC_CUDA(cudaHostAlloc((void **)&h->h_pin_status, 32 * sizeof(int), cudaHostAllocDefault));
+    }
+    cudaStream_t st = h->s_small;
+    if ((rc = ensure_workspace(h, 1, want_post))) return rc;
+    if ((rc = ensure_pipeline(h, 32, 32, want_post))) return rc;
+    if ((rc = ensure_stage_priors(h, 32))) return rc;
+    if (deferred && (rc = begin_verify(h, 32, st))) return rc;  // allocation only matters here; the memset is in the graph
+    memcpy(h->h_pin_in, src.in, (size_t)T * h->SL * sizeof(float));
+    if (special) memcpy(h->h_pin_in_sum, src.in_sum, (size_t)T * h->SLS * sizeof(float));
+
+    PriorSrc dsrc = src;
+    dsrc.in = h->d_in[0];
+    dsrc.in_sum = h->d_in_sum[0];
+    const auto key = std::make_tuple(T, std::max(1, h->max_iter), flags, want_post ? 1 : 0);
+    auto it = h->small_graphs.find(key);
+    if (it == h->small_graphs.end()) {
+        const long long l0 = h->launches, t0 = h->last_trials, w0 = h->last_work;
+        SCALDPC_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        rc = 0;
+        cudaError_t ce = cudaSuccess;
+        do {
+            if ((ce = cudaMemcpyAsync(h->d_in[0], h->h_pin_in, (size_t)T * h->SL * sizeof(float), cudaMemcpyHostToDevice, st))) break;
+            if (special && (ce = cudaMemcpyAsync(h->d_in_sum[0], h->h_pin_in_sum, (size_t)T * h->SLS * sizeof(float), cudaMemcpyHostToDevice, st))) break;
+            if (deferred && (ce = cudaMemsetAsync(h->d_scan_out + 4, 0, 2 * sizeof(int), st))) break;
+            if ((rc = decode_on_device(h, T, dsrc, h->d_ohard[0], want_post ? h->d_opost[0] : nullptr,
+                                       (want_post && special) ? h->d_opost_sum[0] : nullptr, flags, st, nullptr, nullptr, 0, false)))
+                break;
+            if ((ce = cudaMemcpyAsync(h->h_pin_hard, h->d_ohard[0], (size_t)T * h->N, cudaMemcpyDeviceToHost, st))) break;
+            if (want_post && (ce = cudaMemcpyAsync(h->h_pin_post, h->d_opost[0], (size_t)T * h->SL * sizeof(float), cudaMemcpyDeviceToHost, st))) break;
+            if (want_post && special && (ce = cudaMemcpyAsync(h->h_pin_post_sum, h->d_opost_sum[0], (size_t)T * h->SLS * sizeof(float), cudaMemcpyDeviceToHost, st))) break;
+            if ((ce = cudaMemcpyAsync(h->h_pin_status, h->d_status, (size_t)T * sizeof(int), cudaMemcpyDeviceToHost, st))) break;
+            if (deferred && (ce = cudaMemcpyAsync(h->h_scan_out + 4, h->d_scan_out + 4, 2 * sizeof(int), cudaMemcpyDeviceToHost, st))) break;
+        } while (0);
+        cudaGraph_t g = nullptr;
+        const cudaError_t ee = cudaStreamEndCapture(st, &g);
+        const int n_launch = (int)(h->launches - l0);
+        h->launches = l0;  // counted per replay below
+        h->last_trials = t0;
+        h->last_work = w0;
+        if (rc || ce != cudaSuccess || ee != cudaSuccess || !g) {
+            if (g) cudaGraphDestroy(g);
+            cudaGetLastError();
+            h->small_graph_off = true;  // fall back to plain launches from now on
+            return rc ? rc : fail(SCALDPC_ERR_CUDA, "CUDA graph capture of the single-decode path failed: %s",
+                                  cudaGetErrorString(ce != cudaSuccess ? ce : ee));
+        }
+        cudaGraphExec_t ge = nullptr;
+        const cudaError_t ie = cudaGraphInstantiate(&ge, g, 0);
+        cudaGraphDestroy(g);
+        if (ie != cudaSuccess) {
+            h->small_graph_off = true;
+            return fail(SCALDPC_ERR_CUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(ie));
+        }
+        it = h->small_graphs.emplace(key, std::make_pair(ge, n_launch)).first;
+    }
+    SCALDPC_CUDA(cudaGraphLaunch(it->second.first, st));
+    h->launches += it->second.second;
+    h->last_trials += T;
+    h->last_work += (long long)T * std::max(1, h->max_iter);
+    SCALDPC_CUDA(cudaStreamSynchronize(st));
+    int worst = 0;
+    if (deferred && h->h_scan_out[4] > 0) {  // flagged trials: exact-order re-decode, results into the staging rows
+        const int count = h->h_scan_out[4];
+        if ((rc = redecode_exact(h, count, h->d_glist, dsrc, h->d_ohard[0], want_post ? h->d_opost[0] : nullptr,
+                                 (want_post && special) ? h->d_opost_sum[0] : nullptr, flags, st, h->d_glist)))
+            return rc;
+        SCALDPC_CUDA(cudaMemcpyAsync(h->h_pin_hard, h->d_ohard[0], (size_t)T * h->N, cudaMemcpyDeviceToHost, st));
+        if (want_post) {
+            SCALDPC_CUDA(cudaMemcpyAsync(h->h_pin_post, h->d_opost[0], (size_t)T * h->SL * sizeof(float), cudaMemcpyDeviceToHost, st));
+            if (special)
+                SCALDPC_CUDA(cudaMemcpyAsync(h->h_pin_post_sum, h->d_opost_sum[0], (size_t)T * h->SLS * sizeof(float), cudaMemcpyDeviceToHost, st));
+        }
+        SCALDPC_CUDA(cudaStreamSynchronize(st));
+    }
+    memcpy(hard, h->h_pin_hard, (size_t)T * h->N);
+    if (post) memcpy(post, h->h_pin_post, (size_t)T * h->SL * sizeof(float));
+    if (post_sum && special) memcpy(post_sum, h->h_pin_post_sum, (size_t)T * h->SLS * sizeof(float));
+    for (int t = 0; t < T; ++t) worst = std::min(worst, h->h_pin_status[t]);
+    if (status) memcpy(status, h->h_pin_status, (size_t)T * sizeof(int));
+    return status_error(worst);
+}
+
 // Shared body of scaldpc_qary_decode / scaldpc_qary_decode_observed.  `src` holds the caller's pointers (host or
 // device); tables (observed mode) are already resident in the handle as LLRs.
 static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *hard, float *post, float *post_sum,
@@ -1136,6 +1258,12 @@ static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *har
     // default (verified) mode without early termination: the chunks / passes only LIST their at-risk trials, the exact
     // re-decode runs once at the end of the call (finish_verify)
     const bool deferred = !(flags & (SCALDPC_CN_EXACT | SCALDPC_NO_VERIFY | SCALDPC_QARY_EARLY_STOP));
+
+    if (!dev_ptrs && T <= 32 && !src.observed && st == nullptr && !(flags & SCALDPC_QARY_EARLY_STOP) && !h->small_graph_off) {
+        rc = decode_small_graph(h, T, src, hard, post, post_sum, status, flags);
+        if (!h->small_graph_off || rc != SCALDPC_ERR_CUDA) return rc;
+        // capture is not possible here (e.g. another capture in progress): plain launches below
+    }
 
     if (dev_ptrs) {  // asynchronous on `st` (one synchronisation per call unless SCALDPC_NO_VERIFY); at most `max_resident` trials' messages live in the workspace at a time
         const int cap = std::max(32, h->max_resident / 32 * 32);

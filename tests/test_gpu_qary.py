@@ -453,3 +453,35 @@ def test_host_pipeline_deferred_redecode_and_overflow():
     oh, op, ops = d.min_sum_observed(w.table, ob.obs, w.table_sum, ob.obs_sum, want_posterior=True)
     assert d.last_run["redecoded"] == run["redecoded"]
     assert np.array_equal(oh, hard) and np.array_equal(op, post, equal_nan=True) and np.array_equal(ops, posts, equal_nan=True)
+
+
+def test_single_decode_graph_path():
+    """Host buffers with T <= 32 (what min_sum() and the thread-pool combiner produce) replay ONE CUDA graph per (T,
+    iterations, flags); results must equal the plain-launch path (device tensors), on the first call (capture) and on
+    replays, for converging and at-risk trials, with and without posteriors, after a change of the iteration count."""
+    import torch
+
+    w = KyberWorkload("kyber768", sum_weight=6, check_blocks=1, accuracy=0.95, nbits=3, nbits_sum=4, seed=2)
+    b = w.generate(40, seed=8)
+    good = KyberWorkload("kyber768", sum_weight=6, check_blocks=1, accuracy=0.999, nbits=3, nbits_sum=4, seed=2).generate(40, seed=9)
+    d = QaryDecoder(w.H, 4, **w.decoder_kwargs)
+    for it in (4, 6):
+        d.set_iterations(it)
+        for batch in (b, good):
+            for T in (1, 7, 32):
+                pri, pris = batch.priors[:T], batch.priors_sum[:T]
+                ref = d.min_sum_batch(torch.from_numpy(pri).cuda(), torch.from_numpy(pris).cuda())
+                torch.cuda.synchronize()
+                n_re = d.last_run["redecoded"]
+                for _ in range(3):  # capture, replay, replay
+                    got = d.min_sum_batch(pri, pris)
+                    assert d.last_run == {"trials": T, "redecoded": n_re, "trial_iterations": (T + n_re) * it}
+                    for a, c in zip(ref, got):
+                        assert np.array_equal(a.cpu().numpy(), c, equal_nan=True)
+                h2, _, _ = d.min_sum_batch(pri, pris, want_posterior=False)
+                assert np.array_equal(h2, got[0])
+    # the reference-shaped call itself
+    d.set_iterations(5)
+    one = d.min_sum(good.priors[3], good.priors_sum[3])
+    assert one == d.min_sum_batch(good.priors[3:4], good.priors_sum[3:4], want_posterior=False)[0][0].tolist()
+    assert (np.array(one[: w.bvars]) == good.secret[3]).all()
