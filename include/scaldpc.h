@@ -77,7 +77,7 @@ typedef struct scaldpc_qary scaldpc_qary;
                                      parity runs leave this off.  Every iteration emits hard decisions; a trial whose
                                      decisions satisfy every row, sum_j h_ij s_j (+ s_sum,i) = 0, and whose posteriors
                                      are clear of ties (risk margin) is frozen with that iteration's outputs.  Once at
-                                     most 1/8 of a batch of >= 2048 trials is still running the stragglers are re-staged
+                                     most 1/8 of a batch (chunk) of >= 256 trials is still running the stragglers are re-staged
                                      compactly and decoded from scratch (the same results, fewer idle lanes).  Trials
                                      still running at max_iter keep their last decisions (SCALDPC_NO_VERIFY) or are
                                      decoded with the exact-order check node and the fixed iteration count, i.e. they get

@@ -78,7 +78,7 @@ struct scaldpc_qary {
     int *d_iters = nullptr;       // [tiles*32] last iteration of every slot of the current round
     int *d_iters_all = nullptr;   // [cap_iters_T] per-trial iteration counts of the last call
     size_t cap_iters_T = 0;
-    int es_restart_min = 2048;    // batches at least this large restart their stragglers in a compacted second round
+    int es_restart_min = 256;     // batches (chunks) at least this large restart their stragglers in a compacted second round
     // staging for host-pointer calls: the batch is cut into chunks and pipelined (H2D of chunk i+1 and D2H of chunk
     // i-1 overlap the decode of chunk i), so every staging buffer exists twice
     size_t cap_stage_T = 0;  // trials per output staging buffer

@@ -215,7 +215,7 @@ static int hm_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
     const bool exact = flags & SCALDPC_CN_EXACT, force_generic = flags & SCALDPC_CN_GENERIC;
     const bool verify = !(flags & (SCALDPC_CN_EXACT | SCALDPC_NO_VERIFY));  // as decode_on_device (qary.cu)
     const bool early = (flags & SCALDPC_QARY_EARLY_STOP) && !exact;
-    int restart_min = 2048;
+    int restart_min = 256;
     if (const char *e = getenv("SCALDPC_ES_RESTART_MIN")) restart_min = std::max(1, atoi(e));
     const bool may_restart = early && !(flags & kHmNoRestart) && T >= restart_min;
     std::vector<uint32_t> risk(tiles, 0u), done(tiles, 0u);
