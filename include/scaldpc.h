@@ -263,6 +263,32 @@ int scaldpc_bp_decode_scored(scaldpc_bp *h, int T, int n_msg, const int32_t *n_c
  */
 int scaldpc_bp_decode_nested(scaldpc_bp *h, int T, const int32_t *n_checks, const uint8_t *synd, const double *channel_probs,
                              uint8_t *decoding, float *llr, int32_t *iters, int32_t *converged, unsigned flags, void *stream);
+/*
+ * scaldpc_bp_create_multi / scaldpc_bp_decode_multi -- SEGMENTED CSR: one batch over UNRELATED graphs.
+ * The reference draws a NEW code for every simulated attack (hqc.py:1056 make_random_ldpc_parity_check_matrix(N, weight,
+ * rng)) and decodes that attack's growing ladder of check sets on it (hqc.py:953-984); a campaign of attacks is therefore
+ * a batch whose trials live on different graphs of the same shape.  Here the n_graphs graphs share one handle and one
+ * workspace: the graph tables are concatenated, every tile of 32 trial slots belongs to ONE graph (an attack's ladder
+ * levels / noise realisations fill the lanes), so graph indices stay warp-uniform and every kernel is the single-graph
+ * kernel with a per-tile table offset.
+ *   n_graphs   G >= 1 graphs, all m x n
+ *   row_ptr    G x (m+1) int32, every segment starts at 0
+ *   col        the G column arrays back to back (segment g has row_ptr[g][m] entries), ascending within a row
+ * scaldpc_bp_decode_multi:
+ *   graph_of   T int32, HOST pointer even with SCALDPC_DEVICE_PTRS: graph of every trial, any order (trials are grouped
+ *              by graph internally; outputs come back in the caller's order)
+ *   n_checks   NULL or T int32 as scaldpc_bp_decode_nested (every trial its own prefix of its graph's rows)
+ *   truth / weight / stats   all NULL / 0, or as scaldpc_bp_decode_scored (needs H_g = [Hin_g | I])
+ *   decoding, llr, iters, converged, synd, channel_probs, flags, stream   as scaldpc_bp_decode; channel_probs is shared
+ *              by all graphs (n values) or per trial (SCALDPC_BP_PROBS_PER_TRIAL)
+ * Running trials are frozen as they converge but NOT compacted (a tile's lanes must share a graph).
+ * Each trial's results equal a scaldpc_bp_decode on its own graph.
+ */
+int scaldpc_bp_create_multi(int n_graphs, int m, int n, const int32_t *row_ptr, const int32_t *col, int max_iter, int device,
+                            scaldpc_bp **out);
+int scaldpc_bp_decode_multi(scaldpc_bp *h, int T, const int32_t *graph_of, const int32_t *n_checks, const uint8_t *synd,
+                            const double *channel_probs, const int32_t *truth, int weight, int32_t *stats, uint8_t *decoding,
+                            float *llr, int32_t *iters, int32_t *converged, unsigned flags, void *stream);
 /* Shape queries: checks, variables, edges, iteration cap (max_iter = 0 at create time means n, as upstream). */
 int scaldpc_bp_info(const scaldpc_bp *h, int *m, int *n, int *edges, int *max_iter);
 long long scaldpc_bp_launch_count(const scaldpc_bp *h);

@@ -27,6 +27,14 @@ struct scaldpc_bp {
     int m = 0, n = 0, E = 0, dc_max = 0, dv_max = 0;
     int max_iter = 0, device = 0, num_sms = 148;
     int class_end[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    // segmented CSR: G graphs of the same shape (scaldpc_bp_create_multi); E is then the LARGEST edge count (table stride)
+    int G = 1;
+    int class_max[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // largest size of every degree class over the graphs
+    int *d_class_end = nullptr;   // [G][kBpVnClasses+1]
+    int *d_tile_graph = nullptr;  // [cap_tile_graph] graph of every tile of the running decode
+    int *d_slot_orig = nullptr;   // staging of the slot -> trial map
+    size_t cap_tile_graph = 0;
+    const int *cur_tile_graph = nullptr;
     int *d_row_ptr = nullptr, *d_col = nullptr, *d_col_ptr = nullptr, *d_vn_order = nullptr, *d_vn_desc = nullptr;
     uint32_t *d_csc_edge = nullptr;
     int *d_edge_row = nullptr;     // E: check of every edge (first pass with shared priors)
@@ -199,6 +207,14 @@ BpDev view(const scaldpc_bp *h, int cur, bool per_trial_prior, bool want_post)
     p.conv = h->d_conv;
     p.counts = h->d_counts;
     p.nrows = h->cur_nrows;
+    p.g_rp = h->m + 1;
+    p.g_e = h->E;
+    p.g_cp = h->n + 1;
+    p.g_n = h->n;
+    if (h->G > 1) {
+        p.tile_graph = h->cur_tile_graph;
+        p.class_end = h->d_class_end;
+    }
     return p;
 }
 
@@ -216,7 +232,8 @@ int launch_cn(scaldpc_bp *h, const BpDev &p, int tiles, bool first, cudaStream_t
     return 0;
 }
 
-typedef void (*bp_vn_fn)(const BpDev, const int, const int, const int);
+typedef void (*bp_vn_fn)(const BpDev, const int, const int, const int, const int);
+typedef void (*bp_vn_tma_fn)(const BpDev, const int, const int, const int);
 bp_vn_fn vn_class_fn(int c)
 {
     switch (c) {
@@ -232,7 +249,7 @@ bp_vn_fn vn_class_fn(int c)
 }
 
 // TMA-gather variants of the register classes above degree 1 (bp_kernels.cuh k_bp_vn_tma).
-bp_vn_fn vn_class_tma_fn(int c)
+bp_vn_tma_fn vn_class_tma_fn(int c)
 {
     switch (c) {
     case 1: return k_bp_vn_tma<1, 4>;
@@ -253,25 +270,27 @@ int launch_vn(scaldpc_bp *h, const BpDev &p, int tiles, cudaStream_t st)
     if (tiles <= h->vn_single_tiles) {
         // few tiles (the non-converging tail after compaction): the iteration is bound by kernel launches, so ONE launch
         // of the any-degree kernel over all variables replaces one launch per degree class (same arithmetic)
-        k_bp_vn_generic<<<dim3((h->n + h->vn_gen_wpc - 1) / h->vn_gen_wpc, tiles), h->vn_gen_wpc * 32, h->smem_vn, st>>>(p, 0, h->n);
+        k_bp_vn_generic<<<dim3((h->n + h->vn_gen_wpc - 1) / h->vn_gen_wpc, tiles), h->vn_gen_wpc * 32, h->smem_vn, st>>>(p, 0, h->n, -1);
         ++h->launches;
         SCALDPC_CUDA(cudaGetLastError());
         return 0;
     }
+    const bool multi = h->G > 1;  // every tile takes its own graph's slice of the class: [0, largest slice) is launched
     int lo = 0;
     for (int c = 0; c <= kBpVnClasses; ++c) {
-        const int hi = h->class_end[c];
+        const int hi = multi ? h->class_max[c] : h->class_end[c];
+        if (multi) lo = 0;
         if (hi > lo) {
             if (c < kBpVnClasses) {
                 const long long items = (long long)tiles * (hi - lo);
                 const int ctas = (int)std::min<long long>((long long)h->num_sms * h->vn_occ[c], (items + kBpVnWarps - 1) / kBpVnWarps);
-                if (h->vn_tma && vn_class_tma_fn(c))
+                if (h->vn_tma && !multi && vn_class_tma_fn(c))
                     vn_class_tma_fn(c)<<<std::max(1, ctas), kBpVnWarps * 32, vn_tma_smem(c), st>>>(p, lo, hi, tiles);
                 else
-                    vn_class_fn(c)<<<std::max(1, ctas), kBpVnWarps * 32, 0, st>>>(p, lo, hi, tiles);
+                    vn_class_fn(c)<<<std::max(1, ctas), kBpVnWarps * 32, 0, st>>>(p, lo, hi, tiles, multi ? c : -1);
             } else {
                 k_bp_vn_generic<<<dim3((hi - lo + h->vn_gen_wpc - 1) / h->vn_gen_wpc, tiles), h->vn_gen_wpc * 32, h->smem_vn, st>>>(
-                    p, lo, hi);
+                    p, lo, hi, multi ? c : -1);
             }
             ++h->launches;
         }
@@ -319,17 +338,27 @@ int compact(scaldpc_bp *h, int cur, int cur_tiles, int n_run, bool probs_t, uint
 
 extern "C" {
 
-int scaldpc_bp_create(int m, int n, const int32_t *row_ptr, const int32_t *col, int max_iter, int device,
-                      scaldpc_bp **out)
+// G >= 1 graphs of shape m x n: row_ptr = G x (m+1) (every segment starts at 0), col = the G column arrays back to back.
+static int bp_create_impl(int G, int m, int n, const int32_t *row_ptr, const int32_t *col, int max_iter, int device,
+                          scaldpc_bp **out)
 {
     if (!out) return fail(SCALDPC_ERR_ARG, "out is NULL");
     *out = nullptr;
     if (max_iter < 0) return fail(SCALDPC_ERR_ARG, "max_iter must be >= 0");
-    BpHostGraph g;
+    if (G < 1 || !row_ptr || !col) return fail(SCALDPC_ERR_ARG, "bad parity-check matrix");
+    std::vector<BpHostGraph> gs(G);
+    int Emax = 0, dc_max = 0, dv_max = 0;
     {
-        std::string err;
-        const int rc = build_bp_graph(m, n, row_ptr, col, g, err);
-        if (rc) return fail(rc, "%s", err.c_str());
+        size_t coff = 0;
+        for (int g = 0; g < G; ++g) {
+            std::string err;
+            const int rc = build_bp_graph(m, n, row_ptr + (size_t)g * (m + 1), col + coff, gs[g], err);
+            if (rc) return G > 1 ? fail(rc, "graph %d: %s", g, err.c_str()) : fail(rc, "%s", err.c_str());
+            coff += (size_t)gs[g].E;
+            Emax = std::max(Emax, gs[g].E);
+            dc_max = std::max(dc_max, gs[g].dc_max);
+            dv_max = std::max(dv_max, gs[g].dv_max);
+        }
     }
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
@@ -338,12 +367,19 @@ int scaldpc_bp_create(int m, int n, const int32_t *row_ptr, const int32_t *col, 
     std::unique_ptr<scaldpc_bp, void (*)(scaldpc_bp *)> h(new scaldpc_bp, scaldpc_bp_destroy);
     h->m = m;
     h->n = n;
-    h->E = g.E;
-    h->dc_max = std::max(1, g.dc_max);
-    h->dv_max = std::max(1, g.dv_max);
+    h->E = Emax;
+    h->G = G;
+    h->dc_max = std::max(1, dc_max);
+    h->dv_max = std::max(1, dv_max);
     h->max_iter = max_iter == 0 ? n : max_iter;  // upstream: max_iter = 0 means n
     h->device = device;
-    for (int c = 0; c <= kBpVnClasses; ++c) h->class_end[c] = g.class_end[c];
+    for (int c = 0; c <= kBpVnClasses; ++c) h->class_end[c] = gs[0].class_end[c];
+    std::vector<int> class_end_all((size_t)G * (kBpVnClasses + 1));
+    for (int g = 0; g < G; ++g)
+        for (int c = 0; c <= kBpVnClasses; ++c) {
+            class_end_all[(size_t)g * (kBpVnClasses + 1) + c] = gs[g].class_end[c];
+            h->class_max[c] = std::max(h->class_max[c], gs[g].class_end[c] - (c ? gs[g].class_end[c - 1] : 0));
+        }
     // check pass: per warp a double-buffered row stage + the prefix array, 3 x dc_max x 128 B
     const size_t per_warp = (size_t)3 * h->dc_max * 32 * sizeof(float);
     h->cn_warps = (int)std::min<size_t>(kBpCnWarpsMax, (216 * 1024) / per_warp);
@@ -359,18 +395,30 @@ int scaldpc_bp_create(int m, int n, const int32_t *row_ptr, const int32_t *col, 
     }
     SCALDPC_CUDA(cudaSetDevice(device));
     SCALDPC_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
-    int rc;
-    if ((rc = upload_vec(&h->d_row_ptr, g.row_ptr)) || (rc = upload_vec(&h->d_col, g.col)) ||
-        (rc = upload_vec(&h->d_col_ptr, g.col_ptr)) || (rc = upload_vec(&h->d_csc_edge, g.csc_off)) ||
-        (rc = upload_vec(&h->d_vn_order, g.vn_order)) || (rc = upload_vec(&h->d_vn_desc, g.vn_desc)))
-        return rc;
-    {
-        std::vector<int> edge_row(std::max(1, g.E));
+    // the per-graph tables, concatenated with the fixed strides m+1 / Emax / n+1 / n (BpDev g_rp / g_e / g_cp / g_n);
+    // a graph with fewer edges than Emax is padded: its padding edges belong to "row m" (never active) and are never
+    // reached through row_ptr / col_ptr
+    std::vector<int> a_row_ptr((size_t)G * (m + 1)), a_col((size_t)G * std::max(1, Emax), 0), a_col_ptr((size_t)G * (n + 1));
+    std::vector<int> a_vn_order((size_t)G * n), a_vn_desc((size_t)G * 4 * std::max(1, n)), a_edge_row((size_t)G * std::max(1, Emax), m);
+    std::vector<uint32_t> a_csc_off((size_t)G * std::max(1, Emax), 0u);
+    for (int g = 0; g < G; ++g) {
+        const BpHostGraph &q = gs[g];
+        std::copy(q.row_ptr.begin(), q.row_ptr.end(), a_row_ptr.begin() + (size_t)g * (m + 1));
+        std::copy(q.col.begin(), q.col.end(), a_col.begin() + (size_t)g * Emax);
+        std::copy(q.col_ptr.begin(), q.col_ptr.end(), a_col_ptr.begin() + (size_t)g * (n + 1));
+        std::copy(q.vn_order.begin(), q.vn_order.end(), a_vn_order.begin() + (size_t)g * n);
+        std::copy(q.vn_desc.begin(), q.vn_desc.begin() + (size_t)4 * n, a_vn_desc.begin() + (size_t)g * 4 * n);
+        std::copy(q.csc_off.begin(), q.csc_off.begin() + q.E, a_csc_off.begin() + (size_t)g * Emax);
         for (int r = 0; r < m; ++r)
-            for (int e = g.row_ptr[r]; e < g.row_ptr[r + 1]; ++e) edge_row[e] = r;
-        if ((rc = upload_vec(&h->d_edge_row, edge_row))) return rc;
+            for (int e = q.row_ptr[r]; e < q.row_ptr[r + 1]; ++e) a_edge_row[(size_t)g * Emax + e] = r;
     }
-    SCALDPC_CUDA(cudaMalloc((void **)&h->d_first_tab, (size_t)std::max(1, g.E) * sizeof(float)));
+    int rc;
+    if ((rc = upload_vec(&h->d_row_ptr, a_row_ptr)) || (rc = upload_vec(&h->d_col, a_col)) ||
+        (rc = upload_vec(&h->d_col_ptr, a_col_ptr)) || (rc = upload_vec(&h->d_csc_edge, a_csc_off)) ||
+        (rc = upload_vec(&h->d_vn_order, a_vn_order)) || (rc = upload_vec(&h->d_vn_desc, a_vn_desc)) ||
+        (rc = upload_vec(&h->d_edge_row, a_edge_row)) || (rc = upload_vec(&h->d_class_end, class_end_all)))
+        return rc;
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_first_tab, (size_t)G * std::max(1, Emax) * sizeof(float)));
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_prior, (size_t)n * sizeof(float)));
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_nact, sizeof(int)));
     h->cap_counts = h->max_iter + 2;
@@ -380,7 +428,7 @@ int scaldpc_bp_create(int m, int n, const int32_t *row_ptr, const int32_t *col, 
     SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_cn<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_cn));
     if (h->smem_vn)
         SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_vn_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_vn));
-    h->vn_tma = getenv("SCALDPC_BP_VN_TMA") != nullptr;
+    h->vn_tma = getenv("SCALDPC_BP_VN_TMA") != nullptr && G == 1;
     if (const char *e = getenv("SCALDPC_BP_VN_SINGLE")) h->vn_single_tiles = atoi(e);
     for (int c = 0; c < kBpVnClasses; ++c) {
         if (h->vn_tma && vn_class_tma_fn(c)) {
@@ -400,6 +448,19 @@ int scaldpc_bp_create(int m, int n, const int32_t *row_ptr, const int32_t *col, 
     return 0;
 }
 
+int scaldpc_bp_create(int m, int n, const int32_t *row_ptr, const int32_t *col, int max_iter, int device,
+                      scaldpc_bp **out)
+{
+    return bp_create_impl(1, m, n, row_ptr, col, max_iter, device, out);
+}
+
+int scaldpc_bp_create_multi(int n_graphs, int m, int n, const int32_t *row_ptr, const int32_t *col, int max_iter, int device,
+                            scaldpc_bp **out)
+{
+    if (n_graphs < 1) return fail(SCALDPC_ERR_ARG, "n_graphs must be >= 1");
+    return bp_create_impl(n_graphs, m, n, row_ptr, col, max_iter, device, out);
+}
+
 void scaldpc_bp_destroy(scaldpc_bp *h)
 {
     if (!h) return;
@@ -416,6 +477,9 @@ void scaldpc_bp_destroy(scaldpc_bp *h)
     cudaFree(h->d_vn_order);
     cudaFree(h->d_vn_desc);
     cudaFree(h->d_edge_row);
+    cudaFree(h->d_class_end);
+    cudaFree(h->d_tile_graph);
+    cudaFree(h->d_slot_orig);
     cudaFree(h->d_first_tab);
     cudaFree(h->d_prior);
     cudaFree(h->d_nact);
@@ -445,7 +509,7 @@ struct BpScore {
 
 static int bp_decode_impl(scaldpc_bp *h, int T, const uint8_t *synd, const double *channel_probs, uint8_t *decoding,
                           float *llr, int32_t *iters, int32_t *converged, unsigned flags, void *stream,
-                          const BpScore *score, const int32_t *n_checks)
+                          const BpScore *score, const int32_t *n_checks, const int32_t *graph_of = nullptr)
 {
     if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
     if (T < 0) return fail(SCALDPC_ERR_ARG, "T < 0");
@@ -460,14 +524,52 @@ static int bp_decode_impl(scaldpc_bp *h, int T, const uint8_t *synd, const doubl
     }
     const bool probs_t = flags & SCALDPC_BP_PROBS_PER_TRIAL;
     const bool early = !(flags & SCALDPC_BP_NO_EARLY_STOP);
-    const bool compacting = early && !(flags & SCALDPC_BP_NO_COMPACT);
+    const bool multi = h->G > 1;
+    // segmented CSR: a tile's lanes must share a graph, so trials of different graphs are never packed together
+    const bool compacting = early && !(flags & SCALDPC_BP_NO_COMPACT) && !multi;
     const bool want_post = llr != nullptr;
     cudaStream_t st = (cudaStream_t)stream;
 
     std::lock_guard<std::mutex> lk(h->mu);
     SCALDPC_CUDA(cudaSetDevice(h->device));
-    const int tiles = (T + 31) / 32;
+    int tiles = (T + 31) / 32;
     int rc;
+    std::vector<int> slot_orig, tile_graph;  // segmented CSR: every graph's trials get tiles of their own
+    if (multi) {
+        if (!graph_of) return fail(SCALDPC_ERR_ARG, "this handle holds %d graphs: decode with scaldpc_bp_decode_multi", h->G);
+        std::vector<int> cnt(h->G, 0), first(h->G, 0);
+        for (int t = 0; t < T; ++t) {
+            if (graph_of[t] < 0 || graph_of[t] >= h->G)
+                return fail(SCALDPC_ERR_ARG, "graph_of[%d] = %d is outside 0 .. %d", t, graph_of[t], h->G - 1);
+            ++cnt[graph_of[t]];
+        }
+        tiles = 0;
+        for (int g = 0; g < h->G; ++g) {
+            first[g] = tiles;
+            tiles += (cnt[g] + 31) / 32;
+        }
+        tile_graph.resize(std::max(1, tiles));
+        for (int g = 0; g < h->G; ++g)
+            for (int k = 0; k < (cnt[g] + 31) / 32; ++k) tile_graph[first[g] + k] = g;
+        slot_orig.assign((size_t)std::max(1, tiles) * 32, -1);
+        std::fill(cnt.begin(), cnt.end(), 0);
+        for (int t = 0; t < T; ++t) {
+            const int g = graph_of[t];
+            slot_orig[(size_t)first[g] * 32 + cnt[g]++] = t;  // trial order preserved inside a graph
+        }
+        if ((size_t)tiles > h->cap_tile_graph) {
+            cudaFree(h->d_tile_graph);
+            cudaFree(h->d_slot_orig);
+            h->d_tile_graph = h->d_slot_orig = nullptr;
+            h->cap_tile_graph = 0;
+            SCALDPC_CUDA(cudaMalloc((void **)&h->d_tile_graph, (size_t)tiles * sizeof(int)));
+            SCALDPC_CUDA(cudaMalloc((void **)&h->d_slot_orig, (size_t)tiles * 32 * sizeof(int)));
+            h->cap_tile_graph = (size_t)tiles;
+        }
+        SCALDPC_CUDA(cudaMemcpyAsync(h->d_tile_graph, tile_graph.data(), (size_t)tiles * sizeof(int), cudaMemcpyHostToDevice, st));
+        SCALDPC_CUDA(cudaMemcpyAsync(h->d_slot_orig, slot_orig.data(), (size_t)tiles * 32 * sizeof(int), cudaMemcpyHostToDevice, st));
+        h->cur_tile_graph = h->d_tile_graph;
+    }
     if ((rc = ensure_ws(h, tiles, want_post, probs_t))) return rc;
     struct NrowsGuard {  // the kernels see the per-trial row limits only while this decode runs
         scaldpc_bp *h;
@@ -509,12 +611,19 @@ static int bp_decode_impl(scaldpc_bp *h, int T, const uint8_t *synd, const doubl
     // ---- inputs -> tile layout (always into set 0)
     BpSet &s0 = h->set[0];
     const int tb = (tiles + 255) / 256;
-    k_bp_reset<<<tb, 256, 0, st>>>(s0.valid, s0.done, s0.unsat, s0.orig, h->d_iters, h->d_conv, tiles, T, h->max_iter);
+    const int *slot_map = nullptr;  // identity unless the trials were grouped by graph
+    if (multi) {
+        SCALDPC_CUDA(cudaMemcpyAsync(s0.orig, h->d_slot_orig, (size_t)tiles * 32 * sizeof(int), cudaMemcpyDeviceToDevice, st));
+        k_bp_reset_slots<<<tb, 256, 0, st>>>(s0.valid, s0.done, s0.unsat, s0.orig, h->d_iters, h->d_conv, tiles, h->max_iter);
+        slot_map = s0.orig;
+    } else {
+        k_bp_reset<<<tb, 256, 0, st>>>(s0.valid, s0.done, s0.unsat, s0.orig, h->d_iters, h->d_conv, tiles, T, h->max_iter);
+    }
     if (probs_t)
-        k_bp_prior_tiled<<<dim3((h->n + 31) / 32, tiles), 256, 0, st>>>(dprobs, s0.prior_t, T, h->n);
+        k_bp_prior_tiled<<<dim3((h->n + 31) / 32, tiles), 256, 0, st>>>(dprobs, s0.prior_t, T, h->n, slot_map);
     else
         k_bp_prior_shared<<<(h->n + 255) / 256, 256, 0, st>>>(dprobs, h->d_prior, h->n);
-    k_bp_pack_synd<<<dim3((h->m + 31) / 32, tiles), 256, 0, st>>>(dsynd, s0.synd_w, T, h->m);
+    k_bp_pack_synd<<<dim3((h->m + 31) / 32, tiles), 256, 0, st>>>(dsynd, s0.synd_w, T, h->m, slot_map);
     SCALDPC_CUDA(cudaMemsetAsync(h->d_dec_w, 0, (size_t)tiles * h->n * sizeof(uint32_t), st));
     SCALDPC_CUDA(cudaMemsetAsync(h->d_counts, 0, (size_t)h->cap_counts * sizeof(int), st));
     h->launches += 3;
@@ -531,7 +640,7 @@ static int bp_decode_impl(scaldpc_bp *h, int T, const uint8_t *synd, const doubl
         const BpDev p = view(h, cur, probs_t, want_post);
         if (it == 1 && !probs_t && !getenv("SCALDPC_BP_NO_FIRST_TABLE")) {
             // shared priors: the first check-to-bit messages differ between trials only in sign (bp_kernels.cuh)
-            k_bp_first_table<<<(h->m + 127) / 128, 128, 0, st>>>(p, h->d_first_tab);
+            k_bp_first_table<<<dim3((h->m + 127) / 128, h->G), 128, 0, st>>>(p, h->d_first_tab);
             k_bp_first_fill<<<dim3((h->E + 63) / 64, cur_tiles), 256, 0, st>>>(p, h->d_first_tab, h->d_edge_row, cur_tiles);
             h->launches += 2;
             SCALDPC_CUDA(cudaGetLastError());
@@ -621,6 +730,21 @@ int scaldpc_bp_decode_scored(scaldpc_bp *h, int T, int n_msg, const int32_t *n_c
     return bp_decode_impl(h, T, synd, channel_probs, decoding, nullptr, iters, converged, flags, stream, &score, n_checks);
 }
 
+int scaldpc_bp_decode_multi(scaldpc_bp *h, int T, const int32_t *graph_of, const int32_t *n_checks, const uint8_t *synd,
+                            const double *channel_probs, const int32_t *truth, int weight, int32_t *stats, uint8_t *decoding,
+                            float *llr, int32_t *iters, int32_t *converged, unsigned flags, void *stream)
+{
+    if (!graph_of) return fail(SCALDPC_ERR_ARG, "graph_of is NULL");
+    if (h && h->G == 1)
+        for (int t = 0; t < T; ++t)
+            if (graph_of[t] != 0) return fail(SCALDPC_ERR_ARG, "graph_of[%d] = %d, but the handle holds one graph", t, graph_of[t]);
+    if (stats) {
+        const BpScore score{truth, weight, h ? h->n - h->m : 0, stats};
+        return bp_decode_impl(h, T, synd, channel_probs, decoding, llr, iters, converged, flags, stream, &score, n_checks, graph_of);
+    }
+    return bp_decode_impl(h, T, synd, channel_probs, decoding, llr, iters, converged, flags, stream, nullptr, n_checks, graph_of);
+}
+
 int scaldpc_bp_last_run(const scaldpc_bp *h, int *iterations_launched, int *compactions)
 {
     if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
@@ -632,6 +756,7 @@ int scaldpc_bp_last_run(const scaldpc_bp *h, int *iterations_launched, int *comp
 int scaldpc_bp_time_kernel(scaldpc_bp *h, int which, int T, unsigned flags, int reps, void *stream, float *avg_ms)
 {
     if (!h || !avg_ms || reps <= 0 || T <= 0) return fail(SCALDPC_ERR_ARG, "bad argument");
+    if (h->G > 1) return fail(SCALDPC_ERR_UNSUPPORTED, "the timing probe covers single-graph handles");
     std::lock_guard<std::mutex> lk(h->mu);
     SCALDPC_CUDA(cudaSetDevice(h->device));
     const int tiles = (T + 31) / 32;

@@ -63,7 +63,17 @@ struct BpDev {
     int *conv;                // T
     int *counts;              // max_iter+2
     const int *nrows;         // T, indexed by ORIGINAL trial: active checks (a prefix of the rows) of every trial, or null
+    // Segmented CSR: G graphs of one shape m x n behind one handle -- the reference draws a NEW code per
+    // simulated attack (hqc.py:1056).  Every TILE belongs to one graph (its 32 lanes are that attack's decodes), so graph
+    // indices stay warp-uniform.  The per-graph tables are concatenated with fixed strides; null = single graph.
+    const int *tile_graph = nullptr;  // [tiles]
+    int g_rp = 0, g_e = 0, g_cp = 0, g_n = 0;  // strides: m+1 (row_ptr), E = max edges (col, csc_off, first table), n+1, n
+    const int *class_end = nullptr;   // [G][kBpVnClasses+1]: end of every degree class in each graph's sorted variable order
 };
+
+constexpr int kBpVnClassCount = 7;  // == kBpVnClasses (bp_graph.h)
+
+__device__ __forceinline__ int bp_graph(const BpDev &p, int tile) { return p.tile_graph ? __ldg(p.tile_graph + tile) : 0; }
 
 #ifdef SCALDPC_HOST_MODEL
 __device__ __forceinline__ uint32_t bp_bits(float x)
@@ -161,7 +171,7 @@ __global__ void __launch_bounds__(kBpCnWarpsMax * 32) k_bp_cn(const BpDev p, con
 
     const int step_t = nw / p.m, step_c = nw - step_t * p.m;  // item -> item + nw without a division per item
     struct Item {
-        int tile, check, e0, d;
+        int tile, check, e0, d, cb;  // cb: offset of the tile's graph in the column table
     };
     // moves to the next item (stride nw) whose tile still has running trials; tile >= tiles: none left
     auto advance = [&](Item &it, bool first) {
@@ -182,8 +192,11 @@ __global__ void __launch_bounds__(kBpCnWarpsMax * 32) k_bp_cn(const BpDev p, con
             }
         }
         if (it.tile < tiles) {
-            it.e0 = __ldg(p.row_ptr + it.check);
-            it.d = __ldg(p.row_ptr + it.check + 1) - it.e0;
+            const int g = bp_graph(p, it.tile);
+            const int *rp = p.row_ptr + (size_t)g * p.g_rp + it.check;
+            it.e0 = __ldg(rp);
+            it.d = __ldg(rp + 1) - it.e0;
+            it.cb = g * p.g_e;
         }
     };
 #ifndef SCALDPC_HOST_MODEL
@@ -244,7 +257,7 @@ __global__ void __launch_bounds__(kBpCnWarpsMax * 32) k_bp_cn(const BpDev p, con
 #endif
 #pragma unroll 4
                 for (int k = 0; k < d; ++k) {
-                    const float v = bp_prior_of(p, tile, __ldg(p.col + e0 + k), lane);
+                    const float v = bp_prior_of(p, tile, __ldg(p.col + cur.cb + e0 + k), lane);
                     const float q = bp_fold(v);
                     P[k * 32] = pre;
                     park[(size_t)k * 32] = q;
@@ -290,23 +303,27 @@ __global__ void __launch_bounds__(kBpCnWarpsMax * 32) k_bp_cn(const BpDev p, con
 //                     a pure write at HBM speed instead of 4 MUFU + two dependent index loads per edge and trial
 //                     (k_bp_cn<true>: 2.5 ms per 4096 hqc128 trials against 0.93 ms for a later check pass).
 // -----------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_bp_first_table(const BpDev p, float *__restrict__ tab)
+__global__ void __launch_bounds__(128) k_bp_first_table(const BpDev p, float *__restrict__ tab_all)
 {
     const int check = blockIdx.x * blockDim.x + threadIdx.x;
     if (check >= p.m) return;
-    const int e0 = __ldg(p.row_ptr + check), d = __ldg(p.row_ptr + check + 1) - e0;
+    const int g = blockIdx.y;  // one table per graph
+    const int *row_ptr = p.row_ptr + (size_t)g * p.g_rp;
+    const int *col = p.col + (size_t)g * p.g_e;
+    float *tab = tab_all + (size_t)g * p.g_e;
+    const int e0 = __ldg(row_ptr + check), d = __ldg(row_ptr + check + 1) - e0;
     uint32_t neg = 0;  // syndrome bit 0
     float pre = 0.0f;
     for (int k = 0; k < d; ++k) {  // prefix parities are recomputed below instead of stored: tiny kernel
-        const float v = __ldg(p.prior + __ldg(p.col + e0 + k));
+        const float v = __ldg(p.prior + __ldg(col + e0 + k));
         pre = bp_parity(pre, fabsf(bp_fold(v)));
         neg ^= bp_bits(v);
     }
     float suf = 0.0f;
     for (int k = d - 1; k >= 0; --k) {
         float P = 0.0f;
-        for (int j = 0; j < k; ++j) P = bp_parity(P, fabsf(bp_fold(__ldg(p.prior + __ldg(p.col + e0 + j)))));
-        const float x = bp_fold(__ldg(p.prior + __ldg(p.col + e0 + k)));
+        for (int j = 0; j < k; ++j) P = bp_parity(P, fabsf(bp_fold(__ldg(p.prior + __ldg(col + e0 + j)))));
+        const float x = bp_fold(__ldg(p.prior + __ldg(col + e0 + k)));
         const float mag = bp_unfold(bp_parity(P, suf));
         tab[e0 + k] = bp_float(bp_bits(mag) ^ ((neg ^ bp_bits(x)) & 0x80000000u));
         suf = bp_parity(suf, fabsf(x));
@@ -323,6 +340,9 @@ __global__ void __launch_bounds__(256) k_bp_first_fill(const BpDev p, const floa
     const int e_lo = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 8;
     float *msg = p.msg + ((size_t)tile * p.E) * 32 + lane;
     const int limit = bp_row_limit(p, tile, lane);
+    const size_t gb = (size_t)bp_graph(p, tile) * p.g_e;  // this tile's graph: its table and its edge -> row map
+    tab += gb;
+    edge_row += gb;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         const int e = e_lo + i;
@@ -427,7 +447,10 @@ __device__ __forceinline__ void bp_vn_dispatch(const BpDev &p, const BpVnItem &i
 
 // Degree class (DMIN .. DMAX].  The class of degree <= 1 is instantiated as <0, 1> and also takes isolated variables.
 template <int DMIN, int DMAX>
-__global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const int v_lo, const int v_hi, const int tiles)
+// Segmented CSR (p.class_end set): `cls` is the degree class, [v_lo, v_hi) = [0, largest class size over the graphs);
+// every tile takes its own graph's slice of the class and skips the j beyond it.
+__global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const int v_lo, const int v_hi, const int tiles,
+                                                           const int cls)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
     const int gw = blockIdx.x * wpc + warp, nw = gridDim.x * wpc;
@@ -437,6 +460,7 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const 
     // moves to the next item (stride nw) whose tile still has running trials; tile >= tiles: none left
     auto advance = [&](BpVnItem &it, bool first) {
         bool step = !first;
+        int g = 0, lo = v_lo;
         while (true) {
             if (step) {
                 it.tile += step_t;
@@ -446,13 +470,23 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const 
                     ++it.tile;
                 }
             }
-            if (it.tile >= tiles || !bp_tile_done(p, it.tile)) break;
             step = true;
+            if (it.tile >= tiles) break;
+            if (bp_tile_done(p, it.tile)) continue;
+            if (p.class_end) {  // this tile's graph: its slice [lo, hi) of the class
+                g = bp_graph(p, it.tile);
+                const int *ce = p.class_end + g * (kBpVnClassCount + 1);
+                lo = cls > 0 ? __ldg(ce + cls - 1) : 0;
+                if (it.j >= __ldg(ce + cls) - lo) continue;
+            }
+            break;
         }
         if (it.tile < tiles) {
-            it.var = __ldg(p.vn_order + v_lo + it.j);
-            it.p0 = __ldg(p.col_ptr + it.var);
-            it.d = __ldg(p.col_ptr + it.var + 1) - it.p0;  // in (DMIN, DMAX] (host guarantees)
+            it.var = __ldg(p.vn_order + (size_t)g * p.g_n + lo + it.j);
+            const int *cp = p.col_ptr + (size_t)g * p.g_cp + it.var;
+            const int c0 = __ldg(cp);
+            it.d = __ldg(cp + 1) - c0;  // in (DMIN, DMAX] (host guarantees)
+            it.p0 = g * p.g_e + c0;     // position in the (concatenated) csc_off table
         }
     };
     auto gather = [&](const BpVnItem &it, float (&c)[DMAX]) {
@@ -612,17 +646,27 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_tma(const BpDev p, co
 
 // Any degree (columns heavier than the largest register class): per-lane scratch [i][lane] in shared memory,
 // one CTA pass over (variable, tile) without prefetch.
-__global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_generic(const BpDev p, const int v_lo, const int v_hi)
+// Segmented CSR: cls >= 0 -> the tile's own slice of that class (v_lo = 0, v_hi = largest slice); cls < 0 -> [v_lo, v_hi)
+// of every graph's sorted order (all variables in the single-launch tail).
+__global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_generic(const BpDev p, const int v_lo, const int v_hi, const int cls)
 {
     SCALDPC_DYN_SMEM(float, smem);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
-    const int idx = v_lo + blockIdx.x * wpc + warp;
+    int idx = v_lo + blockIdx.x * wpc + warp;
     const int tile = blockIdx.y;
     if (idx >= v_hi) return;
     const uint32_t done = __ldg(p.done + tile);
     if (done == __ldg(p.valid + tile)) return;
-    const int var = __ldg(p.vn_order + idx);
-    const int p0 = __ldg(p.col_ptr + var), d = __ldg(p.col_ptr + var + 1) - p0;
+    const int g = bp_graph(p, tile);
+    if (p.class_end && cls >= 0) {
+        const int *ce = p.class_end + g * (kBpVnClassCount + 1);
+        const int lo = cls > 0 ? __ldg(ce + cls - 1) : 0;
+        idx = lo + (idx - v_lo);
+        if (idx >= __ldg(ce + cls)) return;
+    }
+    const int var = __ldg(p.vn_order + (size_t)g * p.g_n + idx);
+    const int *cp = p.col_ptr + (size_t)g * p.g_cp + var;
+    const int p0 = g * p.g_e + __ldg(cp), d = __ldg(cp + 1) - __ldg(cp);
     float *C = smem + (size_t)warp * 2 * p.dv_max * 32 + lane;
     float *F = C + (size_t)p.dv_max * 32;
     float *msg = p.msg + (size_t)tile * p.E * 32 + lane;
@@ -667,8 +711,11 @@ __global__ void __launch_bounds__(256) k_bp_syndrome(const BpDev p)
     if (check < p.m) {
         const uint32_t *dec = p.dec_w + (size_t)tile * p.n;
         uint32_t par = __ldg(p.synd_w + (size_t)tile * p.m + check);
-        const int e0 = __ldg(p.row_ptr + check), e1 = __ldg(p.row_ptr + check + 1);
-        for (int e = e0; e < e1; ++e) par ^= dec[__ldg(p.col + e)];
+        const int g = bp_graph(p, tile);
+        const int *rp = p.row_ptr + (size_t)g * p.g_rp + check;
+        const int *col = p.col + (size_t)g * p.g_e;
+        const int e0 = __ldg(rp), e1 = __ldg(rp + 1);
+        for (int e = e0; e < e1; ++e) par ^= dec[__ldg(col + e)];
         bad = par;
         if (p.nrows) {  // trials for which this check is inactive cannot fail it
             uint32_t act = 0;
@@ -739,6 +786,27 @@ __global__ void __launch_bounds__(256) k_bp_reset(uint32_t *valid, uint32_t *don
             conv[t] = 0;
         }
     }
+}
+
+// The same reset when the slot -> trial map is given (segmented CSR: every graph's trials fill their own tiles, the
+// last tile of a graph is padded with -1): valid = slots holding a trial.
+__global__ void __launch_bounds__(256) k_bp_reset_slots(uint32_t *valid, uint32_t *done, uint32_t *unsat, const int *orig,
+                                                        int *iters, int *conv, int tiles, int max_iter)
+{
+    const int tile = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tile >= tiles) return;
+    uint32_t v = 0;
+    for (int l = 0; l < 32; ++l) {
+        const int t = orig[tile * 32 + l];
+        if (t >= 0) {
+            v |= 1u << l;
+            iters[t] = max_iter;
+            conv[t] = 0;
+        }
+    }
+    valid[tile] = v;
+    done[tile] = 0;
+    unsat[tile] = 0;
 }
 
 // -----------------------------------------------------------------------------------------------------------
@@ -850,15 +918,17 @@ __global__ void __launch_bounds__(256) k_bp_prior_shared(const double *__restric
     }
 }
 
-__global__ void __launch_bounds__(256) k_bp_prior_tiled(const double *__restrict__ probs, float *__restrict__ out, int T, int n)
+// `orig` (may be null): slot -> trial map; null = identity.
+__global__ void __launch_bounds__(256) k_bp_prior_tiled(const double *__restrict__ probs, float *__restrict__ out, int T, int n,
+                                                        const int *__restrict__ orig)
 {
     __shared__ float sm[32][33];
     const int tile = blockIdx.y, v0 = blockIdx.x * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     for (int t = ty; t < 32; t += 8) {
-        const int trial = tile * 32 + t;
+        const int trial = orig ? orig[tile * 32 + t] : tile * 32 + t;
         float L = 0.0f;
-        if (trial < T && v0 + tx < n) {
+        if (trial >= 0 && trial < T && v0 + tx < n) {
             const double q = probs[(size_t)trial * n + v0 + tx];
             L = (float)log((1.0 - q) / q);
         }
@@ -870,14 +940,15 @@ __global__ void __launch_bounds__(256) k_bp_prior_tiled(const double *__restrict
 }
 
 // syndromes [T][m] bytes -> synd_w [tile][m] words
-__global__ void __launch_bounds__(256) k_bp_pack_synd(const uint8_t *__restrict__ synd, uint32_t *__restrict__ out, int T, int m)
+__global__ void __launch_bounds__(256) k_bp_pack_synd(const uint8_t *__restrict__ synd, uint32_t *__restrict__ out, int T, int m,
+                                                      const int *__restrict__ orig)
 {
     __shared__ uint8_t sm[32][36];
     const int tile = blockIdx.y, c0 = blockIdx.x * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     for (int t = ty; t < 32; t += 8) {
-        const int trial = tile * 32 + t;
-        sm[t][tx] = (trial < T && c0 + tx < m) ? (synd[(size_t)trial * m + c0 + tx] & 1) : 0;
+        const int trial = orig ? orig[tile * 32 + t] : tile * 32 + t;
+        sm[t][tx] = (trial >= 0 && trial < T && c0 + tx < m) ? (synd[(size_t)trial * m + c0 + tx] & 1) : 0;
     }
     __syncthreads();
     for (int c = ty; c < 32; c += 8) {

@@ -263,3 +263,108 @@ def _rep_code(n):
 
 codes = types.ModuleType("ldpc.codes")
 codes.rep_code = _rep_code
+
+
+class bp_decoder_multi:
+    """One decoder over several UNRELATED parity-check graphs of the same shape (segmented CSR; scaldpc_bp_create_multi).
+
+    The reference draws a new code for every simulated attack (hqc.py:1056) and calls `bp_decoder(H, ...)` once per
+    decode (hqc.py:694-699); a campaign of attacks is a batch whose trials live on different graphs.  Here:
+
+        dec = bp_decoder_multi([(row_ptr_0, col_0), (row_ptr_1, col_1), ...], shape=(m, n), max_iter=100,
+                               channel_probs=[...])
+        out = dec.decode_batch(graph_of, syndromes)       # graph_of[t] = which graph trial t is decoded on
+
+    Every trial's result equals bp_decoder(H_g, ...).decode_batch on its own graph."""
+
+    STAT_NAMES = bp_decoder.STAT_NAMES
+
+    def __init__(self, graphs, shape, max_iter=0, channel_probs=None, error_rate=None, device=0):
+        self.m, self.n = (int(x) for x in shape)
+        self.G = len(graphs)
+        if self.G < 1:
+            raise ValueError("at least one graph is needed")
+        rps, cols = [], []
+        for g in graphs:
+            if isinstance(g, tuple) and len(g) == 2 and np.ndim(g[0]) == 1:
+                rp, col = (np.ascontiguousarray(a, dtype=np.int32) for a in g)
+            else:
+                m, n, rp, col = _csr_from_any(g)
+                if (m, n) != (self.m, self.n):
+                    raise ValueError(f"every graph must be {self.m} x {self.n}")
+            if rp.shape != (self.m + 1,):
+                raise ValueError(f"row_ptr of every graph must have m + 1 = {self.m + 1} entries")
+            rps.append(rp)
+            cols.append(col)
+        row_ptr = np.ascontiguousarray(np.concatenate(rps), dtype=np.int32)
+        col = np.ascontiguousarray(np.concatenate(cols), dtype=np.int32)
+        if channel_probs is not None:
+            cp = np.asarray(channel_probs, dtype=np.float64)
+        elif error_rate is not None:
+            cp = np.full(self.n, float(error_rate), dtype=np.float64)
+        else:
+            raise ValueError("either error_rate or channel_probs is required")
+        if cp.shape != (self.n,):
+            raise ValueError(f"channel_probs must have length n = {self.n}")
+        self.channel_probs = np.ascontiguousarray(cp)
+        self.device = int(device)
+        self._h = C.c_void_p()
+        _lib.check(_lib.lib().scaldpc_bp_create_multi(self.G, self.m, self.n, row_ptr.ctypes.data, col.ctypes.data,
+                                                      int(max_iter), self.device, C.byref(self._h)))
+        vals = [C.c_int() for _ in range(4)]
+        _lib.check(_lib.lib().scaldpc_bp_info(self._h, *[C.byref(v) for v in vals]))
+        self.E, self.max_iter = vals[2].value, vals[3].value
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h and _lib._lib is not None:
+            _lib._lib.scaldpc_bp_destroy(h)
+
+    def decode_batch(self, graph_of, syndromes, channel_probs=None, *, truth=None, n_checks=None, want_llr=False,
+                     want_decoding=True, early_stop=True):
+        """graph_of (T,) int32; syndromes (T, m) uint8; channel_probs None / (n,) / (T, n) float64; n_checks optional (T,)
+        int32 (nested prefixes, as bp_decoder.decode_batch); truth optional (T, weight) int32 -> `stats` (T, 6) as
+        bp_decoder.decode_scored.  Returns dict(decoding, log_prob_ratios, iters, converged[, stats])."""
+        flags = 0 if early_stop else _lib.BP_NO_EARLY_STOP
+        synd = np.ascontiguousarray(syndromes, dtype=np.uint8)
+        T = synd.shape[0]
+        if synd.shape != (T, self.m):
+            raise ValueError(f"syndromes must be (T, {self.m}), got {synd.shape}")
+        gof = np.ascontiguousarray(graph_of, dtype=np.int32)
+        if gof.shape != (T,) or (T and (gof.min() < 0 or gof.max() >= self.G)):
+            raise ValueError(f"graph_of must be ({T},) with values in 0 .. {self.G - 1}")
+        cp = self.channel_probs if channel_probs is None else np.ascontiguousarray(channel_probs, dtype=np.float64)
+        if cp.ndim == 2:
+            if cp.shape != (T, self.n):
+                raise ValueError(f"channel_probs must be ({T}, {self.n})")
+            flags |= _lib.BP_PROBS_PER_TRIAL
+        elif cp.shape != (self.n,):
+            raise ValueError(f"channel_probs must have length {self.n}")
+        nc = None
+        if n_checks is not None:
+            nc = np.ascontiguousarray(n_checks, dtype=np.int32)
+            if nc.shape != (T,) or (nc < 0).any() or (nc > self.m).any():
+                raise ValueError(f"n_checks must be ({T},) with values in 0 .. {self.m}")
+        stats = tr = None
+        weight = 0
+        if truth is not None:
+            tr = np.ascontiguousarray(truth, dtype=np.int32)
+            if tr.ndim != 2 or tr.shape[0] != T:
+                raise ValueError(f"truth must be ({T}, weight)")
+            weight = tr.shape[1]
+            stats = np.empty((T, 6), np.int32)
+        dec = np.empty((T, self.n), np.uint8) if (want_decoding or truth is None) else None
+        llr = np.empty((T, self.n), np.float32) if want_llr else None
+        iters = np.empty(T, np.int32)
+        conv = np.empty(T, np.int32)
+        p = lambda a: None if a is None else a.ctypes.data  # noqa: E731
+        _lib.check(_lib.lib().scaldpc_bp_decode_multi(self._h, T, p(gof), p(nc), p(synd), p(cp), p(tr), weight, p(stats),
+                                                      p(dec), p(llr), p(iters), p(conv), flags, None))
+        out = dict(decoding=dec, log_prob_ratios=llr, iters=iters, converged=conv)
+        if stats is not None:
+            out["stats"] = stats
+        return out
+
+    @property
+    def launch_count(self) -> int:
+        return int(_lib.lib().scaldpc_bp_launch_count(self._h))

@@ -417,14 +417,14 @@ int hostmodel_bp_decode(int m, int n, const int32_t *row_ptr, const int32_t *col
             const int hi = g.class_end[c];
             if (hi > lo) {
                 switch (c) {
-                case 0: run_grid(3, 1, 2 * 32, k_bp_vn<0, 1>, p, lo, hi, cur_tiles); break;
-                case 1: run_grid(3, 1, 2 * 32, k_bp_vn<1, 4>, p, lo, hi, cur_tiles); break;
-                case 2: run_grid(3, 1, 2 * 32, k_bp_vn<4, 8>, p, lo, hi, cur_tiles); break;
-                case 3: run_grid(3, 1, 2 * 32, k_bp_vn<8, 12>, p, lo, hi, cur_tiles); break;
-                case 4: run_grid(3, 1, 2 * 32, k_bp_vn<12, 16>, p, lo, hi, cur_tiles); break;
-                case 5: run_grid(3, 1, 2 * 32, k_bp_vn<16, 24>, p, lo, hi, cur_tiles); break;
-                case 6: run_grid(3, 1, 2 * 32, k_bp_vn<24, 32>, p, lo, hi, cur_tiles); break;
-                default: run_grid((hi - lo + 1) / 2, cur_tiles, 2 * 32, k_bp_vn_generic, p, lo, hi);
+                case 0: run_grid(3, 1, 2 * 32, k_bp_vn<0, 1>, p, lo, hi, cur_tiles, -1); break;
+                case 1: run_grid(3, 1, 2 * 32, k_bp_vn<1, 4>, p, lo, hi, cur_tiles, -1); break;
+                case 2: run_grid(3, 1, 2 * 32, k_bp_vn<4, 8>, p, lo, hi, cur_tiles, -1); break;
+                case 3: run_grid(3, 1, 2 * 32, k_bp_vn<8, 12>, p, lo, hi, cur_tiles, -1); break;
+                case 4: run_grid(3, 1, 2 * 32, k_bp_vn<12, 16>, p, lo, hi, cur_tiles, -1); break;
+                case 5: run_grid(3, 1, 2 * 32, k_bp_vn<16, 24>, p, lo, hi, cur_tiles, -1); break;
+                case 6: run_grid(3, 1, 2 * 32, k_bp_vn<24, 32>, p, lo, hi, cur_tiles, -1); break;
+                default: run_grid((hi - lo + 1) / 2, cur_tiles, 2 * 32, k_bp_vn_generic, p, lo, hi, -1);
                 }
             }
             lo = hi;
@@ -463,6 +463,119 @@ int hostmodel_bp_decode(int m, int n, const int32_t *row_ptr, const int32_t *col
         conv[t] = vconv[t];
     }
     if (n_compactions) *n_compactions = compactions;
+    return 0;
+}
+
+
+// Segmented CSR (scaldpc_bp_create_multi + scaldpc_bp_decode_multi, bp.cu): G graphs of one shape, every graph's trials in
+// tiles of their own, no compaction.  row_ptr = G x (m+1), col = the G column arrays back to back, graph_of[T].
+int hostmodel_bp_decode_multi(int G, int m, int n, const int32_t *row_ptr, const int32_t *col, int max_iter, int T,
+                              const int32_t *graph_of, const uint8_t *synd, const double *probs, int early_stop,
+                              uint8_t *decoding, float *llr, int32_t *iters, int32_t *conv)
+{
+    std::vector<BpHostGraph> gs(G);
+    int Emax = 0, dc_max = 1, dv_max = 1;
+    size_t coff = 0;
+    for (int g = 0; g < G; ++g) {
+        std::string err;
+        int rc = build_bp_graph(m, n, row_ptr + (size_t)g * (m + 1), col + coff, gs[g], err);
+        if (rc) return rc;
+        coff += gs[g].E;
+        Emax = std::max(Emax, gs[g].E);
+        dc_max = std::max(dc_max, gs[g].dc_max);
+        dv_max = std::max(dv_max, gs[g].dv_max);
+    }
+    if (max_iter == 0) max_iter = n;
+    std::vector<int> a_row_ptr((size_t)G * (m + 1)), a_col((size_t)G * Emax, 0), a_col_ptr((size_t)G * (n + 1)), a_vn((size_t)G * n);
+    std::vector<uint32_t> a_csc((size_t)G * Emax, 0u);
+    std::vector<int> ce((size_t)G * (kBpVnClasses + 1)), cmax(kBpVnClasses + 1, 0);
+    for (int g = 0; g < G; ++g) {
+        const BpHostGraph &q = gs[g];
+        std::copy(q.row_ptr.begin(), q.row_ptr.end(), a_row_ptr.begin() + (size_t)g * (m + 1));
+        std::copy(q.col.begin(), q.col.end(), a_col.begin() + (size_t)g * Emax);
+        std::copy(q.col_ptr.begin(), q.col_ptr.end(), a_col_ptr.begin() + (size_t)g * (n + 1));
+        std::copy(q.vn_order.begin(), q.vn_order.end(), a_vn.begin() + (size_t)g * n);
+        std::copy(q.csc_off.begin(), q.csc_off.begin() + q.E, a_csc.begin() + (size_t)g * Emax);
+        for (int c = 0; c <= kBpVnClasses; ++c) {
+            ce[(size_t)g * (kBpVnClasses + 1) + c] = q.class_end[c];
+            cmax[c] = std::max(cmax[c], q.class_end[c] - (c ? q.class_end[c - 1] : 0));
+        }
+    }
+    // slots: every graph's trials fill tiles of their own (trial order preserved inside a graph)
+    std::vector<int> cnt(G, 0), first(G, 0);
+    for (int t = 0; t < T; ++t) {
+        if (graph_of[t] < 0 || graph_of[t] >= G) return SCALDPC_ERR_ARG;
+        ++cnt[graph_of[t]];
+    }
+    int tiles = 0;
+    for (int g = 0; g < G; ++g) {
+        first[g] = tiles;
+        tiles += (cnt[g] + 31) / 32;
+    }
+    std::vector<int> tile_graph(std::max(1, tiles)), orig((size_t)std::max(1, tiles) * 32, -1);
+    for (int g = 0; g < G; ++g)
+        for (int k = 0; k < (cnt[g] + 31) / 32; ++k) tile_graph[first[g] + k] = g;
+    std::fill(cnt.begin(), cnt.end(), 0);
+    for (int t = 0; t < T; ++t) orig[(size_t)first[graph_of[t]] * 32 + cnt[graph_of[t]]++] = t;
+    const size_t lanes = (size_t)tiles * 32;
+    std::vector<float> msg(std::max<size_t>(1, lanes * Emax), 0.0f), prior(n), post(lanes * n);
+    std::vector<uint32_t> synd_w((size_t)tiles * m, 0), valid(tiles, 0), done(tiles, 0), unsat(tiles, 0), dec_w((size_t)tiles * n, 0);
+    std::vector<int> vit(T, max_iter), vconv(T, 0), counts(max_iter + 2, 0);
+    run_grid((tiles + 255) / 256, 1, 256, k_bp_reset_slots, valid.data(), done.data(), unsat.data(), (const int *)orig.data(),
+             vit.data(), vconv.data(), tiles, max_iter);
+    for (size_t s_ = 0; s_ < lanes; ++s_) {
+        const int t = orig[s_];
+        if (t < 0) continue;
+        for (int c = 0; c < m; ++c)
+            if (synd[(size_t)t * m + c] & 1) synd_w[(s_ / 32) * m + c] |= 1u << (s_ % 32);
+    }
+    for (int v = 0; v < n; ++v) prior[v] = (float)log((1.0 - probs[v]) / probs[v]);
+    BpDev p;
+    p.m = m; p.n = n; p.E = Emax; p.dc_max = dc_max; p.dv_max = dv_max; p.per_trial_prior = 0;
+    p.row_ptr = a_row_ptr.data(); p.col = a_col.data(); p.col_ptr = a_col_ptr.data(); p.csc_off = a_csc.data();
+    p.vn_order = a_vn.data(); p.vn_desc = nullptr;
+    p.msg = msg.data(); p.prior = prior.data(); p.synd_w = synd_w.data(); p.dec_w = dec_w.data();
+    p.post = llr ? post.data() : nullptr;
+    p.done = done.data(); p.valid = valid.data(); p.unsat = unsat.data(); p.orig = orig.data();
+    p.iters = vit.data(); p.conv = vconv.data(); p.counts = counts.data(); p.nrows = nullptr;
+    p.tile_graph = tile_graph.data(); p.class_end = ce.data();
+    p.g_rp = m + 1; p.g_e = Emax; p.g_cp = n + 1; p.g_n = n;
+    std::vector<float> scratch((size_t)6 * std::max(dc_max, dv_max) * 32);
+    scaldpc_host_model_smem = scratch.data();
+    for (int it = 1; it <= max_iter; ++it) {
+        if (it == 1) run_grid(3, 1, 2 * 32, k_bp_cn<true>, p, tiles);
+        else run_grid(3, 1, 2 * 32, k_bp_cn<false>, p, tiles);
+        for (int c = 0; c <= kBpVnClasses; ++c) {
+            const int nv = cmax[c];
+            if (nv <= 0) continue;
+            switch (c) {
+            case 0: run_grid(3, 1, 2 * 32, k_bp_vn<0, 1>, p, 0, nv, tiles, c); break;
+            case 1: run_grid(3, 1, 2 * 32, k_bp_vn<1, 4>, p, 0, nv, tiles, c); break;
+            case 2: run_grid(3, 1, 2 * 32, k_bp_vn<4, 8>, p, 0, nv, tiles, c); break;
+            case 3: run_grid(3, 1, 2 * 32, k_bp_vn<8, 12>, p, 0, nv, tiles, c); break;
+            case 4: run_grid(3, 1, 2 * 32, k_bp_vn<12, 16>, p, 0, nv, tiles, c); break;
+            case 5: run_grid(3, 1, 2 * 32, k_bp_vn<16, 24>, p, 0, nv, tiles, c); break;
+            case 6: run_grid(3, 1, 2 * 32, k_bp_vn<24, 32>, p, 0, nv, tiles, c); break;
+            default: run_grid((nv + 1) / 2, tiles, 2 * 32, k_bp_vn_generic, p, 0, nv, c);
+            }
+        }
+        run_grid((m + 255) / 256, tiles, 256, k_bp_syndrome, p);
+        run_grid((tiles + 255) / 256, 1, 256, k_bp_finish_iter, p, tiles, it, early_stop, (int)(it == max_iter));
+        if (early_stop && it < max_iter && counts[it] == 0) break;
+    }
+    scaldpc_host_model_smem = nullptr;
+    for (size_t s_ = 0; s_ < lanes; ++s_) {
+        const int t = orig[s_];
+        if (t < 0) continue;
+        for (int v = 0; v < n; ++v) {
+            decoding[(size_t)t * n + v] = (dec_w[(s_ / 32) * n + v] >> (s_ % 32)) & 1u;
+            if (llr) llr[(size_t)t * n + v] = post[((s_ / 32) * n + v) * 32 + s_ % 32];
+        }
+    }
+    for (int t = 0; t < T; ++t) {
+        iters[t] = vit[t];
+        conv[t] = vconv[t];
+    }
     return 0;
 }
 

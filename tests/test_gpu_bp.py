@@ -314,3 +314,77 @@ def test_nested_graphs_hqc128_with_compaction():
     ok = w.success(batch, out["decoding"])
     rates = [ok[n_checks == R].mean() for R in levels]
     assert rates[-1] > rates[0]
+
+
+def test_segmented_csr_batch_of_unrelated_graphs():
+    """SURVEY.md 8f.2 / hqc.py:1056: every simulated attack draws its OWN code.  One batch over G different random codes
+    (scaldpc_bp_create_multi / scaldpc_bp_decode_multi, a graph per tile) == G single-graph fp64-oracle decodes: decisions,
+    iteration counts, convergence, posteriors, and hqc.decode's statistics; with each attack's decode-every ladder as
+    nested prefixes of ITS graph."""
+    from sca_ldpc_b200.ldpc import bp_decoder_multi
+
+    G = 9
+    ws = [HqcWorkload(variant=(997, 12), W=11, R=420, rho=0.97, seed=30 + g) for g in range(G)]
+    m, n = ws[0].m, ws[0].n
+    levels = np.array([140, 280, 420], np.int32)
+    per = [5, 1, 40, 3, 33, 2, 7, 32, 6]                       # trials per graph: ragged, one graph needs two tiles
+    graph_of = np.concatenate([np.full(c, g, np.int32) for g, c in enumerate(per)])
+    perm = np.random.RandomState(0).permutation(len(graph_of))  # the caller's order is arbitrary
+    graph_of = graph_of[perm]
+    T = len(graph_of)
+    synd = np.zeros((T, m), np.uint8)
+    truth = np.zeros((T, ws[0].omega), np.int32)
+    for g, w in enumerate(ws):
+        sel = np.nonzero(graph_of == g)[0]
+        b = w.generate(len(sel), seed=50 + g)
+        synd[sel], truth[sel] = b.syndromes, b.y
+    n_checks = levels[np.arange(T) % 3]
+    dec = bp_decoder_multi([(w.row_ptr, w.col) for w in ws], shape=(m, n), max_iter=30, channel_probs=ws[0].channel_probs)
+    out = dec.decode_batch(graph_of, synd, truth=truth, n_checks=n_checks, want_llr=True)
+    for g, w in enumerate(ws):
+        for R in levels:
+            sel = np.nonzero((graph_of == g) & (n_checks == R))[0]
+            if not len(sel):
+                continue
+            rp, col = w.row_ptr[: R + 1], w.col[: w.row_ptr[R]]
+            ref = O.BinaryBpOracle(csr=(rp, col), shape=(R, w.N + R), max_iter=30, channel_probs=w.channel_probs[: w.N + R]
+                                   ).decode_batch(np.ascontiguousarray(synd[sel, :R]))
+            assert np.array_equal(out["decoding"][sel, : w.N + R], ref["decoding"]), (g, R)
+            assert np.array_equal(out["iters"][sel], ref["iters"]) and np.array_equal(out["converged"][sel], ref["converged"])
+            for i, t in enumerate(sel):
+                assert util.llr_close(out["log_prob_ratios"][t, : w.N + R], ref["log_prob_ratios"][i]), (g, R, t)
+                assert out["stats"][t].tolist() == reference_stats(w.N, ref["decoding"][i], synd[t, :R], truth[t]), (g, R, t)
+    assert 0 < out["stats"][:, 5].sum() < T
+    # one graph behind the multi interface == the plain decoder
+    one = bp_decoder_multi([(ws[2].row_ptr, ws[2].col)], shape=(m, n), max_iter=30, channel_probs=ws[2].channel_probs)
+    sel = np.nonzero(graph_of == 2)[0]
+    a = one.decode_batch(np.zeros(len(sel), np.int32), synd[sel])
+    b = bp_decoder(csr=(ws[2].row_ptr, ws[2].col), shape=(m, n), max_iter=30, channel_probs=ws[2].channel_probs).decode_batch(synd[sel])
+    assert np.array_equal(a["decoding"], b["decoding"]) and np.array_equal(a["iters"], b["iters"])
+    with pytest.raises(ValueError):
+        dec.decode_batch(np.full(T, G, np.int32), synd)
+
+
+def test_segmented_csr_hqc128_full_size():
+    """Four different weight-50 codes of HQC-128 size, 24 trials each in one batch; every graph's first trials against the
+    fp64 oracle on that graph, the rest through the syndrome property."""
+    from sca_ldpc_b200.ldpc import bp_decoder_multi
+
+    ws = [HqcWorkload("hqc128", W=50, R=3000, rho=0.9942, seed=60 + g) for g in range(4)]
+    m, n = ws[0].m, ws[0].n
+    graph_of = np.tile(np.arange(4, dtype=np.int32), 24)
+    synd = np.zeros((96, m), np.uint8)
+    for g, w in enumerate(ws):
+        synd[graph_of == g] = w.generate(24, seed=70 + g).syndromes
+    dec = bp_decoder_multi([(w.row_ptr, w.col) for w in ws], shape=(m, n), max_iter=100, channel_probs=ws[0].channel_probs)
+    out = dec.decode_batch(graph_of, synd)
+    for g, w in enumerate(ws):
+        sel = np.nonzero(graph_of == g)[0]
+        ref = O.BinaryBpOracle(csr=(w.row_ptr, w.col), shape=(m, n), max_iter=100, channel_probs=w.channel_probs).decode_batch(synd[sel[:3]])
+        assert np.array_equal(out["decoding"][sel[:3]], ref["decoding"]) and np.array_equal(out["iters"][sel[:3]], ref["iters"])
+        rows = np.repeat(np.arange(m), np.diff(w.row_ptr))
+        for t in sel[out["converged"][sel].astype(bool)][:6]:
+            s = np.zeros(m, np.uint8)
+            np.bitwise_xor.at(s, rows, out["decoding"][t][w.col])
+            assert np.array_equal(s, synd[t])
+    assert out["converged"].mean() > 0.8

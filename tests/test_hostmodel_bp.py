@@ -122,3 +122,37 @@ def test_active_trial_compaction_is_transparent():
     ref = orc.decode_batch(synd, channel_probs=probs)
     assert np.array_equal(a["iters"], ref["iters"]) and np.array_equal(a["decoding"], ref["decoding"])
     assert (ref["converged"][[3, 40, 41, 77, 99]] == 0).all()
+
+
+def test_segmented_csr_batch_equals_single_graph_decodes():
+    """a batch over several UNRELATED graphs of one shape (the reference draws a new code per simulated
+    attack, hqc.py:1056) through the modelled kernels with per-tile graph tables == the fp64 oracle on every graph by
+    itself.  Trials of the graphs are interleaved, group sizes are not multiples of 32, one trial never converges."""
+    from sca_ldpc_b200.workloads import HqcWorkload
+
+    ws = [HqcWorkload(variant=(499, 6), W=9, R=230, rho=0.97, seed=s) for s in (3, 4, 5)]
+    m, n = ws[0].m, ws[0].n
+    T = 75
+    graph_of = (np.arange(T) * 7 % 3).astype(np.int32)          # interleaved; counts 25 / 25 / 25
+    graph_of[60:] = 1                                            # -> uneven groups, graph 1 spills into a second tile
+    synd = np.zeros((T, m), np.uint8)
+    for g, w in enumerate(ws):
+        sel = np.nonzero(graph_of == g)[0]
+        synd[sel] = w.generate(len(sel), seed=20 + g).syndromes
+    synd[7] = np.random.RandomState(1).randint(0, 2, m)          # garbage: runs to the iteration cap
+    out = util.hostmodel_bp_multi([(w.row_ptr, w.col) for w in ws], m, n, 25, graph_of, synd, ws[0].channel_probs)
+    seen_iters = set()
+    for g, w in enumerate(ws):
+        sel = np.nonzero(graph_of == g)[0]
+        ref = O.BinaryBpOracle(csr=(w.row_ptr, w.col), shape=(m, n), max_iter=25, channel_probs=w.channel_probs).decode_batch(synd[sel])
+        assert np.array_equal(out["decoding"][sel], ref["decoding"]), g
+        assert np.array_equal(out["iters"][sel], ref["iters"]) and np.array_equal(out["converged"][sel], ref["converged"]), g
+        for i, t in enumerate(sel):
+            assert util.llr_close(out["llr"][t], ref["log_prob_ratios"][i]), (g, t)
+        seen_iters |= set(ref["iters"].tolist())
+    assert out["iters"][7] == 25 and not out["converged"][7] and len(seen_iters) >= 3
+    # the graphs really differ: decoding graph 1's trials on graph 0 gives something else
+    w0 = ws[0]
+    sel = np.nonzero(graph_of == 1)[0][:8]
+    other = O.BinaryBpOracle(csr=(w0.row_ptr, w0.col), shape=(m, n), max_iter=25, channel_probs=w0.channel_probs).decode_batch(synd[sel])
+    assert not np.array_equal(other["decoding"], out["decoding"][sel])

@@ -116,6 +116,27 @@ def hostmodel_bp(row_ptr, col, m, n, max_iter, synd, probs, early_stop=True, wan
     return dict(decoding=dec, llr=llr, iters=iters, converged=conv, compactions=ncomp.value)
 
 
+def hostmodel_bp_multi(graphs, m, n, max_iter, graph_of, synd, probs, early_stop=True, want_llr=True):
+    """Segmented-CSR binary BP through the modelled kernels.  graphs: list of (row_ptr, col)."""
+    L = hostmodel()
+    L.hostmodel_bp_decode_multi.restype = C.c_int
+    row_ptr = np.ascontiguousarray(np.concatenate([np.asarray(g[0], np.int32) for g in graphs]), np.int32)
+    col = np.ascontiguousarray(np.concatenate([np.asarray(g[1], np.int32) for g in graphs]), np.int32)
+    graph_of = np.ascontiguousarray(graph_of, np.int32)
+    synd = np.ascontiguousarray(synd, np.uint8)
+    T = synd.shape[0]
+    probs = np.ascontiguousarray(probs, np.float64)
+    dec = np.zeros((T, n), np.uint8)
+    llr = np.zeros((T, n), np.float32) if want_llr else None
+    iters = np.zeros(T, np.int32)
+    conv = np.zeros(T, np.int32)
+    p = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    rc = L.hostmodel_bp_decode_multi(len(graphs), m, n, p(row_ptr), p(col), max_iter, T, p(graph_of), p(synd), p(probs),
+                                     int(early_stop), p(dec), p(llr), p(iters), p(conv))
+    assert rc == 0, rc
+    return dict(decoding=dec, llr=llr, iters=iters, converged=conv)
+
+
 def llr_close(a, b, atol=2e-3, rtol=2e-4):
     """fp32 LLR-domain posteriors against the fp64 ratio-domain oracle: same infinities, finite values close."""
     a = np.asarray(a, np.float64)
