@@ -320,6 +320,28 @@ class bp_decoder_multi:
         if h and _lib._lib is not None:
             _lib._lib.scaldpc_bp_destroy(h)
 
+    @classmethod
+    def from_prefixes(cls, row_ptr, col, shape, levels, **kw):
+        """The decode-every ladder of ONE growing H (hqc.py:953-984) as a family of graphs: graph k = the first levels[k]
+        rows of H = [Hin | I] (the later rows have no edges, the later identity columns are isolated).  A trial decoded on
+        graph k then costs what a decode on H_k costs -- bp_decoder.decode_batch(n_checks=...) on the full graph gives
+        the same results but makes every trial pay for all the rows.  Pass `graph_of` = level index and zero the
+        syndrome bits of the rows a trial does not use (decode_batch(..., n_checks=levels[graph_of]) does that)."""
+        m, n = (int(x) for x in shape)
+        row_ptr = np.ascontiguousarray(row_ptr, dtype=np.int32)
+        col = np.ascontiguousarray(col, dtype=np.int32)
+        graphs = []
+        for R in levels:
+            R = int(R)
+            if not 0 <= R <= m:
+                raise ValueError(f"level {R} is outside 0 .. m = {m}")
+            rp = row_ptr.copy()
+            rp[R:] = row_ptr[R]
+            graphs.append((rp, col[: row_ptr[R]]))
+        dec = cls(graphs, shape, **kw)
+        dec.levels = np.asarray(levels, dtype=np.int32)
+        return dec
+
     def decode_batch(self, graph_of, syndromes, channel_probs=None, *, truth=None, n_checks=None, want_llr=False,
                      want_decoding=True, early_stop=True):
         """graph_of (T,) int32; syndromes (T, m) uint8; channel_probs None / (n,) / (T, n) float64; n_checks optional (T,)
@@ -330,6 +352,9 @@ class bp_decoder_multi:
         T = synd.shape[0]
         if synd.shape != (T, self.m):
             raise ValueError(f"syndromes must be (T, {self.m}), got {synd.shape}")
+        if n_checks is not None and getattr(self, "levels", None) is not None:
+            # prefix graphs: a row beyond the trial's level has no edges, its syndrome bit must not count as unsatisfied
+            synd = np.where(np.arange(self.m)[None, :] < np.asarray(n_checks)[:, None], synd, 0).astype(np.uint8)
         gof = np.ascontiguousarray(graph_of, dtype=np.int32)
         if gof.shape != (T,) or (T and (gof.min() < 0 or gof.max() >= self.G)):
             raise ValueError(f"graph_of must be ({T},) with values in 0 .. {self.G - 1}")

@@ -388,3 +388,25 @@ def test_segmented_csr_hqc128_full_size():
             np.bitwise_xor.at(s, rows, out["decoding"][t][w.col])
             assert np.array_equal(s, synd[t])
     assert out["converged"].mean() > 0.8
+
+
+def test_prefix_graphs_equal_nested_decode():
+    """The decode-every ladder as a family of prefix graphs (bp_decoder_multi.from_prefixes: every level pays for its own
+    rows only) == the same ladder as per-trial row limits on the full graph (scaldpc_bp_decode_nested)."""
+    from sca_ldpc_b200.ldpc import bp_decoder_multi
+
+    w = HqcWorkload(variant=(997, 12), W=11, R=420, rho=0.97, seed=7)
+    T = 90
+    batch = w.generate(T, seed=3)
+    levels = np.array([100, 200, 300, 420], np.int32)
+    lvl = (np.arange(T) % 4).astype(np.int32)
+    n_checks = levels[lvl]
+    full = bp_decoder(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=30, channel_probs=w.channel_probs)
+    a = full.decode_scored(batch.syndromes, batch.y, n_checks=n_checks, want_decoding=True)
+    lad = bp_decoder_multi.from_prefixes(w.row_ptr, w.col, (w.m, w.n), levels, max_iter=30, channel_probs=w.channel_probs)
+    b = lad.decode_batch(lvl, batch.syndromes, truth=batch.y, n_checks=n_checks)
+    assert np.array_equal(a["iters"], b["iters"]) and np.array_equal(a["converged"], b["converged"])
+    assert np.array_equal(a["stats"], b["stats"])
+    for t in range(T):
+        R = n_checks[t]
+        assert np.array_equal(a["decoding"][t, : w.N + R], b["decoding"][t, : w.N + R]), t

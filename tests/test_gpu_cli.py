@@ -44,5 +44,5 @@ def test_kyber_simulate_command(tmp_path):
     out = tmp_path / "k.csv"
     rows = cli.main(["kyber_simulate", "--param-set", "768", "--accuracy", "0.995", "--runs", "2048", "--seed", "3",
                      "--check-blocks", "1", "--csv-output", str(out)])
-    assert rows[0]["trials"] == 2048 and rows[0]["success_rate"] > 0.9
+    assert rows[0]["trials"] == 2048 and rows[0]["success_rate"] > 0.8 and rows[0]["symbol_error_rate"] < 1e-3
     assert list(csv.DictReader(out.open()))[0]["alg"] == "kyber768"

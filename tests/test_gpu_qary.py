@@ -418,8 +418,8 @@ def test_early_termination_full_size(variant, cb, acc, nb, nbs):
     assert run["trial_iterations"] < 0.75 * T * 10
     assert np.array_equal(w.success(b, hard)[~differ], w.success(b, ref)[~differ])
     # observation-indexed priors and the on-device Monte-Carlo loop take the same flag
-    ob = w.generate_observed(2048, seed=1)
-    oh, _, _ = d.min_sum_observed(w.table, ob.obs, w.table_sum, ob.obs_sum, early_stop=True)
+    ob = w.generate_observed(T, seed=1)   # the same trials as b (the generator's stream depends on T)
+    oh, _, _ = d.min_sum_observed(w.table, ob.obs[:2048], w.table_sum, ob.obs_sum[:2048], early_stop=True)
     assert np.array_equal(oh, hard[:2048])
     sim_a = d.simulate(4096, 7, **w.simulate_kwargs)
     sim_b = d.simulate(4096, 7, early_stop=True, **w.simulate_kwargs)
