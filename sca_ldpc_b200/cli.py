@@ -20,7 +20,9 @@ where the decoder's input starts: check i is the true bit (y*r1)[b_i] of a measu
 idealised oracle's error rates (hqc.py:1001-1008: epsilon = (0.9942, 1.0) * (1 - error_rate), indexed by the true value),
 with certainty epsilon[true value] as hqc.py:684-690 feeds it to the decoder.  `oracle_calls` is therefore the number of
 measured checks (one idealised answer each), not the reference's decapsulation count.
-Every run of --runs is one simulated attack: its decode-every ladder is ONE nested-graph batch on the GPU.
+Every run of --runs is one simulated attack with ITS OWN random code (hqc.py:1056); the runs of a pass are ONE batch on
+the GPU: a segmented-CSR handle holding the runs' graphs (scaldpc_bp_create_multi), every run's decode-every ladder as
+nested prefixes of its graph (the lanes of that run's tile).
 """
 from __future__ import annotations
 
@@ -64,6 +66,8 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--accuracy", type=float, default=0.95, help="Kyber: per-bit accuracy of the plaintext-checking oracle.")
     ap.add_argument("--sum-weight", type=int, default=6, help="Kyber: row weight of H' (kyber.py:67-74).")
     ap.add_argument("--check-blocks", type=int, default=2, help="Kyber: check blocks of H (kyber.py:67-74).")
+    ap.add_argument("--shared-code", action="store_true",
+                    help="HQC: one code for all runs (default: a new code per run, as every reference process draws its own, hqc.py:1056)")
     ap.add_argument("--device", type=int, default=0)
     return ap
 
@@ -85,36 +89,40 @@ def _print_table(columns, rows, out=sys.stdout):
 
 
 # ---------------------------------------------------------------------------------------------------------------------
-def hqc_ladders(y, n, weight, decode_every, max_checks, eps, runs, rng):
+def hqc_ladders(y, n, weight, decode_every, max_checks, eps, runs, rng, shared_code=False):
     """Inputs of `runs` simulated attacks on the secret support y (hqc.py:1043-1164 restated from the decoder's side).
 
-    One code for the batch (the reference draws one code per process, hqc.py:1056): r1 = support of the circulant's
-    first column, measured positions b_0, b_1, ... in a per-run random order, check i of a run = (y * r1)[b_i] reported
-    with the idealised oracle's error rates.  Returns (row_ptr, col, levels, synd (runs, R), certainty (runs, R))."""
+    Per run (or once, with shared_code): r1 = support of a random weight-`weight` circulant's first column (hqc.py:1056-1059),
+    measured positions b_0 < b_1 < ..., check i = (y * r1)[b_i] reported with the idealised oracle's error rates.
+    Returns (graphs [(row_ptr, col)] one per run or one in all, levels, synd (runs, R), certainty (runs, R))."""
     from .workloads import sparse_first_row
 
-    r1 = sparse_first_row(n, weight, rng)                                    # make_code.py:220-244, distance_spectrum.py:47-87
     R = max_checks
-    bits = np.sort(rng.choice(n, R, replace=False))                          # which rows of Hgen get measured
-    cols = np.sort((bits[:, None] - r1[None, :]) % n, axis=1)                # row b of circulant(r1): columns (b - r) mod n
-    col = np.concatenate((cols, n + np.arange(R)[:, None]), axis=1).astype(np.int32).reshape(-1)
-    row_ptr = (np.arange(R + 1) * (weight + 1)).astype(np.int32)
     e = np.zeros(n, np.uint8)
     e[y] = 1
-    truth = (e[cols].sum(1) & 1).astype(np.uint8)                            # (y * r1)[b] mod 2, hqc.py:1062-1075, :911-940
-    # the idealised oracle (hqc.py:809-871): the answer for a bit whose true value is v is wrong with probability
-    # 1 - epsilon[v], and its certainty is epsilon[v]
-    eps_of = np.where(truth == 1, eps[1], eps[0])
-    flips = rng.random_sample((runs, R)) > eps_of[None, :]
-    synd = (truth[None, :] ^ flips).astype(np.uint8)
-    certainty = np.broadcast_to(eps_of[None, :], (runs, R))
+    row_ptr = (np.arange(R + 1) * (weight + 1)).astype(np.int32)
+    graphs, synd, certainty = [], np.zeros((runs, R), np.uint8), np.zeros((runs, R))
+    cols = None
+    for r in range(runs):
+        if cols is None or not shared_code:
+            r1 = sparse_first_row(n, weight, rng)                           # make_code.py:220-244, distance_spectrum.py:47-87
+            bits = np.sort(rng.choice(n, R, replace=False))                 # which rows of Hgen get measured
+            cols = np.sort((bits[:, None] - r1[None, :]) % n, axis=1)       # row b of circulant(r1): columns (b - r) mod n
+            col = np.concatenate((cols, n + np.arange(R)[:, None]), axis=1).astype(np.int32).reshape(-1)
+            graphs.append((row_ptr, col))
+            truth = (e[cols].sum(1) & 1).astype(np.uint8)                   # (y * r1)[b] mod 2, hqc.py:1062-1075, :911-940
+            # the idealised oracle (hqc.py:809-871): the answer for a bit whose true value is v is wrong with probability
+            # 1 - epsilon[v], and its certainty is epsilon[v]
+            eps_of = np.where(truth == 1, eps[1], eps[0])
+        synd[r] = truth ^ (rng.random_sample(R) > eps_of)
+        certainty[r] = eps_of
     levels = np.arange(decode_every, R + 1, decode_every, dtype=np.int32)
-    return row_ptr, col, levels, synd, certainty
+    return graphs, levels, synd, certainty
 
 
 def command_hqc_decode_bench(args, out=sys.stdout):
     from . import hqc_keys
-    from .ldpc import bp_decoder
+    from .ldpc import bp_decoder_multi
 
     rng = make_random_state(args.seed)
     name = f"hqc{args.param_set}"
@@ -132,22 +140,26 @@ def command_hqc_decode_bench(args, out=sys.stdout):
     eps = (1.0, 1.0) if isnan(args.error_rate) else (0.9942 * noise, 1.0 * noise)   # hqc.py:1001-1008
     R = args.max_checks or (n // 2 // args.decode_every) * args.decode_every
     R = max(args.decode_every, (R // args.decode_every) * args.decode_every)
-    row_ptr, col, levels, synd, certainty = hqc_ladders(y, n, args.code_weight, args.decode_every, R, eps, args.runs, rng)
     m, nn = R, n + R
     # hqc.py:684-690: omega/n for the message bits, 1 - certainty for every measured check (it depends on the check's true
-    # value, so the priors are per run)
+    # value, so the priors are per trial)
     base = np.full(n, omega / n)
-    dec = bp_decoder(csr=(row_ptr, col), shape=(m, nn), max_iter=args.max_iter,
-                     channel_probs=np.concatenate((base, np.full(R, 0.5))), device=args.device)
-    L = len(levels)
     rows, first_success = [], np.full(args.runs, -1)
-    per_pass = max(1, 2048 // L)                                             # runs per GPU batch (per-run priors: n doubles each)
-    truth = np.ascontiguousarray(np.broadcast_to(y.astype(np.int32), (per_pass * L, omega)))
+    levels = np.arange(args.decode_every, R + 1, args.decode_every, dtype=np.int32)
+    L = len(levels)
+    per_pass = max(1, min(64, 2048 // L))                                    # runs (= graphs) per GPU batch
     for r0 in range(0, args.runs, per_pass):
         rr = min(per_pass, args.runs - r0)
-        s = np.repeat(synd[r0:r0 + rr], L, axis=0)                           # (run, level) pairs: a prefix of the run's checks each
-        probs = np.concatenate((np.broadcast_to(base, (rr * L, n)), np.repeat(1.0 - certainty[r0:r0 + rr], L, axis=0)), axis=1)
-        sc = dec.decode_scored(s, truth[: rr * L], channel_probs=probs, n_checks=np.tile(levels, rr))
+        graphs, levels, synd, certainty = hqc_ladders(y, n, args.code_weight, args.decode_every, R, eps, rr, rng,
+                                                      shared_code=args.shared_code)
+        dec = bp_decoder_multi(graphs, shape=(m, nn), max_iter=args.max_iter,
+                               channel_probs=np.concatenate((base, np.full(R, 0.5))), device=args.device)
+        s = np.repeat(synd, L, axis=0)                                       # (run, level) pairs: a prefix of the run's checks each
+        probs = np.concatenate((np.broadcast_to(base, (rr * L, n)), np.repeat(1.0 - certainty, L, axis=0)), axis=1)
+        graph_of = np.repeat(np.zeros(rr, np.int32) if args.shared_code else np.arange(rr, dtype=np.int32), L)
+        truth = np.ascontiguousarray(np.broadcast_to(y.astype(np.int32), (rr * L, omega)))
+        sc = dec.decode_batch(graph_of, s, channel_probs=probs, truth=truth, n_checks=np.tile(levels, rr), want_decoding=False)
+        del dec
         st = sc["stats"].reshape(rr, L, 6)
         for i in range(rr):
             ok = np.nonzero(st[i, :, 5])[0]
@@ -162,8 +174,9 @@ def command_hqc_decode_bench(args, out=sys.stdout):
     _print_table(HQC_COLUMNS, rows if len(rows) <= 40 else rows[:20] + rows[-20:], out)
     done = first_success[first_success > 0]
     print(f"# {args.runs} simulated attacks on {name} (key file: {args.key_file or 'none, random y'}), code weight "
-          f"{args.code_weight}: {len(done)} recovered y; checks needed: median "
-          f"{int(np.median(done)) if len(done) else 'n/a'}, max {int(done.max()) if len(done) else 'n/a'}", file=out)
+          f"{args.code_weight}, {'one code for all runs' if args.shared_code else 'a new code per run'}: {len(done)} recovered y; "
+          f"checks needed: median {int(np.median(done)) if len(done) else 'n/a'}, max {int(done.max()) if len(done) else 'n/a'}",
+          file=out)
     if args.csv_output:
         _write_csv(args.csv_output, HQC_COLUMNS, rows)
     return rows

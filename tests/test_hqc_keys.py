@@ -88,14 +88,18 @@ def test_cli_arguments_and_ladders(tmp_path):
     assert a.seed == 3 and a.key_file == "k" and a.error_rate != a.error_rate
     rng = np.random.RandomState(1)
     n, y = 997, np.array([4, 50, 333, 700])
-    row_ptr, col, levels, synd, cert = cli.hqc_ladders(y, n, 7, 100, 300, (1.0, 1.0), 5, rng)
-    assert levels.tolist() == [100, 200, 300] and synd.shape == (5, 300) and (synd == synd[0]).all()   # no noise: all runs agree
-    rows = col.reshape(300, 8)
+    graphs, levels, synd, cert = cli.hqc_ladders(y, n, 7, 100, 300, (1.0, 1.0), 5, rng, shared_code=True)
+    assert len(graphs) == 1 and levels.tolist() == [100, 200, 300] and synd.shape == (5, 300) and (synd == synd[0]).all()
+    rows = graphs[0][1].reshape(300, 8)      # no noise, one code: all runs agree
     assert (rows[:, 7] == n + np.arange(300)).all() and (np.diff(rows[:, :7], axis=1) > 0).all()
     e = np.zeros(n, np.uint8)
     e[y] = 1
     assert np.array_equal(synd[0], e[rows[:, :7]].sum(1) & 1)
-    _, _, _, noisy, cert = cli.hqc_ladders(y, n, 7, 100, 300, (0.9, 1.0), 400, np.random.RandomState(1))
+    graphs, _, synd, _ = cli.hqc_ladders(y, n, 7, 100, 300, (1.0, 1.0), 4, np.random.RandomState(2))
+    assert len(graphs) == 4 and not np.array_equal(graphs[0][1], graphs[1][1])   # a new code per run (hqc.py:1056)
+    for g in range(4):
+        assert np.array_equal(synd[g], e[graphs[g][1].reshape(300, 8)[:, :7]].sum(1) & 1)
+    _, _, noisy, cert = cli.hqc_ladders(y, n, 7, 100, 300, (0.9, 1.0), 400, np.random.RandomState(1), shared_code=True)
     truth = noisy[:, :].mean(0)   # checks whose true value is 1 are never wrong (certainty 1), the others flip 10 % of the time
     assert set(np.unique(cert).tolist()) == {0.9, 1.0}
     assert np.all(truth[cert[0] == 1.0] == 1.0) and 0.05 < truth[cert[0] == 0.9].mean() < 0.15
