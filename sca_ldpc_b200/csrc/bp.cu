@@ -63,10 +63,9 @@ struct scaldpc_bp {
     size_t smem_cn = 0;
     int vn_occ[8] = {0};  // bit pass: resident CTAs per SM of each degree-class kernel
     int vn_single_tiles = 64;  // at most this many tiles: one any-degree launch per bit pass (SCALDPC_BP_VN_SINGLE=n)
-    bool vn_tma = false;  // SCALDPC_BP_VN_TMA=1: column gather by bulk-async copies (k_bp_vn_tma) instead of k_bp_vn.
-                          // Measured on hqc128 / hqc256: 1.41 / 1.98 ms against 1.35 / 1.91 ms -- the per-lane bulk copies
-                          // are serialised (one UBLKCP per lane) and four columns in flight per warp buy nothing, so
-                          // the register-prefetch kernel stays the default.
+    // (round 1 also had k_bp_vn_tma: column gather by per-lane bulk-async copies into a 4-stage ring.  Measured on hqc128 /
+    // hqc256: 1.41 / 1.98 ms against 1.35 / 1.91 ms for the register-prefetch kernel -- one UBLKCP per lane is serialised --
+    // so it was removed in round 2.)
     int vn_gen_wpc = 1;   // warps per CTA of the shared-memory kernel for heavier columns
     size_t smem_vn = 0;
     std::mutex mu;
@@ -207,6 +206,8 @@ BpDev view(const scaldpc_bp *h, int cur, bool per_trial_prior, bool want_post)
     p.conv = h->d_conv;
     p.counts = h->d_counts;
     p.nrows = h->cur_nrows;
+    p.first_tab = h->d_first_tab;
+    p.edge_row = h->d_edge_row;
     p.g_rp = h->m + 1;
     p.g_e = h->E;
     p.g_cp = h->n + 1;
@@ -233,44 +234,30 @@ int launch_cn(scaldpc_bp *h, const BpDev &p, int tiles, bool first, cudaStream_t
 }
 
 typedef void (*bp_vn_fn)(const BpDev, const int, const int, const int, const int);
-typedef void (*bp_vn_tma_fn)(const BpDev, const int, const int, const int);
-bp_vn_fn vn_class_fn(int c)
+bp_vn_fn vn_class_fn(int c, bool first = false)
 {
+#define CLS(A_, B_) return first ? k_bp_vn<A_, B_, true> : k_bp_vn<A_, B_, false>
     switch (c) {
-    case 0: return k_bp_vn<0, 1>;
-    case 1: return k_bp_vn<1, 4>;
-    case 2: return k_bp_vn<4, 8>;
-    case 3: return k_bp_vn<8, 12>;
-    case 4: return k_bp_vn<12, 16>;
-    case 5: return k_bp_vn<16, 24>;
-    case 6: return k_bp_vn<24, 32>;
+    case 0: CLS(0, 1);
+    case 1: CLS(1, 4);
+    case 2: CLS(4, 8);
+    case 3: CLS(8, 12);
+    case 4: CLS(12, 16);
+    case 5: CLS(16, 24);
+    case 6: CLS(24, 32);
     default: return nullptr;
     }
+#undef CLS
 }
-
-// TMA-gather variants of the register classes above degree 1 (bp_kernels.cuh k_bp_vn_tma).
-bp_vn_tma_fn vn_class_tma_fn(int c)
-{
-    switch (c) {
-    case 1: return k_bp_vn_tma<1, 4>;
-    case 2: return k_bp_vn_tma<4, 8>;
-    case 3: return k_bp_vn_tma<8, 12>;
-    case 4: return k_bp_vn_tma<12, 16>;
-    case 5: return k_bp_vn_tma<16, 24>;
-    case 6: return k_bp_vn_tma<24, 32>;
-    default: return nullptr;
-    }
-}
-size_t vn_tma_smem(int c) { return (size_t)kBpVnWarps * kBpVnStages * kBpVnClass[c] * 32 * sizeof(float); }
 
 // Bit pass: one persistent launch per non-empty degree class (variables are sorted by degree); columns heavier than
 // the largest register class go through the shared-memory kernel.
-int launch_vn(scaldpc_bp *h, const BpDev &p, int tiles, cudaStream_t st)
+int launch_vn(scaldpc_bp *h, const BpDev &p, int tiles, cudaStream_t st, bool first = false)
 {
     if (tiles <= h->vn_single_tiles) {
         // few tiles (the non-converging tail after compaction): the iteration is bound by kernel launches, so ONE launch
         // of the any-degree kernel over all variables replaces one launch per degree class (same arithmetic)
-        k_bp_vn_generic<<<dim3((h->n + h->vn_gen_wpc - 1) / h->vn_gen_wpc, tiles), h->vn_gen_wpc * 32, h->smem_vn, st>>>(p, 0, h->n, -1);
+        k_bp_vn_generic<<<dim3((h->n + h->vn_gen_wpc - 1) / h->vn_gen_wpc, tiles), h->vn_gen_wpc * 32, h->smem_vn, st>>>(p, 0, h->n, -1, first);
         ++h->launches;
         SCALDPC_CUDA(cudaGetLastError());
         return 0;
@@ -284,13 +271,10 @@ int launch_vn(scaldpc_bp *h, const BpDev &p, int tiles, cudaStream_t st)
             if (c < kBpVnClasses) {
                 const long long items = (long long)tiles * (hi - lo);
                 const int ctas = (int)std::min<long long>((long long)h->num_sms * h->vn_occ[c], (items + kBpVnWarps - 1) / kBpVnWarps);
-                if (h->vn_tma && !multi && vn_class_tma_fn(c))
-                    vn_class_tma_fn(c)<<<std::max(1, ctas), kBpVnWarps * 32, vn_tma_smem(c), st>>>(p, lo, hi, tiles);
-                else
-                    vn_class_fn(c)<<<std::max(1, ctas), kBpVnWarps * 32, 0, st>>>(p, lo, hi, tiles, multi ? c : -1);
+                vn_class_fn(c, first)<<<std::max(1, ctas), kBpVnWarps * 32, 0, st>>>(p, lo, hi, tiles, multi ? c : -1);
             } else {
                 k_bp_vn_generic<<<dim3((hi - lo + h->vn_gen_wpc - 1) / h->vn_gen_wpc, tiles), h->vn_gen_wpc * 32, h->smem_vn, st>>>(
-                    p, lo, hi, multi ? c : -1);
+                    p, lo, hi, multi ? c : -1, first);
             }
             ++h->launches;
         }
@@ -428,16 +412,9 @@ static int bp_create_impl(int G, int m, int n, const int32_t *row_ptr, const int
     SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_cn<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_cn));
     if (h->smem_vn)
         SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_vn_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_vn));
-    h->vn_tma = getenv("SCALDPC_BP_VN_TMA") != nullptr && G == 1;
     if (const char *e = getenv("SCALDPC_BP_VN_SINGLE")) h->vn_single_tiles = atoi(e);
     for (int c = 0; c < kBpVnClasses; ++c) {
-        if (h->vn_tma && vn_class_tma_fn(c)) {
-            SCALDPC_CUDA(cudaFuncSetAttribute(vn_class_tma_fn(c), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vn_tma_smem(c)));
-            SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->vn_occ[c], vn_class_tma_fn(c), kBpVnWarps * 32,
-                                                                       vn_tma_smem(c)));
-        } else {
-            SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->vn_occ[c], vn_class_fn(c), kBpVnWarps * 32, 0));
-        }
+        SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->vn_occ[c], vn_class_fn(c), kBpVnWarps * 32, 0));
         h->vn_occ[c] = std::max(1, h->vn_occ[c]);
     }
     SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->cn_occ[0], k_bp_cn<false>, h->cn_warps * 32, h->smem_cn));
@@ -638,16 +615,25 @@ static int bp_decode_impl(scaldpc_bp *h, int T, const uint8_t *synd, const doubl
     for (; it <= h->max_iter; ++it) {
         const bool last = it == h->max_iter;
         const BpDev p = view(h, cur, probs_t, want_post);
+        bool vn_first = false;
         if (it == 1 && !probs_t && !getenv("SCALDPC_BP_NO_FIRST_TABLE")) {
-            // shared priors: the first check-to-bit messages differ between trials only in sign (bp_kernels.cuh)
+            // shared priors: the first check-to-bit messages differ between trials only in sign (bp_kernels.cuh): one
+            // table per graph; the first bit pass forms +-tab[e] itself (k_bp_vn<.., FIRST>), so iteration 1 writes the
+            // message array once and never reads it.  SCALDPC_BP_FIRST_FILL=1: round 1's way (k_bp_first_fill streams
+            // the messages out, the ordinary bit pass reads them back) -- kept for the bit-identity test.
             k_bp_first_table<<<dim3((h->m + 127) / 128, h->G), 128, 0, st>>>(p, h->d_first_tab);
-            k_bp_first_fill<<<dim3((h->E + 63) / 64, cur_tiles), 256, 0, st>>>(p, h->d_first_tab, h->d_edge_row, cur_tiles);
-            h->launches += 2;
+            ++h->launches;
+            if (getenv("SCALDPC_BP_FIRST_FILL")) {
+                k_bp_first_fill<<<dim3((h->E + 63) / 64, cur_tiles), 256, 0, st>>>(p, h->d_first_tab, h->d_edge_row, cur_tiles);
+                ++h->launches;
+            } else {
+                vn_first = true;
+            }
             SCALDPC_CUDA(cudaGetLastError());
         } else if ((rc = launch_cn(h, p, cur_tiles, it == 1, st))) {
             return rc;
         }
-        if ((rc = launch_vn(h, p, cur_tiles, st))) return rc;
+        if ((rc = launch_vn(h, p, cur_tiles, st, vn_first))) return rc;
         k_bp_syndrome<<<dim3((h->m + 255) / 256, cur_tiles), 256, 0, st>>>(p);
         k_bp_finish_iter<<<(cur_tiles + 255) / 256, 256, 0, st>>>(p, cur_tiles, it, early, last);
         h->launches += 2;

@@ -69,6 +69,10 @@ struct BpDev {
     const int *tile_graph = nullptr;  // [tiles]
     int g_rp = 0, g_e = 0, g_cp = 0, g_n = 0;  // strides: m+1 (row_ptr), E = max edges (col, csc_off, first table), n+1, n
     const int *class_end = nullptr;   // [G][kBpVnClasses+1]: end of every degree class in each graph's sorted variable order
+    // first iteration with shared priors: the check-to-bit messages are +-first_tab[e] (k_bp_first_table); the FIRST variant
+    // of the bit pass forms them on the fly instead of reading a message array that k_bp_first_fill would have to write
+    const float *first_tab = nullptr;  // [G][E]
+    const int *edge_row = nullptr;     // [G][E] check of every edge
 };
 
 constexpr int kBpVnClassCount = 7;  // == kBpVnClasses (bp_graph.h)
@@ -291,7 +295,6 @@ __global__ void __launch_bounds__(kBpCnWarpsMax * 32) k_bp_cn(const BpDev p, con
     }
 }
 
-#ifndef SCALDPC_HOST_MODEL
 // -----------------------------------------------------------------------------------------------------------
 // First check pass when all trials share one prior vector (the HQC call site: channel_probs is one list,
 // hqc.py:684-699).  Then upstream's init b2c = p/(1-p) is the same for every trial, and so is the magnitude of every
@@ -330,6 +333,7 @@ __global__ void __launch_bounds__(128) k_bp_first_table(const BpDev p, float *__
     }
 }
 
+#ifndef SCALDPC_HOST_MODEL
 // One warp per (tile, edge), lane = trial.  edge_row[e] = check of edge e.
 __global__ void __launch_bounds__(256) k_bp_first_fill(const BpDev p, const float *__restrict__ tab,
                                                        const int *__restrict__ edge_row, const int tiles)
@@ -401,52 +405,73 @@ struct BpVnItem {
 // `base` + byte offset, with the base kept as an opaque 64-bit register so that the address is one 64-bit add.
 __device__ __forceinline__ float *bp_at(float *base, uint32_t byte_off) { return (float *)((char *)base + byte_off); }
 
-// The two sweeps of one variable of degree exactly D (straight-line code, no guards).
+// The two sweeps of one variable of degree exactly D (straight-line code, no guards).  `o` = the byte offsets of the
+// column's lines (loaded once by the gather).  Upstream resets a NaN running value to the neutral element; a NaN can only
+// appear when +inf meets -inf, and then the forward total is NaN too, so the sweeps run WITHOUT the per-step tests and a
+// NaN total sends the lane through the tested version (identical results; 4 fewer instructions per edge otherwise).
 template <int D, int DMAX>
 __device__ __forceinline__ void bp_vn_body(const BpDev &p, const BpVnItem &it, int lane, const float (&c)[DMAX],
-                                           const float prior)
+                                           const uint32_t (&o)[DMAX], const float prior)
 {
     const uint32_t done = __ldg(p.done + it.tile);
     float *msg = p.msg + (size_t)it.tile * p.E * 32 + lane;
 #ifndef SCALDPC_HOST_MODEL
     asm volatile("" : "+l"(msg));
 #endif
-    const uint32_t *off = p.csc_off + it.p0;
     float F[D > 0 ? D : 1];
     float temp = prior;
 #pragma unroll
     for (int i = 0; i < D; ++i) {
         F[i] = temp;
         temp += c[i];
-        if (temp != temp) temp = 0.0f;
     }
-    const float post = temp;
-    temp = 0.0f;
+    float post = temp;
+    if (post == post) {
+        temp = 0.0f;
 #pragma unroll
-    for (int i = D - 1; i >= 0; --i) {
-        *bp_at(msg, __ldg(off + i)) = bp_fold(F[i] + temp);
-        temp += c[i];
-        if (temp != temp) temp = 0.0f;
+        for (int i = D - 1; i >= 0; --i) {
+            *bp_at(msg, o[i]) = bp_fold(F[i] + temp);
+            temp += c[i];
+        }
+    } else {  // rare: +inf and -inf among the column's messages -- upstream's "NaN -> neutral element" semantics
+        temp = prior;
+#pragma unroll
+        for (int i = 0; i < D; ++i) {
+            F[i] = temp;
+            temp += c[i];
+            if (temp != temp) temp = 0.0f;
+        }
+        post = temp;
+        temp = 0.0f;
+#pragma unroll
+        for (int i = D - 1; i >= 0; --i) {
+            *bp_at(msg, o[i]) = bp_fold(F[i] + temp);
+            temp += c[i];
+            if (temp != temp) temp = 0.0f;
+        }
     }
     bp_vn_decide(p, it.tile, it.var, lane, done, post);
 }
 
 template <int D, int DMIN, int DMAX>
 __device__ __forceinline__ void bp_vn_dispatch(const BpDev &p, const BpVnItem &it, int lane, const float (&c)[DMAX],
-                                               const float prior)
+                                               const uint32_t (&o)[DMAX], const float prior)
 {
     if constexpr (D < DMIN) {
-        bp_vn_body<DMAX, DMAX>(p, it, lane, c, prior);  // unreachable for a correctly sorted class; keeps the code total
+        bp_vn_body<DMAX, DMAX>(p, it, lane, c, o, prior);  // unreachable for a correctly sorted class; keeps the code total
     } else {
         if (it.d == D)
-            bp_vn_body<D, DMAX>(p, it, lane, c, prior);
+            bp_vn_body<D, DMAX>(p, it, lane, c, o, prior);
         else
-            bp_vn_dispatch<D - 1, DMIN, DMAX>(p, it, lane, c, prior);
+            bp_vn_dispatch<D - 1, DMIN, DMAX>(p, it, lane, c, o, prior);
     }
 }
 
 // Degree class (DMIN .. DMAX].  The class of degree <= 1 is instantiated as <0, 1> and also takes isolated variables.
-template <int DMIN, int DMAX>
+// FIRST (iteration 1, shared priors): the incoming messages are not read from memory but formed from the first-pass table,
+// c = +-first_tab[e] with the sign of the trial's syndrome bit of the edge's check (what k_bp_first_fill would have written;
+// an inactive check of a nested decode sends +0) -- the first iteration then writes the message array once and never reads it.
+template <int DMIN, int DMAX, bool FIRST>
 // Segmented CSR (p.class_end set): `cls` is the degree class, [v_lo, v_hi) = [0, largest class size over the graphs);
 // every tile takes its own graph's slice of the class and skips the j beyond it.
 __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const int v_lo, const int v_hi, const int tiles,
@@ -489,15 +514,28 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const 
             it.p0 = g * p.g_e + c0;     // position in the (concatenated) csc_off table
         }
     };
-    auto gather = [&](const BpVnItem &it, float (&c)[DMAX]) {
+    auto gather = [&](const BpVnItem &it, float (&c)[DMAX], uint32_t (&o)[DMAX]) {
         float *src = p.msg + (size_t)it.tile * p.E * 32 + lane;
 #ifndef SCALDPC_HOST_MODEL
         asm volatile("" : "+l"(src));
 #endif
         const uint32_t *off = p.csc_off + it.p0;
+        const int gb = FIRST ? bp_graph(p, it.tile) * p.g_e : 0;
+        const int limit = FIRST ? bp_row_limit(p, it.tile, lane) : 0;
+        const uint32_t *sw = p.synd_w + (size_t)it.tile * p.m;
 #pragma unroll
         for (int i = 0; i < DMAX; ++i)
-            if ((DMIN > 0 && i <= DMIN) || i < it.d) c[i] = *bp_at(src, __ldg(off + i));  // d > DMIN: the first are unguarded
+            if ((DMIN > 0 && i <= DMIN) || i < it.d) {  // d > DMIN: the first are unguarded
+                o[i] = __ldg(off + i);
+                if (FIRST) {
+                    const int e = gb + (int)(o[i] >> 7);
+                    const int row = __ldg(p.edge_row + e);
+                    const uint32_t v = bp_bits(__ldg(p.first_tab + e)) ^ ((__ldg(sw + row) >> lane) << 31);
+                    c[i] = row < limit ? bp_float(v) : 0.0f;
+                } else {
+                    c[i] = *bp_at(src, o[i]);
+                }
+            }
     };
 
     BpVnItem cur;
@@ -505,150 +543,36 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const 
     cur.j = gw - cur.tile * nv;
     advance(cur, true);
     float c[DMAX], cn[DMAX];
+    uint32_t o[DMAX], on[DMAX];
     float pr = 0.0f, prn = 0.0f;  // the variable's prior travels with its column (44 % of the stall samples sat on it)
     if (cur.tile < tiles) {
-        gather(cur, c);
+        gather(cur, c, o);
         pr = bp_prior_of(p, cur.tile, cur.var, lane);
     }
     while (cur.tile < tiles) {
         BpVnItem nxt = cur;
         advance(nxt, false);
         if (nxt.tile < tiles) {
-            gather(nxt, cn);
+            gather(nxt, cn, on);
             prn = bp_prior_of(p, nxt.tile, nxt.var, lane);
         }
-        bp_vn_dispatch<DMAX, (DMIN == 0 ? 0 : DMIN + 1), DMAX>(p, cur, lane, c, pr);
+        bp_vn_dispatch<DMAX, (DMIN == 0 ? 0 : DMIN + 1), DMAX>(p, cur, lane, c, o, pr);
         cur = nxt;
         pr = prn;
 #pragma unroll
-        for (int i = 0; i < DMAX; ++i) c[i] = cn[i];
+        for (int i = 0; i < DMAX; ++i) {
+            c[i] = cn[i];
+            o[i] = on[i];
+        }
     }
 }
-
-#ifndef SCALDPC_HOST_MODEL
-// The same pass with the column gather done by the TMA engine.  The d lines of a column are scattered, but each is one
-// 128-byte bulk-async copy: lane i of the warp issues the copy of edge i (ONE warp instruction for the whole column)
-// into a shared-memory ring of kBpVnStages columns per warp, completion counted on one mbarrier per stage.  A warp
-// always has kBpVnStages columns in flight (k_bp_vn: one), nothing waits in registers, and the address arithmetic of
-// the gather runs once per lane instead of once per edge.  Arithmetic and stores are bp_vn_body's: results are
-// bit-identical to k_bp_vn (which remains the host-model / fallback kernel and serves the degree <= 1 class).
-constexpr int kBpVnStages = 4;
-
-// An item of k_bp_vn_tma on its way through the software pipeline.
-struct BpVnSlot {
-    BpVnItem it;
-    uint32_t off;  // lane i < d: byte offset of edge i's line (csc_off[p0 + i])
-    float prior;   // channel LLR of the variable (per lane when the priors are per trial)
-};
-
-template <int DMIN, int DMAX>
-__global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_tma(const BpDev p, const int v_lo, const int v_hi, const int tiles)
-{
-    extern __shared__ __align__(128) float sc_vn_smem[];  // [warp][stage][DMAX][32]
-    __shared__ uint64_t bars[kBpVnWarps][kBpVnStages];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
-    const int gw = blockIdx.x * wpc + warp, nw = gridDim.x * wpc;
-    const int nv = v_hi - v_lo;
-    const int step_t = nw / nv, step_j = nw - step_t * nv;
-    float *ring = sc_vn_smem + (size_t)warp * kBpVnStages * DMAX * 32;
-
-    // Three pipeline steps, one loop iteration apart, so that no load is consumed in the iteration that issues it:
-    //   step()     next (tile, j) whose tile still runs; ONE 16-byte load of {var, p0, d}
-    //   resolve()  per-lane line offset + the variable's prior (needs var / p0 of the previous step)
-    //   issue()    lane i < d copies line i of the column into a free stage (needs the offsets)
-    auto step = [&](BpVnItem &it, bool first) {
-        bool go = !first;
-        while (true) {
-            if (go) {
-                it.tile += step_t;
-                it.j += step_j;
-                if (it.j >= nv) {
-                    it.j -= nv;
-                    ++it.tile;
-                }
-            }
-            if (it.tile >= tiles || !bp_tile_done(p, it.tile)) break;
-            go = true;
-        }
-        if (it.tile < tiles) {
-            const int4 dsc = __ldg(p.vn_desc + v_lo + it.j);
-            it.var = dsc.x;
-            it.p0 = dsc.y;
-            it.d = dsc.z;  // in (DMIN, DMAX], d >= 1 here
-        }
-    };
-    auto resolve = [&](const BpVnItem &it) {
-        BpVnSlot s;
-        s.it = it;
-        s.off = 0;
-        s.prior = 0.0f;
-        if (it.tile < tiles) {
-            if (lane < it.d) s.off = __ldg(p.csc_off + it.p0 + lane);
-            s.prior = bp_prior_of(p, it.tile, it.var, lane);
-        }
-        return s;
-    };
-    auto issue = [&](const BpVnSlot &sl, int s) {
-        uint64_t *bar = &bars[warp][s];
-        if (lane == 0) sc_mbar_expect_tx(bar, (uint32_t)sl.it.d * 128u);
-        __syncwarp();
-        if (lane < sl.it.d)
-            sc_bulk_g2s(ring + ((size_t)s * DMAX + lane) * 32, (const char *)(p.msg + (size_t)sl.it.tile * p.E * 32) + sl.off, 128u, bar);
-    };
-
-    if (lane < kBpVnStages) sc_mbar_init(&bars[warp][lane], 1);
-    __syncwarp();
-
-    // f[0] is the current item, f[1 .. S-1] are in flight (f[k] sits in stage (head + k) % S), r is resolved and waits
-    // for a free stage, x is the item after r (its descriptor load is in flight)
-    BpVnSlot f[kBpVnStages], r;
-    BpVnItem x;
-    x.tile = gw / nv;
-    x.j = gw - x.tile * nv;
-    step(x, true);
-#pragma unroll
-    for (int k = 0; k < kBpVnStages; ++k) {
-        f[k] = resolve(x);
-        if (x.tile < tiles) step(x, false);
-    }
-    r = resolve(x);
-    if (x.tile < tiles) step(x, false);
-#pragma unroll
-    for (int k = 0; k < kBpVnStages; ++k)
-        if (f[k].it.tile < tiles) issue(f[k], k);
-
-    int head = 0;
-    uint32_t phases = 0;  // bit s = parity to wait for on stage s
-    while (f[0].it.tile < tiles) {
-        sc_mbar_wait(&bars[warp][head], (phases >> head) & 1u);
-        phases ^= 1u << head;
-        float c[DMAX];
-        const float *st = ring + (size_t)head * DMAX * 32 + lane;
-#pragma unroll
-        for (int i = 0; i < DMAX; ++i)
-            if ((DMIN > 0 && i <= DMIN) || i < f[0].it.d) c[i] = st[i * 32];
-        const BpVnSlot cur = f[0];
-#pragma unroll
-        for (int k = 0; k + 1 < kBpVnStages; ++k) f[k] = f[k + 1];
-        f[kBpVnStages - 1] = r;
-        __syncwarp();  // every lane has drained the stage
-        if (r.it.tile < tiles) {
-            sc_fence_proxy_async();
-            issue(r, head);
-        }
-        r = resolve(x);
-        if (x.tile < tiles) step(x, false);
-        head = head + 1 == kBpVnStages ? 0 : head + 1;
-        bp_vn_dispatch<DMAX, (DMIN == 0 ? 0 : DMIN + 1), DMAX>(p, cur.it, lane, c, cur.prior);
-    }
-}
-#endif
 
 // Any degree (columns heavier than the largest register class): per-lane scratch [i][lane] in shared memory,
 // one CTA pass over (variable, tile) without prefetch.
 // Segmented CSR: cls >= 0 -> the tile's own slice of that class (v_lo = 0, v_hi = largest slice); cls < 0 -> [v_lo, v_hi)
 // of every graph's sorted order (all variables in the single-launch tail).
-__global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_generic(const BpDev p, const int v_lo, const int v_hi, const int cls)
+__global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_generic(const BpDev p, const int v_lo, const int v_hi, const int cls,
+                                                                   const int first)
 {
     SCALDPC_DYN_SMEM(float, smem);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
@@ -673,9 +597,18 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_generic(const BpDev p
     const uint32_t *off = p.csc_off + p0;
 
     float temp = bp_prior_of(p, tile, var, lane);
+    const int limit = first ? bp_row_limit(p, tile, lane) : 0;
 #pragma unroll 4
     for (int i = 0; i < d; ++i) {
-        const float c = *bp_at(msg, __ldg(off + i));
+        float c;
+        if (first) {  // as k_bp_vn<.., FIRST>: +-first_tab[e], sign from the syndrome bit of the edge's check
+            const int e = g * p.g_e + (int)(__ldg(off + i) >> 7);
+            const int row = __ldg(p.edge_row + e);
+            const uint32_t v = bp_bits(__ldg(p.first_tab + e)) ^ ((__ldg(p.synd_w + (size_t)tile * p.m + row) >> lane) << 31);
+            c = row < limit ? bp_float(v) : 0.0f;
+        } else {
+            c = *bp_at(msg, __ldg(off + i));
+        }
         C[i * 32] = c;
         F[i * 32] = temp;
         temp += c;

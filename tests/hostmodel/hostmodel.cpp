@@ -417,14 +417,14 @@ int hostmodel_bp_decode(int m, int n, const int32_t *row_ptr, const int32_t *col
             const int hi = g.class_end[c];
             if (hi > lo) {
                 switch (c) {
-                case 0: run_grid(3, 1, 2 * 32, k_bp_vn<0, 1>, p, lo, hi, cur_tiles, -1); break;
-                case 1: run_grid(3, 1, 2 * 32, k_bp_vn<1, 4>, p, lo, hi, cur_tiles, -1); break;
-                case 2: run_grid(3, 1, 2 * 32, k_bp_vn<4, 8>, p, lo, hi, cur_tiles, -1); break;
-                case 3: run_grid(3, 1, 2 * 32, k_bp_vn<8, 12>, p, lo, hi, cur_tiles, -1); break;
-                case 4: run_grid(3, 1, 2 * 32, k_bp_vn<12, 16>, p, lo, hi, cur_tiles, -1); break;
-                case 5: run_grid(3, 1, 2 * 32, k_bp_vn<16, 24>, p, lo, hi, cur_tiles, -1); break;
-                case 6: run_grid(3, 1, 2 * 32, k_bp_vn<24, 32>, p, lo, hi, cur_tiles, -1); break;
-                default: run_grid((hi - lo + 1) / 2, cur_tiles, 2 * 32, k_bp_vn_generic, p, lo, hi, -1);
+                case 0: run_grid(3, 1, 2 * 32, k_bp_vn<0, 1, false>, p, lo, hi, cur_tiles, -1); break;
+                case 1: run_grid(3, 1, 2 * 32, k_bp_vn<1, 4, false>, p, lo, hi, cur_tiles, -1); break;
+                case 2: run_grid(3, 1, 2 * 32, k_bp_vn<4, 8, false>, p, lo, hi, cur_tiles, -1); break;
+                case 3: run_grid(3, 1, 2 * 32, k_bp_vn<8, 12, false>, p, lo, hi, cur_tiles, -1); break;
+                case 4: run_grid(3, 1, 2 * 32, k_bp_vn<12, 16, false>, p, lo, hi, cur_tiles, -1); break;
+                case 5: run_grid(3, 1, 2 * 32, k_bp_vn<16, 24, false>, p, lo, hi, cur_tiles, -1); break;
+                case 6: run_grid(3, 1, 2 * 32, k_bp_vn<24, 32, false>, p, lo, hi, cur_tiles, -1); break;
+                default: run_grid((hi - lo + 1) / 2, cur_tiles, 2 * 32, k_bp_vn_generic, p, lo, hi, -1, 0);
                 }
             }
             lo = hi;
@@ -542,22 +542,41 @@ int hostmodel_bp_decode_multi(int G, int m, int n, const int32_t *row_ptr, const
     p.g_rp = m + 1; p.g_e = Emax; p.g_cp = n + 1; p.g_n = n;
     std::vector<float> scratch((size_t)6 * std::max(dc_max, dv_max) * 32);
     scaldpc_host_model_smem = scratch.data();
+    // iteration 1 as bp.cu runs it with shared priors: one table of first-pass messages per graph, formed into the bit pass
+    // (k_bp_vn<.., FIRST>) instead of a check pass over the message array
+    std::vector<float> first_tab((size_t)G * Emax, 0.0f);
+    std::vector<int> edge_row((size_t)G * Emax, m);
+    for (int g = 0; g < G; ++g)
+        for (int r = 0; r < m; ++r)
+            for (int e = gs[g].row_ptr[r]; e < gs[g].row_ptr[r + 1]; ++e) edge_row[(size_t)g * Emax + e] = r;
+    p.first_tab = first_tab.data();
+    p.edge_row = edge_row.data();
+    gridDim.y = G;
+    for (unsigned by = 0; by < (unsigned)G; ++by)
+        for (unsigned bx = 0; bx < (unsigned)((m + 127) / 128); ++bx)
+            for (unsigned t = 0; t < 128; ++t) {
+                blockIdx.x = bx; blockIdx.y = by; threadIdx.x = t; blockDim.x = 128;
+                k_bp_first_table(p, first_tab.data());
+            }
     for (int it = 1; it <= max_iter; ++it) {
-        if (it == 1) run_grid(3, 1, 2 * 32, k_bp_cn<true>, p, tiles);
-        else run_grid(3, 1, 2 * 32, k_bp_cn<false>, p, tiles);
+        const bool first = it == 1;
+        if (!first) run_grid(3, 1, 2 * 32, k_bp_cn<false>, p, tiles);
         for (int c = 0; c <= kBpVnClasses; ++c) {
             const int nv = cmax[c];
             if (nv <= 0) continue;
+#define VN_(A_, B_) (first ? run_grid(3, 1, 2 * 32, k_bp_vn<A_, B_, true>, p, 0, nv, tiles, c) \
+                           : run_grid(3, 1, 2 * 32, k_bp_vn<A_, B_, false>, p, 0, nv, tiles, c))
             switch (c) {
-            case 0: run_grid(3, 1, 2 * 32, k_bp_vn<0, 1>, p, 0, nv, tiles, c); break;
-            case 1: run_grid(3, 1, 2 * 32, k_bp_vn<1, 4>, p, 0, nv, tiles, c); break;
-            case 2: run_grid(3, 1, 2 * 32, k_bp_vn<4, 8>, p, 0, nv, tiles, c); break;
-            case 3: run_grid(3, 1, 2 * 32, k_bp_vn<8, 12>, p, 0, nv, tiles, c); break;
-            case 4: run_grid(3, 1, 2 * 32, k_bp_vn<12, 16>, p, 0, nv, tiles, c); break;
-            case 5: run_grid(3, 1, 2 * 32, k_bp_vn<16, 24>, p, 0, nv, tiles, c); break;
-            case 6: run_grid(3, 1, 2 * 32, k_bp_vn<24, 32>, p, 0, nv, tiles, c); break;
-            default: run_grid((nv + 1) / 2, tiles, 2 * 32, k_bp_vn_generic, p, 0, nv, c);
+            case 0: VN_(0, 1); break;
+            case 1: VN_(1, 4); break;
+            case 2: VN_(4, 8); break;
+            case 3: VN_(8, 12); break;
+            case 4: VN_(12, 16); break;
+            case 5: VN_(16, 24); break;
+            case 6: VN_(24, 32); break;
+            default: run_grid((nv + 1) / 2, tiles, 2 * 32, k_bp_vn_generic, p, 0, nv, c, (int)first);
             }
+#undef VN_
         }
         run_grid((m + 255) / 256, tiles, 256, k_bp_syndrome, p);
         run_grid((tiles + 255) / 256, 1, 256, k_bp_finish_iter, p, tiles, it, early_stop, (int)(it == max_iter));

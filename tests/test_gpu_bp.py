@@ -195,16 +195,27 @@ def test_large_batch_compaction_hqc128():
 
 
 def test_shared_prior_first_pass_is_bit_identical(monkeypatch):
-    """k_bp_first_table + k_bp_first_fill (shared priors: the first check-to-bit messages differ between trials only
-    in sign) against k_bp_cn<FIRST>: decisions, iteration counts and posterior LLRs bit for bit."""
+    """Shared priors: the first check-to-bit messages differ between trials only in sign.  Three ways to run iteration 1
+    must agree bit for bit (decisions, iteration counts, posterior LLRs): k_bp_first_table + the FIRST bit pass that forms
+    +-tab[e] on the fly (default), k_bp_first_table + k_bp_first_fill + the ordinary bit pass (round 1's way), and
+    k_bp_cn<FIRST>.  Large enough for the degree-class kernels (> 64 tiles) and small enough for the single-launch path; with
+    nested row limits too (an inactive check sends +0)."""
     w = HqcWorkload(variant=(997, 12), W=11, R=420, rho=0.97, seed=7)
-    b = w.generate(70, seed=3)
     d = bp_decoder(csr=(w.row_ptr, w.col), shape=(w.m, w.n), max_iter=30, channel_probs=w.channel_probs)
-    a = d.decode_batch(b.syndromes, want_llr=True)
-    monkeypatch.setenv("SCALDPC_BP_NO_FIRST_TABLE", "1")
-    c = d.decode_batch(b.syndromes, want_llr=True)
-    assert np.array_equal(a["decoding"], c["decoding"]) and np.array_equal(a["iters"], c["iters"])
-    assert np.array_equal(a["log_prob_ratios"], c["log_prob_ratios"], equal_nan=True)
+    for T in (70, 2100):
+        b = w.generate(T, seed=3)
+        n_checks = np.array([150, 300, 420], np.int32)[np.arange(T) % 3]
+        for nc in (None, n_checks):
+            monkeypatch.delenv("SCALDPC_BP_NO_FIRST_TABLE", raising=False)
+            monkeypatch.delenv("SCALDPC_BP_FIRST_FILL", raising=False)
+            a = d.decode_batch(b.syndromes, want_llr=True, n_checks=nc)
+            monkeypatch.setenv("SCALDPC_BP_FIRST_FILL", "1")
+            f = d.decode_batch(b.syndromes, want_llr=True, n_checks=nc)
+            monkeypatch.setenv("SCALDPC_BP_NO_FIRST_TABLE", "1")
+            c = d.decode_batch(b.syndromes, want_llr=True, n_checks=nc)
+            for other in (f, c):
+                assert np.array_equal(a["decoding"], other["decoding"]) and np.array_equal(a["iters"], other["iters"])
+                assert np.array_equal(a["log_prob_ratios"], other["log_prob_ratios"], equal_nan=True)
 
 
 def reference_stats(N, error, checks, y_sparse):
