@@ -39,6 +39,8 @@ struct scaldpc_bp {
     uint32_t *d_csc_edge = nullptr;
     int *d_edge_row = nullptr;     // E: check of every edge (first pass with shared priors)
     float *d_first_tab = nullptr;  // E: first-iteration check-to-bit messages for syndrome bit 0 (shared priors)
+    float *d_csc_tab = nullptr;    // the same values in CSC order (read by the FIRST bit pass next to csc_off)
+    int *d_csc_row = nullptr, *d_edge_csc = nullptr;  // check of every CSC entry; CSC position of every edge
     // workspace
     int cap_tiles = 0;
     bool cap_post = false, cap_prior_t = false;
@@ -208,6 +210,9 @@ BpDev view(const scaldpc_bp *h, int cur, bool per_trial_prior, bool want_post)
     p.nrows = h->cur_nrows;
     p.first_tab = h->d_first_tab;
     p.edge_row = h->d_edge_row;
+    p.csc_tab = h->d_csc_tab;
+    p.csc_row = h->d_csc_row;
+    p.edge_csc = h->d_edge_csc;
     p.g_rp = h->m + 1;
     p.g_e = h->E;
     p.g_cp = h->n + 1;
@@ -385,6 +390,7 @@ static int bp_create_impl(int G, int m, int n, const int32_t *row_ptr, const int
     std::vector<int> a_row_ptr((size_t)G * (m + 1)), a_col((size_t)G * std::max(1, Emax), 0), a_col_ptr((size_t)G * (n + 1));
     std::vector<int> a_vn_order((size_t)G * n), a_vn_desc((size_t)G * 4 * std::max(1, n)), a_edge_row((size_t)G * std::max(1, Emax), m);
     std::vector<uint32_t> a_csc_off((size_t)G * std::max(1, Emax), 0u);
+    std::vector<int> a_edge_csc((size_t)G * std::max(1, Emax), 0), a_csc_row((size_t)G * std::max(1, Emax), m);
     for (int g = 0; g < G; ++g) {
         const BpHostGraph &q = gs[g];
         std::copy(q.row_ptr.begin(), q.row_ptr.end(), a_row_ptr.begin() + (size_t)g * (m + 1));
@@ -395,14 +401,22 @@ static int bp_create_impl(int G, int m, int n, const int32_t *row_ptr, const int
         std::copy(q.csc_off.begin(), q.csc_off.begin() + q.E, a_csc_off.begin() + (size_t)g * Emax);
         for (int r = 0; r < m; ++r)
             for (int e = q.row_ptr[r]; e < q.row_ptr[r + 1]; ++e) a_edge_row[(size_t)g * Emax + e] = r;
+        for (int i = 0; i < q.E; ++i) {
+            const int e = q.csc_edge[i];
+            a_edge_csc[(size_t)g * Emax + e] = i;
+            a_csc_row[(size_t)g * Emax + i] = a_edge_row[(size_t)g * Emax + e];
+        }
     }
     int rc;
     if ((rc = upload_vec(&h->d_row_ptr, a_row_ptr)) || (rc = upload_vec(&h->d_col, a_col)) ||
         (rc = upload_vec(&h->d_col_ptr, a_col_ptr)) || (rc = upload_vec(&h->d_csc_edge, a_csc_off)) ||
         (rc = upload_vec(&h->d_vn_order, a_vn_order)) || (rc = upload_vec(&h->d_vn_desc, a_vn_desc)) ||
-        (rc = upload_vec(&h->d_edge_row, a_edge_row)) || (rc = upload_vec(&h->d_class_end, class_end_all)))
+        (rc = upload_vec(&h->d_edge_row, a_edge_row)) || (rc = upload_vec(&h->d_class_end, class_end_all)) ||
+        (rc = upload_vec(&h->d_edge_csc, a_edge_csc)) || (rc = upload_vec(&h->d_csc_row, a_csc_row)))
         return rc;
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_first_tab, (size_t)G * std::max(1, Emax) * sizeof(float)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_csc_tab, (size_t)G * std::max(1, Emax) * sizeof(float)));
+    SCALDPC_CUDA(cudaMemset(h->d_csc_tab, 0, (size_t)G * std::max(1, Emax) * sizeof(float)));
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_prior, (size_t)n * sizeof(float)));
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_nact, sizeof(int)));
     h->cap_counts = h->max_iter + 2;
@@ -458,6 +472,9 @@ void scaldpc_bp_destroy(scaldpc_bp *h)
     cudaFree(h->d_tile_graph);
     cudaFree(h->d_slot_orig);
     cudaFree(h->d_first_tab);
+    cudaFree(h->d_csc_tab);
+    cudaFree(h->d_csc_row);
+    cudaFree(h->d_edge_csc);
     cudaFree(h->d_prior);
     cudaFree(h->d_nact);
     cudaFree(h->d_counts);

@@ -73,6 +73,9 @@ struct BpDev {
     // of the bit pass forms them on the fly instead of reading a message array that k_bp_first_fill would have to write
     const float *first_tab = nullptr;  // [G][E]
     const int *edge_row = nullptr;     // [G][E] check of every edge
+    const float *csc_tab = nullptr;    // [G][E] first_tab in CSC order (position of csc_off), written by k_bp_first_table
+    const int *csc_row = nullptr;      // [G][E] check of every edge, CSC order
+    const int *edge_csc = nullptr;     // [G][E] CSC position of every edge
 };
 
 constexpr int kBpVnClassCount = 7;  // == kBpVnClasses (bp_graph.h)
@@ -329,6 +332,7 @@ __global__ void __launch_bounds__(128) k_bp_first_table(const BpDev p, float *__
         const float x = bp_fold(__ldg(p.prior + __ldg(col + e0 + k)));
         const float mag = bp_unfold(bp_parity(P, suf));
         tab[e0 + k] = bp_float(bp_bits(mag) ^ ((neg ^ bp_bits(x)) & 0x80000000u));
+        if (p.csc_tab) ((float *)p.csc_tab)[(size_t)g * p.g_e + __ldg(p.edge_csc + (size_t)g * p.g_e + e0 + k)] = tab[e0 + k];
         suf = bp_parity(suf, fabsf(x));
     }
 }
@@ -405,14 +409,14 @@ struct BpVnItem {
 // `base` + byte offset, with the base kept as an opaque 64-bit register so that the address is one 64-bit add.
 __device__ __forceinline__ float *bp_at(float *base, uint32_t byte_off) { return (float *)((char *)base + byte_off); }
 
-// The two sweeps of one variable of degree exactly D (straight-line code, no guards).  `o` = the byte offsets of the
-// column's lines (loaded once by the gather).  Upstream resets a NaN running value to the neutral element; a NaN can only
+// The two sweeps of one variable of degree exactly D (straight-line code, no guards).  Upstream resets a NaN running value to the neutral element; a NaN can only
 // appear when +inf meets -inf, and then the forward total is NaN too, so the sweeps run WITHOUT the per-step tests and a
 // NaN total sends the lane through the tested version (identical results; 4 fewer instructions per edge otherwise).
 template <int D, int DMAX>
 __device__ __forceinline__ void bp_vn_body(const BpDev &p, const BpVnItem &it, int lane, const float (&c)[DMAX],
-                                           const uint32_t (&o)[DMAX], const float prior)
+                                           const float prior)
 {
+    const uint32_t *o = p.csc_off + it.p0;  // re-read (L1): carrying the offsets in registers costs a resident CTA per SM
     const uint32_t done = __ldg(p.done + it.tile);
     float *msg = p.msg + (size_t)it.tile * p.E * 32 + lane;
 #ifndef SCALDPC_HOST_MODEL
@@ -430,7 +434,7 @@ __device__ __forceinline__ void bp_vn_body(const BpDev &p, const BpVnItem &it, i
         temp = 0.0f;
 #pragma unroll
         for (int i = D - 1; i >= 0; --i) {
-            *bp_at(msg, o[i]) = bp_fold(F[i] + temp);
+            *bp_at(msg, __ldg(o + i)) = bp_fold(F[i] + temp);
             temp += c[i];
         }
     } else {  // rare: +inf and -inf among the column's messages -- upstream's "NaN -> neutral element" semantics
@@ -445,7 +449,7 @@ __device__ __forceinline__ void bp_vn_body(const BpDev &p, const BpVnItem &it, i
         temp = 0.0f;
 #pragma unroll
         for (int i = D - 1; i >= 0; --i) {
-            *bp_at(msg, o[i]) = bp_fold(F[i] + temp);
+            *bp_at(msg, __ldg(o + i)) = bp_fold(F[i] + temp);
             temp += c[i];
             if (temp != temp) temp = 0.0f;
         }
@@ -455,15 +459,15 @@ __device__ __forceinline__ void bp_vn_body(const BpDev &p, const BpVnItem &it, i
 
 template <int D, int DMIN, int DMAX>
 __device__ __forceinline__ void bp_vn_dispatch(const BpDev &p, const BpVnItem &it, int lane, const float (&c)[DMAX],
-                                               const uint32_t (&o)[DMAX], const float prior)
+                                               const float prior)
 {
     if constexpr (D < DMIN) {
-        bp_vn_body<DMAX, DMAX>(p, it, lane, c, o, prior);  // unreachable for a correctly sorted class; keeps the code total
+        bp_vn_body<DMAX, DMAX>(p, it, lane, c, prior);  // unreachable for a correctly sorted class; keeps the code total
     } else {
         if (it.d == D)
-            bp_vn_body<D, DMAX>(p, it, lane, c, o, prior);
+            bp_vn_body<D, DMAX>(p, it, lane, c, prior);
         else
-            bp_vn_dispatch<D - 1, DMIN, DMAX>(p, it, lane, c, o, prior);
+            bp_vn_dispatch<D - 1, DMIN, DMAX>(p, it, lane, c, prior);
     }
 }
 
@@ -514,26 +518,27 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const 
             it.p0 = g * p.g_e + c0;     // position in the (concatenated) csc_off table
         }
     };
-    auto gather = [&](const BpVnItem &it, float (&c)[DMAX], uint32_t (&o)[DMAX]) {
+    auto gather = [&](const BpVnItem &it, float (&c)[DMAX]) {
         float *src = p.msg + (size_t)it.tile * p.E * 32 + lane;
 #ifndef SCALDPC_HOST_MODEL
         asm volatile("" : "+l"(src));
 #endif
         const uint32_t *off = p.csc_off + it.p0;
-        const int gb = FIRST ? bp_graph(p, it.tile) * p.g_e : 0;
+        // FIRST: the column's rows and first-pass messages sit in CSC order next to the offsets (three independent
+        // sequential index loads, then ONE dependent load of the tile's syndrome word, L1-resident)
+        const int *rows = p.csc_row + it.p0;
+        const float *tabs = p.csc_tab + it.p0;
         const int limit = FIRST ? bp_row_limit(p, it.tile, lane) : 0;
         const uint32_t *sw = p.synd_w + (size_t)it.tile * p.m;
 #pragma unroll
         for (int i = 0; i < DMAX; ++i)
             if ((DMIN > 0 && i <= DMIN) || i < it.d) {  // d > DMIN: the first are unguarded
-                o[i] = __ldg(off + i);
                 if (FIRST) {
-                    const int e = gb + (int)(o[i] >> 7);
-                    const int row = __ldg(p.edge_row + e);
-                    const uint32_t v = bp_bits(__ldg(p.first_tab + e)) ^ ((__ldg(sw + row) >> lane) << 31);
+                    const int row = __ldg(rows + i);
+                    const uint32_t v = bp_bits(__ldg(tabs + i)) ^ ((__ldg(sw + row) >> lane) << 31);
                     c[i] = row < limit ? bp_float(v) : 0.0f;
                 } else {
-                    c[i] = *bp_at(src, o[i]);
+                    c[i] = *bp_at(src, __ldg(off + i));
                 }
             }
     };
@@ -543,27 +548,23 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const 
     cur.j = gw - cur.tile * nv;
     advance(cur, true);
     float c[DMAX], cn[DMAX];
-    uint32_t o[DMAX], on[DMAX];
     float pr = 0.0f, prn = 0.0f;  // the variable's prior travels with its column (44 % of the stall samples sat on it)
     if (cur.tile < tiles) {
-        gather(cur, c, o);
+        gather(cur, c);
         pr = bp_prior_of(p, cur.tile, cur.var, lane);
     }
     while (cur.tile < tiles) {
         BpVnItem nxt = cur;
         advance(nxt, false);
         if (nxt.tile < tiles) {
-            gather(nxt, cn, on);
+            gather(nxt, cn);
             prn = bp_prior_of(p, nxt.tile, nxt.var, lane);
         }
-        bp_vn_dispatch<DMAX, (DMIN == 0 ? 0 : DMIN + 1), DMAX>(p, cur, lane, c, o, pr);
+        bp_vn_dispatch<DMAX, (DMIN == 0 ? 0 : DMIN + 1), DMAX>(p, cur, lane, c, pr);
         cur = nxt;
         pr = prn;
 #pragma unroll
-        for (int i = 0; i < DMAX; ++i) {
-            c[i] = cn[i];
-            o[i] = on[i];
-        }
+        for (int i = 0; i < DMAX; ++i) c[i] = cn[i];
     }
 }
 
@@ -602,9 +603,8 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_generic(const BpDev p
     for (int i = 0; i < d; ++i) {
         float c;
         if (first) {  // as k_bp_vn<.., FIRST>: +-first_tab[e], sign from the syndrome bit of the edge's check
-            const int e = g * p.g_e + (int)(__ldg(off + i) >> 7);
-            const int row = __ldg(p.edge_row + e);
-            const uint32_t v = bp_bits(__ldg(p.first_tab + e)) ^ ((__ldg(p.synd_w + (size_t)tile * p.m + row) >> lane) << 31);
+            const int row = __ldg(p.csc_row + p0 + i);
+            const uint32_t v = bp_bits(__ldg(p.csc_tab + p0 + i)) ^ ((__ldg(p.synd_w + (size_t)tile * p.m + row) >> lane) << 31);
             c = row < limit ? bp_float(v) : 0.0f;
         } else {
             c = *bp_at(msg, __ldg(off + i));

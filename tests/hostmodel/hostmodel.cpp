@@ -104,7 +104,7 @@ typedef void (*cn_exact_fn)(const QaryDev, const int, const int, const int);
 cn_exact_fn pick_cn_exact(int sw, int b)
 {
 #define CASE(SW_, B_) \
-    if (sw == SW_ && b == B_) return k_cn_exact<SW_, B_>;
+    if (sw == SW_ && b == B_) return k_cn_exact<SW_, B_, false>;
     CASE(6, 2) CASE(6, 3) CASE(4, 2) CASE(8, 2) CASE(3, 2)
 #undef CASE
     return nullptr;
@@ -549,8 +549,19 @@ int hostmodel_bp_decode_multi(int G, int m, int n, const int32_t *row_ptr, const
     for (int g = 0; g < G; ++g)
         for (int r = 0; r < m; ++r)
             for (int e = gs[g].row_ptr[r]; e < gs[g].row_ptr[r + 1]; ++e) edge_row[(size_t)g * Emax + e] = r;
+    std::vector<float> csc_tab((size_t)G * Emax, 0.0f);
+    std::vector<int> csc_row((size_t)G * Emax, m), edge_csc((size_t)G * Emax, 0);
+    for (int g = 0; g < G; ++g)
+        for (int i = 0; i < gs[g].E; ++i) {
+            const int e = gs[g].csc_edge[i];
+            edge_csc[(size_t)g * Emax + e] = i;
+            csc_row[(size_t)g * Emax + i] = edge_row[(size_t)g * Emax + e];
+        }
     p.first_tab = first_tab.data();
     p.edge_row = edge_row.data();
+    p.csc_tab = csc_tab.data();
+    p.csc_row = csc_row.data();
+    p.edge_csc = edge_csc.data();
     gridDim.y = G;
     for (unsigned by = 0; by < (unsigned)G; ++by)
         for (unsigned bx = 0; bx < (unsigned)((m + 127) / 128); ++bx)
