@@ -65,6 +65,7 @@ struct scaldpc_bp {
     size_t smem_cn = 0;
     int vn_occ[8] = {0};  // bit pass: resident CTAs per SM of each degree-class kernel
     int vn_single_tiles = 64;  // at most this many tiles: one any-degree launch per bit pass (SCALDPC_BP_VN_SINGLE=n)
+    long long vn_single_items = 65536;  // ... and at most this many (tile, variable) items (SCALDPC_BP_VN_SINGLE_ITEMS=n)
     // (round 1 also had k_bp_vn_tma: column gather by per-lane bulk-async copies into a 4-stage ring.  Measured on hqc128 /
     // hqc256: 1.41 / 1.98 ms against 1.35 / 1.91 ms for the register-prefetch kernel -- one UBLKCP per lane is serialised --
     // so it was removed in round 2.)
@@ -259,10 +260,13 @@ bp_vn_fn vn_class_fn(int c, bool first = false)
 // the largest register class go through the shared-memory kernel.
 int launch_vn(scaldpc_bp *h, const BpDev &p, int tiles, cudaStream_t st, bool first = false)
 {
-    if (tiles <= h->vn_single_tiles) {
-        // few tiles (the non-converging tail after compaction): the iteration is bound by kernel launches, so ONE launch
-        // of the any-degree kernel over all variables replaces one launch per degree class (same arithmetic)
-        k_bp_vn_generic<<<dim3((h->n + h->vn_gen_wpc - 1) / h->vn_gen_wpc, tiles), h->vn_gen_wpc * 32, h->smem_vn, st>>>(p, 0, h->n, -1, first);
+    auto generic = first ? k_bp_vn_generic<true> : k_bp_vn_generic<false>;
+    if (tiles <= h->vn_single_tiles && (long long)tiles * h->n <= h->vn_single_items) {
+        // few (tile, variable) items (the non-converging tail after compaction): the iteration is bound by kernel launches,
+        // so ONE launch of the any-degree kernel over all variables replaces one launch per degree class (same arithmetic).
+        // Only while the launch latency dominates: per item the any-degree kernel is ~2x slower than the class kernels
+        // (hqc256, 4 tiles x 65 637 variables: 230 us against ~120 us -- profiles/r2l), so larger tails keep the classes.
+        generic<<<dim3((h->n + h->vn_gen_wpc - 1) / h->vn_gen_wpc, tiles), h->vn_gen_wpc * 32, h->smem_vn, st>>>(p, 0, h->n, -1);
         ++h->launches;
         SCALDPC_CUDA(cudaGetLastError());
         return 0;
@@ -278,8 +282,8 @@ int launch_vn(scaldpc_bp *h, const BpDev &p, int tiles, cudaStream_t st, bool fi
                 const int ctas = (int)std::min<long long>((long long)h->num_sms * h->vn_occ[c], (items + kBpVnWarps - 1) / kBpVnWarps);
                 vn_class_fn(c, first)<<<std::max(1, ctas), kBpVnWarps * 32, 0, st>>>(p, lo, hi, tiles, multi ? c : -1);
             } else {
-                k_bp_vn_generic<<<dim3((hi - lo + h->vn_gen_wpc - 1) / h->vn_gen_wpc, tiles), h->vn_gen_wpc * 32, h->smem_vn, st>>>(
-                    p, lo, hi, multi ? c : -1, first);
+                generic<<<dim3((hi - lo + h->vn_gen_wpc - 1) / h->vn_gen_wpc, tiles), h->vn_gen_wpc * 32, h->smem_vn, st>>>(
+                    p, lo, hi, multi ? c : -1);
             }
             ++h->launches;
         }
@@ -425,8 +429,12 @@ static int bp_create_impl(int G, int m, int n, const int32_t *row_ptr, const int
     SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_cn<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_cn));
     SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_cn<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_cn));
     if (h->smem_vn)
-        SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_vn_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_vn));
+    {
+        SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_vn_generic<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_vn));
+        SCALDPC_CUDA(cudaFuncSetAttribute(k_bp_vn_generic<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_vn));
+    }
     if (const char *e = getenv("SCALDPC_BP_VN_SINGLE")) h->vn_single_tiles = atoi(e);
+    if (const char *e = getenv("SCALDPC_BP_VN_SINGLE_ITEMS")) h->vn_single_items = atoll(e);
     for (int c = 0; c < kBpVnClasses; ++c) {
         SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->vn_occ[c], vn_class_fn(c), kBpVnWarps * 32, 0));
         h->vn_occ[c] = std::max(1, h->vn_occ[c]);

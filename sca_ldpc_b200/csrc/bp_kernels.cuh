@@ -572,9 +572,10 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const 
 // one CTA pass over (variable, tile) without prefetch.
 // Segmented CSR: cls >= 0 -> the tile's own slice of that class (v_lo = 0, v_hi = largest slice); cls < 0 -> [v_lo, v_hi)
 // of every graph's sorted order (all variables in the single-launch tail).
-__global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_generic(const BpDev p, const int v_lo, const int v_hi, const int cls,
-                                                                   const int first)
+template <bool FIRST>
+__global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_generic(const BpDev p, const int v_lo, const int v_hi, const int cls)
 {
+    constexpr bool first = FIRST;  // compile-time: a run-time test inside the gather loop keeps its loads from being batched
     SCALDPC_DYN_SMEM(float, smem);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
     int idx = v_lo + blockIdx.x * wpc + warp;

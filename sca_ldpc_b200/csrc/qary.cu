@@ -452,17 +452,15 @@ const CnFast *pick_cn_fast(int sw, int b)
 // The exact-order check-node kernel for the same shapes (qary_cn_exact.cuh).
 typedef void (*cn_exact_fn)(const QaryDev, const int, const int, const int);
 struct CnExact {
-    cn_exact_fn fn, fn_split;
-    size_t smem, smem_split;
-    int sw;
+    cn_exact_fn fn;
+    size_t smem;
 };
 
 const CnExact *pick_cn_exact(int sw, int b)
 {
 #define CASE(SW_, B_)                                                                            \
     if (sw == SW_ && b == B_) {                                                                  \
-        static const CnExact t = {k_cn_exact<SW_, B_, false>, k_cn_exact<SW_, B_, true>,          \
-                                  CnExactShape<SW_, B_>::smem_bytes, CnExactShape<SW_, B_>::smem_bytes_split, SW_}; \
+        static const CnExact t = {k_cn_exact<SW_, B_>, CnExactShape<SW_, B_>::smem_bytes};       \
         return &t;                                                                               \
     }
     CASE(6, 2) CASE(6, 3) CASE(4, 2) CASE(8, 2) CASE(3, 2)
@@ -538,11 +536,7 @@ int launch_cn(scaldpc_qary *h, const QaryDev &p, int tiles, int it, int iters, u
         // exact-order dynamic programme in registers, one warp per (tile, check)
         const CnExact *ex = pick_cn_exact(h->fast_sw, h->B);
         const int n_items = tiles * h->R;
-        // few items (the re-decode of a handful of flagged trials): one CTA of SW warps per item, a pinned variable each
-        if (n_items < 2 * h->num_sms * kCnExactWarps && !getenv("SCALDPC_EXACT_NO_SPLIT"))
-            ex->fn_split<<<n_items, ex->sw * 32, ex->smem_split, st>>>(p, n_items, first, last);
-        else
-            ex->fn<<<(n_items + kCnExactWarps - 1) / kCnExactWarps, kCnExactWarps * 32, ex->smem, st>>>(p, n_items, first, last);
+        ex->fn<<<(n_items + kCnExactWarps - 1) / kCnExactWarps, kCnExactWarps * 32, ex->smem, st>>>(p, n_items, first, last);
         ++h->launches;
     } else if (h->BSUM == 0 && !exact && !force_generic && h->uniform_ok) {
         // generic decoder, one alphabet: the unrolled / padded forward-backward kernel
@@ -671,7 +665,6 @@ int scaldpc_qary_create(const int8_t *H, int R, int N, int b, int bsum, int dv, 
             SCALDPC_CUDA(cudaFuncSetAttribute(f->fn[i], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f->smem));
         const CnExact *ex = pick_cn_exact(h->fast_sw, b);
         SCALDPC_CUDA(cudaFuncSetAttribute(ex->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ex->smem));
-        SCALDPC_CUDA(cudaFuncSetAttribute(ex->fn_split, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ex->smem_split));
     }
     int rc;
     if ((rc = upload(&h->d_row_ptr, row_ptr)) || (rc = upload(&h->d_col, col)) || (rc = upload(&h->d_sign, sign)) ||
@@ -1021,7 +1014,7 @@ static int decode_on_device(scaldpc_qary *h, int T, const PriorSrc &src, int8_t 
                                     base);
     ++h->launches;
     if (stash) {  // host pipeline: the staging buffer holding these priors is about to be overwritten
-        const int grid = std::min(T, 512);
+        const dim3 grid(8, std::min(T, 64));  // x: slices of a row, y: flagged rows (grid-stride)
         if (src.observed) {
             k_gather_rows<uint16_t><<<grid, 256, 0, st>>>(src.obs, h->d_retry_obs, list_a, h->d_scan_out, h->bvars, (int)h->cap_retry);
             if (h->BSUM > 0)

@@ -25,15 +25,14 @@ template <int SW, int B>
 struct CnExactShape {
     using Sh = CnFastShape<SW, B>;
     static constexpr size_t smem_bytes = (size_t)kCnExactWarps * Sh::NS * 32 * sizeof(float);
-    static constexpr size_t smem_bytes_split = (size_t)SW * Sh::NS * 32 * sizeof(float);
 };
 
-// SPLIT: one CTA of SW warps per (tile, check), warp j pins variable j only (the last one also takes the sum-variable).  The
-// re-decode of a handful of flagged trials is a chain of launches that each fill a fraction of the GPU; splitting the item
-// six ways shortens that chain's critical path ~4x (the prefix tables F_1 .. F_j are recomputed by every warp: cheap).
-template <int SW, int B, bool SPLIT>
-__global__ void __launch_bounds__(SPLIT ? SW * 32 : kCnExactWarps * 32, SPLIT ? 1 : 2)
-    k_cn_exact(const QaryDev p, const int n_items, const int FIRST, const int LAST)
+// (A variant with one CTA of SW warps per item, a pinned variable per warp, was measured for the re-decode of a single tile:
+// 35 us per launch against 27 us -- 251 registers x 192 threads leave one CTA per SM, so 256 items need two waves and each wave
+// lasts as long as its longest warp.  Removed.)
+template <int SW, int B>
+__global__ void __launch_bounds__(kCnExactWarps * 32, 2) k_cn_exact(const QaryDev p, const int n_items, const int FIRST,
+                                                                    const int LAST)
 {
     static_assert(SW >= 2, "k_cn_exact needs at least two B-variables per check");
     using Sh = CnFastShape<SW, B>;
@@ -41,8 +40,7 @@ __global__ void __launch_bounds__(SPLIT ? SW * 32 : kCnExactWarps * 32, SPLIT ? 
     constexpr int NP = (SW - 1) * B + 1;  // pairs of the widest table over the B-variables: 2 (SW-1) B + 1 entries
     const float INF = SC_INF;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int item = SPLIT ? blockIdx.x : blockIdx.x * kCnExactWarps + warp;
-    const int myj = warp;  // SPLIT: the variable this warp pins
+    const int item = blockIdx.x * kCnExactWarps + warp;
     if (item >= n_items) return;
     const int tile = item / p.R, check = item - tile * p.R;
     const int e0 = __ldg(p.row_ptr + check);
@@ -104,9 +102,6 @@ __global__ void __launch_bounds__(SPLIT ? SW * 32 : kCnExactWarps * 32, SPLIT ? 
         }
 #pragma unroll
     for (int i = 0; i < QS; ++i) SX(SW * Q + i) = sanitize(as[i]);  // `as` itself is dead from here on
-#ifndef SCALDPC_HOST_MODEL
-    if (SPLIT) __syncthreads();  // every warp of the check holds its inputs before any of them overwrites a slot
-#endif
 
     // ---- per variable j: every value d pinned in turn; Fp = F_j as pairs (F_j[v] <-> prefix total v - j*B)
     F2 Fp[NP];
@@ -114,7 +109,7 @@ __global__ void __launch_bounds__(SPLIT ? SW * 32 : kCnExactWarps * 32, SPLIT ? 
     for (int j = 0; j < SW; ++j) {
         const int nF = 2 * j * B + 1;  // entries of F_j (compile-time after unrolling)
 #pragma unroll 1
-        for (int d = 0; d < ((!SPLIT || j == myj) ? Q : 0); ++d) {
+        for (int d = 0; d < Q; ++d) {
             const float x = SX(j * Q + d);
             // T = F_j + a_j[d]; index v of T <-> total of the OTHER variables so far, offset (number of them) * B
             F2 Tp[NP];
@@ -146,7 +141,6 @@ __global__ void __launch_bounds__(SPLIT ? SW * 32 : kCnExactWarps * 32, SPLIT ? 
             const float M = acc.get();
             out[(size_t)(j * Q + d) * 32] = (x < INF && M < INF) ? M - x : INF;
         }
-        if (SPLIT && j == myj && j < SW - 1) return;  // this warp's variable is done
         // F_{j+1} = F_j (+) a_j
         float Fs[2 * NP + Q];
         if (j == 0) {

@@ -104,7 +104,7 @@ typedef void (*cn_exact_fn)(const QaryDev, const int, const int, const int);
 cn_exact_fn pick_cn_exact(int sw, int b)
 {
 #define CASE(SW_, B_) \
-    if (sw == SW_ && b == B_) return k_cn_exact<SW_, B_, false>;
+    if (sw == SW_ && b == B_) return k_cn_exact<SW_, B_>;
     CASE(6, 2) CASE(6, 3) CASE(4, 2) CASE(8, 2) CASE(3, 2)
 #undef CASE
     return nullptr;
@@ -424,7 +424,7 @@ int hostmodel_bp_decode(int m, int n, const int32_t *row_ptr, const int32_t *col
                 case 4: run_grid(3, 1, 2 * 32, k_bp_vn<12, 16, false>, p, lo, hi, cur_tiles, -1); break;
                 case 5: run_grid(3, 1, 2 * 32, k_bp_vn<16, 24, false>, p, lo, hi, cur_tiles, -1); break;
                 case 6: run_grid(3, 1, 2 * 32, k_bp_vn<24, 32, false>, p, lo, hi, cur_tiles, -1); break;
-                default: run_grid((hi - lo + 1) / 2, cur_tiles, 2 * 32, k_bp_vn_generic, p, lo, hi, -1, 0);
+                default: run_grid((hi - lo + 1) / 2, cur_tiles, 2 * 32, k_bp_vn_generic<false>, p, lo, hi, -1);
                 }
             }
             lo = hi;
@@ -585,7 +585,9 @@ int hostmodel_bp_decode_multi(int G, int m, int n, const int32_t *row_ptr, const
             case 4: VN_(12, 16); break;
             case 5: VN_(16, 24); break;
             case 6: VN_(24, 32); break;
-            default: run_grid((nv + 1) / 2, tiles, 2 * 32, k_bp_vn_generic, p, 0, nv, c, (int)first);
+            default:
+                if (first) run_grid((nv + 1) / 2, tiles, 2 * 32, k_bp_vn_generic<true>, p, 0, nv, c);
+                else run_grid((nv + 1) / 2, tiles, 2 * 32, k_bp_vn_generic<false>, p, 0, nv, c);
             }
 #undef VN_
         }
