@@ -102,6 +102,12 @@ typedef struct scaldpc_qary scaldpc_qary;
  */
 int scaldpc_qary_create(const int8_t *H, int R, int N, int b, int bsum, int dv, int dc, int max_iter, int device,
                         scaldpc_qary **out);
+/* The same constructor for a SPARSE parity-check matrix (make_code.py:72-94 builds H = [H' | I] from
+ * negacyclic blocks of column weight 1-3 -- 7 entries per row of 768-1280): CSR with columns strictly ascending inside a row
+ * (= the order the reference's row-major scan of the dense matrix visits them, decoder.rs:507-539) and one int8 per entry
+ * whose sign is the entry (no explicit zeros).  Identical handle to scaldpc_qary_create on the dense matrix. */
+int scaldpc_qary_create_csr(int R, int N, const int32_t *row_ptr, const int32_t *col, const int8_t *val, int b, int bsum, int dv,
+                            int dc, int max_iter, int device, scaldpc_qary **out);
 void scaldpc_qary_destroy(scaldpc_qary *h);
 
 /* Shape queries (sizes a caller needs to allocate buffers). */

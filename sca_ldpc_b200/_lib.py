@@ -22,7 +22,7 @@ BP_PROBS_PER_TRIAL, BP_NO_EARLY_STOP, BP_NO_COMPACT = 0x10, 0x20, 0x40
 # every exported symbol of include/scaldpc.h (tests/test_abi.py checks this list against the header)
 SYMBOLS = [
     "scaldpc_last_error", "scaldpc_version", "scaldpc_device_count",
-    "scaldpc_qary_create", "scaldpc_qary_destroy", "scaldpc_qary_info", "scaldpc_qary_set_max_iter",
+    "scaldpc_qary_create", "scaldpc_qary_create_csr", "scaldpc_qary_destroy", "scaldpc_qary_info", "scaldpc_qary_set_max_iter",
     "scaldpc_qary_decode", "scaldpc_qary_decode_observed", "scaldpc_qary_simulate", "scaldpc_qary_launch_count", "scaldpc_qary_time_kernel",
     "scaldpc_qary_last_run", "scaldpc_qary_set_risk_margin", "scaldpc_qary_last_iterations",
     "scaldpc_bp_create", "scaldpc_bp_destroy", "scaldpc_bp_info", "scaldpc_bp_decode", "scaldpc_bp_decode_scored", "scaldpc_bp_decode_nested", "scaldpc_bp_launch_count",
@@ -63,6 +63,8 @@ def lib() -> C.CDLL:
 
     L.scaldpc_qary_create.restype = i
     L.scaldpc_qary_create.argtypes = [vp, i, i, i, i, i, i, i, i, C.POINTER(vp)]
+    L.scaldpc_qary_create_csr.restype = i
+    L.scaldpc_qary_create_csr.argtypes = [i, i, vp, vp, vp, i, i, i, i, i, i, C.POINTER(vp)]
     L.scaldpc_qary_destroy.restype = None
     L.scaldpc_qary_destroy.argtypes = [vp]
     L.scaldpc_qary_info.restype = i

@@ -607,6 +607,9 @@ int scaldpc_device_count(void)
     return n;
 }
 
+static int qary_create_from_graph(const HostGraph &g, int R, int N, int b, int bsum, int max_iter, int device,
+                                  scaldpc_qary **out);
+
 int scaldpc_qary_create(const int8_t *H, int R, int N, int b, int bsum, int dv, int dc, int max_iter, int device,
                         scaldpc_qary **out)
 {
@@ -614,11 +617,30 @@ int scaldpc_qary_create(const int8_t *H, int R, int N, int b, int bsum, int dv, 
     *out = nullptr;
     if (max_iter < 0) return fail(SCALDPC_ERR_ARG, "iterations must be >= 0");
     HostGraph g;
-    {
-        std::string err;
-        const int grc = build_graph(H, R, N, b, bsum, dv, dc, g, err);
-        if (grc) return fail(grc, "%s", err.c_str());
-    }
+    std::string err;
+    const int grc = build_graph(H, R, N, b, bsum, dv, dc, g, err);
+    if (grc) return fail(grc, "%s", err.c_str());
+    return qary_create_from_graph(g, R, N, b, bsum, max_iter, device, out);
+}
+
+int scaldpc_qary_create_csr(int R, int N, const int32_t *row_ptr, const int32_t *col, const int8_t *val, int b, int bsum, int dv,
+                            int dc, int max_iter, int device, scaldpc_qary **out)
+{
+    if (!out) return fail(SCALDPC_ERR_ARG, "out is NULL");
+    *out = nullptr;
+    if (max_iter < 0) return fail(SCALDPC_ERR_ARG, "iterations must be >= 0");
+    HostGraph g;
+    std::string err;
+    const int grc = build_graph_csr(R, N, row_ptr, col, val, b, bsum, dv, dc, g, err);
+    if (grc) return fail(grc, "%s", err.c_str());
+    return qary_create_from_graph(g, R, N, b, bsum, max_iter, device, out);
+}
+
+}  // extern "C"
+
+static int qary_create_from_graph(const HostGraph &g, int R, int N, int b, int bsum, int max_iter, int device,
+                                  scaldpc_qary **out)
+{
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
         return fail(SCALDPC_ERR_CUDA, "CUDA device %d not available (%d visible) -- libscaldpc has no CPU path", device,
@@ -685,6 +707,8 @@ int scaldpc_qary_create(const int8_t *H, int R, int N, int b, int bsum, int dv, 
     *out = h.release();
     return 0;
 }
+
+extern "C" {
 
 void scaldpc_qary_destroy(scaldpc_qary *h)
 {

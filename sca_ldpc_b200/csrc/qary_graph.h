@@ -31,14 +31,27 @@ struct HostGraph {
     std::vector<EdgeRef> csc;
 };
 
+// Sparse input: CSR with columns strictly ascending inside a row (the order the reference's row-major scan of the dense
+// matrix visits them, decoder.rs:507-539) and one int8 value per entry, of which only the sign matters.
 // Returns SCALDPC_OK or an error code; `err` receives the description.
-inline int build_graph(const int8_t *H, int R, int N, int b, int bsum, int dv, int dc, HostGraph &g, std::string &err)
+inline int build_graph_csr(int R, int N, const int32_t *in_row_ptr, const int32_t *in_col, const int8_t *in_val, int b, int bsum,
+                           int dv, int dc, HostGraph &g, std::string &err)
 {
     auto bad = [&](int code, const std::string &m) {
         err = m;
         return code;
     };
-    if (!H || R <= 0 || N <= 0) return bad(SCALDPC_ERR_ARG, "bad parity-check matrix shape");
+    if (!in_row_ptr || !in_col || !in_val || R <= 0 || N <= 0) return bad(SCALDPC_ERR_ARG, "bad parity-check matrix shape");
+    if (in_row_ptr[0] != 0) return bad(SCALDPC_ERR_ARG, "row_ptr[0] must be 0");
+    for (int r = 0; r < R; ++r) {
+        if (in_row_ptr[r + 1] < in_row_ptr[r]) return bad(SCALDPC_ERR_ARG, "row_ptr must be non-decreasing");
+        for (int e = in_row_ptr[r]; e < in_row_ptr[r + 1]; ++e) {
+            if (in_col[e] < 0 || in_col[e] >= N) return bad(SCALDPC_ERR_ARG, "column index out of range in row " + std::to_string(r));
+            if (e > in_row_ptr[r] && in_col[e] <= in_col[e - 1])
+                return bad(SCALDPC_ERR_ARG, "columns must be strictly ascending within row " + std::to_string(r));
+            if (in_val[e] == 0) return bad(SCALDPC_ERR_ARG, "explicit zero entry in row " + std::to_string(r));
+        }
+    }
     if (R > 65535 || N > 65535) return bad(SCALDPC_ERR_ARG, "R and N must fit the reference's u16 keys (decoder.rs:211)");
     if (b <= 0 || 2 * b + 1 > 31) return bad(SCALDPC_ERR_ARG, "B must be in [1, 15]");
     if (bsum < 0 || 2 * bsum + 1 > 127) return bad(SCALDPC_ERR_ARG, "BSUM must be in [0, 63]");
@@ -64,9 +77,9 @@ inline int build_graph(const int8_t *H, int R, int N, int b, int bsum, int dv, i
     for (int r = 0; r < R; ++r) {
         g.row_ptr[r] = (int)g.col.size();
         int nsum = 0, tot = 0;
-        for (int c = 0; c < N; ++c) {
-            const int8_t v = H[(size_t)r * N + c];
-            if (!v) continue;
+        for (int e_in = in_row_ptr[r]; e_in < in_row_ptr[r + 1]; ++e_in) {
+            const int c = in_col[e_in];
+            const int8_t v = in_val[e_in];
             const bool is_sum = c >= g.bvars;
             g.col.push_back(c);
             g.sign.push_back(v < 0 ? -1 : 1);  // only the sign matters (mult_in_gf, decoder.rs:164-172)
@@ -130,6 +143,28 @@ inline int build_graph(const int8_t *H, int R, int N, int b, int bsum, int dv, i
         }
     if (regular && sw0 > 0 && bsum == sw0 * b) g.regular_sw = sw0;
     return SCALDPC_OK;
+}
+
+// Dense input (pydecoder.rs:24-45: the reference's constructor takes the dense R x N int8 matrix): row-major scan -> CSR.
+inline int build_graph(const int8_t *H, int R, int N, int b, int bsum, int dv, int dc, HostGraph &g, std::string &err)
+{
+    if (!H || R <= 0 || N <= 0) {
+        err = "bad parity-check matrix shape";
+        return SCALDPC_ERR_ARG;
+    }
+    std::vector<int32_t> rp(R + 1, 0), col;
+    std::vector<int8_t> val;
+    for (int r = 0; r < R; ++r) {
+        for (int c = 0; c < N; ++c)
+            if (H[(size_t)r * N + c]) {
+                col.push_back(c);
+                val.push_back(H[(size_t)r * N + c]);
+            }
+        rp[r + 1] = (int32_t)col.size();
+    }
+    col.push_back(0);  // never read; keeps data() non-null for an all-zero matrix
+    val.push_back(1);
+    return build_graph_csr(R, N, rp.data(), col.data(), val.data(), b, bsum, dv, dc, g, err);
 }
 
 // Shared-memory scratch (in floats per lane) of the runtime-shape check-node kernel.

@@ -48,7 +48,24 @@ class QaryDecoder:
     QaryDecoder(H, iterations, B=b, BSUM=bsum, DV=v, DC=sw+1)   <-> DecoderSpecial<...>            (decoder_special.rs)
     """
 
-    def __init__(self, H, iterations, B, BSUM=0, DV=0, DC=0, shape=None, device=0):
+    def __init__(self, H, iterations, B, BSUM=0, DV=0, DC=0, shape=None, device=0, csr=None):
+        self._h = C.c_void_p()
+        self._lock = threading.Lock()
+        self._qlock = threading.Lock()
+        self._pending, self._leading = [], False  # min_sum() requests waiting for the next combined batch
+        if csr is not None:
+            # sparse constructor (scaldpc_qary_create_csr): csr = (row_ptr, col, val), `shape` = (R, N); H is ignored
+            if int(iterations) < 0:
+                raise OverflowError("iterations must be a non-negative integer (u32, pydecoder.rs:24)")
+            rp, col, val = (np.ascontiguousarray(a, dtype=dt) for a, dt in zip(csr, (np.int32, np.int32, np.int8)))
+            R, N = (int(x) for x in shape)
+            if rp.shape != (R + 1,) or col.shape != val.shape or col.shape[0] != rp[-1]:
+                raise ValueError("csr = (row_ptr[R+1], col[nnz], val[nnz])")
+            _lib.check(_lib.lib().scaldpc_qary_create_csr(R, N, rp.ctypes.data, col.ctypes.data, val.ctypes.data, int(B),
+                                                          int(BSUM), int(DV), int(DC), int(iterations), int(device),
+                                                          C.byref(self._h)))
+            self._finish_init(B, BSUM, device)
+            return
         H = np.asarray(H) if not _is_torch(H) else H.cpu().numpy()
         if H.dtype != np.int8:
             # pyo3: PyReadonlyArray2<i8> extraction failure (pydecoder.rs:24, 96)
@@ -66,12 +83,11 @@ class QaryDecoder:
             H = H[: shape[0], : shape[1]]
         R, N = H.shape
         H = np.ascontiguousarray(H)
-        self._h = C.c_void_p()
-        self._lock = threading.Lock()
-        self._qlock = threading.Lock()
-        self._pending, self._leading = [], False  # min_sum() requests waiting for the next combined batch
         _lib.check(_lib.lib().scaldpc_qary_create(H.ctypes.data, R, N, int(B), int(BSUM), int(DV), int(DC),
                                                   int(iterations), int(device), C.byref(self._h)))
+        self._finish_init(B, BSUM, device)
+
+    def _finish_init(self, B, BSUM, device):
         vals = [C.c_int() for _ in range(7)]
         _lib.check(_lib.lib().scaldpc_qary_info(self._h, *[C.byref(v) for v in vals]))
         self.R, self.N, self.bvars, self.Q, self.QS, self.E, self.iterations = [v.value for v in vals]

@@ -118,3 +118,33 @@ def test_simulate_rs_class_lookup():
         simulate_rs.DecoderN6R3V3C4B7(np.zeros((3, 6), np.int64), 10)
     with pytest.raises(IndexError):  # smaller than the class's const shape (pydecoder.rs:31)
         simulate_rs.DecoderN6R3V3C4B7(np.zeros((2, 6), np.int8), 10)
+
+
+def test_qary_create_csr_validation(lib):
+    """scaldpc_qary_create_csr: the sparse constructor validates its CSR before it touches the device
+    and then applies the same construction checks as the dense one (decoder_special.rs:388-395, decoder.rs:465-473)."""
+    def create(rp, col, val, R, N, b, bsum, dc=0):
+        rp, col, val = np.asarray(rp, np.int32), np.asarray(col, np.int32), np.asarray(val, np.int8)
+        h = C.c_void_p()
+        rc = lib.scaldpc_qary_create_csr(R, N, rp.ctypes.data, col.ctypes.data, val.ctypes.data, b, bsum, 0, dc, 3, 0, C.byref(h))
+        msg = lib.scaldpc_last_error().decode()
+        if h:
+            lib.scaldpc_qary_destroy(h)
+        return rc, msg
+
+    # H = [[1, 1, 0 | 1, 0], [0, -1, 1 | 0, 1]]
+    rp, col, val = [0, 3, 6], [0, 1, 3, 1, 2, 4], [1, 1, 1, -1, 1, 1]
+    rc, msg = create(rp, col, val, 2, 5, 2, 4)
+    assert rc in (0, _lib.ERR_CUDA), msg              # a valid graph: only the missing device can stop it
+    rc, msg = create(rp, [1, 0, 3, 1, 2, 4], val, 2, 5, 2, 4)
+    assert rc == _lib.ERR_ARG and "ascending" in msg
+    rc, msg = create(rp, [0, 1, 5, 1, 2, 4], val, 2, 5, 2, 4)
+    assert rc == _lib.ERR_ARG and "out of range" in msg
+    rc, msg = create(rp, col, [1, 0, 1, -1, 1, 1], 2, 5, 2, 4)
+    assert rc == _lib.ERR_ARG and "zero" in msg
+    rc, msg = create(rp, col, val, 2, 5, 2, 5)
+    assert rc == _lib.ERR_STRUCTURE and "multiple of B" in msg
+    rc, msg = create(rp, col, val, 2, 5, 2, 4, dc=2)
+    assert rc == _lib.ERR_DEGREE
+    rc, msg = create(rp, col, val, 2, 5, 2, 2)
+    assert rc == _lib.ERR_RANGE

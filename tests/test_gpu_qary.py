@@ -485,3 +485,24 @@ def test_single_decode_graph_path():
     one = d.min_sum(good.priors[3], good.priors_sum[3])
     assert one == d.min_sum_batch(good.priors[3:4], good.priors_sum[3:4], want_posterior=False)[0][0].tolist()
     assert (np.array(one[: w.bvars]) == good.secret[3]).all()
+
+
+def test_sparse_constructor_equals_dense():
+    """scaldpc_qary_create_csr: a decoder built from the CSR of H gives bit-identical results to the one built from the dense
+    int8 matrix (pydecoder.rs:24-45), special and generic decoder."""
+    w = KyberWorkload("kyber768", sum_weight=6, check_blocks=2, accuracy=0.95, nbits=3, nbits_sum=4, seed=4)
+    b = w.generate(50, seed=5)
+    rows, cols = np.nonzero(w.H)
+    rp = np.concatenate(([0], np.cumsum(np.bincount(rows, minlength=w.R)))).astype(np.int32)
+    sparse = QaryDecoder(None, 5, shape=(w.R, w.N), csr=(rp, cols, w.H[rows, cols]), **w.decoder_kwargs)
+    dense = QaryDecoder(w.H, 5, **w.decoder_kwargs)
+    assert (sparse.R, sparse.N, sparse.E, sparse.Q, sparse.QS) == (dense.R, dense.N, dense.E, dense.Q, dense.QS)
+    for a, c in zip(sparse.min_sum_batch(b.priors, b.priors_sum), dense.min_sum_batch(b.priors, b.priors_sum)):
+        assert np.array_equal(a, c, equal_nan=True)
+    z = util.load("rust_unit_tests.npz")
+    Hm = util.dense(z, "Hm")
+    rows, cols = np.nonzero(Hm)
+    rp = np.concatenate(([0], np.cumsum(np.bincount(rows, minlength=150)))).astype(np.int32)
+    g = QaryDecoder(None, 10, B=7, DV=3, DC=7, shape=(150, 450), csr=(rp, cols, Hm[rows, cols]))
+    hard, post, _ = g.min_sum_batch(_corrupted(450)[None], exact=True)
+    assert np.array_equal(hard[0], z["medium_hard"]) and np.array_equal(post[0], z["medium_post"], equal_nan=True)
