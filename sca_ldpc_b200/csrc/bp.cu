@@ -64,6 +64,8 @@ struct scaldpc_bp {
     int cn_warps = 8, cn_occ[2] = {1, 1};
     size_t smem_cn = 0;
     int vn_occ[8] = {0};  // bit pass: resident CTAs per SM of each degree-class kernel
+    int vn_pipe_occ[8] = {0};  // ... of the cp.async-pipelined kernels
+    bool vn_pipe = true;       // SCALDPC_BP_VN_PIPE=0: register-prefetch kernels for every iteration
     int vn_single_tiles = 64;  // at most this many tiles: one any-degree launch per bit pass (SCALDPC_BP_VN_SINGLE=n)
     long long vn_single_items = 65536;  // ... and at most this many (tile, variable) items (SCALDPC_BP_VN_SINGLE_ITEMS=n)
     // (round 1 also had k_bp_vn_tma: column gather by per-lane bulk-async copies into a 4-stage ring.  Measured on hqc128 /
@@ -256,6 +258,32 @@ bp_vn_fn vn_class_fn(int c, bool first = false)
 #undef CLS
 }
 
+// The cp.async-pipelined bit pass of iterations >= 2 (k_bp_vn_pipe) and its shared memory per CTA.
+bp_vn_fn vn_pipe_fn(int c)
+{
+    switch (c) {
+    case 1: return k_bp_vn_pipe<1, 4>;
+    case 2: return k_bp_vn_pipe<4, 8>;
+    case 3: return k_bp_vn_pipe<8, 12>;
+    case 4: return k_bp_vn_pipe<12, 16>;
+    case 5: return k_bp_vn_pipe<16, 24>;
+    case 6: return k_bp_vn_pipe<24, 32>;
+    default: return nullptr;  // degree <= 1: nothing to pipeline
+    }
+}
+size_t vn_pipe_smem(int c)
+{
+    switch (c) {
+    case 1: return BpVnPipe<4>::smem_bytes;
+    case 2: return BpVnPipe<8>::smem_bytes;
+    case 3: return BpVnPipe<12>::smem_bytes;
+    case 4: return BpVnPipe<16>::smem_bytes;
+    case 5: return BpVnPipe<24>::smem_bytes;
+    case 6: return BpVnPipe<32>::smem_bytes;
+    default: return 0;
+    }
+}
+
 // Bit pass: one persistent launch per non-empty degree class (variables are sorted by degree); columns heavier than
 // the largest register class go through the shared-memory kernel.
 int launch_vn(scaldpc_bp *h, const BpDev &p, int tiles, cudaStream_t st, bool first = false)
@@ -279,8 +307,13 @@ int launch_vn(scaldpc_bp *h, const BpDev &p, int tiles, cudaStream_t st, bool fi
         if (hi > lo) {
             if (c < kBpVnClasses) {
                 const long long items = (long long)tiles * (hi - lo);
-                const int ctas = (int)std::min<long long>((long long)h->num_sms * h->vn_occ[c], (items + kBpVnWarps - 1) / kBpVnWarps);
-                vn_class_fn(c, first)<<<std::max(1, ctas), kBpVnWarps * 32, 0, st>>>(p, lo, hi, tiles, multi ? c : -1);
+                const bool pipe = !first && h->vn_pipe && vn_pipe_fn(c);
+                const int occ = pipe ? h->vn_pipe_occ[c] : h->vn_occ[c];
+                const int ctas = (int)std::min<long long>((long long)h->num_sms * occ, (items + kBpVnWarps - 1) / kBpVnWarps);
+                if (pipe)
+                    vn_pipe_fn(c)<<<std::max(1, ctas), kBpVnWarps * 32, vn_pipe_smem(c), st>>>(p, lo, hi, tiles, multi ? c : -1);
+                else
+                    vn_class_fn(c, first)<<<std::max(1, ctas), kBpVnWarps * 32, 0, st>>>(p, lo, hi, tiles, multi ? c : -1);
             } else {
                 generic<<<dim3((hi - lo + h->vn_gen_wpc - 1) / h->vn_gen_wpc, tiles), h->vn_gen_wpc * 32, h->smem_vn, st>>>(
                     p, lo, hi, multi ? c : -1);
@@ -435,9 +468,16 @@ static int bp_create_impl(int G, int m, int n, const int32_t *row_ptr, const int
     }
     if (const char *e = getenv("SCALDPC_BP_VN_SINGLE")) h->vn_single_tiles = atoi(e);
     if (const char *e = getenv("SCALDPC_BP_VN_SINGLE_ITEMS")) h->vn_single_items = atoll(e);
+    if (const char *e = getenv("SCALDPC_BP_VN_PIPE")) h->vn_pipe = atoi(e) != 0;
     for (int c = 0; c < kBpVnClasses; ++c) {
         SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->vn_occ[c], vn_class_fn(c), kBpVnWarps * 32, 0));
         h->vn_occ[c] = std::max(1, h->vn_occ[c]);
+        if (vn_pipe_fn(c)) {
+            SCALDPC_CUDA(cudaFuncSetAttribute(vn_pipe_fn(c), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vn_pipe_smem(c)));
+            SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->vn_pipe_occ[c], vn_pipe_fn(c), kBpVnWarps * 32,
+                                                                       vn_pipe_smem(c)));
+            h->vn_pipe_occ[c] = std::max(1, h->vn_pipe_occ[c]);
+        }
     }
     SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->cn_occ[0], k_bp_cn<false>, h->cn_warps * 32, h->smem_cn));
     SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->cn_occ[1], k_bp_cn<true>, h->cn_warps * 32, h->smem_cn));

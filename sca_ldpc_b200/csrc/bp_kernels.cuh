@@ -568,6 +568,123 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const 
     }
 }
 
+#ifndef SCALDPC_HOST_MODEL
+// -----------------------------------------------------------------------------------------------------------
+// The same pass (iterations >= 2) with the column gather as a software pipeline of per-lane asynchronous copies.
+// ncu on k_bp_vn (profiles/r2n_ncu_bp_vn_hqc128.txt): 3.75 TB/s, long_scoreboard 10 warps per issue, 48-64 registers =
+// 40-32 resident warps with ~1.3 columns in flight each -- ~30 KB in flight per SM is exactly what 3.7 TB/s needs at
+// ~1.2 us of loaded latency (Little), and every byte in flight pins a destination REGISTER until it lands.  Here the
+// landing zone is shared memory: lane l copies ITS 4 bytes of every line of a column with cp.async (LDGSTS, no
+// destination register), kBpVnStages columns per warp are always in flight, and a column costs one LDS per line when its
+// turn comes.  A lane only ever reads what it copied itself, so cp.async.wait_group is the only synchronisation -- no
+// mbarrier, no __syncwarp (the per-lane 128-byte BULK copies of round 1's k_bp_vn_tma were serialised by the TMA unit).
+// Arithmetic and stores are bp_vn_body's: bit-identical to k_bp_vn, which stays for iteration 1 (FIRST) and the host model.
+// -----------------------------------------------------------------------------------------------------------
+template <int DMAX>
+struct BpVnPipe {
+    static constexpr int stages = DMAX <= 12 ? 4 : (DMAX <= 16 ? 3 : 2);
+    static constexpr size_t smem_bytes = (size_t)kBpVnWarps * stages * DMAX * 32 * sizeof(float);
+};
+
+__device__ __forceinline__ void sc_cp_async4(float *smem_dst, const float *gsrc)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void sc_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void sc_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <int DMIN, int DMAX>
+__global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_pipe(const BpDev p, const int v_lo, const int v_hi, const int tiles,
+                                                                const int cls)
+{
+    constexpr int S = BpVnPipe<DMAX>::stages;
+    extern __shared__ __align__(128) float sc_vn_ring[];  // [warp][stage][DMAX][32]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
+    const int gw = blockIdx.x * wpc + warp, nw = gridDim.x * wpc;
+    const int nv = v_hi - v_lo;
+    const int step_t = nw / nv, step_j = nw - step_t * nv;
+    float *ring = sc_vn_ring + (size_t)warp * S * DMAX * 32 + lane;
+
+    auto advance = [&](BpVnItem &it, bool first) {  // as k_bp_vn
+        bool step = !first;
+        int g = 0, lo = v_lo;
+        while (true) {
+            if (step) {
+                it.tile += step_t;
+                it.j += step_j;
+                if (it.j >= nv) {
+                    it.j -= nv;
+                    ++it.tile;
+                }
+            }
+            step = true;
+            if (it.tile >= tiles) break;
+            if (bp_tile_done(p, it.tile)) continue;
+            if (p.class_end) {
+                g = bp_graph(p, it.tile);
+                const int *ce = p.class_end + g * (kBpVnClassCount + 1);
+                lo = cls > 0 ? __ldg(ce + cls - 1) : 0;
+                if (it.j >= __ldg(ce + cls) - lo) continue;
+            }
+            break;
+        }
+        if (it.tile < tiles) {
+            it.var = __ldg(p.vn_order + (size_t)g * p.g_n + lo + it.j);
+            const int *cp = p.col_ptr + (size_t)g * p.g_cp + it.var;
+            const int c0 = __ldg(cp);
+            it.d = __ldg(cp + 1) - c0;
+            it.p0 = g * p.g_e + c0;
+        }
+    };
+    auto issue = [&](const BpVnItem &it, int s) {  // lane l: its 4 bytes of every line of the column -> stage s
+        const float *src = p.msg + (size_t)it.tile * p.E * 32 + lane;
+        const uint32_t *off = p.csc_off + it.p0;
+        float *dst = ring + (size_t)s * DMAX * 32;
+#pragma unroll
+        for (int i = 0; i < DMAX; ++i)
+            if ((DMIN > 0 && i <= DMIN) || i < it.d) sc_cp_async4(dst + i * 32, (const float *)((const char *)src + __ldg(off + i)));
+    };
+
+    BpVnItem it[S], x;
+    float pr[S];
+    x.tile = gw / nv;
+    x.j = gw - x.tile * nv;
+    advance(x, true);
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+        it[s] = x;
+        pr[s] = 0.0f;
+        if (x.tile < tiles) {
+            issue(x, s);
+            pr[s] = bp_prior_of(p, x.tile, x.var, lane);
+            advance(x, false);
+        }
+        sc_cp_async_commit();
+    }
+    while (true) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            if (it[s].tile >= tiles) return;  // items are consumed in order: nothing is pending behind an empty stage
+            sc_cp_async_wait<S - 1>();
+            float c[DMAX];
+            const float *st = ring + (size_t)s * DMAX * 32;
+#pragma unroll
+            for (int i = 0; i < DMAX; ++i)
+                if ((DMIN > 0 && i <= DMIN) || i < it[s].d) c[i] = st[i * 32];
+            bp_vn_dispatch<DMAX, (DMIN == 0 ? 0 : DMIN + 1), DMAX>(p, it[s], lane, c, pr[s]);
+            it[s] = x;  // refill the stage (its values sit in registers now)
+            if (x.tile < tiles) {
+                issue(x, s);
+                pr[s] = bp_prior_of(p, x.tile, x.var, lane);
+                advance(x, false);
+            }
+            sc_cp_async_commit();
+        }
+    }
+}
+#endif
+
 // Any degree (columns heavier than the largest register class): per-lane scratch [i][lane] in shared memory,
 // one CTA pass over (variable, tile) without prefetch.
 // Segmented CSR: cls >= 0 -> the tile's own slice of that class (v_lo = 0, v_hi = largest slice); cls < 0 -> [v_lo, v_hi)
