@@ -292,6 +292,19 @@ int scaldpc_bp_decode_nested(scaldpc_bp *h, int T, const int32_t *n_checks, cons
  */
 int scaldpc_bp_create_multi(int n_graphs, int m, int n, const int32_t *row_ptr, const int32_t *col, int max_iter, int device,
                             scaldpc_bp **out);
+/*
+ * scaldpc_bp_create_circulant -- the graphs of scaldpc_bp_create_multi built ON THE DEVICE from what the reference builds them
+ * from.  The reference makes a dense N x N circulant of a sparse first column per attack (make_code.py:220-244
+ * make_random_ldpc_parity_check_matrix, 2.5 GB for HQC-128), takes the rows of the measured positions (add_check,
+ * hqc.py:885-908) and appends the identity (hqc.py:680).  Here:
+ *   first_col  G x weight int32: support of every circulant's first column (= r1_sparse, hqc.py:1059), distinct, any order
+ *   rows       G x m int32: the measured positions b_0 .. b_{m-1} of every graph, in the order the checks were added
+ * Row i of graph g is { (rows[g][i] - r) mod n_msg : r in first_col[g] } and the identity column n_msg + i.  CSR, CSC, the
+ * degree-sorted variable order and every other table the decoder uses are produced by kernels (bp_build.cuh); the handle is
+ * indistinguishable from one made by scaldpc_bp_create_multi on the same matrices.  weight <= 128.
+ */
+int scaldpc_bp_create_circulant(int n_graphs, int n_msg, int weight, int m, const int32_t *first_col, const int32_t *rows,
+                                int max_iter, int device, scaldpc_bp **out);
 int scaldpc_bp_decode_multi(scaldpc_bp *h, int T, const int32_t *graph_of, const int32_t *n_checks, const uint8_t *synd,
                             const double *channel_probs, const int32_t *truth, int weight, int32_t *stats, uint8_t *decoding,
                             float *llr, int32_t *iters, int32_t *converged, unsigned flags, void *stream);

@@ -10,6 +10,7 @@
 
 #include "bp_graph.h"
 #include "bp_kernels.cuh"
+#include "bp_build.cuh"
 #include "common.h"
 
 using namespace scaldpc;
@@ -65,7 +66,8 @@ struct scaldpc_bp {
     size_t smem_cn = 0;
     int vn_occ[8] = {0};  // bit pass: resident CTAs per SM of each degree-class kernel
     int vn_pipe_occ[8] = {0};  // ... of the cp.async-pipelined kernels
-    bool vn_pipe = true;       // SCALDPC_BP_VN_PIPE=0: register-prefetch kernels for every iteration
+    bool vn_pipe = false;      // SCALDPC_BP_VN_PIPE=1: cp.async-pipelined bit pass.  Measured SLOWER than the register-prefetch
+                               // kernels (hqc128 413 k vs 454 k trials/s, profiles/r2o_*): off, kept for experiments
     int vn_single_tiles = 64;  // at most this many tiles: one any-degree launch per bit pass (SCALDPC_BP_VN_SINGLE=n)
     long long vn_single_items = 65536;  // ... and at most this many (tile, variable) items (SCALDPC_BP_VN_SINGLE_ITEMS=n)
     // (round 1 also had k_bp_vn_tma: column gather by per-lane bulk-async copies into a 4-stage ring.  Measured on hqc128 /
@@ -364,6 +366,36 @@ int compact(scaldpc_bp *h, int cur, int cur_tiles, int n_run, bool probs_t, uint
 
 extern "C" {
 
+static int bp_finish_create(scaldpc_bp *h);
+
+// Degree-class bounds of all graphs -> the handle's launch parameters; shared-memory budgets of the kernels whose scratch
+// depends on the largest row / column degree (h->dc_max, h->dv_max).
+static int bp_size_kernels(scaldpc_bp *h, const std::vector<int> &class_end_all)
+{
+    for (int c = 0; c <= kBpVnClasses; ++c) {
+        h->class_end[c] = class_end_all[c];
+        h->class_max[c] = 0;
+    }
+    for (int g = 0; g < h->G; ++g)
+        for (int c = 0; c <= kBpVnClasses; ++c) {
+            const int *ce = &class_end_all[(size_t)g * (kBpVnClasses + 1)];
+            h->class_max[c] = std::max(h->class_max[c], ce[c] - (c ? ce[c - 1] : 0));
+        }
+    // check pass: per warp a double-buffered row stage + the prefix array, 3 x dc_max x 128 B
+    const size_t per_warp = (size_t)3 * h->dc_max * 32 * sizeof(float);
+    h->cn_warps = (int)std::min<size_t>(kBpCnWarpsMax, (216 * 1024) / per_warp);
+    if (h->cn_warps < 1)
+        return fail(SCALDPC_ERR_UNSUPPORTED, "row degree %d too large for the shared-memory staging", h->dc_max);
+    h->smem_cn = per_warp * h->cn_warps;
+    // shared-memory bit-pass kernel: heavy columns, and the whole pass of small (launch-bound) batches
+    const size_t pw = (size_t)2 * h->dv_max * 32 * sizeof(float);
+    h->vn_gen_wpc = (int)std::min<size_t>(kBpVnWarps, (216 * 1024) / pw);
+    if (h->vn_gen_wpc < 1)
+        return fail(SCALDPC_ERR_UNSUPPORTED, "column degree %d too large for the shared-memory scratch", h->dv_max);
+    h->smem_vn = pw * h->vn_gen_wpc;
+    return 0;
+}
+
 // G >= 1 graphs of shape m x n: row_ptr = G x (m+1) (every segment starts at 0), col = the G column arrays back to back.
 static int bp_create_impl(int G, int m, int n, const int32_t *row_ptr, const int32_t *col, int max_iter, int device,
                           scaldpc_bp **out)
@@ -399,28 +431,12 @@ static int bp_create_impl(int G, int m, int n, const int32_t *row_ptr, const int
     h->dv_max = std::max(1, dv_max);
     h->max_iter = max_iter == 0 ? n : max_iter;  // upstream: max_iter = 0 means n
     h->device = device;
-    for (int c = 0; c <= kBpVnClasses; ++c) h->class_end[c] = gs[0].class_end[c];
     std::vector<int> class_end_all((size_t)G * (kBpVnClasses + 1));
     for (int g = 0; g < G; ++g)
-        for (int c = 0; c <= kBpVnClasses; ++c) {
-            class_end_all[(size_t)g * (kBpVnClasses + 1) + c] = gs[g].class_end[c];
-            h->class_max[c] = std::max(h->class_max[c], gs[g].class_end[c] - (c ? gs[g].class_end[c - 1] : 0));
-        }
-    // check pass: per warp a double-buffered row stage + the prefix array, 3 x dc_max x 128 B
-    const size_t per_warp = (size_t)3 * h->dc_max * 32 * sizeof(float);
-    h->cn_warps = (int)std::min<size_t>(kBpCnWarpsMax, (216 * 1024) / per_warp);
-    if (h->cn_warps < 1)
-        return fail(SCALDPC_ERR_UNSUPPORTED, "row degree %d too large for the shared-memory staging", h->dc_max);
-    h->smem_cn = per_warp * h->cn_warps;
-    {  // shared-memory bit-pass kernel: heavy columns, and the whole pass of small (launch-bound) batches
-        const size_t pw = (size_t)2 * h->dv_max * 32 * sizeof(float);
-        h->vn_gen_wpc = (int)std::min<size_t>(kBpVnWarps, (216 * 1024) / pw);
-        if (h->vn_gen_wpc < 1)
-            return fail(SCALDPC_ERR_UNSUPPORTED, "column degree %d too large for the shared-memory scratch", h->dv_max);
-        h->smem_vn = pw * h->vn_gen_wpc;
-    }
+        for (int c = 0; c <= kBpVnClasses; ++c) class_end_all[(size_t)g * (kBpVnClasses + 1) + c] = gs[g].class_end[c];
+    int rc;
+    if ((rc = bp_size_kernels(h.get(), class_end_all))) return rc;
     SCALDPC_CUDA(cudaSetDevice(device));
-    SCALDPC_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
     // the per-graph tables, concatenated with the fixed strides m+1 / Emax / n+1 / n (BpDev g_rp / g_e / g_cp / g_n);
     // a graph with fewer edges than Emax is padded: its padding edges belong to "row m" (never active) and are never
     // reached through row_ptr / col_ptr
@@ -444,13 +460,23 @@ static int bp_create_impl(int G, int m, int n, const int32_t *row_ptr, const int
             a_csc_row[(size_t)g * Emax + i] = a_edge_row[(size_t)g * Emax + e];
         }
     }
-    int rc;
     if ((rc = upload_vec(&h->d_row_ptr, a_row_ptr)) || (rc = upload_vec(&h->d_col, a_col)) ||
         (rc = upload_vec(&h->d_col_ptr, a_col_ptr)) || (rc = upload_vec(&h->d_csc_edge, a_csc_off)) ||
         (rc = upload_vec(&h->d_vn_order, a_vn_order)) || (rc = upload_vec(&h->d_vn_desc, a_vn_desc)) ||
         (rc = upload_vec(&h->d_edge_row, a_edge_row)) || (rc = upload_vec(&h->d_class_end, class_end_all)) ||
         (rc = upload_vec(&h->d_edge_csc, a_edge_csc)) || (rc = upload_vec(&h->d_csc_row, a_csc_row)))
         return rc;
+    if ((rc = bp_finish_create(h.get()))) return rc;
+    *out = h.release();
+    return 0;
+}
+
+// Everything of a handle that does not depend on where its graph tables came from: work buffers, kernel attributes,
+// occupancies.  The tables (d_row_ptr ... d_csc_row, d_class_end) are on the device, bp_size_kernels() has run.
+static int bp_finish_create(scaldpc_bp *h)
+{
+    const int G = h->G, Emax = h->E, n = h->n, device = h->device;
+    SCALDPC_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_first_tab, (size_t)G * std::max(1, Emax) * sizeof(float)));
     SCALDPC_CUDA(cudaMalloc((void **)&h->d_csc_tab, (size_t)G * std::max(1, Emax) * sizeof(float)));
     SCALDPC_CUDA(cudaMemset(h->d_csc_tab, 0, (size_t)G * std::max(1, Emax) * sizeof(float)));
@@ -483,7 +509,6 @@ static int bp_create_impl(int G, int m, int n, const int32_t *row_ptr, const int
     SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->cn_occ[1], k_bp_cn<true>, h->cn_warps * 32, h->smem_cn));
     h->cn_occ[0] = std::max(1, h->cn_occ[0]);
     h->cn_occ[1] = std::max(1, h->cn_occ[1]);
-    *out = h.release();
     return 0;
 }
 
@@ -779,6 +804,84 @@ int scaldpc_bp_decode_scored(scaldpc_bp *h, int T, int n_msg, const int32_t *n_c
 {
     const BpScore score{truth, weight, n_msg, stats};
     return bp_decode_impl(h, T, synd, channel_probs, decoding, nullptr, iters, converged, flags, stream, &score, n_checks);
+}
+
+int scaldpc_bp_create_circulant(int n_graphs, int n_msg, int weight, int m, const int32_t *first_col, const int32_t *rows,
+                                int max_iter, int device, scaldpc_bp **out)
+{
+    if (!out) return fail(SCALDPC_ERR_ARG, "out is NULL");
+    *out = nullptr;
+    if (max_iter < 0) return fail(SCALDPC_ERR_ARG, "max_iter must be >= 0");
+    if (n_graphs < 1 || n_msg < 1 || m < 1 || weight < 1 || weight > 128 || weight > n_msg || !first_col || !rows)
+        return fail(SCALDPC_ERR_ARG, "bad circulant description (1 <= weight <= 128)");
+    const long long E = (long long)m * (weight + 1);
+    if (E * 128 > 0xffffffffLL) return fail(SCALDPC_ERR_UNSUPPORTED, "too many edges");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
+        return fail(SCALDPC_ERR_CUDA, "CUDA device %d not available (%d visible) -- libscaldpc has no CPU path", device,
+                    ndev);
+    std::unique_ptr<scaldpc_bp, void (*)(scaldpc_bp *)> h(new scaldpc_bp, scaldpc_bp_destroy);
+    const int G = n_graphs, n = n_msg + m;
+    h->m = m;
+    h->n = n;
+    h->E = (int)E;
+    h->G = G;
+    h->dc_max = weight + 1;
+    h->max_iter = max_iter == 0 ? n : max_iter;
+    h->device = device;
+    SCALDPC_CUDA(cudaSetDevice(device));
+    // every table of bp_create_impl, allocated empty and filled by the kernels of bp_build.cuh
+    const size_t ge = (size_t)G * E;
+    int *d_first = nullptr, *d_rows = nullptr, *d_cursor = nullptr, *d_err = nullptr, *d_csc_edge = nullptr, *d_bound = nullptr;
+    struct Scratch {
+        int **p[6];
+        ~Scratch() { for (auto q : p) if (q && *q) cudaFree(*q); }
+    } scratch{{&d_first, &d_rows, &d_cursor, &d_err, &d_csc_edge, &d_bound}};
+    SCALDPC_CUDA(cudaMalloc((void **)&d_first, (size_t)G * weight * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&d_rows, (size_t)G * m * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&d_cursor, (size_t)G * n * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&d_err, 2 * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&d_csc_edge, ge * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&d_bound, kBpVnClasses * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_row_ptr, (size_t)G * (m + 1) * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_col, ge * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_col_ptr, (size_t)G * (n + 1) * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_csc_edge, ge * sizeof(uint32_t)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_vn_order, (size_t)G * n * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_vn_desc, (size_t)G * 4 * n * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_edge_row, ge * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_edge_csc, ge * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_csc_row, ge * sizeof(int)));
+    SCALDPC_CUDA(cudaMalloc((void **)&h->d_class_end, (size_t)G * (kBpVnClasses + 1) * sizeof(int)));
+    SCALDPC_CUDA(cudaMemcpy(d_first, first_col, (size_t)G * weight * sizeof(int), cudaMemcpyHostToDevice));
+    SCALDPC_CUDA(cudaMemcpy(d_rows, rows, (size_t)G * m * sizeof(int), cudaMemcpyHostToDevice));
+    SCALDPC_CUDA(cudaMemcpy(d_bound, kBpVnClass, kBpVnClasses * sizeof(int), cudaMemcpyHostToDevice));
+    SCALDPC_CUDA(cudaMemset(d_cursor, 0, (size_t)G * n * sizeof(int)));
+    SCALDPC_CUDA(cudaMemset(d_err, 0, 2 * sizeof(int)));
+    CircDev d;
+    d.G = G; d.N = n_msg; d.W = weight; d.m = m; d.n = n; d.E = (int)E;
+    d.first_col = d_first; d.rows = d_rows;
+    d.row_ptr = h->d_row_ptr; d.col = h->d_col; d.col_ptr = h->d_col_ptr; d.vn_order = h->d_vn_order; d.vn_desc = h->d_vn_desc;
+    d.edge_row = h->d_edge_row; d.edge_csc = h->d_edge_csc; d.csc_row = h->d_csc_row; d.class_end = h->d_class_end;
+    d.csc_off = h->d_csc_edge; d.cursor = d_cursor; d.err = d_err;
+    k_circ_sort_support<<<(G + 63) / 64, 64>>>(d);
+    k_circ_rows<<<(unsigned)((ge + 255) / 256), 256>>>(d);
+    k_circ_scan<<<G, 1024>>>(d);
+    k_circ_fill<<<(unsigned)((ge + 255) / 256), 256>>>(d, d_csc_edge);
+    k_circ_order<<<(unsigned)(((size_t)G * n + 255) / 256), 256>>>(d, d_csc_edge);
+    int herr[2] = {0, 0};
+    SCALDPC_CUDA(cudaMemcpy(herr, d_err, sizeof herr, cudaMemcpyDeviceToHost));  // also the first synchronisation point
+    if (herr[0]) return fail(SCALDPC_ERR_ARG, "first_col needs %d distinct positions in 0 .. n_msg-1 per graph, rows positions in 0 .. n_msg-1", weight);
+    h->dv_max = std::max(1, herr[1]);
+    k_circ_degsort<<<G, 1024>>>(d, h->dv_max, d_bound, kBpVnClasses);
+    h->launches += 6;
+    SCALDPC_CUDA(cudaGetLastError());
+    std::vector<int> class_end_all((size_t)G * (kBpVnClasses + 1));
+    SCALDPC_CUDA(cudaMemcpy(class_end_all.data(), h->d_class_end, class_end_all.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    int rc;
+    if ((rc = bp_size_kernels(h.get(), class_end_all)) || (rc = bp_finish_create(h.get()))) return rc;
+    *out = h.release();
+    return 0;
 }
 
 int scaldpc_bp_decode_multi(scaldpc_bp *h, int T, const int32_t *graph_of, const int32_t *n_checks, const uint8_t *synd,

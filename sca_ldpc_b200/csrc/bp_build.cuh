@@ -52,7 +52,7 @@ __global__ void __launch_bounds__(256) k_circ_rows(const CircDev d)
 {
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const int per = d.W + 1;
-    if (idx >= (long long)d.G * d.m * per) return;
+    if (idx >= (long long)d.G * d.m * per || d.err[0]) return;  // a bad support (k_circ_sort_support) stops everything
     const int k = (int)(idx % per);
     const int i = (int)((idx / per) % d.m);
     const int g = (int)(idx / ((long long)per * d.m));
@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(1024) k_circ_scan(const CircDev d)
 __global__ void __launch_bounds__(256) k_circ_fill(const CircDev d, int *csc_edge)
 {
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= (long long)d.G * d.E) return;
+    if (idx >= (long long)d.G * d.E || d.err[0]) return;  // after a bad description `col` is not fully written
     const int g = (int)(idx / d.E), e = (int)(idx % d.E);
     const int c = d.col[idx];
     const int left = atomicSub(d.cursor + (size_t)g * d.n + c, 1);  // degree .. 1
@@ -142,7 +142,7 @@ __global__ void __launch_bounds__(256) k_circ_fill(const CircDev d, int *csc_edg
 __global__ void __launch_bounds__(256) k_circ_order(const CircDev d, int *csc_edge)
 {
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= (long long)d.G * d.n) return;
+    if (idx >= (long long)d.G * d.n || d.err[0]) return;
     const int g = (int)(idx / d.n), v = (int)(idx % d.n);
     const int *cp = d.col_ptr + (size_t)g * (d.n + 1) + v;
     const int p0 = cp[0], deg = cp[1] - cp[0];

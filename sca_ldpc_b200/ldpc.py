@@ -279,8 +279,21 @@ class bp_decoder_multi:
 
     STAT_NAMES = bp_decoder.STAT_NAMES
 
-    def __init__(self, graphs, shape, max_iter=0, channel_probs=None, error_rate=None, device=0):
+    def __init__(self, graphs, shape, max_iter=0, channel_probs=None, error_rate=None, device=0, _circulant=None):
         self.m, self.n = (int(x) for x in shape)
+        if _circulant is not None:  # from_circulants: the graphs are built on the device
+            first_col, rows, n_msg = _circulant
+            self.G = first_col.shape[0]
+            self._set_probs(channel_probs, error_rate)
+            self.device = int(device)
+            self._h = C.c_void_p()
+            _lib.check(_lib.lib().scaldpc_bp_create_circulant(self.G, int(n_msg), first_col.shape[1], self.m,
+                                                              first_col.ctypes.data, rows.ctypes.data, int(max_iter),
+                                                              self.device, C.byref(self._h)))
+            vals = [C.c_int() for _ in range(4)]
+            _lib.check(_lib.lib().scaldpc_bp_info(self._h, *[C.byref(v) for v in vals]))
+            self.E, self.max_iter = vals[2].value, vals[3].value
+            return
         self.G = len(graphs)
         if self.G < 1:
             raise ValueError("at least one graph is needed")
@@ -298,15 +311,7 @@ class bp_decoder_multi:
             cols.append(col)
         row_ptr = np.ascontiguousarray(np.concatenate(rps), dtype=np.int32)
         col = np.ascontiguousarray(np.concatenate(cols), dtype=np.int32)
-        if channel_probs is not None:
-            cp = np.asarray(channel_probs, dtype=np.float64)
-        elif error_rate is not None:
-            cp = np.full(self.n, float(error_rate), dtype=np.float64)
-        else:
-            raise ValueError("either error_rate or channel_probs is required")
-        if cp.shape != (self.n,):
-            raise ValueError(f"channel_probs must have length n = {self.n}")
-        self.channel_probs = np.ascontiguousarray(cp)
+        self._set_probs(channel_probs, error_rate)
         self.device = int(device)
         self._h = C.c_void_p()
         _lib.check(_lib.lib().scaldpc_bp_create_multi(self.G, self.m, self.n, row_ptr.ctypes.data, col.ctypes.data,
@@ -319,6 +324,30 @@ class bp_decoder_multi:
         h, self._h = getattr(self, "_h", None), None
         if h and _lib._lib is not None:
             _lib._lib.scaldpc_bp_destroy(h)
+
+    def _set_probs(self, channel_probs, error_rate):
+        if channel_probs is not None:
+            cp = np.asarray(channel_probs, dtype=np.float64)
+        elif error_rate is not None:
+            cp = np.full(self.n, float(error_rate), dtype=np.float64)
+        else:
+            raise ValueError("either error_rate or channel_probs is required")
+        if cp.shape != (self.n,):
+            raise ValueError(f"channel_probs must have length n = {self.n}")
+        self.channel_probs = np.ascontiguousarray(cp)
+
+    @classmethod
+    def from_circulants(cls, first_cols, rows, n_msg, **kw):
+        """G graphs H_g = [rows of circulant(first_cols[g]) | I] built ON THE DEVICE (scaldpc_bp_create_circulant): what
+        make_random_ldpc_parity_check_matrix (make_code.py:220-244) + add_check (hqc.py:885-908) + hqc.py:680 build as dense
+        matrices.  first_cols (G, W) int32 = support of every first column (r1_sparse, hqc.py:1059); rows (G, m) int32 = the
+        measured positions in the order they were added."""
+        first_cols = np.ascontiguousarray(first_cols, dtype=np.int32)
+        rows = np.ascontiguousarray(rows, dtype=np.int32)
+        if first_cols.ndim != 2 or rows.ndim != 2 or rows.shape[0] != first_cols.shape[0]:
+            raise ValueError("first_cols must be (G, W) and rows (G, m)")
+        m = rows.shape[1]
+        return cls(None, (m, int(n_msg) + m), _circulant=(first_cols, rows, int(n_msg)), **kw)
 
     @classmethod
     def from_prefixes(cls, row_ptr, col, shape, levels, **kw):

@@ -421,3 +421,55 @@ def test_prefix_graphs_equal_nested_decode():
     for t in range(T):
         R = n_checks[t]
         assert np.array_equal(a["decoding"][t, : w.N + R], b["decoding"][t, : w.N + R]), t
+
+
+def test_graphs_built_on_the_device_equal_host_built_graphs():
+    """scaldpc_bp_create_circulant: the graphs of a batch of simulated attacks built by kernels from
+    (support of the circulant's first column, measured positions) == the same graphs built on the host from their CSR
+    (which tests above tie to the fp64 oracle): identical decisions, iteration counts and posteriors, bit for bit; and the
+    rows are the reference's: rows of scipy-style circulant(first column) (make_code.py:220-244) plus the identity."""
+    from sca_ldpc_b200.ldpc import bp_decoder_multi
+
+    rs = np.random.RandomState(11)
+    G, N, W, m = 7, 997, 11, 420
+    first_cols = np.stack([rs.choice(N, W, replace=False) for _ in range(G)]).astype(np.int32)      # unsorted on purpose
+    rows = np.stack([rs.choice(N, m, replace=False) for _ in range(G)]).astype(np.int32)            # order of measurement
+    rows[3, 5] = rows[3, 4]                                                                          # a position measured twice
+    graphs = []
+    for g in range(G):
+        first = np.zeros(N, np.int8)
+        first[first_cols[g]] = 1
+        circ = np.stack([np.roll(first, k) for k in range(N)], axis=1)      # circulant(c)[i, j] = c[(i - j) mod N]
+        H = np.concatenate((circ[rows[g]], np.identity(m, dtype=np.int8)), axis=1)
+        r, c = np.nonzero(H)
+        graphs.append((np.concatenate(([0], np.cumsum(np.bincount(r, minlength=m)))).astype(np.int32), c.astype(np.int32)))
+    probs = np.concatenate((np.full(N, 12 / N), np.full(m, 0.03)))
+    T = 150
+    graph_of = rs.randint(0, G, T).astype(np.int32)
+    synd = rs.randint(0, 2, (T, m)).astype(np.uint8)
+    ys = np.stack([rs.choice(N, 12, replace=False) for _ in range(T)])
+    for t in range(0, T, 2):   # half of the trials decodable: syndrome of a sparse y plus a little noise
+        e = np.zeros(N + m, np.uint8)
+        e[ys[t]] = 1
+        rp, col = graphs[graph_of[t]]
+        synd[t] = np.array([e[col[rp[i]:rp[i + 1]]].sum() & 1 for i in range(m)], np.uint8) ^ (rs.rand(m) < 0.02)
+    host = bp_decoder_multi(graphs, shape=(m, N + m), max_iter=30, channel_probs=probs)
+    dev = bp_decoder_multi.from_circulants(first_cols, rows, N, max_iter=30, channel_probs=probs)
+    assert dev.E == host.E and dev.G == G
+    n_checks = np.array([140, 280, 420], np.int32)[np.arange(T) % 3]
+    for nc in (None, n_checks):
+        a = host.decode_batch(graph_of, synd, n_checks=nc, want_llr=True)
+        b = dev.decode_batch(graph_of, synd, n_checks=nc, want_llr=True)
+        assert np.array_equal(a["decoding"], b["decoding"]) and np.array_equal(a["iters"], b["iters"])
+        assert np.array_equal(a["converged"], b["converged"])
+        assert np.array_equal(a["log_prob_ratios"], b["log_prob_ratios"], equal_nan=True)
+    assert 0 < a["converged"].sum() < T
+    # bad descriptions are refused
+    bad = first_cols.copy()
+    bad[2, 1] = bad[2, 0]
+    with pytest.raises(Exception):
+        bp_decoder_multi.from_circulants(bad, rows, N, max_iter=30, channel_probs=probs)
+    bad_rows = rows.copy()
+    bad_rows[1, 7] = N
+    with pytest.raises(Exception):
+        bp_decoder_multi.from_circulants(first_cols, bad_rows, N, max_iter=30, channel_probs=probs)
