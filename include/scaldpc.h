@@ -309,6 +309,23 @@ int scaldpc_bp_decode_multi(scaldpc_bp *h, int T, const int32_t *graph_of, const
                             const double *channel_probs, const int32_t *truth, int weight, int32_t *stats, uint8_t *decoding,
                             float *llr, int32_t *iters, int32_t *converged, unsigned flags, void *stream);
 /* Shape queries: checks, variables, edges, iteration cap (max_iter = 0 at create time means n, as upstream). */
+/*
+ * scaldpc_bp_decode_static -- scaldpc_bp_decode for callers that must not allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid
+ * cudaMalloc.  The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine) and never synchronises: it
+ * is a fixed sequence of launches on `stream`; all of max_iter iterations are launched, converged trials freeze on the device
+ * exactly as in scaldpc_bp_decode, so decisions, iteration counts and convergence flags are identical to that call's.
+ *   synd T x m uint8, channel_probs n doubles (shared by the trials), decoding T x n uint8, iters / converged T int32 (may be
+ *   NULL): all DEVICE pointers.  Single-graph handles only.
+ * Every per-decode buffer lives in one file-scope device array of SCALDPC_BP_STATIC_BYTES that every GPU loading the library
+ * holds until exit; a decode needs about T/32 * (128 * edges + 4 * (m + n)) bytes of it, and a call that needs more is
+ * refused with SCALDPC_ERR_ARG (the message states both sizes).  All calls -- any handle, any stream -- share the array, which
+ * keeps the last call's contents (the call clears what must start at zero): calls that overlap on the GPU race, so serialise
+ * them on one stream or with events.  Calls on ONE handle also share its [n] prior table with scaldpc_bp_decode.
+ */
+#define SCALDPC_BP_STATIC_BYTES (8u << 20)
+int scaldpc_bp_decode_static(scaldpc_bp *h, int T, const uint8_t *synd, const double *channel_probs, uint8_t *decoding,
+                             int32_t *iters, int32_t *converged, void *stream);
 int scaldpc_bp_info(const scaldpc_bp *h, int *m, int *n, int *edges, int *max_iter);
 long long scaldpc_bp_launch_count(const scaldpc_bp *h);
 /* Statistics of the last decode on this handle: iterations launched (the slowest trial's count) and the number of

@@ -17,6 +17,7 @@ ERR_ARG, ERR_PROB_SUM, ERR_NO_MAX, ERR_NO_CONFIG, ERR_DEGREE, ERR_STRUCTURE, ERR
     -1, -2, -3, -4, -5, -6, -7, -8, -9)
 # decode flags
 IN_LLR, DEVICE_PTRS, CN_EXACT, CN_GENERIC, NO_VERIFY, QARY_EARLY_STOP = 0x1, 0x2, 0x4, 0x8, 0x100, 0x200
+BP_STATIC_BYTES = 8 << 20  # SCALDPC_BP_STATIC_BYTES: the static scratch of scaldpc_bp_decode_static
 BP_PROBS_PER_TRIAL, BP_NO_EARLY_STOP, BP_NO_COMPACT = 0x10, 0x20, 0x40
 
 # every exported symbol of include/scaldpc.h (tests/test_abi.py checks this list against the header)
@@ -26,7 +27,7 @@ SYMBOLS = [
     "scaldpc_qary_decode", "scaldpc_qary_decode_observed", "scaldpc_qary_simulate", "scaldpc_qary_launch_count", "scaldpc_qary_time_kernel",
     "scaldpc_qary_last_run", "scaldpc_qary_set_risk_margin", "scaldpc_qary_last_iterations",
     "scaldpc_bp_create", "scaldpc_bp_destroy", "scaldpc_bp_info", "scaldpc_bp_decode", "scaldpc_bp_decode_scored", "scaldpc_bp_decode_nested", "scaldpc_bp_launch_count",
-    "scaldpc_bp_create_multi", "scaldpc_bp_decode_multi", "scaldpc_bp_create_circulant",
+    "scaldpc_bp_create_multi", "scaldpc_bp_decode_multi", "scaldpc_bp_create_circulant", "scaldpc_bp_decode_static",
     "scaldpc_bp_last_run", "scaldpc_bp_time_kernel",
 ]
 
@@ -105,6 +106,8 @@ def lib() -> C.CDLL:
     L.scaldpc_bp_create_multi.argtypes = [i, i, i, vp, vp, i, i, C.POINTER(vp)]
     L.scaldpc_bp_create_circulant.restype = i
     L.scaldpc_bp_create_circulant.argtypes = [i, i, i, i, vp, vp, i, i, C.POINTER(vp)]
+    L.scaldpc_bp_decode_static.restype = i
+    L.scaldpc_bp_decode_static.argtypes = [vp, i, vp, vp, vp, vp, vp, vp]
     L.scaldpc_bp_decode_multi.restype = i
     L.scaldpc_bp_decode_multi.argtypes = [vp, i, vp, vp, vp, vp, vp, i, vp, vp, vp, vp, vp, u, vp]
     L.scaldpc_bp_launch_count.restype = C.c_longlong

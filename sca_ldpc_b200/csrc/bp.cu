@@ -944,3 +944,157 @@ int scaldpc_bp_time_kernel(scaldpc_bp *h, int which, int T, unsigned flags, int 
 }
 
 }  // extern "C"
+
+// -----------------------------------------------------------------------------------------------------------
+// scaldpc_bp_decode_static: the decode of scaldpc_bp_decode for callers that must not allocate (CUDA graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Every per-decode buffer (messages, syndrome / decision bit-planes, slot masks, iteration counters) is carved
+// out of ONE file-scope device array of kBpStaticBytes; the graph tables and the [n] prior / first-pass tables belong to the
+// handle and were allocated when it was created.  Every GPU that loads the library holds the array until exit.
+// In host code `g_bp_static` is a host-side stand-in, not a device address: bp_static_base() resolves the address once per
+// device with cudaGetSymbolAddress (that device current) and only that pointer is handed to kernels.
+// All calls (all handles, all streams) share the array and it keeps the last call's contents: whatever must start at zero is
+// cleared here, and two calls that overlap on the GPU race.
+// -----------------------------------------------------------------------------------------------------------
+constexpr size_t kBpStaticBytes = (size_t)SCALDPC_BP_STATIC_BYTES;
+static __device__ __align__(256) unsigned char g_bp_static[kBpStaticBytes];
+
+namespace {
+constexpr int kBpStaticMaxDevices = 64;
+std::mutex g_bp_static_mu;
+unsigned char *g_bp_static_ptr[kBpStaticMaxDevices] = {nullptr};
+
+// The device address of g_bp_static on `device` (which must be current).
+int bp_static_base(int device, unsigned char **base)
+{
+    if (device < 0 || device >= kBpStaticMaxDevices) return fail(SCALDPC_ERR_ARG, "device %d out of range", device);
+    std::lock_guard<std::mutex> lk(g_bp_static_mu);
+    if (!g_bp_static_ptr[device]) {
+        void *ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&ptr, g_bp_static);
+        if (e != cudaSuccess || !ptr)
+            return fail(SCALDPC_ERR_CUDA, "cudaGetSymbolAddress(static scratch) on device %d: %s", device, cudaGetErrorString(e));
+        g_bp_static_ptr[device] = (unsigned char *)ptr;
+    }
+    *base = g_bp_static_ptr[device];
+    return 0;
+}
+
+// Carves `bytes` (rounded up to 256) from the scratch; `used` runs ahead even when base is null (size query).
+template <class T>
+T *bp_static_take(unsigned char *base, size_t &used, size_t count)
+{
+    T *p = base ? (T *)(base + used) : nullptr;
+    used += (count * sizeof(T) + 255) & ~(size_t)255;
+    return p;
+}
+}  // namespace
+
+extern "C" {
+
+static size_t bp_static_bytes_needed(const scaldpc_bp *h, int T)  // not exported
+{
+    if (!h || T <= 0) return 0;
+    const size_t tiles = ((size_t)T + 31) / 32;
+    size_t used = 0;
+    bp_static_take<float>(nullptr, used, tiles * 32 * std::max(1, h->E));  // messages
+    bp_static_take<uint32_t>(nullptr, used, tiles * h->m);                  // syndrome bit-planes
+    bp_static_take<uint32_t>(nullptr, used, tiles * h->n);                  // decision bit-planes
+    for (int i = 0; i < 3; ++i) bp_static_take<uint32_t>(nullptr, used, tiles);  // valid / done / unsat
+    for (int i = 0; i < 3; ++i) bp_static_take<int>(nullptr, used, tiles * 32);  // slot -> trial, iterations, converged
+    return used;
+}
+
+int scaldpc_bp_decode_static(scaldpc_bp *h, int T, const uint8_t *synd, const double *channel_probs, uint8_t *decoding,
+                             int32_t *iters, int32_t *converged, void *stream)
+{
+    if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
+    if (T < 0) return fail(SCALDPC_ERR_ARG, "T < 0");
+    if (T == 0) return 0;
+    if (!synd || !channel_probs || !decoding) return fail(SCALDPC_ERR_ARG, "NULL input/output pointer");
+    if (h->G > 1) return fail(SCALDPC_ERR_UNSUPPORTED, "scaldpc_bp_decode_static covers single-graph handles");
+    const size_t need = bp_static_bytes_needed(h, T);
+    if (need > kBpStaticBytes)
+        return fail(SCALDPC_ERR_ARG,
+                    "scaldpc_bp_decode_static: %d trials on this graph need %zu bytes of scratch, the static array holds %zu "
+                    "(SCALDPC_BP_STATIC_BYTES) -- use scaldpc_bp_decode",
+                    T, need, kBpStaticBytes);
+    cudaStream_t st = (cudaStream_t)stream;
+    std::lock_guard<std::mutex> lk(h->mu);
+    SCALDPC_CUDA(cudaSetDevice(h->device));
+    unsigned char *base = nullptr;
+    int rc;
+    if ((rc = bp_static_base(h->device, &base))) return rc;
+
+    const int tiles = (T + 31) / 32;
+    size_t used = 0;
+    float *msg = bp_static_take<float>(base, used, (size_t)tiles * 32 * std::max(1, h->E));
+    uint32_t *synd_w = bp_static_take<uint32_t>(base, used, (size_t)tiles * h->m);
+    uint32_t *dec_w = bp_static_take<uint32_t>(base, used, (size_t)tiles * h->n);
+    uint32_t *valid = bp_static_take<uint32_t>(base, used, tiles);
+    uint32_t *done = bp_static_take<uint32_t>(base, used, tiles);
+    uint32_t *unsat = bp_static_take<uint32_t>(base, used, tiles);
+    int *orig = bp_static_take<int>(base, used, (size_t)tiles * 32);
+    int *d_iters = bp_static_take<int>(base, used, (size_t)tiles * 32);
+    int *d_conv = bp_static_take<int>(base, used, (size_t)tiles * 32);
+
+    // the handle's view with every per-decode buffer replaced by its slice of the static array
+    struct NrowsGuard {
+        scaldpc_bp *h;
+        const int32_t *saved;
+        ~NrowsGuard() { h->cur_nrows = saved; }
+    } guard{h, h->cur_nrows};
+    h->cur_nrows = nullptr;
+    BpDev p = view(h, 0, false, false);
+    p.msg = msg;
+    p.prior = h->d_prior;
+    p.synd_w = synd_w;
+    p.dec_w = dec_w;
+    p.post = nullptr;
+    p.done = done;
+    p.valid = valid;
+    p.unsat = unsat;
+    p.orig = orig;
+    p.iters = d_iters;
+    p.conv = d_conv;
+
+    // ---- inputs -> tile layout; the array keeps the last call's contents: masks, counters and decision words start clean
+    const int tb = (tiles + 255) / 256;
+    k_bp_reset<<<tb, 256, 0, st>>>(valid, done, unsat, orig, d_iters, d_conv, tiles, T, h->max_iter);
+    k_bp_prior_shared<<<(h->n + 255) / 256, 256, 0, st>>>(channel_probs, h->d_prior, h->n);
+    k_bp_pack_synd<<<dim3((h->m + 31) / 32, tiles), 256, 0, st>>>(synd, synd_w, T, h->m, nullptr);
+    SCALDPC_CUDA(cudaMemsetAsync(dec_w, 0, (size_t)tiles * h->n * sizeof(uint32_t), st));
+    SCALDPC_CUDA(cudaMemsetAsync(h->d_counts, 0, (size_t)h->cap_counts * sizeof(int), st));
+    h->launches += 3;
+    SCALDPC_CUDA(cudaGetLastError());
+
+    // ---- iterations: converged trials freeze on the device (k_bp_finish_iter), finished tiles exit at the top of every
+    // kernel; the host never reads anything back, so the call is a fixed sequence of launches
+    for (int it = 1; it <= h->max_iter; ++it) {
+        bool vn_first = false;
+        if (it == 1) {
+            k_bp_first_table<<<dim3((h->m + 127) / 128, h->G), 128, 0, st>>>(p, h->d_first_tab);
+            ++h->launches;
+            vn_first = true;
+            SCALDPC_CUDA(cudaGetLastError());
+        } else if ((rc = launch_cn(h, p, tiles, false, st))) {
+            return rc;
+        }
+        if ((rc = launch_vn(h, p, tiles, st, vn_first))) return rc;
+        k_bp_syndrome<<<dim3((h->m + 255) / 256, tiles), 256, 0, st>>>(p);
+        k_bp_finish_iter<<<(tiles + 255) / 256, 256, 0, st>>>(p, tiles, it, 1, it == h->max_iter);
+        h->launches += 2;
+        SCALDPC_CUDA(cudaGetLastError());
+    }
+    h->last_iters_run = h->max_iter;
+    h->last_compactions = 0;
+
+    k_bp_unpack_dec<<<dim3((h->n + 31) / 32, tiles), 256, 0, st>>>(dec_w, decoding, orig, valid, h->n);
+    ++h->launches;
+    SCALDPC_CUDA(cudaGetLastError());
+    if (iters) SCALDPC_CUDA(cudaMemcpyAsync(iters, d_iters, (size_t)T * sizeof(int), cudaMemcpyDeviceToDevice, st));
+    if (converged) SCALDPC_CUDA(cudaMemcpyAsync(converged, d_conv, (size_t)T * sizeof(int), cudaMemcpyDeviceToDevice, st));
+    return 0;
+}
+
+}  // extern "C"
