@@ -483,11 +483,15 @@ def run_ours(args, kind, wl, iters, cfg):
             with ThreadPoolExecutor(max_workers=nthr) as ex:
                 call = (lambda i: dec.min_sum(batch.priors[i], batch.priors_sum[i])) if special else (lambda i: dec.min_sum(batch.priors[i]))
                 list(ex.map(call, range(64)))
+                r0, b0 = dec.combining_stats()
                 t0 = time.perf_counter()
                 list(ex.map(call, range(ncall)))
-                single["threadpool"] = {"threads": nthr, "calls": ncall,
-                                        "trials_per_s": ncall / (time.perf_counter() - t0),
-                                        "note": "concurrent min_sum() calls on one decoder are combined into batches"}
+                dt = time.perf_counter() - t0
+                r1, b1 = dec.combining_stats()
+                single["threadpool"] = {"threads": nthr, "calls": ncall, "trials_per_s": ncall / dt,
+                                        "calls_per_batch": (r1 - r0) / max(1, b1 - b0),
+                                        "note": "concurrent min_sum() calls on one decoder are combined into batches inside "
+                                                "the library (scaldpc_qary_decode_one)"}
 
     # ---- roofline of the dominant kernel (rank 0, N=1 semantics: one GPU's kernel against one GPU's peak)
     line = None
@@ -531,7 +535,7 @@ def run_ours(args, kind, wl, iters, cfg):
         if os.path.exists(traffic_file):
             try:
                 tr = json.load(open(traffic_file)).get(cfg["workload"].split(":")[0])
-                if tr and tr.get("kernel", "k_cn") in roofline["kernel"]:
+                if tr and tr.get("match", "k_cn") in roofline["kernel"]:
                     roofline["traffic"] = tr["dram_bytes_per_launch"] * (T / tr["trials"])
                     roofline["traffic_source"] = tr.get("source")
             except Exception:

@@ -139,6 +139,19 @@ int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in
                         float *post_sum, int32_t *status, unsigned flags, void *stream);
 
 /*
+ * scaldpc_qary_decode_one -- ONE decode in the reference's call shape: pydecoder.rs:53-65 / 125-145
+ * (min_sum(channel_output[, channel_output_sum]) -> Vec<i8>, GIL released), called from a thread pool at
+ * simulate/decode.py:247-262.  in = bvars x q probabilities, in_sum = R x qs (NULL for the generic decoder), hard = N int8.
+ * Blocking, host pointers.  Concurrent calls on one handle are COMBINED inside the library: the thread that finds no batch in
+ * progress decodes every request queued so far as one batch (up to 32 = one tile, a CUDA graph replay) and wakes the others.
+ * Returns the status of THIS trial: 0, or SCALDPC_ERR_PROB_SUM / NO_MAX / NO_CONFIG where the reference panics
+ * (decoder.rs:618, 680, 683-684); other calls of the same batch are unaffected.
+ * scaldpc_qary_one_stats: requests served and batches launched so far (requests / batches = the combining factor).
+ */
+int scaldpc_qary_decode_one(scaldpc_qary *h, const float *in, const float *in_sum, int8_t *hard);
+int scaldpc_qary_one_stats(scaldpc_qary *h, long long *requests, long long *batches);
+
+/*
  * scaldpc_qary_decode_observed -- the same decode fed by ORACLE OBSERVATIONS instead of prior vectors.
  * Replaces the reference-side composition that produces min_sum's arguments for every trial:
  *   max_likelihood.s_distribution_from_hard_y (simulate/max_likelihood.py:87-105)  posterior of a value given the

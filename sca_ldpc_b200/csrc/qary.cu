@@ -2,6 +2,8 @@
 // (include/scaldpc.h).  Replaces the reference's Rust decoder core behind the same boundary
 // (simulate_rs/src/pydecoder.rs, decoder.rs, decoder_special.rs).  No CPU compute path exists here.
 #include <algorithm>
+#include <condition_variable>
+#include <deque>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -110,6 +112,20 @@ struct scaldpc_qary {
     cudaStream_t s_in = nullptr, s_out = nullptr;
     cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
     std::mutex mu;
+    // scaldpc_qary_decode_one: concurrent single decodes are combined into one batch (leader / followers)
+    struct OneReq {
+        const float *in, *in_sum;
+        int8_t *hard;
+        int status = 0;   // per-trial status, or the batch's error code
+        bool done = false;
+    };
+    std::mutex one_mu;
+    std::condition_variable one_cv;
+    std::deque<OneReq *> one_q;
+    bool one_leading = false;
+    std::vector<float> one_in, one_in_sum;
+    std::vector<int8_t> one_hard;
+    long long one_batches = 0, one_requests = 0;
     long long launches = 0;
 };
 
@@ -1408,6 +1424,88 @@ int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in
     src.in = in;
     src.in_sum = in_sum;
     return decode_batch(h, T, src, hard, post, post_sum, status, flags, (cudaStream_t)stream);
+}
+
+// One decode, the reference's call shape (pydecoder.rs:53-65, 125-145: min_sum(channel_output[, channel_output_sum]) with the
+// GIL released, called from a thread pool at simulate/decode.py:247-262).  Concurrent callers on one handle are COMBINED: the
+// thread that finds no batch in progress becomes the leader, decodes every request queued so far (at most 32 = one tile: they
+// cost what one costs, and the T <= 32 path is a CUDA graph replay) and wakes the others; a request left over elects the next
+// leader.  Returns this trial's status: 0 or SCALDPC_ERR_PROB_SUM / NO_MAX / NO_CONFIG (the reference panics in THAT call only).
+int scaldpc_qary_decode_one(scaldpc_qary *h, const float *in, const float *in_sum, int8_t *hard)
+{
+    if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
+    const bool special = h->BSUM > 0;
+    if (!in || !hard || (special && !in_sum)) return fail(SCALDPC_ERR_ARG, "NULL input/output pointer");
+    scaldpc_qary::OneReq me;
+    me.in = in;
+    me.in_sum = in_sum;
+    me.hard = hard;
+    std::unique_lock<std::mutex> lk(h->one_mu);
+    h->one_q.push_back(&me);
+    while (!me.done) {
+        if (h->one_leading) {
+            h->one_cv.wait(lk);
+            continue;
+        }
+        h->one_leading = true;
+        int rounds = 0;
+    next_batch:
+        scaldpc_qary::OneReq *batch[32];
+        int T = 0;
+        while (T < 32 && !h->one_q.empty()) {
+            batch[T++] = h->one_q.front();
+            h->one_q.pop_front();
+        }
+        lk.unlock();
+        int rc = 0;
+        int32_t status[32] = {0};
+        {
+            std::lock_guard<std::mutex> dk(h->mu);
+            h->one_in.resize((size_t)32 * h->SL);
+            h->one_in_sum.resize(std::max<size_t>(1, (size_t)32 * h->SLS));
+            h->one_hard.resize((size_t)32 * h->N);
+            for (int i = 0; i < T; ++i) {
+                memcpy(h->one_in.data() + (size_t)i * h->SL, batch[i]->in, (size_t)h->SL * sizeof(float));
+                if (special) memcpy(h->one_in_sum.data() + (size_t)i * h->SLS, batch[i]->in_sum, (size_t)h->SLS * sizeof(float));
+            }
+            if (cudaSetDevice(h->device) != cudaSuccess) {
+                rc = fail(SCALDPC_ERR_CUDA, "cudaSetDevice(%d) failed", h->device);
+            } else {
+                PriorSrc src;
+                src.in = h->one_in.data();
+                src.in_sum = h->one_in_sum.data();
+                rc = decode_batch(h, T, src, h->one_hard.data(), nullptr, nullptr, status, 0u, nullptr);
+            }
+            const bool per_trial = rc == 0 || rc == SCALDPC_ERR_PROB_SUM || rc == SCALDPC_ERR_NO_MAX || rc == SCALDPC_ERR_NO_CONFIG;
+            for (int i = 0; i < T; ++i) {
+                batch[i]->status = per_trial ? status[i] : rc;
+                if (per_trial && status[i] == 0) memcpy(batch[i]->hard, h->one_hard.data() + (size_t)i * h->N, (size_t)h->N);
+            }
+            ++h->one_batches;
+            h->one_requests += T;
+        }
+        lk.lock();
+        for (int i = 0; i < T; ++i) batch[i]->done = true;
+        h->one_cv.notify_all();
+        // requests that arrived meanwhile: the leader goes on (handing over costs a wake-up during which the GPU idles),
+        // a bounded number of times so that its own caller is not starved
+        if (!h->one_q.empty() && ++rounds < 8) goto next_batch;
+        h->one_leading = false;
+    }
+    lk.unlock();
+    if (me.status == 0) return 0;
+    const int st = status_error(me.status);
+    return st ? st : fail(me.status, "the batch this decode was combined into failed with status %d", me.status);
+}
+
+// (requests combined so far, batches they were decoded in) of scaldpc_qary_decode_one on this handle
+int scaldpc_qary_one_stats(scaldpc_qary *h, long long *requests, long long *batches)
+{
+    if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
+    std::lock_guard<std::mutex> lk(h->one_mu);
+    if (requests) *requests = h->one_requests;
+    if (batches) *batches = h->one_batches;
+    return 0;
 }
 
 // tables -> device LLR tables (into_llr once per row, decoder.rs:668-692), on the compute stream

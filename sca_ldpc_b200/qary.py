@@ -33,14 +33,6 @@ _STATUS_TEXT = {
 }
 
 
-class _Request:
-    """One min_sum() call waiting to be decoded as part of a combined batch."""
-    __slots__ = ("co", "cos", "result", "error", "done")
-
-    def __init__(self, co, cos):
-        self.co, self.cos, self.result, self.error, self.done = co, cos, None, None, threading.Event()
-
-
 class QaryDecoder:
     """q-ary min-sum decoder on one B200.
 
@@ -51,8 +43,6 @@ class QaryDecoder:
     def __init__(self, H, iterations, B, BSUM=0, DV=0, DC=0, shape=None, device=0, csr=None):
         self._h = C.c_void_p()
         self._lock = threading.Lock()
-        self._qlock = threading.Lock()
-        self._pending, self._leading = [], False  # min_sum() requests waiting for the next combined batch
         if csr is not None:
             # sparse constructor (scaldpc_qary_create_csr): csr = (row_ptr, col, val), `shape` = (R, N); H is ignored
             if int(iterations) < 0:
@@ -111,43 +101,23 @@ class QaryDecoder:
             cos = self._one(channel_output_sum, self.R, self.QS, "channel_output_sum")
         elif channel_output_sum is not None:
             raise TypeError("min_sum() takes 1 positional argument but 2 were given")
-        # Concurrent callers are COMBINED: the reference calls one decoder object from a ThreadPoolExecutor
-        # (simulate/decode.py:247-262, GIL released in pydecoder.rs:55).  Whichever thread finds no batch in progress
-        # becomes the leader and decodes every request queued so far as one batch (a tile holds 32 trials, so 32
-        # concurrent decodes cost what one costs); the others wait for their row of the result.
-        req = _Request(co, cos)
-        with self._qlock:
-            self._pending.append(req)
-            leader = not self._leading
-            if leader:
-                self._leading = True
-        if leader:
-            while True:
-                with self._qlock:
-                    batch, self._pending = self._pending, []
-                    if not batch:
-                        self._leading = False
-                        break
-                try:
-                    x = np.stack([r.co for r in batch])
-                    xs = np.stack([r.cos for r in batch]) if self.special else None
-                    hard, _, _, status = self.min_sum_batch(x, xs, want_posterior=False, want_status=True)
-                    for i, r in enumerate(batch):
-                        if status[i] == 0:
-                            r.result = hard[i].tolist()  # Python ints, like the pyo3 return value
-                        else:  # the reference panics in THAT call only (decoder.rs:618, 680, 683-684)
-                            r.error = ValueError(_STATUS_TEXT.get(int(status[i]), f"libscaldpc status {int(status[i])}"))
-                except BaseException as e:  # noqa: BLE001 -- every waiter must be released
-                    for r in batch:
-                        if r.result is None and r.error is None:
-                            r.error = e
-                finally:
-                    for r in batch:
-                        r.done.set()
-        req.done.wait()
-        if req.error is not None:
-            raise req.error
-        return req.result
+        # Concurrent callers are COMBINED inside the library (scaldpc_qary_decode_one): the reference calls one decoder object
+        # from a ThreadPoolExecutor (simulate/decode.py:247-262, GIL released in pydecoder.rs:55); ctypes releases the GIL for
+        # the call, the first thread in decodes every request queued so far as one batch (a tile holds 32 trials, so 32
+        # concurrent decodes cost what one costs) and the others wait for their row of the result.
+        hard = np.empty(self.N, np.int8)
+        rc = _lib.lib().scaldpc_qary_decode_one(self._h, co.ctypes.data, cos.ctypes.data if cos is not None else None,
+                                                hard.ctypes.data)
+        if rc in _STATUS_TEXT:  # the reference panics in THAT call only (decoder.rs:618, 680, 683-684)
+            raise ValueError(_STATUS_TEXT[rc])
+        _lib.check(rc)
+        return hard.tolist()  # Python ints, like the pyo3 return value
+
+    def combining_stats(self):
+        """(single decodes served, batches they were decoded in) by min_sum() on this decoder."""
+        a, b = C.c_longlong(), C.c_longlong()
+        _lib.check(_lib.lib().scaldpc_qary_one_stats(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     @staticmethod
     def _one(x, rows, q, name):

@@ -359,8 +359,11 @@ def test_concurrent_min_sum_calls_are_combined():
         return d.min_sum(b.priors[i], b.priors_sum[i])
 
     n0 = d.launch_count
+    r0, b0 = d.combining_stats()
     with ThreadPoolExecutor(max_workers=16) as ex:
         out = list(ex.map(call, range(96)))
+    r1, b1 = d.combining_stats()
+    assert r1 - r0 == 96 and 0 < b1 - b0 < 96  # scaldpc_qary_decode_one: every call served, in fewer batches than calls
     for i, o in enumerate(out):
         if i != 5:
             assert o == ref[i].tolist(), i
