@@ -44,6 +44,8 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+        dist.all_reduce(torch.zeros(1, device=dev))  # NCCL sets its communicator up on the first collective (~1.5 s):
+        torch.cuda.synchronize(dev)                  # not part of any accuracy level's campaign time
     n_batches = (args.trials + args.batch - 1) // args.batch
     for acc in (float(a) for a in args.accuracies.split(",")):
         wl = KyberWorkload("kyber1024", sum_weight=args.sum_weight, check_blocks=1, accuracy=acc, nbits=5, nbits_sum=6, seed=0)
