@@ -509,3 +509,26 @@ def test_sparse_constructor_equals_dense():
     g = QaryDecoder(None, 10, B=7, DV=3, DC=7, shape=(150, 450), csr=(rp, cols, Hm[rows, cols]))
     hard, post, _ = g.min_sum_batch(_corrupted(450)[None], exact=True)
     assert np.array_equal(hard[0], z["medium_hard"]) and np.array_equal(post[0], z["medium_post"], equal_nan=True)
+
+
+@pytest.mark.parametrize("variant,sw,cb,acc,nb,nbs", [("kyber768", 6, 2, 0.95, 3, 4), ("kyber1024", 8, 1, 0.95, 5, 6),
+                                                      ("kyber1024", 4, 1, 0.99, 5, 6)])
+def test_default_path_equals_exact_kernel_at_scale(variant, sw, cb, acc, nb, nbs):
+    """The other BASELINE.json shapes at batch size (2048 trials, a mix of converging and non-converging ones): the default
+    path (fast check node + verification) against the exact-order kernel = the reference's arithmetic
+    (decoder_special.rs:539-553; tied to the enumeration oracle by test_batched_parity_with_oracle): hard decisions identical
+    for every trial, posteriors within 1e-4 absolute with the same inf/NaN masks."""
+    w = KyberWorkload(variant, sw, cb, accuracy=acc, nbits=nb, nbits_sum=nbs, seed=3)
+    T = 2048
+    b = w.generate(T, seed=4)
+    d = QaryDecoder(w.H, 10, **w.decoder_kwargs)
+    hard, post, posts = d.min_sum_batch(b.priors, b.priors_sum)
+    n_re = d.last_run["redecoded"]
+    eh, ep, eps_ = d.min_sum_batch(b.priors, b.priors_sum, exact=True)
+    assert np.array_equal(hard, eh)
+    assert util.same_nonfinite(post, ep) and util.max_abs_diff(post, ep) < TOL
+    assert util.same_nonfinite(posts, eps_) and util.max_abs_diff(posts, eps_) < TOL
+    ok = w.success(b, hard)
+    print(variant, sw, "re-decoded", n_re, "success", ok.mean())
+    assert n_re > 0 and ok.mean() < 1.0          # the verification had something to do
+    assert n_re < T or ok.mean() == 0.0          # ... and re-decoded everything only where nothing decodes
