@@ -109,6 +109,7 @@ struct scaldpc_qary {
     int8_t *h_pin_hard = nullptr;
     int *h_pin_status = nullptr;
     bool small_graph_off = false;  // SCALDPC_NO_GRAPH=1
+    int exact_split_items = 0;     // k_cn_exact: items up to which the split variant runs (SCALDPC_EXACT_SPLIT_ITEMS)
     cudaStream_t s_in = nullptr, s_out = nullptr;
     cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
     std::mutex mu;
@@ -470,13 +471,16 @@ typedef void (*cn_exact_fn)(const QaryDev, const int, const int, const int);
 struct CnExact {
     cn_exact_fn fn;
     size_t smem;
+    cn_exact_fn fn_split;  // one CTA of `nr` warps per item (few items: the re-decode of one or two tiles)
+    int nr;
 };
 
 const CnExact *pick_cn_exact(int sw, int b)
 {
 #define CASE(SW_, B_)                                                                            \
     if (sw == SW_ && b == B_) {                                                                  \
-        static const CnExact t = {k_cn_exact<SW_, B_>, CnExactShape<SW_, B_>::smem_bytes};       \
+        static const CnExact t = {k_cn_exact<SW_, B_, false>, CnExactShape<SW_, B_>::smem_bytes, \
+                                  k_cn_exact<SW_, B_, true>, CnExactSplit<SW_>::NR};             \
         return &t;                                                                               \
     }
     CASE(6, 2) CASE(6, 3) CASE(4, 2) CASE(8, 2) CASE(3, 2)
@@ -552,7 +556,10 @@ int launch_cn(scaldpc_qary *h, const QaryDev &p, int tiles, int it, int iters, u
         // exact-order dynamic programme in registers, one warp per (tile, check)
         const CnExact *ex = pick_cn_exact(h->fast_sw, h->B);
         const int n_items = tiles * h->R;
-        ex->fn<<<(n_items + kCnExactWarps - 1) / kCnExactWarps, kCnExactWarps * 32, ex->smem, st>>>(p, n_items, first, last);
+        if (n_items <= h->exact_split_items)  // too few items to fill the GPU with a warp each: a CTA of nr warps per item
+            ex->fn_split<<<n_items, ex->nr * 32, ex->smem, st>>>(p, n_items, first, last);
+        else
+            ex->fn<<<(n_items + kCnExactWarps - 1) / kCnExactWarps, kCnExactWarps * 32, ex->smem, st>>>(p, n_items, first, last);
         ++h->launches;
     } else if (h->BSUM == 0 && !exact && !force_generic && h->uniform_ok) {
         // generic decoder, one alphabet: the unrolled / padded forward-backward kernel
@@ -676,6 +683,7 @@ static int qary_create_from_graph(const HostGraph &g, int R, int N, int b, int b
     if (const char *e = getenv("SCALDPC_RISK_MARGIN")) h->risk_eps = std::max(0.0f, (float)atof(e));
     if (const char *e = getenv("SCALDPC_ES_RESTART_MIN")) h->es_restart_min = std::max(1, atoi(e));
     if (const char *e = getenv("SCALDPC_NO_GRAPH")) h->small_graph_off = atoi(e) != 0;
+
     h->E = g.E;
     h->S = g.S;
     h->SL = g.SL;
@@ -697,12 +705,15 @@ static int qary_create_from_graph(const HostGraph &g, int R, int N, int b, int b
 
     SCALDPC_CUDA(cudaSetDevice(device));
     SCALDPC_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
+    h->exact_split_items = 2 * h->num_sms;  // one wave of 2 CTAs per SM
+    if (const char *e = getenv("SCALDPC_EXACT_SPLIT_ITEMS")) h->exact_split_items = atoi(e);
     if (h->fast_sw) {
         const CnFast *f = pick_cn_fast(h->fast_sw, b);
         for (int i = 0; i < kCnFastVariants; ++i)
             SCALDPC_CUDA(cudaFuncSetAttribute(f->fn[i], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f->smem));
         const CnExact *ex = pick_cn_exact(h->fast_sw, b);
         SCALDPC_CUDA(cudaFuncSetAttribute(ex->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ex->smem));
+        SCALDPC_CUDA(cudaFuncSetAttribute(ex->fn_split, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ex->smem));
     }
     int rc;
     if ((rc = upload(&h->d_row_ptr, row_ptr)) || (rc = upload(&h->d_col, col)) || (rc = upload(&h->d_sign, sign)) ||

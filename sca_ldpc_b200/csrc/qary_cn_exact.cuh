@@ -27,20 +27,30 @@ struct CnExactShape {
     static constexpr size_t smem_bytes = (size_t)kCnExactWarps * Sh::NS * 32 * sizeof(float);
 };
 
-// (A variant with one CTA of SW warps per item, a pinned variable per warp, was measured for the re-decode of a single tile:
-// 35 us per launch against 27 us -- 251 registers x 192 threads leave one CTA per SM, so 256 items need two waves and each wave
-// lasts as long as its longest warp.  Removed.)
-template <int SW, int B>
+// SPLIT: the re-decode of a FEW at-risk trials (one or two tiles: a few hundred items, not enough to fill the GPU with one warp
+// each) is bound by the ~15 k dependent instructions of one warp.  One CTA of NR = ceil(SW/2) warps takes an item and warp r pins
+// the variables r and SW-1-r -- the pinned variable j costs SW-1-j convolutions per value, so every warp gets SW-1 of them; all
+// warps read the inputs, one barrier, then each writes its own variables' slots (the messages are updated in place).
+// (A first variant with SW warps per item, one pinned variable each, was slower than the plain kernel: 35 us against 27 us --
+// unbalanced warps, and 251 registers x 192 threads left one CTA per SM = two waves for 256 items.)
+template <int SW>
+struct CnExactSplit {
+    static constexpr int NR = (SW + 1) / 2;
+};
+
+template <int SW, int B, bool SPLIT = false>
 __global__ void __launch_bounds__(kCnExactWarps * 32, 2) k_cn_exact(const QaryDev p, const int n_items, const int FIRST,
                                                                     const int LAST)
 {
     static_assert(SW >= 2, "k_cn_exact needs at least two B-variables per check");
+    static_assert(CnExactSplit<SW>::NR <= kCnExactWarps, "the split variant uses one CTA of NR warps per item");
     using Sh = CnFastShape<SW, B>;
     constexpr int Q = Sh::Q, BS = Sh::BS, QS = Sh::QS, NS = Sh::NS;
     constexpr int NP = (SW - 1) * B + 1;  // pairs of the widest table over the B-variables: 2 (SW-1) B + 1 entries
     const float INF = SC_INF;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int item = blockIdx.x * kCnExactWarps + warp;
+    const int item = SPLIT ? (int)blockIdx.x : blockIdx.x * kCnExactWarps + warp;
+    const int role = SPLIT ? warp : -1;  // SPLIT: blockDim.x == NR * 32
     if (item >= n_items) return;
     const int tile = item / p.R, check = item - tile * p.R;
     const int e0 = __ldg(p.row_ptr + check);
@@ -102,14 +112,18 @@ __global__ void __launch_bounds__(kCnExactWarps * 32, 2) k_cn_exact(const QaryDe
         }
 #pragma unroll
     for (int i = 0; i < QS; ++i) SX(SW * Q + i) = sanitize(as[i]);  // `as` itself is dead from here on
+#ifndef SCALDPC_HOST_MODEL
+    if (SPLIT) __syncthreads();  // every warp of the item has read the slots before anyone overwrites them
+#endif
 
     // ---- per variable j: every value d pinned in turn; Fp = F_j as pairs (F_j[v] <-> prefix total v - j*B)
     F2 Fp[NP];
 #pragma unroll
     for (int j = 0; j < SW; ++j) {
         const int nF = 2 * j * B + 1;  // entries of F_j (compile-time after unrolling)
+        const bool mine = !SPLIT || role == (j < SW - 1 - j ? j : SW - 1 - j);
 #pragma unroll 1
-        for (int d = 0; d < Q; ++d) {
+        for (int d = 0; d < (mine ? Q : 0); ++d) {
             const float x = SX(j * Q + d);
             // T = F_j + a_j[d]; index v of T <-> total of the OTHER variables so far, offset (number of them) * B
             F2 Tp[NP];
@@ -153,7 +167,7 @@ __global__ void __launch_bounds__(kCnExactWarps * 32, 2) k_cn_exact(const QaryDe
             Fs[nF + Q - 1] = INF;
 #pragma unroll
             for (int jj = 0; jj < (nF + Q) / 2; ++jj) Fp[jj] = f2_make(Fs[2 * jj], Fs[2 * jj + 1]);
-        } else {
+        } else if (!SPLIT || role == 0) {
             // ---- the sum-variable: beta_sum[t] = (F_SW[-t] + a_sum[t]) - a_sum[t]; Fs = F_SW, QS entries
             float min_val = INF;
             int arg = negs ? QS - 1 : 0;
