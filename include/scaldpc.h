@@ -139,6 +139,17 @@ int scaldpc_qary_decode(scaldpc_qary *h, int T, const float *in, const float *in
                         float *post_sum, int32_t *status, unsigned flags, void *stream);
 
 /*
+ * scaldpc_qary_decode_f64 -- the fp64 VERIFICATION mode (north_star: "fp32 log-domain; fp64 option for verification"): the
+ * decode of scaldpc_qary_decode with every LLR, message and posterior in double -- into_llr (decoder.rs:668-692), check node in
+ * the reference's order of additions (decoder.rs:600-629, decoder_special.rs:539-553), variable node (decoder.rs:634-658,
+ * decoder_special.rs:566-609) with f64 in place of f32.  in / in_sum are the f32 priors of scaldpc_qary_decode (pydecoder.rs:53
+ * takes f32); post T x bvars x q and post_sum T x R x qs are DOUBLE (may be NULL).  flags: 0 or SCALDPC_IN_LLR.  Host pointers,
+ * synchronous, run-time-shape kernels, temporary buffers per call: a checker for the f32 path, not a fast path.
+ */
+int scaldpc_qary_decode_f64(scaldpc_qary *h, int T, const float *in, const float *in_sum, int8_t *hard, double *post,
+                            double *post_sum, int32_t *status, unsigned flags);
+
+/*
  * scaldpc_qary_decode_one -- ONE decode in the reference's call shape: pydecoder.rs:53-65 / 125-145
  * (min_sum(channel_output[, channel_output_sum]) -> Vec<i8>, GIL released), called from a thread pool at
  * simulate/decode.py:247-262.  in = bvars x q probabilities, in_sum = R x qs (NULL for the generic decoder), hard = N int8.

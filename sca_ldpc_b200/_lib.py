@@ -27,7 +27,7 @@ SYMBOLS = [
     "scaldpc_qary_decode", "scaldpc_qary_decode_observed", "scaldpc_qary_simulate", "scaldpc_qary_launch_count", "scaldpc_qary_time_kernel",
     "scaldpc_qary_last_run", "scaldpc_qary_set_risk_margin", "scaldpc_qary_last_iterations",
     "scaldpc_bp_create", "scaldpc_bp_destroy", "scaldpc_bp_info", "scaldpc_bp_decode", "scaldpc_bp_decode_scored", "scaldpc_bp_decode_nested", "scaldpc_bp_launch_count",
-    "scaldpc_bp_create_multi", "scaldpc_bp_decode_multi", "scaldpc_bp_create_circulant", "scaldpc_bp_decode_static", "scaldpc_qary_decode_one", "scaldpc_qary_one_stats",
+    "scaldpc_bp_create_multi", "scaldpc_bp_decode_multi", "scaldpc_bp_create_circulant", "scaldpc_bp_decode_static", "scaldpc_qary_decode_one", "scaldpc_qary_decode_f64", "scaldpc_qary_one_stats",
     "scaldpc_bp_last_run", "scaldpc_bp_time_kernel",
 ]
 
@@ -106,6 +106,8 @@ def lib() -> C.CDLL:
     L.scaldpc_bp_create_multi.argtypes = [i, i, i, vp, vp, i, i, C.POINTER(vp)]
     L.scaldpc_bp_create_circulant.restype = i
     L.scaldpc_bp_create_circulant.argtypes = [i, i, i, i, vp, vp, i, i, C.POINTER(vp)]
+    L.scaldpc_qary_decode_f64.restype = i
+    L.scaldpc_qary_decode_f64.argtypes = [vp, i, vp, vp, vp, vp, vp, vp, C.c_uint]
     L.scaldpc_qary_decode_one.restype = i
     L.scaldpc_qary_decode_one.argtypes = [vp, vp, vp, vp]
     L.scaldpc_qary_one_stats.restype = i

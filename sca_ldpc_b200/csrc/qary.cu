@@ -729,7 +729,7 @@ static int qary_create_from_graph(const HostGraph &g, int R, int N, int b, int b
         const size_t smem = generic_smem_bytes(h.get(), &g);
         if (smem > 227 * 1024)
             return fail(SCALDPC_ERR_UNSUPPORTED, "check-node scratch of %zu bytes exceeds shared memory", smem);
-        SCALDPC_CUDA(cudaFuncSetAttribute(k_cn_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        SCALDPC_CUDA(cudaFuncSetAttribute(k_cn_generic<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     }
     *out = h.release();
     return 0;
@@ -1517,6 +1517,112 @@ int scaldpc_qary_one_stats(scaldpc_qary *h, long long *requests, long long *batc
     if (requests) *requests = h->one_requests;
     if (batches) *batches = h->one_batches;
     return 0;
+}
+
+// ---- fp64 verification mode -------------------------------------------------------------------------------
+typedef void (*vn64_fn)(const QaryDevT<double>, const int);
+static vn64_fn pick_vn64(int q)
+{
+    switch (q) {
+#define CASE(Q_) \
+    case Q_:     \
+        return k_vn<Q_, double>;
+        CASE(3) CASE(5) CASE(7) CASE(9) CASE(11) CASE(13) CASE(15) CASE(17) CASE(19) CASE(21) CASE(23) CASE(25)
+        CASE(27) CASE(29) CASE(31)
+#undef CASE
+    default:
+        return nullptr;
+    }
+}
+
+// The decode of scaldpc_qary_decode with every message, LLR and posterior in DOUBLE (north_star: "fp32 log-domain; fp64 option
+// for verification").  Reference semantics with f64 in place of f32: into_llr (decoder.rs:668-692), the check node in the
+// reference's order of additions (decoder.rs:600-629 / decoder_special.rs:539-553; exact-order dynamic programme, k_cn_generic),
+// the variable node (decoder.rs:634-658 / decoder_special.rs:566-609).  A checker, not a product path: run-time-shape kernels,
+// buffers allocated and freed per call, at most 512 trials resident, synchronous, host pointers.
+int scaldpc_qary_decode_f64(scaldpc_qary *h, int T, const float *in, const float *in_sum, int8_t *hard, double *post,
+                            double *post_sum, int32_t *status, unsigned flags)
+{
+    if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
+    if (T < 0) return fail(SCALDPC_ERR_ARG, "T < 0");
+    if (T == 0) return 0;
+    const bool special = h->BSUM > 0;
+    if (!in || !hard || (special && !in_sum)) return fail(SCALDPC_ERR_ARG, "NULL input/output pointer");
+    if (flags & ~(unsigned)SCALDPC_IN_LLR) return fail(SCALDPC_ERR_ARG, "scaldpc_qary_decode_f64 takes SCALDPC_IN_LLR only");
+    const vn64_fn vn = pick_vn64(h->Q);
+    if (!vn) return fail(SCALDPC_ERR_UNSUPPORTED, "no fp64 variable-node kernel for q = %d", h->Q);
+    CnGenericArgs g;
+    const size_t smem = 2 * generic_smem_bytes(h, &g);  // the float figure, in doubles
+    if (smem > 227 * 1024) return fail(SCALDPC_ERR_UNSUPPORTED, "fp64 check-node scratch of %zu bytes exceeds shared memory", smem);
+    std::lock_guard<std::mutex> lk(h->mu);
+    SCALDPC_CUDA(cudaSetDevice(h->device));
+    SCALDPC_CUDA(cudaFuncSetAttribute(k_cn_generic<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int cap = 512, cap_tiles = cap / 32;
+    const int iters = std::max(1, h->max_iter);
+    const bool is_llr = flags & SCALDPC_IN_LLR;
+    struct Bufs {
+        void *p[9] = {nullptr};
+        ~Bufs() { for (void *q : p) cudaFree(q); }
+    } b;
+    const size_t sizes[9] = {(size_t)cap * h->SL * sizeof(float),      std::max<size_t>(1, (size_t)cap * h->SLS) * sizeof(float),
+                             (size_t)cap * h->SL * sizeof(double),     std::max<size_t>(1, (size_t)cap * h->SLS) * sizeof(double),
+                             (size_t)cap * h->S * sizeof(double),      (size_t)cap * h->SL * sizeof(double),
+                             std::max<size_t>(1, (size_t)cap * h->SLS) * sizeof(double), (size_t)cap * h->N,
+                             (size_t)cap * (sizeof(int) + h->N)};
+    for (int i = 0; i < 9; ++i) SCALDPC_CUDA(cudaMalloc(&b.p[i], sizes[i]));
+    float *d_in = (float *)b.p[0], *d_in_sum = (float *)b.p[1];
+    double *d_llr = (double *)b.p[2], *d_llr_sum = (double *)b.p[3], *d_msg = (double *)b.p[4], *d_post = (double *)b.p[5],
+           *d_post_sum = (double *)b.p[6];
+    int8_t *d_hard_t = (int8_t *)b.p[7];
+    int *d_status = (int *)b.p[8];
+    int8_t *d_hard = (int8_t *)(d_status + cap);
+    // row-major staging of the posteriors reuses the LLR buffers once the iterations are over
+    cudaStream_t st = nullptr;
+    int worst = 0;
+    std::vector<int> hstatus(cap);
+    for (int t0 = 0; t0 < T; t0 += cap) {
+        const int tc = std::min(cap, T - t0), tiles = (tc + 31) / 32;
+        SCALDPC_CUDA(cudaMemcpyAsync(d_in, in + (size_t)t0 * h->SL, (size_t)tc * h->SL * sizeof(float), cudaMemcpyHostToDevice, st));
+        if (special)
+            SCALDPC_CUDA(cudaMemcpyAsync(d_in_sum, in_sum + (size_t)t0 * h->SLS, (size_t)tc * h->SLS * sizeof(float), cudaMemcpyHostToDevice, st));
+        SCALDPC_CUDA(cudaMemsetAsync(d_status, 0, (size_t)cap * sizeof(int), st));
+        k_load_priors_f64<<<dim3((h->bvars + 7) / 8, tiles), 256, 0, st>>>(d_in, d_llr, tc, h->bvars, h->Q, is_llr, d_status);
+        if (special) k_load_priors_f64<<<dim3((h->R + 7) / 8, tiles), 256, 0, st>>>(d_in_sum, d_llr_sum, tc, h->R, h->QS, is_llr, d_status);
+        QaryDevT<double> p;
+        p.R = h->R; p.N = h->N; p.bvars = h->bvars; p.B = h->B; p.BSUM = h->BSUM; p.Q = h->Q; p.QS = h->QS;
+        p.S = h->S; p.SL = h->SL; p.SLS = h->SLS;
+        p.row_ptr = h->d_row_ptr; p.col = h->d_col; p.sign = h->d_sign; p.edge_off = h->d_edge_off; p.col_ptr = h->d_col_ptr;
+        p.csc = h->d_csc;
+        p.msg = d_msg; p.llr = d_llr; p.llr_sum = d_llr_sum; p.post = d_post; p.post_sum = special ? d_post_sum : nullptr;
+        p.hard_t = d_hard_t; p.status = d_status;
+        for (int it = 1; it <= iters; ++it) {
+            g.exact = 1;
+            g.first = it == 1;
+            g.last = it == iters;
+            if (it == 1) k_init_v2c<double><<<dim3((h->E + 7) / 8, tiles), 256, 0, st>>>(p, h->E);
+            k_cn_generic<double><<<dim3(h->R, tiles), 32, smem, st>>>(p, g);
+            vn<<<dim3((h->bvars + kVnWarps - 1) / kVnWarps, tiles), kVnWarps * 32, 0, st>>>(p, it == iters);
+            h->launches += 2 + (it == 1);
+        }
+        SCALDPC_CUDA(cudaGetLastError());
+        const dim3 block(32, kTrRows);
+        k_untile<int8_t><<<dim3((h->N + 31) / 32, tiles), block, 0, st>>>(d_hard_t, d_hard, tc, h->N, nullptr);
+        SCALDPC_CUDA(cudaMemcpyAsync(hard + (size_t)t0 * h->N, d_hard, (size_t)tc * h->N, cudaMemcpyDeviceToHost, st));
+        if (post) {
+            k_untile<double><<<dim3((h->SL + 31) / 32, tiles), block, 0, st>>>(d_post, d_llr, tc, h->SL, nullptr);
+            SCALDPC_CUDA(cudaMemcpyAsync(post + (size_t)t0 * h->SL, d_llr, (size_t)tc * h->SL * sizeof(double), cudaMemcpyDeviceToHost, st));
+        }
+        if (post_sum && special) {
+            k_untile<double><<<dim3((h->SLS + 31) / 32, tiles), block, 0, st>>>(d_post_sum, d_llr_sum, tc, h->SLS, nullptr);
+            SCALDPC_CUDA(cudaMemcpyAsync(post_sum + (size_t)t0 * h->SLS, d_llr_sum, (size_t)tc * h->SLS * sizeof(double), cudaMemcpyDeviceToHost, st));
+        }
+        SCALDPC_CUDA(cudaMemcpyAsync(hstatus.data(), d_status, (size_t)tc * sizeof(int), cudaMemcpyDeviceToHost, st));
+        SCALDPC_CUDA(cudaStreamSynchronize(st));
+        SCALDPC_CUDA(cudaGetLastError());
+        for (int t = 0; t < tc; ++t) worst = std::min(worst, hstatus[t]);
+        if (status) memcpy(status + t0, hstatus.data(), (size_t)tc * sizeof(int));
+    }
+    return status_error(worst);
 }
 
 // tables -> device LLR tables (into_llr once per row, decoder.rs:668-692), on the compute stream

@@ -30,7 +30,10 @@
 
 namespace scaldpc {
 
-struct QaryDev {
+// Real = float everywhere on the product path; double = the fp64 verification mode (scaldpc_qary_decode_f64), which runs
+// the run-time-shape kernels (k_init_v2c, k_cn_generic exact-order, k_vn) on double messages.
+template <class Real>
+struct QaryDevT {
     int R, N, bvars, B, BSUM, Q, QS;
     int S;    // message slots per trial
     int SL;   // bvars * Q
@@ -41,11 +44,11 @@ struct QaryDev {
     const int *edge_off;    // E+1 slot offset of each edge
     const int *col_ptr;     // N+1
     const int2 *csc;        // E: {slot offset, sign} of each variable's edges, rows ascending
-    float *msg;
-    const float *llr;
-    const float *llr_sum;
-    float *post;            // may be null
-    float *post_sum;        // may be null
+    Real *msg;
+    const Real *llr;
+    const Real *llr_sum;
+    Real *post;             // may be null
+    Real *post_sum;         // may be null
     int8_t *hard_t;
     int *status;            // per trial, tiles*32 entries
     // at-risk detection of the fast (forward/backward) path, last iteration only; null = off.  Bit l of risk[tile] is set
@@ -58,9 +61,17 @@ struct QaryDev {
     // first held are final and are not written again; a tile whose 32 bits are all set is skipped altogether.  null = off.
     const uint32_t *done = nullptr;
 };
+using QaryDev = QaryDevT<float>;
+
+// +inf, min (NaN operand ignored, f32::min / f64::min) and "NaN -> +inf" for either scalar type
+template <class Real>
+__device__ __forceinline__ Real sc_inf() { return (Real)__builtin_huge_valf(); }
+__device__ __forceinline__ float sc_min(float a, float b) { return fminf(a, b); }
+__device__ __forceinline__ double sc_min(double a, double b) { return fmin(a, b); }
 
 // Frozen-lane helpers for the kernels (warp-uniform word, per-lane bit).
-__device__ __forceinline__ uint32_t done_word(const QaryDev &p, int tile) { return p.done ? __ldg(p.done + tile) : 0u; }
+template <class Real>
+__device__ __forceinline__ uint32_t done_word(const QaryDevT<Real> &p, int tile) { return p.done ? __ldg(p.done + tile) : 0u; }
 
 // The two smallest entries of a vector (NaN = excluded = +inf).
 struct Min2 {
@@ -77,7 +88,8 @@ struct Min2 {
 };
 
 // Every lane of the warp calls this with its own verdict; one atomic per warp.
-__device__ __forceinline__ void flag_risk(const QaryDev &p, int tile, int lane, bool risky)
+template <class Real>
+__device__ __forceinline__ void flag_risk(const QaryDevT<Real> &p, int tile, int lane, bool risky)
 {
 #ifdef SCALDPC_HOST_MODEL
     if (risky) p.risk[tile] |= 1u << lane;
@@ -100,6 +112,7 @@ __device__ __forceinline__ float min3f(float a, float b, float c)
 
 // NaN -> +inf, everything else unchanged (min.f32 returns the non-NaN operand): "non-finite => excluded".
 __device__ __forceinline__ float sanitize(float x) { return fminf(x, SC_INF); }
+__device__ __forceinline__ double sanitize(double x) { return fmin(x, (double)SC_INF); }
 
 // Running minimum that folds two new candidates per FMNMX3.
 struct MinAcc {
@@ -129,10 +142,10 @@ struct MinAcc {
 // -----------------------------------------------------------------------------------------------------------
 constexpr int kVnWarps = 8;
 
-template <int Q>
-__global__ void __launch_bounds__(kVnWarps * 32) k_vn(const QaryDev p, const int LAST)
+template <int Q, class Real = float>
+__global__ void __launch_bounds__(kVnWarps * 32) k_vn(const QaryDevT<Real> p, const int LAST)
 {
-    const float INF = SC_INF;
+    const Real INF = sc_inf<Real>();
     const int lane = threadIdx.x & 31;
     const int var = blockIdx.x * kVnWarps + (threadIdx.x >> 5);
     const int tile = blockIdx.y;
@@ -140,10 +153,10 @@ __global__ void __launch_bounds__(kVnWarps * 32) k_vn(const QaryDev p, const int
     const uint32_t frozen_w = done_word(p, tile);
     if (frozen_w == 0xffffffffu) return;  // early termination: every trial of the tile is final
     const bool frozen = (frozen_w >> lane) & 1u;
-    float *msg = p.msg + (size_t)tile * p.S * 32 + lane;
-    const float *llr = p.llr + (size_t)tile * p.SL * 32 + lane;
+    Real *msg = p.msg + (size_t)tile * p.S * 32 + lane;
+    const Real *llr = p.llr + (size_t)tile * p.SL * 32 + lane;
 
-    float tot[Q];
+    Real tot[Q];
 #pragma unroll
     for (int i = 0; i < Q; ++i) tot[i] = llr[(size_t)(var * Q + i) * 32];
     const int p0 = __ldg(p.col_ptr + var), p1 = __ldg(p.col_ptr + var + 1);
@@ -156,20 +169,20 @@ __global__ void __launch_bounds__(kVnWarps * 32) k_vn(const QaryDev p, const int
     for (int e = p0; e < p1; ++e) {
         const int2 es = __ldg(p.csc + e);
         const bool neg = es.y < 0;
-        float prim[Q];
-        float m = INF;
+        Real prim[Q];
+        Real m = INF;
 #pragma unroll
         for (int i = 0; i < Q; ++i) {  // i: check frame
-            const float c = msg[(size_t)(es.x + i) * 32];
-            const float t = neg ? tot[Q - 1 - i] : tot[i];
+            const Real c = msg[(size_t)(es.x + i) * 32];
+            const Real t = neg ? tot[Q - 1 - i] : tot[i];
             prim[i] = t - c;
-            m = fminf(m, prim[i]);
+            m = sc_min(m, prim[i]);
         }
 #pragma unroll
         for (int i = 0; i < Q; ++i) msg[(size_t)(es.x + i) * 32] = prim[i] - m;
     }
     if (LAST) {
-        float min_val = INF;
+        Real min_val = INF;
         int arg = 0;
 #pragma unroll
         for (int i = 0; i < Q; ++i)
@@ -181,11 +194,11 @@ __global__ void __launch_bounds__(kVnWarps * 32) k_vn(const QaryDev p, const int
         if (p.risk) {
             Min2 mm;
 #pragma unroll
-            for (int i = 0; i < Q; ++i) mm.add(tot[i]);
+            for (int i = 0; i < Q; ++i) mm.add((float)tot[i]);
             flag_risk(p, tile, lane, !frozen && mm.risky(p.risk_eps));
         }
         if (p.post && !frozen) {
-            float *post = p.post + (size_t)tile * p.SL * 32 + lane;
+            Real *post = p.post + (size_t)tile * p.SL * 32 + lane;
 #pragma unroll
             for (int i = 0; i < Q; ++i) post[(size_t)(var * Q + i) * 32] = tot[i];
         }
@@ -276,7 +289,8 @@ __global__ void __launch_bounds__(kVnWarps * 32) k_vn_reg(const QaryDev p, const
 
 // First-iteration initialisation of the B-edges for the runtime-shape path: v2c = perm_h(channel)
 // (decoder.rs:567-573).  One warp = (tile, edge).
-__global__ void __launch_bounds__(256) k_init_v2c(const QaryDev p, int E)
+template <class Real = float>
+__global__ void __launch_bounds__(256) k_init_v2c(const QaryDevT<Real> p, int E)
 {
     const int lane = threadIdx.x & 31;
     const int e = blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -286,8 +300,8 @@ __global__ void __launch_bounds__(256) k_init_v2c(const QaryDev p, int E)
     if (c >= p.bvars) return;  // sum-variable edges are handled inside the check-node kernel
     const bool neg = __ldg(p.sign + e) < 0;
     const int off = __ldg(p.edge_off + e);
-    float *msg = p.msg + (size_t)tile * p.S * 32 + lane;
-    const float *llr = p.llr + (size_t)tile * p.SL * 32 + lane;
+    Real *msg = p.msg + (size_t)tile * p.S * 32 + lane;
+    const Real *llr = p.llr + (size_t)tile * p.SL * 32 + lane;
     for (int i = 0; i < p.Q; ++i) msg[(size_t)(off + i) * 32] = llr[(size_t)(c * p.Q + (neg ? p.Q - 1 - i : i)) * 32];
 }
 
@@ -309,10 +323,12 @@ struct CnGenericArgs {
     int LMAX;  // max row degree
 };
 
-__global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGenericArgs g)
+template <class Real = float>
+__global__ void __launch_bounds__(32) k_cn_generic(const QaryDevT<Real> p, const CnGenericArgs g)
 {
-    SCALDPC_DYN_SMEM(float, smem);
-    const float INF = SC_INF;
+    SCALDPC_DYN_SMEM(double, smem_generic_raw);  // (double: 8-byte alignment for either scalar type)
+    Real *smem = reinterpret_cast<Real *>(smem_generic_raw);
+    const Real INF = sc_inf<Real>();
     const int lane = threadIdx.x;
     const int check = blockIdx.x, tile = blockIdx.y;
     const int e0 = __ldg(p.row_ptr + check), L = __ldg(p.row_ptr + check + 1) - e0;
@@ -320,14 +336,14 @@ __global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGene
     const uint32_t frozen_w = done_word(p, tile);
     if (frozen_w == 0xffffffffu) return;
     const bool frozen = (frozen_w >> lane) & 1u;
-    float *msg = p.msg + (size_t)tile * p.S * 32 + lane;
+    Real *msg = p.msg + (size_t)tile * p.S * 32 + lane;
     const bool special = p.BSUM > 0;
 
     // scratch: a[L][QM], P[(L+1)][W], A[W], Bv[W]   (all x 32 lanes)
-    float *sa = smem + lane;
-    float *sP = sa + (size_t)g.LMAX * g.QM * 32;
-    float *sA = sP + (size_t)(g.LMAX + 1) * g.W * 32;
-    float *sB = sA + (size_t)g.W * 32;
+    Real *sa = smem + lane;
+    Real *sP = sa + (size_t)g.LMAX * g.QM * 32;
+    Real *sA = sP + (size_t)(g.LMAX + 1) * g.W * 32;
+    Real *sB = sA + (size_t)g.W * 32;
 #define A_(k, i) sa[((k)*g.QM + (i)) * 32]
 #define P_(k, u) sP[((k)*g.W + (u)) * 32]
 #define TA_(u) sA[(u)*32]
@@ -352,15 +368,15 @@ __global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGene
         if (c >= p.bvars) {  // sum-variable: fused variable-node update
             const int vs = c - p.bvars;
             const bool neg = __ldg(p.sign + e0 + k) < 0;
-            const float *llrs = p.llr_sum + (size_t)tile * p.SLS * 32 + lane;
-            float m = INF;
+            const Real *llrs = p.llr_sum + (size_t)tile * p.SLS * 32 + lane;
+            Real m = INF;
             for (int i = 0; i < p.QS; ++i) {
-                float x = llrs[(size_t)(vs * p.QS + (neg ? p.QS - 1 - i : i)) * 32];
+                Real x = llrs[(size_t)(vs * p.QS + (neg ? p.QS - 1 - i : i)) * 32];
                 if (!g.first) {
-                    const float cc = msg[(size_t)(off + i) * 32];
-                    const float t = x + cc;
+                    const Real cc = msg[(size_t)(off + i) * 32];
+                    const Real t = x + cc;
                     x = t - cc;
-                    m = fminf(m, x);
+                    m = sc_min(m, x);
                 }
                 A_(k, i) = x;
             }
@@ -373,15 +389,15 @@ __global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGene
 
     // ---- forward table P_k[u], u offset by tot
     for (int u = 0; u < W; ++u) P_(0, u) = INF;
-    P_(0, tot) = 0.0f;
+    P_(0, tot) = (Real)0;
     for (int k = 0; k < L; ++k) {
         const int bk = BK_(k);
         for (int u = 0; u < W; ++u) {
-            float best = INF;
+            Real best = INF;
             for (int i = 0; i <= 2 * bk; ++i) {
                 const int up = u - (i - bk);
                 if (up < 0 || up >= W) continue;
-                best = fminf(best, P_(k, up) + A_(k, i));
+                best = sc_min(best, P_(k, up) + A_(k, i));
             }
             P_(k + 1, u) = best;
         }
@@ -395,8 +411,8 @@ __global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGene
             const int bj = BK_(j);
             const int offj = __ldg(p.edge_off + e0 + j);
             for (int i = 0; i <= 2 * bj; ++i) {
-                const float x = A_(j, i);
-                float r = INF;
+                const Real x = A_(j, i);
+                Real r = INF;
                 if (x < INF) {
                     for (int u = 0; u < W; ++u) {
                         const int up = u - (i - bj);
@@ -405,17 +421,17 @@ __global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGene
                     for (int k = j + 1; k < L; ++k) {
                         const int bk = BK_(k);
                         for (int u = 0; u < W; ++u) {
-                            float best = INF;
+                            Real best = INF;
                             for (int i2 = 0; i2 <= 2 * bk; ++i2) {
                                 const int up = u - (i2 - bk);
                                 if (up < 0 || up >= W) continue;
-                                best = fminf(best, TA_(up) + A_(k, i2));
+                                best = sc_min(best, TA_(up) + A_(k, i2));
                             }
                             TB_(u) = best;
                         }
                         for (int u = 0; u < W; ++u) TA_(u) = TB_(u);
                     }
-                    const float M = TA_(tot);
+                    const Real M = TA_(tot);
                     r = (M < INF) ? M - x : INF;
                 }
                 msg[(size_t)(offj + i) * 32] = r;
@@ -424,29 +440,29 @@ __global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGene
     } else {
         // backward rolling table: TA = G_{k+1}[u] = cost of the suffix when it must total (u - tot)
         for (int u = 0; u < W; ++u) TA_(u) = INF;
-        TA_(tot) = 0.0f;
+        TA_(tot) = (Real)0;
         for (int j = L - 1; j >= 0; --j) {
             const int bj = BK_(j);
             const int offj = __ldg(p.edge_off + e0 + j);
             for (int i = 0; i <= 2 * bj; ++i) {
-                float r = INF;
+                Real r = INF;
                 if (A_(j, i) < INF) {
                     const int d = i - bj;
                     for (int u = 0; u < W; ++u) {
                         const int us = -(u - tot) - d + tot;
                         if (us < 0 || us >= W) continue;
-                        r = fminf(r, P_(j, u) + TA_(us));
+                        r = sc_min(r, P_(j, u) + TA_(us));
                     }
                 }
                 msg[(size_t)(offj + i) * 32] = r;
             }
             if (j > 0) {
                 for (int u = 0; u < W; ++u) {
-                    float best = INF;
+                    Real best = INF;
                     for (int i = 0; i <= 2 * bj; ++i) {
                         const int up = u - (i - bj);
                         if (up < 0 || up >= W) continue;
-                        best = fminf(best, A_(j, i) + TA_(up));
+                        best = sc_min(best, A_(j, i) + TA_(up));
                     }
                     TB_(u) = best;
                 }
@@ -463,19 +479,19 @@ __global__ void __launch_bounds__(32) k_cn_generic(const QaryDev p, const CnGene
             const int vs = c - p.bvars;
             const bool neg = __ldg(p.sign + e0 + k) < 0;
             const int off = __ldg(p.edge_off + e0 + k);
-            const float *llrs = p.llr_sum + (size_t)tile * p.SLS * 32 + lane;
-            float *post = p.post_sum ? p.post_sum + (size_t)tile * p.SLS * 32 + lane : nullptr;
-            float min_val = INF;
+            const Real *llrs = p.llr_sum + (size_t)tile * p.SLS * 32 + lane;
+            Real *post = p.post_sum ? p.post_sum + (size_t)tile * p.SLS * 32 + lane : nullptr;
+            Real min_val = INF;
             int arg = 0;
             Min2 mm;
             for (int iv = 0; iv < p.QS; ++iv) {  // variable frame, ascending
                 const int i = neg ? p.QS - 1 - iv : iv;
-                const float t = llrs[(size_t)(vs * p.QS + iv) * 32] + msg[(size_t)(off + i) * 32];
+                const Real t = llrs[(size_t)(vs * p.QS + iv) * 32] + msg[(size_t)(off + i) * 32];
                 if (t < min_val) {
                     min_val = t;
                     arg = iv;
                 }
-                mm.add(t);
+                mm.add((float)t);
                 if (post && !frozen) post[(size_t)(vs * p.QS + iv) * 32] = t;
             }
             if (!frozen) p.hard_t[((size_t)tile * p.N + p.bvars + vs) * 32 + lane] = (int8_t)(arg - p.BSUM);
@@ -758,6 +774,42 @@ __global__ void __launch_bounds__(32 * kTrRows) k_load_priors(const float *__res
     }
     float *o = out + ((size_t)tile * per_trial + (size_t)r0 * q) * 32;
     for (int i = ty; i < n; i += kTrRows) o[(size_t)i * 32 + tx] = sm[tx * pitch + i];
+}
+
+// fp64 verification mode: probabilities (f32, row-major [T][rows*q], pydecoder.rs:53) -> LLRs in double, tile layout.
+// into_llr (decoder.rs:668-692) with every operation in double: sum and maximum of the row, ln(max / p).  One warp =
+// (tile, variable), lane = trial; speed is no concern here.  CUDA's log() is within 1 ulp, not correctly rounded: the
+// results agree with a CPU f64 evaluation to ~1e-15 relative, not bit for bit.
+__global__ void __launch_bounds__(256) k_load_priors_f64(const float *__restrict__ in, double *__restrict__ out, int T, int rows,
+                                                         int q, int is_llr, int *__restrict__ status)
+{
+    const int lane = threadIdx.x & 31;
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int tile = blockIdx.y;
+    if (row >= rows) return;
+    const int trial = tile * 32 + lane;
+    const bool live = trial < T;
+    const float *v = in + ((size_t)(live ? trial : 0) * rows + row) * q;
+    double *o = out + ((size_t)tile * rows + row) * q * 32 + lane;
+    if (is_llr || !live) {
+        for (int i = 0; i < q; ++i) o[(size_t)i * 32] = live ? (double)v[i] : 0.0;
+        return;
+    }
+    double sum = 0.0, mx = 0.0;
+    bool have_max = false;
+    for (int i = 0; i < q; ++i) {
+        const double x = (double)v[i];
+        sum += x;
+        if (x == x && (!have_max || x > mx)) {  // NotNan::new filters NaN (decoder.rs:676-680)
+            mx = x;
+            have_max = true;
+        }
+    }
+    int err = 0;
+    if (!have_max) err = SCALDPC_ERR_NO_MAX;
+    else if (!(sum < 1.0 + 0.001) || !(sum > 1.0 - 0.001)) err = SCALDPC_ERR_PROB_SUM;
+    if (err && status) atomicMin(status + trial, err);
+    for (int i = 0; i < q; ++i) o[(size_t)i * 32] = log(mx / (double)v[i]);
 }
 
 // ---- priors given as ORACLE OBSERVATIONS -----------------------------------------------------

@@ -113,6 +113,31 @@ class QaryDecoder:
         _lib.check(rc)
         return hard.tolist()  # Python ints, like the pyo3 return value
 
+    def min_sum_batch_f64(self, priors, priors_sum=None, *, llr=False, want_status=False):
+        """fp64 verification mode (scaldpc_qary_decode_f64): the decode of min_sum_batch with every LLR, message and posterior in
+        double.  priors (T, bvars, q) float32 [+ priors_sum (T, R, qs)]; returns hard int8 (T, N), posteriors float64
+        (T, bvars, q), posteriors_sum float64 (T, R, qs) or None [+ status].  A checker for the f32 path, not a fast path."""
+        x = np.ascontiguousarray(priors, dtype=np.float32)
+        T = x.shape[0]
+        if x.shape != (T, self.bvars, self.Q):
+            raise ValueError(f"priors must be (T, {self.bvars}, {self.Q}), got {x.shape}")
+        xs = None
+        if self.special:
+            if priors_sum is None:
+                raise TypeError("priors_sum is required for the special decoder")
+            xs = np.ascontiguousarray(priors_sum, dtype=np.float32)
+            if xs.shape != (T, self.R, self.QS):
+                raise ValueError(f"priors_sum must be (T, {self.R}, {self.QS}), got {xs.shape}")
+        hard = np.empty((T, self.N), np.int8)
+        post = np.empty((T, self.bvars, self.Q), np.float64)
+        posts = np.empty((T, self.R, self.QS), np.float64) if self.special else None
+        status = np.zeros(T, np.int32)
+        rc = _lib.lib().scaldpc_qary_decode_f64(self._h, T, x.ctypes.data, xs.ctypes.data if xs is not None else None,
+                                                hard.ctypes.data, post.ctypes.data,
+                                                posts.ctypes.data if posts is not None else None, status.ctypes.data,
+                                                _lib.IN_LLR if llr else 0)
+        return self._finish(rc, hard, post, posts, status, want_status)
+
     def combining_stats(self):
         """(single decodes served, batches they were decoded in) by min_sum() on this decoder."""
         a, b = C.c_longlong(), C.c_longlong()

@@ -254,18 +254,18 @@ static int hm_qary_decode(const int8_t *H, int R, int N, int b, int bsum, int dv
                      n_items, first, last);
         } else if (g.BSUM == 0 && !exact && !force_generic && (g.Q == 3 || g.Q == 15)) {
             // generic decoder, one alphabet: k_cn_uniform<Q>, as launch_cn chooses it (qary.cu)
-            if (first) run_grid((g.E + 7) / 8, tiles, 256, k_init_v2c, p, g.E);
+            if (first) run_grid((g.E + 7) / 8, tiles, 256, k_init_v2c<float>, p, g.E);
             std::vector<float> us(((size_t)g.lmax * g.Q + (size_t)(g.lmax + 2 + 1) * (g.wmax + 2 * g.B)) * 32);
             scaldpc_host_model_smem = us.data();
             if (g.Q == 3) run_grid(g.R, tiles, 32, k_cn_uniform<3>, p, g.lmax, (g.wmax - 1) / 2);
             else run_grid(g.R, tiles, 32, k_cn_uniform<15>, p, g.lmax, (g.wmax - 1) / 2);
             scaldpc_host_model_smem = scratch.data();
         } else {
-            if (first) run_grid((g.E + 7) / 8, tiles, 256, k_init_v2c, p, g.E);
+            if (first) run_grid((g.E + 7) / 8, tiles, 256, k_init_v2c<float>, p, g.E);
             CnGenericArgs a;
             a.exact = exact; a.first = first; a.last = last;
             a.QM = std::max(g.Q, g.QS); a.W = g.wmax; a.LMAX = g.lmax;
-            run_grid(g.R, tiles, 32, k_cn_generic, p, a);
+            run_grid(g.R, tiles, 32, k_cn_generic<float>, p, a);
         }
         run_grid((g.bvars + kVnWarps - 1) / kVnWarps, tiles, kVnWarps * 32, vn, p, last);
         if (early) {  // early_stop_round (qary.cu): row tests, freeze, count

@@ -532,3 +532,50 @@ def test_default_path_equals_exact_kernel_at_scale(variant, sw, cb, acc, nb, nbs
     print(variant, sw, "re-decoded", n_re, "success", ok.mean())
     assert n_re > 0 and ok.mean() < 1.0          # the verification had something to do
     assert n_re < T or ok.mean() == 0.0          # ... and re-decoded everything only where nothing decodes
+
+
+def test_fp64_verification_mode_on_the_gpu():
+    """scaldpc_qary_decode_f64 (north_star: "fp64 option for verification") against the oracle's f64 instantiation
+    (oracle/qary_oracle.c, REAL = double; exact-order DP, asserted bit-equal to the enumeration in f32): hard decisions
+    identical, posteriors within 1e-9 (CUDA's log() is within 1 ulp of libm's, everything else is the same sequence of
+    double operations); and the f32 product path lies within 1e-4 of it wherever no decision is at a tie."""
+    # special decoder: reference-produced kyber768 priors (lib.rs:54-64) ...
+    z = util.load("kyber768_cb1.npz")
+    H = util.dense(z)
+    it = int(z["iterations"][0])
+    d = simulate_rs.DecoderN1024R256SW6(H, it)
+    orc = O.QaryOracle(H, it, B=2, BSUM=12, DC=7, algo=O.ALGO_EXACT_DP)
+    n = 4
+    same_it = [i for i in range(len(z["iterations"])) if int(z["iterations"][i]) == it][:n]
+    co, cos = z["channel_output"][same_it], z["channel_output_sum"][same_it]
+    hard, post, posts = d.min_sum_batch_f64(co, cos)
+    assert post.dtype == np.float64 and posts.dtype == np.float64
+    for k, i in enumerate(same_it):
+        h64, p64, ps64 = orc.decode_probs(co[k], cos[k], dtype=np.float64)
+        assert np.array_equal(hard[k], h64)
+        assert util.same_nonfinite(post[k], p64) and util.same_nonfinite(posts[k], ps64)
+        assert util.max_abs_diff(post[k], p64) < 1e-9 and util.max_abs_diff(posts[k], ps64) < 1e-9
+        assert np.array_equal(hard[k], z["hard"][i])                     # = the reference's own f32 decisions
+        assert util.max_abs_diff(post[k].astype(np.float32), z["post"][i]) < TOL
+    # ... and a kyber512 batch larger than one tile, against the f32 product path
+    w = KyberWorkload("kyber512", 6, 1, accuracy=0.98, nbits=4, nbits_sum=5, seed=0)
+    b = w.generate(70, seed=9)
+    d5 = QaryDecoder(w.H, 6, **w.decoder_kwargs)
+    h64, p64, ps64 = d5.min_sum_batch_f64(b.priors, b.priors_sum)
+    h32, p32, ps32 = d5.min_sum_batch(b.priors, b.priors_sum)
+    o5 = O.QaryOracle(w.H, 6, algo=O.ALGO_EXACT_DP, **w.decoder_kwargs)
+    for t in (0, 33, 69):
+        oh, op, ops = o5.decode_probs(b.priors[t], b.priors_sum[t], dtype=np.float64)
+        assert np.array_equal(h64[t], oh) and util.max_abs_diff(p64[t], op) < 1e-9 and util.max_abs_diff(ps64[t], ops) < 1e-9
+    agree = (h64 == h32).all(1)
+    assert agree.mean() > 0.9                                             # ties between f32 and f64 are rare
+    assert util.max_abs_diff(p64[agree].astype(np.float32), p32[agree]) < 2e-4
+    # generic decoder (decoder.rs doctest input): per-trial errors are reported as in the f32 path
+    z = util.load("decode_doctest_seed1.npz")
+    dg = getattr(simulate_rs, "DecoderN450R150V3C7B1")(util.dense(z).astype(np.int8), 5)
+    hg, pg, _ = dg.min_sum_batch_f64(z["channel_output"][None])
+    assert np.array_equal(hg[0], z["hard"]) and util.max_abs_diff(pg[0].astype(np.float32), z["post"]) < TOL
+    bad = np.stack([z["channel_output"], z["channel_output"]])
+    bad[1, 3] *= 0.5
+    _, _, _, st = dg.min_sum_batch_f64(bad, want_status=True)
+    assert st.tolist() == [0, -2]
