@@ -355,6 +355,11 @@ long long scaldpc_bp_launch_count(const scaldpc_bp *h);
 /* Statistics of the last decode on this handle: iterations launched (the slowest trial's count) and the number of
  * active-trial compactions performed. */
 int scaldpc_bp_last_run(const scaldpc_bp *h, int *iterations_launched, int *compactions);
+/* Host-buffer decodes into PAGE-LOCKED output arrays send the T x n decision bytes (and LLRs) home while the non-converging
+ * stragglers still iterate: at the first compaction that leaves <= 256 trials running, every other row is final and the whole
+ * array is copied on a side stream; the stragglers' rows are sent again at the end.  rows = stragglers at that moment in the
+ * last decode on this handle, -1 = the copy ran at the end as usual (pageable output, small batch, no such compaction). */
+int scaldpc_bp_last_early_copy(const scaldpc_bp *h, int *rows);
 /* Per-kernel timing probe (bench.py roofline leg), as scaldpc_qary_time_kernel:
  *   which  0 = check-to-bit kernel, 1 = bit-to-check kernel; every tile of the previous decode is re-activated. */
 int scaldpc_bp_time_kernel(scaldpc_bp *h, int which, int T, unsigned flags, int reps, void *stream, float *avg_ms);

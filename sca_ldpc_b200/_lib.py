@@ -27,7 +27,7 @@ SYMBOLS = [
     "scaldpc_qary_decode", "scaldpc_qary_decode_observed", "scaldpc_qary_simulate", "scaldpc_qary_launch_count", "scaldpc_qary_time_kernel",
     "scaldpc_qary_last_run", "scaldpc_qary_set_risk_margin", "scaldpc_qary_last_iterations",
     "scaldpc_bp_create", "scaldpc_bp_destroy", "scaldpc_bp_info", "scaldpc_bp_decode", "scaldpc_bp_decode_scored", "scaldpc_bp_decode_nested", "scaldpc_bp_launch_count",
-    "scaldpc_bp_create_multi", "scaldpc_bp_decode_multi", "scaldpc_bp_create_circulant", "scaldpc_bp_decode_static", "scaldpc_qary_decode_one", "scaldpc_qary_decode_f64", "scaldpc_qary_one_stats",
+    "scaldpc_bp_create_multi", "scaldpc_bp_decode_multi", "scaldpc_bp_create_circulant", "scaldpc_bp_decode_static", "scaldpc_bp_last_early_copy", "scaldpc_qary_decode_one", "scaldpc_qary_decode_f64", "scaldpc_qary_one_stats",
     "scaldpc_bp_last_run", "scaldpc_bp_time_kernel",
 ]
 
@@ -112,6 +112,8 @@ def lib() -> C.CDLL:
     L.scaldpc_qary_decode_one.argtypes = [vp, vp, vp, vp]
     L.scaldpc_qary_one_stats.restype = i
     L.scaldpc_qary_one_stats.argtypes = [vp, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
+    L.scaldpc_bp_last_early_copy.restype = i
+    L.scaldpc_bp_last_early_copy.argtypes = [vp, C.POINTER(i)]
     L.scaldpc_bp_decode_static.restype = i
     L.scaldpc_bp_decode_static.argtypes = [vp, i, vp, vp, vp, vp, vp, vp]
     L.scaldpc_bp_decode_multi.restype = i

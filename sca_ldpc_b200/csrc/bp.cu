@@ -78,6 +78,11 @@ struct scaldpc_bp {
     std::mutex mu;
     long long launches = 0;
     int last_iters_run = 0, last_compactions = 0;
+    // host path: device-to-host copy of the finished rows while the stragglers still iterate (bp_decode_impl)
+    cudaStream_t s_copy = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    int early_copy_max = 256;  // start it at the first compaction that leaves at most this many running (SCALDPC_BP_EARLY_COPY)
+    int last_early_copy_rows = -1;
 };
 
 namespace {
@@ -495,6 +500,7 @@ static int bp_finish_create(scaldpc_bp *h)
     if (const char *e = getenv("SCALDPC_BP_VN_SINGLE")) h->vn_single_tiles = atoi(e);
     if (const char *e = getenv("SCALDPC_BP_VN_SINGLE_ITEMS")) h->vn_single_items = atoll(e);
     if (const char *e = getenv("SCALDPC_BP_VN_PIPE")) h->vn_pipe = atoi(e) != 0;
+    if (const char *e = getenv("SCALDPC_BP_EARLY_COPY")) h->early_copy_max = atoi(e);
     for (int c = 0; c < kBpVnClasses; ++c) {
         SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->vn_occ[c], vn_class_fn(c), kBpVnWarps * 32, 0));
         h->vn_occ[c] = std::max(1, h->vn_occ[c]);
@@ -552,6 +558,9 @@ void scaldpc_bp_destroy(scaldpc_bp *h)
     cudaFree(h->d_nact);
     cudaFree(h->d_counts);
     if (h->h_pin) cudaFreeHost(h->h_pin);
+    if (h->s_copy) cudaStreamDestroy(h->s_copy);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
     delete h;
 }
 
@@ -701,6 +710,24 @@ static int bp_decode_impl(scaldpc_bp *h, int T, const uint8_t *synd, const doubl
     // launching at zero and compacts the running trials when they fill at most half of the current slots.
     int cur = 0, cur_tiles = tiles;
     h->last_compactions = 0;
+    h->last_early_copy_rows = -1;
+    bool early_copy = false, early_copy_ok = false;
+    std::vector<int> tail_orig;
+    if (!dev_ptrs && decoding && compacting && !score && h->early_copy_max > 0 && (long long)T * h->n >= (8 << 20)) {
+        // only into page-locked memory: a copy into pageable memory blocks the host thread that must keep launching
+        cudaPointerAttributes pa;
+        bool pinned = cudaPointerGetAttributes(&pa, decoding) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+        if (pinned && llr) pinned = cudaPointerGetAttributes(&pa, llr) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+        cudaGetLastError();
+        if (pinned) {
+            if (!h->s_copy) {
+                SCALDPC_CUDA(cudaStreamCreateWithFlags(&h->s_copy, cudaStreamNonBlocking));
+                SCALDPC_CUDA(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+                SCALDPC_CUDA(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
+            }
+            early_copy_ok = true;
+        }
+    }
     int it = 1;
     for (; it <= h->max_iter; ++it) {
         const bool last = it == h->max_iter;
@@ -732,15 +759,35 @@ static int bp_decode_impl(scaldpc_bp *h, int T, const uint8_t *synd, const doubl
         // trials converge (the first four) or while the batch is large enough to hide it, then every 4th / 8th --
         // kernels launched for tiles that have retired meanwhile exit at once
         if (early && !last && (it <= 4 || cur_tiles >= 512 || (it <= 16 ? it % 4 == 0 : it % 8 == 0))) {
-            SCALDPC_CUDA(cudaMemcpyAsync(h->h_pin, h->d_counts + it, sizeof(int), cudaMemcpyDeviceToHost, st));
+            // the count comes home through a store into page-locked host memory, not through the copy engine: a 4-byte
+            // copy would queue behind the early copy of the finished rows (below) and stall the stragglers for its duration
+            k_bp_publish<<<1, 1, 0, st>>>(h->d_counts + it, h->h_pin);
+            ++h->launches;
             SCALDPC_CUDA(cudaStreamSynchronize(st));
-            const int n_run = h->h_pin[0];
+            const int n_run = *(volatile int *)h->h_pin;
             if (n_run == 0) break;
             if (compacting && cur_tiles >= 2 && (long long)n_run * 2 <= (long long)cur_tiles * 32) {
                 if ((rc = compact(h, cur, cur_tiles, n_run, probs_t, ddec, dllr, st))) return rc;
                 cur ^= 1;
                 cur_tiles = (n_run + 31) / 32;
                 ++h->last_compactions;
+                if (early_copy_ok && !early_copy && n_run <= h->early_copy_max) {
+                    // Every row of d_dec / d_llr but those of the n_run stragglers is final (compact() wrote the finished
+                    // trials out): send the whole arrays home on a side stream while the stragglers iterate -- the tail
+                    // lasts tens of iterations on a few tiles, the copy of T x n bytes a few ms -- and send the stragglers'
+                    // rows again at the end.
+                    tail_orig.resize((size_t)cur_tiles * 32);
+                    SCALDPC_CUDA(cudaMemcpyAsync(tail_orig.data(), h->set[cur].orig, tail_orig.size() * sizeof(int),
+                                                 cudaMemcpyDeviceToHost, st));
+                    SCALDPC_CUDA(cudaEventRecord(h->ev_fork, st));
+                    SCALDPC_CUDA(cudaStreamSynchronize(st));
+                    SCALDPC_CUDA(cudaStreamWaitEvent(h->s_copy, h->ev_fork, 0));
+                    SCALDPC_CUDA(cudaMemcpyAsync(decoding, h->d_dec, (size_t)T * h->n, cudaMemcpyDeviceToHost, h->s_copy));
+                    if (llr) SCALDPC_CUDA(cudaMemcpyAsync(llr, h->d_llr, (size_t)T * h->n * sizeof(float), cudaMemcpyDeviceToHost, h->s_copy));
+                    SCALDPC_CUDA(cudaEventRecord(h->ev_join, h->s_copy));
+                    early_copy = true;
+                    h->last_early_copy_rows = n_run;
+                }
             }
         }
     }
@@ -775,7 +822,15 @@ static int bp_decode_impl(scaldpc_bp *h, int T, const uint8_t *synd, const doubl
         if (!dev_ptrs)
             SCALDPC_CUDA(cudaMemcpyAsync(score->stats, h->d_stats, (size_t)T * 6 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     }
-    if (!dev_ptrs) {
+    if (!dev_ptrs && early_copy) {
+        SCALDPC_CUDA(cudaStreamWaitEvent(st, h->ev_join, 0));  // the stragglers' rows are rewritten AFTER the early copy
+        for (int o : tail_orig) {
+            if (o < 0) continue;
+            SCALDPC_CUDA(cudaMemcpyAsync(decoding + (size_t)o * h->n, h->d_dec + (size_t)o * h->n, (size_t)h->n, kind, st));
+            if (llr)
+                SCALDPC_CUDA(cudaMemcpyAsync(llr + (size_t)o * h->n, h->d_llr + (size_t)o * h->n, (size_t)h->n * sizeof(float), kind, st));
+        }
+    } else if (!dev_ptrs) {
         if (decoding) SCALDPC_CUDA(cudaMemcpyAsync(decoding, h->d_dec, (size_t)T * h->n, kind, st));
         if (llr) SCALDPC_CUDA(cudaMemcpyAsync(llr, h->d_llr, (size_t)T * h->n * sizeof(float), kind, st));
     }
@@ -904,6 +959,13 @@ int scaldpc_bp_last_run(const scaldpc_bp *h, int *iterations_launched, int *comp
     if (!h) return fail(SCALDPC_ERR_ARG, "handle is NULL");
     if (iterations_launched) *iterations_launched = h->last_iters_run;
     if (compactions) *compactions = h->last_compactions;
+    return 0;
+}
+
+int scaldpc_bp_last_early_copy(const scaldpc_bp *h, int *rows)
+{
+    if (!h || !rows) return fail(SCALDPC_ERR_ARG, "NULL argument");
+    *rows = h->last_early_copy_rows;
     return 0;
 }
 

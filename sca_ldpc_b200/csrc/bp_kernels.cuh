@@ -818,6 +818,16 @@ __global__ void __launch_bounds__(256) k_bp_finish_iter(const BpDev p, int tiles
     }
 }
 
+// One word of device memory -> page-locked host memory (UVA: the host pointer is valid on the device).  The host reads it
+// after synchronising the stream.
+#ifndef SCALDPC_HOST_MODEL
+__global__ void k_bp_publish(const int *__restrict__ src, int *dst)
+{
+    *dst = *src;
+    __threadfence_system();
+}
+#endif
+
 // Reset of the per-decode state.  One thread per tile: valid mask from T, done = 0, identity slot map,
 // iters = max_iter, conv = 0.
 __global__ void __launch_bounds__(256) k_bp_reset(uint32_t *valid, uint32_t *done, uint32_t *unsat, int *orig, int *iters,

@@ -473,3 +473,30 @@ def test_graphs_built_on_the_device_equal_host_built_graphs():
     bad_rows[1, 7] = N
     with pytest.raises(Exception):
         bp_decoder_multi.from_circulants(first_cols, bad_rows, N, max_iter=30, channel_probs=probs)
+
+
+def test_early_copy_of_finished_rows_is_transparent():
+    """Host-buffer decodes into page-locked outputs copy the finished rows home while the stragglers iterate
+    (scaldpc_bp_last_early_copy): same decisions, LLRs, iteration counts as the plain path into pageable memory."""
+    import ctypes as C
+
+    import torch
+
+    from sca_ldpc_b200 import _lib
+
+    wl = HqcWorkload("hqc128", seed=0)
+    T = 2048
+    b = wl.generate(T, seed=5)
+    dec = bp_decoder(csr=(wl.row_ptr, wl.col), shape=(wl.m, wl.n), max_iter=40, channel_probs=wl.channel_probs)
+    plain = dec.decode_batch(b.syndromes, want_llr=True)
+    rows = C.c_int()
+    _lib.check(_lib.lib().scaldpc_bp_last_early_copy(dec._h, C.byref(rows)))
+    assert rows.value == -1                      # pageable output: the ordinary copy
+    out = torch.empty((T, wl.n), dtype=torch.uint8).pin_memory().numpy()
+    out[:] = 7
+    pinned = dec.decode_batch(b.syndromes, out=out)
+    _lib.check(_lib.lib().scaldpc_bp_last_early_copy(dec._h, C.byref(rows)))
+    assert 0 < rows.value <= 256                 # the early copy ran, with stragglers re-sent at the end
+    assert 0 < (plain["converged"] == 0).sum()   # ... and there were stragglers to re-send
+    assert np.array_equal(pinned["decoding"], plain["decoding"]) and pinned["decoding"] is out
+    assert np.array_equal(pinned["iters"], plain["iters"]) and np.array_equal(pinned["converged"], plain["converged"])
