@@ -511,11 +511,19 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const 
             break;
         }
         if (it.tile < tiles) {
+#ifdef SCALDPC_HOST_MODEL
             it.var = __ldg(p.vn_order + (size_t)g * p.g_n + lo + it.j);
             const int *cp = p.col_ptr + (size_t)g * p.g_cp + it.var;
             const int c0 = __ldg(cp);
             it.d = __ldg(cp + 1) - c0;  // in (DMIN, DMAX] (host guarantees)
             it.p0 = g * p.g_e + c0;     // position in the (concatenated) csc_off table
+#else
+            // {variable, col_ptr, degree} of the sorted position in ONE 16-byte load instead of vn_order -> col_ptr x 2
+            const int4 q = __ldg(p.vn_desc + (size_t)g * p.g_n + lo + it.j);
+            it.var = q.x;
+            it.d = q.z;
+            it.p0 = g * p.g_e + q.y;
+#endif
         }
     };
     auto gather = [&](const BpVnItem &it, float (&c)[DMAX]) {
@@ -707,9 +715,14 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_generic(const BpDev p
         idx = lo + (idx - v_lo);
         if (idx >= __ldg(ce + cls)) return;
     }
+#ifdef SCALDPC_HOST_MODEL
     const int var = __ldg(p.vn_order + (size_t)g * p.g_n + idx);
     const int *cp = p.col_ptr + (size_t)g * p.g_cp + var;
     const int p0 = g * p.g_e + __ldg(cp), d = __ldg(cp + 1) - __ldg(cp);
+#else
+    const int4 q = __ldg(p.vn_desc + (size_t)g * p.g_n + idx);  // {variable, col_ptr, degree}: one load
+    const int var = q.x, p0 = g * p.g_e + q.y, d = q.z;
+#endif
     float *C = smem + (size_t)warp * 2 * p.dv_max * 32 + lane;
     float *F = C + (size_t)p.dv_max * 32;
     float *msg = p.msg + (size_t)tile * p.E * 32 + lane;
