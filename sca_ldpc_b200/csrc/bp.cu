@@ -249,9 +249,11 @@ int launch_cn(scaldpc_bp *h, const BpDev &p, int tiles, bool first, cudaStream_t
 }
 
 typedef void (*bp_vn_fn)(const BpDev, const int, const int, const int, const int);
-bp_vn_fn vn_class_fn(int c, bool first = false)
+bp_vn_fn vn_class_fn(int c, bool first = false, bool shared = false)
 {
-#define CLS(A_, B_) return first ? k_bp_vn<A_, B_, true> : k_bp_vn<A_, B_, false>
+#define CLS(A_, B_)                                                                                  \
+    return first ? k_bp_vn<A_, B_, true, true> /* the first-pass table implies shared priors */     \
+                 : (shared ? k_bp_vn<A_, B_, false, true> : k_bp_vn<A_, B_, false, false>)
     switch (c) {
     case 0: CLS(0, 1);
     case 1: CLS(1, 4);
@@ -320,7 +322,7 @@ int launch_vn(scaldpc_bp *h, const BpDev &p, int tiles, cudaStream_t st, bool fi
                 if (pipe)
                     vn_pipe_fn(c)<<<std::max(1, ctas), kBpVnWarps * 32, vn_pipe_smem(c), st>>>(p, lo, hi, tiles, multi ? c : -1);
                 else
-                    vn_class_fn(c, first)<<<std::max(1, ctas), kBpVnWarps * 32, 0, st>>>(p, lo, hi, tiles, multi ? c : -1);
+                    vn_class_fn(c, first, !p.per_trial_prior)<<<std::max(1, ctas), kBpVnWarps * 32, 0, st>>>(p, lo, hi, tiles, multi ? c : -1);
             } else {
                 generic<<<dim3((hi - lo + h->vn_gen_wpc - 1) / h->vn_gen_wpc, tiles), h->vn_gen_wpc * 32, h->smem_vn, st>>>(
                     p, lo, hi, multi ? c : -1);
@@ -502,8 +504,10 @@ static int bp_finish_create(scaldpc_bp *h)
     if (const char *e = getenv("SCALDPC_BP_VN_PIPE")) h->vn_pipe = atoi(e) != 0;
     if (const char *e = getenv("SCALDPC_BP_EARLY_COPY")) h->early_copy_max = atoi(e);
     for (int c = 0; c < kBpVnClasses; ++c) {
+        int occ_shared = 0;
         SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->vn_occ[c], vn_class_fn(c), kBpVnWarps * 32, 0));
-        h->vn_occ[c] = std::max(1, h->vn_occ[c]);
+        SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shared, vn_class_fn(c, false, true), kBpVnWarps * 32, 0));
+        h->vn_occ[c] = std::max(1, std::min(h->vn_occ[c], occ_shared));
         if (vn_pipe_fn(c)) {
             SCALDPC_CUDA(cudaFuncSetAttribute(vn_pipe_fn(c), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vn_pipe_smem(c)));
             SCALDPC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->vn_pipe_occ[c], vn_pipe_fn(c), kBpVnWarps * 32,

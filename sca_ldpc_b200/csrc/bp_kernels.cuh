@@ -475,7 +475,9 @@ __device__ __forceinline__ void bp_vn_dispatch(const BpDev &p, const BpVnItem &i
 // FIRST (iteration 1, shared priors): the incoming messages are not read from memory but formed from the first-pass table,
 // c = +-first_tab[e] with the sign of the trial's syndrome bit of the edge's check (what k_bp_first_fill would have written;
 // an inactive check of a nested decode sends +0) -- the first iteration then writes the message array once and never reads it.
-template <int DMIN, int DMAX, bool FIRST>
+// SHARED: the priors are known to be shared by the trials (the HQC call site): the per-trial address arithmetic, which a
+// run-time test only predicates off (~16 issue slots per item), is not generated.
+template <int DMIN, int DMAX, bool FIRST, bool SHARED = false>
 // Segmented CSR (p.class_end set): `cls` is the degree class, [v_lo, v_hi) = [0, largest class size over the graphs);
 // every tile takes its own graph's slice of the class and skips the j beyond it.
 __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const int v_lo, const int v_hi, const int tiles,
@@ -559,14 +561,14 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const 
     float pr = 0.0f, prn = 0.0f;  // the variable's prior travels with its column (44 % of the stall samples sat on it)
     if (cur.tile < tiles) {
         gather(cur, c);
-        pr = bp_prior_of(p, cur.tile, cur.var, lane);
+        pr = SHARED ? __ldg(p.prior + cur.var) : bp_prior_of(p, cur.tile, cur.var, lane);
     }
     while (cur.tile < tiles) {
         BpVnItem nxt = cur;
         advance(nxt, false);
         if (nxt.tile < tiles) {
             gather(nxt, cn);
-            prn = bp_prior_of(p, nxt.tile, nxt.var, lane);
+            prn = SHARED ? __ldg(p.prior + nxt.var) : bp_prior_of(p, nxt.tile, nxt.var, lane);
         }
         bp_vn_dispatch<DMAX, (DMIN == 0 ? 0 : DMIN + 1), DMAX>(p, cur, lane, c, pr);
         cur = nxt;
