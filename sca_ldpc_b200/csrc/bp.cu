@@ -252,8 +252,8 @@ typedef void (*bp_vn_fn)(const BpDev, const int, const int, const int, const int
 bp_vn_fn vn_class_fn(int c, bool first = false, bool shared = false)
 {
 #define CLS(A_, B_)                                                                                  \
-    return first ? k_bp_vn<A_, B_, true, true> /* the first-pass table implies shared priors */     \
-                 : (shared ? k_bp_vn<A_, B_, false, true> : k_bp_vn<A_, B_, false, false>)
+    return shared ? (first ? k_bp_vn<A_, B_, true, true> : k_bp_vn<A_, B_, false, true>)            \
+                  : (first ? k_bp_vn<A_, B_, true, false> : k_bp_vn<A_, B_, false, false>)
     switch (c) {
     case 0: CLS(0, 1);
     case 1: CLS(1, 4);
@@ -322,7 +322,7 @@ int launch_vn(scaldpc_bp *h, const BpDev &p, int tiles, cudaStream_t st, bool fi
                 if (pipe)
                     vn_pipe_fn(c)<<<std::max(1, ctas), kBpVnWarps * 32, vn_pipe_smem(c), st>>>(p, lo, hi, tiles, multi ? c : -1);
                 else
-                    vn_class_fn(c, first, !p.per_trial_prior)<<<std::max(1, ctas), kBpVnWarps * 32, 0, st>>>(p, lo, hi, tiles, multi ? c : -1);
+                    vn_class_fn(c, first, !p.per_trial_prior && !p.post)<<<std::max(1, ctas), kBpVnWarps * 32, 0, st>>>(p, lo, hi, tiles, multi ? c : -1);
             } else {
                 generic<<<dim3((hi - lo + h->vn_gen_wpc - 1) / h->vn_gen_wpc, tiles), h->vn_gen_wpc * 32, h->smem_vn, st>>>(
                     p, lo, hi, multi ? c : -1);

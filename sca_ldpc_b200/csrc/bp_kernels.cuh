@@ -378,10 +378,11 @@ __global__ void __launch_bounds__(256) k_bp_first_fill(const BpDev p, const floa
 // -----------------------------------------------------------------------------------------------------------
 constexpr int kBpVnWarps = 8;
 
+template <bool LEAN = false>  // LEAN: no posterior output (p.post is known to be null)
 __device__ __forceinline__ void bp_vn_decide(const BpDev &p, int tile, int var, int lane, uint32_t done, float post)
 {
     const bool active = !((done >> lane) & 1u);
-    if (p.post && active) p.post[((size_t)tile * p.n + var) * 32 + lane] = post;
+    if (!LEAN && p.post && active) p.post[((size_t)tile * p.n + var) * 32 + lane] = post;
 #ifdef SCALDPC_HOST_MODEL
     uint32_t &w = p.dec_w[(size_t)tile * p.n + var];
     if (active) w = (w & ~(1u << lane)) | ((post <= 0.0f ? 1u : 0u) << lane);
@@ -412,7 +413,7 @@ __device__ __forceinline__ float *bp_at(float *base, uint32_t byte_off) { return
 // The two sweeps of one variable of degree exactly D (straight-line code, no guards).  Upstream resets a NaN running value to the neutral element; a NaN can only
 // appear when +inf meets -inf, and then the forward total is NaN too, so the sweeps run WITHOUT the per-step tests and a
 // NaN total sends the lane through the tested version (identical results; 4 fewer instructions per edge otherwise).
-template <int D, int DMAX>
+template <int D, int DMAX, bool LEAN = false>
 __device__ __forceinline__ void bp_vn_body(const BpDev &p, const BpVnItem &it, int lane, const float (&c)[DMAX],
                                            const float prior)
 {
@@ -454,20 +455,20 @@ __device__ __forceinline__ void bp_vn_body(const BpDev &p, const BpVnItem &it, i
             if (temp != temp) temp = 0.0f;
         }
     }
-    bp_vn_decide(p, it.tile, it.var, lane, done, post);
+    bp_vn_decide<LEAN>(p, it.tile, it.var, lane, done, post);
 }
 
-template <int D, int DMIN, int DMAX>
+template <int D, int DMIN, int DMAX, bool LEAN = false>
 __device__ __forceinline__ void bp_vn_dispatch(const BpDev &p, const BpVnItem &it, int lane, const float (&c)[DMAX],
                                                const float prior)
 {
     if constexpr (D < DMIN) {
-        bp_vn_body<DMAX, DMAX>(p, it, lane, c, prior);  // unreachable for a correctly sorted class; keeps the code total
+        bp_vn_body<DMAX, DMAX, LEAN>(p, it, lane, c, prior);  // unreachable for a correctly sorted class; keeps the code total
     } else {
         if (it.d == D)
-            bp_vn_body<D, DMAX>(p, it, lane, c, prior);
+            bp_vn_body<D, DMAX, LEAN>(p, it, lane, c, prior);
         else
-            bp_vn_dispatch<D - 1, DMIN, DMAX>(p, it, lane, c, prior);
+            bp_vn_dispatch<D - 1, DMIN, DMAX, LEAN>(p, it, lane, c, prior);
     }
 }
 
@@ -475,8 +476,9 @@ __device__ __forceinline__ void bp_vn_dispatch(const BpDev &p, const BpVnItem &i
 // FIRST (iteration 1, shared priors): the incoming messages are not read from memory but formed from the first-pass table,
 // c = +-first_tab[e] with the sign of the trial's syndrome bit of the edge's check (what k_bp_first_fill would have written;
 // an inactive check of a nested decode sends +0) -- the first iteration then writes the message array once and never reads it.
-// SHARED: the priors are known to be shared by the trials (the HQC call site): the per-trial address arithmetic, which a
-// run-time test only predicates off (~16 issue slots per item), is not generated.
+// SHARED ("lean"): the priors are known to be shared by the trials and no posterior is wanted (the HQC call site): the
+// per-trial prior's and the posterior's address arithmetic, which run-time tests only predicate off (~20 issue slots per
+// item), is not generated.
 template <int DMIN, int DMAX, bool FIRST, bool SHARED = false>
 // Segmented CSR (p.class_end set): `cls` is the degree class, [v_lo, v_hi) = [0, largest class size over the graphs);
 // every tile takes its own graph's slice of the class and skips the j beyond it.
@@ -570,7 +572,7 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const 
             gather(nxt, cn);
             prn = SHARED ? __ldg(p.prior + nxt.var) : bp_prior_of(p, nxt.tile, nxt.var, lane);
         }
-        bp_vn_dispatch<DMAX, (DMIN == 0 ? 0 : DMIN + 1), DMAX>(p, cur, lane, c, pr);
+        bp_vn_dispatch<DMAX, (DMIN == 0 ? 0 : DMIN + 1), DMAX, SHARED>(p, cur, lane, c, pr);
         cur = nxt;
         pr = prn;
 #pragma unroll
