@@ -29,7 +29,7 @@ ERRORS = {
     -7: "sum value out of [-BSUM, BSUM] (decoder_special.rs:546)",
 }
 
-ALGO_ENUMERATE, ALGO_EXACT_DP, ALGO_FWD_BWD, ALGO_FAST = 0, 1, 2, 3
+ALGO_ENUMERATE, ALGO_EXACT_DP, ALGO_FWD_BWD, ALGO_FAST, ALGO_SPLIT = 0, 1, 2, 3, 4
 
 
 class OracleError(RuntimeError):

@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(kVnWarps * 32) k_vn(const QaryDevT<Real> p, co
             m = sc_min(m, prim[i]);
         }
 #pragma unroll
-        for (int i = 0; i < Q; ++i) msg[(size_t)(es.x + i) * 32] = prim[i] - m;
+        for (int i = 0; i < Q; ++i) msg[(size_t)(es.x + i) * 32] = sanitize(prim[i] - m);  // NaN (excluded value) travels as +inf
     }
     if (LAST) {
         Real min_val = INF;
@@ -261,7 +261,7 @@ __global__ void __launch_bounds__(kVnWarps * 32) k_vn_reg(const QaryDev p, const
         for (int i = 0; i < Q; ++i) m = fminf(m, prim[i]);
         float *dst = msg + (size_t)es[e].x * 32;
 #pragma unroll
-        for (int i = 0; i < Q; ++i) dst[i * 32] = prim[i] - m;
+        for (int i = 0; i < Q; ++i) dst[i * 32] = sanitize(prim[i] - m);  // NaN (excluded value) travels as +inf
     }
     if (LAST) {
         float min_val = INF;

@@ -58,8 +58,8 @@ def test_fast_kernel_equals_fast_oracle_bitwise():
         rc, hard, post, posts, _, fast = util.hostmodel_qary(H, 2, 12, it, llr, llrs, dc=7, flags=NO_VERIFY)
         assert rc == 0 and fast and np.array_equal(hard[0], h2)
         assert np.array_equal(post[0], p2, equal_nan=True) and np.array_equal(posts[0], ps2, equal_nan=True)
-        if it == 1:  # a single iteration has no simplification at all: equals the forward/backward model
-            h3, p3, ps3 = d.decode_llr(llr[0], llrs[0], algo=O.ALGO_FWD_BWD)
+        if it == 1:  # a single iteration has no simplification at all: equals the plain split forward/backward model
+            h3, p3, ps3 = d.decode_llr(llr[0], llrs[0], algo=O.ALGO_SPLIT)
             assert np.array_equal(p2, p3, equal_nan=True) and np.array_equal(ps2, ps3, equal_nan=True)
 
 

@@ -148,7 +148,8 @@ def llr_close(a, b, atol=2e-3, rtol=2e-4):
 
 
 def early_stop_model(w, llr, llrs, iters, verify, eps=1e-2):
-    """Per-trial early termination restated with the oracle: plain forward/backward flooding (algo 2); the trial stops in
+    """Per-trial early termination restated with the oracle: plain forward/backward flooding in the fast kernel's order of
+    additions (algo 4, the sum-variables' messages make the full round trip); the trial stops in
     the first iteration whose hard decisions satisfy every row and whose posteriors are clear of ties; a trial that never
     does gets the reference's fixed-iteration decode (exact-order) in verified mode, else its last decisions."""
     T = llr.shape[0]
@@ -167,7 +168,7 @@ def early_stop_model(w, llr, llrs, iters, verify, eps=1e-2):
 
     for k in range(1, iters + 1):
         d = O.QaryOracle(w.H, k, B=w.B, BSUM=w.BSUM, DC=w.sum_weight + 1)
-        h, p, ps, _ = d.decode_batch(llr, llrs, from_probs=False, algo=O.ALGO_FWD_BWD)
+        h, p, ps, _ = d.decode_batch(llr, llrs, from_probs=False, algo=O.ALGO_SPLIT)
         ok = ((h.astype(np.int32) @ Hs.T) == 0).all(1) & (np.minimum(margin(p), margin(ps)) > eps)
         newly = open_ & ok
         hard[newly], its[newly] = h[newly], k
