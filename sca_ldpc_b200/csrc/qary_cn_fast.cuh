@@ -166,6 +166,14 @@ struct CnFastShape {
 // different normalisation constant -- shifts all of the check's outputs uniformly, which the variable node's own
 // normalisation removes from every later message.  It survives only in the posteriors, which is why the LAST
 // iteration uses the reference's formula on the c2v the iteration before it stored (oracle algo 3 models exactly this).
+// "Own entry non-finite => +inf out" (decoder.rs:307-311) is NOT applied to the B-variables' messages: an own entry v2c[i] is
+// non-finite exactly when the variable's total[i] was, that is when its channel LLR[i] is +inf or some check finds the value
+// infeasible given the other variables' exclusions -- both persist (exclusions only grow), so total[i] stays +inf whether this
+// check adds +inf or a finite r[i] to it, every message derived from total[i] is excluded (+inf after sanitising) either way,
+// and the finite entries of every total never see a masked term.  Decisions, posteriors and every later message are
+// bit-identical to the masked computation (the oracle's algo 3 keeps the mask; tests/test_hostmodel.py and the GPU parity
+// tests compare bit for bit, priors with excluded values included); 2 x SW x Q ALU instructions per item saved.
+constexpr bool kCnMaskOwn = false;
 constexpr int kCnFirst = 1, kCnLast = 2, kCnWsum = 4, kCnRsum = 8;
 
 template <int SW, int B, int MODE>
@@ -443,7 +451,7 @@ __global__ void __launch_bounds__(kCnWarps * 32, 1) k_cn_fast(const QaryDev p, c
                     for (int i = 0; i < Q; ++i) r[i] = acc[i].get();
                 }
 #pragma unroll
-                for (int i = 0; i < Q; ++i) out[(size_t)(var * Q + i) * 32] = (a[var][i] == INF) ? INF : r[i];
+                for (int i = 0; i < Q; ++i) out[(size_t)(var * Q + i) * 32] = kCnMaskOwn ? ((a[var][i] == INF) ? INF : r[i]) : r[i];
                 if (k > 0) {  // G_k[o] = min_i x_k[i] + G_{k+1}[o + i]
                     float Gs[2 * (P > M ? P : M) * B + 2];
                     cn_conv_bwd<Q>(Gp, nk, a[var], Gs);

@@ -146,6 +146,42 @@ def test_batched_parity_with_oracle(variant, sw, cb, acc, nb, nbs, T, it):
     assert np.array_equal(w.success(b, hard), w.success(b, rh))
 
 
+@pytest.mark.parametrize("variant,sw,cb", [("kyber512", 6, 1), ("kyber768", 6, 2), ("kyber1024", 8, 1), ("kyber1024", 4, 1)])
+def test_fast_kernel_with_excluded_values(variant, sw, cb):
+    """Priors in which a third of the entries of both kinds of variable are zero (LLR +inf) on every template shape.
+    k_cn_fast does not apply "own entry non-finite => +inf out" to the B-variables' messages (kCnMaskOwn): unverified it must
+    still equal its CPU model, which applies it, bit for bit; the default path must give the reference's decisions
+    (exact-order DP) and posteriors within 1e-4 with identical inf masks."""
+    w = KyberWorkload(variant, sum_weight=sw, check_blocks=cb, accuracy=0.95, seed=11)
+    rs = np.random.RandomState(5)
+    T, Q, QS, bv, R = 40, 2 * w.B + 1, 2 * w.BSUM + 1, w.H.shape[1] - w.H.shape[0], w.H.shape[0]
+    pri = rs.dirichlet(np.ones(Q), size=(T, bv)).astype(np.float32)
+    pri[rs.rand(T, bv, Q) < 0.33] = 0.0
+    pri[..., w.B] += 1e-3
+    pri /= pri.sum(-1, keepdims=True)
+    pris = rs.dirichlet(np.ones(QS), size=(T, R)).astype(np.float32)
+    pris[rs.rand(T, R, QS) < 0.33] = 0.0
+    pris[..., w.BSUM] += 1e-3
+    pris /= pris.sum(-1, keepdims=True)
+    llr = np.stack([O.into_llr(x) for x in pri])
+    llrs = np.stack([O.into_llr(x) for x in pris])
+    for it in (1, 2, 3, 5):
+        d = QaryDecoder(w.H, it, **w.decoder_kwargs)
+        orc = O.QaryOracle(w.H, it, **w.decoder_kwargs)
+        fh, fp, fps, st = orc.decode_batch(llr, llrs, from_probs=False, algo=O.ALGO_FAST)
+        assert (st == 0).all()
+        uh, up, ups = d.min_sum_batch(llr, llrs, llr=True, verify=False)
+        assert np.array_equal(uh, fh)
+        assert np.array_equal(up, fp, equal_nan=True) and np.array_equal(ups, fps, equal_nan=True)
+        n = 8  # the reference's arithmetic on a few trials (the exact-order DP is slow on 37-value alphabets)
+        rh, rp, rps, st = orc.decode_batch(llr[:n], llrs[:n], from_probs=False, algo=O.ALGO_EXACT_DP)
+        hard, post, posts = d.min_sum_batch(llr, llrs, llr=True)
+        assert np.array_equal(hard[:n], rh)
+        assert util.same_nonfinite(post[:n], rp) and util.max_abs_diff(post[:n], rp) < TOL
+        assert util.same_nonfinite(posts[:n], rps) and util.max_abs_diff(posts[:n], rps) < TOL
+
+
+
 @pytest.mark.parametrize("variant,sw,cb", [("kyber512", 6, 1), ("kyber768", 6, 2), ("kyber1024", 8, 1),
                                            ("kyber1024", 4, 1)])
 def test_batched_api_variants(variant, sw, cb):

@@ -244,3 +244,35 @@ def test_early_termination_rounds(monkeypatch, restart_min):
         # slot-iterations launched: the compacted second round makes it fewer than the fixed-iteration decode's T * it
         work = util.hostmodel_last_work()
         assert work < T * it if restart_min == "1" else work == T * it + (never.sum() * it if verify else 0)
+
+
+@pytest.mark.parametrize("variant,sw,cb", [("kyber512", 6, 1), ("kyber768", 6, 1), ("kyber1024", 4, 1)])
+def test_fast_kernel_with_excluded_values_equals_fast_oracle_bitwise(variant, sw, cb):
+    """k_cn_fast does not apply "own entry non-finite => +inf out" to the B-variables' messages (qary_cn_fast.cuh, kCnMaskOwn):
+    an excluded value stays excluded through the variable's total either way.  The oracle's algo 3 DOES apply it
+    (decoder.rs:307-311); decisions and posteriors must agree bit for bit on priors in which a third of the entries of both
+    kinds of variable are zero (LLR +inf), for every kernel-variant schedule (1, 2, 3 and 5 iterations)."""
+    from sca_ldpc_b200 import workloads as W
+    w = W.KyberWorkload(variant, sum_weight=sw, check_blocks=cb, accuracy=0.95, seed=11)
+    rs = np.random.RandomState(5)
+    T, Q, QS, bv, R = 3, 2 * w.B + 1, 2 * w.BSUM + 1, w.H.shape[1] - w.H.shape[0], w.H.shape[0]
+    pri = rs.dirichlet(np.ones(Q), size=(T, bv)).astype(np.float32)
+    pri[rs.rand(T, bv, Q) < 0.33] = 0.0
+    pri[..., w.B] += 1e-3  # never a variable without any value
+    pri /= pri.sum(-1, keepdims=True)
+    pris = rs.dirichlet(np.ones(QS), size=(T, R)).astype(np.float32)
+    pris[rs.rand(T, R, QS) < 0.33] = 0.0
+    pris[..., w.BSUM] += 1e-3
+    pris /= pris.sum(-1, keepdims=True)
+    llr = np.stack([O.into_llr(x) for x in pri])
+    llrs = np.stack([O.into_llr(x) for x in pris])
+    assert np.isinf(llr).mean() > 0.2 and np.isinf(llrs).mean() > 0.2
+    for it in (1, 2, 3, 5):
+        d = O.QaryOracle(w.H, it, B=w.B, BSUM=w.BSUM, DC=sw + 1)
+        rc, hard, post, posts, _, fast = util.hostmodel_qary(w.H, w.B, w.BSUM, it, llr, llrs, dc=sw + 1, flags=NO_VERIFY)
+        assert rc == 0 and fast
+        for t in range(T):
+            h2, p2, ps2 = d.decode_llr(llr[t], llrs[t], algo=O.ALGO_FAST)
+            assert np.array_equal(hard[t], h2), (it, t)
+            assert np.array_equal(post[t], p2, equal_nan=True) and np.array_equal(posts[t], ps2, equal_nan=True), (it, t)
+        assert np.isinf(post).any() and np.isfinite(post).any()
