@@ -549,7 +549,7 @@ int launch_cn(scaldpc_qary *h, const QaryDev &p, int tiles, int it, int iters, u
     if (fast) {
         // persistent: one CTA of kCnWarps warps per SM, warps stride over the (tile, check) items
         const int n_items = tiles * h->R;
-        const int grid = std::max(1, std::min(h->num_sms, (n_items + kCnWarps - 1) / kCnWarps));
+        const int grid = std::max(1, std::min(h->num_sms, n_items));  // few items: a warp each on as many SMs as possible
         fast->fn[cn_mode_index(it, iters, decide)]<<<grid, kCnWarps * 32, fast->smem, st>>>(p, n_items);
         ++h->launches;
     } else if (exact && !force_generic && h->fast_sw) {
@@ -1349,7 +1349,12 @@ static int decode_batch(scaldpc_qary *h, int T, const PriorSrc &src, int8_t *har
     // prior vectors: 8 chunks keep the PCIe link busy behind the decode; observations are ~35x smaller, so two large
     // chunks (better-filled persistent kernels) are enough to overlap the copies
     int chunk = T;
-    if (T >= 4096) chunk = src.observed ? (T + 1) / 2 : std::max(1024, (T + 7) / 8);
+    static const int n_prior_chunks = [] {  // experiment knob: SCALDPC_QARY_CHUNKS=<n> (default 8)
+        const char *e = getenv("SCALDPC_QARY_CHUNKS");
+        const int v = e ? atoi(e) : 0;
+        return v >= 1 && v <= 64 ? v : 8;
+    }();
+    if (T >= 4096) chunk = src.observed ? (T + 1) / 2 : std::max(512, (T + n_prior_chunks - 1) / n_prior_chunks);
     chunk = (chunk + 31) / 32 * 32;
     const int nchunks = (T + chunk - 1) / chunk;
     if ((rc = ensure_workspace(h, chunk / 32, want_post))) return rc;

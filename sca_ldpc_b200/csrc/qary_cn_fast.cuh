@@ -188,7 +188,9 @@ __global__ void __launch_bounds__(kCnWarps * 32, 1) k_cn_fast(const QaryDev p, c
     constexpr int P = SW / 2, M = SW - P;  // left / right variables of the split chain (see the header comment)
     const float INF = SC_INF;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int gw = blockIdx.x * kCnWarps + warp, nw = gridDim.x * kCnWarps;
+    // warp-major numbering: consecutive items go to different CTAs, so a batch with fewer items than resident warps (one tile:
+    // the reference-shaped single decode) spreads over the SMs one warp per scheduler instead of filling a few SMs
+    const int gw = warp * gridDim.x + blockIdx.x, nw = gridDim.x * kCnWarps;
 #ifdef SCALDPC_HOST_MODEL
     float hbuf[Sh::NB];  // the host model stages per thread
 #define SC_BUF(idx) hbuf[(idx)]
