@@ -171,7 +171,7 @@ __global__ void __launch_bounds__(kBpCnWarpsMax * 32) k_bp_cn(const BpDev p, con
 {
     SCALDPC_DYN_SMEM(float, smem);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
-    const int gw = blockIdx.x * wpc + warp, nw = gridDim.x * wpc;
+    const int gw = warp * gridDim.x + blockIdx.x, nw = gridDim.x * wpc;  // warp-major: consecutive items on different SMs
     const int stride = p.dc_max * 32;                // floats per per-warp array
     float *wbase = smem + (size_t)warp * 3 * stride;  // stage[2], P
     float *P = wbase + 2 * stride + lane;
@@ -486,7 +486,7 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn(const BpDev p, const 
                                                            const int cls)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
-    const int gw = blockIdx.x * wpc + warp, nw = gridDim.x * wpc;
+    const int gw = blockIdx.x * wpc + warp, nw = gridDim.x * wpc;  // block-major: a CTA's warps share the descriptor / offset lines (warp-major measured slower here)
     const int nv = v_hi - v_lo;
     const int step_t = nw / nv, step_j = nw - step_t * nv;  // item -> item + nw without a division per item
 
@@ -613,7 +613,7 @@ __global__ void __launch_bounds__(kBpVnWarps * 32) k_bp_vn_pipe(const BpDev p, c
     constexpr int S = BpVnPipe<DMAX>::stages;
     extern __shared__ __align__(128) float sc_vn_ring[];  // [warp][stage][DMAX][32]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
-    const int gw = blockIdx.x * wpc + warp, nw = gridDim.x * wpc;
+    const int gw = blockIdx.x * wpc + warp, nw = gridDim.x * wpc;  // block-major: a CTA's warps share the descriptor / offset lines (warp-major measured slower here)
     const int nv = v_hi - v_lo;
     const int step_t = nw / nv, step_j = nw - step_t * nv;
     float *ring = sc_vn_ring + (size_t)warp * S * DMAX * 32 + lane;
