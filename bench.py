@@ -514,12 +514,14 @@ def run_ours(args, kind, wl, iters, cfg):
         dom, sec = (k_cn, k_vn) if cn_ms >= vn_ms else (k_vn, k_cn)
         roofline = {
             # the ROOFLINE is HBM bandwidth (irregular gather + small (min,+) convolutions); what ncu says
-            # actually limits the q-ary check pass is instruction issue (profiles/r1n_ncu_full_k512.txt), see `limiter`
+            # actually limits the q-ary check pass is instruction issue (profiles/r2zn_ncu_cn_fast_k512.txt), see `limiter`
             "bound": "hbm", "kernel": dom["kernel"],
             "achieved": dom["achieved"], "peak": peak, "unit": "GB/s", "frac": dom["frac"], "traffic": None,
             "peak_source": peak_src, "ms_per_launch": dom["ms_per_launch"],
             "algorithmic_bytes_per_launch": dom["algorithmic_bytes_per_launch"],
-            "limiter": ("issue (FADD2 + FMNMX3 are half-rate pipes; ncu: issue active 55 %, math-pipe throttle)"
+            "limiter": ("issue (two warps per scheduler at 255 registers; ncu profiles/r2zn_ncu_cn_fast_k512.txt: issue active 55 %, "
+                         "dispatch stall + math-pipe throttle, ~1 870 warp-instructions per item of which ~1 530 are the FADD2 / "
+                         "FMNMX3 the (min,+) candidates need)"
                         if kind == "qary" and special else
                         ("shared-memory latency, one warp per scheduler" if kind == "qary" else
                          "latency of the scattered column gather (ncu: long_scoreboard)")),

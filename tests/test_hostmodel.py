@@ -276,3 +276,35 @@ def test_fast_kernel_with_excluded_values_equals_fast_oracle_bitwise(variant, sw
             assert np.array_equal(hard[t], h2), (it, t)
             assert np.array_equal(post[t], p2, equal_nan=True) and np.array_equal(posts[t], ps2, equal_nan=True), (it, t)
         assert np.isinf(post).any() and np.isfinite(post).any()
+
+
+def test_fast_kernel_negative_sum_coefficient_equals_fast_oracle_bitwise():
+    """H = [H' | -I]: the sum-variable enters its check with coefficient -1 (its vectors are mirrored in the check frame,
+    decoder.rs:164-172).  Never the case for the reference's own matrices, but the fast kernel keeps the branch -- and the
+    table it parks in the sum-variable's slots is stored in the CHECK's frame -- so it is compared with its CPU model bit for
+    bit for every kernel-variant schedule, excluded values included."""
+    from sca_ldpc_b200 import workloads as W
+    w = W.KyberWorkload("kyber768", sum_weight=6, check_blocks=1, accuracy=0.95, seed=12)
+    H = w.H.copy()
+    R = H.shape[0]
+    bv = H.shape[1] - R
+    H[:, bv:] = -H[:, bv:]
+    rs = np.random.RandomState(9)
+    T, Q, QS = 2, 2 * w.B + 1, 2 * w.BSUM + 1
+    pri = rs.dirichlet(np.ones(Q), size=(T, bv)).astype(np.float32)
+    pris = rs.dirichlet(np.ones(QS), size=(T, R)).astype(np.float32)
+    pris[rs.rand(T, R, QS) < 0.2] = 0.0
+    pris[..., w.BSUM] += 1e-3
+    pris /= pris.sum(-1, keepdims=True)
+    llr = np.stack([O.into_llr(x) for x in pri])
+    llrs = np.stack([O.into_llr(x) for x in pris])
+    for it in (1, 2, 3, 5):
+        d = O.QaryOracle(H, it, B=w.B, BSUM=w.BSUM, DC=7)
+        rc, hard, post, posts, _, fast = util.hostmodel_qary(H, w.B, w.BSUM, it, llr, llrs, dc=7, flags=NO_VERIFY)
+        assert rc == 0 and fast
+        for t in range(T):
+            h2, p2, ps2 = d.decode_llr(llr[t], llrs[t], algo=O.ALGO_FAST)
+            assert np.array_equal(hard[t], h2), (it, t)
+            assert np.array_equal(post[t], p2, equal_nan=True) and np.array_equal(posts[t], ps2, equal_nan=True), (it, t)
+            h1, p1, ps1 = d.decode_llr(llr[t], llrs[t], algo=O.ALGO_EXACT_DP)
+            assert util.same_nonfinite(posts[t], ps1) and util.max_abs_diff(posts[t], ps1) < 1e-4
