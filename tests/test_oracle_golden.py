@@ -76,8 +76,9 @@ def test_decode_doctest_seed1():
 @pytest.mark.parametrize("cb", [1, 2])
 def test_kyber768_fixture(cb):
     """DecoderSpecial (decoder_special.rs:471-617) on reference-produced Kyber-768 priors: the enumeration oracle
-    reproduces the stored outputs; the exact-order DP is bit-identical; forward/backward gives identical hard
-    decisions and posteriors within 1e-4 (the north-star tolerance)."""
+    reproduces the stored outputs; the exact-order DP is bit-identical; forward/backward -- plain (algo 2), split around
+    the sum-variable (algo 4, the fast kernel's order of additions) and split with the sum-variables' messages staying home
+    (algo 3, the fast kernel's schedule) -- gives identical hard decisions and posteriors within 1e-4 (the north-star tolerance)."""
     z = util.load(f"kyber768_cb{cb}.npz")
     H = util.dense(z)
     meta = json.loads(str(z["meta"]))
@@ -85,11 +86,11 @@ def test_kyber768_fixture(cb):
         it = int(z["iterations"][i])
         d = O.QaryOracle(H, it, B=2, BSUM=12, DC=7)
         llr, llrs = O.into_llr(z["channel_output"][i]), O.into_llr(z["channel_output_sum"][i])
-        algos = [O.ALGO_EXACT_DP, O.ALGO_FWD_BWD, O.ALGO_FAST] + ([O.ALGO_ENUMERATE] if (cb == 1 and i == 0) else [])
+        algos = [O.ALGO_EXACT_DP, O.ALGO_FWD_BWD, O.ALGO_SPLIT, O.ALGO_FAST] + ([O.ALGO_ENUMERATE] if (cb == 1 and i == 0) else [])
         for algo in algos:
             hard, post, posts = d.decode_llr(llr, llrs, algo=algo)
             assert np.array_equal(hard, z["hard"][i]), (cb, i, algo)
-            if algo in (O.ALGO_FWD_BWD, O.ALGO_FAST):
+            if algo in (O.ALGO_FWD_BWD, O.ALGO_SPLIT, O.ALGO_FAST):
                 assert util.same_nonfinite(post, z["post"][i]) and util.same_nonfinite(posts, z["post_sum"][i])
                 assert util.max_abs_diff(post, z["post"][i]) < 1e-4
                 assert util.max_abs_diff(posts, z["post_sum"][i]) < 1e-4
@@ -198,3 +199,33 @@ def test_special_oracle_equals_pinned_generic_oracle_when_alphabets_coincide(B, 
     # and the two are not trivially equal to the priors' decisions: the checks did move something
     prior_dec = np.concatenate([pri, pris], axis=1).argmax(-1) - B
     assert (sh != prior_dec).any()
+
+
+def test_split_forward_backward_equals_enumeration_in_exact_arithmetic():
+    """cn_split (oracle algo 4: the order of additions of the GPU fast kernel since round 2) is the same minimum over the same
+    configurations as the reference's enumeration (decoder_special.rs:531-554), associated differently.  On priors whose LLRs
+    are small integers every f32 sum is exact, so the two must agree BIT FOR BIT -- hard decisions and posteriors of both kinds
+    of variable -- for even and odd sum_weight, three alphabets, a negative coefficient, excluded values and 1..3 iterations."""
+    rs = np.random.RandomState(21)
+    for sw, B, R, bv in ((2, 1, 4, 6), (3, 2, 5, 9), (4, 1, 4, 8), (5, 1, 3, 9), (6, 1, 3, 9)):
+        Q, BS = 2 * B + 1, sw * B
+        QS = 2 * BS + 1
+        Hp = np.zeros((R, bv), np.int8)
+        for r in range(R):
+            cols = rs.choice(bv, sw, replace=False)
+            Hp[r, cols] = rs.choice([-1, 1], sw)
+        H = np.concatenate([Hp, np.eye(R, dtype=np.int8)], axis=1)
+        H[0, bv] = -1  # one sum-variable enters its check mirrored
+        llr = rs.randint(0, 9, size=(bv, Q)).astype(np.float32)
+        llr[rs.rand(bv, Q) < 0.15] = np.inf
+        llr[:, B] = 0.0
+        llrs = rs.randint(0, 9, size=(R, QS)).astype(np.float32)
+        llrs[rs.rand(R, QS) < 0.15] = np.inf
+        llrs[:, BS] = 0.0
+        for it in (1, 2, 3):
+            d = O.QaryOracle(H, it, B=B, BSUM=BS, DC=sw + 1)
+            h0, p0, ps0 = d.decode_llr(llr, llrs, algo=O.ALGO_ENUMERATE)
+            for algo in (O.ALGO_EXACT_DP, O.ALGO_FWD_BWD, O.ALGO_SPLIT):
+                h, p, ps = d.decode_llr(llr, llrs, algo=algo)
+                assert np.array_equal(h, h0), (sw, B, it, algo)
+                assert np.array_equal(p, p0, equal_nan=True) and np.array_equal(ps, ps0, equal_nan=True), (sw, B, it, algo)
