@@ -8,4 +8,4 @@ timeout 900 bash -c "$(declare -f run); N=$N; run 29512 --steps 10 --warmup 3" >
 if [ "$N" = "2" ]; then
 timeout 900 bash -c "$(declare -f run); N=$N; run 29513 --impl reference --steps 2 --warmup 1" > $out/${tag}_bench_reference_n$N.json 2> $out/${tag}_bench_reference_n$N.err; echo "exit $?" >> $out/${tag}_bench_reference_n$N.err
 fi
-for f in $out/${tag}_bench_*_n$N.json; do echo $f; head -c 700 $f; echo; done; tail -3 $out/${tag}_bench_*_n$N.err
+for f in $out/${tag}_bench_*_n$N.json; do echo $f; head -c 700 $f; echo; done; tail -q -n 3 $out/${tag}_bench_*_n$N.err
