@@ -1,8 +1,10 @@
 """Test-time shim: import the reference's *Python* helpers (simulate.kyber, simulate.make_code, ...) from
 /root/reference when it is present (it is in the build container, NOT on the GPU box).
 
-Used only by tests/golden/make_golden.py (fixture generation) and tests/test_reference_doctests.py (both skip
-when /root/reference is absent).  Nothing here is on the product path.
+Used only by tests/golden/make_golden.py (fixture generation) and by the tests that compare this repository's host-side
+restatements with the reference's own Python functions (tests/test_workloads.py, tests/test_oracle_golden.py,
+tests/test_hostmodel_bp.py); all of them skip those comparisons when /root/reference is absent.  Nothing here is on the
+product path.
 
 The reference modules import three things that are not installed here:
   * coloredlogs            (simulate/utils.py:7)            -> empty stub
