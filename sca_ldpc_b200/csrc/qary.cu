@@ -602,7 +602,15 @@ int launch_vn(scaldpc_qary *h, const QaryDev &p, int tiles, bool last, unsigned 
 int load_priors(scaldpc_qary *h, const float *in, float *out, int T, int tiles, int rows, int q, bool is_llr,
                 cudaStream_t st, int *status, const int *map)
 {
-    const int rpb = std::max(1, 256 / q);
+    int rpb = std::max(1, 256 / q);
+    // Few tiles (the reference-shaped single decode, the re-decode of the flagged trials): the kernel's time is the serial chain
+    // of division + logarithm a thread walks through, rpb / 8 rows of q entries -- cut the rows into more, smaller CTAs until
+    // the machine has a couple of CTAs per SM.  Large batches keep 256 / q rows per CTA (fewer, fuller CTAs).
+    const long long want = 2LL * h->num_sms;
+    if ((long long)tiles * ((rows + rpb - 1) / rpb) < want) {
+        const int per_tile = (int)((want + tiles - 1) / tiles);
+        rpb = std::max(1, std::min(rpb, (rows + per_tile - 1) / per_tile));
+    }
     const int pitch = (rpb * q) | 1;
     dim3 grid((rows + rpb - 1) / rpb, tiles), block(32, kTrRows);
     k_load_priors<<<grid, block, (size_t)32 * pitch * sizeof(float), st>>>(in, out, T, rows, q, rpb, is_llr, status,
