@@ -762,7 +762,11 @@ static int bp_decode_impl(scaldpc_bp *h, int T, const uint8_t *synd, const doubl
         // polling = one 4-byte D2H + a stream sync (the GPU idles for the round trip, ~30 us): every iteration while most
         // trials converge (the first four) or while the batch is large enough to hide it, then every 4th / 8th --
         // kernels launched for tiles that have retired meanwhile exit at once
-        if (early && !last && (it <= 4 || cur_tiles >= 512 || (it <= 16 ? it % 4 == 0 : it % 8 == 0))) {
+        // a batch of a few tiles (the reference-shaped single decode, hqc.py:694-708) is bound by exactly these round trips: it
+        // polls after iterations 3 and 5 instead of 1, 2, 3, 4 -- the launches of a converged tile exit at once, a sync costs more
+        const bool poll = cur_tiles <= 4 ? (it == 3 || it == 5 || (it >= 8 && (it <= 16 ? it % 4 == 0 : it % 8 == 0)))
+                                         : (it <= 4 || cur_tiles >= 512 || (it <= 16 ? it % 4 == 0 : it % 8 == 0));
+        if (early && !last && poll) {
             // the count comes home through a store into page-locked host memory, not through the copy engine: a 4-byte
             // copy would queue behind the early copy of the finished rows (below) and stall the stragglers for its duration
             k_bp_publish<<<1, 1, 0, st>>>(h->d_counts + it, h->h_pin);
