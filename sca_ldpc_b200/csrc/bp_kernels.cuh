@@ -784,6 +784,7 @@ __global__ void __launch_bounds__(256) k_bp_syndrome(const BpDev p)
         const int *rp = p.row_ptr + (size_t)g * p.g_rp + check;
         const int *col = p.col + (size_t)g * p.g_e;
         const int e0 = __ldg(rp), e1 = __ldg(rp + 1);
+#pragma unroll 8  // eight (index, word) load pairs in flight: the rolled loop waited for every word before the next index
         for (int e = e0; e < e1; ++e) par ^= dec[__ldg(col + e)];
         bad = par;
         if (p.nrows) {  // trials for which this check is inactive cannot fail it
